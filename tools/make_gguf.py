@@ -1,0 +1,153 @@
+#!/usr/bin/env python
+"""Write a random-init GGUF v3 file of a llama-arch model (TEST TOOLING, not product code).
+
+There is no network for checkpoints, so every model in BASELINE.json's configs is a seeded random
+initialisation of the named architecture.  Tensor names and hyper-parameter keys are the ones the
+reference loader reads (/root/reference/llama.cpp:2227-2276 hparams, :351-403 tensor tables,
+:2756-2812 llama tensors).  The vocabulary is synthetic and character-level (see `synth_vocab`), so
+neither this script nor the tests need the reference's models/ggml-vocab-*.gguf.
+
+Two weight flavours:
+  iid     every 2-D weight ~ N(0, 0.02^2): target and draft disagree, acceptance ~ 0 (exercises cancel).
+  bigram  token_embd[t] = g_t, output[pi(t)] = g_t for a fixed permutation pi, block weights scaled by
+          --eps so the residual stream stays ~ g_t: both models predict pi(last token), so drafts get
+          accepted.  --agree A makes a draft (built with --draft-perturb) agree with pi on a fraction A.
+
+Quantisation: tensors are written as F32 and then passed through the reference's own
+`quantize --pure` (oracle/_ref/quantize) by `--quant q8_0|q4_0|q4_k` so that block contents come from
+the reference quantiser, not from a re-implementation.
+"""
+import argparse
+import os
+import subprocess
+import sys
+
+import numpy as np
+import gguf
+
+N_SPECIAL = 3          # <unk> <s> </s>
+N_BYTE = 256           # <0x00>..<0xFF>
+CHAR0 = N_SPECIAL + N_BYTE   # first printable-character token (space == U+2581)
+
+
+def synth_vocab(n_vocab):
+    """3 specials, 256 byte tokens, 95 single printable ASCII characters, then filler pieces that no
+    text can produce.  With it the reference SPM tokenizer (/root/reference/llama.cpp:5970-6110) maps a
+    prompt one character -> one token, so tests know the ids without running a tokenizer."""
+    toks, scores, types = [], [], []
+    for t, ty in (("<unk>", 2), ("<s>", 3), ("</s>", 3)):
+        toks.append(t); scores.append(0.0); types.append(ty)
+    for b in range(256):
+        toks.append("<0x%02X>" % b); scores.append(0.0); types.append(6)
+    for c in range(0x20, 0x7F):
+        toks.append("▁" if c == 0x20 else chr(c)); scores.append(-1.0); types.append(1)
+    i = 0
+    while len(toks) < n_vocab:
+        toks.append("▁§%d§" % i); scores.append(-1000.0 - i); types.append(1)
+        i += 1
+    return toks[:n_vocab], scores[:n_vocab], types[:n_vocab]
+
+
+def text_to_ids(text):
+    """ids the reference tokenizer yields for printable-ASCII `text` with the synthetic vocab
+    (BOS, then the SPM space prefix, then one token per character)."""
+    return [1, CHAR0] + [CHAR0 + (ord(c) - 0x20) for c in text]
+
+
+def perm(n_vocab, seed):
+    return np.random.default_rng(seed).permutation(n_vocab)
+
+
+def build(args):
+    rng = np.random.default_rng(args.seed)
+    E, L, H, HKV, FF, V = args.n_embd, args.n_layer, args.n_head, args.n_head_kv, args.n_ff, args.n_vocab
+    hd = E // H
+    w = gguf.GGUFWriter(args.out if args.quant == "f32" else args.out + ".f32.gguf", "llama")
+    w.add_name(args.name)
+    w.add_context_length(args.n_ctx_train)
+    w.add_embedding_length(E)
+    w.add_block_count(L)
+    w.add_feed_forward_length(FF)
+    w.add_rope_dimension_count(hd)
+    w.add_head_count(H)
+    w.add_head_count_kv(HKV)
+    w.add_layer_norm_rms_eps(1e-5)
+    w.add_file_type(0)
+    toks, scores, types = synth_vocab(V)
+    w.add_tokenizer_model("llama")
+    w.add_token_list(toks)
+    w.add_token_scores(scores)
+    w.add_token_types(types)
+    w.add_bos_token_id(1)
+    w.add_eos_token_id(2)
+    w.add_unk_token_id(0)
+
+    def mat(rows, cols, std):
+        return (rng.standard_normal((rows, cols), dtype=np.float32) * np.float32(std))
+
+    if args.flavour == "bigram":
+        g = rng.standard_normal((V, E), dtype=np.float32)
+        g /= np.linalg.norm(g, axis=1, keepdims=True)
+        p = perm(V, 7)
+        if args.agree < 1.0:   # a draft that disagrees with the target on a deterministic token subset
+            p2 = perm(V, 8)
+            flip = np.random.default_rng(9).random(V) >= args.agree
+            p = np.where(flip, p2, p)
+        emb = (g * np.float32(args.emb_scale)).astype(np.float32)
+        out = np.zeros((V, E), dtype=np.float32)
+        out[p] = g * np.float32(args.emb_scale)
+        std = 0.02 * args.eps
+    else:
+        emb = mat(V, E, 0.02)
+        out = mat(V, E, 0.02)
+        std = 0.02
+    w.add_tensor("token_embd.weight", emb)
+    for il in range(L):
+        pre = "blk.%d." % il
+        w.add_tensor(pre + "attn_norm.weight", np.ones(E, dtype=np.float32))
+        w.add_tensor(pre + "attn_q.weight", mat(E, E, std))
+        w.add_tensor(pre + "attn_k.weight", mat(hd * HKV, E, std))
+        w.add_tensor(pre + "attn_v.weight", mat(hd * HKV, E, std))
+        w.add_tensor(pre + "attn_output.weight", mat(E, E, std))
+        w.add_tensor(pre + "ffn_norm.weight", np.ones(E, dtype=np.float32))
+        w.add_tensor(pre + "ffn_gate.weight", mat(FF, E, std))
+        w.add_tensor(pre + "ffn_down.weight", mat(E, FF, std))
+        w.add_tensor(pre + "ffn_up.weight", mat(FF, E, std))
+    w.add_tensor("output_norm.weight", np.ones(E, dtype=np.float32))
+    w.add_tensor("output.weight", out)
+    w.write_header_to_file()
+    w.write_kv_data_to_file()
+    w.write_tensors_to_file()
+    w.close()
+    if args.quant != "f32":
+        q = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle", "_ref", "quantize")
+        r = subprocess.run([q, "--pure", args.out + ".f32.gguf", args.out, args.quant.upper()],
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout)
+            raise SystemExit("reference quantize failed")
+        os.unlink(args.out + ".f32.gguf")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", required=True)
+    ap.add_argument("--name", default="random-llama")
+    ap.add_argument("--n-layer", type=int, default=2)
+    ap.add_argument("--n-embd", type=int, default=512)
+    ap.add_argument("--n-head", type=int, default=8)
+    ap.add_argument("--n-head-kv", type=int, default=8)
+    ap.add_argument("--n-ff", type=int, default=1408)
+    ap.add_argument("--n-vocab", type=int, default=32000)
+    ap.add_argument("--n-ctx-train", type=int, default=2048)
+    ap.add_argument("--quant", default="q8_0", choices=["f32", "q8_0", "q4_0", "q4_k"])
+    ap.add_argument("--flavour", default="iid", choices=["iid", "bigram"])
+    ap.add_argument("--eps", type=float, default=0.25)
+    ap.add_argument("--emb-scale", type=float, default=1.0)
+    ap.add_argument("--agree", type=float, default=1.0)
+    ap.add_argument("--seed", type=int, default=1234)
+    build(ap.parse_args())
+
+
+if __name__ == "__main__":
+    main()
