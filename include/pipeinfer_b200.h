@@ -1,0 +1,95 @@
+/*
+ * pipeinfer_b200.h -- C ABI of libpipeinfer_b200.so, operator level.
+ *
+ * B200 (sm_100a) implementation of the arithmetic on PipeInfer's asynchronous pipelined speculation path.  Each
+ * entry point names the reference interface it replaces (paths relative to the reference repository,
+ * AutonomicPerfectionist/PipeInfer).  Plain C types only; "dev" pointers are CUDA device pointers on the device
+ * passed to pib_init, "host" pointers are ordinary host memory.  All functions return PIB_OK (0) or a negative
+ * PIB_ERR_* code; pib_last_error() gives the message.  There is no CPU fallback: without a CUDA device every entry
+ * point fails with PIB_ERR_CUDA.
+ *
+ * The model/runtime level (llama_decode, llama_batch, llama_kv_cache_seq_*, ggml_mpi_*) is in pipeinfer_llama.h.
+ */
+#ifndef PIPEINFER_B200_H
+#define PIPEINFER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PIB_OK            0
+#define PIB_ERR_CUDA     (-1)
+#define PIB_ERR_ARG      (-2)
+#define PIB_ERR_NOMEM    (-3)
+#define PIB_ERR_UNSUPP   (-4)
+
+/* ggml type ids of the weight formats on the path (ggml.h:305-333) */
+#define PIB_TYPE_F32   0
+#define PIB_TYPE_Q4_0  2
+#define PIB_TYPE_Q8_0  8
+#define PIB_TYPE_Q4_K 12
+
+#define PIB_MAX_BATCH 16          /* verification batch handled by the dequant-GEMV path (north_star: batch 1-16) */
+
+typedef struct pib_weight pib_weight;   /* a weight matrix repacked into HBM (layout private to the library) */
+typedef void * pib_stream;              /* cudaStream_t, or NULL for the legacy default stream */
+
+/* ---- library ------------------------------------------------------------------------------------------------- */
+/* Select the device and upload the fp16 exp/silu/gelu tables (the reference builds them in ggml_init, ggml.c:2185). */
+int          pib_init(int device);
+const char * pib_last_error(void);
+int          pib_device_sm_count(void);
+void *       pib_dev_alloc(size_t bytes);                         /* cudaMalloc; NULL on failure */
+void         pib_dev_free(void * dev);
+int          pib_memcpy_h2d(void * dev, const void * host, size_t bytes, pib_stream s);
+int          pib_memcpy_d2h(void * host, const void * dev, size_t bytes, pib_stream s);
+int          pib_stream_sync(pib_stream s);
+
+/* ---- weights ------------------------------------------------------------------------------------------------- */
+/* Upload an [N][K] matrix given in the reference's block layout (block_q4_0 / block_q8_0 / block_q4_K rows,
+ * ggml-quants.h:10-15, 42-47, 116-122) and repack it for the GEMV kernels.  Layout-only: no value changes.
+ * Replaces: the mmap'ed tensor data that ggml_compute_forward_mul_mat reads as src0 (ggml.c:9388). */
+pib_weight * pib_weight_upload(int type, const void * host_blocks, int64_t N, int64_t K);
+/* Same, for blocks that are already in device memory (used by the synthetic-model generator). */
+pib_weight * pib_weight_from_device(int type, const void * dev_blocks, int64_t N, int64_t K);
+void         pib_weight_free(pib_weight * w);
+size_t       pib_weight_bytes(const pib_weight * w);             /* algorithmic bytes: N * K * bits-per-weight / 8 */
+/* Copy row `row` back out in the reference block layout (inverse of the repack; for round-trip tests). */
+int          pib_weight_row_blocks(const pib_weight * w, int64_t row, void * host_blocks_out);
+
+/* ---- K2: activation quantisation ------------------------------------------------------------------------------ */
+/* Bytes of the device buffer that holds `b` quantised activation rows of length K for weights of `wtype`. */
+size_t pib_act_bytes(int wtype, int64_t K, int b);
+/* x_dev float [b][K] -> act_dev.  Q8_0 blocks for Q4_0/Q8_0 weights, Q8_K super-blocks for Q4_K weights, with the
+ * rounding of the reference's x86 build.  Replaces: quantize_row_q8_0 (ggml-quants.c:632, AVX2 branch :701-760) and
+ * quantize_row_q8_K (ggml-quants.c:2329), called from the INIT phase of mul_mat (ggml.c:9493-9509). */
+int pib_quantize_act(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, pib_stream s);
+/* Fused row norm -> * weight -> quantise.  norm_kind 1 = RMSNorm (ggml.c:9028 + ggml_mul, llama.cpp:3590-3598).
+ * xnorm_dev (optional, may be NULL) receives the normalised float rows. */
+int pib_norm_quantize_act(int wtype, int norm_kind, const float * x_dev, const float * norm_w_dev, float eps, int b,
+                          int64_t K, void * act_dev, float * xnorm_dev, pib_stream s);
+/* Copy a quantised activation buffer back in the reference's block layout (block_q8_0 / block_q8_K rows). */
+int pib_act_to_blocks(int wtype, const void * act_dev, int b, int64_t K, void * host_blocks_out);
+
+/* ---- K1: quantised matmul at verification batch 1..16 ---------------------------------------------------------- */
+/* y_dev float [b][N] = W[N][K] . act (b rows).  Integer block dot products, fp16 block scales, fp32 accumulation.
+ * Replaces: ggml_compute_forward_mul_mat (ggml.c:9388) with ggml_vec_dot_q4_0_q8_0 / q8_0_q8_0 / q4_K_q8_K
+ * (ggml-quants.c:2426, 3521, 5216).  `variant`: 0 = default (fastest available), 1 = warp-per-row dp4a kernel,
+ * 2 = TMA-staged tensor-core kernel. */
+int pib_gemv(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, pib_stream s);
+/* Host-buffer convenience used by the parity tests and the end-to-end timing: x_host float [b][K] -> y_host [b][N];
+ * includes the H2D copy of x, quantisation, GEMV and the D2H copy of y. */
+int pib_mul_mat_host(const pib_weight * w, const float * x_host, int b, float * y_host, int variant);
+
+/* ---- K3: embedding rows ---------------------------------------------------------------------------------------- */
+/* out_dev float [n][K] = dequantised rows `ids` of W.  Replaces: ggml_compute_forward_get_rows_q (ggml.c:10161) with
+ * dequantize_row_q4_0 / q8_0 / q4_K (ggml-quants.c:1074, 1168, 1917). */
+int pib_get_rows(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, pib_stream s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -378,10 +378,9 @@ void po_rope(float * x, int n_head, int head_dim, int n_dims, int pos, int mode,
                     theta_base *= theta_scale;
                     const int   i0 = ib * n_dims + ic / 2;
                     const float x0 = v[i0], x1 = v[i0 + n_dims / 2];
-                    /* the reference is compiled with gcc's default -ffp-contract=fast: a*b - c*d becomes
-                     * fma(a, b, -(c*d)) / fma(a, b, c*d) on FMA hardware; written out here (checked against _ref). */
-                    v[i0]              = fmaf(x0, cos_theta, -(x1 * sin_theta));
-                    v[i0 + n_dims / 2] = fmaf(x0, sin_theta, x1 * cos_theta);
+                    /* the reference Makefile builds with -std=c11 (ISO mode => -ffp-contract=off): no fused ops here */
+                    v[i0]              = x0 * cos_theta - x1 * sin_theta;
+                    v[i0 + n_dims / 2] = x0 * sin_theta + x1 * cos_theta;
                 }
             }
         }

@@ -1,0 +1,209 @@
+// act_quant.cu -- activation quantisation (K2), fused with the producer that precedes each matmul (K4 / K8).
+//
+// The reference's CPU matmul first quantises every activation row to the weight type's "vec_dot type" (reference
+// ggml.c:9493-9509): Q8_0 blocks for Q4_0 / Q8_0 weights (ggml-quants.c:632; on x86 the AVX2 branch :701-760:
+// d = max|x| / 127 stored as fp16, q = round-half-even(x * (127 / max|x|))) and Q8_K super-blocks for Q4_K weights
+// (ggml-quants.c:2329-2363: iscale = -128 / (signed value of the first max-|x| element), q = min(127, rne(iscale*x)),
+// d = 1 / iscale, 16-wide bsums).  Greedy parity needs exactly this integer arithmetic, so it is reproduced bit for
+// bit; only the layout differs (planes instead of blocks, see pib_act_layout in pib_common.cuh).
+//
+// One CTA per token row.  Prologues (template PRO):
+//   PRO_PLAIN     v = x
+//   PRO_RMSNORM   v = (x * 1/sqrtf(mean(x^2) + eps)) * w        (ggml.c:9028 with the double accumulator, then ggml_mul)
+//   PRO_SILU_MUL  v = silu_f16lut(x) * x2                        (ggml.c:1490 table look-up, then ggml_mul; llama.cpp:3680)
+//   PRO_GELU      v = gelu_f16lut(x)                             (ggml.c:1433; falcon MLP)
+#include "pib_common.cuh"
+
+enum { PRO_PLAIN = 0, PRO_RMSNORM = 1, PRO_SILU_MUL = 2, PRO_GELU = 3 };
+
+#define AQ_THREADS 256
+
+template <int PRO>
+__device__ __forceinline__ float aq_value(const float * __restrict__ xr, const float * __restrict__ x2r, float scale,
+                                          const uint16_t * __restrict__ lut, int64_t i) {
+    const float x = xr[i];
+    if (PRO == PRO_RMSNORM) return __fmul_rn(__fmul_rn(x, scale), x2r[i]);
+    if (PRO == PRO_SILU_MUL) return __fmul_rn(pib_h2f(lut[pib_f2h(x)]), x2r[i]);
+    if (PRO == PRO_GELU) return pib_h2f(lut[pib_f2h(x)]);
+    return x;
+}
+
+template <bool Q8K, int PRO>
+__global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * __restrict__ x, const float * __restrict__ x2,
+                                                               int x2_per_row, float eps, int64_t K,
+                                                               int8_t * __restrict__ qs, float * __restrict__ dplane,
+                                                               void * __restrict__ bsplane, float * __restrict__ vout,
+                                                               const uint16_t * __restrict__ lut) {
+    const int     row  = blockIdx.x;
+    const float * xr   = x + (size_t) row * K;
+    const float * x2r  = x2 ? (x2_per_row ? x2 + (size_t) row * K : x2) : nullptr;
+    const int     lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int     nwarp = AQ_THREADS / 32;
+
+    float scale = 1.0f;
+    if (PRO == PRO_RMSNORM) {
+        __shared__ double red[AQ_THREADS / 32];
+        __shared__ float  s_scale;
+        double            s = 0.0;
+        for (int64_t i = threadIdx.x; i < K; i += AQ_THREADS) {
+            const float v = xr[i];
+            s += (double) __fmul_rn(v, v);
+        }
+        s = warp_sum_d(s);
+        if (lane == 0) red[warp] = s;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int w = 0; w < nwarp; w++) t += red[w];
+            const float mean = (float) (t / (double) K);
+            s_scale          = 1.0f / sqrtf(mean + eps);
+        }
+        __syncthreads();
+        scale = s_scale;
+    }
+
+    if (!Q8K) {
+        // one warp per 32-element block, lane == element
+        const int64_t nb = K / PIB_QK;
+        for (int64_t blk = warp; blk < nb; blk += nwarp) {
+            const int64_t i    = blk * PIB_QK + lane;
+            const float   v    = aq_value<PRO>(xr, x2r, scale, lut, i);
+            const float   amax = warp_max(fabsf(v));
+            const float   d    = amax / 127.f;
+            const float   id   = (amax != 0.0f) ? 127.f / amax : 0.0f;
+            int           q    = __float2int_rn(__fmul_rn(v, id));
+            q                  = max(-128, min(127, q));
+            qs[(size_t) row * K + i] = (int8_t) q;
+            if (vout) vout[(size_t) row * K + i] = v;
+            int sum = q;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            if (lane == 0) {
+                dplane[(size_t) row * nb + blk]            = pib_h2f(pib_f2h(d));   // the reference stores d as fp16
+                ((int32_t *) bsplane)[(size_t) row * nb + blk] = sum;
+            }
+        }
+    } else {
+        // one warp per 256-element super-block, lane owns 8 consecutive elements
+        const int64_t nsb = K / PIB_QK_K;
+        for (int64_t sb = warp; sb < nsb; sb += nwarp) {
+            const int64_t i0 = sb * PIB_QK_K + lane * 8;
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = aq_value<PRO>(xr, x2r, scale, lut, i0 + j);
+            // first element (in index order) with the largest |x|: strict '>' scan, ties keep the lower index
+            float amax = 0.0f, mx = 0.0f;
+            int   idx  = 1 << 30;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const float ax = fabsf(v[j]);
+                if (ax > amax) { amax = ax; mx = v[j]; idx = lane * 8 + j; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
+                const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+                const int   oi = __shfl_xor_sync(0xffffffffu, idx, o);
+                if (oa > amax || (oa == amax && oi < idx)) { amax = oa; mx = om; idx = oi; }
+            }
+            int q[8];
+            float dval = 0.0f;
+            if (amax == 0.0f) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) q[j] = 0;
+            } else {
+                const float iscale = -128.f / mx;
+#pragma unroll
+                for (int j = 0; j < 8; j++) q[j] = min(127, __float2int_rn(__fmul_rn(iscale, v[j])));
+                dval = 1.0f / iscale;
+            }
+            int2 packed;
+            packed.x = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((q[3] & 0xff) << 24);
+            packed.y = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((q[7] & 0xff) << 24);
+            *reinterpret_cast<int2 *>(qs + (size_t) row * K + i0) = packed;
+            if (vout) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) vout[(size_t) row * K + i0 + j] = v[j];
+            }
+            int s8 = q[0] + q[1] + q[2] + q[3] + q[4] + q[5] + q[6] + q[7];
+            int s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
+            if ((lane & 1) == 0) ((int16_t *) bsplane)[(size_t) row * (K / 16) + sb * 16 + (lane >> 1)] = (int16_t) s16;
+            if (lane == 0) dplane[(size_t) row * nsb + sb] = dval;
+        }
+    }
+}
+
+template <int PRO>
+static int launch_aq(int wtype, const float * x, const float * x2, int x2_per_row, float eps, int b, int64_t K, void * act,
+                     float * vout, const uint16_t * lut, cudaStream_t st) {
+    const pib_act_layout L = pib_act_layout_of(wtype, K, b);
+    int8_t * qs = (int8_t *) act + L.qs_off;
+    float *  d  = (float *) ((uint8_t *) act + L.d_off);
+    void *   bs = (uint8_t *) act + L.bs_off;
+    if (wtype == PIB_TYPE_Q4_K) act_quant_kernel<true, PRO><<<b, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut);
+    else                        act_quant_kernel<false, PRO><<<b, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+
+static int check_args(int wtype, int b, int64_t K) {
+    const int blk = wtype == PIB_TYPE_Q4_K ? PIB_QK_K : PIB_QK;
+    if ((wtype != PIB_TYPE_Q4_0 && wtype != PIB_TYPE_Q8_0 && wtype != PIB_TYPE_Q4_K) || b < 1 || K < blk || K % blk != 0) {
+        pib_set_error("act quantise: bad arguments (type %d, b %d, K %lld)", wtype, b, (long long) K);
+        return PIB_ERR_ARG;
+    }
+    return PIB_OK;
+}
+
+extern "C" size_t pib_act_bytes(int wtype, int64_t K, int b) { return pib_act_layout_of(wtype, K, b).total; }
+
+extern "C" int pib_quantize_act(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, pib_stream s) {
+    if (check_args(wtype, b, K) != PIB_OK) return PIB_ERR_ARG;
+    return launch_aq<PRO_PLAIN>(wtype, x_dev, nullptr, 0, 0.f, b, K, act_dev, nullptr, nullptr, (cudaStream_t) s);
+}
+
+extern "C" int pib_norm_quantize_act(int wtype, int norm_kind, const float * x_dev, const float * norm_w_dev, float eps, int b,
+                                     int64_t K, void * act_dev, float * xnorm_dev, pib_stream s) {
+    if (check_args(wtype, b, K) != PIB_OK) return PIB_ERR_ARG;
+    if (norm_kind != 1) { pib_set_error("pib_norm_quantize_act: only RMSNorm (1) is implemented"); return PIB_ERR_UNSUPP; }
+    return launch_aq<PRO_RMSNORM>(wtype, x_dev, norm_w_dev, 0, eps, b, K, act_dev, xnorm_dev, nullptr, (cudaStream_t) s);
+}
+
+// internal (engine): silu(gate) * up -> quantised activations for the down projection
+int pib_silu_mul_quantize_act(int wtype, const float * gate_dev, const float * up_dev, int b, int64_t K, void * act_dev,
+                              cudaStream_t st) {
+    if (check_args(wtype, b, K) != PIB_OK) return PIB_ERR_ARG;
+    return launch_aq<PRO_SILU_MUL>(wtype, gate_dev, up_dev, 1, 0.f, b, K, act_dev, nullptr, pib_get_luts().silu_f16, st);
+}
+
+extern "C" int pib_act_to_blocks(int wtype, const void * act_dev, int b, int64_t K, void * out) {
+    if (check_args(wtype, b, K) != PIB_OK) return PIB_ERR_ARG;
+    const pib_act_layout L = pib_act_layout_of(wtype, K, b);
+    uint8_t * h = (uint8_t *) malloc(L.total);
+    cudaError_t e = cudaMemcpy(h, act_dev, L.total, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) { free(h); PIB_CHECK(e); }
+    uint8_t * o = (uint8_t *) out;
+    if (wtype == PIB_TYPE_Q4_K) {
+        const int64_t nsb = K / 256;
+        for (int t = 0; t < b; t++)
+            for (int64_t s = 0; s < nsb; s++) {
+                uint8_t * blk = o + ((size_t) t * nsb + s) * 292;
+                memcpy(blk, h + L.d_off + ((size_t) t * nsb + s) * 4, 4);
+                memcpy(blk + 4, h + L.qs_off + (size_t) t * K + s * 256, 256);
+                memcpy(blk + 260, h + L.bs_off + ((size_t) t * (K / 16) + s * 16) * 2, 32);
+            }
+    } else {
+        const int64_t nb = K / 32;
+        for (int t = 0; t < b; t++)
+            for (int64_t s = 0; s < nb; s++) {
+                uint8_t * blk = o + ((size_t) t * nb + s) * 34;
+                float     d;
+                memcpy(&d, h + L.d_off + ((size_t) t * nb + s) * 4, 4);
+                const __half hd = __float2half_rn(d);
+                memcpy(blk, &hd, 2);
+                memcpy(blk + 2, h + L.qs_off + (size_t) t * K + s * 32, 32);
+            }
+    }
+    free(h);
+    return PIB_OK;
+}

@@ -1,0 +1,186 @@
+// lib.cu -- library state (device, look-up tables, error string), small C-ABI helpers, GEMV dispatch, embedding rows.
+#include "pib_common.cuh"
+
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include <mutex>
+
+static thread_local char g_err[512] = "";
+
+void pib_set_error(const char * fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char * pib_last_error(void) { return g_err; }
+
+#define PIB_MAX_DEV 16
+static pib_luts   g_luts[PIB_MAX_DEV];
+static int        g_sms[PIB_MAX_DEV];
+static bool       g_ready[PIB_MAX_DEV];
+static std::mutex g_mu;
+
+static inline uint16_t host_f2h(float f) { const __half h = __float2half_rn(f); uint16_t u; memcpy(&u, &h, 2); return u; }
+static inline float    host_h2f(uint16_t u) { __half h; memcpy(&h, &u, 2); return __half2float(h); }
+
+extern "C" int pib_init(int device) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        pib_set_error("pib_init: no CUDA device (libpipeinfer_b200 has no CPU path)");
+        return PIB_ERR_CUDA;
+    }
+    if (device < 0 || device >= n || device >= PIB_MAX_DEV) { pib_set_error("pib_init: bad device %d", device); return PIB_ERR_ARG; }
+    PIB_CHECK(cudaSetDevice(device));
+    if (g_ready[device]) return PIB_OK;
+    cudaDeviceProp prop;
+    PIB_CHECK(cudaGetDeviceProperties(&prop, device));
+    g_sms[device] = prop.multiProcessorCount;
+    // the reference fills these tables in ggml_init with the host libm (ggml.c:2190-2200): value = fp16(f(fp32(fp16 i)))
+    const int  n16 = 1 << 16;
+    uint16_t * h   = (uint16_t *) malloc(3 * n16 * sizeof(uint16_t));
+    for (int i = 0; i < n16; i++) {
+        const float f = host_h2f((uint16_t) i);
+        h[i]           = host_f2h(expf(f));
+        h[n16 + i]     = host_f2h(f / (1.0f + expf(-f)));
+        h[2 * n16 + i] = host_f2h(0.5f * f * (1.0f + tanhf(0.79788456080286535587989211986876f * f * (1.0f + 0.044715f * f * f))));
+    }
+    uint16_t * d = nullptr;
+    PIB_CHECK(cudaMalloc(&d, 3 * n16 * sizeof(uint16_t)));
+    PIB_CHECK(cudaMemcpy(d, h, 3 * n16 * sizeof(uint16_t), cudaMemcpyHostToDevice));
+    free(h);
+    g_luts[device].exp_f16  = d;
+    g_luts[device].silu_f16 = d + n16;
+    g_luts[device].gelu_f16 = d + 2 * n16;
+    g_ready[device]         = true;
+    return PIB_OK;
+}
+
+const pib_luts & pib_get_luts() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= PIB_MAX_DEV || !g_ready[dev]) {
+        fprintf(stderr, "libpipeinfer_b200: pib_init() was not called for device %d\n", dev);
+        abort();
+    }
+    return g_luts[dev];
+}
+
+int pib_num_sms() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev >= 0 && dev < PIB_MAX_DEV && g_ready[dev]) ? g_sms[dev] : 148;
+}
+
+extern "C" int pib_device_sm_count(void) { return pib_num_sms(); }
+
+extern "C" void * pib_dev_alloc(size_t bytes) {
+    void * p = nullptr;
+    if (cudaMalloc(&p, bytes ? bytes : 1) != cudaSuccess) {
+        pib_set_error("pib_dev_alloc(%zu): %s", bytes, cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+    }
+    return p;
+}
+extern "C" void pib_dev_free(void * p) { if (p) cudaFree(p); }
+extern "C" int  pib_memcpy_h2d(void * dev, const void * host, size_t bytes, pib_stream s) {
+    PIB_CHECK(cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, (cudaStream_t) s));
+    return PIB_OK;
+}
+extern "C" int pib_memcpy_d2h(void * host, const void * dev, size_t bytes, pib_stream s) {
+    PIB_CHECK(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, (cudaStream_t) s));
+    return PIB_OK;
+}
+extern "C" int pib_stream_sync(pib_stream s) {
+    PIB_CHECK(cudaStreamSynchronize((cudaStream_t) s));
+    return PIB_OK;
+}
+
+// ---- K1 dispatch ----------------------------------------------------------------------------------------------------
+int pib_gemv_dp4a(const pib_weight * w, const void * act_dev, int b, float * y_dev, cudaStream_t st);
+int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_dev, cudaStream_t st);
+bool pib_gemv_mma_supported(const pib_weight * w, int b);
+
+extern "C" int pib_gemv(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, pib_stream s) {
+    if (!w || !act_dev || !y_dev || b < 1 || b > PIB_MAX_BATCH) {
+        pib_set_error("pib_gemv: bad arguments (b = %d, limit %d)", b, PIB_MAX_BATCH);
+        return PIB_ERR_ARG;
+    }
+    if (variant == 2 || (variant == 0 && b > 1 && pib_gemv_mma_supported(w, b))) {
+        if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: variant 2 does not support this shape"); return PIB_ERR_UNSUPP; }
+        return pib_gemv_mma(w, act_dev, b, y_dev, (cudaStream_t) s);
+    }
+    return pib_gemv_dp4a(w, act_dev, b, y_dev, (cudaStream_t) s);
+}
+
+extern "C" int pib_mul_mat_host(const pib_weight * w, const float * x_host, int b, float * y_host, int variant) {
+    if (!w || b < 1 || b > PIB_MAX_BATCH) { pib_set_error("pib_mul_mat_host: bad arguments"); return PIB_ERR_ARG; }
+    const size_t xb = (size_t) b * w->K * 4, yb = (size_t) b * w->N * 4, ab = pib_act_bytes(w->type, w->K, b);
+    uint8_t *    buf = nullptr;
+    PIB_CHECK(cudaMalloc(&buf, xb + yb + ab + 512));
+    float * x   = (float *) buf;
+    float * y   = (float *) (buf + ((xb + 255) & ~(size_t) 255));
+    void *  act = buf + ((xb + 255) & ~(size_t) 255) + ((yb + 255) & ~(size_t) 255);
+    int     rc  = PIB_OK;
+    if (cudaMemcpy(x, x_host, xb, cudaMemcpyHostToDevice) != cudaSuccess) rc = PIB_ERR_CUDA;
+    if (rc == PIB_OK) rc = pib_quantize_act(w->type, x, b, w->K, act, nullptr);
+    if (rc == PIB_OK) rc = pib_gemv(w, act, b, y, variant, nullptr);
+    if (rc == PIB_OK && cudaMemcpy(y_host, y, yb, cudaMemcpyDeviceToHost) != cudaSuccess) rc = PIB_ERR_CUDA;
+    if (rc == PIB_ERR_CUDA) pib_set_error("pib_mul_mat_host: %s", cudaGetErrorString(cudaGetLastError()));
+    cudaFree(buf);
+    return rc;
+}
+
+// ---- K3: embedding rows ---------------------------------------------------------------------------------------------
+// out[n][K] = dequantised row ids[n] (reference dequantize_row_q4_0 / q8_0 / q4_K: ggml-quants.c:1074, 1168, 1917;
+// every element is one fp32 multiply (and one subtract for Q4_K), so results are bit-exact)
+__global__ void get_rows_kernel(int type, const uint8_t * __restrict__ qs, const uint16_t * __restrict__ d, int64_t K,
+                                const int32_t * __restrict__ ids, float * __restrict__ out) {
+    const int64_t row = ids[blockIdx.x];
+    float *       o   = out + (size_t) blockIdx.x * K;
+    if (type == PIB_TYPE_Q8_0) {
+        const int8_t * q = (const int8_t *) qs + row * K;
+        for (int64_t i = threadIdx.x; i < K; i += blockDim.x) o[i] = (float) q[i] * pib_h2f(d[row * (K / 32) + i / 32]);
+    } else if (type == PIB_TYPE_Q4_0) {
+        const uint8_t * q = qs + row * (K / 2);
+        for (int64_t i = threadIdx.x; i < K; i += blockDim.x) {
+            const int64_t blk = i / 32;
+            const int     j   = (int) (i % 32);
+            const uint8_t by  = q[blk * 16 + (j & 15)];
+            const int     v   = (j < 16 ? (by & 0x0F) : (by >> 4)) - 8;
+            o[i]              = (float) v * pib_h2f(d[row * (K / 32) + blk]);
+        }
+    } else {
+        const uint8_t * q   = qs + row * (K / 2);
+        const uint8_t * hdr = (const uint8_t *) d + row * (K / 256) * 16;
+        for (int64_t i = threadIdx.x; i < K; i += blockDim.x) {
+            const int64_t   sb = i / 256;
+            const int       e  = (int) (i % 256);
+            const int       c  = e / 64, r = e % 64;        // chunk of 64: low nibbles = first 32 elements
+            const uint8_t * h  = hdr + sb * 16;
+            const float     dd = pib_h2f((uint16_t) (h[0] | (h[1] << 8)));
+            const float     mn = pib_h2f((uint16_t) (h[2] | (h[3] << 8)));
+            const int       j  = 2 * c + (r >= 32);
+            const uint8_t * sc = h + 4;
+            int s, m;
+            if (j < 4) { s = sc[j] & 63; m = sc[j + 4] & 63; }
+            else       { s = (sc[j + 4] & 0xF) | ((sc[j - 4] >> 6) << 4); m = (sc[j + 4] >> 4) | ((sc[j] >> 6) << 4); }
+            const uint8_t by = q[sb * 128 + c * 32 + (r & 31)];
+            const int     v  = r < 32 ? (by & 0xF) : (by >> 4);
+            const float   d1 = __fmul_rn(dd, (float) s), m1 = __fmul_rn(mn, (float) m);
+            o[i]             = __fsub_rn(__fmul_rn(d1, (float) v), m1);
+        }
+    }
+}
+
+extern "C" int pib_get_rows(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, pib_stream s) {
+    if (!w || !ids_dev || !out_dev || n < 1) { pib_set_error("pib_get_rows: bad arguments"); return PIB_ERR_ARG; }
+    get_rows_kernel<<<n, 256, 0, (cudaStream_t) s>>>(w->type, w->qs, w->d, w->K, ids_dev, out_dev);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}

@@ -1,0 +1,113 @@
+// pib_common.cuh -- shared device/host helpers for libpipeinfer_b200 (sm_100a only).
+#pragma once
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "../../include/pipeinfer_b200.h"
+
+#define PIB_CHECK(expr)                                                                                      \
+    do {                                                                                                     \
+        cudaError_t e__ = (expr);                                                                            \
+        if (e__ != cudaSuccess) {                                                                            \
+            pib_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__));            \
+            return PIB_ERR_CUDA;                                                                             \
+        }                                                                                                    \
+    } while (0)
+
+#define PIB_CHECK_PTR(expr)                                                                                  \
+    do {                                                                                                     \
+        cudaError_t e__ = (expr);                                                                            \
+        if (e__ != cudaSuccess) {                                                                            \
+            pib_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__));            \
+            return nullptr;                                                                                  \
+        }                                                                                                    \
+    } while (0)
+
+void pib_set_error(const char * fmt, ...);
+
+// block geometry of the three weight formats on the path (reference: ggml-quants.h:10-15, 42-47, 116-122, 161-166)
+#define PIB_QK   32
+#define PIB_QK_K 256
+
+// fp16 look-up tables (exp / silu / gelu), uploaded by pib_init from host-computed values so that they are the very
+// tables the reference builds with the host libm (ggml.c:2185-2203)
+struct pib_luts {
+    const uint16_t * exp_f16;
+    const uint16_t * silu_f16;
+    const uint16_t * gelu_f16;
+};
+const pib_luts & pib_get_luts();   // asserts pib_init was called on the current device
+int pib_num_sms();
+
+// ---- device helpers ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float pib_h2f(uint16_t h) { return __half2float(__ushort_as_half(h)); }
+__device__ __forceinline__ uint16_t pib_f2h(float f) { return __half_as_ushort(__float2half_rn(f)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// 128-bit read-only streaming load that does not allocate in L1 (weights are read exactly once per launch)
+__device__ __forceinline__ int4 ld_stream_v4(const void * p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ int2 ld_stream_v2(const void * p) {
+    int2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.s32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+    return r;
+}
+
+// device view of a repacked weight matrix (see weights.cu for the layouts)
+struct pib_weight {
+    int      type;      // PIB_TYPE_*
+    int64_t  N, K;      // rows (outputs), columns (inputs)
+    void *   base;      // one allocation
+    size_t   bytes;     // algorithmic bytes == bytes of the reference block layout (N * K/blk * blk_bytes)
+    // v1 planes (row-major SoA)
+    uint8_t * qs;       // Q8_0: int8 [N][K];  Q4_0: [N][K/2] nibbles in block order;  Q4_K: [N][K/2] nibbles
+    uint16_t * d;       // Q8_0/Q4_0: fp16 [N][K/32];  Q4_K: 16-byte headers {d, dmin, scales[12]} as [N][K/256][8] halves
+    // v2 tiles (fragment-major, see gemv_mma.cu)
+    uint8_t * tiles;
+    size_t    tile_bytes;
+    int       owns;
+};
+
+// byte layout of a quantised-activation buffer for `b` tokens (device, produced by act_quant.cu)
+struct pib_act_layout {
+    size_t qs_off;     // int8  [b][K]
+    size_t d_off;      // float [b][K/32] (Q8_0 family) or [b][K/256] (Q8_K family)
+    size_t bs_off;     // Q8_0 family: int32 [b][K/32] block sums (unused by the reference, used for the -8 offset);
+                       // Q8_K family: int16 [b][K/16] bsums exactly as block_q8_K
+    size_t total;
+};
+__host__ __device__ inline pib_act_layout pib_act_layout_of(int wtype, int64_t K, int b) {
+    pib_act_layout L;
+    L.qs_off = 0;
+    size_t qs = (size_t) b * K;
+    L.d_off  = (qs + 255) & ~(size_t) 255;
+    size_t nd = (wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / PIB_QK_K) : (size_t) b * (K / PIB_QK);
+    L.bs_off = (L.d_off + nd * 4 + 255) & ~(size_t) 255;
+    size_t nbs = (wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / 16) * 2 : (size_t) b * (K / PIB_QK) * 4;
+    L.total  = (L.bs_off + nbs + 255) & ~(size_t) 255;
+    return L;
+}

@@ -1,0 +1,136 @@
+"""Parity of the CUDA operators (through the C ABI of libpipeinfer_b200.so) against the oracle and the golden fixtures.
+Integer work (activation blocks, weight round trip, embedding rows) must be bit-exact; fp32 dot products may differ
+from the reference only by the order of fp32 additions (tolerance below; north_star: logits within 1e-2 max-abs)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle_py as op
+
+pytestmark = pytest.mark.gpu
+
+TYPES = list(op.TYPE_NAMES.items())
+REL_TOL = 3e-5     # of max|y|: fp32 reassociation over <= 896 block terms
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from pipeinfer_b200 import load
+    L = load()
+    L.init(0)
+    return L
+
+
+@pytest.fixture(scope="module")
+def kern(golden_dir):
+    return np.load(os.path.join(golden_dir, "kernels.npz"))
+
+
+def rand_blocks(rng, wt, N, K):
+    """random but valid weight blocks generated directly (no quantiser needed on the GPU box)"""
+    be, bb = op.BLOCK[wt]
+    nb = K // be
+    blk = rng.integers(0, 256, (N, nb, bb), dtype=np.uint8)
+    d = (rng.uniform(0.5, 1.5, (N, nb)) * 0.02 / 8).astype(np.float16).view(np.uint8).reshape(N, nb, 2)
+    blk[:, :, 0:2] = d
+    if wt == op.TYPE_Q4_K:
+        dm = (rng.uniform(0.5, 1.5, (N, nb)) * 0.01 / 8).astype(np.float16).view(np.uint8).reshape(N, nb, 2)
+        blk[:, :, 2:4] = dm
+    return blk.reshape(N, nb * bb)
+
+
+@pytest.mark.parametrize("name,wt", TYPES)
+def test_weight_repack_round_trip(lib, kern, name, wt):
+    w = kern[name + "_w"]
+    K = kern[name + "_x"].shape[1]
+    h = lib.weight_upload(wt, w, K)
+    assert np.array_equal(lib.weight_rows(h, wt, w.shape[0], K), w)
+    lib.L.pib_weight_free(h)
+
+
+@pytest.mark.parametrize("name,wt", TYPES)
+def test_activation_quantiser_bit_exact_vs_golden(lib, kern, name, wt):
+    assert np.array_equal(lib.quantize_act(wt, kern[name + "_x"]), kern[name + "_act"])
+
+
+@pytest.mark.parametrize("name,wt", TYPES)
+@pytest.mark.parametrize("K", [256, 4096, 11008 // 256 * 256])
+def test_activation_quantiser_bit_exact_vs_oracle(lib, oracle, name, wt, K):
+    rng = np.random.default_rng(K)
+    x = (rng.standard_normal((7, K)) * rng.uniform(0.01, 30.0, (7, 1))).astype(np.float32)
+    x[3, :K // 2] = 0
+    x[5, 17] = -x[5, 100]          # two elements with the same |x| (Q8_K keeps the sign of the first)
+    assert np.array_equal(lib.quantize_act(wt, x), oracle.quantize_act(wt, x))
+
+
+@pytest.mark.parametrize("name,wt", TYPES)
+def test_rmsnorm_quantise_bit_exact_vs_oracle(lib, oracle, name, wt):
+    import ctypes as C
+    rng = np.random.default_rng(11)
+    K = 2048
+    x = (rng.standard_normal((5, K)) * 3).astype(np.float32)
+    w = rng.uniform(0.5, 1.5, K).astype(np.float32)
+    xn = np.empty_like(x)
+    for t in range(5):
+        oracle.L.po_rms_norm(x[t].ctypes.data_as(C.c_void_p), xn[t].ctypes.data_as(C.c_void_p), K, C.c_float(1e-5))
+    xn *= w
+    assert np.array_equal(lib.quantize_act(wt, x, norm_w=w, eps=1e-5), oracle.quantize_act(wt, xn))
+
+
+@pytest.mark.parametrize("name,wt", TYPES)
+def test_get_rows_bit_exact(lib, kern, name, wt):
+    w = kern[name + "_w"]
+    K = kern[name + "_x"].shape[1]
+    h = lib.weight_upload(wt, w, K)
+    ids = np.array([3, 0, 11, 3], dtype=np.int32)
+    got = lib.get_rows(h, ids, K)
+    assert np.array_equal(got.view(np.uint32), kern[name + "_deq"][ids].view(np.uint32))
+    lib.L.pib_weight_free(h)
+
+
+@pytest.mark.parametrize("variant", [1])
+@pytest.mark.parametrize("name,wt", TYPES)
+def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
+    w, x, y = kern[name + "_w"], kern[name + "_x"], kern[name + "_y"]
+    h = lib.weight_upload(wt, w, x.shape[1])
+    got = lib.mul_mat(h, x, w.shape[0], variant)
+    assert np.abs(got - y).max() <= REL_TOL * max(1.0, np.abs(y).max())
+    lib.L.pib_weight_free(h)
+
+
+@pytest.mark.parametrize("variant", [1])
+@pytest.mark.parametrize("name,wt", TYPES)
+@pytest.mark.parametrize("b", [1, 2, 5, 8, 9, 16])
+def test_mul_mat_vs_oracle_batches(lib, oracle, name, wt, b, variant):
+    rng = np.random.default_rng(100 + b)
+    N, K = 96, 2048
+    w = rand_blocks(rng, wt, N, K)
+    x = (rng.standard_normal((b, K)) * 2).astype(np.float32)
+    h = lib.weight_upload(wt, w, K)
+    got = lib.mul_mat(h, x, N, variant)
+    ref = oracle.mul_mat(wt, w, x)
+    assert np.abs(got - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max())
+    lib.L.pib_weight_free(h)
+
+
+@pytest.mark.parametrize("name,wt", TYPES)
+def test_mul_mat_ragged_rows_and_long_k(lib, oracle, name, wt):
+    # N not a multiple of the rows-per-CTA, K = 28672 (the 70B down projection)
+    rng = np.random.default_rng(5)
+    N, K = 37, 28672
+    w = rand_blocks(rng, wt, N, K)
+    x = (rng.standard_normal((3, K))).astype(np.float32)
+    h = lib.weight_upload(wt, w, K)
+    got = lib.mul_mat(h, x, N, 1)
+    ref = oracle.mul_mat(wt, w, x)
+    assert np.abs(got - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max())
+    lib.L.pib_weight_free(h)
+
+
+def test_bad_arguments_are_rejected(lib):
+    import ctypes as C
+    assert lib.L.pib_gemv(None, None, 1, None, 0, None) < 0
+    assert lib.L.pib_weight_upload(3, None, 4, 64) is None          # unsupported type
+    assert lib.L.pib_quantize_act(op.TYPE_Q4_K, None, 1, 100, None, None) < 0   # K not a multiple of 256
+    assert b"" != lib.L.pib_last_error()
