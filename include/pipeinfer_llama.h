@@ -1,0 +1,196 @@
+/*
+ * pipeinfer_llama.h -- C ABI of libpipeinfer_b200.so, runtime level: the subset of the reference's llama.h that
+ * examples/speculative/speculative.cpp, examples/main/main.cpp and common/ call on PipeInfer's path, with the same
+ * names, argument meaning, struct layouts and return codes, so that those programs can be linked against this library
+ * in place of llama.o + ggml*.o.  Citations are to the reference repository.
+ *
+ * One process drives one GPU (one pipeline stage).  Under a multi-process launch (torchrun / mpirun-style, one rank per
+ * GPU) rank 0 is the pipeline head and runs the scheduler; other ranks enter llama_decode once and serve as stages
+ * until shutdown, exactly like the reference's worker loop (llama.cpp:9941-9977, 9995-10007).
+ */
+#ifndef PIPEINFER_LLAMA_H
+#define PIPEINFER_LLAMA_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+struct llama_model;
+struct llama_context;
+struct ggml_cgraph;                 /* opaque run handle of the async API (never dereferenced by callers) */
+
+typedef int32_t llama_pos;
+typedef int32_t llama_token;
+typedef int32_t llama_seq_id;
+
+/* llama.h:118-128 */
+typedef struct llama_token_data { llama_token id; float logit; float p; } llama_token_data;
+typedef struct llama_token_data_array { llama_token_data * data; size_t size; bool sorted; } llama_token_data_array;
+typedef void (*llama_progress_callback)(float progress, void * ctx);
+
+/* llama.h:142-162 (incl. PipeInfer's trailing batch_id / max_n_seq); passed BY VALUE */
+typedef struct llama_batch {
+    int32_t        n_tokens;
+    llama_token *  token;
+    float *        embd;
+    llama_pos *    pos;
+    int32_t *      n_seq_id;
+    llama_seq_id ** seq_id;
+    int8_t *       logits;
+    llama_pos      all_pos_0;
+    llama_pos      all_pos_1;
+    llama_seq_id   all_seq_id;
+    int32_t        batch_id;
+    int32_t        max_n_seq;
+} llama_batch;
+
+/* llama.h:164-178; n_gpu_layers / main_gpu / tensor_split / mmap flags are accepted and ignored (always on the GPU) */
+struct llama_model_params {
+    int32_t       n_gpu_layers;
+    int32_t       main_gpu;
+    const float * tensor_split;
+    llama_progress_callback progress_callback;
+    void *        progress_callback_user_data;
+    bool          vocab_only;
+    bool          use_mmap;
+    bool          use_mlock;
+};
+
+/* llama.h:180-203; thread counts and YaRN fields are accepted and ignored */
+struct llama_context_params {
+    uint32_t seed;
+    uint32_t n_ctx;
+    uint32_t n_batch;
+    uint32_t n_threads;
+    uint32_t n_threads_batch;
+    int8_t   rope_scaling_type;
+    float    rope_freq_base;
+    float    rope_freq_scale;
+    float    yarn_ext_factor;
+    float    yarn_attn_factor;
+    float    yarn_beta_fast;
+    float    yarn_beta_slow;
+    uint32_t yarn_orig_ctx;
+    bool     mul_mat_q;
+    bool     f16_kv;
+    bool     logits_all;
+    bool     embedding;
+};
+
+/* llama.h:389-430 */
+struct llama_kv_cache_view_cell { llama_pos pos; };
+struct llama_kv_cache_view {
+    int32_t n_cells;
+    int32_t n_max_seq;
+    int32_t token_count;
+    int32_t used_cells;
+    int32_t max_contiguous;
+    int32_t max_contiguous_idx;
+    struct llama_kv_cache_view_cell * cells;
+    llama_seq_id * cells_sequences;
+};
+
+/* ---- start-up / tear-down (llama.h:263-300; llama.cpp:8642, 8671, 8707) ---- */
+struct llama_model_params   llama_model_default_params(void);
+struct llama_context_params llama_context_default_params(void);
+void llama_backend_init(bool numa);
+void llama_backend_free(void);
+struct llama_model *   llama_load_model_from_file(const char * path_model, struct llama_model_params params);
+void                   llama_free_model(struct llama_model * model);
+struct llama_context * llama_new_context_with_model(struct llama_model * model, struct llama_context_params params);
+void                   llama_free(struct llama_context * ctx);
+int64_t                llama_time_us(void);
+void llama_set_n_threads(struct llama_context * ctx, uint32_t n_threads, uint32_t n_threads_batch);   /* no-op */
+
+/* ---- model / vocabulary queries (llama.h:302-330, 619-670) ---- */
+const struct llama_model * llama_get_model(const struct llama_context * ctx);
+int   llama_n_ctx(const struct llama_context * ctx);
+int   llama_n_vocab(const struct llama_model * model);
+int   llama_n_ctx_train(const struct llama_model * model);
+int   llama_n_embd(const struct llama_model * model);
+llama_token llama_token_bos(const struct llama_model * model);
+llama_token llama_token_eos(const struct llama_model * model);
+llama_token llama_token_nl(const struct llama_model * model);
+int   llama_add_bos_token(const struct llama_model * model);
+int   llama_tokenize(const struct llama_model * model, const char * text, int text_len, llama_token * tokens,
+                     int n_max_tokens, bool add_bos, bool special);                       /* SPM, llama.cpp:5970-6110 */
+int   llama_token_to_piece(const struct llama_model * model, llama_token token, char * buf, int length);
+
+/* ---- batches (llama.cpp:9839-9898) ---- */
+struct llama_batch llama_batch_get_one(llama_token * tokens, int32_t n_tokens, llama_pos pos_0, llama_seq_id seq_id);
+struct llama_batch llama_batch_init(int32_t n_tokens, int32_t embd, int32_t n_seq_max);
+#ifdef __cplusplus
+void llama_batch_free(struct llama_batch & batch);                 /* llama.h:585 takes a C++ reference */
+#else
+void llama_batch_free(struct llama_batch * batch);
+#endif
+
+/* ---- decode (llama.cpp:9995 llama_decode; :5850 / :5857 async pair; :5457 iprobe; :9981 cancel) ----
+ * llama_decode: 0 on success, -1 on any failure including "no KV slot" (this fork, llama.cpp:5562-5565, 5841-5847).
+ * llama_start_async_decode: enqueues the whole stage on the GPU stream and returns a run handle (NULL on failure).
+ * llama_finish_async_decode: waits for the handle; 1 on success, -1 on a NULL handle (llama.cpp:5865-5867).
+ * llama_mpi_iprobe: true when the OLDEST run in flight has finished (the reference: "have logits arrived?").
+ * llama_cancel_run: marks batch ids cancelled; kernels of those runs that have not started yet exit at their first
+ *   instruction; KV cells stay allocated and head still advances, as in the reference (llama.cpp:5700-5714). */
+int llama_decode(struct llama_context * ctx, struct llama_batch batch);
+#ifdef __cplusplus
+struct ggml_cgraph * llama_start_async_decode(struct llama_context & lctx, struct llama_batch batch);
+int                  llama_finish_async_decode(struct llama_context & lctx, struct llama_batch batch, struct ggml_cgraph * cgraph);
+#else
+struct ggml_cgraph * llama_start_async_decode(struct llama_context * lctx, struct llama_batch batch);
+int                  llama_finish_async_decode(struct llama_context * lctx, struct llama_batch batch, struct ggml_cgraph * cgraph);
+#endif
+bool llama_mpi_iprobe(struct llama_context * lctx);
+void llama_cancel_run(struct llama_context * ctx, int32_t * canceled, int count);
+float * llama_get_logits(struct llama_context * ctx);                      /* lazy device->host copy */
+float * llama_get_logits_ith(struct llama_context * ctx, int32_t i);       /* llama.cpp:10019-10025 */
+
+/* ---- KV cache sequence ops (llama.cpp:9238-9359 wrappers over :1657-1734) ---- */
+void llama_kv_cache_clear(struct llama_context * ctx);
+void llama_kv_cache_seq_rm(struct llama_context * ctx, llama_seq_id seq_id, llama_pos p0, llama_pos p1);
+void llama_kv_cache_seq_cp(struct llama_context * ctx, llama_seq_id seq_id_src, llama_seq_id seq_id_dst, llama_pos p0, llama_pos p1);
+void llama_kv_cache_seq_keep(struct llama_context * ctx, llama_seq_id seq_id);
+int  llama_get_kv_cache_token_count(const struct llama_context * ctx);
+int  llama_get_kv_cache_used_cells(const struct llama_context * ctx);
+struct llama_kv_cache_view llama_kv_cache_view_init(const struct llama_context * ctx, int32_t n_max_seq);
+void llama_kv_cache_view_free(struct llama_kv_cache_view * view);
+void llama_kv_cache_view_update(const struct llama_context * ctx, struct llama_kv_cache_view * view);
+
+/* ---- communicator helpers (llama.cpp:8901-8938).  Both heads live in one process here, so the token syncs are
+ * no-ops; split_layers_weighted partitions the layers over the pipeline stages with ggml_mpi_split_range's rule. ---- */
+void llama_split_comm(struct llama_context * ctx, int color);
+void llama_swap_comm(struct llama_context * ctx);
+void llama_sync_token(struct llama_context * ctx, llama_token * token, int root);
+void llama_sync_token_data(struct llama_context * ctx, llama_token_data * data, int root);
+void llama_split_layers_weighted(struct llama_context * ctx, float device_weights[], size_t num_weights);
+int  llama_node_id(struct llama_context * ctx);
+
+/* ---- samplers used under greedy decoding (llama.cpp:7019, 7496) ---- */
+void        llama_sample_softmax(struct llama_context * ctx, llama_token_data_array * candidates);
+llama_token llama_sample_token_greedy(struct llama_context * ctx, llama_token_data_array * candidates);
+
+/* ---- additive extensions (no counterpart in llama.h; needed for device-side acceptance) ---- */
+/* sorted top-8 {id, logit, p} of logits row i of the last finished run: 96 bytes instead of n_vocab floats */
+int  llama_pib_get_top8(struct llama_context * ctx, int32_t i, llama_token_data * out8);
+/* logit bias applied on the device before argmax (the reference adds it on the host, common/sampling.cpp:134-136) */
+void llama_pib_set_logit_bias(struct llama_context * ctx, const llama_token * ids, const float * bias, int n);
+/* random-init model of the llama architecture generated directly in HBM (no file); flavour 0 iid, 1 bigram */
+struct llama_model * llama_pib_synthetic_model(int n_layer, int n_embd, int n_head, int n_head_kv, int n_ff, int n_vocab,
+                                               int wtype, uint64_t seed, int flavour, float agree);
+/* context with an explicit sequence-id capacity (the reference sizes std::set on demand) */
+struct llama_context * llama_pib_new_context(struct llama_model * model, uint32_t n_ctx, int32_t max_seq_ids);
+/* KV bookkeeping probes for parity tests: head / used / n, cell positions and sequence bitset rows, host mirror (0)
+ * or device replica (1) */
+int  llama_pib_kv_state(struct llama_context * ctx, int from_device, int32_t * scalars3, int32_t * pos, uint32_t * bits);
+int  llama_pib_kv_words(const struct llama_context * ctx);
+uint64_t llama_pib_kernel_launches(const struct llama_context * ctx);
+size_t   llama_pib_weight_bytes(const struct llama_model * model);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

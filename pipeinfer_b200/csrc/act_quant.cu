@@ -29,14 +29,17 @@ __device__ __forceinline__ float aq_value(const float * __restrict__ xr, const f
 }
 
 template <bool Q8K, int PRO>
-__global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * __restrict__ x, const float * __restrict__ x2,
+__global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, const float * __restrict__ x2,
                                                                int x2_per_row, float eps, int64_t K,
                                                                int8_t * __restrict__ qs, float * __restrict__ dplane,
                                                                void * __restrict__ bsplane, float * __restrict__ vout,
-                                                               const uint16_t * __restrict__ lut) {
+                                                               const uint16_t * __restrict__ lut,
+                                                               const float * __restrict__ addend, float * sum_out,
+                                                               const int * __restrict__ cancel, int64_t xstride) {
+    if (cancel && *cancel) return;
     const int     row  = blockIdx.x;
-    const float * xr   = x + (size_t) row * K;
-    const float * x2r  = x2 ? (x2_per_row ? x2 + (size_t) row * K : x2) : nullptr;
+    const float * xr   = x + (size_t) row * xstride;
+    const float * x2r  = x2 ? (x2_per_row ? x2 + (size_t) row * xstride : x2) : nullptr;
     const int     lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int     nwarp = AQ_THREADS / 32;
 
@@ -45,10 +48,15 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * __r
         __shared__ double red[AQ_THREADS / 32];
         __shared__ float  s_scale;
         double            s = 0.0;
+        // optional residual add fused in front (reference ggml_add, llama.cpp:3944 / :3962): sum_out = x + addend
+        const float * ar = addend ? addend + (size_t) row * K : nullptr;
+        float *       so = sum_out ? sum_out + (size_t) row * K : nullptr;
         for (int64_t i = threadIdx.x; i < K; i += AQ_THREADS) {
-            const float v = xr[i];
+            float v = xr[i];
+            if (ar) { v = __fadd_rn(v, ar[i]); so[i] = v; }
             s += (double) __fmul_rn(v, v);
         }
+        if (ar) xr = so;     // pass 2 re-reads the sums (visible CTA-wide after the barrier below)
         s = warp_sum_d(s);
         if (lane == 0) red[warp] = s;
         __syncthreads();
@@ -135,13 +143,15 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * __r
 
 template <int PRO>
 static int launch_aq(int wtype, const float * x, const float * x2, int x2_per_row, float eps, int b, int64_t K, void * act,
-                     float * vout, const uint16_t * lut, cudaStream_t st) {
+                     float * vout, const uint16_t * lut, cudaStream_t st, const float * addend = nullptr,
+                     float * sum_out = nullptr, const int * cancel = nullptr, int64_t xstride = 0) {
+    if (xstride == 0) xstride = K;
     const pib_act_layout L = pib_act_layout_of(wtype, K, b);
     int8_t * qs = (int8_t *) act + L.qs_off;
     float *  d  = (float *) ((uint8_t *) act + L.d_off);
     void *   bs = (uint8_t *) act + L.bs_off;
-    if (wtype == PIB_TYPE_Q4_K) act_quant_kernel<true, PRO><<<b, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut);
-    else                        act_quant_kernel<false, PRO><<<b, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut);
+    if (wtype == PIB_TYPE_Q4_K) act_quant_kernel<true, PRO><<<b, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut, addend, sum_out, cancel, xstride);
+    else                        act_quant_kernel<false, PRO><<<b, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut, addend, sum_out, cancel, xstride);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }
@@ -169,11 +179,27 @@ extern "C" int pib_norm_quantize_act(int wtype, int norm_kind, const float * x_d
     return launch_aq<PRO_RMSNORM>(wtype, x_dev, norm_w_dev, 0, eps, b, K, act_dev, xnorm_dev, nullptr, (cudaStream_t) s);
 }
 
-// internal (engine): silu(gate) * up -> quantised activations for the down projection
-int pib_silu_mul_quantize_act(int wtype, const float * gate_dev, const float * up_dev, int b, int64_t K, void * act_dev,
-                              cudaStream_t st) {
+// ---- internal (engine) entry points ---------------------------------------------------------------------------------
+// silu(gate) * up -> quantised activations for the down projection; gate_up: [b][2*K] rows = {gate[K], up[K]}
+int pib_silu_mul_quantize_act(int wtype, const float * gate_dev, const float * up_dev, int64_t row_stride, int b, int64_t K,
+                              void * act_dev, const int * cancel, cudaStream_t st) {
     if (check_args(wtype, b, K) != PIB_OK) return PIB_ERR_ARG;
-    return launch_aq<PRO_SILU_MUL>(wtype, gate_dev, up_dev, 1, 0.f, b, K, act_dev, nullptr, pib_get_luts().silu_f16, st);
+    return launch_aq<PRO_SILU_MUL>(wtype, gate_dev, up_dev, 1, 0.f, b, K, act_dev, nullptr, pib_get_luts().silu_f16, st,
+                                   nullptr, nullptr, cancel, row_stride);
+}
+
+int pib_quantize_act_c(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, const int * cancel, cudaStream_t st) {
+    if (check_args(wtype, b, K) != PIB_OK) return PIB_ERR_ARG;
+    return launch_aq<PRO_PLAIN>(wtype, x_dev, nullptr, 0, 0.f, b, K, act_dev, nullptr, nullptr, st, nullptr, nullptr, cancel);
+}
+
+// [sum_out = x + addend;] act = quantise(rmsnorm(sum or x) * w)
+int pib_add_rmsnorm_quantize_act(int wtype, const float * x_dev, const float * addend_dev, float * sum_out_dev,
+                                 const float * norm_w_dev, float eps, int b, int64_t K, void * act_dev, const int * cancel,
+                                 cudaStream_t st) {
+    if (check_args(wtype, b, K) != PIB_OK) return PIB_ERR_ARG;
+    return launch_aq<PRO_RMSNORM>(wtype, x_dev, norm_w_dev, 0, eps, b, K, act_dev, nullptr, nullptr, st, addend_dev, sum_out_dev,
+                                  cancel);
 }
 
 extern "C" int pib_act_to_blocks(int wtype, const void * act_dev, int b, int64_t K, void * out) {

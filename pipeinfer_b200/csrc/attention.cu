@@ -1,0 +1,242 @@
+// attention.cu -- RoPE + KV store (K5, K6) and multi-sequence masked attention over the KV cache (K7).
+//
+// Reference op chain (llama.cpp:3913-3944 build_llama, :3546 llm_build_kv_store, :3698 llm_build_kqv; CPU kernels
+// ggml.c:11006 rope, :6528 dup f32->f16, :1200 vec_dot_f16, :9937 scale, :10551 soft_max):
+//   Q,K <- rope(pos)             theta_i = pos * base^(-2i/d) by repeated multiply, cosf/sinf of the host libm
+//   cache K (f16), cache V (f16)  at cells kv_head + t
+//   S = (K . fp16(Q)) * 1/sqrt(d)   fp32 accumulate of exact fp16 products
+//   S += mask (0 / -inf)            cell visible iff it shares a sequence id with the token and cell.pos <= token.pos
+//   P = softmax(S)                  exp through the fp16 table on fp16(S - max), sum in double, P = val * (float)(1/sum)
+//   O = V . fp16(P)
+// Everything that is rounded in the reference is rounded identically here (fp16 Q, fp16 K/V, fp16 exp table, fp16 P);
+// the double sum of fp16 values is exact in any order, so only the fp32 dot-product association differs.
+//
+// cos/sin come from a table built on the host with the reference's recurrence (rope_table_build), so RoPE itself is
+// bit-exact.  The V cache is kept [cell][n_embd_gqa] (not transposed as in the reference, llama.cpp:3569): the layout
+// is private and this one is coalesced for both the store and the P.V pass.
+#include "pib_common.cuh"
+#include "desc.cuh"
+
+#include <math.h>
+
+#include <vector>
+
+// ---- RoPE table -----------------------------------------------------------------------------------------------------
+// tab[pos][i] = {cos(theta), sin(theta)}, theta as in reference rope_f32 (ggml.c:11062, 11111-11123) with ext_factor 0:
+// theta_base = pos; per pair: theta = freq_scale * theta_base; theta_base *= theta_scale.  mode 2 (NeoX) pre-multiplies
+// theta_base by freq_scale once more (ggml.c:11137).
+void rope_table_build(std::vector<float2> & tab, int n_pos, int n_dims, int mode, float freq_base, float freq_scale) {
+    const float theta_scale = powf(freq_base, -2.0f / n_dims);
+    tab.resize((size_t) n_pos * (n_dims / 2));
+    for (int p = 0; p < n_pos; p++) {
+        float theta_base = (float) p;
+        if (mode & 2) theta_base *= freq_scale;
+        for (int i = 0; i < n_dims / 2; i++) {
+            const float theta = freq_scale * theta_base;
+            tab[(size_t) p * (n_dims / 2) + i] = make_float2(cosf(theta), sinf(theta));
+            theta_base *= theta_scale;
+        }
+    }
+}
+
+// one CTA per token: rotate Q (-> fp16) and K (-> fp16 cache), copy V (-> fp16 cache)
+// qkv: [b][E + 2*GQA] fp32 (fused projection output);  mode 0: pairs (2i, 2i+1);  mode 2: pairs (i, i + hd/2)
+__global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8_t * __restrict__ desc,
+                                     const float2 * __restrict__ rope, int rope_n_pos, int E, int GQA, int hd, int mode,
+                                     __half * __restrict__ q16, __half * __restrict__ kcache, __half * __restrict__ vcache,
+                                     const int * __restrict__ cancel) {
+    const int32_t * hdr = reinterpret_cast<const int32_t *>(desc + PIB_DESC_HDR_OFF);
+    if (cancel && *cancel) return;
+    const int       t    = blockIdx.x;
+    const int       pos  = reinterpret_cast<const int32_t *>(desc + PIB_DESC_POS_OFF)[t];
+    const int       cell = hdr[PIB_DH_KVHEAD] + t;
+    const float *   row  = qkv + (size_t) t * (E + 2 * GQA);
+    const int       half = hd / 2;
+    const float2 *  cs   = rope + (size_t) min(pos, rope_n_pos - 1) * half;
+    const int       nq = E / 2, nk = GQA / 2;
+    for (int i = threadIdx.x; i < nq + nk; i += blockDim.x) {
+        const bool    isq  = i < nq;
+        const int     pi   = isq ? i : i - nq;          // pair index inside Q or K
+        const int     h    = pi / half, j = pi % half;
+        const float * src  = (isq ? row : row + E) + (size_t) h * hd;
+        const float2  c    = cs[j];
+        int i0, i1;
+        if (mode & 2) { i0 = j; i1 = j + half; } else { i0 = 2 * j; i1 = 2 * j + 1; }
+        const float x0 = src[i0], x1 = src[i1];
+        // unfused: the reference is built without fp contraction (-std=c11)
+        const float y0 = __fsub_rn(__fmul_rn(x0, c.x), __fmul_rn(x1, c.y));
+        const float y1 = __fadd_rn(__fmul_rn(x0, c.y), __fmul_rn(x1, c.x));
+        __half * dst = isq ? q16 + (size_t) t * E + (size_t) h * hd : kcache + (size_t) cell * GQA + (size_t) h * hd;
+        dst[i0] = __float2half_rn(y0);
+        dst[i1] = __float2half_rn(y1);
+    }
+    const float * v = row + E + GQA;
+    for (int i = threadIdx.x; i < GQA; i += blockDim.x) vcache[(size_t) cell * GQA + i] = __float2half_rn(v[i]);
+}
+
+// ---- attention ------------------------------------------------------------------------------------------------------
+// grid (n_head_kv, n_tokens); one CTA serves the G = n_head / n_head_kv query heads that share a KV head, for one
+// token, over all n cells: K and V of that head are read once per token (GQA broadcast, ggml.c:9567 i02 = i12 / r2).
+// Masked cells are skipped entirely (no K/V load): in a speculative run most cells of other partitions are masked.
+#define ATT_THREADS 256
+#define ATT_WARPS   (ATT_THREADS / 32)
+
+template <int HD, int G>
+__global__ void __launch_bounds__(ATT_THREADS) attention_kernel(const __half * __restrict__ q16, const __half * __restrict__ kcache,
+                                                                const __half * __restrict__ vcache,
+                                                                const uint8_t * __restrict__ mask, const int32_t * __restrict__ scalars,
+                                                                const uint8_t * __restrict__ desc, const uint16_t * __restrict__ exp_lut,
+                                                                int E, int GQA, int n_ctx, float kq_scale, float * __restrict__ out,
+                                                                const int * __restrict__ cancel) {
+    if (cancel && *cancel) return;
+    (void) desc;
+    extern __shared__ float smem[];
+    const int kvh = blockIdx.x, t = blockIdx.y;
+    const int n   = scalars[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int DPL = HD / 32;                 // dims per lane: 4 (hd 128) or 2 (hd 64)
+    float * s = smem;                            // [G][n] scores, then probabilities (fp16-rounded values)
+    const uint8_t * mrow = mask + (size_t) t * n_ctx;
+
+    // the lane's slice of the G query vectors, already rounded to fp16 by rope_kv_store
+    float q[G][DPL];
+#pragma unroll
+    for (int g = 0; g < G; g++)
+#pragma unroll
+        for (int j = 0; j < DPL; j++) q[g][j] = __half2float(q16[(size_t) t * E + (size_t) (kvh * G + g) * HD + lane * DPL + j]);
+
+    // phase 1: scores
+    for (int i = warp; i < n; i += ATT_WARPS) {
+        if (mrow[i]) {
+            if (lane < G) s[(size_t) lane * n + i] = -INFINITY;
+            continue;
+        }
+        const __half * kr = kcache + (size_t) i * GQA + (size_t) kvh * HD + lane * DPL;
+        float kf[DPL];
+        if (DPL == 4) {
+            const uint2 raw = *reinterpret_cast<const uint2 *>(kr);
+            const __half2 h0 = *reinterpret_cast<const __half2 *>(&raw.x), h1 = *reinterpret_cast<const __half2 *>(&raw.y);
+            kf[0] = __low2float(h0); kf[1] = __high2float(h0); kf[2] = __low2float(h1); kf[3] = __high2float(h1);
+        } else {
+            const __half2 h0 = *reinterpret_cast<const __half2 *>(kr);
+            kf[0] = __low2float(h0); kf[1] = __high2float(h0);
+        }
+        float acc[G];
+#pragma unroll
+        for (int g = 0; g < G; g++) {
+            float a = 0.f;
+#pragma unroll
+            for (int j = 0; j < DPL; j++) a = fmaf(kf[j], q[g][j], a);
+            acc[g] = a;
+        }
+#pragma unroll
+        for (int g = 0; g < G; g++) {
+            const float v = warp_sum(acc[g]);
+            if (lane == g) s[(size_t) g * n + i] = __fmul_rn(v, kq_scale);
+        }
+    }
+    __syncthreads();
+
+    // phase 2: softmax per query head (warp g -> head g, looping when G > ATT_WARPS is impossible: G <= 8)
+    for (int g = warp; g < G; g += ATT_WARPS) {
+        float * sg = s + (size_t) g * n;
+        float   mx = -INFINITY;
+        for (int i = lane; i < n; i += 32) mx = fmaxf(mx, sg[i]);
+        mx = warp_max(mx);
+        double sum = 0.0;
+        for (int i = lane; i < n; i += 32) {
+            const float x = sg[i];
+            float       v = 0.0f;
+            if (x != -INFINITY) {
+                v = pib_h2f(exp_lut[pib_f2h(__fsub_rn(x, mx))]);
+                sum += (double) v;
+            }
+            sg[i] = v;
+        }
+        sum = warp_sum_d(sum);                   // exact: fp16 values, <= 2^12 terms
+        const float inv = (float) (1.0 / sum);
+        for (int i = lane; i < n; i += 32) sg[i] = __half2float(__float2half_rn(__fmul_rn(sg[i], inv)));
+    }
+    __syncthreads();
+
+    // phase 3: O = V . P ; thread -> (cell group, pair of dims), fp32 accumulate, cross-group reduce in smem
+    constexpr int TPR = HD / 2;                  // threads per cell row (half2 each)
+    constexpr int NGR = ATT_THREADS / TPR;       // cell groups: 4 (hd 128) or 8 (hd 64)
+    const int grp = tid / TPR, dp = tid % TPR;
+    float o[G][2];
+#pragma unroll
+    for (int g = 0; g < G; g++) { o[g][0] = 0.f; o[g][1] = 0.f; }
+    for (int i = grp; i < n; i += NGR) {
+        if (mrow[i]) continue;
+        const __half2 vv = *reinterpret_cast<const __half2 *>(vcache + (size_t) i * GQA + (size_t) kvh * HD + dp * 2);
+        const float   v0 = __low2float(vv), v1 = __high2float(vv);
+#pragma unroll
+        for (int g = 0; g < G; g++) {
+            const float p = s[(size_t) g * n + i];
+            o[g][0] = fmaf(v0, p, o[g][0]);
+            o[g][1] = fmaf(v1, p, o[g][1]);
+        }
+    }
+    __syncthreads();
+    float * red = smem;                          // reuse: [NGR][G][HD]   (needs NGR*G*HD <= G*n floats or the extra tail)
+    float * redbuf = smem + (size_t) G * n;      // separate region sized by the launcher
+    (void) red;
+#pragma unroll
+    for (int g = 0; g < G; g++) {
+        redbuf[((size_t) grp * G + g) * HD + dp * 2]     = o[g][0];
+        redbuf[((size_t) grp * G + g) * HD + dp * 2 + 1] = o[g][1];
+    }
+    __syncthreads();
+    for (int j = tid; j < G * HD; j += ATT_THREADS) {
+        float a = 0.f;
+#pragma unroll
+        for (int r = 0; r < NGR; r++) a += redbuf[(size_t) r * G * HD + j];
+        const int g = j / HD, d = j % HD;
+        out[(size_t) t * E + (size_t) (kvh * G + g) * HD + d] = a;
+    }
+}
+
+template <int HD, int G>
+static int launch_att(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
+                      const uint8_t * desc, int E, int GQA, int n_ctx, int n_tokens, int n_head_kv, float * out,
+                      const int * cancel, cudaStream_t st) {
+    const size_t smem = ((size_t) G * n_ctx + (size_t) (ATT_THREADS / (HD / 2)) * G * HD) * sizeof(float);
+    static size_t configured = 0;
+    if (smem > configured) {
+        PIB_CHECK(cudaFuncSetAttribute(attention_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        configured = smem;
+    }
+    attention_kernel<HD, G><<<dim3(n_head_kv, n_tokens), ATT_THREADS, smem, st>>>(
+        q16, kc, vc, mask, scalars, desc, pib_get_luts().exp_f16, E, GQA, n_ctx, 1.0f / sqrtf((float) HD), out, cancel);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+
+int pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * rope, int rope_n_pos, int n_tokens, int E, int GQA,
+                      int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st) {
+    rope_kv_store_kernel<<<n_tokens, 256, 0, st>>>(qkv, desc, rope, rope_n_pos, E, GQA, hd, mode, q16, kc, vc, cancel);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+
+bool pib_attention_supported(int hd, int n_head, int n_head_kv, int n_ctx) {
+    if (hd != 64 && hd != 128) return false;
+    if (n_head % n_head_kv) return false;
+    const int G = n_head / n_head_kv;
+    if (G != 1 && G != 2 && G != 4 && G != 8) return false;
+    const size_t smem = ((size_t) G * n_ctx + (size_t) (ATT_THREADS / (hd / 2)) * G * hd) * sizeof(float);
+    return smem <= 220 * 1024;
+}
+
+int pib_attention(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
+                  const uint8_t * desc, int n_tokens, int n_head, int n_head_kv, int hd, int n_ctx, float * out,
+                  const int * cancel, cudaStream_t st) {
+    const int E = n_head * hd, GQA = n_head_kv * hd, G = n_head / n_head_kv;
+#define ATT_CASE(HDv, Gv) \
+    if (hd == HDv && G == Gv) return launch_att<HDv, Gv>(q16, kc, vc, mask, scalars, desc, E, GQA, n_ctx, n_tokens, n_head_kv, out, cancel, st);
+    ATT_CASE(128, 1) ATT_CASE(128, 2) ATT_CASE(128, 4) ATT_CASE(128, 8)
+    ATT_CASE(64, 1) ATT_CASE(64, 2) ATT_CASE(64, 4) ATT_CASE(64, 8)
+#undef ATT_CASE
+    pib_set_error("attention: unsupported head_dim %d / group %d", hd, G);
+    return PIB_ERR_UNSUPP;
+}

@@ -1,0 +1,600 @@
+// engine.cu -- model loading (GGUF / synthetic), context, and the decode path of one pipeline stage.
+//
+// Replaces, for the llama architecture, the reference's llm_load_tensors (llama.cpp:2684-2968), llama_new_context_with_model
+// (:8707), llama_decode_internal_phased (:5461-5848: phase 0 = enqueue, phase 1 = results) and build_llama (:3872-3980).
+// Kernel sequence per chunk of <= 16 tokens and per layer (fusion boundaries follow the reference's op order):
+//   [x = down + ffn_inp] -> RMSNorm*w -> quantise          act_quant.cu   (K9 + K4 + K2)
+//   Wq|Wk|Wv GEMV (one launch, rows concatenated)          gemv_*.cu      (K1)
+//   RoPE(Q,K) -> fp16 Q, K/V cache store                   attention.cu   (K5 + K6)
+//   masked multi-sequence attention                        attention.cu   (K7)
+//   quantise -> Wo GEMV                                    (K2 + K1)
+//   ffn_inp = o + x -> RMSNorm*w -> quantise               (K9 + K4 + K2)
+//   Wgate|Wup GEMV -> silu(gate)*up -> quantise -> Wdown   (K1 + K8 + K2 + K1)
+// then final RMSNorm -> lm_head GEMV -> argmax/top-8 on the device (K10).
+#include "engine.cuh"
+#include "gguf.cuh"
+
+#include <math.h>
+#include <string.h>
+#include <sys/time.h>
+
+#include <algorithm>
+
+// kernels implemented in the other translation units
+int  pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, const int * cancel, cudaStream_t st);
+int  pib_silu_mul_quantize_act(int wtype, const float * gate_dev, const float * up_dev, int64_t row_stride, int b, int64_t K,
+                               void * act_dev, const int * cancel, cudaStream_t st);
+int  pib_quantize_act_c(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, const int * cancel, cudaStream_t st);
+int  pib_add_rmsnorm_quantize_act(int wtype, const float * x_dev, const float * addend_dev, float * sum_out_dev,
+                                  const float * norm_w_dev, float eps, int b, int64_t K, void * act_dev, const int * cancel, cudaStream_t st);
+void rope_table_build(std::vector<float2> & tab, int n_pos, int n_dims, int mode, float freq_base, float freq_scale);
+int  pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * rope, int rope_n_pos, int n_tokens, int E, int GQA,
+                       int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st);
+bool pib_attention_supported(int hd, int n_head, int n_head_kv, int n_ctx);
+int  pib_attention(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
+                   const uint8_t * desc, int n_tokens, int n_head, int n_head_kv, int hd, int n_ctx, float * out, const int * cancel,
+                   cudaStream_t st);
+int  pib_sample_topk(float * logits_dev, int n_rows, int n_vocab, const int32_t * bias_ids_dev, const float * bias_val_dev, int n_bias,
+                     void * out_dev, const uint8_t * desc, const int * cancel, cudaStream_t st);
+pib_weight * pib_weight_alloc(int type, int64_t N, int64_t K);
+
+static int64_t now_us() {
+    struct timeval tv;
+    gettimeofday(&tv, nullptr);
+    return (int64_t) tv.tv_sec * 1000000 + tv.tv_usec;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// model: GGUF
+static float * upload_f32(const GgufTensor * t, int64_t n) {
+    if (!t || t->type != 0 || t->ne[0] != n) return nullptr;
+    float * d = nullptr;
+    if (cudaMalloc(&d, (size_t) n * 4) != cudaSuccess) return nullptr;
+    cudaMemcpy(d, t->data, (size_t) n * 4, cudaMemcpyHostToDevice);
+    return d;
+}
+
+static size_t row_bytes_of(int type, int64_t K) {
+    switch (type) {
+        case PIB_TYPE_Q4_0: return (size_t) (K / 32) * 18;
+        case PIB_TYPE_Q8_0: return (size_t) (K / 32) * 34;
+        case PIB_TYPE_Q4_K: return (size_t) (K / 256) * 144;
+    }
+    return 0;
+}
+
+// upload the row-wise concatenation of several [N_i][K] tensors as one matrix
+static pib_weight * upload_concat(const std::vector<const GgufTensor *> & ts, int wtype, int64_t K) {
+    int64_t N = 0;
+    for (auto t : ts) {
+        if (!t || t->type != wtype || t->ne[0] != K) return nullptr;
+        N += t->ne[1];
+    }
+    if (ts.size() == 1) return pib_weight_upload(wtype, ts[0]->data, N, K);
+    const size_t rb = row_bytes_of(wtype, K);
+    std::vector<uint8_t> tmp((size_t) N * rb);
+    size_t off = 0;
+    for (auto t : ts) { memcpy(tmp.data() + off, t->data, (size_t) t->ne[1] * rb); off += (size_t) t->ne[1] * rb; }
+    return pib_weight_upload(wtype, tmp.data(), N, K);
+}
+
+pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_end, bool want_embd, bool want_output) {
+    GgufFile g;
+    if (!g.open(path)) { pib_set_error("gguf: %s", g.error.c_str()); return nullptr; }
+    const std::string arch = g.get_s("general.architecture", "");
+    if (arch != "llama") { pib_set_error("gguf: architecture '%s' not supported (llama only)", arch.c_str()); return nullptr; }
+    pib_model * m = new pib_model();
+    m->name        = g.get_s("general.name", "");
+    m->n_layer     = (int) g.get_i(arch + ".block_count", 0);
+    m->n_embd      = (int) g.get_i(arch + ".embedding_length", 0);
+    m->n_head      = (int) g.get_i(arch + ".attention.head_count", 0);
+    m->n_head_kv   = (int) g.get_i(arch + ".attention.head_count_kv", m->n_head);
+    m->n_ff        = (int) g.get_i(arch + ".feed_forward_length", 0);
+    m->n_ctx_train = (int) g.get_i(arch + ".context_length", 2048);
+    m->n_rot       = (int) g.get_i(arch + ".rope.dimension_count", m->n_head ? m->n_embd / m->n_head : 0);
+    m->rms_eps        = (float) g.get_f(arch + ".attention.layer_norm_rms_epsilon", 1e-5);
+    m->rope_freq_base = (float) g.get_f(arch + ".rope.freq_base", 10000.0);
+    m->tok_bos = (int) g.get_i("tokenizer.ggml.bos_token_id", 1);
+    m->tok_eos = (int) g.get_i("tokenizer.ggml.eos_token_id", 2);
+    if (g.kv.count("tokenizer.ggml.tokens")) m->tok_text = g.kv["tokenizer.ggml.tokens"].arr_s;
+    if (g.kv.count("tokenizer.ggml.scores")) for (double f : g.kv["tokenizer.ggml.scores"].arr_f) m->tok_score.push_back((float) f);
+    if (g.kv.count("tokenizer.ggml.token_type")) for (int64_t i : g.kv["tokenizer.ggml.token_type"].arr_i) m->tok_type.push_back((int32_t) i);
+    const GgufTensor * emb = g.tensor("token_embd.weight");
+    if (!emb || m->n_layer <= 0 || m->n_embd <= 0 || m->n_head <= 0) { pib_set_error("gguf: missing hyper-parameters / token_embd"); delete m; return nullptr; }
+    m->n_vocab = (int) emb->ne[1];
+    m->wtype   = emb->type;
+    if (m->wtype != PIB_TYPE_Q4_0 && m->wtype != PIB_TYPE_Q8_0 && m->wtype != PIB_TYPE_Q4_K) {
+        pib_set_error("gguf: tensor type %d not supported (Q4_0, Q8_0, Q4_K; make the file with quantize --pure)", m->wtype);
+        delete m;
+        return nullptr;
+    }
+    if (layer_end <= 0 || layer_end > m->n_layer) layer_end = m->n_layer;
+    m->layer_begin = layer_begin;
+    m->layer_end   = layer_end;
+    m->layers.resize(m->n_layer);
+    const int E = m->n_embd, FF = m->n_ff;
+    bool ok = true;
+    if (want_embd) { m->tok_embd = upload_concat({ emb }, m->wtype, E); ok = ok && m->tok_embd; }
+    if (want_output) {
+        m->output_norm = upload_f32(g.tensor("output_norm.weight"), E);
+        m->output      = upload_concat({ g.tensor("output.weight") }, m->wtype, E);
+        ok = ok && m->output_norm && m->output;
+    }
+    for (int il = layer_begin; il < layer_end && ok; il++) {
+        const std::string p = "blk." + std::to_string(il) + ".";
+        pib_layer & L = m->layers[il];
+        L.attn_norm = upload_f32(g.tensor(p + "attn_norm.weight"), E);
+        L.ffn_norm  = upload_f32(g.tensor(p + "ffn_norm.weight"), E);
+        L.wqkv  = upload_concat({ g.tensor(p + "attn_q.weight"), g.tensor(p + "attn_k.weight"), g.tensor(p + "attn_v.weight") }, m->wtype, E);
+        L.wo    = upload_concat({ g.tensor(p + "attn_output.weight") }, m->wtype, E);
+        L.wgu   = upload_concat({ g.tensor(p + "ffn_gate.weight"), g.tensor(p + "ffn_up.weight") }, m->wtype, E);
+        L.wdown = upload_concat({ g.tensor(p + "ffn_down.weight") }, m->wtype, FF);
+        ok = L.attn_norm && L.ffn_norm && L.wqkv && L.wo && L.wgu && L.wdown;
+        if (ok) m->weight_bytes += pib_weight_bytes(L.wqkv) + pib_weight_bytes(L.wo) + pib_weight_bytes(L.wgu) + pib_weight_bytes(L.wdown);
+    }
+    if (!ok) {
+        if (!*pib_last_error()) pib_set_error("gguf: missing or mistyped tensor");
+        pib_model_free(m);
+        return nullptr;
+    }
+    if (m->output) m->weight_bytes += pib_weight_bytes(m->output);
+    return m;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// model: synthetic (random init generated directly as quantised blocks on the device)
+__device__ __forceinline__ uint32_t hash32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ uint32_t hash3(uint32_t seed, uint32_t a, uint32_t b) { return hash32(seed ^ hash32(a * 0x9E3779B9U + hash32(b + 0x85ebca6bU))); }
+
+// one thread per 16 bytes of the qs plane / per scale entry; `rowmap` (optional) gives the logical row whose random
+// stream a physical row uses (token_embd row t and output row pi(t) share one stream in the bigram flavour)
+__global__ void synth_fill_kernel(int type, uint8_t * qs, uint16_t * d, int64_t N, int64_t K, uint32_t seed, const int32_t * rowmap,
+                                  float dscale) {
+    const int64_t qs_row = type == PIB_TYPE_Q8_0 ? K : K / 2;
+    const int64_t nq     = N * qs_row / 16;
+    const int64_t i      = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nq) {
+        const int64_t  row = i / (qs_row / 16), c = i % (qs_row / 16);
+        const uint32_t lr  = rowmap ? (uint32_t) rowmap[row] : (uint32_t) row;
+        uint4 v;
+        v.x = hash3(seed, lr, (uint32_t) (c * 4 + 0)); v.y = hash3(seed, lr, (uint32_t) (c * 4 + 1));
+        v.z = hash3(seed, lr, (uint32_t) (c * 4 + 2)); v.w = hash3(seed, lr, (uint32_t) (c * 4 + 3));
+        reinterpret_cast<uint4 *>(qs)[i] = v;
+    }
+    const int64_t nd = type == PIB_TYPE_Q4_K ? N * (K / 256) : N * (K / 32);
+    if (i < nd) {
+        const int64_t  bpr = type == PIB_TYPE_Q4_K ? K / 256 : K / 32;
+        const int64_t  row = i / bpr, c = i % bpr;
+        const uint32_t lr  = rowmap ? (uint32_t) rowmap[row] : (uint32_t) row;
+        const uint32_t h   = hash3(seed ^ 0xA5A5A5A5u, lr, (uint32_t) c);
+        const float    u   = 0.5f + (float) (h & 0xffff) / 65536.0f;       // U(0.5, 1.5)
+        if (type != PIB_TYPE_Q4_K) {
+            // Q8_0: value = d * q, q ~ U{-128..127} (std 74);  Q4_0: d * (q - 8) (std 4.6)
+            const float dd = type == PIB_TYPE_Q8_0 ? dscale * u / 74.0f : dscale * u / 4.6f;
+            d[i] = __half_as_ushort(__float2half_rn(dd));
+        } else {
+            // value = d*sc*q - dmin*m with m = sc and dmin = 7.5*d  =>  d*sc*(q - 7.5): zero mean, std = d*sc*4.6
+            uint8_t * hdr = reinterpret_cast<uint8_t *>(d) + i * 16;
+            const float dd = dscale * u / (32.0f * 4.6f);
+            const uint16_t hd = __half_as_ushort(__float2half_rn(dd)), hm = __half_as_ushort(__float2half_rn(7.5f * __half2float(__float2half_rn(dd))));
+            hdr[0] = hd & 0xff; hdr[1] = hd >> 8; hdr[2] = hm & 0xff; hdr[3] = hm >> 8;
+            uint8_t s[8];
+            for (int j = 0; j < 8; j++) s[j] = 16 + (hash3(seed ^ 0x5C5C5C5Cu, lr, (uint32_t) (c * 8 + j)) & 31);   // 16..47
+            uint8_t * q = hdr + 4;
+            for (int j = 0; j < 4; j++) { q[j] = s[j] | ((s[j + 4] >> 4) << 6); q[j + 4] = s[j] | ((s[j + 4] >> 4) << 6); }
+            for (int j = 4; j < 8; j++) q[j + 4] = (s[j] & 0xF) | ((s[j] & 0xF) << 4);
+        }
+    }
+}
+
+static pib_weight * synth_weight(int type, int64_t N, int64_t K, uint32_t seed, const int32_t * rowmap_dev, float dscale) {
+    pib_weight * w = pib_weight_alloc(type, N, K);
+    if (!w) return nullptr;
+    const int64_t qs_row = type == PIB_TYPE_Q8_0 ? K : K / 2;
+    const int64_t n      = N * qs_row / 16;
+    synth_fill_kernel<<<(unsigned) ((n + 255) / 256), 256>>>(type, w->qs, w->d, N, K, seed, rowmap_dev, dscale);
+    if (cudaGetLastError() != cudaSuccess) { pib_weight_free(w); return nullptr; }
+    return w;
+}
+
+static float * const_f32(int64_t n, float v) {
+    std::vector<float> h((size_t) n, v);
+    float * d = nullptr;
+    if (cudaMalloc(&d, (size_t) n * 4) != cudaSuccess) return nullptr;
+    cudaMemcpy(d, h.data(), (size_t) n * 4, cudaMemcpyHostToDevice);
+    return d;
+}
+
+// flavour 0: iid weights.  flavour 1: "bigram": token_embd[t] = g_t and output[pi(t)] = g_t, layer weights small, so
+// the model predicts pi(last token); a draft built with agree < 1 uses pi on a fraction `agree` of the tokens and a
+// cyclic shift of pi on the rest, giving a known per-token acceptance probability.
+pib_model * pib_model_synthetic(int n_layer, int n_embd, int n_head, int n_head_kv, int n_ff, int n_vocab, int wtype, uint64_t seed,
+                                int flavour, float agree, int layer_begin, int layer_end, bool want_embd, bool want_output) {
+    const int blk = wtype == PIB_TYPE_Q4_K ? 256 : 32;
+    if (n_embd % blk || n_ff % blk || n_embd % n_head || n_head % n_head_kv) { pib_set_error("synthetic model: bad shape"); return nullptr; }
+    pib_model * m = new pib_model();
+    m->name = "synthetic";
+    m->n_layer = n_layer; m->n_embd = n_embd; m->n_head = n_head; m->n_head_kv = n_head_kv; m->n_ff = n_ff; m->n_vocab = n_vocab;
+    m->n_rot = n_embd / n_head; m->n_ctx_train = 4096; m->wtype = wtype;
+    if (layer_end <= 0 || layer_end > n_layer) layer_end = n_layer;
+    m->layer_begin = layer_begin; m->layer_end = layer_end;
+    m->layers.resize(n_layer);
+    const int E = n_embd, GQA = m->n_embd_gqa(), FF = n_ff;
+    // permutations are a function of the vocabulary size only (shared by target and draft)
+    std::vector<int32_t> pi(n_vocab), inv(n_vocab);
+    {
+        uint64_t s = 0x9E3779B97F4A7C15ull ^ (uint64_t) n_vocab;
+        auto rnd = [&]() { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return s; };
+        for (int i = 0; i < n_vocab; i++) pi[i] = i;
+        for (int i = n_vocab - 1; i > 0; i--) { int j = (int) (rnd() % (uint64_t) (i + 1)); std::swap(pi[i], pi[j]); }
+        if (agree < 1.0f) {
+            std::vector<int> dis;
+            uint64_t s2 = 0xD1B54A32D192ED03ull ^ (uint64_t) n_vocab;
+            auto rnd2 = [&]() { s2 ^= s2 << 13; s2 ^= s2 >> 7; s2 ^= s2 << 17; return s2; };
+            for (int t = 0; t < n_vocab; t++) if ((double) (rnd2() % 1000000) / 1e6 >= agree) dis.push_back(t);
+            if (dis.size() > 1) {
+                const int32_t first = pi[dis[0]];
+                for (size_t k = 0; k + 1 < dis.size(); k++) pi[dis[k]] = pi[dis[k + 1]];
+                pi[dis.back()] = first;
+            }
+        }
+        for (int t = 0; t < n_vocab; t++) inv[pi[t]] = t;
+    }
+    int32_t * inv_dev = nullptr;
+    cudaMalloc(&inv_dev, (size_t) n_vocab * 4);
+    cudaMemcpy(inv_dev, inv.data(), (size_t) n_vocab * 4, cudaMemcpyHostToDevice);
+    const uint32_t s32   = (uint32_t) (seed * 2654435761u);
+    const float    lstd  = flavour == 1 ? 0.02f * 0.25f : 0.02f;       // layer weight std
+    const uint32_t embseed = flavour == 1 ? 0xE3B0C442u : s32 ^ 0x11111111u;   // bigram: the same g_t for target and draft
+    bool ok = true;
+    if (want_embd) { m->tok_embd = synth_weight(wtype, n_vocab, E, embseed, nullptr, flavour == 1 ? 1.0f : 0.02f); ok = ok && m->tok_embd; }
+    if (want_output) {
+        m->output_norm = const_f32(E, 1.0f);
+        m->output = flavour == 1 ? synth_weight(wtype, n_vocab, E, embseed, inv_dev, 1.0f) : synth_weight(wtype, n_vocab, E, s32 ^ 0x22222222u, nullptr, 0.02f);
+        ok = ok && m->output && m->output_norm;
+    }
+    for (int il = layer_begin; il < layer_end && ok; il++) {
+        pib_layer & L = m->layers[il];
+        const uint32_t ls = s32 ^ (uint32_t) (il * 7919 + 13);
+        L.attn_norm = const_f32(E, 1.0f);
+        L.ffn_norm  = const_f32(E, 1.0f);
+        L.wqkv  = synth_weight(wtype, E + 2 * GQA, E, ls ^ 0x1u, nullptr, lstd);
+        L.wo    = synth_weight(wtype, E, E, ls ^ 0x2u, nullptr, lstd);
+        L.wgu   = synth_weight(wtype, 2 * FF, E, ls ^ 0x3u, nullptr, lstd);
+        L.wdown = synth_weight(wtype, E, FF, ls ^ 0x4u, nullptr, lstd);
+        ok = L.attn_norm && L.ffn_norm && L.wqkv && L.wo && L.wgu && L.wdown;
+        if (ok) m->weight_bytes += pib_weight_bytes(L.wqkv) + pib_weight_bytes(L.wo) + pib_weight_bytes(L.wgu) + pib_weight_bytes(L.wdown);
+    }
+    cudaDeviceSynchronize();
+    cudaFree(inv_dev);
+    if (!ok || cudaGetLastError() != cudaSuccess) {
+        if (!*pib_last_error()) pib_set_error("synthetic model: allocation failed");
+        pib_model_free(m);
+        return nullptr;
+    }
+    if (m->output) m->weight_bytes += pib_weight_bytes(m->output);
+    return m;
+}
+
+void pib_model_free(pib_model * m) {
+    if (!m) return;
+    pib_weight_free(m->tok_embd);
+    pib_weight_free(m->output);
+    if (m->output_norm) cudaFree(m->output_norm);
+    for (auto & L : m->layers) {
+        if (L.attn_norm) cudaFree(L.attn_norm);
+        if (L.ffn_norm) cudaFree(L.ffn_norm);
+        pib_weight_free(L.wqkv); pib_weight_free(L.wo); pib_weight_free(L.wgu); pib_weight_free(L.wdown);
+    }
+    delete m;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// context
+#define CK(expr) do { if ((expr) != cudaSuccess) { pib_set_error("%s:%d %s: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(cudaGetLastError())); goto fail; } } while (0)
+
+pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_stage stage) {
+    if (!pib_attention_supported(m->head_dim(), m->n_head, m->n_head_kv, (int) n_ctx)) {
+        pib_set_error("context: head_dim %d / n_head %d / n_head_kv %d / n_ctx %u not supported by the attention kernel",
+                      m->head_dim(), m->n_head, m->n_head_kv, n_ctx);
+        return nullptr;
+    }
+    pib_context * c = new pib_context();
+    c->model = m; c->n_ctx = n_ctx; c->max_seq = max_seq < 1 ? 1 : max_seq; c->n_words = (c->max_seq + 31) / 32; c->stage = stage;
+    c->t_start_us = now_us();
+    const int    E = m->n_embd, GQA = m->n_embd_gqa(), FF = m->n_ff, B = PIB_CHUNK;
+    const int    nl = m->layer_end - m->layer_begin;
+    const size_t kvb = (size_t) nl * n_ctx * GQA * sizeof(__half);
+    int lo, hi;
+    std::vector<float2> tab;
+    size_t actb;
+    CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CK(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, lo));
+    CK(cudaStreamCreateWithPriority(&c->ctrl, cudaStreamNonBlocking, hi));
+    c->kv.init(n_ctx, c->max_seq);
+    if (kv_device_init(&c->kvd, n_ctx, c->n_words) != PIB_OK) goto fail;
+    CK(cudaMalloc(&c->kcache, kvb ? kvb : 16));
+    CK(cudaMalloc(&c->vcache, kvb ? kvb : 16));
+    CK(cudaMemset(c->kcache, 0, kvb));
+    CK(cudaMemset(c->vcache, 0, kvb));
+    CK(cudaMalloc(&c->x, (size_t) B * E * 4));
+    CK(cudaMalloc(&c->x2, (size_t) B * E * 4));
+    CK(cudaMalloc(&c->qkv, (size_t) B * (E + 2 * GQA) * 4));
+    CK(cudaMalloc(&c->att, (size_t) B * E * 4));
+    CK(cudaMalloc(&c->proj, (size_t) B * E * 4));
+    CK(cudaMalloc(&c->gu, (size_t) B * 2 * FF * 4));
+    CK(cudaMalloc(&c->q16, (size_t) B * E * 2));
+    CK(cudaMalloc(&c->mask, (size_t) B * n_ctx));
+    actb = std::max(pib_act_bytes(m->wtype, E, B), pib_act_bytes(m->wtype, FF, B));
+    CK(cudaMalloc(&c->act, actb));
+    c->rope_n_pos = (int) std::max<uint32_t>(n_ctx, (uint32_t) m->n_ctx_train) + 64;
+    rope_table_build(tab, c->rope_n_pos, m->n_rot, 0, m->rope_freq_base, m->rope_freq_scale);
+    CK(cudaMalloc(&c->rope, tab.size() * sizeof(float2)));
+    CK(cudaMemcpy(c->rope, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&c->cancel_table, 65536 * sizeof(int) + 16));
+    CK(cudaMemset(c->cancel_table, 0, 65536 * sizeof(int) + 16));
+    c->cancel_one = c->cancel_table + 65536;
+    { int one = 1; CK(cudaMemcpy(c->cancel_one, &one, 4, cudaMemcpyHostToDevice)); }
+    c->desc_stride = pib_desc_stride(c->n_words);
+    c->desc_slots  = 256;
+    CK(cudaMallocHost(&c->desc_host, c->desc_stride * c->desc_slots));
+    CK(cudaMalloc(&c->desc_dev, c->desc_stride * c->desc_slots));
+    c->desc_ev.assign(c->desc_slots, nullptr);
+    c->ops_cap = 1 << 16;
+    CK(cudaMallocHost(&c->ops_host, sizeof(KvOp) * c->ops_cap));
+    CK(cudaMalloc(&c->ops_dev, sizeof(KvOp) * c->ops_cap));
+    c->runs.resize(64);
+    for (int i = 0; i < (int) c->runs.size(); i++) c->runs[i].id = i;
+    return c;
+fail:
+    pib_context_free(c);
+    return nullptr;
+}
+
+void pib_context_free(pib_context * c) {
+    if (!c) return;
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    kv_device_free(&c->kvd);
+    void * bufs[] = { c->kcache, c->vcache, c->x, c->x2, c->qkv, c->att, c->proj, c->gu, c->q16, c->mask, c->act, c->rope,
+                      c->cancel_table, c->desc_dev, c->ops_dev, c->bias_ids_dev, c->bias_val_dev };
+    for (void * b : bufs) if (b) cudaFree(b);
+    if (c->desc_host) cudaFreeHost(c->desc_host);
+    if (c->ops_host) cudaFreeHost(c->ops_host);
+    for (auto & r : c->runs) {
+        if (r.done) cudaEventDestroy(r.done);
+        if (r.logits) cudaFree(r.logits);
+        if (r.res_dev) cudaFree(r.res_dev);
+        if (r.res_host) cudaFreeHost(r.res_host);
+    }
+    for (auto e : c->desc_ev) if (e) cudaEventDestroy(e);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->ctrl) cudaStreamDestroy(c->ctrl);
+    delete c;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// KV op-log front end: see kvlog_* in kv_meta.cu (lazy, coalescing; shared with the CPU-only test hooks)
+void pib_kv_push(pib_context * c, const KvOp & op) { kvlog_push(c->pending, op); }
+void pib_kv_flush_host(pib_context * c) { kvlog_flush(c->kv, c->pending, c->devops); }
+static std::vector<KvOp> & devq(pib_context * c) { return c->devops; }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// decode
+static int take_desc_slot(pib_context * c) {
+    const int s = c->desc_next;
+    c->desc_next = (c->desc_next + 1) % c->desc_slots;
+    if (c->desc_ev[s]) cudaEventSynchronize(c->desc_ev[s]);
+    else cudaEventCreateWithFlags(&c->desc_ev[s], cudaEventDisableTiming);
+    return s;
+}
+
+__global__ void add_kernel(const float * __restrict__ a, const float * __restrict__ b, float * __restrict__ o, int64_t n,
+                           const int * __restrict__ cancel) {
+    if (cancel && *cancel) return;
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) o[i] = __fadd_rn(a[i], b[i]);
+}
+
+// hooks installed by pipeline.cu on multi-GPU runs (nullptr on a single GPU)
+int (*pib_hop_recv)(pib_context * c, float * x, int n_tokens, const int * cancel) = nullptr;
+int (*pib_hop_send)(pib_context * c, const float * x, int n_tokens, const int * cancel) = nullptr;
+
+static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int slot) {
+    pib_model *    m    = c->model;
+    const int      E = m->n_embd, GQA = m->n_embd_gqa(), FF = m->n_ff, hd = m->head_dim(), wt = m->wtype, var = c->gemv_variant;
+    cudaStream_t   st   = c->stream;
+    const uint8_t * desc = c->desc_dev + (size_t) slot * c->desc_stride;
+    const int *    cancel = c->cancel_table + (run.batch_id & 0xffff);
+    const int32_t * tok  = reinterpret_cast<const int32_t *>(desc + PIB_DESC_TOK_OFF);
+    const int32_t * tpos = reinterpret_cast<const int32_t *>(desc + PIB_DESC_POS_OFF);
+    const uint32_t * tbits = reinterpret_cast<const uint32_t *>(desc + PIB_DESC_BITS_OFF);
+    int rc;
+#define RC(e) do { rc = (e); if (rc != PIB_OK) return rc; c->n_kernels++; } while (0)
+    RC(kv_device_mask(&c->kvd, tpos, tbits, ntok, c->mask, st));
+    if (c->stage.first()) RC(pib_get_rows(m->tok_embd, tok, ntok, c->x, st));
+    else if (pib_hop_recv) RC(pib_hop_recv(c, c->x, ntok, cancel));
+    // x holds layer_inp; `pending_add` = a down-projection result still to be added to x2 (ffn_inp) to form the next x
+    bool pending_add = false;
+    for (int il = m->layer_begin; il < m->layer_end; il++) {
+        const pib_layer & L  = m->layers[il];
+        const size_t      lo = (size_t) (il - m->layer_begin) * c->n_ctx * GQA;
+        if (pending_add) RC(pib_add_rmsnorm_quantize_act(wt, c->proj, c->x2, c->x, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
+        else             RC(pib_add_rmsnorm_quantize_act(wt, c->x, nullptr, nullptr, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
+        RC(pib_gemv_internal(L.wqkv, c->act, ntok, c->qkv, var, cancel, st));
+        RC(pib_rope_kv_store(c->qkv, desc, c->rope, c->rope_n_pos, ntok, E, GQA, hd, 0, c->q16, c->kcache + lo, c->vcache + lo, cancel, st));
+        RC(pib_attention(c->q16, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, desc, ntok, m->n_head, m->n_head_kv, hd,
+                         (int) c->n_ctx, c->att, cancel, st));
+        RC(pib_quantize_act_c(wt, c->att, ntok, E, c->act, cancel, st));
+        RC(pib_gemv_internal(L.wo, c->act, ntok, c->proj, var, cancel, st));
+        RC(pib_add_rmsnorm_quantize_act(wt, c->proj, c->x, c->x2, L.ffn_norm, m->rms_eps, ntok, E, c->act, cancel, st));   // x2 = ffn_inp
+        RC(pib_gemv_internal(L.wgu, c->act, ntok, c->gu, var, cancel, st));
+        RC(pib_silu_mul_quantize_act(wt, c->gu, c->gu + FF, 2 * (int64_t) FF, ntok, FF, c->act, cancel, st));
+        RC(pib_gemv_internal(L.wdown, c->act, ntok, c->proj, var, cancel, st));
+        pending_add = true;
+    }
+    if (c->stage.last()) {
+        if (pending_add) RC(pib_add_rmsnorm_quantize_act(wt, c->proj, c->x2, c->x, m->output_norm, m->rms_eps, ntok, E, c->act, cancel, st));
+        else             RC(pib_add_rmsnorm_quantize_act(wt, c->x, nullptr, nullptr, m->output_norm, m->rms_eps, ntok, E, c->act, cancel, st));
+        float * lg = run.logits + (size_t) chunk * PIB_CHUNK * m->n_vocab;
+        RC(pib_gemv_internal(m->output, c->act, ntok, lg, var, cancel, st));
+        RC(pib_sample_topk(lg, ntok, m->n_vocab, c->bias_ids_dev, c->bias_val_dev, c->n_bias, run.res_dev + (size_t) chunk * PIB_CHUNK,
+                           desc, cancel, st));
+    } else {
+        if (pending_add) {
+            const int64_t n = (int64_t) ntok * E;
+            add_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(c->proj, c->x2, c->x, n, cancel);
+            c->n_kernels++;
+        }
+        if (pib_hop_send) RC(pib_hop_send(c, c->x, ntok, cancel));
+    }
+#undef RC
+    return PIB_OK;
+}
+
+static pib_run * take_run(pib_context * c, int n_tokens) {
+    for (auto & r : c->runs) {
+        if (r.in_use || r.id == c->last_finished) continue;
+        if (!r.done) cudaEventCreateWithFlags(&r.done, cudaEventDisableTiming);
+        const int cap = ((n_tokens + PIB_CHUNK - 1) / PIB_CHUNK) * PIB_CHUNK;
+        if (c->stage.last() && r.cap_tokens < cap) {
+            if (r.logits) { cudaStreamSynchronize(c->stream); cudaFree(r.logits); cudaFree(r.res_dev); cudaFreeHost(r.res_host); }
+            r.logits = nullptr; r.res_dev = nullptr; r.res_host = nullptr;
+            if (cudaMalloc(&r.logits, (size_t) cap * c->model->n_vocab * 4) != cudaSuccess ||
+                cudaMalloc(&r.res_dev, (size_t) cap * sizeof(pib_row_result)) != cudaSuccess ||
+                cudaMallocHost(&r.res_host, (size_t) cap * sizeof(pib_row_result)) != cudaSuccess) {
+                pib_set_error("decode: out of memory for logits of %d tokens", cap);
+                cudaGetLastError();
+                return nullptr;
+            }
+            r.cap_tokens = cap;
+        }
+        return &r;
+    }
+    pib_set_error("decode: more than %zu runs in flight", c->runs.size());
+    return nullptr;
+}
+
+int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const int32_t * pos, const int32_t * n_seq_id,
+                     const int32_t * const * seq_id, int batch_id) {
+    if (n_tokens <= 0) { pib_set_error("decode: n_tokens == 0"); return -1; }
+    pib_model * m = c->model;
+    pib_kv_flush_host(c);
+    std::vector<KvOp> & dq = devq(c);
+    const int W = c->n_words;
+    // per-token sequence bitsets (the reference's SEQ_IDS message, ggml-mpi.c:318-334, as rows of n_words words)
+    std::vector<uint32_t> tb((size_t) n_tokens * W, 0u);
+    for (int i = 0; i < n_tokens; i++)
+        for (int j = 0; j < n_seq_id[i]; j++) {
+            const int s = seq_id[i][j];
+            if (s < 0 || s >= W * 32) { pib_set_error("decode: sequence id %d out of range (max_seq %d)", s, c->max_seq); return -1; }
+            tb[(size_t) i * W + (s >> 5)] |= 1u << (s & 31);
+        }
+    for (int i = 0; i < n_tokens; i++)
+        if (c->stage.first() && (token[i] < 0 || token[i] >= m->n_vocab)) { pib_set_error("decode: token id %d out of range", token[i]); return -1; }
+    // llama.cpp:5548-5571: head-reset heuristic, find_slot, attended range n
+    const bool found = kvlog_decode_begin(c->kv, dq, n_tokens, pos, tb.data());
+    pib_run *  run   = found ? take_run(c, n_tokens) : nullptr;
+    if (!found) pib_set_error("decode: no KV slot for %d tokens", n_tokens);
+    if (!run) return -1;      // bookkeeping done so far (flushed ops, head moves) stays queued for the device
+    const uint32_t head = c->kv.head;
+    const int n_chunks = (n_tokens + PIB_CHUNK - 1) / PIB_CHUNK;
+    std::vector<int> slots(n_chunks);
+    for (int ch = 0; ch < n_chunks; ch++) {
+        const int t0 = ch * PIB_CHUNK, nt = std::min(PIB_CHUNK, n_tokens - t0);
+        const int s  = take_desc_slot(c);
+        slots[ch]    = s;
+        uint8_t * d  = c->desc_host + (size_t) s * c->desc_stride;
+        int32_t * hdr = reinterpret_cast<int32_t *>(d + PIB_DESC_HDR_OFF);
+        memset(d, 0, c->desc_stride);
+        hdr[PIB_DH_NTOK] = nt; hdr[PIB_DH_KVHEAD] = (int32_t) (head + t0); hdr[PIB_DH_BATCHID] = batch_id; hdr[PIB_DH_NKV] = (int32_t) c->kv.n;
+        memcpy(d + PIB_DESC_TOK_OFF, token + t0, sizeof(int32_t) * nt);
+        memcpy(d + PIB_DESC_POS_OFF, pos + t0, sizeof(int32_t) * nt);
+        memcpy(d + PIB_DESC_BITS_OFF, tb.data() + (size_t) t0 * W, sizeof(uint32_t) * (size_t) nt * W);
+        dq.push_back({ KVOP_ALLOC, (int32_t) (head + t0), nt, (int32_t) c->kv.n, s, 0 });
+        cudaMemcpyAsync(c->desc_dev + (size_t) s * c->desc_stride, d, c->desc_stride, cudaMemcpyHostToDevice, c->stream);
+    }
+    dq.push_back({ KVOP_ADVANCE, n_tokens, 0, 0, 0, 0 });
+    kvlog_decode_end(c->kv, n_tokens);                                    // llama.cpp:5708-5713
+    // ship the op-log and replay it on the device
+    {
+        const int n = (int) dq.size();
+        if (n > c->ops_cap) { pib_set_error("decode: KV op-log overflow (%d ops)", n); return -1; }
+        if (c->ops_next + n > c->ops_cap) { cudaStreamSynchronize(c->stream); c->ops_next = 0; }
+        memcpy(c->ops_host + c->ops_next, dq.data(), sizeof(KvOp) * n);
+        cudaMemcpyAsync(c->ops_dev + c->ops_next, c->ops_host + c->ops_next, sizeof(KvOp) * n, cudaMemcpyHostToDevice, c->stream);
+        if (kv_device_apply(&c->kvd, c->ops_dev + c->ops_next, n, c->desc_dev, c->desc_stride, c->stream) != PIB_OK) return -1;
+        c->n_kernels++;
+        c->ops_next += n;
+        dq.clear();
+    }
+    run->in_use = true; run->batch_id = batch_id; run->n_tokens = n_tokens; run->failed = false;
+    for (int ch = 0; ch < n_chunks; ch++) {
+        const int nt = std::min(PIB_CHUNK, n_tokens - ch * PIB_CHUNK);
+        if (run_chunk(c, *run, ch, nt, slots[ch]) != PIB_OK) { run->failed = true; break; }
+        cudaEventRecord(c->desc_ev[slots[ch]], c->stream);
+    }
+    if (c->stage.last() && !run->failed)
+        cudaMemcpyAsync(run->res_host, run->res_dev, sizeof(pib_row_result) * (size_t) n_tokens, cudaMemcpyDeviceToHost, c->stream);
+    cudaEventRecord(run->done, c->stream);
+    c->inflight.push_back(run->id);
+    c->n_decode++;
+    return run->id;
+}
+
+bool pib_run_ready(pib_context * c, int run) {
+    if (run < 0 || run >= (int) c->runs.size() || !c->runs[run].in_use) return false;
+    return cudaEventQuery(c->runs[run].done) == cudaSuccess;
+}
+
+int pib_run_finish(pib_context * c, int run) {
+    if (run < 0 || run >= (int) c->runs.size() || !c->runs[run].in_use) { pib_set_error("finish: bad run handle"); return -1; }
+    pib_run & r = c->runs[run];
+    if (cudaEventSynchronize(r.done) != cudaSuccess) { pib_set_error("finish: %s", cudaGetErrorString(cudaGetLastError())); return -1; }
+    // the batch id may be reused from here on: drop its cancel flag (ordered after every kernel of the run)
+    cudaMemsetAsync(c->cancel_table + (r.batch_id & 0xffff), 0, sizeof(int), c->stream);
+    for (auto it = c->inflight.begin(); it != c->inflight.end(); ++it) if (*it == run) { c->inflight.erase(it); break; }
+    r.in_use         = false;
+    c->last_finished = run;     // its buffers stay reserved until the next finish (llama_get_logits_ith contract)
+    c->logits_row_valid.assign((size_t) r.n_tokens, 0);
+    return r.failed ? -1 : 0;
+}
+
+const pib_row_result * pib_last_results(pib_context * c) {
+    return c->last_finished >= 0 ? c->runs[c->last_finished].res_host : nullptr;
+}
+
+const float * pib_logits_row(pib_context * c, int i) {
+    if (c->last_finished < 0) return nullptr;
+    pib_run & r = c->runs[c->last_finished];
+    if (i < 0 || i >= r.n_tokens || !r.logits) return nullptr;
+    const size_t V = (size_t) c->model->n_vocab;
+    if (c->logits_host.size() < (size_t) r.n_tokens * V) c->logits_host.resize((size_t) r.n_tokens * V);
+    if (!c->logits_row_valid[i]) {
+        cudaMemcpyAsync(c->logits_host.data() + (size_t) i * V, r.logits + (size_t) i * V, V * 4, cudaMemcpyDeviceToHost, c->stream);
+        cudaStreamSynchronize(c->stream);
+        c->logits_row_valid[i] = 1;
+    }
+    return c->logits_host.data() + (size_t) i * V;
+}
+
+void pib_cancel(pib_context * c, const int32_t * batch_ids, int n) {
+    for (int i = 0; i < n; i++)
+        if (batch_ids[i] >= 0)
+            cudaMemcpyAsync(c->cancel_table + (batch_ids[i] & 0xffff), c->cancel_one, sizeof(int), cudaMemcpyDeviceToDevice, c->ctrl);
+}
+
+void pib_set_logit_bias(pib_context * c, const int32_t * ids, const float * vals, int n) {
+    cudaStreamSynchronize(c->stream);
+    if (c->bias_ids_dev) cudaFree(c->bias_ids_dev);
+    if (c->bias_val_dev) cudaFree(c->bias_val_dev);
+    c->bias_ids_dev = nullptr; c->bias_val_dev = nullptr; c->n_bias = 0;
+    if (n <= 0) return;
+    cudaMalloc(&c->bias_ids_dev, sizeof(int32_t) * n);
+    cudaMalloc(&c->bias_val_dev, sizeof(float) * n);
+    cudaMemcpy(c->bias_ids_dev, ids, sizeof(int32_t) * n, cudaMemcpyHostToDevice);
+    cudaMemcpy(c->bias_val_dev, vals, sizeof(float) * n, cudaMemcpyHostToDevice);
+    c->n_bias = n;
+}

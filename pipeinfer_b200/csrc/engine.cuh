@@ -1,0 +1,139 @@
+// engine.cuh -- model, context and run records of the host runtime (C++), shared by engine.cu / llama_api.cu /
+// pipeline.cu / speculative.cu.
+#pragma once
+
+#include "pib_common.cuh"
+#include "desc.cuh"
+#include "kv_meta.cuh"
+
+#include <deque>
+#include <string>
+#include <vector>
+
+#define PIB_TOPK 8
+struct pib_row_result {            // per logits row: sorted top-8 {id, logit, p}; entry 0 is the greedy token
+    int32_t id[PIB_TOPK];
+    float   logit[PIB_TOPK];
+    float   p[PIB_TOPK];
+};
+
+struct pib_layer {
+    float *      attn_norm = nullptr;   // [n_embd]
+    pib_weight * wqkv      = nullptr;   // rows: Wq (n_embd) | Wk (n_embd_gqa) | Wv (n_embd_gqa)
+    pib_weight * wo        = nullptr;
+    float *      ffn_norm  = nullptr;
+    pib_weight * wgu       = nullptr;   // rows: gate (n_ff) | up (n_ff)
+    pib_weight * wdown     = nullptr;
+};
+
+struct pib_model {
+    // hyper-parameters (reference llm_load_hparams, llama.cpp:2203-2290)
+    int   n_layer = 0, n_embd = 0, n_head = 0, n_head_kv = 0, n_ff = 0, n_vocab = 0, n_rot = 0, n_ctx_train = 0;
+    float rms_eps = 1e-5f, rope_freq_base = 10000.f, rope_freq_scale = 1.f;
+    int   wtype = 0;
+    int   tok_bos = 1, tok_eos = 2, tok_nl = 13;
+    // tensors (only those of the layer range this process owns are resident)
+    int          layer_begin = 0, layer_end = 0;
+    pib_weight * tok_embd    = nullptr;
+    float *      output_norm = nullptr;
+    pib_weight * output      = nullptr;
+    std::vector<pib_layer> layers;
+    // vocabulary (for llama_token_to_piece / the char-level prompt path)
+    std::vector<std::string> tok_text;
+    std::vector<float>       tok_score;
+    std::vector<int32_t>     tok_type;
+    std::string              name;
+    size_t                   weight_bytes = 0;     // algorithmic bytes of all resident matrices
+
+    int head_dim() const { return n_embd / n_head; }
+    int n_embd_gqa() const { return head_dim() * n_head_kv; }
+};
+
+struct pib_run {                   // one (possibly still executing) decode: the opaque handle of the async API
+    int          id        = -1;   // index in the context's run table
+    bool         in_use    = false;
+    int          batch_id  = 0;
+    int          n_tokens  = 0;
+    bool         failed    = false;
+    cudaEvent_t  done      = nullptr;
+    float *      logits    = nullptr;     // device [n_tokens][n_vocab]
+    pib_row_result * res_dev  = nullptr;  // device [n_tokens]
+    pib_row_result * res_host = nullptr;  // pinned [n_tokens]
+    int          cap_tokens = 0;
+};
+
+struct pib_stage {                 // pipeline position of this process (1-GPU: first && last)
+    int  rank = 0, size = 1;
+    bool first() const { return rank == 0; }
+    bool last() const { return rank == size - 1; }
+};
+
+struct pib_context {
+    pib_model *  model   = nullptr;
+    uint32_t     n_ctx   = 0;
+    int          max_seq = 1;
+    int          n_words = 1;
+    pib_stage    stage;
+    cudaStream_t stream  = nullptr;       // everything of this context runs in order on this stream
+    cudaStream_t ctrl    = nullptr;       // high-priority control stream: cancel flags overtake queued work
+    int          gemv_variant = 0;
+
+    KvMirror kv;                           // host mirror (lazy: pending ops are applied before any observation)
+    KvDevice kvd;
+    std::vector<KvOp> pending;             // API-level op-log not yet applied to mirror / device
+    std::vector<KvOp> devops;              // applied to the mirror, waiting to ride to the device with the next decode
+    __half * kcache = nullptr, * vcache = nullptr;     // [n_layer_local][n_ctx][n_embd_gqa]
+
+    // per-chunk work buffers
+    float * x = nullptr, * x2 = nullptr, * qkv = nullptr, * att = nullptr, * proj = nullptr, * gu = nullptr;
+    __half * q16 = nullptr;
+    uint8_t * mask = nullptr;
+    void *  act = nullptr;
+    float2 * rope = nullptr;
+    int      rope_n_pos = 0;
+    int *    cancel_table = nullptr;       // device int[65536], indexed by batch_id & 0xffff
+    int *    cancel_one   = nullptr;       // device int {1}: source of the cancel writes
+
+    // host->device staging rings (pinned host + device copies)
+    uint8_t * desc_host = nullptr, * desc_dev = nullptr;
+    size_t    desc_stride = 0;
+    int       desc_slots = 0, desc_next = 0;
+    std::vector<cudaEvent_t> desc_ev;
+    KvOp *    ops_host = nullptr, * ops_dev = nullptr;
+    int       ops_cap = 0, ops_next = 0;
+
+    // logit bias (e.g. EOS -> -inf) applied on the device before argmax
+    int32_t * bias_ids_dev = nullptr;
+    float *   bias_val_dev = nullptr;
+    int       n_bias = 0;
+
+    std::vector<pib_run> runs;
+    std::deque<int>      inflight;        // run ids in issue order
+    int                  last_finished = -1;
+    std::vector<float>   logits_host;     // lazily filled rows of the last finished run
+    std::vector<uint8_t> logits_row_valid;
+    bool                 logits_all = true;
+    uint64_t             n_kernels = 0;   // launches issued by this context (bench: gpu_launches)
+    uint64_t             n_decode  = 0;
+    int64_t              t_start_us = 0;
+};
+
+// engine.cu
+pib_model *   pib_model_load_gguf(const char * path, int layer_begin, int layer_end, bool want_embd, bool want_output);
+pib_model *   pib_model_synthetic(int n_layer, int n_embd, int n_head, int n_head_kv, int n_ff, int n_vocab, int wtype,
+                                  uint64_t seed, int flavour, float agree, int layer_begin, int layer_end, bool want_embd,
+                                  bool want_output);
+void          pib_model_free(pib_model * m);
+pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_stage stage);
+void          pib_context_free(pib_context * c);
+void          pib_kv_push(pib_context * c, const KvOp & op);          // API-level KV op (lazy, coalescing)
+void          pib_kv_flush_host(pib_context * c);                     // apply pending ops to the mirror + queue for device
+// start a decode of n_tokens tokens; returns run id or -1 (no KV slot / error)
+int  pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const int32_t * pos, const int32_t * n_seq_id,
+                      const int32_t * const * seq_id, int batch_id);
+bool pib_run_ready(pib_context * c, int run);
+int  pib_run_finish(pib_context * c, int run);                         // waits; makes results available; frees the slot
+const pib_row_result * pib_last_results(pib_context * c);
+const float *          pib_logits_row(pib_context * c, int i);         // lazy D2H of one row of the last finished run
+void pib_cancel(pib_context * c, const int32_t * batch_ids, int n);
+void pib_set_logit_bias(pib_context * c, const int32_t * ids, const float * vals, int n);

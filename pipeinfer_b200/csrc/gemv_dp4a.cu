@@ -28,7 +28,8 @@ __device__ __forceinline__ int dot8(const int4 & w0, const int4 & w1, const int4
 template <int B>
 __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q8_0_kernel(const int8_t * __restrict__ wqs, const uint16_t * __restrict__ wd,
                                                                   const int8_t * __restrict__ aqs, const float * __restrict__ ad,
-                                                                  float * __restrict__ y, int N, int K) {
+                                                                  float * __restrict__ y, int N, int K, const int * __restrict__ cancel) {
+    if (cancel && *cancel) return;
     const int lane = threadIdx.x & 31;
     const int row  = blockIdx.x * GV_WARPS + (threadIdx.x >> 5);
     if (row >= N) return;
@@ -61,7 +62,8 @@ __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q8_0_kernel(const int8_t *
 template <int B>
 __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q4_0_kernel(const uint8_t * __restrict__ wqs, const uint16_t * __restrict__ wd,
                                                                   const int8_t * __restrict__ aqs, const float * __restrict__ ad,
-                                                                  float * __restrict__ y, int N, int K) {
+                                                                  float * __restrict__ y, int N, int K, const int * __restrict__ cancel) {
+    if (cancel && *cancel) return;
     const int lane = threadIdx.x & 31;
     const int row  = blockIdx.x * GV_WARPS + (threadIdx.x >> 5);
     if (row >= N) return;
@@ -111,7 +113,8 @@ template <int B>
 __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q4_K_kernel(const uint8_t * __restrict__ wqs, const uint8_t * __restrict__ whdr,
                                                                   const int8_t * __restrict__ aqs, const float * __restrict__ ad,
                                                                   const int16_t * __restrict__ absum, float * __restrict__ y,
-                                                                  int N, int K) {
+                                                                  int N, int K, const int * __restrict__ cancel) {
+    if (cancel && *cancel) return;
     const int lane = threadIdx.x & 31;
     const int row  = blockIdx.x * GV_WARPS + (threadIdx.x >> 5);
     if (row >= N) return;
@@ -163,7 +166,7 @@ __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q4_K_kernel(const uint8_t 
 }
 
 template <int B>
-static void launch_b(const pib_weight * w, const uint8_t * act, const pib_act_layout & L, int t0, int b_total, float * y, cudaStream_t st) {
+static void launch_b(const pib_weight * w, const uint8_t * act, const pib_act_layout & L, int t0, int b_total, float * y, const int * cancel, cudaStream_t st) {
     const int     N = (int) w->N, K = (int) w->K;
     const dim3    grid((N + GV_WARPS - 1) / GV_WARPS), block(GV_WARPS * 32);
     const int8_t * aqs = (const int8_t *) (act + L.qs_off) + (size_t) t0 * K;
@@ -171,31 +174,31 @@ static void launch_b(const pib_weight * w, const uint8_t * act, const pib_act_la
     (void) b_total;
     if (w->type == PIB_TYPE_Q8_0) {
         const float * ad = (const float *) (act + L.d_off) + (size_t) t0 * (K / 32);
-        gemv_q8_0_kernel<B><<<grid, block, 0, st>>>((const int8_t *) w->qs, w->d, aqs, ad, yo, N, K);
+        gemv_q8_0_kernel<B><<<grid, block, 0, st>>>((const int8_t *) w->qs, w->d, aqs, ad, yo, N, K, cancel);
     } else if (w->type == PIB_TYPE_Q4_0) {
         const float * ad = (const float *) (act + L.d_off) + (size_t) t0 * (K / 32);
-        gemv_q4_0_kernel<B><<<grid, block, 0, st>>>(w->qs, w->d, aqs, ad, yo, N, K);
+        gemv_q4_0_kernel<B><<<grid, block, 0, st>>>(w->qs, w->d, aqs, ad, yo, N, K, cancel);
     } else {
         const float *   ad = (const float *) (act + L.d_off) + (size_t) t0 * (K / 256);
         const int16_t * bs = (const int16_t *) (act + L.bs_off) + (size_t) t0 * (K / 16);
-        gemv_q4_K_kernel<B><<<grid, block, 0, st>>>(w->qs, (const uint8_t *) w->d, aqs, ad, bs, yo, N, K);
+        gemv_q4_K_kernel<B><<<grid, block, 0, st>>>(w->qs, (const uint8_t *) w->d, aqs, ad, bs, yo, N, K, cancel);
     }
 }
 
-int pib_gemv_dp4a(const pib_weight * w, const void * act_dev, int b, float * y_dev, cudaStream_t st) {
+int pib_gemv_dp4a(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
     const pib_act_layout L   = pib_act_layout_of(w->type, w->K, b);
     const uint8_t *      act = (const uint8_t *) act_dev;
     for (int t0 = 0; t0 < b; t0 += 8) {
         const int nb = b - t0 < 8 ? b - t0 : 8;
         switch (nb) {
-            case 1: launch_b<1>(w, act, L, t0, b, y_dev, st); break;
-            case 2: launch_b<2>(w, act, L, t0, b, y_dev, st); break;
-            case 3: launch_b<3>(w, act, L, t0, b, y_dev, st); break;
-            case 4: launch_b<4>(w, act, L, t0, b, y_dev, st); break;
-            case 5: launch_b<5>(w, act, L, t0, b, y_dev, st); break;
-            case 6: launch_b<6>(w, act, L, t0, b, y_dev, st); break;
-            case 7: launch_b<7>(w, act, L, t0, b, y_dev, st); break;
-            default: launch_b<8>(w, act, L, t0, b, y_dev, st); break;
+            case 1: launch_b<1>(w, act, L, t0, b, y_dev, cancel, st); break;
+            case 2: launch_b<2>(w, act, L, t0, b, y_dev, cancel, st); break;
+            case 3: launch_b<3>(w, act, L, t0, b, y_dev, cancel, st); break;
+            case 4: launch_b<4>(w, act, L, t0, b, y_dev, cancel, st); break;
+            case 5: launch_b<5>(w, act, L, t0, b, y_dev, cancel, st); break;
+            case 6: launch_b<6>(w, act, L, t0, b, y_dev, cancel, st); break;
+            case 7: launch_b<7>(w, act, L, t0, b, y_dev, cancel, st); break;
+            default: launch_b<8>(w, act, L, t0, b, y_dev, cancel, st); break;
         }
     }
     PIB_CHECK(cudaGetLastError());

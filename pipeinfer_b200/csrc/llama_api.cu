@@ -1,0 +1,439 @@
+// llama_api.cu -- the llama.h-compatible C ABI (include/pipeinfer_llama.h) on top of the engine.
+#include "engine.cuh"
+#include "../../include/pipeinfer_llama.h"
+
+#include <string.h>
+#include <sys/time.h>
+
+#include <algorithm>
+#include <map>
+#include <queue>
+#include <string>
+#include <vector>
+
+struct llama_model {
+    pib_model * m = nullptr;
+    std::map<std::string, int32_t> tok_index;     // piece text -> id (built on first tokenize)
+};
+
+struct llama_context {
+    llama_model * model = nullptr;
+    pib_context * c     = nullptr;
+    std::vector<float> dummy_logits;
+};
+
+static void ensure_init() {
+    static bool done = false;
+    if (done) return;
+    int dev = 0;
+    const char * lr = getenv("LOCAL_RANK");
+    if (lr) dev = atoi(lr);
+    if (pib_init(dev) != PIB_OK) {
+        fprintf(stderr, "libpipeinfer_b200: %s\n", pib_last_error());
+        abort();      // the reference's hard failures are GGML_ASSERT -> abort; there is no CPU path
+    }
+    done = true;
+}
+
+extern "C" {
+
+struct llama_model_params llama_model_default_params(void) {
+    struct llama_model_params p;
+    memset(&p, 0, sizeof(p));
+    p.use_mmap = true;
+    return p;
+}
+
+struct llama_context_params llama_context_default_params(void) {
+    struct llama_context_params p;
+    memset(&p, 0, sizeof(p));
+    p.seed = 0xFFFFFFFFu; p.n_ctx = 512; p.n_batch = 512; p.n_threads = 4; p.n_threads_batch = 4; p.rope_scaling_type = -1;
+    p.yarn_ext_factor = -1.0f; p.yarn_attn_factor = 1.0f; p.yarn_beta_fast = 32.0f; p.yarn_beta_slow = 1.0f;
+    p.mul_mat_q = true; p.f16_kv = true;
+    return p;
+}
+
+void llama_backend_init(bool numa) { (void) numa; ensure_init(); }
+void llama_backend_free(void) {}
+
+struct llama_model * llama_load_model_from_file(const char * path_model, struct llama_model_params params) {
+    (void) params;
+    ensure_init();
+    pib_model * m = pib_model_load_gguf(path_model, 0, 0, true, true);
+    if (!m) { fprintf(stderr, "llama_load_model_from_file: %s\n", pib_last_error()); return nullptr; }
+    llama_model * lm = new llama_model();
+    lm->m = m;
+    return lm;
+}
+
+struct llama_model * llama_pib_synthetic_model(int n_layer, int n_embd, int n_head, int n_head_kv, int n_ff, int n_vocab,
+                                               int wtype, uint64_t seed, int flavour, float agree) {
+    ensure_init();
+    pib_model * m = pib_model_synthetic(n_layer, n_embd, n_head, n_head_kv, n_ff, n_vocab, wtype, seed, flavour, agree, 0, 0, true, true);
+    if (!m) { fprintf(stderr, "llama_pib_synthetic_model: %s\n", pib_last_error()); return nullptr; }
+    llama_model * lm = new llama_model();
+    lm->m = m;
+    return lm;
+}
+
+void llama_free_model(struct llama_model * model) {
+    if (!model) return;
+    pib_model_free(model->m);
+    delete model;
+}
+
+struct llama_context * llama_pib_new_context(struct llama_model * model, uint32_t n_ctx, int32_t max_seq_ids) {
+    if (!model) return nullptr;
+    pib_stage st;
+    pib_context * c = pib_context_new(model->m, n_ctx ? n_ctx : (uint32_t) model->m->n_ctx_train, max_seq_ids, st);
+    if (!c) { fprintf(stderr, "llama_new_context_with_model: %s\n", pib_last_error()); return nullptr; }
+    llama_context * lc = new llama_context();
+    lc->model = model;
+    lc->c     = c;
+    const char * v = getenv("PIB_GEMV_VARIANT");
+    if (v) c->gemv_variant = atoi(v);
+    return lc;
+}
+
+struct llama_context * llama_new_context_with_model(struct llama_model * model, struct llama_context_params params) {
+    // PipeInfer's scheduler uses sequence ids up to 1000*np + 1 (speculative.cpp:140-145); 4096 bits cover np <= 4
+    const char * ms = getenv("PIB_MAX_SEQ");
+    llama_context * lc = llama_pib_new_context(model, params.n_ctx, ms ? atoi(ms) : 4096);
+    if (lc) lc->c->logits_all = params.logits_all;
+    return lc;
+}
+
+void llama_free(struct llama_context * ctx) {
+    if (!ctx) return;
+    pib_context_free(ctx->c);
+    delete ctx;
+}
+
+int64_t llama_time_us(void) {
+    struct timeval tv;
+    gettimeofday(&tv, nullptr);
+    return (int64_t) tv.tv_sec * 1000000 + tv.tv_usec;
+}
+
+void llama_set_n_threads(struct llama_context * ctx, uint32_t a, uint32_t b) { (void) ctx; (void) a; (void) b; }
+
+const struct llama_model * llama_get_model(const struct llama_context * ctx) { return ctx->model; }
+int llama_n_ctx(const struct llama_context * ctx) { return (int) ctx->c->n_ctx; }
+int llama_n_vocab(const struct llama_model * model) { return model->m->n_vocab; }
+int llama_n_ctx_train(const struct llama_model * model) { return model->m->n_ctx_train; }
+int llama_n_embd(const struct llama_model * model) { return model->m->n_embd; }
+llama_token llama_token_bos(const struct llama_model * model) { return model->m->tok_bos; }
+llama_token llama_token_eos(const struct llama_model * model) { return model->m->tok_eos; }
+llama_token llama_token_nl(const struct llama_model * model) { return model->m->tok_nl; }
+int llama_add_bos_token(const struct llama_model * model) { (void) model; return -1; }
+size_t llama_pib_weight_bytes(const struct llama_model * model) { return model->m->weight_bytes; }
+
+// ---- tokenizer: SentencePiece-style bigram merging (reference llm_tokenizer_spm, llama.cpp:5970-6110) ----------------
+static size_t utf8_len(unsigned char c) { return c < 0x80 ? 1 : (c >> 5) == 6 ? 2 : (c >> 4) == 14 ? 3 : (c >> 3) == 30 ? 4 : 1; }
+
+int llama_tokenize(const struct llama_model * model, const char * text, int text_len, llama_token * tokens, int n_max_tokens,
+                   bool add_bos, bool special) {
+    (void) special;
+    llama_model * lm = const_cast<llama_model *>(model);
+    const pib_model * m = lm->m;
+    if (lm->tok_index.empty()) for (size_t i = 0; i < m->tok_text.size(); i++) lm->tok_index.emplace(m->tok_text[i], (int32_t) i);
+    std::vector<llama_token> out;
+    if (add_bos) out.push_back(m->tok_bos);
+    std::string s = " " + std::string(text, (size_t) text_len);        // SPM space prefix, then ' ' -> U+2581
+    std::string esc;
+    for (char ch : s) { if (ch == ' ') esc += "\xe2\x96\x81"; else esc += ch; }
+    if (text_len > 0) {
+        struct sym { size_t off, n; int prev, next; };
+        std::vector<sym> syms;
+        for (size_t off = 0; off < esc.size();) {
+            size_t n = std::min(utf8_len((unsigned char) esc[off]), esc.size() - off);
+            syms.push_back({ off, n, (int) syms.size() - 1, off + n >= esc.size() ? -1 : (int) syms.size() + 1 });
+            off += n;
+        }
+        struct bigram { int left, right; float score; size_t size; };
+        auto cmp = [](const bigram & a, const bigram & b) { return a.score < b.score || (a.score == b.score && a.left > b.left); };
+        std::priority_queue<bigram, std::vector<bigram>, decltype(cmp)> q(cmp);
+        auto try_add = [&](int l, int r) {
+            if (l < 0 || r < 0) return;
+            const std::string piece = esc.substr(syms[l].off, syms[l].n + syms[r].n);
+            auto it = lm->tok_index.find(piece);
+            if (it == lm->tok_index.end()) return;
+            q.push({ l, r, (size_t) it->second < m->tok_score.size() ? m->tok_score[it->second] : 0.f, piece.size() });
+        };
+        for (int i = 1; i < (int) syms.size(); i++) try_add(i - 1, i);
+        while (!q.empty()) {
+            bigram b = q.top(); q.pop();
+            sym & L = syms[b.left]; sym & R = syms[b.right];
+            if (L.n == 0 || R.n == 0 || L.n + R.n != b.size) continue;
+            L.n += R.n; R.n = 0;
+            L.next = R.next;
+            if (R.next >= 0) syms[R.next].prev = b.left;
+            try_add(L.prev, b.left);
+            try_add(b.left, L.next);
+        }
+        for (int i = 0; i != -1; i = syms[i].next) {
+            const std::string piece = esc.substr(syms[i].off, syms[i].n);
+            auto it = lm->tok_index.find(piece);
+            if (it != lm->tok_index.end()) { out.push_back(it->second); continue; }
+            for (unsigned char ch : piece) {                                  // byte fallback <0xXX>
+                char buf[8];
+                snprintf(buf, sizeof(buf), "<0x%02X>", ch);
+                auto bt = lm->tok_index.find(buf);
+                out.push_back(bt != lm->tok_index.end() ? bt->second : 0);
+            }
+        }
+    }
+    if ((int) out.size() > n_max_tokens) return -(int) out.size();
+    for (size_t i = 0; i < out.size(); i++) tokens[i] = out[i];
+    return (int) out.size();
+}
+
+int llama_token_to_piece(const struct llama_model * model, llama_token token, char * buf, int length) {
+    const pib_model * m = model->m;
+    if (token < 0 || (size_t) token >= m->tok_text.size()) return 0;
+    const int ty = (size_t) token < m->tok_type.size() ? m->tok_type[token] : 1;
+    std::string r;
+    if (ty == 1) {                       // normal: U+2581 -> ' '
+        const std::string & t = m->tok_text[token];
+        for (size_t i = 0; i < t.size();) {
+            if (i + 2 < t.size() && (unsigned char) t[i] == 0xE2 && (unsigned char) t[i + 1] == 0x96 && (unsigned char) t[i + 2] == 0x81) { r += ' '; i += 3; }
+            else r += t[i++];
+        }
+    } else if (ty == 6) {                // byte token <0xXX>
+        r = std::string(1, (char) strtol(m->tok_text[token].substr(3, 2).c_str(), nullptr, 16));
+    } else if (ty == 2) {
+        r = "\xe2\x96\x85";
+    }
+    if ((int) r.size() > length) return -(int) r.size();
+    memcpy(buf, r.data(), r.size());
+    return (int) r.size();
+}
+
+// ---- batches ----------------------------------------------------------------------------------------------------------
+struct llama_batch llama_batch_get_one(llama_token * tokens, int32_t n_tokens, llama_pos pos_0, llama_seq_id seq_id) {
+    struct llama_batch b;
+    memset(&b, 0, sizeof(b));
+    b.n_tokens = n_tokens; b.token = tokens; b.all_pos_0 = pos_0; b.all_pos_1 = 1; b.all_seq_id = seq_id; b.batch_id = 0; b.max_n_seq = 1;
+    return b;
+}
+
+struct llama_batch llama_batch_init(int32_t n_tokens, int32_t embd, int32_t n_seq_max) {
+    struct llama_batch b;
+    memset(&b, 0, sizeof(b));
+    b.max_n_seq = n_seq_max;
+    if (embd) b.embd = (float *) malloc(sizeof(float) * n_tokens * embd);
+    else      b.token = (llama_token *) malloc(sizeof(llama_token) * n_tokens);
+    b.pos      = (llama_pos *) malloc(sizeof(llama_pos) * n_tokens);
+    b.n_seq_id = (int32_t *) malloc(sizeof(int32_t) * n_tokens);
+    b.seq_id   = (llama_seq_id **) malloc(sizeof(llama_seq_id *) * n_tokens);
+    for (int i = 0; i < n_tokens; ++i) b.seq_id[i] = (llama_seq_id *) malloc(sizeof(llama_seq_id) * n_seq_max);
+    b.logits   = (int8_t *) malloc(sizeof(int8_t) * n_tokens);
+    return b;
+}
+
+void llama_batch_free(struct llama_batch & batch) {
+    // like the reference (llama.cpp:9877-9898) this frees seq_id[i] only for i < n_tokens
+    free(batch.token); free(batch.embd); free(batch.pos); free(batch.n_seq_id);
+    if (batch.seq_id) { for (int i = 0; i < batch.n_tokens; ++i) free(batch.seq_id[i]); free(batch.seq_id); }
+    free(batch.logits);
+    batch.token = nullptr; batch.embd = nullptr; batch.pos = nullptr; batch.n_seq_id = nullptr; batch.seq_id = nullptr; batch.logits = nullptr;
+}
+
+// ---- decode -----------------------------------------------------------------------------------------------------------
+static int start_from_batch(llama_context * ctx, const llama_batch & batch) {
+    if (batch.embd && !batch.token) { pib_set_error("decode: embedding input is not supported"); return -1; }
+    const int n = batch.n_tokens;
+    if (n <= 0) return -1;
+    std::vector<llama_pos> pos;
+    std::vector<int32_t>   nseq;
+    std::vector<llama_seq_id> seq1;
+    std::vector<const llama_seq_id *> seqp;
+    const llama_pos * p = batch.pos;
+    if (!p) { pos.resize(n); for (int i = 0; i < n; i++) pos[i] = batch.all_pos_0 + i * batch.all_pos_1; p = pos.data(); }
+    const int32_t * ns = batch.n_seq_id;
+    const llama_seq_id * const * sp = (const llama_seq_id * const *) batch.seq_id;
+    if (!batch.seq_id) {
+        nseq.assign(n, 1); seq1.assign(n, batch.all_seq_id); seqp.resize(n);
+        for (int i = 0; i < n; i++) seqp[i] = &seq1[i];
+        ns = nseq.data(); sp = seqp.data();
+    }
+    return pib_decode_start(ctx->c, n, batch.token, p, ns, sp, batch.batch_id);
+}
+
+int llama_decode(struct llama_context * ctx, struct llama_batch batch) {
+    const int run = start_from_batch(ctx, batch);
+    if (run < 0) return -1;
+    return pib_run_finish(ctx->c, run) == 0 ? 0 : -1;
+}
+
+struct ggml_cgraph * llama_start_async_decode(struct llama_context & lctx, struct llama_batch batch) {
+    const int run = start_from_batch(&lctx, batch);
+    return run < 0 ? nullptr : reinterpret_cast<struct ggml_cgraph *>((intptr_t) (run + 1));
+}
+
+int llama_finish_async_decode(struct llama_context & lctx, struct llama_batch batch, struct ggml_cgraph * cgraph) {
+    (void) batch;
+    if (!cgraph) return -1;
+    return pib_run_finish(lctx.c, (int) ((intptr_t) cgraph - 1)) == 0 ? 1 : -1;
+}
+
+bool llama_mpi_iprobe(struct llama_context * lctx) {
+    pib_context * c = lctx->c;
+    return !c->inflight.empty() && pib_run_ready(c, c->inflight.front());
+}
+
+void llama_cancel_run(struct llama_context * ctx, int32_t * canceled, int count) { pib_cancel(ctx->c, canceled, count); }
+
+float * llama_get_logits_ith(struct llama_context * ctx, int32_t i) { return const_cast<float *>(pib_logits_row(ctx->c, i)); }
+float * llama_get_logits(struct llama_context * ctx) {
+    pib_context * c = ctx->c;
+    if (c->last_finished < 0) return nullptr;
+    const int n = c->runs[c->last_finished].n_tokens;
+    for (int i = 0; i < n; i++) pib_logits_row(c, i);
+    return c->logits_host.data();
+}
+
+int llama_pib_get_top8(struct llama_context * ctx, int32_t i, llama_token_data * out8) {
+    pib_context * c = ctx->c;
+    const pib_row_result * r = pib_last_results(c);
+    if (!r || i < 0 || i >= c->runs[c->last_finished].n_tokens) return -1;
+    for (int k = 0; k < PIB_TOPK; k++) { out8[k].id = r[i].id[k]; out8[k].logit = r[i].logit[k]; out8[k].p = r[i].p[k]; }
+    return 0;
+}
+
+void llama_pib_set_logit_bias(struct llama_context * ctx, const llama_token * ids, const float * bias, int n) {
+    pib_set_logit_bias(ctx->c, ids, bias, n);
+}
+
+uint64_t llama_pib_kernel_launches(const struct llama_context * ctx) { return ctx->c->n_kernels; }
+
+// ---- KV cache ---------------------------------------------------------------------------------------------------------
+void llama_kv_cache_clear(struct llama_context * ctx) { pib_kv_push(ctx->c, { KVOP_CLEAR, 0, 0, 0, 0, 0 }); }
+void llama_kv_cache_seq_rm(struct llama_context * ctx, llama_seq_id seq_id, llama_pos p0, llama_pos p1) {
+    pib_kv_push(ctx->c, { KVOP_RM, seq_id, 0, p0, p1, 0 });
+}
+void llama_kv_cache_seq_cp(struct llama_context * ctx, llama_seq_id src, llama_seq_id dst, llama_pos p0, llama_pos p1) {
+    pib_kv_push(ctx->c, { KVOP_CP, src, dst, p0, p1, 0 });
+}
+void llama_kv_cache_seq_keep(struct llama_context * ctx, llama_seq_id seq_id) { pib_kv_push(ctx->c, { KVOP_KEEP, seq_id, 0, 0, 0, 0 }); }
+
+int llama_get_kv_cache_used_cells(const struct llama_context * ctx) {
+    pib_kv_flush_host(ctx->c);
+    return (int) ctx->c->kv.used;
+}
+
+int llama_get_kv_cache_token_count(const struct llama_context * ctx) {
+    pib_kv_flush_host(ctx->c);
+    int n = 0;
+    for (uint32_t w : ctx->c->kv.bits) n += __builtin_popcount(w);
+    return n;
+}
+
+struct llama_kv_cache_view llama_kv_cache_view_init(const struct llama_context * ctx, int32_t n_max_seq) {
+    (void) ctx;
+    struct llama_kv_cache_view v;
+    memset(&v, 0, sizeof(v));
+    v.n_max_seq = n_max_seq;
+    return v;
+}
+
+void llama_kv_cache_view_free(struct llama_kv_cache_view * view) {
+    free(view->cells); free(view->cells_sequences);
+    view->cells = nullptr; view->cells_sequences = nullptr;
+}
+
+// same fields and fill rules as the reference (llama.cpp:9160-9222)
+void llama_kv_cache_view_update(const struct llama_context * ctx, struct llama_kv_cache_view * view) {
+    pib_context * c = ctx->c;
+    pib_kv_flush_host(c);
+    const KvMirror & kv = c->kv;
+    if ((uint32_t) view->n_cells < kv.size || !view->cells) {
+        view->n_cells = (int32_t) kv.size;
+        view->cells = (struct llama_kv_cache_view_cell *) realloc(view->cells, sizeof(struct llama_kv_cache_view_cell) * view->n_cells);
+        view->cells_sequences = (llama_seq_id *) realloc(view->cells_sequences, sizeof(llama_seq_id) * view->n_max_seq * view->n_cells);
+    }
+    int32_t used = 0, tokens = 0, cur = -1, best_idx = -1;
+    uint32_t best = 0;
+    for (int32_t i = 0; i < (int32_t) kv.size; i++) {
+        llama_seq_id * cs = view->cells_sequences + (size_t) i * view->n_max_seq;
+        view->cells[i].pos = kv.pos[i];
+        int k = 0, cnt = 0;
+        for (int w = 0; w < kv.n_words; w++) {
+            uint32_t bits = kv.bits[(size_t) i * kv.n_words + w];
+            cnt += __builtin_popcount(bits);
+            while (bits) { const int b = __builtin_ctz(bits); bits &= bits - 1; if (k < view->n_max_seq) cs[k++] = w * 32 + b; }
+        }
+        tokens += cnt;
+        if (cnt > 0) {
+            if (cur >= 0 && (uint32_t) (i - cur) > best) { best = (uint32_t) (i - cur); best_idx = cur; }
+            cur = -1;
+            used++;
+        } else if (cur < 0) cur = i;
+        for (; k < view->n_max_seq; k++) cs[k] = -1;
+    }
+    if (cur >= 0 && kv.size - (uint32_t) cur > best) { best_idx = cur; best = kv.size - (uint32_t) cur; }
+    view->max_contiguous = (int32_t) best; view->max_contiguous_idx = best_idx; view->token_count = tokens; view->used_cells = used;
+}
+
+int llama_pib_kv_words(const struct llama_context * ctx) { return ctx->c->n_words; }
+
+int llama_pib_kv_state(struct llama_context * ctx, int from_device, int32_t * scalars3, int32_t * pos, uint32_t * bits) {
+    pib_context * c = ctx->c;
+    pib_kv_flush_host(c);
+    const size_t nb = (size_t) c->n_ctx * c->n_words;
+    if (!from_device) {
+        scalars3[0] = (int32_t) c->kv.head; scalars3[1] = (int32_t) c->kv.used; scalars3[2] = (int32_t) c->kv.n;
+        memcpy(pos, c->kv.pos.data(), sizeof(int32_t) * c->n_ctx);
+        memcpy(bits, c->kv.bits.data(), sizeof(uint32_t) * nb);
+        return 0;
+    }
+    // ops that were flushed to the mirror but not yet shipped ride with the next decode; push them now
+    if (!c->devops.empty()) {
+        const int n = (int) c->devops.size();
+        if (c->ops_next + n > c->ops_cap) { cudaStreamSynchronize(c->stream); c->ops_next = 0; }
+        memcpy(c->ops_host + c->ops_next, c->devops.data(), sizeof(KvOp) * n);
+        cudaMemcpyAsync(c->ops_dev + c->ops_next, c->ops_host + c->ops_next, sizeof(KvOp) * n, cudaMemcpyHostToDevice, c->stream);
+        kv_device_apply(&c->kvd, c->ops_dev + c->ops_next, n, c->desc_dev, c->desc_stride, c->stream);
+        c->ops_next += n;
+        c->devops.clear();
+    }
+    int32_t s[4];
+    if (cudaMemcpyAsync(s, c->kvd.scalars, 16, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaMemcpyAsync(pos, c->kvd.pos, sizeof(int32_t) * c->n_ctx, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaMemcpyAsync(bits, c->kvd.bits, sizeof(uint32_t) * nb, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        cudaStreamSynchronize(c->stream) != cudaSuccess) return -1;
+    scalars3[0] = s[0]; scalars3[1] = s[1]; scalars3[2] = s[2];
+    return 0;
+}
+
+// ---- communicator helpers: single-process heads => no-ops ---------------------------------------------------------------
+void llama_split_comm(struct llama_context * ctx, int color) { (void) ctx; (void) color; }
+void llama_swap_comm(struct llama_context * ctx) { (void) ctx; }
+void llama_sync_token(struct llama_context * ctx, llama_token * token, int root) { (void) ctx; (void) token; (void) root; }
+void llama_sync_token_data(struct llama_context * ctx, llama_token_data * data, int root) { (void) ctx; (void) data; (void) root; }
+void llama_split_layers_weighted(struct llama_context * ctx, float device_weights[], size_t num_weights) {
+    (void) ctx; (void) device_weights; (void) num_weights;
+}
+int llama_node_id(struct llama_context * ctx) { return ctx->c->stage.rank; }
+
+// ---- host samplers kept for API completeness (the scheduler uses the device results) -----------------------------------
+void llama_sample_softmax(struct llama_context * ctx, llama_token_data_array * cand) {
+    (void) ctx;
+    if (!cand->sorted) {
+        std::sort(cand->data, cand->data + cand->size, [](const llama_token_data & a, const llama_token_data & b) { return a.logit > b.logit; });
+        cand->sorted = true;
+    }
+    const float max_l = cand->data[0].logit;
+    float cum = 0.0f;
+    for (size_t i = 0; i < cand->size; ++i) { cand->data[i].p = expf(cand->data[i].logit - max_l); cum += cand->data[i].p; }
+    for (size_t i = 0; i < cand->size; ++i) cand->data[i].p /= cum;
+}
+
+llama_token llama_sample_token_greedy(struct llama_context * ctx, llama_token_data_array * cand) {
+    (void) ctx;
+    size_t best = 0;
+    for (size_t i = 1; i < cand->size; i++) if (cand->data[best].logit < cand->data[i].logit) best = i;
+    return cand->data[best].id;
+}
+
+}   // extern "C"

@@ -1,0 +1,81 @@
+// sampling.cu -- device-side token acceptance inputs (K10 / R9): per-row argmax and sorted top-8 probabilities.
+//
+// The reference pulls n_vocab floats per sampled row to the host and runs std::sort over the whole vocabulary there
+// (common/sampling.cpp:131, llama.cpp:7019-7046 llama_sample_softmax, :7496 llama_sample_token_greedy).  Here the
+// logits stay in HBM; per row the host receives 8 x {id, logit, p} (the llama_token_data the scheduler consumes at
+// speculative.cpp:977-1010), entry 0 being the greedy token:
+//   id    first index of the maximum (std::max_element semantics)
+//   p_i   expf(l_i - max) / sum_j expf(l_j - max); the sum is accumulated in double (the reference adds floats in
+//         sorted order), so p agrees to ~1e-7 relative -- the ids are exact.
+// logit_bias entries (e.g. EOS = -inf under --ignore-eos, common.cpp:1061-1063 / sampling.cpp:134-136) are applied
+// in the kernel before anything else, in place, as the reference does.
+#include "engine.cuh"
+
+#define SMP_THREADS 1024
+#define SMP_TOPK    8
+
+__global__ void __launch_bounds__(SMP_THREADS) sample_topk_kernel(float * __restrict__ logits, int n_vocab,
+                                                                  const int32_t * __restrict__ bias_ids, const float * __restrict__ bias_val,
+                                                                  int n_bias, pib_row_result * __restrict__ out,
+                                                                  const uint8_t * __restrict__ desc, const int * __restrict__ cancel) {
+    (void) desc;
+    if (cancel && *cancel) return;
+    __shared__ float  s_val[SMP_THREADS / 32];
+    __shared__ int    s_idx[SMP_THREADS / 32];
+    __shared__ double s_sum[SMP_THREADS / 32];
+    __shared__ float  s_best;
+    __shared__ int    s_besti;
+    __shared__ int    s_taken[SMP_TOPK];
+    float *   l    = logits + (size_t) blockIdx.x * n_vocab;
+    const int tid  = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int k = tid; k < n_bias; k += SMP_THREADS) l[bias_ids[k]] += bias_val[k];
+    __syncthreads();
+    float max_l = 0.f;
+    for (int k = 0; k < SMP_TOPK; k++) {
+        float bv = -INFINITY;
+        int   bi = 0x7fffffff;
+        for (int i = tid; i < n_vocab; i += SMP_THREADS) {
+            bool taken = false;
+            for (int j = 0; j < k; j++) taken |= (s_taken[j] == i);
+            const float v = l[i];
+            if (!taken && (v > bv || (v == bv && i < bi))) { bv = v; bi = i; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const int   oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if (lane == 0) { s_val[warp] = bv; s_idx[warp] = bi; }
+        __syncthreads();
+        if (tid == 0) {
+            float v = s_val[0];
+            int   i = s_idx[0];
+            for (int w = 1; w < SMP_THREADS / 32; w++)
+                if (s_val[w] > v || (s_val[w] == v && s_idx[w] < i)) { v = s_val[w]; i = s_idx[w]; }
+            s_best = v; s_besti = i; s_taken[k] = i;
+            out[blockIdx.x].id[k] = i;
+            out[blockIdx.x].logit[k] = v;
+        }
+        __syncthreads();
+        if (k == 0) max_l = s_best;
+    }
+    double sum = 0.0;
+    for (int i = tid; i < n_vocab; i += SMP_THREADS) sum += (double) expf(l[i] - max_l);
+    sum = warp_sum_d(sum);
+    if (lane == 0) s_sum[warp] = sum;
+    __syncthreads();
+    if (tid == 0) {
+        double t = 0.0;
+        for (int w = 0; w < SMP_THREADS / 32; w++) t += s_sum[w];
+        for (int k = 0; k < SMP_TOPK; k++) out[blockIdx.x].p[k] = (float) ((double) expf(out[blockIdx.x].logit[k] - max_l) / t);
+    }
+}
+
+int pib_sample_topk(float * logits_dev, int n_rows, int n_vocab, const int32_t * bias_ids_dev, const float * bias_val_dev,
+                    int n_bias, void * out_dev, const uint8_t * desc, const int * cancel, cudaStream_t st) {
+    sample_topk_kernel<<<n_rows, SMP_THREADS, 0, st>>>(logits_dev, n_vocab, bias_ids_dev, bias_val_dev, n_bias,
+                                                       (pib_row_result *) out_dev, desc, cancel);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}

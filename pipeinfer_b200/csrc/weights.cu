@@ -104,6 +104,8 @@ static int repack_from_device(pib_weight * w, const uint8_t * src, int64_t row0,
     return PIB_OK;
 }
 
+pib_weight * pib_weight_alloc(int type, int64_t N, int64_t K) { return alloc_weight(type, N, K); }
+
 extern "C" pib_weight * pib_weight_upload(int type, const void * host_blocks, int64_t N, int64_t K) {
     pib_weight * w = alloc_weight(type, N, K);
     if (!w) return nullptr;

@@ -1,0 +1,93 @@
+"""CPU-only: the host side of the KV bookkeeping (KvMirror + the lazy, coalescing op-log front end in
+pipeinfer_b200/csrc/kv_meta.cu) against the reference's llama_kv_cache_view dumps and against the oracle.
+Uses the pib_kvtest_* hooks of libpipeinfer_b200.so, which make no CUDA call."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle_py as op
+from tests.replay import replay
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+SO = os.path.join(ROOT, "pipeinfer_b200", "libpipeinfer_b200.so")
+KVOP_CLEAR, KVOP_RM, KVOP_CP, KVOP_KEEP = 1, 2, 3, 4
+
+
+class KvTest:
+    def __init__(self, n_ctx, max_seq):
+        if not os.path.exists(SO):
+            import __graft_entry__
+            __graft_entry__.build()
+        self.L = C.CDLL(SO)
+        self.L.pib_kvtest_new.restype = C.c_void_p
+        self.L.pib_kvtest_new.argtypes = [C.c_uint32, C.c_int32]
+        self.L.pib_kvtest_free.argtypes = [C.c_void_p]
+        self.L.pib_kvtest_op.argtypes = [C.c_void_p] + [C.c_int] * 5
+        self.L.pib_kvtest_pending.argtypes = [C.c_void_p]
+        self.L.pib_kvtest_decode.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.L.pib_kvtest_state.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.h = self.L.pib_kvtest_new(n_ctx, max_seq)
+        self.n_ctx, self.W = n_ctx, (max_seq + 31) // 32
+
+    def decode(self, tokens, pos, seqs):
+        ps = np.array(pos, dtype=np.int32)
+        ns, ptrs, keep = op.seq_ptrs(seqs)
+        return self.L.pib_kvtest_decode(self.h, len(tokens), ps.ctypes.data, ns.ctypes.data, ptrs), None
+
+    def seq_rm(self, s, p0, p1):
+        self.L.pib_kvtest_op(self.h, KVOP_RM, s, 0, p0, p1)
+
+    def seq_cp(self, a, b, p0, p1):
+        self.L.pib_kvtest_op(self.h, KVOP_CP, a, b, p0, p1)
+
+    def seq_keep(self, s):
+        self.L.pib_kvtest_op(self.h, KVOP_KEEP, s, 0, 0, 0)
+
+    def state(self):
+        sc = np.zeros(3, np.int32); pos = np.zeros(self.n_ctx, np.int32); bits = np.zeros((self.n_ctx, self.W), np.uint32)
+        self.L.pib_kvtest_state(self.h, sc.ctypes.data, pos.ctypes.data, bits.ctypes.data)
+        return dict(head=int(sc[0]), used=int(sc[1]), n=int(sc[2]), pos=pos, bits=bits)
+
+    def cells(self):
+        st = self.state()
+        return st["used"], op.kv_state_to_cells(st)
+
+
+@pytest.mark.parametrize("stem", ["kvops", "decode_q8_0"])
+def test_host_mirror_matches_reference_kv_view(golden_dir, stem):
+    kv = KvTest(48, 8)
+    n_dec, n_kv = replay(golden_dir, stem, kv.decode, kv.seq_rm, kv.seq_cp, kv.seq_keep, kv.cells)
+    assert n_kv >= 8
+
+
+def test_commit_loop_is_coalesced_and_identical_to_the_literal_loop(oracle):
+    # speculative.cpp:603-612: for i in 1..max_seq: seq_rm(i, p0, p1); seq_cp(0, i, p0, p1)  ->  one KVOP_SWEEP
+    rng = np.random.default_rng(3)
+    n_ctx, max_seq = 64, 100
+    for trial in range(20):
+        kv = KvTest(n_ctx, max_seq)
+        okv = oracle.L.po_kv_new(n_ctx, max_seq)
+        pos_next = 0
+        for _ in range(6):          # random population: tokens in random sequence subsets
+            n = int(rng.integers(1, 7))
+            seqs = [sorted(set(rng.integers(0, max_seq, int(rng.integers(1, 5))).tolist()) | ({0} if rng.random() < 0.6 else set()))
+                    for _ in range(n)]
+            ps = np.arange(pos_next, pos_next + n, dtype=np.int32); pos_next += n
+            ns, ptrs, keep = op.seq_ptrs(seqs)
+            assert kv.decode([0] * n, ps.tolist(), seqs)[0] == 0
+            oracle.L.po_kv_find_slot(okv, n, ps.ctypes.data, ns.ctypes.data, ptrs)
+            okv.contents.head = (okv.contents.head + n) % n_ctx
+        p0, p1 = int(rng.integers(0, pos_next)), int(rng.integers(1, pos_next + 2))
+        first, last = 1, int(rng.integers(1, max_seq))
+        for i in range(first, last + 1):
+            kv.seq_rm(i, p0, p1); kv.seq_cp(0, i, p0, p1)
+            oracle.L.po_kv_seq_rm(okv, i, p0, p1); oracle.L.po_kv_seq_cp(okv, 0, i, p0, p1)
+        assert kv.L.pib_kvtest_pending(kv.h) == 1            # collapsed into a single op
+        st = kv.state()
+        o = okv.contents
+        assert (st["head"], st["used"]) == (o.head, o.used)
+        assert np.array_equal(st["pos"], np.ctypeslib.as_array(o.pos, shape=(n_ctx,)))
+        assert np.array_equal(st["bits"], np.ctypeslib.as_array(o.bits, shape=(n_ctx, o.n_words)))
+        oracle.L.po_kv_free(okv)
