@@ -180,12 +180,18 @@ __global__ void synth_fill_kernel(int type, uint8_t * qs, uint16_t * d, int64_t 
             uint8_t * hdr = reinterpret_cast<uint8_t *>(d) + i * 16;
             const float dd = dscale * u / (32.0f * 4.6f);
             const uint16_t hd = __half_as_ushort(__float2half_rn(dd)), hm = __half_as_ushort(__float2half_rn(7.5f * __half2float(__float2half_rn(dd))));
-            hdr[0] = hd & 0xff; hdr[1] = hd >> 8; hdr[2] = hm & 0xff; hdr[3] = hm >> 8;
-            uint8_t s[8];
-            for (int j = 0; j < 8; j++) s[j] = 16 + (hash3(seed ^ 0x5C5C5C5Cu, lr, (uint32_t) (c * 8 + j)) & 31);   // 16..47
-            uint8_t * q = hdr + 4;
+            uint32_t s[8];
+            for (int j = 0; j < 8; j++) s[j] = 16u + (hash3(seed ^ 0x5C5C5C5Cu, lr, (uint32_t) (c * 8 + j)) & 31u);   // 16..47
+            // 12 packed bytes such that get_scale_min_k4 yields sc_j = m_j = s[j] (reference ggml-quants.c:1446-1454)
+            uint32_t q[12];
             for (int j = 0; j < 4; j++) { q[j] = s[j] | ((s[j + 4] >> 4) << 6); q[j + 4] = s[j] | ((s[j + 4] >> 4) << 6); }
-            for (int j = 4; j < 8; j++) q[j + 4] = (s[j] & 0xF) | ((s[j] & 0xF) << 4);
+            for (int j = 4; j < 8; j++) q[j + 4] = (s[j] & 0xFu) | ((s[j] & 0xFu) << 4);
+            uint4 w;
+            w.x = (uint32_t) hd | ((uint32_t) hm << 16);
+            w.y = q[0] | (q[1] << 8) | (q[2] << 16) | (q[3] << 24);
+            w.z = q[4] | (q[5] << 8) | (q[6] << 16) | (q[7] << 24);
+            w.w = q[8] | (q[9] << 8) | (q[10] << 16) | (q[11] << 24);
+            *reinterpret_cast<uint4 *>(hdr) = w;
         }
     }
 }
@@ -247,7 +253,9 @@ pib_model * pib_model_synthetic(int n_layer, int n_embd, int n_head, int n_head_
     cudaMalloc(&inv_dev, (size_t) n_vocab * 4);
     cudaMemcpy(inv_dev, inv.data(), (size_t) n_vocab * 4, cudaMemcpyHostToDevice);
     const uint32_t s32   = (uint32_t) (seed * 2654435761u);
-    const float    lstd  = flavour == 1 ? 0.02f * 0.25f : 0.02f;       // layer weight std
+    // layer weight std: iid flavour 0.02; bigram flavour 0.1/sqrt(K) so that a layer perturbs the residual stream by ~1%
+    // of its norm whatever the width (80 layers of a 70B-shaped model then still predict pi(last token))
+    const float    lstdE = flavour == 1 ? 0.1f / sqrtf((float) E) : 0.02f, lstdF = flavour == 1 ? 0.1f / sqrtf((float) FF) : 0.02f;
     const uint32_t embseed = flavour == 1 ? 0xE3B0C442u : s32 ^ 0x11111111u;   // bigram: the same g_t for target and draft
     bool ok = true;
     if (want_embd) { m->tok_embd = synth_weight(wtype, n_vocab, E, embseed, nullptr, flavour == 1 ? 1.0f : 0.02f); ok = ok && m->tok_embd; }
@@ -261,10 +269,10 @@ pib_model * pib_model_synthetic(int n_layer, int n_embd, int n_head, int n_head_
         const uint32_t ls = s32 ^ (uint32_t) (il * 7919 + 13);
         L.attn_norm = const_f32(E, 1.0f);
         L.ffn_norm  = const_f32(E, 1.0f);
-        L.wqkv  = synth_weight(wtype, E + 2 * GQA, E, ls ^ 0x1u, nullptr, lstd);
-        L.wo    = synth_weight(wtype, E, E, ls ^ 0x2u, nullptr, lstd);
-        L.wgu   = synth_weight(wtype, 2 * FF, E, ls ^ 0x3u, nullptr, lstd);
-        L.wdown = synth_weight(wtype, E, FF, ls ^ 0x4u, nullptr, lstd);
+        L.wqkv  = synth_weight(wtype, E + 2 * GQA, E, ls ^ 0x1u, nullptr, lstdE);
+        L.wo    = synth_weight(wtype, E, E, ls ^ 0x2u, nullptr, lstdE);
+        L.wgu   = synth_weight(wtype, 2 * FF, E, ls ^ 0x3u, nullptr, lstdE);
+        L.wdown = synth_weight(wtype, E, FF, ls ^ 0x4u, nullptr, lstdF);
         ok = L.attn_norm && L.ffn_norm && L.wqkv && L.wo && L.wgu && L.wdown;
         if (ok) m->weight_bytes += pib_weight_bytes(L.wqkv) + pib_weight_bytes(L.wo) + pib_weight_bytes(L.wgu) + pib_weight_bytes(L.wdown);
     }

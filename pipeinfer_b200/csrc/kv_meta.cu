@@ -32,19 +32,29 @@ void KvMirror::clear() {
     used = 0;
 }
 
-void KvMirror::seq_rm(int32_t seq, int32_t p0, int32_t p1) {
+static inline void host_range(uint32_t * r, int W, int first, int last, bool set) {
+    for (int s = first; s <= last;) {
+        const int      w = s >> 5, lo = s & 31;
+        const int      hi = (last >> 5) == w ? (last & 31) : 31;
+        const uint32_t m  = (hi == 31 ? 0xffffffffu : ((1u << (hi + 1)) - 1u)) & ~((1u << lo) - 1u);
+        if (w < W) { if (set) r[w] |= m; else r[w] &= ~m; }
+        s = (w + 1) << 5;
+    }
+}
+
+// seq_rm for every sequence in [first, last] (first < 0: all sequences), evaluated per cell in one pass.  Identical to
+// the literal loop: within a run of seq_rm calls cells only lose bits, so "became empty at some point" == "is empty at
+// the end", `used` drops once per emptied cell, and head = min(head, first empty cell in range).
+void KvMirror::seq_rm(int32_t first, int32_t last, int32_t p0, int32_t p1) {
     uint32_t new_head = size;
     if (p0 < 0) p0 = 0;
     if (p1 < 0) p1 = INT_MAX;
-    const bool     in_range = seq >= 0 && seq < n_words * 32;
-    const uint32_t m        = in_range ? (1u << (seq & 31)) : 0u;
-    const int      wi       = in_range ? (seq >> 5) : 0;
     for (uint32_t i = 0; i < size; ++i) {
         const int32_t p = pos[i];
         if ((p >= p0 || p < 0) && p < p1) {
             uint32_t * r = &bits[(size_t) i * n_words];
-            if (seq < 0) memset(r, 0, sizeof(uint32_t) * n_words);
-            else r[wi] &= ~m;
+            if (first < 0) memset(r, 0, sizeof(uint32_t) * n_words);
+            else host_range(r, n_words, first, last, false);
             if (empty(i)) {
                 if (p >= 0) used--;
                 pos[i] = -1;
@@ -55,13 +65,14 @@ void KvMirror::seq_rm(int32_t seq, int32_t p0, int32_t p1) {
     if (new_head != size && new_head < head) head = new_head;
 }
 
-void KvMirror::seq_cp(int32_t src, int32_t dst, int32_t p0, int32_t p1) {
+// seq_cp(src -> d) for every d in [dfirst, dlast] in one pass (head = 0 as after any seq_cp)
+void KvMirror::seq_cp(int32_t src, int32_t dfirst, int32_t dlast, int32_t p0, int32_t p1) {
     if (p0 < 0) p0 = 0;
     if (p1 < 0) p1 = INT_MAX;
     head = 0;
-    if (dst < 0 || dst >= n_words * 32) return;
+    if (dfirst < 0) return;
     for (uint32_t i = 0; i < size; ++i)
-        if (has(i, src) && pos[i] >= p0 && pos[i] < p1) bits[(size_t) i * n_words + (dst >> 5)] |= 1u << (dst & 31);
+        if (has(i, src) && pos[i] >= p0 && pos[i] < p1) host_range(&bits[(size_t) i * n_words], n_words, dfirst, dlast, true);
 }
 
 void KvMirror::seq_keep(int32_t seq) {
@@ -88,7 +99,7 @@ void KvMirror::seq_keep(int32_t seq) {
 void KvMirror::sweep(int32_t first, int32_t last, int32_t p0, int32_t p1) {
     if (first > last) return;
     if (first < 1) {                 // not the pattern this op was made for: fall back to the literal loop
-        for (int32_t i = first; i <= last; i++) { seq_rm(i, p0, p1); seq_cp(0, i, p0, p1); }
+        for (int32_t i = first; i <= last; i++) { seq_rm(i, i, p0, p1); seq_cp(0, i, i, p0, p1); }
         return;
     }
     int32_t q0 = p0 < 0 ? 0 : p0, q1 = p1 < 0 ? INT_MAX : p1;
@@ -163,6 +174,17 @@ __device__ __forceinline__ bool row_empty(const uint32_t * r, int W) {
     return true;
 }
 
+// set or clear the bits [first, last] of a cell row
+__device__ __forceinline__ void dev_range(uint32_t * r, int W, int first, int last, bool set) {
+    for (int s = first; s <= last;) {
+        const int      w = s >> 5, lo = s & 31;
+        const int      hi = (last >> 5) == w ? (last & 31) : 31;
+        const uint32_t m  = (hi == 31 ? 0xffffffffu : ((1u << (hi + 1)) - 1u)) & ~((1u << lo) - 1u);
+        if (w < W) { if (set) r[w] |= m; else r[w] &= ~m; }
+        s = (w + 1) << 5;
+    }
+}
+
 // One CTA replays the log in order; every op is a parallel sweep over the cells followed by a block-wide reduction of
 // (first emptied cell, number of cells that became empty) where the op needs them.
 __global__ void __launch_bounds__(KVT) kv_apply_kernel(int32_t * __restrict__ pos, uint32_t * __restrict__ bits,
@@ -186,13 +208,13 @@ __global__ void __launch_bounds__(KVT) kv_apply_kernel(int32_t * __restrict__ po
                 for (int w = 0; w < W; w++) bits[(size_t) i * W + w] = 0u;
             }
         } else if (op.op == KVOP_RM) {
-            const int seq = op.a;
+            const int first = op.a, last = op.b;
             for (int i = tid; i < size; i += KVT) {
                 const int p = pos[i];
                 if ((p >= q0 || p < 0) && p < q1) {
                     uint32_t * r = bits + (size_t) i * W;
-                    if (seq < 0) { for (int w = 0; w < W; w++) r[w] = 0u; }
-                    else if (seq < W * 32) r[seq >> 5] &= ~(1u << (seq & 31));
+                    if (first < 0) { for (int w = 0; w < W; w++) r[w] = 0u; }
+                    else dev_range(r, W, first, last, false);
                     if (row_empty(r, W)) {
                         if (p >= 0) my_cnt++;
                         pos[i] = -1;
@@ -201,12 +223,12 @@ __global__ void __launch_bounds__(KVT) kv_apply_kernel(int32_t * __restrict__ po
                 }
             }
         } else if (op.op == KVOP_CP) {
-            const int src = op.a, dst = op.b;
-            if (dst >= 0 && dst < W * 32 && src >= 0 && src < W * 32) {
+            const int src = op.a, dfirst = op.b, dlast = op.pad;
+            if (dfirst >= 0 && src >= 0 && src < W * 32) {
                 for (int i = tid; i < size; i += KVT) {
                     const int  p = pos[i];
                     uint32_t * r = bits + (size_t) i * W;
-                    if (((r[src >> 5] >> (src & 31)) & 1u) && p >= q0 && p < q1) r[dst >> 5] |= 1u << (dst & 31);
+                    if (((r[src >> 5] >> (src & 31)) & 1u) && p >= q0 && p < q1) dev_range(r, W, dfirst, dlast, true);
                 }
             }
         } else if (op.op == KVOP_KEEP) {
@@ -341,10 +363,15 @@ int kv_device_mask(const KvDevice * kv, const int32_t * tpos_dev, const uint32_t
 // kvlog_push: the public llama_kv_cache_seq_* calls only append; RM(i, p0, p1) directly followed by CP(0 -> i, p0, p1)
 // for consecutive i -- the scheduler's commit loop, speculative.cpp:603-612, ~2*max_seq calls -- collapses into one
 // KVOP_SWEEP with identical results.
-void kvlog_push(std::vector<KvOp> & q, const KvOp & op) {
-    if (op.op == KVOP_CP && op.a == 0 && op.b >= 1 && !q.empty()) {
+void kvlog_push(std::vector<KvOp> & q, const KvOp & op_in) {
+    KvOp op = op_in;
+    if (op.op == KVOP_RM && op.a >= 0) op.b = op.a;          // single sequence == range [a, a]
+    if (op.op == KVOP_CP) op.pad = op.b;                     // single destination == range [b, b]
+    if (!q.empty()) {
         KvOp & last = q.back();
-        if (last.op == KVOP_RM && last.a == op.b && last.p0 == op.p0 && last.p1 == op.p1) {
+        const bool same = last.p0 == op.p0 && last.p1 == op.p1;
+        if (op.op == KVOP_CP && op.a == 0 && op.b >= 1 && same && last.op == KVOP_RM && last.a == op.b && last.b == op.b) {
+            // RM(i) directly followed by CP(0 -> i): start or extend a sweep
             if (q.size() >= 2) {
                 KvOp & prev = q[q.size() - 2];
                 if (prev.op == KVOP_SWEEP && prev.b + 1 == op.b && prev.p0 == op.p0 && prev.p1 == op.p1) {
@@ -354,10 +381,12 @@ void kvlog_push(std::vector<KvOp> & q, const KvOp & op) {
                 }
             }
             last.op = KVOP_SWEEP;
-            last.a  = op.b;
-            last.b  = op.b;
             return;
         }
+        // RM(i), RM(i+1), ...  /  CP(s -> i), CP(s -> i+1), ...  with one position range: one ranged op
+        if (op.op == KVOP_RM && op.a >= 0 && last.op == KVOP_RM && last.a >= 0 && same && last.b + 1 == op.a) { last.b = op.b; return; }
+        if (op.op == KVOP_CP && last.op == KVOP_CP && same && last.a == op.a && last.pad + 1 == op.b &&
+            (op.a < last.b || op.a > op.b)) { last.pad = op.b; return; }
     }
     q.push_back(op);
 }
@@ -366,8 +395,8 @@ void kvlog_flush(KvMirror & kv, std::vector<KvOp> & pending, std::vector<KvOp> &
     for (const KvOp & op : pending) {
         switch (op.op) {
             case KVOP_CLEAR: kv.clear(); break;
-            case KVOP_RM:    kv.seq_rm(op.a, op.p0, op.p1); break;
-            case KVOP_CP:    kv.seq_cp(op.a, op.b, op.p0, op.p1); break;
+            case KVOP_RM:    kv.seq_rm(op.a, op.b, op.p0, op.p1); break;
+            case KVOP_CP:    kv.seq_cp(op.a, op.b, op.pad, op.p0, op.p1); break;
             case KVOP_KEEP:  kv.seq_keep(op.a); break;
             case KVOP_SWEEP: kv.sweep(op.a, op.b, op.p0, op.p1); break;
         }

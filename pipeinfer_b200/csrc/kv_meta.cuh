@@ -18,8 +18,8 @@
 
 enum {
     KVOP_CLEAR = 1,     // llama_kv_cache_clear
-    KVOP_RM    = 2,     // a=seq (or -1), p0, p1                     llama_kv_cache_seq_rm   (PipeInfer predicate)
-    KVOP_CP    = 3,     // a=src, b=dst, p0, p1                      llama_kv_cache_seq_cp   (head = 0)
+    KVOP_RM    = 2,     // a..b = sequence range (a = -1: all), p0, p1   llama_kv_cache_seq_rm   (PipeInfer predicate)
+    KVOP_CP    = 3,     // a=src, b..pad = destination range, p0, p1     llama_kv_cache_seq_cp   (head = 0)
     KVOP_KEEP  = 4,     // a=seq                                     llama_kv_cache_seq_keep
     KVOP_ALLOC = 5,     // a=head, b=n_tokens, p0=n (attended range), p1=descriptor slot: cells [head, head+n_tokens)
                         //   take pos / seq bits of the batch         llama_kv_cache_find_slot (resolved on the host)
@@ -45,8 +45,8 @@ struct KvMirror {
     }
     bool empty(uint32_t cell) const;
     void clear();
-    void seq_rm(int32_t seq, int32_t p0, int32_t p1);
-    void seq_cp(int32_t src, int32_t dst, int32_t p0, int32_t p1);
+    void seq_rm(int32_t first, int32_t last, int32_t p0, int32_t p1);
+    void seq_cp(int32_t src, int32_t dfirst, int32_t dlast, int32_t p0, int32_t p1);
     void seq_keep(int32_t seq);
     void sweep(int32_t first, int32_t last, int32_t p0, int32_t p1);
     // find_slot: returns false when there is no run of n_tokens free cells; on success head points at the slot and the

@@ -437,3 +437,20 @@ llama_token llama_sample_token_greedy(struct llama_context * ctx, llama_token_da
 }
 
 }   // extern "C"
+
+// debugging aid for parity work: read back a work buffer of the last chunk (0: residual stream x, 1: ffn_inp x2,
+// 2: attention output, 3: last projection output)
+extern "C" int llama_pib_debug_read(struct llama_context * ctx, int which, float * out, int n_floats) {
+    pib_context * c = ctx->c;
+    const float * src = which == 0 ? c->x : which == 1 ? c->x2 : which == 2 ? c->att : c->proj;
+    if (cudaStreamSynchronize(c->stream) != cudaSuccess) return -1;
+    return cudaMemcpy(out, src, sizeof(float) * (size_t) n_floats, cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : -1;
+}
+
+// debugging aid: handle of a resident weight matrix (layer < 0: 0 = token_embd, 1 = output; else 0 qkv, 1 o, 2 gate|up, 3 down)
+extern "C" const pib_weight * llama_pib_debug_weight(const struct llama_model * model, int layer, int which) {
+    const pib_model * m = model->m;
+    if (layer < 0) return which == 0 ? m->tok_embd : m->output;
+    const pib_layer & L = m->layers[layer];
+    return which == 0 ? L.wqkv : which == 1 ? L.wo : which == 2 ? L.wgu : L.wdown;
+}

@@ -1,0 +1,512 @@
+// scheduler.cu -- PipeInfer's continuous asynchronous speculation scheduler (host, integer logic) on top of the
+// llama.h-compatible ABI of this library.
+//
+// Behavioural restatement of the reference's examples/speculative/speculative.cpp (S1-S6 of SURVEY.md §8a), re-organised as
+// one class; every step cites the reference lines whose behaviour it reproduces.  What differs by design:
+//   * both pipeline heads live in this process, so the MPI_Bcast lock-step of the two head ranks (llama_sync_token /
+//     llama_sync_token_data / llama_swap_comm, speculative.cpp:323-326, 454, 973-983) disappears;
+//   * sampling reads 8 x {id, logit, p} per row produced on the device (sampling.cu) instead of sorting n_vocab floats
+//     on the host (common/sampling.cpp:102-216); greedy only (--temp <= 0, --repeat-last-n 0: the configuration of the
+//     authors' launch scripts, examples/speculative/scripts/*.sh);
+//   * the target runs asynchronously on its stream (or pipeline), the draft synchronously on its own stream.
+#include "engine.cuh"
+#include "../../include/pipeinfer_llama.h"
+#include "../../include/pipeinfer_sched.h"
+
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <deque>
+#include <vector>
+
+namespace {
+
+struct Draft {                       // speculative.cpp:16-28 seq_draft
+    bool active = false, drafting = false, skip = false;
+    int  i_batch_dft = 0;
+    std::vector<int>         i_batch_tgt;
+    std::vector<llama_token> tokens, prefix_tokens;
+};
+
+struct Batch {                       // an owned llama_batch (tokens, positions, per-token sequence-id lists)
+    std::vector<llama_token>               token;
+    std::vector<llama_pos>                 pos;
+    std::vector<std::vector<llama_seq_id>> seq;
+    int32_t                                batch_id = 0;
+    std::vector<int32_t>        nseq_;
+    std::vector<llama_seq_id *> ptr_;
+    std::vector<int8_t>         lg_;
+    void clear() { token.clear(); pos.clear(); seq.clear(); }
+    int  size() const { return (int) token.size(); }
+    void add(llama_token t, llama_pos p, std::vector<llama_seq_id> s) { token.push_back(t); pos.push_back(p); seq.push_back(std::move(s)); }
+    llama_batch view(int max_n_seq) {
+        const int n = size();
+        nseq_.resize(n); ptr_.resize(n); lg_.assign(n, 1);
+        for (int i = 0; i < n; i++) { nseq_[i] = (int32_t) seq[i].size(); ptr_[i] = seq[i].data(); }
+        llama_batch b;
+        b.n_tokens = n; b.token = token.data(); b.embd = nullptr; b.pos = pos.data(); b.n_seq_id = nseq_.data(); b.seq_id = ptr_.data();
+        b.logits = lg_.data(); b.all_pos_0 = 0; b.all_pos_1 = 0; b.all_seq_id = 0; b.batch_id = batch_id; b.max_n_seq = max_n_seq;
+        return b;
+    }
+};
+
+struct Run {                         // speculative.cpp:30-43 seq_async_run
+    struct ggml_cgraph * handle = nullptr;
+    Batch              batch;
+    std::vector<Draft> drafts;
+    int  n_past_tgt = 0, prefix_n_past_tgt = 0, n_past_dft = 0, s_keep = 0, seq_offset = 0, n_past_max = 0;
+    bool speculative = false, canceled = false;
+};
+
+class Scheduler {
+  public:
+    Scheduler(llama_context * tgt, llama_context * dft, const pib_spec_params & p) : ctx_tgt(tgt), ctx_dft(dft), P(p) {
+        np      = std::max(1, P.n_parallel);
+        max_seq = 1000 * np + 1;                                           // :140-145
+        for (int i = 0; i < 1000; i++) free_offsets.push_back(i * np + 1);
+        drafts.assign(np, Draft());
+    }
+
+    int run(const llama_token * prompt, int n_prompt, llama_token * out, int out_cap, pib_spec_result * res, double * itl_us, int itl_cap);
+
+  private:
+    llama_context * ctx_tgt, * ctx_dft;
+    pib_spec_params P;
+    int np, max_seq;
+    std::deque<int>    free_offsets;
+    std::vector<Draft> drafts;
+    std::deque<Run>    tgt_runs;          // push_front new, back() oldest  (:1262 / :331)
+    std::vector<llama_token> generated;
+    int32_t batch_id = 0;
+    int n_predict = 0, n_drafted = 0, n_accept = 0, n_rejected = 0, n_cancel = 0, n_spec_runs = 0;
+    int n_past_tgt = 0, n_past_dft = 0, spec_past_tgt = 0, spec_past_dft = 0;
+    bool first_run = true, failed = false;
+    llama_token id = 0;
+    Run current;                          // the run whose logits are being verified (only the scalar fields are used)
+    Batch batch_tgt, batch_dft;
+
+    static llama_token greedy(llama_context * c, int row) { llama_token_data t[8]; llama_pib_get_top8(c, row, t); return t[0].id; }
+
+    void check_for_cancel();
+    void begin_async_run(llama_context * ctx, std::deque<Run> & q, const std::vector<Draft> & dr, int & n_past, int n_past_dft_arg,
+                         bool is_spec, Batch & batch, int n_past_max, int prefix_n_past, int seq_offset);
+    void begin_non_spec_run(llama_context * ctx, std::deque<Run> & q, int & n_past, int n_past_dft_arg);
+    bool start_spec_run(int prefix_n_past, int n_past_dft_arg, int orig_offset, float p_adjust);
+    void speculation_loop();
+    float p_adjust_of(int iter) const { return iter * P.p_recovery - std::max(n_rejected * P.p_decay, 0.0f); }   // :846-848
+};
+
+// :1277-1359 -- a run is cancelled when it is entirely stale (n_past_max < n_past_tgt) or when prefix_tokens ++ tokens of
+// every non-empty branch diverges from what has been generated since the run's prefix position
+void Scheduler::check_for_cancel() {
+    std::vector<int32_t> ids;
+    for (Run & run : tgt_runs) {
+        if (run.canceled) continue;
+        bool correct_prefix = true;
+        if (run.speculative && n_past_tgt >= run.prefix_n_past_tgt) {
+            for (int d = np - 1; d >= 0; d--) {
+                if (run.drafts[d].tokens.empty()) continue;
+                correct_prefix = true;
+                std::vector<llama_token> cat = run.drafts[d].prefix_tokens;
+                cat.insert(cat.end(), run.drafts[d].tokens.begin(), run.drafts[d].tokens.end());
+                size_t di = 0, gi = (size_t) run.prefix_n_past_tgt;
+                while (gi < generated.size() && di < cat.size() && generated.size() > (size_t) run.prefix_n_past_tgt) {
+                    if (generated[gi] != cat[di]) { correct_prefix = false; break; }
+                    di++;
+                    gi = (size_t) run.prefix_n_past_tgt + di;
+                }
+                if (correct_prefix) run.s_keep = d;
+            }
+        }
+        if (run.n_past_max < n_past_tgt || !correct_prefix) {
+            if (run.speculative) ids.push_back(run.batch.batch_id);
+            run.canceled = true;
+        }
+    }
+    if (!ids.empty()) { n_cancel += (int) ids.size(); llama_cancel_run(ctx_tgt, ids.data(), (int) ids.size()); }
+}
+
+// :1182-1275
+void Scheduler::begin_async_run(llama_context * ctx, std::deque<Run> & q, const std::vector<Draft> & dr, int & n_past, int n_past_dft_arg,
+                                bool is_spec, Batch & batch, int n_past_max, int prefix_n_past, int seq_offset) {
+    batch_id++;
+    Run run;
+    run.seq_offset = seq_offset;
+    run.batch = batch;
+    run.batch.batch_id = batch_id;
+    run.drafts = dr;
+    run.n_past_tgt = n_past; run.prefix_n_past_tgt = prefix_n_past; run.n_past_max = n_past_max; run.n_past_dft = n_past_dft_arg;
+    run.speculative = is_spec;
+    if (!is_spec) { for (int i = 0; i <= max_seq; i++) llama_kv_cache_seq_rm(ctx, i, n_past, n_past + 1); }        // :1252-1255
+    else          { for (int i = 0; i < np; i++) llama_kv_cache_seq_rm(ctx, i + seq_offset, n_past, n_past + 1); } // :1256-1260
+    run.handle = llama_start_async_decode(*ctx, run.batch.view(max_seq + 1));                                      // :1261
+    if (!run.handle) failed = true;     // no KV slot left: the reference would spin forever here
+    q.push_front(std::move(run));
+    if (!is_spec) for (int i = 1; i <= max_seq; i++) llama_kv_cache_seq_cp(ctx, 0, i, n_past, n_past + 1);         // :1264-1268
+}
+
+// :850-879
+void Scheduler::begin_non_spec_run(llama_context * ctx, std::deque<Run> & q, int & n_past, int n_past_dft_arg) {
+    std::vector<Draft> ns(np);
+    for (int s = 0; s < np; s++) {
+        ns[s].i_batch_tgt = { 0 };
+        ns[s].i_batch_dft = drafts[s].i_batch_dft;
+        ns[s].tokens      = { id };
+        ns[s].active = drafts[s].active; ns[s].drafting = drafts[s].drafting; ns[s].skip = drafts[s].skip;
+    }
+    Batch b;
+    b.add(id, n_past, { 0 });
+    begin_async_run(ctx, q, ns, n_past, n_past_dft_arg, false, b, n_past + 1, n_past, 0);
+    n_past++;
+}
+
+// :881-1180 -- one speculative run: seed the partition's KV from sequence 0 (first run after a verification) or from the
+// previous partition (chained runs), tree-draft up to n_draft tokens with synchronous draft decodes, launch the target
+// verification batch asynchronously.  Returns true when speculation should stop.
+bool Scheduler::start_spec_run(int prefix_n_past, int n_past_dft_arg, int orig_offset, float p_adjust) {
+    const int off = current.seq_offset;
+    for (int i = 0; i < np; i++) {                                                                       // :891-905
+        llama_kv_cache_seq_rm(ctx_tgt, i + off, first_run ? prefix_n_past : prefix_n_past - 1, -1);
+        llama_kv_cache_seq_rm(ctx_dft, i + off, first_run ? n_past_dft_arg : n_past_dft_arg - 1, -1);
+        llama_kv_cache_seq_cp(ctx_tgt, first_run ? 0 : orig_offset, i + off, first_run ? prefix_n_past : prefix_n_past - 1, spec_past_tgt + 1);
+        llama_kv_cache_seq_cp(ctx_dft, first_run ? 0 : orig_offset, i + off, first_run ? n_past_dft_arg : n_past_dft_arg - 1, spec_past_dft + 1);
+    }
+    batch_tgt.clear();
+    for (int s = 0; s < np; s++) {                                                                       // :910-922
+        drafts[s].active = false;
+        if (!first_run) drafts[s].prefix_tokens.insert(drafts[s].prefix_tokens.end(), drafts[s].tokens.begin(), drafts[s].tokens.end());
+        else drafts[s].prefix_tokens.clear();
+        drafts[s].tokens.clear();
+        drafts[s].i_batch_tgt.clear();
+    }
+    drafts[0].tokens.push_back(id);                                                                      // erased after drafting
+    batch_dft.clear();
+    int n_seq_cur = 0, max_ran_seq = 0, n_past_cur = spec_past_dft;
+    for (int s = 0; s < np; s++) { drafts[s].skip = true; drafts[s].active = false; drafts[s].drafting = false; }
+    drafts[0].active = true; drafts[0].drafting = true; drafts[0].skip = false; drafts[0].i_batch_dft = 0;
+
+    for (int i = 0; i < P.n_draft; ++i) {                                                                // :957-1104
+        batch_dft.clear();
+        for (int s = 0; s <= max_ran_seq; ++s) {
+            if (!drafts[s].drafting || drafts[s].skip) continue;
+            llama_token_data cur_p[8];
+            llama_pib_get_top8(ctx_dft, drafts[s].i_batch_dft, cur_p);                                   // :975-983
+            if (cur_p[0].p < P.p_accept + p_adjust) { drafts[s].drafting = false; continue; }           // :998-1003
+            std::vector<int> sa(1, s);
+            for (int f = 1; f < 8; ++f) {                                                                // :1009-1050 branch split
+                if (n_seq_cur < np - 1 && cur_p[f].p > P.p_split + p_adjust) {
+                    n_seq_cur++;
+                    llama_kv_cache_seq_rm(ctx_dft, n_seq_cur + off, n_past_dft_arg, n_past_cur);
+                    llama_kv_cache_seq_cp(ctx_dft, s + off, n_seq_cur + off, n_past_dft_arg, n_past_cur);
+                    for (int t = 0; t < batch_tgt.size(); ++t)                                           // earlier tokens join the new branch
+                        for (size_t p = 0; p < batch_tgt.seq[t].size(); ++p)
+                            if (batch_tgt.seq[t][p] == s + off) { batch_tgt.seq[t].push_back(n_seq_cur + off); break; }
+                    drafts[n_seq_cur].active = true; drafts[n_seq_cur].drafting = true; drafts[n_seq_cur].skip = false;
+                    drafts[n_seq_cur].tokens = drafts[s].tokens;
+                    drafts[n_seq_cur].i_batch_tgt = drafts[s].i_batch_tgt;
+                    sa.push_back(n_seq_cur);
+                } else break;
+            }
+            for (int is = 0; is < (int) sa.size(); ++is) {                                               // :1054-1081
+                const llama_token tok = cur_p[is].id;
+                const int sq = sa[is];
+                drafts[sq].tokens.push_back(tok);
+                drafts[sq].i_batch_tgt.push_back(batch_tgt.size());
+                batch_tgt.add(tok, spec_past_tgt + i, { sq + off });
+                drafts[sq].i_batch_dft = batch_dft.size();
+                batch_dft.add(tok, n_past_cur, { sq + off });
+                if (batch_tgt.size() > P.n_draft) drafts[sq].drafting = false;
+            }
+        }
+        if (batch_dft.size() == 0) break;
+        llama_decode(ctx_dft, batch_dft.view(max_seq + 1));                                              // :1090 synchronous draft step
+        ++n_past_cur;
+        ++n_drafted;
+        max_ran_seq = n_seq_cur;
+        batch_dft.clear();
+        if (batch_tgt.size() > P.n_draft) break;
+    }
+    if (batch_dft.size() != 0) llama_decode(ctx_dft, batch_dft.view(max_seq + 1));                       // :1107-1113
+
+    if (batch_tgt.size() == 0) {                                                                         // :1129-1135
+        free_offsets.push_back(off);
+        n_rejected++;
+        return true;
+    }
+    for (int s = 0; s < np; ++s) {                                                                       // :1149-1157
+        if (!drafts[s].active) continue;
+        drafts[s].tokens.erase(drafts[s].tokens.begin());
+    }
+    if (first_run) ++n_drafted;
+    n_spec_runs++;
+    begin_async_run(ctx_tgt, tgt_runs, drafts, spec_past_tgt, n_past_dft_arg, true, batch_tgt,
+                    spec_past_tgt + (int) drafts[0].tokens.size(), prefix_n_past, off);                 // :1163
+    spec_past_tgt += (int) drafts[0].tokens.size();
+    spec_past_dft += (int) drafts[0].tokens.size();
+    id = drafts[0].tokens.back();
+    first_run = false;
+    return false;
+}
+
+// :765-844
+void Scheduler::speculation_loop() {
+    bool is_waiting = llama_mpi_iprobe(ctx_tgt);
+    if (is_waiting) free_offsets.push_back(current.seq_offset);
+    int   iter = 0;
+    float p_adjust;
+    while (!is_waiting && P.p_accept + (p_adjust = p_adjust_of(iter)) < 1.0f) {
+        const int orig_offset = current.seq_offset;
+        bool should_run = true;
+        do {                                                                                             // :791-807
+            should_run = true;
+            for (const Run & r : tgt_runs) {
+                if (r.seq_offset == current.seq_offset && r.speculative) {
+                    should_run = false;
+                    if (!free_offsets.empty()) { current.seq_offset = free_offsets.front(); free_offsets.pop_front(); }
+                    break;
+                }
+            }
+        } while (!should_run && !free_offsets.empty());
+        if (!should_run) break;
+        auto it = std::find(free_offsets.begin(), free_offsets.end(), current.seq_offset);
+        if (it != free_offsets.end()) free_offsets.erase(it);
+        if (start_spec_run(n_past_tgt, n_past_dft, orig_offset, p_adjust)) break;
+        is_waiting = llama_mpi_iprobe(ctx_tgt);
+        first_run  = false;
+        iter++;
+        if (P.max_spec_runs > 0 && (int) tgt_runs.size() >= P.max_spec_runs) break;   // optional bound (0 = reference behaviour)
+    }
+}
+
+int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, int out_cap, pib_spec_result * res, double * itl_us, int itl_cap) {
+    if (n_prompt < 2) { pib_set_error("speculative: the prompt needs at least 2 tokens"); return -1; }
+    const int64_t t_enc_start = llama_time_us();
+    std::vector<llama_seq_id> all_ids(max_seq + 1);
+    for (int i = 0; i <= max_seq; i++) all_ids[i] = i;
+    {   // :230-246 prompt: every token belongs to every sequence; target decodes n-1 tokens, then the last one
+        Batch bt, bd;
+        for (int i = 0; i < n_prompt - 1; i++) { bt.add(prompt[i], i, all_ids); bd.add(prompt[i], i, all_ids); }
+        if (llama_decode(ctx_tgt, bt.view(max_seq + 1)) != 0) return -1;
+        bt.clear();
+        bt.add(prompt[n_prompt - 1], n_prompt - 1, all_ids);
+        bd.add(prompt[n_prompt - 1], n_prompt - 1, all_ids);
+        if (llama_decode(ctx_tgt, bt.view(max_seq + 1)) != 0) return -1;
+        if (llama_decode(ctx_dft, bd.view(max_seq + 1)) != 0) return -1;
+    }
+    const int64_t t_enc_end = llama_time_us();
+    n_past_tgt = n_past_dft = n_prompt;
+    generated.assign(prompt, prompt + n_prompt);
+    drafts[0].i_batch_tgt = { 0 };                                                                       // :284-286
+    current = Run();
+    current.n_past_tgt = n_past_tgt - 1; current.n_past_max = n_past_tgt; current.n_past_dft = n_past_dft - 1;
+    current.seq_offset = free_offsets.front();
+    spec_past_tgt = n_past_tgt; spec_past_dft = n_past_dft;
+    std::deque<Run> dft_runs;
+    bool has_eos = false, first_token = false, has_run_first_token = false;
+    int64_t ttft = llama_time_us(), itt_start = 0;
+    std::vector<int64_t> itl;
+    const int64_t t_dec_start = llama_time_us();
+    first_run = true;
+    int n_out = 0;
+
+    while (!failed) {
+        int i_dft = 0, s_keep = 0;
+        const bool is_waiting = llama_mpi_iprobe(ctx_tgt);                                               // :323
+        if (!tgt_runs.empty() && is_waiting) {                                                           // :328-395
+            check_for_cancel();
+            Run & run = tgt_runs.back();
+            if (run.canceled) {
+                llama_finish_async_decode(*ctx_tgt, run.batch.view(max_seq + 1), run.handle);           // drain (:366)
+                if (run.speculative) free_offsets.push_back(run.seq_offset);
+                tgt_runs.pop_back();
+                continue;
+            }
+            drafts = run.drafts;
+            current.speculative = run.speculative; current.n_past_max = run.n_past_max; current.n_past_tgt = run.n_past_tgt;
+            current.n_past_dft = run.n_past_dft; current.seq_offset = run.seq_offset;
+            s_keep = run.s_keep;
+            for (int s = 0; s < np; ++s) if (drafts[s].active) drafts[s].tokens.erase(drafts[s].tokens.begin());
+            llama_finish_async_decode(*ctx_tgt, run.batch.view(max_seq + 1), run.handle);
+            tgt_runs.pop_back();
+            spec_past_tgt = n_past_tgt; spec_past_dft = n_past_dft;
+            first_run = true;
+        } else if (!tgt_runs.empty()) {                                                                  // :397-403 speculate while waiting
+            speculation_loop();
+            continue;
+        }
+
+        // ---- verification walk (:439-560) ----
+        bool any_match = false;
+        int  keep0 = s_keep;
+        bool keeps_nonempty = true;
+        while (keeps_nonempty) {
+            id = greedy(ctx_tgt, drafts[keep0].i_batch_tgt[i_dft]);                                      // :448
+            if (current.n_past_tgt + i_dft == n_past_tgt - 1) {                                          // a token nobody has seen yet (:465)
+                any_match = true;
+                ++n_predict;
+                if (current.speculative) n_accept++;
+                if (has_run_first_token) {
+                    if (first_token) { ttft = llama_time_us() - ttft; first_token = false; }
+                    else itl.push_back(llama_time_us() - itt_start);
+                    itt_start = llama_time_us();
+                }
+                generated.push_back(id);
+                if (n_out < out_cap) out[n_out] = id;
+                n_out++;
+            }
+            if (id == llama_token_eos(llama_get_model(ctx_tgt)) && !P.ignore_eos) has_eos = true;
+            if (!current.speculative) break;
+            bool matches = false;                                                                        // :518-535
+            keeps_nonempty = false;
+            for (int s = 0; s < np; ++s) {
+                if (!drafts[s].active) continue;
+                if (i_dft < (int) drafts[s].tokens.size() && id == drafts[s].tokens[i_dft]) {
+                    if (!matches) { keep0 = s; s_keep = s; }
+                    matches = true;
+                    keeps_nonempty = true;
+                } else drafts[s].active = false;
+            }
+            if (matches) {                                                                               // :537-552
+                if (current.n_past_tgt + i_dft == n_past_tgt - 1) { ++n_accept; ++n_past_tgt; ++n_past_dft; }
+                ++i_dft;
+            }
+        }
+        if (!any_match) {                                                                                // :569-577
+            if (current.speculative) free_offsets.push_back(current.seq_offset);
+            continue;
+        }
+        n_rejected = 0;
+        check_for_cancel();                                                                              // :581
+
+        if (current.speculative) {                                                                       // :585-628 KV commit
+            for (int i = 0; i < np; i++) {
+                llama_kv_cache_seq_rm(ctx_tgt, i + current.seq_offset, n_past_tgt, -1);
+                llama_kv_cache_seq_rm(ctx_dft, i + current.seq_offset, n_past_dft, -1);
+            }
+            llama_kv_cache_seq_rm(ctx_tgt, 0, current.n_past_tgt + 1, n_past_tgt);
+            llama_kv_cache_seq_rm(ctx_dft, 0, current.n_past_dft + 1, n_past_dft);
+            llama_kv_cache_seq_cp(ctx_tgt, s_keep + current.seq_offset, 0, current.n_past_tgt + 1, n_past_tgt);
+            llama_kv_cache_seq_cp(ctx_dft, s_keep + current.seq_offset, 0, current.n_past_dft + 1, n_past_dft);
+            // the reference interleaves the two contexts inside one loop; the contexts are independent, so two loops
+            // give the same per-context call order (and let the op-log collapse each into one KVOP_SWEEP)
+            for (int i = 1; i <= max_seq; i++) {
+                llama_kv_cache_seq_rm(ctx_tgt, i, current.n_past_tgt + 1, n_past_tgt);
+                llama_kv_cache_seq_cp(ctx_tgt, 0, i, current.n_past_tgt + 1, n_past_tgt);
+            }
+            for (int i = 1; i <= max_seq; i++) {
+                llama_kv_cache_seq_rm(ctx_dft, i, current.n_past_dft + 1, n_past_dft);
+                llama_kv_cache_seq_cp(ctx_dft, 0, i, current.n_past_dft + 1, n_past_dft);
+            }
+        }
+        begin_non_spec_run(ctx_tgt, tgt_runs, n_past_tgt, n_past_dft);                                   // :630 (async)
+        begin_non_spec_run(ctx_dft, dft_runs, n_past_dft, n_past_dft);                                   // :633 (finished right away)
+        if (!has_run_first_token) { has_run_first_token = true; first_token = true; }
+        {
+            Run & dr = dft_runs.back();
+            llama_finish_async_decode(*ctx_dft, dr.batch.view(max_seq + 1), dr.handle);
+            dft_runs.pop_back();
+        }
+        spec_past_tgt = n_past_tgt; spec_past_dft = n_past_dft;
+        if (!current.speculative) {                                                                      // :653-662
+            if (free_offsets.empty()) continue;
+            current.seq_offset = free_offsets.front();
+            free_offsets.pop_front();
+        }
+        speculation_loop();                                                                              // :666
+        if (n_predict > P.n_predict || has_eos || failed) break;                                         // :672
+    }
+    const int64_t t_dec_end = llama_time_us();
+    for (int i = (int) tgt_runs.size() - 1; i >= 0; i--) llama_finish_async_decode(*ctx_tgt, tgt_runs[i].batch.view(max_seq + 1), tgt_runs[i].handle);
+    tgt_runs.clear();
+    if (res) {
+        res->n_predict = n_predict; res->n_drafted = n_drafted; res->n_accept = n_accept; res->n_cancelled = n_cancel; res->n_spec_runs = n_spec_runs;
+        res->t_encode_s = (t_enc_end - t_enc_start) / 1e6; res->t_decode_s = (t_dec_end - t_dec_start) / 1e6;
+        res->decode_tok_per_s = res->t_decode_s > 0 ? n_predict / res->t_decode_s : 0;                  // :697
+        res->ttft_s = ttft / 1e6;
+        res->n_itl = (int) itl.size();
+        double sum = 0;
+        for (int64_t v : itl) sum += (double) v;
+        res->itl_mean_s = itl.empty() ? 0 : sum / itl.size() / 1e6;                                      // the reference reports the mean (:683-688)
+        std::vector<int64_t> srt = itl;
+        std::sort(srt.begin(), srt.end());
+        res->itl_p50_s = srt.empty() ? 0 : srt[srt.size() / 2] / 1e6;
+    }
+    for (int i = 0; i < (int) itl.size() && i < itl_cap; i++) itl_us[i] = (double) itl[i];
+    return n_out;
+}
+
+}   // namespace
+
+extern "C" {
+
+pib_spec_params pib_spec_default_params(void) {
+    pib_spec_params p;
+    p.n_draft = 16; p.n_parallel = 1; p.p_accept = 0.5f; p.p_split = 0.1f; p.p_recovery = 0.0f; p.p_decay = 0.0f;   // common.h:54-61
+    p.n_predict = 128; p.ignore_eos = 1; p.max_spec_runs = 0;
+    return p;
+}
+
+int pib_speculative_generate(struct llama_context * ctx_tgt, struct llama_context * ctx_dft, const llama_token * prompt, int n_prompt,
+                             const pib_spec_params * params, llama_token * out_tokens, int out_cap, pib_spec_result * result,
+                             double * itl_us, int itl_cap) {
+    if (!ctx_tgt || !ctx_dft || !prompt || !params) { pib_set_error("pib_speculative_generate: bad arguments"); return -1; }
+    const int need = 1000 * std::max(1, params->n_parallel) + 2;
+    if (llama_pib_kv_words(ctx_tgt) * 32 < need || llama_pib_kv_words(ctx_dft) * 32 < need) {
+        pib_set_error("pib_speculative_generate: contexts need a sequence-id capacity of %d (llama_pib_new_context)", need);
+        return -1;
+    }
+    if (params->ignore_eos) {          // common.cpp:1061-1063: logit_bias[eos] = -inf, applied on the device before argmax
+        const llama_token e_t = llama_token_eos(llama_get_model(ctx_tgt)), e_d = llama_token_eos(llama_get_model(ctx_dft));
+        const float ninf = -INFINITY;
+        llama_pib_set_logit_bias(ctx_tgt, &e_t, &ninf, 1);
+        llama_pib_set_logit_bias(ctx_dft, &e_d, &ninf, 1);
+    }
+    Scheduler s(ctx_tgt, ctx_dft, *params);
+    return s.run(prompt, n_prompt, out_tokens, out_cap, result, itl_us, itl_cap);
+}
+
+// plain (non-speculative) greedy decode: the reference's examples/main under the same launch (the "Sequential" bar of the
+// paper, scripts/dolphin_sequential_8_nodes.sh) -- the denominator of the 3x target
+int pib_plain_generate(struct llama_context * ctx, const llama_token * prompt, int n_prompt, int n_predict, llama_token * out_tokens,
+                       pib_spec_result * result, double * itl_us, int itl_cap) {
+    if (!ctx || !prompt || n_prompt < 1) { pib_set_error("pib_plain_generate: bad arguments"); return -1; }
+    const int64_t t0 = llama_time_us();
+    Batch b;
+    for (int i = 0; i < n_prompt; i++) b.add(prompt[i], i, { 0 });
+    if (llama_decode(ctx, b.view(1)) != 0) return -1;
+    const int64_t t1 = llama_time_us();
+    llama_token_data t8[8];
+    llama_pib_get_top8(ctx, n_prompt - 1, t8);
+    llama_token id = t8[0].id;
+    int n_past = n_prompt, n_out = 0;
+    std::vector<int64_t> itl;
+    int64_t last = llama_time_us(), ttft = 0;
+    while (n_out < n_predict) {
+        out_tokens[n_out++] = id;
+        const int64_t now = llama_time_us();
+        if (n_out == 1) ttft = now - t1; else itl.push_back(now - last);
+        last = now;
+        if (n_out >= n_predict) break;
+        b.clear();
+        b.add(id, n_past++, { 0 });
+        if (llama_decode(ctx, b.view(1)) != 0) return -1;
+        llama_pib_get_top8(ctx, 0, t8);
+        id = t8[0].id;
+    }
+    const int64_t t2 = llama_time_us();
+    if (result) {
+        memset(result, 0, sizeof(*result));
+        result->n_predict = n_out; result->t_encode_s = (t1 - t0) / 1e6; result->t_decode_s = (t2 - t1) / 1e6;
+        result->decode_tok_per_s = n_out / std::max(1e-9, result->t_decode_s);
+        result->ttft_s = ttft / 1e6; result->n_itl = (int) itl.size();
+        double sum = 0; for (int64_t v : itl) sum += (double) v;
+        result->itl_mean_s = itl.empty() ? 0 : sum / itl.size() / 1e6;
+        std::vector<int64_t> srt = itl; std::sort(srt.begin(), srt.end());
+        result->itl_p50_s = srt.empty() ? 0 : srt[srt.size() / 2] / 1e6;
+    }
+    for (int i = 0; i < (int) itl.size() && i < itl_cap; i++) itl_us[i] = (double) itl[i];
+    return n_out;
+}
+
+}   // extern "C"

@@ -208,3 +208,87 @@ class Context:
         if self.model:
             self.L.llama_free_model(self.model)
             self.model = None
+
+
+# ---- scheduler level (include/pipeinfer_sched.h) ----------------------------------------------------------------------
+class SpecParams(C.Structure):
+    _fields_ = [("n_draft", C.c_int32), ("n_parallel", C.c_int32), ("p_accept", C.c_float), ("p_split", C.c_float),
+                ("p_recovery", C.c_float), ("p_decay", C.c_float), ("n_predict", C.c_int32), ("ignore_eos", C.c_int32),
+                ("max_spec_runs", C.c_int32)]
+
+
+class SpecResult(C.Structure):
+    _fields_ = [("n_predict", C.c_int32), ("n_drafted", C.c_int32), ("n_accept", C.c_int32), ("n_cancelled", C.c_int32),
+                ("n_spec_runs", C.c_int32), ("n_itl", C.c_int32), ("t_encode_s", C.c_double), ("t_decode_s", C.c_double),
+                ("decode_tok_per_s", C.c_double), ("ttft_s", C.c_double), ("itl_mean_s", C.c_double), ("itl_p50_s", C.c_double)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+def _bind_sched(L):
+    if getattr(L, "_pib_sched_bound", False):
+        return
+    L.pib_spec_default_params.restype = SpecParams
+    L.pib_speculative_generate.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int, C.POINTER(SpecParams),
+                                           C.POINTER(C.c_int32), C.c_int, C.POINTER(SpecResult), C.POINTER(C.c_double), C.c_int]
+    L.pib_plain_generate.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int, C.c_int, C.POINTER(C.c_int32),
+                                     C.POINTER(SpecResult), C.POINTER(C.c_double), C.c_int]
+    L._pib_sched_bound = True
+
+
+def spec_params(**kw):
+    L = api()
+    _bind_sched(L)
+    p = L.pib_spec_default_params()
+    for k, v in kw.items():
+        setattr(p, k, v)
+    return p
+
+
+def speculative_generate(tgt, dft, prompt_ids, params):
+    """tgt / dft: Context objects created with max_seq >= 1000 * n_parallel + 2.  Returns (token ids, result dict, itl_us)."""
+    L = api()
+    _bind_sched(L)
+    n = len(prompt_ids)
+    pr = (C.c_int32 * n)(*prompt_ids)
+    cap = params.n_predict + 64
+    out = (C.c_int32 * cap)()
+    itl = (C.c_double * cap)()
+    res = SpecResult()
+    k = L.pib_speculative_generate(tgt.ctx, dft.ctx, pr, n, C.byref(params), out, cap, C.byref(res), itl, cap)
+    if k < 0:
+        raise PibError(L.pib_last_error().decode())
+    return list(out[:min(k, cap)]), res.as_dict(), list(itl[:res.n_itl])
+
+
+def plain_generate(ctx, prompt_ids, n_predict):
+    L = api()
+    _bind_sched(L)
+    n = len(prompt_ids)
+    pr = (C.c_int32 * n)(*prompt_ids)
+    out = (C.c_int32 * (n_predict + 1))()
+    itl = (C.c_double * (n_predict + 1))()
+    res = SpecResult()
+    k = L.pib_plain_generate(ctx.ctx, pr, n, n_predict, out, C.byref(res), itl, n_predict + 1)
+    if k < 0:
+        raise PibError(L.pib_last_error().decode())
+    return list(out[:k]), res.as_dict(), list(itl[:res.n_itl])
+
+
+def tokenize(ctx, text, add_bos=True):
+    L = api()
+    buf = (C.c_int32 * (len(text) * 4 + 8))()
+    raw = text.encode()
+    n = L.llama_tokenize(ctx.model, raw, len(raw), buf, len(buf), add_bos, True)
+    return list(buf[:n])
+
+
+def detokenize(ctx, ids):
+    L = api()
+    out = b""
+    b = C.create_string_buffer(64)
+    for t in ids:
+        n = L.llama_token_to_piece(ctx.model, t, b, 64)
+        out += b.raw[:max(n, 0)]
+    return out

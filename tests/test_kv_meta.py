@@ -91,3 +91,36 @@ def test_commit_loop_is_coalesced_and_identical_to_the_literal_loop(oracle):
         assert np.array_equal(st["pos"], np.ctypeslib.as_array(o.pos, shape=(n_ctx,)))
         assert np.array_equal(st["bits"], np.ctypeslib.as_array(o.bits, shape=(n_ctx, o.n_words)))
         oracle.L.po_kv_free(okv)
+
+
+def test_non_spec_run_loops_are_coalesced_and_identical(oracle):
+    # speculative.cpp:1252-1268: for i in 0..max_seq: seq_rm(i, n, n+1)  ...decode...  for i in 1..max_seq: seq_cp(0, i, n, n+1)
+    rng = np.random.default_rng(4)
+    n_ctx, max_seq = 64, 70
+    for trial in range(20):
+        kv = KvTest(n_ctx, max_seq + 1)
+        okv = oracle.L.po_kv_new(n_ctx, max_seq + 1)
+        pos_next = 0
+        for _ in range(5):
+            n = int(rng.integers(1, 7))
+            seqs = [sorted(set(rng.integers(0, max_seq + 1, int(rng.integers(1, 6))).tolist())) for _ in range(n)]
+            ps = np.arange(pos_next, pos_next + n, dtype=np.int32); pos_next += n
+            ns, ptrs, keep = op.seq_ptrs(seqs)
+            assert kv.decode([0] * n, ps.tolist(), seqs)[0] == 0
+            oracle.L.po_kv_find_slot(okv, n, ps.ctypes.data, ns.ctypes.data, ptrs)
+            okv.contents.head = (okv.contents.head + n) % n_ctx
+        n_past = int(rng.integers(0, pos_next))
+        lo = int(rng.integers(0, 3)); hi = int(rng.integers(lo, max_seq + 1))
+        for i in range(lo, hi + 1):
+            kv.seq_rm(i, n_past, n_past + 1); oracle.L.po_kv_seq_rm(okv, i, n_past, n_past + 1)
+        assert kv.L.pib_kvtest_pending(kv.h) == 1
+        src = int(rng.integers(0, 2))
+        for i in range(src + 1, hi + 1):
+            kv.seq_cp(src, i, n_past - 2, -1); oracle.L.po_kv_seq_cp(okv, src, i, n_past - 2, -1)
+        assert kv.L.pib_kvtest_pending(kv.h) <= 2
+        st = kv.state()
+        o = okv.contents
+        assert (st["head"], st["used"]) == (o.head, o.used)
+        assert np.array_equal(st["pos"], np.ctypeslib.as_array(o.pos, shape=(n_ctx,)))
+        assert np.array_equal(st["bits"], np.ctypeslib.as_array(o.bits, shape=(n_ctx, o.n_words)))
+        oracle.L.po_kv_free(okv)
