@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""bench.py -- accepted tokens/s + p50 per-token latency of PipeInfer-style asynchronous pipelined speculation.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--config 70b|7b|tiny]
+
+Workload (BASELINE.json configs[2], the one the metric is quoted on): Dolphin/Llama-2-70B-architecture target in Q4_K
+(38.8 GB, fits one B200) + TinyLlama-1.1B-architecture draft, random-init weights generated in HBM ("bigram" flavour:
+both models predict a fixed permutation of the last token, the draft agreeing with the target on --agree of the tokens),
+synthetic 64-token prompt, flags of the authors' launch script (examples/speculative/scripts/dolphin_tinyllama_8_nodes.sh:
+--draft 3 -np 3 -pa 0.1 -ps 0.9 -n 128 -c 1024, greedy).  One step = one generation of 128 tokens.
+
+value  = sum(n_predict) / sum(t_decode) over the timed steps: the reference's own metric (speculative.cpp:697), prompt
+         already ingested (inputs resident in HBM).
+e2e    = sum(n_predict) / wall time of the timed steps through the public C ABI (pib_speculative_generate) with host
+         buffers: prompt ids in, KV clear, prompt ingestion, every descriptor / op-log H2D and result D2H included.
+The roofline object times the dominant kernel (the gate|up projection GEMV of the target, 264 MB of Q4_K weights per
+launch) with CUDA events on its own stream during the timed steps.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import re
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+Q4_K, Q4_0, Q8_0 = 12, 2, 8
+CONFIGS = {
+    # name: (target (L, E, H, HKV, FF, V, type), draft (...), label)
+    "70b": ((80, 8192, 64, 8, 28672, 32000, Q4_K), (22, 2048, 32, 4, 5632, 32000, Q4_K),
+            "Llama-2-70B-arch Q4_K target + TinyLlama-1.1B-arch Q4_K draft"),
+    "7b": ((32, 4096, 32, 32, 11008, 32000, Q4_0), (22, 2048, 32, 4, 5632, 32000, Q4_0),
+           "Llama-2-7B-arch Q4_0 target + TinyLlama-1.1B-arch Q4_0 draft"),
+    "tiny": ((8, 1024, 8, 2, 2048, 4096, Q4_K), (2, 512, 8, 2, 1024, 4096, Q4_K), "8-layer 1024-wide target + 2-layer draft (smoke)"),
+}
+TYPE_NAME = {Q4_K: "q4_k", Q4_0: "q4_0", Q8_0: "q8_0"}
+BPW = {Q4_K: 4.5, Q4_0: 4.5, Q8_0: 8.5}
+KIND = {0: "qkv", 1: "attn_out", 2: "gate_up", 3: "down", 4: "lm_head"}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)"""
+
+    def __init__(self, gpu):
+        self.rows, self.proc, self.gpu = [], None, gpu
+
+    def start(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the UNMODIFIED reference `speculative` (oracle/_ref, built from /root/reference by
+# oracle/Makefile) under the mini-MPI shim on this box's host cores.  A 70B-width model cannot be run at full depth on the
+# host in bounded time, so the sample is depth-reduced (same width, same draft) at two depths and the per-token time is
+# extrapolated linearly in the number of target layers.
+def run_reference_sample(cfg_name, args, budget="small"):
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    spec, shim = os.path.join(ref, "speculative"), os.path.join(ref, "mpirun_shim")
+    if not (os.path.exists(spec) and os.path.exists(shim)):
+        return None
+    (L, E, H, HKV, FF, V, wt), (dL, dE, dH, dHKV, dFF, dV, dwt), label = CONFIGS[cfg_name]
+    cores = os.cpu_count() or 1
+    n_tgt_ranks = 2
+    threads = max(1, cores // (n_tgt_ranks + 1))
+    depths = (2, 4) if budget == "small" else (2, 6)
+    n_pred = 12 if budget == "small" else 24
+    if cfg_name == "tiny":
+        depths = (2, 4)
+    tmp = "/tmp/pib_ref_%d" % os.getpid()
+    os.makedirs(tmp, exist_ok=True)
+    mk = [sys.executable, os.path.join(ROOT, "tools", "make_gguf.py"), "--direct", "--quant", TYPE_NAME[wt]]
+    dft = os.path.join(tmp, "dft.gguf")
+    subprocess.run(mk + ["--out", dft, "--n-layer", str(dL), "--n-embd", str(dE), "--n-head", str(dH), "--n-head-kv", str(dHKV),
+                         "--n-ff", str(dFF), "--n-vocab", str(dV), "--agree", str(args.agree), "--seed", "5"], check=True)
+    prompt = os.path.join(tmp, "prompt.txt")
+    open(prompt, "w").write("".join(chr(0x21 + (i * 7) % 90) for i in range(args.prompt_len - 2)))
+    res = {}
+    for d in depths:
+        tgt = os.path.join(tmp, "tgt_%d.gguf" % d)
+        subprocess.run(mk + ["--out", tgt, "--n-layer", str(d), "--n-embd", str(E), "--n-head", str(H), "--n-head-kv", str(HKV),
+                             "--n-ff", str(FF), "--n-vocab", str(V), "--agree", "1.0", "--seed", "3"], check=True)
+        pre = os.path.join(tmp, "run_%d" % d)
+        t0 = time.time()
+        subprocess.run([shim, "-np", str(n_tgt_ranks + 1), "--timeout", "900", "--out-prefix", pre, spec, "-m", tgt, "-md", dft,
+                        "-f", prompt, "-n", str(n_pred), "-c", "1024", "--temp", "-1", "--repeat-last-n", "0", "--ignore-eos",
+                        "--draft", str(args.draft), "-np", str(args.np), "-pa", str(args.pa), "-ps", str(args.ps), "-pr", "0.0",
+                        "-t", str(threads), "-tb", str(threads), "--mpi-layer-split", "0.5,0.5/1.0"],
+                       check=True, cwd=tmp, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        err = open(pre + ".0.err", errors="replace").read()
+        m = re.search(r"decoded\s+(\d+) tokens in\s+([0-9.]+) seconds", err)
+        itl = re.search(r"Average inter-token latency: ([0-9.]+)", err)
+        acc = re.search(r"n_accept\s+=\s+(\d+)", err)
+        drf = re.search(r"n_drafted\s+=\s+(\d+)", err)
+        res[d] = dict(tokens=int(m.group(1)), seconds=float(m.group(2)), itl_mean_s=float(itl.group(1)) if itl else None,
+                      n_accept=int(acc.group(1)) if acc else None, n_drafted=int(drf.group(1)) if drf else None,
+                      wall_s=time.time() - t0)
+        os.unlink(tgt)
+    os.unlink(dft)
+    d0, d1 = depths
+    t0_tok, t1_tok = res[d0]["seconds"] / res[d0]["tokens"], res[d1]["seconds"] / res[d1]["tokens"]
+    per_layer = max(0.0, (t1_tok - t0_tok) / (d1 - d0))
+    fixed = max(0.0, t0_tok - per_layer * d0)
+    full = fixed + per_layer * L
+    sample = ("reference `speculative` (oracle/_ref) under the mini-MPI shim, 2 target ranks + 1 draft rank x %d threads, "
+              "same flags; %s-width target at %d and %d layers (%.3f / %.3f s per accepted token), full draft; value = "
+              "1 / (%.4f + %d * %.4f) s extrapolated to %d layers" % (threads, "x".join(map(str, (E, FF))), d0, d1, t0_tok, t1_tok,
+                                                                     fixed, L, per_layer, L))
+    return dict(value=1.0 / full if full > 0 else None, unit="tokens/s", cores=cores, kind="reference", sample=sample,
+                raw={str(k): v for k, v in res.items()}, itl_est_s=full)
+
+
+# --------------------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="70b", choices=sorted(CONFIGS))
+    ap.add_argument("--agree", type=float, default=0.8, help="fraction of tokens on which the random-init draft predicts the target's token")
+    ap.add_argument("--n-predict", type=int, default=128)
+    ap.add_argument("--prompt-len", type=int, default=64)
+    ap.add_argument("--draft", type=int, default=3)
+    ap.add_argument("--np", type=int, default=3)
+    ap.add_argument("--pa", type=float, default=0.1)
+    ap.add_argument("--ps", type=float, default=0.9)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    (L, E, H, HKV, FF, V, wt), dshape, label = CONFIGS[args.config]
+    config = {"workload": "%s, random-init (bigram flavour, draft agreement %.2f), %d-token synthetic prompt, greedy, "
+                          "--draft %d -np %d -pa %g -ps %g -n %d -c 1024, layer split over %d GPU(s)"
+                          % (label, args.agree, args.prompt_len, args.draft, args.np, args.pa, args.ps, args.n_predict, args.gpus),
+              "l2_policy": "inputs larger than L2: every pass streams the target's weights (38.8 GB >> 126 MB)"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        t0 = time.time()
+        r = run_reference_sample(args.config, args, budget="large")
+        if r is None:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/speculative not built (needs /root/reference at build time)"}))
+            return 0
+        line = {"impl": "reference", "metric": "accepted tokens/sec", "value": r["value"], "unit": "tokens/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * args.n_predict / r["value"] if r["value"] else None,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int8 x int4/int8 blocks, fp32 accumulate",
+                "data": "synthetic", "config": config, "latency_p50_ms": None, "latency_mean_ms": 1000.0 * r["itl_est_s"],
+                "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": r["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "raw": r["raw"], "wall_s": time.time() - t0}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    from pipeinfer_b200 import llama
+    lib = llama.api()
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0"))))
+    dev = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(dev)
+    if world > 1:
+        from pipeinfer_b200 import pipeline
+        return pipeline.bench_multi_gpu(args, config, CONFIGS)
+
+    lib.llama_pib_io_bytes.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    lib.llama_pib_profile_layer.argtypes = [C.c_void_p, C.c_int]
+    lib.llama_pib_profile_read.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    lib.llama_pib_matrix_shape.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_uint64)]
+    cap = 1000 * args.np + 2
+    t_load = time.time()
+    tgt = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=(L, E, H, HKV, FF, V, wt, 1, 1, 1.0))
+    dft = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=dshape + (2, 1, args.agree))
+    t_load = time.time() - t_load
+    prompt = [1] + [3 + (i * 7919) % (V - 3) for i in range(args.prompt_len - 1)]
+    params = llama.spec_params(n_draft=args.draft, n_parallel=args.np, p_accept=args.pa, p_split=args.ps, n_predict=args.n_predict)
+
+    def io(ctx):
+        a, b = C.c_uint64(), C.c_uint64()
+        lib.llama_pib_io_bytes(ctx.ctx, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def step():
+        lib.llama_kv_cache_clear(tgt.ctx)
+        lib.llama_kv_cache_clear(dft.ctx)
+        return llama.speculative_generate(tgt, dft, prompt, params)
+
+    first = None
+    for _ in range(args.warmup):
+        toks, res, itl = step()
+        first = first or toks
+    prof_layer = L // 2
+    lib.llama_pib_profile_layer(tgt.ctx, prof_layer)
+    k0 = lib.llama_pib_kernel_launches(tgt.ctx) + lib.llama_pib_kernel_launches(dft.ctx)
+    io0 = [io(tgt), io(dft)]
+    clocks = ClockSampler(dev)
+    clocks.start()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    results, itls = [], []
+    for _ in range(args.steps):
+        toks, res, itl = step()
+        assert toks[:len(first)] == first[:len(toks)], "non-deterministic generation"
+        results.append(res)
+        itls += itl
+    torch.cuda.synchronize()
+    e1.record()
+    e1.synchronize()
+    wall_ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    lib.llama_pib_profile_layer(tgt.ctx, -1)
+    k1 = lib.llama_pib_kernel_launches(tgt.ctx) + lib.llama_pib_kernel_launches(dft.ctx)
+    io1 = [io(tgt), io(dft)]
+
+    n_tok = sum(r["n_predict"] for r in results)
+    t_dec = sum(r["t_decode_s"] for r in results)
+    itls_ms = sorted(x / 1000.0 for x in itls)
+    p50 = itls_ms[len(itls_ms) // 2] if itls_ms else None
+
+    # roofline of the dominant kernel from the per-launch events
+    n = 8192
+    kind, bb, ms = (C.c_int32 * n)(), (C.c_int32 * n)(), (C.c_float * n)()
+    cnt = lib.llama_pib_profile_read(tgt.ctx, kind, bb, ms, n)
+    peak, peak_src = measured_peaks()
+    per_kind = {}
+    for i in range(cnt):
+        per_kind.setdefault(kind[i], []).append((bb[i], ms[i]))
+    kernels = {}
+    for k, lst in per_kind.items():
+        N_, K_, by = C.c_int64(), C.c_int64(), C.c_uint64()
+        lib.llama_pib_matrix_shape(tgt.model, prof_layer, k, C.byref(N_), C.byref(K_), C.byref(by))
+        mean_b = sum(x[0] for x in lst) / len(lst)
+        mean_ms = sum(x[1] for x in lst) / len(lst)
+        alg = by.value + mean_b * K_.value * 4 + mean_b * N_.value * 4        # weights + F32 activations in + F32 out
+        kernels[KIND[k]] = {"launches": len(lst), "N": N_.value, "K": K_.value, "mean_batch": round(mean_b, 2), "mean_ms": mean_ms,
+                            "algorithmic_bytes": alg, "achieved_gbs": alg / mean_ms / 1e6, "frac": alg / mean_ms / 1e6 / peak}
+    dom = kernels.get("gate_up")
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get("gate_up_dram_bytes_per_launch")
+    roofline = None
+    if dom:
+        roofline = {"bound": "hbm", "kernel": "dequant-GEMV %s, gate|up projection %dx%d, layer %d of the target" % (TYPE_NAME[wt], dom["N"], dom["K"], prof_layer),
+                    "achieved": dom["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": dom["frac"], "traffic": traffic,
+                    "peak_source": peak_src, "frac_of_8TBs_nominal": dom["achieved_gbs"] / 8000.0, "all_matmuls": kernels}
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        try:
+            r = run_reference_sample(args.config, args, budget="small")
+            if r:
+                cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        except Exception as e:      # the baseline is informative; never lose the GPU line over it
+            cpu = {"value": None, "unit": "tokens/s", "cores": os.cpu_count(), "kind": "reference", "sample": "failed: %r" % (e,)}
+
+    h2d = sum(io1[i][0] - io0[i][0] for i in range(2)) + 4 * len(prompt) * args.steps
+    d2h = sum(io1[i][1] - io0[i][1] for i in range(2))
+    acc = sum(r["n_accept"] for r in results) / max(1, sum(r["n_drafted"] for r in results))
+    line = {"metric": "accepted tokens/sec", "value": n_tok / t_dec, "unit": "tokens/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": wall_ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "int8 x int4 blocks (Q4_K x Q8_K), fp32 accumulate", "data": "synthetic", "config": config,
+            "latency_p50_ms": p50, "latency_mean_ms": sum(itls_ms) / len(itls_ms) if itls_ms else None,
+            "ttft_ms": 1000.0 * results[-1]["ttft_s"], "accept_rate": acc,
+            "spec": {k: sum(r[k] for r in results) / len(results) for k in ("n_predict", "n_drafted", "n_accept", "n_cancelled", "n_spec_runs")},
+            "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": {"value": n_tok / (wall_ms / 1000.0), "unit": "tokens/s", "h2d_bytes_per_step": h2d // args.steps,
+                    "d2h_bytes_per_step": d2h // args.steps},
+            "gpu_launches": int(k1 - k0), "weights_gb": (lib.llama_pib_weight_bytes(tgt.model) + lib.llama_pib_weight_bytes(dft.model)) / 1e9,
+            "model_build_s": t_load}
+    print(json.dumps(line))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

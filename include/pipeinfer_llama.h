@@ -189,6 +189,15 @@ int  llama_pib_kv_state(struct llama_context * ctx, int from_device, int32_t * s
 int  llama_pib_kv_words(const struct llama_context * ctx);
 uint64_t llama_pib_kernel_launches(const struct llama_context * ctx);
 size_t   llama_pib_weight_bytes(const struct llama_model * model);
+/* measurement hooks used by bench.py: host<->device bytes issued so far; CUDA-event timing of every matmul launch of
+ * one layer (kind 0 qkv, 1 o, 2 gate|up, 3 down, 4 lm_head) on the launching stream; shape of a resident matrix */
+void llama_pib_io_bytes(const struct llama_context * ctx, uint64_t * h2d, uint64_t * d2h);
+void llama_pib_profile_layer(struct llama_context * ctx, int layer);
+int  llama_pib_profile_read(struct llama_context * ctx, int32_t * kind, int32_t * b, float * ms, int cap);
+int  llama_pib_matrix_shape(const struct llama_model * model, int layer, int kind, int64_t * N, int64_t * K, uint64_t * bytes);
+/* debugging aids for parity work: a work buffer of the last chunk; the handle of a resident weight matrix */
+int  llama_pib_debug_read(struct llama_context * ctx, int which, float * out, int n_floats);
+const struct pib_weight * llama_pib_debug_weight(const struct llama_model * model, int layer, int which);
 
 #ifdef __cplusplus
 }

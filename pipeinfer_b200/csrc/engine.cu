@@ -421,6 +421,15 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
     const uint32_t * tbits = reinterpret_cast<const uint32_t *>(desc + PIB_DESC_BITS_OFF);
     int rc;
 #define RC(e) do { rc = (e); if (rc != PIB_OK) return rc; c->n_kernels++; } while (0)
+    // matmul launch, optionally bracketed by events (kind: 0 qkv, 1 o, 2 gate|up, 3 down, 4 lm_head)
+#define GEMV(kind, il_, w, out) do {                                                                                   \
+        const bool pr__ = (il_) == c->prof_layer && c->prof.size() < 8192;                                             \
+        pib_context::ProfRec r__ = { (kind), ntok, nullptr, nullptr };                                                 \
+        if (pr__) { cudaEventCreate(&r__.e0); cudaEventCreate(&r__.e1); cudaEventRecord(r__.e0, st); }                 \
+        RC(pib_gemv_internal((w), c->act, ntok, (out), var, cancel, st));                                              \
+        if (ntok > 8 && var != 2) c->n_kernels++;                                                                      \
+        if (pr__) { cudaEventRecord(r__.e1, st); c->prof.push_back(r__); }                                             \
+    } while (0)
     RC(kv_device_mask(&c->kvd, tpos, tbits, ntok, c->mask, st));
     if (c->stage.first()) RC(pib_get_rows(m->tok_embd, tok, ntok, c->x, st));
     else if (pib_hop_recv) RC(pib_hop_recv(c, c->x, ntok, cancel));
@@ -431,23 +440,23 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
         const size_t      lo = (size_t) (il - m->layer_begin) * c->n_ctx * GQA;
         if (pending_add) RC(pib_add_rmsnorm_quantize_act(wt, c->proj, c->x2, c->x, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
         else             RC(pib_add_rmsnorm_quantize_act(wt, c->x, nullptr, nullptr, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
-        RC(pib_gemv_internal(L.wqkv, c->act, ntok, c->qkv, var, cancel, st));
+        GEMV(0, il, L.wqkv, c->qkv);
         RC(pib_rope_kv_store(c->qkv, desc, c->rope, c->rope_n_pos, ntok, E, GQA, hd, 0, c->q16, c->kcache + lo, c->vcache + lo, cancel, st));
         RC(pib_attention(c->q16, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, desc, ntok, m->n_head, m->n_head_kv, hd,
                          (int) c->n_ctx, c->att, cancel, st));
         RC(pib_quantize_act_c(wt, c->att, ntok, E, c->act, cancel, st));
-        RC(pib_gemv_internal(L.wo, c->act, ntok, c->proj, var, cancel, st));
+        GEMV(1, il, L.wo, c->proj);
         RC(pib_add_rmsnorm_quantize_act(wt, c->proj, c->x, c->x2, L.ffn_norm, m->rms_eps, ntok, E, c->act, cancel, st));   // x2 = ffn_inp
-        RC(pib_gemv_internal(L.wgu, c->act, ntok, c->gu, var, cancel, st));
+        GEMV(2, il, L.wgu, c->gu);
         RC(pib_silu_mul_quantize_act(wt, c->gu, c->gu + FF, 2 * (int64_t) FF, ntok, FF, c->act, cancel, st));
-        RC(pib_gemv_internal(L.wdown, c->act, ntok, c->proj, var, cancel, st));
+        GEMV(3, il, L.wdown, c->proj);
         pending_add = true;
     }
     if (c->stage.last()) {
         if (pending_add) RC(pib_add_rmsnorm_quantize_act(wt, c->proj, c->x2, c->x, m->output_norm, m->rms_eps, ntok, E, c->act, cancel, st));
         else             RC(pib_add_rmsnorm_quantize_act(wt, c->x, nullptr, nullptr, m->output_norm, m->rms_eps, ntok, E, c->act, cancel, st));
         float * lg = run.logits + (size_t) chunk * PIB_CHUNK * m->n_vocab;
-        RC(pib_gemv_internal(m->output, c->act, ntok, lg, var, cancel, st));
+        GEMV(4, c->prof_layer >= 0 ? c->prof_layer : -2, m->output, lg);
         RC(pib_sample_topk(lg, ntok, m->n_vocab, c->bias_ids_dev, c->bias_val_dev, c->n_bias, run.res_dev + (size_t) chunk * PIB_CHUNK,
                            desc, cancel, st));
     } else {
@@ -458,6 +467,7 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
         }
         if (pib_hop_send) RC(pib_hop_send(c, c->x, ntok, cancel));
     }
+#undef GEMV
 #undef RC
     return PIB_OK;
 }
@@ -523,6 +533,7 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
         memcpy(d + PIB_DESC_BITS_OFF, tb.data() + (size_t) t0 * W, sizeof(uint32_t) * (size_t) nt * W);
         dq.push_back({ KVOP_ALLOC, (int32_t) (head + t0), nt, (int32_t) c->kv.n, s, 0 });
         cudaMemcpyAsync(c->desc_dev + (size_t) s * c->desc_stride, d, c->desc_stride, cudaMemcpyHostToDevice, c->stream);
+        c->h2d_bytes += c->desc_stride;
     }
     dq.push_back({ KVOP_ADVANCE, n_tokens, 0, 0, 0, 0 });
     kvlog_decode_end(c->kv, n_tokens);                                    // llama.cpp:5708-5713
@@ -533,6 +544,7 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
         if (c->ops_next + n > c->ops_cap) { cudaStreamSynchronize(c->stream); c->ops_next = 0; }
         memcpy(c->ops_host + c->ops_next, dq.data(), sizeof(KvOp) * n);
         cudaMemcpyAsync(c->ops_dev + c->ops_next, c->ops_host + c->ops_next, sizeof(KvOp) * n, cudaMemcpyHostToDevice, c->stream);
+        c->h2d_bytes += sizeof(KvOp) * n;
         if (kv_device_apply(&c->kvd, c->ops_dev + c->ops_next, n, c->desc_dev, c->desc_stride, c->stream) != PIB_OK) return -1;
         c->n_kernels++;
         c->ops_next += n;
@@ -544,8 +556,10 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
         if (run_chunk(c, *run, ch, nt, slots[ch]) != PIB_OK) { run->failed = true; break; }
         cudaEventRecord(c->desc_ev[slots[ch]], c->stream);
     }
-    if (c->stage.last() && !run->failed)
+    if (c->stage.last() && !run->failed) {
         cudaMemcpyAsync(run->res_host, run->res_dev, sizeof(pib_row_result) * (size_t) n_tokens, cudaMemcpyDeviceToHost, c->stream);
+        c->d2h_bytes += sizeof(pib_row_result) * (size_t) n_tokens;
+    }
     cudaEventRecord(run->done, c->stream);
     c->inflight.push_back(run->id);
     c->n_decode++;
@@ -583,6 +597,7 @@ const float * pib_logits_row(pib_context * c, int i) {
     if (!c->logits_row_valid[i]) {
         cudaMemcpyAsync(c->logits_host.data() + (size_t) i * V, r.logits + (size_t) i * V, V * 4, cudaMemcpyDeviceToHost, c->stream);
         cudaStreamSynchronize(c->stream);
+        c->d2h_bytes += V * 4;
         c->logits_row_valid[i] = 1;
     }
     return c->logits_host.data() + (size_t) i * V;

@@ -114,6 +114,11 @@ struct pib_context {
     std::vector<uint8_t> logits_row_valid;
     bool                 logits_all = true;
     uint64_t             n_kernels = 0;   // launches issued by this context (bench: gpu_launches)
+    uint64_t             h2d_bytes = 0, d2h_bytes = 0;     // host<->device traffic issued by this context
+    // optional per-launch timing of the matmuls of one layer (bench.py roofline): CUDA events on the launching stream
+    struct ProfRec { int kind, b; cudaEvent_t e0, e1; };
+    int                  prof_layer = -1;
+    std::vector<ProfRec> prof;
     uint64_t             n_decode  = 0;
     int64_t              t_start_us = 0;
 };

@@ -191,3 +191,8 @@ extern "C" int pib_get_rows(const pib_weight * w, const int32_t * ids_dev, int n
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }
+
+// ---- profiler range control (ncu --profile-from-start off) ------------------------------------------------------------
+#include <cuda_profiler_api.h>
+extern "C" void pib_profiler_start(void) { cudaProfilerStart(); }
+extern "C" void pib_profiler_stop(void) { cudaDeviceSynchronize(); cudaProfilerStop(); }

@@ -454,3 +454,33 @@ extern "C" const pib_weight * llama_pib_debug_weight(const struct llama_model * 
     const pib_layer & L = m->layers[layer];
     return which == 0 ? L.wqkv : which == 1 ? L.wo : which == 2 ? L.wgu : L.wdown;
 }
+
+// ---- measurement hooks (bench.py) -----------------------------------------------------------------------------------
+extern "C" void llama_pib_io_bytes(const struct llama_context * ctx, uint64_t * h2d, uint64_t * d2h) {
+    *h2d = ctx->c->h2d_bytes; *d2h = ctx->c->d2h_bytes;
+}
+// time every matmul launch of `layer` (and the lm_head) with CUDA events on the launching stream; -1 = off
+extern "C" void llama_pib_profile_layer(struct llama_context * ctx, int layer) { ctx->c->prof_layer = layer; }
+// fetch and clear the records: kind (0 qkv, 1 o, 2 gate|up, 3 down, 4 lm_head), batch, milliseconds; returns the count
+extern "C" int llama_pib_profile_read(struct llama_context * ctx, int32_t * kind, int32_t * b, float * ms, int cap) {
+    pib_context * c = ctx->c;
+    cudaStreamSynchronize(c->stream);
+    int n = 0;
+    for (auto & r : c->prof) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, r.e0, r.e1);
+        if (n < cap) { kind[n] = r.kind; b[n] = r.b; ms[n] = t; n++; }
+        cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
+    }
+    c->prof.clear();
+    return n;
+}
+// shape of a resident matrix: N, K, algorithmic bytes (kind as above; layer ignored for the lm_head)
+extern "C" int llama_pib_matrix_shape(const struct llama_model * model, int layer, int kind, int64_t * N, int64_t * K, uint64_t * bytes) {
+    const pib_model * m = model->m;
+    const pib_weight * w = kind == 4 ? m->output : (layer < 0 || layer >= m->n_layer) ? nullptr :
+                           kind == 0 ? m->layers[layer].wqkv : kind == 1 ? m->layers[layer].wo : kind == 2 ? m->layers[layer].wgu : m->layers[layer].wdown;
+    if (!w) return -1;
+    *N = w->N; *K = w->K; *bytes = w->bytes;
+    return 0;
+}

@@ -129,6 +129,98 @@ def build(args):
         os.unlink(args.out + ".f32.gguf")
 
 
+def direct_blocks(rng, qtype, rows, cols, std):
+    """random weights written directly as quantised blocks (no F32 detour): value = d * (q - mid) with d chosen so that
+    the dequantised std is `std`.  Used for the 70B-width CPU samples, where an F32 source would not fit."""
+    if qtype == "q8_0":
+        nb = cols // 32
+        blk = rng.integers(0, 256, (rows, nb, 34), dtype=np.uint8)
+        d = (rng.uniform(0.5, 1.5, (rows, nb)) * std / 74.0).astype(np.float16)
+        blk[:, :, 0:2] = d.view(np.uint8).reshape(rows, nb, 2)
+        return blk.reshape(rows, nb * 34), gguf.GGMLQuantizationType.Q8_0
+    if qtype == "q4_0":
+        nb = cols // 32
+        blk = rng.integers(0, 256, (rows, nb, 18), dtype=np.uint8)
+        d = (rng.uniform(0.5, 1.5, (rows, nb)) * std / 4.6).astype(np.float16)
+        blk[:, :, 0:2] = d.view(np.uint8).reshape(rows, nb, 2)
+        return blk.reshape(rows, nb * 18), gguf.GGMLQuantizationType.Q4_0
+    nb = cols // 256
+    blk = rng.integers(0, 256, (rows, nb, 144), dtype=np.uint8)
+    d = (rng.uniform(0.5, 1.5, (rows, nb)) * std / (32.0 * 4.6)).astype(np.float16)
+    dmin = (d.astype(np.float32) * 7.5).astype(np.float16)          # with m_j = sc_j: value = d * sc * (q - 7.5)
+    blk[:, :, 0:2] = d.view(np.uint8).reshape(rows, nb, 2)
+    blk[:, :, 2:4] = dmin.view(np.uint8).reshape(rows, nb, 2)
+    s = rng.integers(16, 48, (rows, nb, 8), dtype=np.uint8)
+    q = np.zeros((rows, nb, 12), dtype=np.uint8)
+    for j in range(4):
+        q[:, :, j] = s[:, :, j] | ((s[:, :, j + 4] >> 4) << 6)
+        q[:, :, j + 4] = s[:, :, j] | ((s[:, :, j + 4] >> 4) << 6)
+        q[:, :, j + 8] = (s[:, :, j + 4] & 0xF) | ((s[:, :, j + 4] & 0xF) << 4)
+    blk[:, :, 4:16] = q
+    return blk.reshape(rows, nb * 144), gguf.GGMLQuantizationType.Q4_K
+
+
+def build_direct(args):
+    """bigram-flavour model written directly in the quantised type (see direct_blocks)."""
+    rng = np.random.default_rng(args.seed)
+    E, L, H, HKV, FF, V = args.n_embd, args.n_layer, args.n_head, args.n_head_kv, args.n_ff, args.n_vocab
+    hd = E // H
+    w = gguf.GGUFWriter(args.out, "llama")
+    w.add_name(args.name)
+    w.add_context_length(args.n_ctx_train)
+    w.add_embedding_length(E)
+    w.add_block_count(L)
+    w.add_feed_forward_length(FF)
+    w.add_rope_dimension_count(hd)
+    w.add_head_count(H)
+    w.add_head_count_kv(HKV)
+    w.add_layer_norm_rms_eps(1e-5)
+    w.add_file_type(0)
+    toks, scores, types = synth_vocab(V)
+    w.add_tokenizer_model("llama")
+    w.add_token_list(toks)
+    w.add_token_scores(scores)
+    w.add_token_types(types)
+    w.add_bos_token_id(1)
+    w.add_eos_token_id(2)
+    w.add_unk_token_id(0)
+
+    def put(name, rows, cols, std, blocks=None):
+        b, qt = direct_blocks(rng, args.quant, rows, cols, std) if blocks is None else blocks
+        w.add_tensor(name, b, raw_dtype=qt)
+        return b, qt
+
+    erng = np.random.default_rng(4242)                 # the same g_t for target and draft of one vocabulary / width
+    emb, qt = direct_blocks(erng, args.quant, V, E, 1.0)
+    p = perm(V, 7)
+    if args.agree < 1.0:
+        flip = np.nonzero(np.random.default_rng(9).random(V) >= args.agree)[0]
+        if len(flip) > 1:
+            p = p.copy()
+            p[flip] = np.roll(p[flip], -1)
+    out = np.empty_like(emb)
+    out[p] = emb
+    w.add_tensor("token_embd.weight", emb, raw_dtype=qt)
+    sE, sF = 0.1 / np.sqrt(E), 0.1 / np.sqrt(FF)
+    for il in range(L):
+        pre = "blk.%d." % il
+        w.add_tensor(pre + "attn_norm.weight", np.ones(E, dtype=np.float32))
+        put(pre + "attn_q.weight", E, E, sE)
+        put(pre + "attn_k.weight", hd * HKV, E, sE)
+        put(pre + "attn_v.weight", hd * HKV, E, sE)
+        put(pre + "attn_output.weight", E, E, sE)
+        w.add_tensor(pre + "ffn_norm.weight", np.ones(E, dtype=np.float32))
+        put(pre + "ffn_gate.weight", FF, E, sE)
+        put(pre + "ffn_down.weight", E, FF, sF)
+        put(pre + "ffn_up.weight", FF, E, sE)
+    w.add_tensor("output_norm.weight", np.ones(E, dtype=np.float32))
+    w.add_tensor("output.weight", out, raw_dtype=qt)
+    w.write_header_to_file()
+    w.write_kv_data_to_file()
+    w.write_tensors_to_file()
+    w.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", required=True)
@@ -146,7 +238,12 @@ def main():
     ap.add_argument("--emb-scale", type=float, default=1.0)
     ap.add_argument("--agree", type=float, default=1.0)
     ap.add_argument("--seed", type=int, default=1234)
-    build(ap.parse_args())
+    ap.add_argument("--direct", action="store_true", help="write random quantised blocks directly (no F32 source, no quantize)")
+    a = ap.parse_args()
+    if a.direct:
+        build_direct(a)
+    else:
+        build(a)
 
 
 if __name__ == "__main__":
