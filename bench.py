@@ -41,7 +41,8 @@ CONFIGS = {
 }
 TYPE_NAME = {Q4_K: "q4_k", Q4_0: "q4_0", Q8_0: "q8_0"}
 BPW = {Q4_K: 4.5, Q4_0: 4.5, Q8_0: 8.5}
-KIND = {0: "qkv", 1: "attn_out", 2: "gate_up", 3: "down", 4: "lm_head"}
+KIND = {0: "qkv", 1: "attn_out", 2: "gate_up", 3: "down", 4: "lm_head", 5: "attn_norm_quant", 6: "rope_kv_store", 7: "attention",
+        8: "attn_out_quant", 9: "resid_ffn_norm_quant", 10: "silu_mul_quant"}
 
 
 def measured_peaks():
@@ -263,6 +264,11 @@ def main():
     for i in range(cnt):
         per_kind.setdefault(kind[i], []).append((bb[i], ms[i]))
     kernels = {}
+    others = {}
+    for k, lst in list(per_kind.items()):
+        if k >= 5:
+            others[KIND[k]] = {"launches": len(lst), "mean_ms": sum(x[1] for x in lst) / len(lst)}
+            del per_kind[k]
     for k, lst in per_kind.items():
         N_, K_, by = C.c_int64(), C.c_int64(), C.c_uint64()
         lib.llama_pib_matrix_shape(tgt.model, prof_layer, k, C.byref(N_), C.byref(K_), C.byref(by))
@@ -280,7 +286,8 @@ def main():
     if dom:
         roofline = {"bound": "hbm", "kernel": "dequant-GEMV %s, gate|up projection %dx%d, layer %d of the target" % (TYPE_NAME[wt], dom["N"], dom["K"], prof_layer),
                     "achieved": dom["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": dom["frac"], "traffic": traffic,
-                    "peak_source": peak_src, "frac_of_8TBs_nominal": dom["achieved_gbs"] / 8000.0, "all_matmuls": kernels}
+                    "peak_source": peak_src, "frac_of_8TBs_nominal": dom["achieved_gbs"] / 8000.0, "all_matmuls": kernels,
+                    "other_kernels_of_the_layer": others}
 
     cpu = None
     if not args.no_cpu_baseline:

@@ -51,6 +51,8 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
         // optional residual add fused in front (reference ggml_add, llama.cpp:3944 / :3962): sum_out = x + addend
         const float * ar = addend ? addend + (size_t) row * K : nullptr;
         float *       so = sum_out ? sum_out + (size_t) row * K : nullptr;
+        // (with several CTAs per row each one recomputes the whole row's sum -- K floats from L2 -- and all of them
+        //  write the same sums, so pass 2 never depends on another CTA)
         for (int64_t i = threadIdx.x; i < K; i += AQ_THREADS) {
             float v = xr[i];
             if (ar) { v = __fadd_rn(v, ar[i]); so[i] = v; }
@@ -73,7 +75,7 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
     if (!Q8K) {
         // one warp per 32-element block, lane == element
         const int64_t nb = K / PIB_QK;
-        for (int64_t blk = warp; blk < nb; blk += nwarp) {
+        for (int64_t blk = (int64_t) blockIdx.y * nwarp + warp; blk < nb; blk += (int64_t) gridDim.y * nwarp) {
             const int64_t i    = blk * PIB_QK + lane;
             const float   v    = aq_value<PRO>(xr, x2r, scale, lut, i);
             const float   amax = warp_max(fabsf(v));
@@ -94,7 +96,7 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
     } else {
         // one warp per 256-element super-block, lane owns 8 consecutive elements
         const int64_t nsb = K / PIB_QK_K;
-        for (int64_t sb = warp; sb < nsb; sb += nwarp) {
+        for (int64_t sb = (int64_t) blockIdx.y * nwarp + warp; sb < nsb; sb += (int64_t) gridDim.y * nwarp) {
             const int64_t i0 = sb * PIB_QK_K + lane * 8;
             float v[8];
 #pragma unroll
@@ -150,8 +152,11 @@ static int launch_aq(int wtype, const float * x, const float * x2, int x2_per_ro
     int8_t * qs = (int8_t *) act + L.qs_off;
     float *  d  = (float *) ((uint8_t *) act + L.d_off);
     void *   bs = (uint8_t *) act + L.bs_off;
-    if (wtype == PIB_TYPE_Q4_K) act_quant_kernel<true, PRO><<<b, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut, addend, sum_out, cancel, xstride);
-    else                        act_quant_kernel<false, PRO><<<b, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut, addend, sum_out, cancel, xstride);
+    const int64_t units = wtype == PIB_TYPE_Q4_K ? K / PIB_QK_K : K / PIB_QK / 4;        // super-blocks, or groups of 4 blocks
+    const int     parts = (int) max((int64_t) 1, min((int64_t) 32, units / (AQ_THREADS / 32)));
+    const dim3    grid(b, parts);
+    if (wtype == PIB_TYPE_Q4_K) act_quant_kernel<true, PRO><<<grid, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut, addend, sum_out, cancel, xstride);
+    else                        act_quant_kernel<false, PRO><<<grid, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut, addend, sum_out, cancel, xstride);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }

@@ -54,7 +54,8 @@ __global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8
     const int       half = hd / 2;
     const float2 *  cs   = rope + (size_t) min(pos, rope_n_pos - 1) * half;
     const int       nq = E / 2, nk = GQA / 2;
-    for (int i = threadIdx.x; i < nq + nk; i += blockDim.x) {
+    const int       tid0 = blockIdx.y * blockDim.x + threadIdx.x, nthr = gridDim.y * blockDim.x;
+    for (int i = tid0; i < nq + nk; i += nthr) {
         const bool    isq  = i < nq;
         const int     pi   = isq ? i : i - nq;          // pair index inside Q or K
         const int     h    = pi / half, j = pi % half;
@@ -71,7 +72,7 @@ __global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8
         dst[i1] = __float2half_rn(y1);
     }
     const float * v = row + E + GQA;
-    for (int i = threadIdx.x; i < GQA; i += blockDim.x) vcache[(size_t) cell * GQA + i] = __float2half_rn(v[i]);
+    for (int i = tid0; i < GQA; i += nthr) vcache[(size_t) cell * GQA + i] = __float2half_rn(v[i]);
 }
 
 // ---- attention ------------------------------------------------------------------------------------------------------
@@ -87,11 +88,14 @@ __global__ void __launch_bounds__(ATT_THREADS) attention_kernel(const __half * _
                                                                 const uint8_t * __restrict__ mask, const int32_t * __restrict__ scalars,
                                                                 const uint8_t * __restrict__ desc, const uint16_t * __restrict__ exp_lut,
                                                                 int E, int GQA, int n_ctx, float kq_scale, float * __restrict__ out,
-                                                                const int * __restrict__ cancel) {
+                                                                const int * __restrict__ cancel, int gdiv) {
     if (cancel && *cancel) return;
     (void) desc;
     extern __shared__ float smem[];
-    const int kvh = blockIdx.x, t = blockIdx.y;
+    // gdiv == 1: blockIdx.x is a KV head serving its G query heads (K/V read once per token; best at long contexts).
+    // gdiv  > 1: blockIdx.x is a query head (template G == 1) reading KV head blockIdx.x / gdiv: G times more CTAs,
+    //            K/V re-read through L2 -- the better trade at the short contexts of verification batches.
+    const int qh0 = blockIdx.x * G, kvh = blockIdx.x / gdiv, t = blockIdx.y;
     const int n   = scalars[2];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int DPL = HD / 32;                 // dims per lane: 4 (hd 128) or 2 (hd 64)
@@ -103,7 +107,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attention_kernel(const __half * _
 #pragma unroll
     for (int g = 0; g < G; g++)
 #pragma unroll
-        for (int j = 0; j < DPL; j++) q[g][j] = __half2float(q16[(size_t) t * E + (size_t) (kvh * G + g) * HD + lane * DPL + j]);
+        for (int j = 0; j < DPL; j++) q[g][j] = __half2float(q16[(size_t) t * E + (size_t) (qh0 + g) * HD + lane * DPL + j]);
 
     // phase 1: scores
     for (int i = warp; i < n; i += ATT_WARPS) {
@@ -192,13 +196,13 @@ __global__ void __launch_bounds__(ATT_THREADS) attention_kernel(const __half * _
 #pragma unroll
         for (int r = 0; r < NGR; r++) a += redbuf[(size_t) r * G * HD + j];
         const int g = j / HD, d = j % HD;
-        out[(size_t) t * E + (size_t) (kvh * G + g) * HD + d] = a;
+        out[(size_t) t * E + (size_t) (qh0 + g) * HD + d] = a;
     }
 }
 
 template <int HD, int G>
 static int launch_att(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
-                      const uint8_t * desc, int E, int GQA, int n_ctx, int n_tokens, int n_head_kv, float * out,
+                      const uint8_t * desc, int E, int GQA, int n_ctx, int n_tokens, int n_blocks_x, int gdiv, float * out,
                       const int * cancel, cudaStream_t st) {
     const size_t smem = ((size_t) G * n_ctx + (size_t) (ATT_THREADS / (HD / 2)) * G * HD) * sizeof(float);
     static size_t configured = 0;
@@ -206,15 +210,16 @@ static int launch_att(const __half * q16, const __half * kc, const __half * vc, 
         PIB_CHECK(cudaFuncSetAttribute(attention_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         configured = smem;
     }
-    attention_kernel<HD, G><<<dim3(n_head_kv, n_tokens), ATT_THREADS, smem, st>>>(
-        q16, kc, vc, mask, scalars, desc, pib_get_luts().exp_f16, E, GQA, n_ctx, 1.0f / sqrtf((float) HD), out, cancel);
+    attention_kernel<HD, G><<<dim3(n_blocks_x, n_tokens), ATT_THREADS, smem, st>>>(
+        q16, kc, vc, mask, scalars, desc, pib_get_luts().exp_f16, E, GQA, n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }
 
 int pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * rope, int rope_n_pos, int n_tokens, int E, int GQA,
                       int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st) {
-    rope_kv_store_kernel<<<n_tokens, 256, 0, st>>>(qkv, desc, rope, rope_n_pos, E, GQA, hd, mode, q16, kc, vc, cancel);
+    const int parts = max(1, min(16, (E / 2 + GQA / 2 + 511) / 512));
+    rope_kv_store_kernel<<<dim3(n_tokens, parts), 256, 0, st>>>(qkv, desc, rope, rope_n_pos, E, GQA, hd, mode, q16, kc, vc, cancel);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }
@@ -232,8 +237,14 @@ int pib_attention(const __half * q16, const __half * kc, const __half * vc, cons
                   const uint8_t * desc, int n_tokens, int n_head, int n_head_kv, int hd, int n_ctx, float * out,
                   const int * cancel, cudaStream_t st) {
     const int E = n_head * hd, GQA = n_head_kv * hd, G = n_head / n_head_kv;
+    // per-query-head CTAs unless the context is long enough for the G-fold K/V re-reads to matter
+    const bool per_q = G > 1 && n_ctx <= 2048;
+    if (per_q) {
+        if (hd == 128) return launch_att<128, 1>(q16, kc, vc, mask, scalars, desc, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
+        if (hd == 64)  return launch_att<64, 1>(q16, kc, vc, mask, scalars, desc, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
+    }
 #define ATT_CASE(HDv, Gv) \
-    if (hd == HDv && G == Gv) return launch_att<HDv, Gv>(q16, kc, vc, mask, scalars, desc, E, GQA, n_ctx, n_tokens, n_head_kv, out, cancel, st);
+    if (hd == HDv && G == Gv) return launch_att<HDv, Gv>(q16, kc, vc, mask, scalars, desc, E, GQA, n_ctx, n_tokens, n_head_kv, 1, out, cancel, st);
     ATT_CASE(128, 1) ATT_CASE(128, 2) ATT_CASE(128, 4) ATT_CASE(128, 8)
     ATT_CASE(64, 1) ATT_CASE(64, 2) ATT_CASE(64, 4) ATT_CASE(64, 8)
 #undef ATT_CASE

@@ -37,6 +37,7 @@ int  pib_attention(const __half * q16, const __half * kc, const __half * vc, con
 int  pib_sample_topk(float * logits_dev, int n_rows, int n_vocab, const int32_t * bias_ids_dev, const float * bias_val_dev, int n_bias,
                      void * out_dev, const uint8_t * desc, const int * cancel, cudaStream_t st);
 pib_weight * pib_weight_alloc(int type, int64_t N, int64_t K);
+int pib_weight_build_tiles(pib_weight * w);
 
 static int64_t now_us() {
     struct timeval tv;
@@ -202,7 +203,7 @@ static pib_weight * synth_weight(int type, int64_t N, int64_t K, uint32_t seed, 
     const int64_t qs_row = type == PIB_TYPE_Q8_0 ? K : K / 2;
     const int64_t n      = N * qs_row / 16;
     synth_fill_kernel<<<(unsigned) ((n + 255) / 256), 256>>>(type, w->qs, w->d, N, K, seed, rowmap_dev, dscale);
-    if (cudaGetLastError() != cudaSuccess) { pib_weight_free(w); return nullptr; }
+    if (cudaGetLastError() != cudaSuccess || pib_weight_build_tiles(w) != PIB_OK) { pib_weight_free(w); return nullptr; }
     return w;
 }
 
@@ -430,6 +431,15 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
         if (ntok > 8 && var != 2) c->n_kernels++;                                                                      \
         if (pr__) { cudaEventRecord(r__.e1, st); c->prof.push_back(r__); }                                             \
     } while (0)
+    // any other launch of the profiled layer, bracketed the same way (kind: 5 attn-norm+quant, 6 rope+kv store, 7 attention,
+    // 8 quant of the attention output, 9 residual+ffn-norm+quant, 10 silu*up+quant)
+#define TL(kind, il_, call) do {                                                                                       \
+        const bool pr__ = (il_) == c->prof_layer && c->prof.size() < 8192;                                             \
+        pib_context::ProfRec r__ = { (kind), ntok, nullptr, nullptr };                                                 \
+        if (pr__) { cudaEventCreate(&r__.e0); cudaEventCreate(&r__.e1); cudaEventRecord(r__.e0, st); }                 \
+        RC(call);                                                                                                      \
+        if (pr__) { cudaEventRecord(r__.e1, st); c->prof.push_back(r__); }                                             \
+    } while (0)
     RC(kv_device_mask(&c->kvd, tpos, tbits, ntok, c->mask, st));
     if (c->stage.first()) RC(pib_get_rows(m->tok_embd, tok, ntok, c->x, st));
     else if (pib_hop_recv) RC(pib_hop_recv(c, c->x, ntok, cancel));
@@ -438,17 +448,17 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
     for (int il = m->layer_begin; il < m->layer_end; il++) {
         const pib_layer & L  = m->layers[il];
         const size_t      lo = (size_t) (il - m->layer_begin) * c->n_ctx * GQA;
-        if (pending_add) RC(pib_add_rmsnorm_quantize_act(wt, c->proj, c->x2, c->x, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
-        else             RC(pib_add_rmsnorm_quantize_act(wt, c->x, nullptr, nullptr, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
+        if (pending_add) TL(5, il, pib_add_rmsnorm_quantize_act(wt, c->proj, c->x2, c->x, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
+        else             TL(5, il, pib_add_rmsnorm_quantize_act(wt, c->x, nullptr, nullptr, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
         GEMV(0, il, L.wqkv, c->qkv);
-        RC(pib_rope_kv_store(c->qkv, desc, c->rope, c->rope_n_pos, ntok, E, GQA, hd, 0, c->q16, c->kcache + lo, c->vcache + lo, cancel, st));
-        RC(pib_attention(c->q16, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, desc, ntok, m->n_head, m->n_head_kv, hd,
-                         (int) c->n_ctx, c->att, cancel, st));
-        RC(pib_quantize_act_c(wt, c->att, ntok, E, c->act, cancel, st));
+        TL(6, il, pib_rope_kv_store(c->qkv, desc, c->rope, c->rope_n_pos, ntok, E, GQA, hd, 0, c->q16, c->kcache + lo, c->vcache + lo, cancel, st));
+        TL(7, il, pib_attention(c->q16, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, desc, ntok, m->n_head, m->n_head_kv, hd,
+                                (int) c->n_ctx, c->att, cancel, st));
+        TL(8, il, pib_quantize_act_c(wt, c->att, ntok, E, c->act, cancel, st));
         GEMV(1, il, L.wo, c->proj);
-        RC(pib_add_rmsnorm_quantize_act(wt, c->proj, c->x, c->x2, L.ffn_norm, m->rms_eps, ntok, E, c->act, cancel, st));   // x2 = ffn_inp
+        TL(9, il, pib_add_rmsnorm_quantize_act(wt, c->proj, c->x, c->x2, L.ffn_norm, m->rms_eps, ntok, E, c->act, cancel, st));   // x2 = ffn_inp
         GEMV(2, il, L.wgu, c->gu);
-        RC(pib_silu_mul_quantize_act(wt, c->gu, c->gu + FF, 2 * (int64_t) FF, ntok, FF, c->act, cancel, st));
+        TL(10, il, pib_silu_mul_quantize_act(wt, c->gu, c->gu + FF, 2 * (int64_t) FF, ntok, FF, c->act, cancel, st));
         GEMV(3, il, L.wdown, c->proj);
         pending_add = true;
     }
@@ -467,6 +477,7 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
         }
         if (pib_hop_send) RC(pib_hop_send(c, c->x, ntok, cancel));
     }
+#undef TL
 #undef GEMV
 #undef RC
     return PIB_OK;

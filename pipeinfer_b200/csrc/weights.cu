@@ -104,6 +104,8 @@ static int repack_from_device(pib_weight * w, const uint8_t * src, int64_t row0,
     return PIB_OK;
 }
 
+int pib_weight_build_tiles(pib_weight * w);   // gemv_mma.cu
+
 pib_weight * pib_weight_alloc(int type, int64_t N, int64_t K) { return alloc_weight(type, N, K); }
 
 extern "C" pib_weight * pib_weight_upload(int type, const void * host_blocks, int64_t N, int64_t K) {
@@ -135,6 +137,7 @@ extern "C" pib_weight * pib_weight_upload(int type, const void * host_blocks, in
         }
     }
     cudaFree(stage);
+    if (pib_weight_build_tiles(w) != PIB_OK || cudaDeviceSynchronize() != cudaSuccess) { pib_weight_free(w); return nullptr; }
     return w;
 }
 
@@ -146,6 +149,7 @@ extern "C" pib_weight * pib_weight_from_device(int type, const void * dev_blocks
         pib_weight_free(w);
         return nullptr;
     }
+    if (pib_weight_build_tiles(w) != PIB_OK || cudaDeviceSynchronize() != cudaSuccess) { pib_weight_free(w); return nullptr; }
     return w;
 }
 

@@ -89,9 +89,15 @@ def test_get_rows_bit_exact(lib, kern, name, wt):
     lib.L.pib_weight_free(h)
 
 
-@pytest.mark.parametrize("variant", [1])
+def variants(wt):
+    return [1, 2] if wt == op.TYPE_Q4_K else [1]      # variant 2 (tensor-core tiles) exists for Q4_K
+
+
+@pytest.mark.parametrize("variant", [1, 2])
 @pytest.mark.parametrize("name,wt", TYPES)
 def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
+    if variant not in variants(wt):
+        pytest.skip("variant 2 is Q4_K only")
     w, x, y = kern[name + "_w"], kern[name + "_x"], kern[name + "_y"]
     h = lib.weight_upload(wt, w, x.shape[1])
     got = lib.mul_mat(h, x, w.shape[0], variant)
@@ -99,10 +105,12 @@ def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
     lib.L.pib_weight_free(h)
 
 
-@pytest.mark.parametrize("variant", [1])
+@pytest.mark.parametrize("variant", [1, 2])
 @pytest.mark.parametrize("name,wt", TYPES)
 @pytest.mark.parametrize("b", [1, 2, 5, 8, 9, 16])
 def test_mul_mat_vs_oracle_batches(lib, oracle, name, wt, b, variant):
+    if variant not in variants(wt):
+        pytest.skip("variant 2 is Q4_K only")
     rng = np.random.default_rng(100 + b)
     N, K = 96, 2048
     w = rand_blocks(rng, wt, N, K)
@@ -122,9 +130,27 @@ def test_mul_mat_ragged_rows_and_long_k(lib, oracle, name, wt):
     w = rand_blocks(rng, wt, N, K)
     x = (rng.standard_normal((3, K))).astype(np.float32)
     h = lib.weight_upload(wt, w, K)
-    got = lib.mul_mat(h, x, N, 1)
     ref = oracle.mul_mat(wt, w, x)
-    assert np.abs(got - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max())
+    for variant in variants(wt):
+        got = lib.mul_mat(h, x, N, variant)
+        assert np.abs(got - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max()), variant
+    lib.L.pib_weight_free(h)
+
+
+@pytest.mark.parametrize("N,K,b", [(2560, 2048, 3), (48, 8192, 16), (200, 1024, 1)])
+def test_mul_mat_tensor_core_k_split_path(lib, oracle, N, K, b):
+    # few row tiles -> the kernel splits K over several CTAs and reduces partial sums through scratch memory in a fixed order;
+    # run twice: the per-tile arrival counters must be left clean
+    rng = np.random.default_rng(N)
+    wt = op.TYPE_Q4_K
+    w = rand_blocks(rng, wt, N, K)
+    x = rng.standard_normal((b, K)).astype(np.float32)
+    h = lib.weight_upload(wt, w, K)
+    ref = oracle.mul_mat(wt, w, x)
+    a1 = lib.mul_mat(h, x, N, 2)
+    a2 = lib.mul_mat(h, x, N, 2)
+    assert np.array_equal(a1, a2)                      # deterministic
+    assert np.abs(a1 - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max())
     lib.L.pib_weight_free(h)
 
 
