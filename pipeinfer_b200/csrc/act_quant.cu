@@ -32,7 +32,9 @@ template <bool Q8K, int PRO>
 __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, const float * __restrict__ x2,
                                                                int x2_per_row, float eps, int64_t K,
                                                                int8_t * __restrict__ qs, float * __restrict__ dplane,
-                                                               void * __restrict__ bsplane, float * __restrict__ vout,
+                                                               void * __restrict__ bsplane, int8_t * __restrict__ bs8plane,
+                                                               int8_t * __restrict__ qsp,
+                                                               float * __restrict__ vout,
                                                                const uint16_t * __restrict__ lut,
                                                                const float * __restrict__ addend, float * sum_out,
                                                                const int * __restrict__ cancel, int64_t xstride) {
@@ -131,6 +133,8 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
             packed.x = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((q[3] & 0xff) << 24);
             packed.y = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((q[7] & 0xff) << 24);
             *reinterpret_cast<int2 *>(qs + (size_t) row * K + i0) = packed;
+            // fragment-order copy for the tensor-core GEMV: lane = 8c + 4h + t  ->  offset 64t + 16c + 8h
+            *reinterpret_cast<int2 *>(qsp + (size_t) row * K + sb * PIB_QK_K + (lane & 3) * 64 + (lane >> 3) * 16 + ((lane >> 2) & 1) * 8) = packed;
             if (vout) {
 #pragma unroll
                 for (int j = 0; j < 8; j++) vout[(size_t) row * K + i0 + j] = v[j];
@@ -138,6 +142,12 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
             int s8 = q[0] + q[1] + q[2] + q[3] + q[4] + q[5] + q[6] + q[7];
             int s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
             if ((lane & 1) == 0) ((int16_t *) bsplane)[(size_t) row * (K / 16) + sb * 16 + (lane >> 1)] = (int16_t) s16;
+            const int s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);        // the 32-element sub-block sum (lanes 4j..4j+3)
+            if ((lane & 3) == 0) {
+                int8_t * o = bs8plane + ((size_t) row * nsb + sb) * 16 + (lane >> 2);
+                o[0] = (int8_t) (s32 >> 6);
+                o[8] = (int8_t) (s32 & 63);
+            }
             if (lane == 0) dplane[(size_t) row * nsb + sb] = dval;
         }
     }
@@ -152,11 +162,13 @@ static int launch_aq(int wtype, const float * x, const float * x2, int x2_per_ro
     int8_t * qs = (int8_t *) act + L.qs_off;
     float *  d  = (float *) ((uint8_t *) act + L.d_off);
     void *   bs = (uint8_t *) act + L.bs_off;
+    int8_t * b8 = (int8_t *) act + L.bs8_off;
+    int8_t * qp = (int8_t *) act + L.qsp_off;
     const int64_t units = wtype == PIB_TYPE_Q4_K ? K / PIB_QK_K : K / PIB_QK / 4;        // super-blocks, or groups of 4 blocks
     const int     parts = (int) max((int64_t) 1, min((int64_t) 32, units / (AQ_THREADS / 32)));
     const dim3    grid(b, parts);
-    if (wtype == PIB_TYPE_Q4_K) act_quant_kernel<true, PRO><<<grid, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut, addend, sum_out, cancel, xstride);
-    else                        act_quant_kernel<false, PRO><<<grid, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, vout, lut, addend, sum_out, cancel, xstride);
+    if (wtype == PIB_TYPE_Q4_K) act_quant_kernel<true, PRO><<<grid, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride);
+    else                        act_quant_kernel<false, PRO><<<grid, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }

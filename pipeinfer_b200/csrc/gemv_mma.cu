@@ -1,6 +1,7 @@
 // gemv_mma.cu -- variant 2 of the quantised matmul (K1) for Q4_K weights: fragment-major weight tiles streamed with
 // coalesced 128-bit loads, int8 tensor-core dot products (mma.sync m16n8k32 s8), per-sub-block integer scaling,
-// fp32 super-block accumulation, cross-warp + (optional) cross-CTA reduction in a fixed order.
+// fp32 super-block accumulation, cross-warp + (optional) cross-CTA reduction in a fixed order.  Persistent CTAs; every warp
+// keeps a private ring of tiles in shared memory filled by TMA bulk copies (cp.async.bulk + mbarrier).
 //
 // Arithmetic is the reference's (ggml-quants.c:5216 ggml_vec_dot_q4_K_q8_K): per super-block
 //     sum_j sc_j * <q_j, x_j>   (exact int32)      times   d_w * d_x
@@ -72,6 +73,13 @@ __device__ __forceinline__ void mma_s8(int (&c)[4], int a0, int a1, int a2, int 
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
+// A unsigned: the high nibbles are used in place (q << 4, 0..240); the factor 16 is shifted out of the scaled sum
+__device__ __forceinline__ void mma_u8s8(int (&c)[4], int a0, int a1, int a2, int a3, int b0, int b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
 struct q4k_hdr {          // one row's decoded super-block header
     float    d, dmin;
     uint32_t sc_lo, sc_hi;   // sc0..3 | sc4..7 as bytes
@@ -90,65 +98,151 @@ __device__ __forceinline__ q4k_hdr decode_hdr(const uint4 h) {
     return r;
 }
 
-// NT = number of 8-token n-tiles (1: b <= 8, 2: b <= 16).  grid = (row tiles, k splits); each warp of a CTA takes every
-// MM_WARPS-th super-block of the CTA's k range.  partial != nullptr: write fp32 partial sums [split][b][N] instead of y.
+// ---- TMA bulk copy + mbarrier helpers (sm_90+ PTX; SASS: UBLKCP / SYNCS) ----------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_LOOP:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra WAIT_DONE;\n\tbra WAIT_LOOP;\n\tWAIT_DONE:\n\t}"
+                 ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void * src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+#define MM_STAGES 3            // ring stages per warp
+#define MM_CHUNK  2            // consecutive super-blocks per stage = per TMA bulk copy (2 x 2304 B)
+#define MM_STAGE_BYTES (MM_CHUNK * MM_TILE_BYTES)
+
 template <int NT>
-__global__ void __launch_bounds__(MM_THREADS, 4)
-gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, const int8_t * __restrict__ aqs,
-                    const float * __restrict__ ad, const int16_t * __restrict__ absum, int b, float * __restrict__ y,
-                    float * __restrict__ partial, unsigned int * __restrict__ counters, const int * __restrict__ cancel) {
+struct act_frag {           // everything a lane needs from the activations for one super-block
+    int4  q[NT][4];                 // chunk c: B fragments {lo.x, lo.y, hi.x, hi.y} of sub-blocks 2c / 2c+1, token column g
+    int   mh[NT], ml[NT];           // B fragments of the min term: hi / lo bytes of the eight 32-wide block sums
+    float dx[NT][2];                // activation scale of the tokens of C columns 2t, 2t+1
+};
+
+// Persistent kernel, warp-granular work.  Work item = (row tile T, k split p) = sb_per consecutive super-blocks of 16 rows;
+// item i belongs to warp (i mod total warps): no cross-warp reduction, no CTA barrier in the main loop.  Every warp owns a
+// private ring of MM_STAGES tiles in shared memory that one lane fills with 1-D TMA bulk copies (cp.async.bulk -> mbarrier
+// complete_tx); the ring runs MM_STAGES super-blocks ahead across item boundaries and the activation fragments one ahead,
+// so weight bytes keep streaming while results are written.  NT = number of 8-token n-tiles (1: b <= 8, 2: b <= 16).
+// nsplit (a power of two, dividing nsb) > 1: fp32 partial sums [split][b][N] go through `partial`; the last warp to arrive
+// for a row tile (per-tile counter) adds them in split order -- deterministic -- and resets the counter.
+template <int NT>
+__global__ void __launch_bounds__(MM_THREADS, NT == 1 ? 4 : 3)
+gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int n_tiles, int lg_split, int N, int K,
+                    const int8_t * __restrict__ aqs, const float * __restrict__ ad, const int8_t * __restrict__ abs8, int b,
+                    float * __restrict__ y, float * __restrict__ partial, unsigned int * __restrict__ counters,
+                    const int * __restrict__ cancel) {
     if (cancel && *cancel) return;
+    extern __shared__ __align__(128) uint8_t dsm[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
-    const int T = blockIdx.x;
-    const int nsplit = gridDim.y, split = blockIdx.y;
-    const int sb_per = (nsb + nsplit - 1) / nsplit;
-    const int sb0 = split * sb_per, sb1 = min(nsb, sb0 + sb_per);
-    const uint8_t * tbase = tiles + (size_t) T * nsb * MM_TILE_BYTES;
+    uint8_t *      ring = dsm + (size_t) warp * MM_STAGES * MM_STAGE_BYTES;
+    const uint32_t ring_a = smem_u32(ring);
+    const uint32_t bar_a  = smem_u32(dsm + (size_t) MM_WARPS * MM_STAGES * MM_STAGE_BYTES) + (uint32_t) warp * MM_STAGES * 8;
+    const int nsplit = 1 << lg_split, pmask = nsplit - 1;
+    const int n_items = n_tiles << lg_split;
+    const int sb_per  = nsb >> lg_split;
+    const int gw = (int) blockIdx.x * MM_WARPS + warp, wtot = (int) gridDim.x * MM_WARPS;
+
+    if (lane == 0) {
+        for (int i = 0; i < MM_STAGES; i++) mbar_init(bar_a + i * 8, 1);
+        fence_async_smem();
+    }
+    __syncwarp();
+
+    // three cursors over this warp's sequence of super-blocks: weights (TMA), activations (registers), compute
+    struct cur_t { int item, sl, s; };           // s: super-block index inside the row, sl: inside the item
+    auto cur_init = [&](cur_t & c) { c.item = gw; c.sl = 0; c.s = (gw & pmask) * sb_per; };
+    auto cur_next = [&](cur_t & c) {
+        c.sl++; c.s++;
+        if (c.sl == sb_per) { c.sl = 0; c.item += wtot; c.s = (c.item & pmask) * sb_per; }
+    };
+    cur_t wc, ac, cc;
+    cur_init(wc); cur_init(ac); cur_init(cc);
+    uint32_t issued = 0, consumed = 0;
+    // the weight cursor moves in chunks of up to MM_CHUNK consecutive super-blocks of one item: one bulk copy each
+    auto issue = [&]() {
+        const int      csz   = min(MM_CHUNK, sb_per - wc.sl);
+        const uint32_t bytes = (uint32_t) csz * MM_TILE_BYTES;
+        if (lane == 0) {
+            const uint32_t st = issued % MM_STAGES;
+            mbar_expect_tx(bar_a + st * 8, bytes);
+            bulk_g2s(ring_a + st * MM_STAGE_BYTES, tiles + ((size_t) (wc.item >> lg_split) * nsb + wc.s) * MM_TILE_BYTES, bytes,
+                     bar_a + st * 8);
+        }
+        issued++;
+        for (int i = 0; i < csz; i++) cur_next(wc);
+    };
+    for (int i = 0; i < MM_STAGES && wc.item < n_items; i++) issue();
+
+    // per-lane activation base pointers (token column g of each n-tile; C columns 2t, 2t+1).  Token indices are clamped
+    // to b - 1: padded columns compute on a duplicate of the last token and are never stored.
+    const int8_t * a_qs[NT];
+    const int8_t * a_b8[NT];
+    const float *  a_dx[NT][2];
+#pragma unroll
+    for (int n = 0; n < NT; n++) {
+        const int tok = min(n * 8 + g, b - 1);
+        a_qs[n] = aqs + (size_t) tok * K + t * 64;
+        a_b8[n] = abs8 + (size_t) tok * nsb * 16 + (t & 1) * 4;
+#pragma unroll
+        for (int e = 0; e < 2; e++) a_dx[n][e] = ad + (size_t) min(n * 8 + 2 * t + e, b - 1) * nsb;
+    }
+    auto load_act = [&](act_frag<NT> & f, int s) {
+#pragma unroll
+        for (int n = 0; n < NT; n++) {
+            const int4 * ap = reinterpret_cast<const int4 *>(a_qs[n] + (size_t) s * 256);
+#pragma unroll
+            for (int c = 0; c < 4; c++) f.q[n][c] = __ldg(ap + c);
+            const int * bp = reinterpret_cast<const int *>(a_b8[n] + (size_t) s * 16);
+            f.mh[n] = __ldg(bp);
+            f.ml[n] = __ldg(bp + 2);
+#pragma unroll
+            for (int e = 0; e < 2; e++) f.dx[n][e] = __ldg(a_dx[n][e] + s);
+        }
+    };
+    act_frag<NT> A0;
+    if (ac.item < n_items) { load_act(A0, ac.s); cur_next(ac); }
 
     float acc[NT][4];
 #pragma unroll
     for (int n = 0; n < NT; n++) { acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f; }
 
-    // tokens this lane supplies B fragments for (column g of each n-tile) and owns C columns of (2t, 2t+1)
-    int  tokB[NT];
-    bool okB[NT];
-#pragma unroll
-    for (int n = 0; n < NT; n++) { tokB[n] = n * 8 + g; okB[n] = tokB[n] < b; }
+    while (cc.item < n_items) {
+        act_frag<NT> A1;
+        const bool more = ac.item < n_items;
+        if (more) { load_act(A1, ac.s); cur_next(ac); }         // activations of the next super-block: in flight during this one
 
-    uint4 wq[4], hq[2];
-    int   s = sb0 + warp;
-    if (s < sb1) {
-        const uint8_t * p = tbase + (size_t) s * MM_TILE_BYTES;
+        const uint32_t st  = consumed % MM_STAGES;
+        const int      cin = cc.sl % MM_CHUNK;                   // position inside the chunk
+        if (cin == 0) mbar_wait(bar_a + st * 8, (consumed / MM_STAGES) & 1);
+        const uint8_t * p = ring + (size_t) st * MM_STAGE_BYTES + (size_t) cin * MM_TILE_BYTES;
+        uint4 wq[4];
 #pragma unroll
-        for (int c = 0; c < 4; c++) wq[c] = *reinterpret_cast<const uint4 *>(p + c * 512 + lane * 16);   // streamed below via ld_stream
-        hq[0] = *reinterpret_cast<const uint4 *>(p + 2048 + g * 16);
-        hq[1] = *reinterpret_cast<const uint4 *>(p + 2048 + (g + 8) * 16);
-    }
-    for (; s < sb1; s += MM_WARPS) {
-        // prefetch the next super-block of this warp while this one is consumed
-        uint4 wn[4], hn[2];
-        const int sn = s + MM_WARPS;
-        if (sn < sb1) {
-            const uint8_t * p = tbase + (size_t) sn * MM_TILE_BYTES;
-#pragma unroll
-            for (int c = 0; c < 4; c++) {
-                const int4 v = ld_stream_v4(p + c * 512 + lane * 16);
-                wn[c] = make_uint4((uint32_t) v.x, (uint32_t) v.y, (uint32_t) v.z, (uint32_t) v.w);
-            }
-            const int4 h0 = ld_stream_v4(p + 2048 + g * 16), h1 = ld_stream_v4(p + 2048 + (g + 8) * 16);
-            hn[0] = make_uint4((uint32_t) h0.x, (uint32_t) h0.y, (uint32_t) h0.z, (uint32_t) h0.w);
-            hn[1] = make_uint4((uint32_t) h1.x, (uint32_t) h1.y, (uint32_t) h1.z, (uint32_t) h1.w);
+        for (int c = 0; c < 4; c++) wq[c] = *reinterpret_cast<const uint4 *>(p + c * 512 + lane * 16);
+        const q4k_hdr H0 = decode_hdr(*reinterpret_cast<const uint4 *>(p + 2048 + g * 16));
+        const q4k_hdr H1 = decode_hdr(*reinterpret_cast<const uint4 *>(p + 2048 + (g + 8) * 16));
+        if (cin == MM_CHUNK - 1 || cc.sl == sb_per - 1) {   // last super-block of the chunk: the stage is drained
+            __syncwarp();                                   // every lane has read its part
+            if (wc.item < n_items) { if (lane == 0) fence_async_smem(); issue(); }
+            consumed++;
         }
-        const q4k_hdr H0 = decode_hdr(hq[0]), H1 = decode_hdr(hq[1]);     // rows g and g + 8
-        int sumi[NT][4];
+
+        int sumi[NT][4], sumh[NT][4];        // low-nibble sub-blocks; high-nibble sub-blocks (x 16)
 #pragma unroll
-        for (int n = 0; n < NT; n++) { sumi[n][0] = sumi[n][1] = sumi[n][2] = sumi[n][3] = 0; }
+        for (int n = 0; n < NT; n++)
+#pragma unroll
+            for (int i = 0; i < 4; i++) { sumi[n][i] = 0; sumh[n][i] = 0; }
 #pragma unroll
         for (int c = 0; c < 4; c++) {
             const uint4 w = wq[c];            // {row g: x, y ; row g+8: z, w}
-            const int a_lo[4] = { (int) (w.x & 0x0F0F0F0Fu), (int) (w.z & 0x0F0F0F0Fu), (int) (w.y & 0x0F0F0F0Fu), (int) (w.w & 0x0F0F0F0Fu) };
-            const int a_hi[4] = { (int) ((w.x >> 4) & 0x0F0F0F0Fu), (int) ((w.z >> 4) & 0x0F0F0F0Fu), (int) ((w.y >> 4) & 0x0F0F0F0Fu),
-                                  (int) ((w.w >> 4) & 0x0F0F0F0Fu) };
             const int j0 = 2 * c, j1 = 2 * c + 1;
             const int sc0_lo = (int) (((j0 < 4 ? H0.sc_lo : H0.sc_hi) >> (8 * (j0 & 3))) & 0xff);
             const int sc1_lo = (int) (((j0 < 4 ? H1.sc_lo : H1.sc_hi) >> (8 * (j0 & 3))) & 0xff);
@@ -156,48 +250,191 @@ gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, c
             const int sc1_hi = (int) (((j1 < 4 ? H1.sc_lo : H1.sc_hi) >> (8 * (j1 & 3))) & 0xff);
 #pragma unroll
             for (int n = 0; n < NT; n++) {
-                int2 b_lo = make_int2(0, 0), b_hi = make_int2(0, 0);
-                if (okB[n]) {
-                    const int8_t * ap = aqs + (size_t) tokB[n] * K + (size_t) s * 256 + c * 64 + t * 8;
-                    b_lo = __ldg(reinterpret_cast<const int2 *>(ap));            // sub-block 2c   : elements 8t .. 8t+7
-                    b_hi = __ldg(reinterpret_cast<const int2 *>(ap + 32));       // sub-block 2c+1
-                }
                 int c_lo[4] = { 0, 0, 0, 0 }, c_hi[4] = { 0, 0, 0, 0 };
-                mma_s8(c_lo, a_lo[0], a_lo[1], a_lo[2], a_lo[3], b_lo.x, b_lo.y);
-                mma_s8(c_hi, a_hi[0], a_hi[1], a_hi[2], a_hi[3], b_hi.x, b_hi.y);
-                sumi[n][0] += sc0_lo * c_lo[0] + sc0_hi * c_hi[0];
-                sumi[n][1] += sc0_lo * c_lo[1] + sc0_hi * c_hi[1];
-                sumi[n][2] += sc1_lo * c_lo[2] + sc1_hi * c_hi[2];
-                sumi[n][3] += sc1_lo * c_lo[3] + sc1_hi * c_hi[3];
+                mma_u8s8(c_lo, (int) (w.x & 0x0F0F0F0Fu), (int) (w.z & 0x0F0F0F0Fu), (int) (w.y & 0x0F0F0F0Fu), (int) (w.w & 0x0F0F0F0Fu),
+                         A0.q[n][c].x, A0.q[n][c].y);
+                mma_u8s8(c_hi, (int) (w.x & 0xF0F0F0F0u), (int) (w.z & 0xF0F0F0F0u), (int) (w.y & 0xF0F0F0F0u), (int) (w.w & 0xF0F0F0F0u),
+                         A0.q[n][c].z, A0.q[n][c].w);
+                sumi[n][0] += sc0_lo * c_lo[0]; sumh[n][0] += sc0_hi * c_hi[0];
+                sumi[n][1] += sc0_lo * c_lo[1]; sumh[n][1] += sc0_hi * c_hi[1];
+                sumi[n][2] += sc1_lo * c_lo[2]; sumh[n][2] += sc1_hi * c_hi[2];
+                sumi[n][3] += sc1_lo * c_lo[3]; sumh[n][3] += sc1_hi * c_hi[3];
             }
         }
-        // mins: sum_j m_j * (bsums[2j] + bsums[2j+1]) with dp2a on the int16 pairs exactly as block_q8_K stores them
-        const int m0_01 = (int) __byte_perm(H0.m_lo, 0, 0x1100), m0_23 = (int) __byte_perm(H0.m_lo, 0, 0x3322);
-        const int m0_45 = (int) __byte_perm(H0.m_hi, 0, 0x1100), m0_67 = (int) __byte_perm(H0.m_hi, 0, 0x3322);
-        const int m1_01 = (int) __byte_perm(H1.m_lo, 0, 0x1100), m1_23 = (int) __byte_perm(H1.m_lo, 0, 0x3322);
-        const int m1_45 = (int) __byte_perm(H1.m_hi, 0, 0x1100), m1_67 = (int) __byte_perm(H1.m_hi, 0, 0x3322);
+        // min term sum_j m_j * bsum_j on the tensor core as well: bsum_j = 64 * hi_j + lo_j (bytes prepared by the
+        // activation quantiser); k-slots 0..7 carry j, the rest are zero
+        const int am0 = t == 0 ? (int) H0.m_lo : t == 1 ? (int) H0.m_hi : 0;
+        const int am1 = t == 0 ? (int) H1.m_lo : t == 1 ? (int) H1.m_hi : 0;
 #pragma unroll
         for (int n = 0; n < NT; n++) {
+            int c_mh[4] = { 0, 0, 0, 0 }, c_ml[4] = { 0, 0, 0, 0 };
+            const int bmh = t < 2 ? A0.mh[n] : 0, bml = t < 2 ? A0.ml[n] : 0;
+            mma_s8(c_mh, am0, am1, 0, 0, bmh, 0);
+            mma_s8(c_ml, am0, am1, 0, 0, bml, 0);
 #pragma unroll
             for (int e = 0; e < 2; e++) {
-                const int tok = n * 8 + 2 * t + e;
-                if (tok < b) {
-                    const int4 * bp = reinterpret_cast<const int4 *>(absum + (size_t) tok * (K / 16) + (size_t) s * 16);
-                    const int4  q0 = __ldg(bp), q1 = __ldg(bp + 1);            // int16 pairs for sub-blocks 0..3 | 4..7
-                    int mi0 = __dp2a_lo(q0.x, m0_01, 0); mi0 = __dp2a_hi(q0.y, m0_01, mi0);
-                    mi0 = __dp2a_lo(q0.z, m0_23, mi0);   mi0 = __dp2a_hi(q0.w, m0_23, mi0);
-                    mi0 = __dp2a_lo(q1.x, m0_45, mi0);   mi0 = __dp2a_hi(q1.y, m0_45, mi0);
-                    mi0 = __dp2a_lo(q1.z, m0_67, mi0);   mi0 = __dp2a_hi(q1.w, m0_67, mi0);
-                    int mi1 = __dp2a_lo(q0.x, m1_01, 0); mi1 = __dp2a_hi(q0.y, m1_01, mi1);
-                    mi1 = __dp2a_lo(q0.z, m1_23, mi1);   mi1 = __dp2a_hi(q0.w, m1_23, mi1);
-                    mi1 = __dp2a_lo(q1.x, m1_45, mi1);   mi1 = __dp2a_hi(q1.y, m1_45, mi1);
-                    mi1 = __dp2a_lo(q1.z, m1_67, mi1);   mi1 = __dp2a_hi(q1.w, m1_67, mi1);
-                    const float dx = __ldg(ad + (size_t) tok * nsb + s);
-                    acc[n][e]     = fmaf(__fmul_rn(dx, H0.d), (float) sumi[n][e], acc[n][e]);
-                    acc[n][e]     = fmaf(__fmul_rn(-dx, H0.dmin), (float) mi0, acc[n][e]);
-                    acc[n][2 + e] = fmaf(__fmul_rn(dx, H1.d), (float) sumi[n][2 + e], acc[n][2 + e]);
-                    acc[n][2 + e] = fmaf(__fmul_rn(-dx, H1.dmin), (float) mi1, acc[n][2 + e]);
+                const float dx = A0.dx[n][e];
+                acc[n][e]     = fmaf(__fmul_rn(dx, H0.d), (float) (sumi[n][e] + (sumh[n][e] >> 4)), acc[n][e]);
+                acc[n][e]     = fmaf(__fmul_rn(-dx, H0.dmin), (float) (64 * c_mh[e] + c_ml[e]), acc[n][e]);
+                acc[n][2 + e] = fmaf(__fmul_rn(dx, H1.d), (float) (sumi[n][2 + e] + (sumh[n][2 + e] >> 4)), acc[n][2 + e]);
+                acc[n][2 + e] = fmaf(__fmul_rn(-dx, H1.dmin), (float) (64 * c_mh[2 + e] + c_ml[2 + e]), acc[n][2 + e]);
+            }
+        }
+        if (more) A0 = A1;
+
+        if (cc.sl == sb_per - 1) {                          // the item is complete: 16 rows x b tokens of (partial) sums
+            const int T = cc.item >> lg_split, split = cc.item & pmask;
+            const int r0 = T * 16 + g, r1 = r0 + 8;
+#pragma unroll
+            for (int n = 0; n < NT; n++)
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+                    const int tok = n * 8 + 2 * t + e;
+                    if (tok < b) {
+                        float * o = nsplit == 1 ? y + (size_t) tok * N : partial + ((size_t) split * b + tok) * N;
+                        if (r0 < N) o[r0] = acc[n][e];
+                        if (r1 < N) o[r1] = acc[n][2 + e];
+                    }
+                    acc[n][e] = 0.f; acc[n][2 + e] = 0.f;
                 }
+            if (nsplit > 1) {
+                __threadfence();
+                __syncwarp();
+                unsigned int old = 0;
+                if (lane == 0) old = atomicAdd(&counters[T], 1u);
+                old = __shfl_sync(0xffffffffu, old, 0);
+                if (old == (unsigned) nsplit - 1) {         // last to arrive: add the splits in order
+                    __threadfence();
+#pragma unroll
+                    for (int n = 0; n < NT; n++)
+#pragma unroll
+                        for (int e = 0; e < 2; e++) {
+                            const int tok = n * 8 + 2 * t + e;
+                            if (tok < b) {
+                                float v0 = 0.f, v1 = 0.f;
+                                for (int sp = 0; sp < nsplit; sp++) {
+                                    const float * q = partial + ((size_t) sp * b + tok) * N;
+                                    if (r0 < N) v0 += __ldcg(q + r0);
+                                    if (r1 < N) v1 += __ldcg(q + r1);
+                                }
+                                if (r0 < N) y[(size_t) tok * N + r0] = v0;
+                                if (r1 < N) y[(size_t) tok * N + r1] = v1;
+                            }
+                        }
+                    __syncwarp();
+                    if (lane == 0) counters[T] = 0;         // self-cleaning: ready for the next launch
+                }
+            }
+        }
+        cur_next(cc);
+    }
+}
+
+// ---- direct variant: one CTA per (row tile, k split), the four warps interleave the super-blocks, weights prefetched one
+// super-block ahead into registers with streaming 128-bit loads (no shared-memory staging); same arithmetic core -------------
+template <int NT>
+__global__ void __launch_bounds__(MM_THREADS, NT == 1 ? 4 : 3)
+gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, const int8_t * __restrict__ aqs,
+                       const float * __restrict__ ad, const int8_t * __restrict__ abs8, int b, float * __restrict__ y,
+                       float * __restrict__ partial, unsigned int * __restrict__ counters, const int * __restrict__ cancel) {
+    if (cancel && *cancel) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    const int T = blockIdx.x;
+    const int nsplit = gridDim.y, split = blockIdx.y;
+    const int sb_per = (nsb + nsplit - 1) / nsplit;
+    const int sb0 = split * sb_per, sb1 = min(nsb, sb0 + sb_per);
+    const uint8_t * tbase = tiles + (size_t) T * nsb * MM_TILE_BYTES + lane * 16;
+    const uint8_t * hbase = tiles + (size_t) T * nsb * MM_TILE_BYTES + 2048 + g * 16;
+
+    float acc[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; n++) { acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f; }
+    const int8_t * a_qs[NT];
+    const int8_t * a_b8[NT];
+    const float *  a_dx[NT][2];
+#pragma unroll
+    for (int n = 0; n < NT; n++) {
+        const int tok = min(n * 8 + g, b - 1);
+        a_qs[n] = aqs + (size_t) tok * K + t * 64;
+        a_b8[n] = abs8 + (size_t) tok * nsb * 16 + (t & 1) * 4;
+#pragma unroll
+        for (int e = 0; e < 2; e++) a_dx[n][e] = ad + (size_t) min(n * 8 + 2 * t + e, b - 1) * nsb;
+    }
+
+    int4 wq[4], hq[2];
+    int  s = sb0 + warp;
+    if (s < sb1) {
+#pragma unroll
+        for (int c = 0; c < 4; c++) wq[c] = ld_stream_v4(tbase + (size_t) s * MM_TILE_BYTES + c * 512);
+        hq[0] = ld_stream_v4(hbase + (size_t) s * MM_TILE_BYTES);
+        hq[1] = ld_stream_v4(hbase + (size_t) s * MM_TILE_BYTES + 128);
+    }
+    for (; s < sb1; s += MM_WARPS) {
+        int4 wn[4], hn[2];
+        const int sn = s + MM_WARPS;
+        if (sn < sb1) {
+#pragma unroll
+            for (int c = 0; c < 4; c++) wn[c] = ld_stream_v4(tbase + (size_t) sn * MM_TILE_BYTES + c * 512);
+            hn[0] = ld_stream_v4(hbase + (size_t) sn * MM_TILE_BYTES);
+            hn[1] = ld_stream_v4(hbase + (size_t) sn * MM_TILE_BYTES + 128);
+        }
+        const q4k_hdr H0 = decode_hdr(make_uint4((uint32_t) hq[0].x, (uint32_t) hq[0].y, (uint32_t) hq[0].z, (uint32_t) hq[0].w));
+        const q4k_hdr H1 = decode_hdr(make_uint4((uint32_t) hq[1].x, (uint32_t) hq[1].y, (uint32_t) hq[1].z, (uint32_t) hq[1].w));
+        int4  aq[NT][4];
+        int   amh[NT], aml[NT];
+        float adx[NT][2];
+#pragma unroll
+        for (int n = 0; n < NT; n++) {
+            const int4 * ap = reinterpret_cast<const int4 *>(a_qs[n] + (size_t) s * 256);
+#pragma unroll
+            for (int c = 0; c < 4; c++) aq[n][c] = __ldg(ap + c);
+            const int * bp = reinterpret_cast<const int *>(a_b8[n] + (size_t) s * 16);
+            amh[n] = __ldg(bp);
+            aml[n] = __ldg(bp + 2);
+#pragma unroll
+            for (int e = 0; e < 2; e++) adx[n][e] = __ldg(a_dx[n][e] + s);
+        }
+        int sumi[NT][4], sumh[NT][4];
+#pragma unroll
+        for (int n = 0; n < NT; n++)
+#pragma unroll
+            for (int i = 0; i < 4; i++) { sumi[n][i] = 0; sumh[n][i] = 0; }
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const uint32_t wx = (uint32_t) wq[c].x, wy = (uint32_t) wq[c].y, wz = (uint32_t) wq[c].z, ww = (uint32_t) wq[c].w;
+            const int j0 = 2 * c, j1 = 2 * c + 1;
+            const int sc0_lo = (int) __byte_perm(j0 < 4 ? H0.sc_lo : H0.sc_hi, 0, 0x4440 + (j0 & 3));
+            const int sc1_lo = (int) __byte_perm(j0 < 4 ? H1.sc_lo : H1.sc_hi, 0, 0x4440 + (j0 & 3));
+            const int sc0_hi = (int) __byte_perm(j1 < 4 ? H0.sc_lo : H0.sc_hi, 0, 0x4440 + (j1 & 3));
+            const int sc1_hi = (int) __byte_perm(j1 < 4 ? H1.sc_lo : H1.sc_hi, 0, 0x4440 + (j1 & 3));
+#pragma unroll
+            for (int n = 0; n < NT; n++) {
+                int c_lo[4] = { 0, 0, 0, 0 }, c_hi[4] = { 0, 0, 0, 0 };
+                mma_u8s8(c_lo, (int) (wx & 0x0F0F0F0Fu), (int) (wz & 0x0F0F0F0Fu), (int) (wy & 0x0F0F0F0Fu), (int) (ww & 0x0F0F0F0Fu),
+                         aq[n][c].x, aq[n][c].y);
+                mma_u8s8(c_hi, (int) (wx & 0xF0F0F0F0u), (int) (wz & 0xF0F0F0F0u), (int) (wy & 0xF0F0F0F0u), (int) (ww & 0xF0F0F0F0u),
+                         aq[n][c].z, aq[n][c].w);
+                sumi[n][0] += sc0_lo * c_lo[0]; sumh[n][0] += sc0_hi * c_hi[0];
+                sumi[n][1] += sc0_lo * c_lo[1]; sumh[n][1] += sc0_hi * c_hi[1];
+                sumi[n][2] += sc1_lo * c_lo[2]; sumh[n][2] += sc1_hi * c_hi[2];
+                sumi[n][3] += sc1_lo * c_lo[3]; sumh[n][3] += sc1_hi * c_hi[3];
+            }
+        }
+        const int am0 = t == 0 ? (int) H0.m_lo : t == 1 ? (int) H0.m_hi : 0;
+        const int am1 = t == 0 ? (int) H1.m_lo : t == 1 ? (int) H1.m_hi : 0;
+#pragma unroll
+        for (int n = 0; n < NT; n++) {
+            int c_mh[4] = { 0, 0, 0, 0 }, c_ml[4] = { 0, 0, 0, 0 };
+            const int bmh = t < 2 ? amh[n] : 0, bml = t < 2 ? aml[n] : 0;
+            mma_s8(c_mh, am0, am1, 0, 0, bmh, 0);
+            mma_s8(c_ml, am0, am1, 0, 0, bml, 0);
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+                const float dx = adx[n][e];
+                acc[n][e]     = fmaf(__fmul_rn(dx, H0.d), (float) (sumi[n][e] + (sumh[n][e] >> 4)), acc[n][e]);
+                acc[n][e]     = fmaf(__fmul_rn(-dx, H0.dmin), (float) (64 * c_mh[e] + c_ml[e]), acc[n][e]);
+                acc[n][2 + e] = fmaf(__fmul_rn(dx, H1.d), (float) (sumi[n][2 + e] + (sumh[n][2 + e] >> 4)), acc[n][2 + e]);
+                acc[n][2 + e] = fmaf(__fmul_rn(-dx, H1.dmin), (float) (64 * c_mh[2 + e] + c_ml[2 + e]), acc[n][2 + e]);
             }
         }
         if (sn < sb1) {
@@ -207,8 +444,9 @@ gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, c
         }
     }
 
-    // cross-warp reduction in warp order, then (k-split) cross-CTA reduction in split order by the last CTA to arrive
+    // cross-warp reduction in warp order, then (k split) cross-CTA reduction in split order by the last CTA to arrive
     __shared__ float red[MM_WARPS][NT * 8][16];
+    __shared__ bool  s_last;
 #pragma unroll
     for (int n = 0; n < NT; n++)
 #pragma unroll
@@ -217,7 +455,6 @@ gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, c
             red[warp][n * 8 + 2 * t + e][g + 8] = acc[n][2 + e];
         }
     __syncthreads();
-    __shared__ bool s_last;
     for (int i = threadIdx.x; i < NT * 8 * 16; i += MM_THREADS) {
         const int tok = i / 16, r = i % 16, row = T * 16 + r;
         if (tok < b && row < N) {
@@ -229,12 +466,10 @@ gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, c
         }
     }
     if (nsplit == 1) return;
-    __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) s_last = atomicAdd(&counters[T], 1u) == (unsigned) nsplit - 1;
+    if (threadIdx.x == 0) { __threadfence(); s_last = atomicAdd(&counters[T], 1u) == (unsigned) nsplit - 1; }
     __syncthreads();
     if (!s_last) return;
-    __threadfence();
     for (int i = threadIdx.x; i < NT * 8 * 16; i += MM_THREADS) {
         const int tok = i / 16, r = i % 16, row = T * 16 + r;
         if (tok < b && row < N) {
@@ -277,12 +512,38 @@ bool pib_gemv_mma_supported(const pib_weight * w, int b) {
     return w && w->type == PIB_TYPE_Q4_K && w->tiles != nullptr && b >= 1 && b <= PIB_MAX_BATCH;
 }
 
-// number of k splits: enough CTAs to fill the machine when there are few row tiles (small N: draft model, Wk/Wv)
-static int choose_split(int n_tiles, int nsb) {
+// log2 of the number of k splits: items (row tiles x splits) should outnumber the resident warps a few times over for load
+// balance; a split must divide the super-block count and keep at least two super-blocks per item
+static int choose_lg_split(int n_tiles, int nsb) {
+    const int target = 3 * 4 * MM_WARPS * pib_num_sms();
+    int lg = 0;
+    while ((n_tiles << lg) < target && nsb % (2 << lg) == 0 && (nsb >> (lg + 1)) >= 2 && lg < 6) lg++;
+    return lg;
+}
+
+static size_t mm_smem_bytes() { return (size_t) MM_WARPS * MM_STAGES * MM_STAGE_BYTES + (size_t) MM_WARPS * MM_STAGES * 8; }
+
+// k splits of the direct variant: enough CTAs to fill the machine when there are few row tiles
+static int choose_split_direct(int n_tiles, int nsb) {
     const int target = 4 * pib_num_sms();
     int split = 1;
     while (n_tiles * split < target && split * 2 * MM_WARPS <= nsb && split < 16) split *= 2;
     return split;
+}
+
+int pib_gemv_direct_launch(const pib_weight * w, const void * act_dev, int b, float * y_dev, int split, float * partial,
+                           unsigned int * counters, const int * cancel, cudaStream_t st) {
+    const pib_act_layout L   = pib_act_layout_of(w->type, w->K, b);
+    const uint8_t *      act = (const uint8_t *) act_dev;
+    const int            nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    const dim3           grid(n_tiles, split);
+    const int8_t *       aqs = (const int8_t *) (act + L.qsp_off);
+    const float *        ad  = (const float *) (act + L.d_off);
+    const int8_t *       bs  = (const int8_t *) (act + L.bs8_off);
+    if (b <= 8) gemv_q4k_direct_kernel<1><<<grid, MM_THREADS, 0, st>>>(w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev, partial, counters, cancel);
+    else        gemv_q4k_direct_kernel<2><<<grid, MM_THREADS, 0, st>>>(w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev, partial, counters, cancel);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
 }
 
 int pib_gemv_mma_launch(const pib_weight * w, const void * act_dev, int b, float * y_dev, int split, float * partial,
@@ -290,23 +551,44 @@ int pib_gemv_mma_launch(const pib_weight * w, const void * act_dev, int b, float
     const pib_act_layout L   = pib_act_layout_of(w->type, w->K, b);
     const uint8_t *      act = (const uint8_t *) act_dev;
     const int            nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
-    const dim3           grid(n_tiles, split);
-    const int8_t *       aqs = (const int8_t *) (act + L.qs_off);
+    const int8_t *       aqs = (const int8_t *) (act + L.qsp_off);      // fragment-order quants
     const float *        ad  = (const float *) (act + L.d_off);
-    const int16_t *      bs  = (const int16_t *) (act + L.bs_off);
-    if (b <= 8) gemv_q4k_mma_kernel<1><<<grid, MM_THREADS, 0, st>>>(w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev, partial, counters, cancel);
-    else        gemv_q4k_mma_kernel<2><<<grid, MM_THREADS, 0, st>>>(w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev, partial, counters, cancel);
+    const int8_t *       bs  = (const int8_t *) (act + L.bs8_off);
+    static bool configured = false;
+    if (!configured) {
+        PIB_CHECK(cudaFuncSetAttribute(gemv_q4k_mma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) mm_smem_bytes()));
+        PIB_CHECK(cudaFuncSetAttribute(gemv_q4k_mma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) mm_smem_bytes()));
+        configured = true;
+    }
+    const int items = n_tiles << split;                                            // `split` is log2 of the split count here
+    const int ctas  = (items + MM_WARPS - 1) / MM_WARPS;
+    const int grid  = ctas < 4 * pib_num_sms() ? ctas : 4 * pib_num_sms();         // persistent: 4 CTAs per SM
+    if (b <= 8) gemv_q4k_mma_kernel<1><<<grid, MM_THREADS, mm_smem_bytes(), st>>>(w->tiles, nsb, n_tiles, split, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev, partial, counters, cancel);
+    else        gemv_q4k_mma_kernel<2><<<grid, MM_THREADS, mm_smem_bytes(), st>>>(w->tiles, nsb, n_tiles, split, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev, partial, counters, cancel);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }
 
-int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
+// variant 2: direct (register-prefetched) kernel
+int pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
     if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: variant 2 needs Q4_K weights with tiles"); return PIB_ERR_UNSUPP; }
     const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
-    const int split = choose_split(n_tiles, nsb);
+    const int split = choose_split_direct(n_tiles, nsb);
     mm_scratch * s = nullptr;
     if (split > 1) {
         if (ensure_scratch((size_t) split * b * w->N, (size_t) n_tiles, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
+    }
+    return pib_gemv_direct_launch(w, act_dev, b, y_dev, split, s ? s->partial : nullptr, s ? s->counters : nullptr, cancel, st);
+}
+
+// variant 3: persistent TMA-staged kernel
+int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
+    if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: variant 3 needs Q4_K weights with tiles"); return PIB_ERR_UNSUPP; }
+    const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    const int split = choose_lg_split(n_tiles, nsb);
+    mm_scratch * s = nullptr;
+    if (split > 0) {
+        if (ensure_scratch(((size_t) b << split) * w->N, (size_t) n_tiles, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
     }
     return pib_gemv_mma_launch(w, act_dev, b, y_dev, split, s ? s->partial : nullptr, s ? s->counters : nullptr, cancel, st);
 }

@@ -104,12 +104,14 @@ extern "C" int pib_stream_sync(pib_stream s) {
 // ---- K1 dispatch ----------------------------------------------------------------------------------------------------
 int pib_gemv_dp4a(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
+int pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 bool pib_gemv_mma_supported(const pib_weight * w, int b);
 
 int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, const int * cancel,
                       cudaStream_t st) {
-    if (variant == 2 || (variant == 0 && b > 1 && pib_gemv_mma_supported(w, b)))
-        return pib_gemv_mma(w, act_dev, b, y_dev, cancel, st);
+    const bool tc = pib_gemv_mma_supported(w, b);
+    if (variant == 3 && tc) return pib_gemv_mma(w, act_dev, b, y_dev, cancel, st);
+    if ((variant == 2 || variant == 0) && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);
     return pib_gemv_dp4a(w, act_dev, b, y_dev, cancel, st);
 }
 
@@ -118,11 +120,11 @@ extern "C" int pib_gemv(const pib_weight * w, const void * act_dev, int b, float
         pib_set_error("pib_gemv: bad arguments (b = %d, limit %d)", b, PIB_MAX_BATCH);
         return PIB_ERR_ARG;
     }
-    if (variant == 2 || (variant == 0 && b > 1 && pib_gemv_mma_supported(w, b))) {
-        if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: variant 2 does not support this shape"); return PIB_ERR_UNSUPP; }
-        return pib_gemv_mma(w, act_dev, b, y_dev, nullptr, (cudaStream_t) s);
+    if ((variant == 2 || variant == 3) && !pib_gemv_mma_supported(w, b)) {
+        pib_set_error("pib_gemv: variants 2 / 3 need Q4_K weights");
+        return PIB_ERR_UNSUPP;
     }
-    return pib_gemv_dp4a(w, act_dev, b, y_dev, nullptr, (cudaStream_t) s);
+    return pib_gemv_internal(w, act_dev, b, y_dev, variant, nullptr, (cudaStream_t) s);
 }
 
 extern "C" int pib_mul_mat_host(const pib_weight * w, const float * x_host, int b, float * y_host, int variant) {

@@ -98,6 +98,12 @@ struct pib_act_layout {
     size_t d_off;      // float [b][K/32] (Q8_0 family) or [b][K/256] (Q8_K family)
     size_t bs_off;     // Q8_0 family: int32 [b][K/32] block sums (unused by the reference, used for the -8 offset);
                        // Q8_K family: int16 [b][K/16] bsums exactly as block_q8_K
+    size_t bs8_off;    // Q8_K family: int8 [b][K/256][16] = {hi_0..hi_7, lo_0..lo_7}: sub-block sums bsums[2j] + bsums[2j+1]
+                       //   split as 64 * hi + lo (hi in [-64, 63], lo in [0, 63]) so that the min term of Q4_K can be a
+                       //   tensor-core dot product; redundant with bs_off (same numbers)
+    size_t qsp_off;    // Q8_K family: int8 [b][K], the same quants as qs_off in tensor-core fragment order: inside each
+                       //   super-block, element e = 64c + 32h + 8t + i (chunk c, low/high-nibble half h, lane quarter t) is
+                       //   stored at 64t + 16c + 8h + i, so a lane's B fragments for all four chunks are 64 contiguous bytes
     size_t total;
 };
 __host__ __device__ inline pib_act_layout pib_act_layout_of(int wtype, int64_t K, int b) {
@@ -108,6 +114,9 @@ __host__ __device__ inline pib_act_layout pib_act_layout_of(int wtype, int64_t K
     size_t nd = (wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / PIB_QK_K) : (size_t) b * (K / PIB_QK);
     L.bs_off = (L.d_off + nd * 4 + 255) & ~(size_t) 255;
     size_t nbs = (wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / 16) * 2 : (size_t) b * (K / PIB_QK) * 4;
-    L.total  = (L.bs_off + nbs + 255) & ~(size_t) 255;
+    L.bs8_off = (L.bs_off + nbs + 255) & ~(size_t) 255;
+    size_t nbs8 = (wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / PIB_QK_K) * 16 : 0;
+    L.qsp_off = (L.bs8_off + nbs8 + 255) & ~(size_t) 255;
+    L.total  = (L.qsp_off + ((wtype == PIB_TYPE_Q4_K) ? qs : 0) + 255) & ~(size_t) 255;
     return L;
 }

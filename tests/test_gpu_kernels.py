@@ -90,14 +90,14 @@ def test_get_rows_bit_exact(lib, kern, name, wt):
 
 
 def variants(wt):
-    return [1, 2] if wt == op.TYPE_Q4_K else [1]      # variant 2 (tensor-core tiles) exists for Q4_K
+    return [1, 2, 3] if wt == op.TYPE_Q4_K else [1]      # variants 2 (direct) and 3 (TMA-staged) exist for Q4_K
 
 
-@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("variant", [1, 2, 3])
 @pytest.mark.parametrize("name,wt", TYPES)
 def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
     if variant not in variants(wt):
-        pytest.skip("variant 2 is Q4_K only")
+        pytest.skip("variants 2 and 3 are Q4_K only")
     w, x, y = kern[name + "_w"], kern[name + "_x"], kern[name + "_y"]
     h = lib.weight_upload(wt, w, x.shape[1])
     got = lib.mul_mat(h, x, w.shape[0], variant)
@@ -105,12 +105,12 @@ def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
     lib.L.pib_weight_free(h)
 
 
-@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("variant", [1, 2, 3])
 @pytest.mark.parametrize("name,wt", TYPES)
 @pytest.mark.parametrize("b", [1, 2, 5, 8, 9, 16])
 def test_mul_mat_vs_oracle_batches(lib, oracle, name, wt, b, variant):
     if variant not in variants(wt):
-        pytest.skip("variant 2 is Q4_K only")
+        pytest.skip("variants 2 and 3 are Q4_K only")
     rng = np.random.default_rng(100 + b)
     N, K = 96, 2048
     w = rand_blocks(rng, wt, N, K)
@@ -147,10 +147,11 @@ def test_mul_mat_tensor_core_k_split_path(lib, oracle, N, K, b):
     x = rng.standard_normal((b, K)).astype(np.float32)
     h = lib.weight_upload(wt, w, K)
     ref = oracle.mul_mat(wt, w, x)
-    a1 = lib.mul_mat(h, x, N, 2)
-    a2 = lib.mul_mat(h, x, N, 2)
-    assert np.array_equal(a1, a2)                      # deterministic
-    assert np.abs(a1 - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max())
+    for variant in (2, 3):
+        a1 = lib.mul_mat(h, x, N, variant)
+        a2 = lib.mul_mat(h, x, N, variant)
+        assert np.array_equal(a1, a2)                      # deterministic
+        assert np.abs(a1 - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max())
     lib.L.pib_weight_free(h)
 
 
