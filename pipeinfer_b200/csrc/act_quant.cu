@@ -19,13 +19,33 @@ enum { PRO_PLAIN = 0, PRO_RMSNORM = 1, PRO_SILU_MUL = 2, PRO_GELU = 3 };
 #define AQ_THREADS 256
 
 template <int PRO>
-__device__ __forceinline__ float aq_value(const float * __restrict__ xr, const float * __restrict__ x2r, float scale,
+__device__ __forceinline__ float aq_value(const float * xr, const float * __restrict__ x2r, float scale,
                                           const uint16_t * __restrict__ lut, int64_t i) {
     const float x = xr[i];
     if (PRO == PRO_RMSNORM) return __fmul_rn(__fmul_rn(x, scale), x2r[i]);
     if (PRO == PRO_SILU_MUL) return __fmul_rn(pib_h2f(lut[pib_f2h(x)]), x2r[i]);
     if (PRO == PRO_GELU) return pib_h2f(lut[pib_f2h(x)]);
     return x;
+}
+
+// eight consecutive values (32-byte aligned) with two 128-bit loads per operand
+template <int PRO>
+__device__ __forceinline__ void aq_value8(const float * xr, const float * __restrict__ x2r, float scale,
+                                          const uint16_t * __restrict__ lut, int64_t i0, float * v) {
+    const float4 xa = *reinterpret_cast<const float4 *>(xr + i0), xb = *reinterpret_cast<const float4 *>(xr + i0 + 4);
+    const float  x[8] = { xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w };
+    float        w[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    if (PRO == PRO_RMSNORM || PRO == PRO_SILU_MUL) {
+        const float4 wa = *reinterpret_cast<const float4 *>(x2r + i0), wb = *reinterpret_cast<const float4 *>(x2r + i0 + 4);
+        w[0] = wa.x; w[1] = wa.y; w[2] = wa.z; w[3] = wa.w; w[4] = wb.x; w[5] = wb.y; w[6] = wb.z; w[7] = wb.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        if (PRO == PRO_RMSNORM)       v[j] = __fmul_rn(__fmul_rn(x[j], scale), w[j]);
+        else if (PRO == PRO_SILU_MUL) v[j] = __fmul_rn(pib_h2f(lut[pib_f2h(x[j])]), w[j]);
+        else if (PRO == PRO_GELU)     v[j] = pib_h2f(lut[pib_f2h(x[j])]);
+        else                          v[j] = x[j];
+    }
 }
 
 template <bool Q8K, int PRO>
@@ -50,17 +70,27 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
         __shared__ double red[AQ_THREADS / 32];
         __shared__ float  s_scale;
         double            s = 0.0;
-        // optional residual add fused in front (reference ggml_add, llama.cpp:3944 / :3962): sum_out = x + addend
-        const float * ar = addend ? addend + (size_t) row * K : nullptr;
-        float *       so = sum_out ? sum_out + (size_t) row * K : nullptr;
+        // optional residual add fused in front (reference ggml_add, llama.cpp:3944 / :3962): sum_out = x + addend.
         // (with several CTAs per row each one recomputes the whole row's sum -- K floats from L2 -- and all of them
-        //  write the same sums, so pass 2 never depends on another CTA)
-        for (int64_t i = threadIdx.x; i < K; i += AQ_THREADS) {
-            float v = xr[i];
-            if (ar) { v = __fadd_rn(v, ar[i]); so[i] = v; }
-            s += (double) __fmul_rn(v, v);
+        //  write the same sums, so pass 2 never depends on another CTA).  128-bit loads, four in flight per thread.
+        const float4 * __restrict__ x4 = reinterpret_cast<const float4 *>(xr);
+        const float4 * __restrict__ a4 = addend ? reinterpret_cast<const float4 *>(addend + (size_t) row * K) : nullptr;
+        float4 *                    o4 = sum_out ? reinterpret_cast<float4 *>(sum_out + (size_t) row * K) : nullptr;
+        const int n4 = (int) (K / 4);
+#pragma unroll 4
+        for (int i = threadIdx.x; i < n4; i += AQ_THREADS) {
+            float4 v = x4[i];
+            if (a4) {
+                const float4 a = a4[i];
+                v.x = __fadd_rn(v.x, a.x); v.y = __fadd_rn(v.y, a.y); v.z = __fadd_rn(v.z, a.z); v.w = __fadd_rn(v.w, a.w);
+                o4[i] = v;
+            }
+            s += (double) __fmul_rn(v.x, v.x);
+            s += (double) __fmul_rn(v.y, v.y);
+            s += (double) __fmul_rn(v.z, v.z);
+            s += (double) __fmul_rn(v.w, v.w);
         }
-        if (ar) xr = so;     // pass 2 re-reads the sums (visible CTA-wide after the barrier below)
+        if (a4) xr = sum_out + (size_t) row * K;     // pass 2 re-reads the sums (visible CTA-wide after the barrier below)
         s = warp_sum_d(s);
         if (lane == 0) red[warp] = s;
         __syncthreads();
@@ -101,8 +131,7 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
         for (int64_t sb = (int64_t) blockIdx.y * nwarp + warp; sb < nsb; sb += (int64_t) gridDim.y * nwarp) {
             const int64_t i0 = sb * PIB_QK_K + lane * 8;
             float v[8];
-#pragma unroll
-            for (int j = 0; j < 8; j++) v[j] = aq_value<PRO>(xr, x2r, scale, lut, i0 + j);
+            aq_value8<PRO>(xr, x2r, scale, lut, i0, v);
             // first element (in index order) with the largest |x|: strict '>' scan, ties keep the lower index
             float amax = 0.0f, mx = 0.0f;
             int   idx  = 1 << 30;
@@ -136,8 +165,9 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
             // fragment-order copy for the tensor-core GEMV: lane = 8c + 4h + t  ->  offset 64t + 16c + 8h
             *reinterpret_cast<int2 *>(qsp + (size_t) row * K + sb * PIB_QK_K + (lane & 3) * 64 + (lane >> 3) * 16 + ((lane >> 2) & 1) * 8) = packed;
             if (vout) {
-#pragma unroll
-                for (int j = 0; j < 8; j++) vout[(size_t) row * K + i0 + j] = v[j];
+                float4 * vo = reinterpret_cast<float4 *>(vout + (size_t) row * K + i0);
+                vo[0] = make_float4(v[0], v[1], v[2], v[3]);
+                vo[1] = make_float4(v[4], v[5], v[6], v[7]);
             }
             int s8 = q[0] + q[1] + q[2] + q[3] + q[4] + q[5] + q[6] + q[7];
             int s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);

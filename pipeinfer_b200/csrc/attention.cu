@@ -19,6 +19,7 @@
 
 #include <math.h>
 
+#include <algorithm>
 #include <vector>
 
 // ---- RoPE table -----------------------------------------------------------------------------------------------------
@@ -200,6 +201,122 @@ __global__ void __launch_bounds__(ATT_THREADS) attention_kernel(const __half * _
     }
 }
 
+// ---- per-query-head variant (short contexts: verification batches) -----------------------------------------------------
+// grid (n_head, n_tokens), 256 threads.  Phase 1 gives every thread whole cells: a lane reads one K row with 128-bit loads
+// and keeps the dot product in four independent fp32 accumulators (no shuffles); phase 3 gives every thread a pair of
+// output dims over a slice of the cells, eight V loads in flight.  K/V of a KV head are re-read by its G query heads
+// through L2 -- a few MB per layer at these context lengths.
+#define ATQ_THREADS 256
+template <int HD>
+__global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half * __restrict__ q16, const __half * __restrict__ kcache,
+                                                                   const __half * __restrict__ vcache, const uint8_t * __restrict__ mask,
+                                                                   const int32_t * __restrict__ scalars, const uint16_t * __restrict__ exp_lut,
+                                                                   int E, int GQA, int n_ctx, float kq_scale, float * __restrict__ out,
+                                                                   const int * __restrict__ cancel, int gdiv) {
+    if (cancel && *cancel) return;
+    extern __shared__ float smem[];
+    __shared__ float  sq[HD];
+    __shared__ float  s_redf[ATQ_THREADS / 32];
+    __shared__ double s_redd[ATQ_THREADS / 32];
+    __shared__ float  s_max, s_inv;
+    const int head = blockIdx.x, kvh = head / gdiv, t = blockIdx.y;
+    const int n = scalars[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float *         s    = smem;                       // [n] scores -> probabilities
+    const uint8_t * mrow = mask + (size_t) t * n_ctx;
+    if (tid < HD) sq[tid] = __half2float(q16[(size_t) t * E + (size_t) head * HD + tid]);
+    __syncthreads();
+
+    // phase 1: scores
+    float lmax = -INFINITY;
+    for (int i = tid; i < n; i += ATQ_THREADS) {
+        float sc = -INFINITY;
+        if (!mrow[i]) {
+            const uint4 * kr = reinterpret_cast<const uint4 *>(kcache + (size_t) i * GQA + (size_t) kvh * HD);
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+            for (int v = 0; v < HD / 8; v++) {
+                const uint4   k8 = kr[v];
+                const __half2 h0 = *reinterpret_cast<const __half2 *>(&k8.x), h1 = *reinterpret_cast<const __half2 *>(&k8.y);
+                const __half2 h2 = *reinterpret_cast<const __half2 *>(&k8.z), h3 = *reinterpret_cast<const __half2 *>(&k8.w);
+                const float4  qa = *reinterpret_cast<const float4 *>(sq + v * 8), qb = *reinterpret_cast<const float4 *>(sq + v * 8 + 4);
+                a0 = fmaf(__low2float(h0), qa.x, a0); a1 = fmaf(__high2float(h0), qa.y, a1);
+                a2 = fmaf(__low2float(h1), qa.z, a2); a3 = fmaf(__high2float(h1), qa.w, a3);
+                a0 = fmaf(__low2float(h2), qb.x, a0); a1 = fmaf(__high2float(h2), qb.y, a1);
+                a2 = fmaf(__low2float(h3), qb.z, a2); a3 = fmaf(__high2float(h3), qb.w, a3);
+            }
+            sc = __fmul_rn((a0 + a1) + (a2 + a3), kq_scale);
+        }
+        s[i] = sc;
+        lmax = fmaxf(lmax, sc);
+    }
+    lmax = warp_max(lmax);
+    if (lane == 0) s_redf[warp] = lmax;
+    __syncthreads();
+    if (tid == 0) { float m = s_redf[0]; for (int w = 1; w < ATQ_THREADS / 32; w++) m = fmaxf(m, s_redf[w]); s_max = m; }
+    __syncthreads();
+
+    // phase 2: exp through the fp16 table, exact double sum, fp16-rounded probabilities
+    const float mx = s_max;
+    double sum = 0.0;
+    for (int i = tid; i < n; i += ATQ_THREADS) {
+        const float x = s[i];
+        float       v = 0.0f;
+        if (x != -INFINITY) { v = pib_h2f(exp_lut[pib_f2h(__fsub_rn(x, mx))]); sum += (double) v; }
+        s[i] = v;
+    }
+    sum = warp_sum_d(sum);
+    if (lane == 0) s_redd[warp] = sum;
+    __syncthreads();
+    if (tid == 0) { double a = 0.0; for (int w = 0; w < ATQ_THREADS / 32; w++) a += s_redd[w]; s_inv = (float) (1.0 / a); }
+    __syncthreads();
+    const float inv = s_inv;
+    for (int i = tid; i < n; i += ATQ_THREADS) s[i] = __half2float(__float2half_rn(__fmul_rn(s[i], inv)));
+    __syncthreads();
+
+    // phase 3: O = V . P
+    constexpr int TPR = HD / 2, NGR = ATQ_THREADS / TPR;
+    const int grp = tid / TPR, dp = tid % TPR;
+    const __half * vb = vcache + (size_t) kvh * HD + dp * 2;
+    float o0 = 0.f, o1 = 0.f;
+    int i = grp;
+    for (; i + 7 * NGR < n; i += 8 * NGR) {
+        __half2 vv[8];
+        float   pp[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) { vv[u] = *reinterpret_cast<const __half2 *>(vb + (size_t) (i + u * NGR) * GQA); pp[u] = s[i + u * NGR]; }
+#pragma unroll
+        for (int u = 0; u < 8; u++) { o0 = fmaf(__low2float(vv[u]), pp[u], o0); o1 = fmaf(__high2float(vv[u]), pp[u], o1); }
+    }
+    for (; i < n; i += NGR) {
+        const float p = s[i];
+        if (p != 0.f) {
+            const __half2 vv = *reinterpret_cast<const __half2 *>(vb + (size_t) i * GQA);
+            o0 = fmaf(__low2float(vv), p, o0); o1 = fmaf(__high2float(vv), p, o1);
+        }
+    }
+    __syncthreads();
+    float * red = smem;                                 // reuse: [NGR][HD]
+    red[grp * HD + dp * 2] = o0; red[grp * HD + dp * 2 + 1] = o1;
+    __syncthreads();
+    if (tid < HD) {
+        float a = 0.f;
+#pragma unroll
+        for (int r = 0; r < NGR; r++) a += red[r * HD + tid];
+        out[(size_t) t * E + (size_t) head * HD + tid] = a;
+    }
+}
+
+template <int HD>
+static int launch_att_qh(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
+                         int E, int GQA, int n_ctx, int n_tokens, int n_head, int gdiv, float * out, const int * cancel, cudaStream_t st) {
+    const size_t smem = (size_t) std::max(n_ctx, (ATQ_THREADS / (HD / 2)) * HD) * sizeof(float);
+    attention_qh_kernel<HD><<<dim3(n_head, n_tokens), ATQ_THREADS, smem, st>>>(q16, kc, vc, mask, scalars, pib_get_luts().exp_f16, E, GQA,
+                                                                               n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+
 template <int HD, int G>
 static int launch_att(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
                       const uint8_t * desc, int E, int GQA, int n_ctx, int n_tokens, int n_blocks_x, int gdiv, float * out,
@@ -238,10 +355,9 @@ int pib_attention(const __half * q16, const __half * kc, const __half * vc, cons
                   const int * cancel, cudaStream_t st) {
     const int E = n_head * hd, GQA = n_head_kv * hd, G = n_head / n_head_kv;
     // per-query-head CTAs unless the context is long enough for the G-fold K/V re-reads to matter
-    const bool per_q = G > 1 && n_ctx <= 2048;
-    if (per_q) {
-        if (hd == 128) return launch_att<128, 1>(q16, kc, vc, mask, scalars, desc, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
-        if (hd == 64)  return launch_att<64, 1>(q16, kc, vc, mask, scalars, desc, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
+    if (n_ctx <= 4096) {
+        if (hd == 128) return launch_att_qh<128>(q16, kc, vc, mask, scalars, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
+        if (hd == 64)  return launch_att_qh<64>(q16, kc, vc, mask, scalars, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
     }
 #define ATT_CASE(HDv, Gv) \
     if (hd == HDv && G == Gv) return launch_att<HDv, Gv>(q16, kc, vc, mask, scalars, desc, E, GQA, n_ctx, n_tokens, n_head_kv, 1, out, cancel, st);
