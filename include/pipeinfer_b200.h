@@ -78,8 +78,23 @@ int pib_act_to_blocks(int wtype, const void * act_dev, int b, int64_t K, void * 
 /* y_dev float [b][N] = W[N][K] . act (b rows).  Integer block dot products, fp16 block scales, fp32 accumulation.
  * Replaces: ggml_compute_forward_mul_mat (ggml.c:9388) with ggml_vec_dot_q4_0_q8_0 / q8_0_q8_0 / q4_K_q8_K
  * (ggml-quants.c:2426, 3521, 5216).  `variant`: 0 = default (fastest available), 1 = warp-per-row dp4a kernel,
- * 2 = TMA-staged tensor-core kernel. */
+ * 2 = tensor-core kernel with register-prefetched weight tiles (Q4_K; the default there), 3 = persistent TMA-staged
+ * tensor-core kernel (Q4_K). */
 int pib_gemv(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, pib_stream s);
+/* Same product as pib_gemv(variant 0) for Q4_K weights, for callers that must not allocate device memory while they
+ * run (a latency-critical serving loop that cannot take the allocator's lock or its device-wide synchronisation; a
+ * process whose HBM is already fully committed; a host that forbids allocation after start-up).  No counterpart in the
+ * reference.  When few output rows leave the GPU under-filled the kernel splits K over several CTAs and sums their
+ * partial results through global scratch; pib_gemv takes that scratch from cudaMalloc on first use, this entry point
+ * keeps it in a fixed PIB_GEMV_NOALLOC_SCRATCH_BYTES array inside the library image and calls no allocating routine.
+ * Limits: split * b * N * 4 bytes of partial sums must fit in the array less 16 KiB and N <= 65536 whenever a split is
+ * used (true for every matrix the current split rule splits); otherwise PIB_ERR_ARG with the sizes in pib_last_error.
+ * The first call on each device looks the array's address up (cudaGetSymbolAddress): issue it before any stream
+ * capture.  All calls on a device share the array: calls that overlap in time (other streams, other threads) corrupt
+ * each other's sums -- serialise them.  Results are bit-identical to pib_gemv's. */
+#define PIB_GEMV_NOALLOC_SCRATCH_BYTES (2u * 1024u * 1024u)
+#define PIB_MAX_DEV_NOALLOC 64
+int pib_gemv_q4k_noalloc(const pib_weight * w, const void * act_dev, int b, float * y_dev, pib_stream s);
 /* Host-buffer convenience used by the parity tests and the end-to-end timing: x_host float [b][K] -> y_host [b][N];
  * includes the H2D copy of x, quantisation, GEMV and the D2H copy of y. */
 int pib_mul_mat_host(const pib_weight * w, const float * x_host, int b, float * y_host, int variant);

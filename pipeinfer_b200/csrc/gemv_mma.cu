@@ -592,3 +592,55 @@ int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_de
     }
     return pib_gemv_mma_launch(w, act_dev, b, y_dev, split, s ? s->partial : nullptr, s ? s->counters : nullptr, cancel, st);
 }
+
+// ---- allocation-free entry point ------------------------------------------------------------------------------------
+// The k-split reduction above needs global scratch (partial sums + arrival counters).  pib_gemv gets it from cudaMalloc
+// on first use, which some callers cannot afford: a real-time serving loop that must not take the allocator's lock or
+// its implicit device synchronisation in the middle of a decode, code running while another component has device
+// memory fully committed, or a host that forbids allocation after start-up.  For them the same kernel runs with its
+// scratch in a fixed array that lives in the library's own device image.
+//
+// `noalloc_scratch` below is, on the host side, only a handle for the symbol: its device address is obtained once per
+// device with cudaGetSymbolAddress (with that device current) and cached.  That look-up happens inside the FIRST call
+// on each device, so make that first call outside any stream capture.
+//
+// The array is shared by every call on a device and keeps whatever the previous call left in it.  The arrival counters
+// must start at zero, so each call clears the ones it uses (stream-ordered, in front of the kernel); partial sums are
+// always written before they are read.  Two calls in flight at once on the same device (different streams or threads)
+// would use the same counters and sums and corrupt each other: serialise them.
+#define PIB_NOALLOC_COUNTER_BYTES (16u * 1024u)                                    /* 4096 row tiles */
+static __device__ __align__(256) unsigned char noalloc_scratch[PIB_GEMV_NOALLOC_SCRATCH_BYTES];
+static unsigned char * g_noalloc_ptr[PIB_MAX_DEV_NOALLOC];
+
+extern "C" int pib_gemv_q4k_noalloc(const pib_weight * w, const void * act_dev, int b, float * y_dev, pib_stream stream) {
+    if (!w || !act_dev || !y_dev) { pib_set_error("pib_gemv_q4k_noalloc: null argument"); return PIB_ERR_ARG; }
+    if (b < 1 || b > PIB_MAX_BATCH) { pib_set_error("pib_gemv_q4k_noalloc: b = %d outside 1..%d", b, PIB_MAX_BATCH); return PIB_ERR_ARG; }
+    if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv_q4k_noalloc: needs a Q4_K weight handle"); return PIB_ERR_UNSUPP; }
+    int dev = -1;
+    PIB_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= PIB_MAX_DEV_NOALLOC) { pib_set_error("pib_gemv_q4k_noalloc: device ordinal %d not supported (max %d)", dev, PIB_MAX_DEV_NOALLOC - 1); return PIB_ERR_UNSUPP; }
+    if (!g_noalloc_ptr[dev]) {                       // once per device, with that device current
+        void * p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, noalloc_scratch);
+        if (e != cudaSuccess || !p) { pib_set_error("pib_gemv_q4k_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e)); return PIB_ERR_CUDA; }
+        g_noalloc_ptr[dev] = (unsigned char *) p;
+    }
+    const int    nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    const int    split = choose_split_direct(n_tiles, nsb);
+    float *        partial  = nullptr;
+    unsigned int * counters = nullptr;
+    if (split > 1) {
+        const size_t need_partial  = (size_t) split * b * w->N * sizeof(float);
+        const size_t need_counters = (size_t) n_tiles * sizeof(unsigned int);
+        if (need_counters > PIB_NOALLOC_COUNTER_BYTES || need_partial > PIB_GEMV_NOALLOC_SCRATCH_BYTES - PIB_NOALLOC_COUNTER_BYTES) {
+            pib_set_error("pib_gemv_q4k_noalloc: N = %lld, b = %d with %d k-splits needs %zu + %zu bytes of scratch; the built-in "
+                          "array holds %u + %u (use pib_gemv)", (long long) w->N, b, split, need_partial, need_counters,
+                          PIB_GEMV_NOALLOC_SCRATCH_BYTES - PIB_NOALLOC_COUNTER_BYTES, PIB_NOALLOC_COUNTER_BYTES);
+            return PIB_ERR_ARG;
+        }
+        counters = reinterpret_cast<unsigned int *>(g_noalloc_ptr[dev]);
+        partial  = reinterpret_cast<float *>(g_noalloc_ptr[dev] + PIB_NOALLOC_COUNTER_BYTES);
+        PIB_CHECK(cudaMemsetAsync(counters, 0, need_counters, (cudaStream_t) stream));
+    }
+    return pib_gemv_direct_launch(w, act_dev, b, y_dev, split, partial, counters, nullptr, (cudaStream_t) stream);
+}

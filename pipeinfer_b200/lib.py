@@ -54,6 +54,7 @@ class Lib:
                                             C.c_void_p, C.c_void_p, C.c_void_p]
         L.pib_act_to_blocks.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int64, C.c_void_p]
         L.pib_gemv.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+        L.pib_gemv_q4k_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.pib_mul_mat_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
         L.pib_get_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
 
