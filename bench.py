@@ -161,6 +161,8 @@ def main():
     ap.add_argument("--pa", type=float, default=0.1)
     ap.add_argument("--ps", type=float, default=0.9)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--layer-split", default="", help="comma-separated per-stage weights, as the reference's --mpi-layer-split")
+    ap.add_argument("--head-share", type=float, default=None, help="share of the target's layers on the head GPU (which also runs the draft)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -189,16 +191,22 @@ def main():
         return 0
 
     import torch
-    from pipeinfer_b200 import llama
+    from pipeinfer_b200 import llama, pipeline
     lib = llama.api()
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0"))))
     dev = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(dev)
+    dist = None
     if world > 1:
-        from pipeinfer_b200 import pipeline
-        return pipeline.bench_multi_gpu(args, config, CONFIGS)
+        import torch.distributed as dist
+        dist.init_process_group("cpu:gloo,cuda:nccl")
+        pipeline.open_pipeline(rank, world, dev)
+
+    def allreduce(vals, op="sum"):
+        if world == 1:
+            return list(vals)
+        t = torch.tensor(list(vals), dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+        return t.tolist()
 
     lib.llama_pib_io_bytes.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     lib.llama_pib_profile_layer.argtypes = [C.c_void_p, C.c_int]
@@ -206,8 +214,15 @@ def main():
     lib.llama_pib_matrix_shape.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_uint64)]
     cap = 1000 * args.np + 2
     t_load = time.time()
-    tgt = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=(L, E, H, HKV, FF, V, wt, 1, 1, 1.0))
-    dft = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=dshape + (2, 1, args.agree))
+    weights = [float(x) for x in args.layer_split.split(",")] if args.layer_split else pipeline.default_weights(world, args.head_share)
+    ranges = pipeline.split_layers(L, weights) if world > 1 else [(0, L)]
+    config["layer_ranges"] = ranges
+    if world > 1:
+        tgt = pipeline.StageContext(rank, world, ranges, 1024, cap, synthetic=(L, E, H, HKV, FF, V, wt, 1, 1, 1.0))
+    else:
+        tgt = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=(L, E, H, HKV, FF, V, wt, 1, 1, 1.0))
+    dft = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=dshape + (2, 1, args.agree)) if rank == 0 else None
+    ctxs = [c for c in (tgt, dft) if c is not None]
     t_load = time.time() - t_load
     prompt = [1] + [3 + (i * 7919) % (V - 3) for i in range(args.prompt_len - 1)]
     params = llama.spec_params(n_draft=args.draft, n_parallel=args.np, p_accept=args.pa, p_split=args.ps, n_predict=args.n_predict)
@@ -218,37 +233,68 @@ def main():
         return a.value, b.value
 
     def step():
+        if rank != 0:                                   # a stage: serve until the head pauses the pipeline
+            tgt.serve()
+            return None, None, None
         lib.llama_kv_cache_clear(tgt.ctx)
         lib.llama_kv_cache_clear(dft.ctx)
-        return llama.speculative_generate(tgt, dft, prompt, params)
+        out = llama.speculative_generate(tgt, dft, prompt, params)
+        if world > 1:
+            tgt.pause()
+        return out
+
+    def launches():
+        return sum(lib.llama_pib_kernel_launches(c.ctx) for c in ctxs)
 
     first = None
     for _ in range(args.warmup):
         toks, res, itl = step()
         first = first or toks
-    prof_layer = L // 2
+    b0, e0l = ranges[rank] if world > 1 else (0, L)
+    prof_layer = (b0 + e0l) // 2
     lib.llama_pib_profile_layer(tgt.ctx, prof_layer)
-    k0 = lib.llama_pib_kernel_launches(tgt.ctx) + lib.llama_pib_kernel_launches(dft.ctx)
-    io0 = [io(tgt), io(dft)]
+    k0 = launches()
+    io0 = [io(c) for c in ctxs]
+    tr0 = pipeline.traffic()
     clocks = ClockSampler(dev)
     clocks.start()
+    allreduce([0.0])                                    # barrier
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     results, itls = [], []
     for _ in range(args.steps):
         toks, res, itl = step()
-        assert toks[:len(first)] == first[:len(toks)], "non-deterministic generation"
-        results.append(res)
-        itls += itl
+        if rank == 0:
+            assert toks[:len(first)] == first[:len(toks)], "non-deterministic generation"
+            results.append(res)
+            itls += itl
     torch.cuda.synchronize()
     e1.record()
     e1.synchronize()
-    wall_ms = e0.elapsed_time(e1)
+    wall_ms = allreduce([e0.elapsed_time(e1)], "max")[0]        # barrier + max over ranks
     clk = clocks.stop()
     lib.llama_pib_profile_layer(tgt.ctx, -1)
-    k1 = lib.llama_pib_kernel_launches(tgt.ctx) + lib.llama_pib_kernel_launches(dft.ctx)
-    io1 = [io(tgt), io(dft)]
+    k1 = launches()
+    io1 = [io(c) for c in ctxs]
+    tr1 = pipeline.traffic()
+    h2d_all, d2h_all, launches_all, wbytes_all = allreduce([
+        sum(io1[i][0] - io0[i][0] for i in range(len(ctxs))), sum(io1[i][1] - io0[i][1] for i in range(len(ctxs))), k1 - k0,
+        sum(lib.llama_pib_weight_bytes(c.model) for c in ctxs)])
+    hops = None
+    if world > 1:
+        per_rank = [torch.zeros(3, dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(per_rank, torch.tensor([tr1[i] - tr0[i] for i in range(3)], dtype=torch.float64))
+        hops = [{"rank": r, "activation_bytes_to_next_stage": int(t[0]), "messages": int(t[1]), "result_bytes_to_head": int(t[2])}
+                for r, t in enumerate(per_rank)]
+        if rank == 0:
+            tgt.shutdown()
+        else:
+            assert tgt.serve() == 1
+        pipeline.close_pipeline()
+        dist.destroy_process_group()
+        if rank != 0:
+            return 0
 
     n_tok = sum(r["n_predict"] for r in results)
     t_dec = sum(r["t_decode_s"] for r in results)
@@ -290,7 +336,7 @@ def main():
                     "other_kernels_of_the_layer": others}
 
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:
         try:
             r = run_reference_sample(args.config, args, budget="small")
             if r:
@@ -298,10 +344,10 @@ def main():
         except Exception as e:      # the baseline is informative; never lose the GPU line over it
             cpu = {"value": None, "unit": "tokens/s", "cores": os.cpu_count(), "kind": "reference", "sample": "failed: %r" % (e,)}
 
-    h2d = sum(io1[i][0] - io0[i][0] for i in range(2)) + 4 * len(prompt) * args.steps
-    d2h = sum(io1[i][1] - io0[i][1] for i in range(2))
+    h2d = int(h2d_all) + 4 * len(prompt) * args.steps
+    d2h = int(d2h_all)
     acc = sum(r["n_accept"] for r in results) / max(1, sum(r["n_drafted"] for r in results))
-    line = {"metric": "accepted tokens/sec", "value": n_tok / t_dec, "unit": "tokens/s", "n_gpus": 1, "steps": args.steps,
+    line = {"metric": "accepted tokens/sec", "value": n_tok / t_dec, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": wall_ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 x int4 blocks (Q4_K x Q8_K), fp32 accumulate", "data": "synthetic", "config": config,
             "latency_p50_ms": p50, "latency_mean_ms": sum(itls_ms) / len(itls_ms) if itls_ms else None,
@@ -310,8 +356,9 @@ def main():
             "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
             "e2e": {"value": n_tok / (wall_ms / 1000.0), "unit": "tokens/s", "h2d_bytes_per_step": h2d // args.steps,
                     "d2h_bytes_per_step": d2h // args.steps},
-            "gpu_launches": int(k1 - k0), "weights_gb": (lib.llama_pib_weight_bytes(tgt.model) + lib.llama_pib_weight_bytes(dft.model)) / 1e9,
-            "model_build_s": t_load}
+            "gpu_launches": int(launches_all), "weights_gb": wbytes_all / 1e9, "model_build_s": t_load}
+    if hops is not None:
+        line["nvlink_hops"] = {"per_rank_over_timed_steps": hops, "formula": "n_tokens * n_embd * 4 B of fp32 activations per hop (%d B per token) + 96 B per sampled row back to the head" % (E * 4)}
     print(json.dumps(line))
     return 0
 

@@ -181,6 +181,17 @@ void llama_pib_set_logit_bias(struct llama_context * ctx, const llama_token * id
 /* random-init model of the llama architecture generated directly in HBM (no file); flavour 0 iid, 1 bigram */
 struct llama_model * llama_pib_synthetic_model(int n_layer, int n_embd, int n_head, int n_head_kv, int n_ff, int n_vocab,
                                                int wtype, uint64_t seed, int flavour, float agree);
+/* pipeline stages (multi-GPU, one process per GPU; see pipeinfer_mpi.h): a stage's share of a model and a context bound
+ * to stage `rank` of `size`; llama_pib_stage_serve is the worker loop of ranks > 0 (reference llama.cpp:9941-9977):
+ * returns 0 when the head paused the pipeline, 1 on shutdown, -1 on error */
+struct llama_model * llama_pib_synthetic_model_slice(int n_layer, int n_embd, int n_head, int n_head_kv, int n_ff, int n_vocab,
+                                                     int wtype, uint64_t seed, int flavour, float agree, int layer_begin,
+                                                     int layer_end, int want_embd, int want_output);
+struct llama_model * llama_pib_load_model_slice(const char * path_model, int layer_begin, int layer_end, int want_embd, int want_output);
+struct llama_context * llama_pib_new_context_stage(struct llama_model * model, uint32_t n_ctx, int32_t max_seq_ids, int rank, int size);
+int  llama_pib_stage_serve(struct llama_context * ctx);
+int  llama_pib_pipe_pause(struct llama_context * ctx);
+int  llama_pib_pipe_shutdown(struct llama_context * ctx);
 /* context with an explicit sequence-id capacity (the reference sizes std::set on demand) */
 struct llama_context * llama_pib_new_context(struct llama_model * model, uint32_t n_ctx, int32_t max_seq_ids);
 /* KV bookkeeping probes for parity tests: head / used / n, cell positions and sequence bitset rows, host mirror (0)

@@ -1,0 +1,70 @@
+/*
+ * pipeinfer_mpi.h -- C ABI of libpipeinfer_b200.so, transport level: the reference's ggml-mpi.h entry points
+ * (ggml-mpi.h:70-301) mapped onto a shared-memory control ring (host records, in order, head -> every stage) and NCCL
+ * send/recv over NVLink (device data), plus the calls that open that transport.  One process per GPU of one node.
+ * Citations are to the reference repository.
+ */
+#ifndef PIPEINFER_MPI_H
+#define PIPEINFER_MPI_H
+
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- opening the transport (replaces mpirun + MPI_Init_thread, ggml-mpi.c:58-82) ----
+ * Every rank: pib_pipe_ring_open(name, rank, n, bytes) (rank 0 creates /dev/shm/<name>), then -- GPU runs only --
+ * rank 0 draws two ids with pib_pipe_unique_id, the launcher's store (torch.distributed) hands them to all ranks, and
+ * every rank calls pib_pipe_nccl_init collectively.  pib_pipe_barrier is a host barrier over the ring's ranks. */
+int  pib_pipe_ring_open(const char * name, int rank, int n_ranks, size_t cap_bytes);
+void pib_pipe_ring_close(void);
+int  pib_pipe_barrier(void);
+int  pib_pipe_rank(void);
+int  pib_pipe_size(void);
+int  pib_pipe_unique_id(uint8_t * out128);
+int  pib_pipe_nccl_init(int rank, int size, const uint8_t * id_fwd, const uint8_t * id_back);
+void pib_pipe_nccl_free(void);
+/* bytes / messages of activations this rank sent to its next stage, and bytes of sampled rows it sent to the head */
+void pib_pipe_traffic(uint64_t * hop_bytes, uint64_t * hop_msgs, uint64_t * back_bytes);
+/* layer partition rule of ggml_mpi_split_range (ggml-mpi.c:523-559) without a context: out_pairs[2*i], [2*i+1] */
+void pib_split_range(int n_stages, int start, int end, const float * weights, uint16_t * out_pairs);
+
+/* ---- ggml-mpi.h ---- */
+struct ggml_mpi_context;
+void   ggml_mpi_backend_init(void);                                                        /* ggml-mpi.c:58  */
+void   ggml_mpi_backend_free(void);                                                        /* :63  */
+struct ggml_mpi_context * ggml_mpi_init(void);                                             /* :67  */
+void   ggml_mpi_free(struct ggml_mpi_context * ctx);                                       /* :100 */
+int    ggml_mpi_rank(struct ggml_mpi_context * ctx);                                       /* :128 */
+size_t ggml_mpi_size(struct ggml_mpi_context * ctx);                                       /* :132 */
+void   ggml_mpi_barrier(struct ggml_mpi_context * ctx);                                    /* :136 */
+int    ggml_mpi_next_node(struct ggml_mpi_context * ctx_mpi);                              /* :164 */
+int    ggml_mpi_prev_node(struct ggml_mpi_context * ctx_mpi);                              /* :168 */
+int    ggml_mpi_trans_id(struct ggml_mpi_context * ctx_mpi);                               /* :38  */
+int    ggml_mpi_recv_trans_id(struct ggml_mpi_context * ctx_mpi);                          /* :42  */
+void   ggml_mpi_inc_trans_id(struct ggml_mpi_context * ctx_mpi);                           /* :46  */
+void   ggml_mpi_sync_ints_pipelined(struct ggml_mpi_context * ctx_mpi, int32_t * vals, int count, int tag);   /* :349 */
+void   ggml_mpi_probe(struct ggml_mpi_context * ctx_mpi, int src, int tag);                /* :140 */
+int    ggml_mpi_iprobe(struct ggml_mpi_context * ctx_mpi, int src, int tag);               /* :146 */
+int    ggml_mpi_status_tag(struct ggml_mpi_context * ctx_mpi);                             /* :154 */
+int    ggml_mpi_status_count_int32(struct ggml_mpi_context * ctx_mpi);                     /* :158 */
+/* `val` is a DEVICE pointer; NCCL send / recv between any two ranks */
+void   ggml_mpi_send_float_array_async(struct ggml_mpi_context * ctx_mpi, float * val, int arr_size, int dest, int tag);   /* :411 */
+void   ggml_mpi_recv_float_array(struct ggml_mpi_context * ctx_mpi, float * val, int arr_size, int src, int tag);          /* :399 */
+uint16_t ** ggml_mpi_split_range(struct ggml_mpi_context * ctx_mpi, uint16_t start, uint16_t end, float node_weights[]);   /* :523 */
+void   ggml_mpi_scatter_layers(struct ggml_mpi_context * ctx_mpi, uint16_t ** layer_ranges);                               /* :561 */
+/* additive: the range ggml_mpi_scatter_layers delivered to this rank */
+void   ggml_mpi_layer_range(struct ggml_mpi_context * ctx_mpi, uint16_t * start, uint16_t * end);
+
+/* ---- CPU-only test hooks: KV bookkeeping replicated through the control ring (no CUDA call) ---- */
+void pib_kvtest_ship(void * kvtest, int enable);                 /* head: pib_kvtest_decode also publishes its record */
+int  pib_kvtest_replay(void * kvtest);                            /* stage: apply records until the head pauses (0) */
+int  pib_kvtest_pause(void * kvtest);                             /* head: flush the op-log, then pause the stages */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

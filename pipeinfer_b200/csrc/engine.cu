@@ -483,15 +483,17 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
     return PIB_OK;
 }
 
+static int enqueue_decode(pib_context * c, pib_run * run, int n_tokens, int batch_id, const std::vector<int> & slots);
+
 static pib_run * take_run(pib_context * c, int n_tokens) {
     for (auto & r : c->runs) {
         if (r.in_use || r.id == c->last_finished) continue;
         if (!r.done) cudaEventCreateWithFlags(&r.done, cudaEventDisableTiming);
         const int cap = ((n_tokens + PIB_CHUNK - 1) / PIB_CHUNK) * PIB_CHUNK;
-        if (c->stage.last() && r.cap_tokens < cap) {
-            if (r.logits) { cudaStreamSynchronize(c->stream); cudaFree(r.logits); cudaFree(r.res_dev); cudaFreeHost(r.res_host); }
+        if ((c->stage.last() || c->stage.first()) && r.cap_tokens < cap) {
+            if (r.res_dev) { cudaStreamSynchronize(c->stream); cudaFree(r.logits); cudaFree(r.res_dev); cudaFreeHost(r.res_host); }
             r.logits = nullptr; r.res_dev = nullptr; r.res_host = nullptr;
-            if (cudaMalloc(&r.logits, (size_t) cap * c->model->n_vocab * 4) != cudaSuccess ||
+            if ((c->stage.last() && cudaMalloc(&r.logits, (size_t) cap * c->model->n_vocab * 4) != cudaSuccess) ||
                 cudaMalloc(&r.res_dev, (size_t) cap * sizeof(pib_row_result)) != cudaSuccess ||
                 cudaMallocHost(&r.res_host, (size_t) cap * sizeof(pib_row_result)) != cudaSuccess) {
                 pib_set_error("decode: out of memory for logits of %d tokens", cap);
@@ -548,19 +550,46 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
     }
     dq.push_back({ KVOP_ADVANCE, n_tokens, 0, 0, 0, 0 });
     kvlog_decode_end(c->kv, n_tokens);                                    // llama.cpp:5708-5713
-    // ship the op-log and replay it on the device
-    {
-        const int n = (int) dq.size();
-        if (n > c->ops_cap) { pib_set_error("decode: KV op-log overflow (%d ops)", n); return -1; }
-        if (c->ops_next + n > c->ops_cap) { cudaStreamSynchronize(c->stream); c->ops_next = 0; }
-        memcpy(c->ops_host + c->ops_next, dq.data(), sizeof(KvOp) * n);
-        cudaMemcpyAsync(c->ops_dev + c->ops_next, c->ops_host + c->ops_next, sizeof(KvOp) * n, cudaMemcpyHostToDevice, c->stream);
-        c->h2d_bytes += sizeof(KvOp) * n;
-        if (kv_device_apply(&c->kvd, c->ops_dev + c->ops_next, n, c->desc_dev, c->desc_stride, c->stream) != PIB_OK) return -1;
-        c->n_kernels++;
-        c->ops_next += n;
-        dq.clear();
+    if (c->stage.size > 1 && c->stage.first()) {          // tell the other stages first, so that their receives are posted early
+        std::vector<const uint8_t *> dp(n_chunks);
+        for (int ch = 0; ch < n_chunks; ch++) dp[ch] = c->desc_host + (size_t) slots[ch] * c->desc_stride;
+        if (pib_pipe_ship_decode(batch_id, n_tokens, n_chunks, dp.data(), c->desc_stride, slots.data(), dq.data(), (int) dq.size()) != PIB_OK) return -1;
     }
+    return enqueue_decode(c, run, n_tokens, batch_id, slots);
+}
+
+// ship the queued device-level op-log to the GPU and replay it on the KV replica
+int pib_apply_devops(pib_context * c) {
+    std::vector<KvOp> & dq = devq(c);
+    const int n = (int) dq.size();
+    if (n == 0) return PIB_OK;
+    if (n > c->ops_cap) { pib_set_error("decode: KV op-log overflow (%d ops)", n); return PIB_ERR_ARG; }
+    if (c->ops_next + n > c->ops_cap) { cudaStreamSynchronize(c->stream); c->ops_next = 0; }
+    memcpy(c->ops_host + c->ops_next, dq.data(), sizeof(KvOp) * n);
+    cudaMemcpyAsync(c->ops_dev + c->ops_next, c->ops_host + c->ops_next, sizeof(KvOp) * n, cudaMemcpyHostToDevice, c->stream);
+    c->h2d_bytes += sizeof(KvOp) * n;
+    if (kv_device_apply(&c->kvd, c->ops_dev + c->ops_next, n, c->desc_dev, c->desc_stride, c->stream) != PIB_OK) return PIB_ERR_CUDA;
+    c->n_kernels++;
+    c->ops_next += n;
+    dq.clear();
+    return PIB_OK;
+}
+
+// head: bring every replica (its own GPU's and the other stages') up to date with the KV ops issued so far, without a decode
+int pib_kv_sync_replicas(pib_context * c) {
+    pib_kv_flush_host(c);
+    std::vector<KvOp> & dq = devq(c);
+    if (dq.empty()) return PIB_OK;
+    if (c->stage.size > 1 && c->stage.first() &&
+        pib_pipe_ship_decode(0, 0, 0, nullptr, c->desc_stride, nullptr, dq.data(), (int) dq.size()) != PIB_OK) return PIB_ERR_NOMEM;
+    return pib_apply_devops(c);
+}
+
+// device part of a decode, common to the head and the other stages: replay the op-log on the KV replica, run the chunks,
+// hand the sampled rows to whoever needs them
+static int enqueue_decode(pib_context * c, pib_run * run, int n_tokens, int batch_id, const std::vector<int> & slots) {
+    const int n_chunks = (int) slots.size();
+    if (pib_apply_devops(c) != PIB_OK) return -1;
     run->in_use = true; run->batch_id = batch_id; run->n_tokens = n_tokens; run->failed = false;
     for (int ch = 0; ch < n_chunks; ch++) {
         const int nt = std::min(PIB_CHUNK, n_tokens - ch * PIB_CHUNK);
@@ -568,13 +597,64 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
         cudaEventRecord(c->desc_ev[slots[ch]], c->stream);
     }
     if (c->stage.last() && !run->failed) {
-        cudaMemcpyAsync(run->res_host, run->res_dev, sizeof(pib_row_result) * (size_t) n_tokens, cudaMemcpyDeviceToHost, c->stream);
-        c->d2h_bytes += sizeof(pib_row_result) * (size_t) n_tokens;
+        if (c->stage.size > 1) {
+            if (pib_pipe_send_results(c, *run) != PIB_OK) run->failed = true;
+        } else {
+            cudaMemcpyAsync(run->res_host, run->res_dev, sizeof(pib_row_result) * (size_t) n_tokens, cudaMemcpyDeviceToHost, c->stream);
+            c->d2h_bytes += sizeof(pib_row_result) * (size_t) n_tokens;
+        }
     }
     cudaEventRecord(run->done, c->stream);
+    if (c->stage.size > 1 && c->stage.first() && !run->failed) {
+        // the rows come back from the last stage on the result stream; `done` then means "rows are in pinned host memory"
+        if (pib_pipe_post_result_recv(c, *run) != PIB_OK) run->failed = true;
+    }
     c->inflight.push_back(run->id);
     c->n_decode++;
     return run->id;
+}
+
+int pib_decode_replay(pib_context * c, int batch_id, int n_tokens, int n_chunks, const uint8_t * descs, size_t desc_stride,
+                      const KvOp * ops, int n_ops) {
+    if (desc_stride != c->desc_stride) { pib_set_error("stage: descriptor stride %zu != %zu (contexts differ in max_seq)", desc_stride, c->desc_stride); return PIB_ERR_ARG; }
+    if (n_tokens == 0) {                                  // KV ops only (pib_kv_sync_replicas on the head)
+        std::vector<KvOp> & q = devq(c);
+        q.insert(q.end(), ops, ops + n_ops);
+        return pib_apply_devops(c);
+    }
+    pib_run * run = take_run(c, n_tokens);
+    if (!run) return PIB_ERR_NOMEM;
+    std::vector<int> slots(n_chunks);
+    for (int ch = 0; ch < n_chunks; ch++) {
+        const int s = take_desc_slot(c);
+        slots[ch]   = s;
+        uint8_t * d = c->desc_host + (size_t) s * c->desc_stride;
+        memcpy(d, descs + (size_t) ch * desc_stride, desc_stride);
+        cudaMemcpyAsync(c->desc_dev + (size_t) s * c->desc_stride, d, c->desc_stride, cudaMemcpyHostToDevice, c->stream);
+        c->h2d_bytes += c->desc_stride;
+    }
+    std::vector<KvOp> & dq = devq(c);
+    for (int i = 0; i < n_ops; i++) {
+        KvOp op = ops[i];
+        if (op.op == KVOP_ALLOC) {
+            if (op.p1 < 0 || op.p1 >= n_chunks) { pib_set_error("stage: bad chunk index in op-log"); return PIB_ERR_ARG; }
+            op.p1 = slots[op.p1];
+        }
+        dq.push_back(op);
+    }
+    return enqueue_decode(c, run, n_tokens, batch_id, slots) >= 0 ? PIB_OK : PIB_ERR_CUDA;
+}
+
+void pib_stage_finish(pib_context * c, int batch_id) {
+    for (auto it = c->inflight.begin(); it != c->inflight.end(); ++it) {
+        pib_run & r = c->runs[*it];
+        if (r.in_use && r.batch_id == batch_id) {
+            cudaMemsetAsync(c->cancel_table + (batch_id & 0xffff), 0, sizeof(int), c->stream);
+            r.in_use = false;
+            c->inflight.erase(it);
+            return;
+        }
+    }
 }
 
 bool pib_run_ready(pib_context * c, int run) {
@@ -588,6 +668,7 @@ int pib_run_finish(pib_context * c, int run) {
     if (cudaEventSynchronize(r.done) != cudaSuccess) { pib_set_error("finish: %s", cudaGetErrorString(cudaGetLastError())); return -1; }
     // the batch id may be reused from here on: drop its cancel flag (ordered after every kernel of the run)
     cudaMemsetAsync(c->cancel_table + (r.batch_id & 0xffff), 0, sizeof(int), c->stream);
+    if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_ints(2, 0, &r.batch_id, 1);
     for (auto it = c->inflight.begin(); it != c->inflight.end(); ++it) if (*it == run) { c->inflight.erase(it); break; }
     r.in_use         = false;
     c->last_finished = run;     // its buffers stay reserved until the next finish (llama_get_logits_ith contract)
@@ -602,7 +683,10 @@ const pib_row_result * pib_last_results(pib_context * c) {
 const float * pib_logits_row(pib_context * c, int i) {
     if (c->last_finished < 0) return nullptr;
     pib_run & r = c->runs[c->last_finished];
-    if (i < 0 || i >= r.n_tokens || !r.logits) return nullptr;
+    if (i < 0 || i >= r.n_tokens || !r.logits) {
+        if (!r.logits) pib_set_error("logits: full rows live on the last pipeline stage; the head receives the top-8 of every row");
+        return nullptr;
+    }
     const size_t V = (size_t) c->model->n_vocab;
     if (c->logits_host.size() < (size_t) r.n_tokens * V) c->logits_host.resize((size_t) r.n_tokens * V);
     if (!c->logits_row_valid[i]) {
@@ -618,9 +702,11 @@ void pib_cancel(pib_context * c, const int32_t * batch_ids, int n) {
     for (int i = 0; i < n; i++)
         if (batch_ids[i] >= 0)
             cudaMemcpyAsync(c->cancel_table + (batch_ids[i] & 0xffff), c->cancel_one, sizeof(int), cudaMemcpyDeviceToDevice, c->ctrl);
+    if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_ints(3, 0, batch_ids, n);
 }
 
 void pib_set_logit_bias(pib_context * c, const int32_t * ids, const float * vals, int n) {
+    if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_bias(ids, vals, n);
     cudaStreamSynchronize(c->stream);
     if (c->bias_ids_dev) cudaFree(c->bias_ids_dev);
     if (c->bias_val_dev) cudaFree(c->bias_val_dev);

@@ -141,4 +141,24 @@ int  pib_run_finish(pib_context * c, int run);                         // waits;
 const pib_row_result * pib_last_results(pib_context * c);
 const float *          pib_logits_row(pib_context * c, int i);         // lazy D2H of one row of the last finished run
 void pib_cancel(pib_context * c, const int32_t * batch_ids, int n);
+// stages > 0: replay one decode record of the head (descriptors + resolved KV op-log) / release a finished run
+int  pib_decode_replay(pib_context * c, int batch_id, int n_tokens, int n_chunks, const uint8_t * descs, size_t desc_stride,
+                       const KvOp * ops, int n_ops);
+void pib_stage_finish(pib_context * c, int batch_id);
+int  pib_apply_devops(pib_context * c);
+int  pib_kv_sync_replicas(pib_context * c);
+
+// pipeline.cu
+bool pib_pipe_ring_active();
+bool pib_pipe_nccl_active();
+void pib_pipe_install_hooks();
+int  pib_pipe_ship_decode(int batch_id, int n_tokens, int n_chunks, const uint8_t * const * descs, size_t desc_stride,
+                          const int * slots, const KvOp * ops, int n_ops);
+int  pib_pipe_ship_ints(int kind, int tag, const int32_t * vals, int n);      // kind: 2 finish, 3 cancel, 5 return, 6 shutdown
+int  pib_pipe_ship_bias(const int32_t * ids, const float * vals, int n);
+int  pib_pipe_send_results(pib_context * c, pib_run & run);
+int  pib_pipe_post_result_recv(pib_context * c, pib_run & run);
+int  pib_stage_serve(pib_context * c);
+extern int (*pib_hop_recv)(pib_context * c, float * x, int n_tokens, const int * cancel);
+extern int (*pib_hop_send)(pib_context * c, const float * x, int n_tokens, const int * cancel);
 void pib_set_logit_bias(pib_context * c, const int32_t * ids, const float * vals, int n);

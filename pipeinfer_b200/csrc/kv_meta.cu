@@ -159,6 +159,30 @@ bool KvMirror::find_slot(int n_tokens_i, const int32_t * tpos, const uint32_t * 
     return true;
 }
 
+// host replay of one device-level op-log record (what kv_apply_kernel does on the replica)
+void KvMirror::apply(const KvOp & op, const int32_t * tpos, const uint32_t * tokbits) {
+    switch (op.op) {
+        case KVOP_CLEAR:   clear(); break;
+        case KVOP_RM:      seq_rm(op.a, op.b, op.p0, op.p1); break;
+        case KVOP_CP:      seq_cp(op.a, op.b, op.pad, op.p0, op.p1); break;
+        case KVOP_KEEP:    seq_keep(op.a); break;
+        case KVOP_SWEEP:   sweep(op.a, op.b, op.p0, op.p1); break;
+        case KVOP_SETHEAD: head = (uint32_t) op.a; break;
+        case KVOP_ALLOC:
+            head = (uint32_t) op.a;
+            for (int i = 0; i < op.b; i++) {
+                pos[head + i] = tpos[i];
+                uint32_t * r = &bits[(size_t) (head + i) * n_words];
+                for (int w = 0; w < n_words; w++) r[w] |= tokbits[(size_t) i * n_words + w];
+            }
+            used += (uint32_t) op.b;
+            n = (uint32_t) op.p0;
+            break;
+        case KVOP_ADVANCE: head += (uint32_t) op.a; if (head >= size) head = 0; break;
+        default: break;
+    }
+}
+
 int32_t KvMirror::cell_max() const {
     for (uint32_t i = size - 1; i > 0; --i)
         if (pos[i] >= 0 && !empty(i)) return (int32_t) (i + 1);
@@ -427,10 +451,7 @@ void kvlog_decode_end(KvMirror & kv, int n_tokens) {
 }
 
 // ---- CPU-only test hooks (no CUDA call): drive the host mirror through the same front end the engine uses -------------
-struct pib_kvtest {
-    KvMirror          kv;
-    std::vector<KvOp> pending, devops;
-};
+void pib_kvtest_ship_decode(pib_kvtest * t, int n_tokens, const int32_t * pos, const uint32_t * tokbits);   // pipeline.cu
 
 extern "C" void * pib_kvtest_new(uint32_t n_ctx, int32_t max_seq) {
     pib_kvtest * t = new pib_kvtest();
@@ -448,6 +469,7 @@ extern "C" int pib_kvtest_decode(void * h, int n_tokens, const int32_t * pos, co
     for (int i = 0; i < n_tokens; i++)
         for (int j = 0; j < n_seq_id[i]; j++) tb[(size_t) i * W + (seq_id[i][j] >> 5)] |= 1u << (seq_id[i][j] & 31);
     if (!kvlog_decode_begin(t->kv, t->devops, n_tokens, pos, tb.data())) return -1;
+    if (t->ship) pib_kvtest_ship_decode(t, n_tokens, pos, tb.data());
     kvlog_decode_end(t->kv, n_tokens);
     return 0;
 }

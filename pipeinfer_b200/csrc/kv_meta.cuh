@@ -56,6 +56,13 @@ struct KvMirror {
     void    apply(const KvOp & op, const int32_t * tpos, const uint32_t * tokbits);
 };
 
+// CPU-only test harness around the mirror and the op-log front end (kv_meta.cu; pipeline.cu for the replicated variant)
+struct pib_kvtest {
+    KvMirror          kv;
+    std::vector<KvOp> pending, devops;
+    bool              ship = false;     // publish every decode's record on the control ring (head of a pipeline)
+};
+
 // device replica
 struct KvDevice {
     int32_t *  pos     = nullptr;   // [size]

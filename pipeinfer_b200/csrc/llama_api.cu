@@ -76,6 +76,30 @@ struct llama_model * llama_pib_synthetic_model(int n_layer, int n_embd, int n_he
     return lm;
 }
 
+// one pipeline stage's share of a model: layers [layer_begin, layer_end), the token embedding on the first stage, the
+// final norm + output matrix on the last (reference: every rank loads the whole file, llama.cpp:2684-2968; here a
+// stage keeps only what it computes with)
+struct llama_model * llama_pib_synthetic_model_slice(int n_layer, int n_embd, int n_head, int n_head_kv, int n_ff, int n_vocab,
+                                                     int wtype, uint64_t seed, int flavour, float agree, int layer_begin,
+                                                     int layer_end, int want_embd, int want_output) {
+    ensure_init();
+    pib_model * m = pib_model_synthetic(n_layer, n_embd, n_head, n_head_kv, n_ff, n_vocab, wtype, seed, flavour, agree, layer_begin,
+                                        layer_end, want_embd != 0, want_output != 0);
+    if (!m) { fprintf(stderr, "llama_pib_synthetic_model_slice: %s\n", pib_last_error()); return nullptr; }
+    llama_model * lm = new llama_model();
+    lm->m = m;
+    return lm;
+}
+
+struct llama_model * llama_pib_load_model_slice(const char * path_model, int layer_begin, int layer_end, int want_embd, int want_output) {
+    ensure_init();
+    pib_model * m = pib_model_load_gguf(path_model, layer_begin, layer_end, want_embd != 0, want_output != 0);
+    if (!m) { fprintf(stderr, "llama_pib_load_model_slice: %s\n", pib_last_error()); return nullptr; }
+    llama_model * lm = new llama_model();
+    lm->m = m;
+    return lm;
+}
+
 void llama_free_model(struct llama_model * model) {
     if (!model) return;
     pib_model_free(model->m);
@@ -83,8 +107,17 @@ void llama_free_model(struct llama_model * model) {
 }
 
 struct llama_context * llama_pib_new_context(struct llama_model * model, uint32_t n_ctx, int32_t max_seq_ids) {
+    return llama_pib_new_context_stage(model, n_ctx, max_seq_ids, 0, 1);
+}
+
+struct llama_context * llama_pib_new_context_stage(struct llama_model * model, uint32_t n_ctx, int32_t max_seq_ids, int rank, int size) {
     if (!model) return nullptr;
     pib_stage st;
+    st.rank = rank; st.size = size < 1 ? 1 : size;
+    if (st.size > 1) {
+        if (!pib_pipe_ring_active() || !pib_pipe_nccl_active()) { fprintf(stderr, "llama_pib_new_context_stage: open the pipeline first (pib_pipe_ring_open + pib_pipe_nccl_init)\n"); return nullptr; }
+        pib_pipe_install_hooks();
+    }
     pib_context * c = pib_context_new(model->m, n_ctx ? n_ctx : (uint32_t) model->m->n_ctx_train, max_seq_ids, st);
     if (!c) { fprintf(stderr, "llama_new_context_with_model: %s\n", pib_last_error()); return nullptr; }
     llama_context * lc = new llama_context();
@@ -101,6 +134,20 @@ struct llama_context * llama_new_context_with_model(struct llama_model * model, 
     llama_context * lc = llama_pib_new_context(model, params.n_ctx, ms ? atoi(ms) : 4096);
     if (lc) lc->c->logits_all = params.logits_all;
     return lc;
+}
+
+int llama_pib_stage_serve(struct llama_context * ctx) { return pib_stage_serve(ctx->c); }
+// head: let every stage drain its stream and return from llama_pib_stage_serve (kind 5), or end for good (kind 6)
+int llama_pib_pipe_pause(struct llama_context * ctx) {
+    if (ctx->c->stage.size < 2) return 0;
+    if (pib_kv_sync_replicas(ctx->c) != PIB_OK) return -1;
+    const int rc = pib_pipe_ship_ints(5, 0, nullptr, 0);
+    cudaStreamSynchronize(ctx->c->stream);
+    return rc;
+}
+int llama_pib_pipe_shutdown(struct llama_context * ctx) {
+    if (ctx->c->stage.size < 2) return 0;
+    return pib_pipe_ship_ints(6, 0, nullptr, 0);
 }
 
 void llama_free(struct llama_context * ctx) {
@@ -387,16 +434,8 @@ int llama_pib_kv_state(struct llama_context * ctx, int from_device, int32_t * sc
         memcpy(bits, c->kv.bits.data(), sizeof(uint32_t) * nb);
         return 0;
     }
-    // ops that were flushed to the mirror but not yet shipped ride with the next decode; push them now
-    if (!c->devops.empty()) {
-        const int n = (int) c->devops.size();
-        if (c->ops_next + n > c->ops_cap) { cudaStreamSynchronize(c->stream); c->ops_next = 0; }
-        memcpy(c->ops_host + c->ops_next, c->devops.data(), sizeof(KvOp) * n);
-        cudaMemcpyAsync(c->ops_dev + c->ops_next, c->ops_host + c->ops_next, sizeof(KvOp) * n, cudaMemcpyHostToDevice, c->stream);
-        kv_device_apply(&c->kvd, c->ops_dev + c->ops_next, n, c->desc_dev, c->desc_stride, c->stream);
-        c->ops_next += n;
-        c->devops.clear();
-    }
+    // ops that were flushed to the mirror but not yet shipped ride with the next decode; push them now (to every stage)
+    if (pib_kv_sync_replicas(c) != PIB_OK) return -1;
     int32_t s[4];
     if (cudaMemcpyAsync(s, c->kvd.scalars, 16, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
         cudaMemcpyAsync(pos, c->kvd.pos, sizeof(int32_t) * c->n_ctx, cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||

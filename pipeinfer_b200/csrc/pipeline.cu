@@ -1,0 +1,572 @@
+// pipeline.cu -- pipeline stages across GPUs: the replacement of the reference's ggml-mpi.c transport.
+//
+// One process per GPU.  Rank 0 is the head: it runs the scheduler and the draft model, owns the first layers of the
+// target, and tells the other stages what to do.  Two channels replace the reference's 21 MPI tags (ggml-mpi.h:15-55):
+//
+//  * control ring -- a single-producer / multi-consumer byte ring in POSIX shared memory (one node).  The head appends
+//    one record per decode (batch descriptors + the resolved KV op-log), per finished run, per cancel, per logit-bias
+//    change; every stage consumes all records in order.  This gives the property the reference gets from per-sender MPI
+//    ordering (ggml-mpi.c:173-234 sync_pipelined): every stage observes every KV op and decode in issue order, so the
+//    KV metadata replicas stay identical.  The stages' HOST code needs these records to enqueue kernels; nothing in
+//    them is read by a GPU of another process, so they do not travel over NVLink.
+//  * data plane -- NCCL send/recv over NVLink, enqueued in the compute stream: activations [n_tokens][n_embd] fp32 to the
+//    next stage (reference ggml_mpi_tensor_send / _recv, ggml-mpi.c:451-503), and the sampled rows (top-8 ids / logits /
+//    probabilities, 96 B per row) from the last stage back to the head (the reference returns n_vocab floats per row,
+//    llama.cpp:5757-5786).  Two communicators so that the head's result receives (own stream) never queue behind its
+//    activation sends.
+//
+// Cancellation (reference GGML_MPI_CANCEL_RUN, llama.cpp:9981-9993): the record reaches every stage's host through the
+// ring and the stage writes its device cancel table from its high-priority stream; kernels of a cancelled run exit at
+// their first instruction, sends and receives still take place (payload ignored) so the pipeline stays in step.
+#include "engine.cuh"
+
+#include <dlfcn.h>
+#include <fcntl.h>
+#include <nccl.h>
+#include <sched.h>
+#include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <sys/time.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <atomic>
+#include <string>
+
+// ---------------------------------------------------------------------------------------------------------------------
+// control ring
+#define PIPE_MAX_RANKS 16
+#define PIPE_MAGIC     0x31424950u
+enum { REC_PAD = 0, REC_DECODE = 1, REC_FINISH = 2, REC_CANCEL = 3, REC_BIAS = 4, REC_RETURN = 5, REC_SHUTDOWN = 6, REC_INTS = 7 };
+
+struct alignas(64) ring_word { std::atomic<uint64_t> v; char pad[56]; };
+struct ring_hdr {
+    ring_word head;                      // bytes published by the head rank (monotonic)
+    ring_word tail[PIPE_MAX_RANKS];      // bytes consumed by each stage
+    ring_word bar_count, bar_gen;        // sense-reversing barrier over all ranks
+    uint64_t  cap;
+    uint32_t  n_ranks;
+    std::atomic<uint32_t> magic;
+};
+struct rec_hdr { uint32_t bytes, kind; };
+struct rec_decode { int32_t batch_id, n_tokens, n_chunks, n_ops; uint32_t desc_stride, pad; };
+
+struct pipe_state {
+    int        rank = 0, size = 1;
+    ring_hdr * h = nullptr;
+    uint8_t *  data = nullptr;
+    size_t     map_bytes = 0;
+    std::string name;
+    uint64_t   wpos = 0;                 // producer cursor
+    uint32_t   open_bytes = 0;           // record being written
+    // NCCL
+    void *     nccl_lib = nullptr;
+    ncclComm_t fwd = nullptr, back = nullptr;
+    cudaStream_t res_stream = nullptr;
+    uint64_t   hop_bytes = 0, hop_msgs = 0, back_bytes = 0;
+    // last int record seen by the ggml_mpi_* shim
+    int        last_tag = -1, last_count = 0;
+};
+static pipe_state P;
+
+static double now_s() { struct timeval tv; gettimeofday(&tv, nullptr); return tv.tv_sec + 1e-6 * tv.tv_usec; }
+
+// spin, then yield; gives up after `PIB_PIPE_TIMEOUT` seconds (default 600) so a dead peer cannot hang a GPU box for ever
+struct spinner {
+    int    n = 0;
+    double t0 = 0;
+    bool   step() {
+        if (++n < 2000) { __builtin_ia32_pause(); return true; }
+        sched_yield();
+        if ((n & 0xfff) == 0) {
+            if (t0 == 0) t0 = now_s();
+            static double limit = getenv("PIB_PIPE_TIMEOUT") ? atof(getenv("PIB_PIPE_TIMEOUT")) : 600.0;
+            if (now_s() - t0 > limit) return false;
+        }
+        return true;
+    }
+};
+
+extern "C" int pib_pipe_ring_open(const char * name, int rank, int n_ranks, size_t cap_bytes) {
+    if (P.h) { pib_set_error("pipe: ring already open"); return PIB_ERR_ARG; }
+    if (n_ranks < 1 || n_ranks > PIPE_MAX_RANKS || rank < 0 || rank >= n_ranks) { pib_set_error("pipe: bad rank %d / %d", rank, n_ranks); return PIB_ERR_ARG; }
+    cap_bytes = (cap_bytes + 4095) & ~(size_t) 4095;
+    const size_t total = 4096 + cap_bytes;
+    static_assert(sizeof(ring_hdr) <= 4096, "ring header must fit its page");
+    int fd = -1;
+    if (rank == 0) {
+        shm_unlink(name);
+        fd = shm_open(name, O_CREAT | O_EXCL | O_RDWR, 0600);
+        if (fd < 0 || ftruncate(fd, (off_t) total) != 0) { pib_set_error("pipe: cannot create shared ring %s", name); if (fd >= 0) close(fd); return PIB_ERR_NOMEM; }
+    } else {
+        spinner sp;
+        while (true) {
+            fd = shm_open(name, O_RDWR, 0600);
+            struct stat st;
+            if (fd >= 0 && fstat(fd, &st) == 0 && (size_t) st.st_size >= total) break;
+            if (fd >= 0) close(fd);
+            usleep(1000);
+            if (!sp.step()) { pib_set_error("pipe: shared ring %s never appeared", name); return PIB_ERR_ARG; }
+        }
+    }
+    void * p = mmap(nullptr, total, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    close(fd);
+    if (p == MAP_FAILED) { pib_set_error("pipe: mmap of %s failed", name); return PIB_ERR_NOMEM; }
+    P.h = (ring_hdr *) p; P.data = (uint8_t *) p + 4096; P.map_bytes = total; P.rank = rank; P.size = n_ranks; P.name = name; P.wpos = 0;
+    if (rank == 0) {
+        P.h->cap = cap_bytes; P.h->n_ranks = (uint32_t) n_ranks;
+        P.h->head.v.store(0); P.h->bar_count.v.store(0); P.h->bar_gen.v.store(0);
+        for (int i = 0; i < PIPE_MAX_RANKS; i++) P.h->tail[i].v.store(0);
+        P.h->magic.store(PIPE_MAGIC, std::memory_order_release);
+    } else {
+        spinner sp;
+        while (P.h->magic.load(std::memory_order_acquire) != PIPE_MAGIC) if (!sp.step()) { pib_set_error("pipe: ring %s never initialised", name); return PIB_ERR_ARG; }
+    }
+    return PIB_OK;
+}
+
+extern "C" int pib_pipe_barrier(void) {
+    if (!P.h) return PIB_OK;
+    const uint64_t gen = P.h->bar_gen.v.load(std::memory_order_acquire);
+    if (P.h->bar_count.v.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint64_t) P.size) {
+        P.h->bar_count.v.store(0, std::memory_order_relaxed);
+        P.h->bar_gen.v.store(gen + 1, std::memory_order_release);
+    } else {
+        spinner sp;
+        while (P.h->bar_gen.v.load(std::memory_order_acquire) == gen) if (!sp.step()) { pib_set_error("pipe: barrier timed out"); return PIB_ERR_ARG; }
+    }
+    return PIB_OK;
+}
+
+extern "C" void pib_pipe_ring_close(void) {
+    if (!P.h) return;
+    pib_pipe_barrier();
+    const bool owner = P.rank == 0;
+    munmap((void *) P.h, P.map_bytes);
+    if (owner) shm_unlink(P.name.c_str());
+    P.h = nullptr; P.data = nullptr; P.size = 1; P.rank = 0;
+}
+
+extern "C" int pib_pipe_rank(void) { return P.rank; }
+extern "C" int pib_pipe_size(void) { return P.size; }
+
+static bool wait_space(uint64_t need) {
+    spinner sp;
+    while (true) {
+        uint64_t mn = UINT64_MAX;
+        for (int r = 1; r < P.size; r++) { const uint64_t t = P.h->tail[r].v.load(std::memory_order_acquire); if (t < mn) mn = t; }
+        if (P.size == 1 || P.wpos + need - mn <= P.h->cap) return true;
+        if (!sp.step()) return false;
+    }
+}
+
+// producer: reserve a record of `payload` bytes; returns the payload pointer (nullptr: ring closed or consumers stuck)
+static uint8_t * rec_begin(uint32_t kind, size_t payload) {
+    if (!P.h || P.rank != 0) return nullptr;
+    const uint64_t need = (sizeof(rec_hdr) + payload + 7) & ~(uint64_t) 7;
+    if (need > P.h->cap / 2) { pib_set_error("pipe: record of %zu bytes does not fit the control ring", payload); return nullptr; }
+    uint64_t pos = P.wpos % P.h->cap;
+    if (P.h->cap - pos < need) {
+        const uint64_t pad = P.h->cap - pos;
+        if (!wait_space(pad)) { pib_set_error("pipe: control ring full (a stage stopped consuming)"); return nullptr; }
+        rec_hdr * ph = (rec_hdr *) (P.data + pos);
+        ph->bytes = (uint32_t) pad; ph->kind = REC_PAD;
+        P.wpos += pad;
+        P.h->head.v.store(P.wpos, std::memory_order_release);
+        pos = 0;
+    }
+    if (!wait_space(need)) { pib_set_error("pipe: control ring full (a stage stopped consuming)"); return nullptr; }
+    rec_hdr * h = (rec_hdr *) (P.data + pos);
+    h->bytes = (uint32_t) need; h->kind = kind;
+    P.open_bytes = (uint32_t) need;
+    return (uint8_t *) (h + 1);
+}
+static void rec_commit() {
+    P.wpos += P.open_bytes;
+    P.open_bytes = 0;
+    P.h->head.v.store(P.wpos, std::memory_order_release);
+}
+
+// consumer: next record (blocking unless `nowait`); PAD records are skipped
+static const rec_hdr * rec_peek(bool nowait) {
+    if (!P.h || P.rank == 0) return nullptr;
+    spinner sp;
+    while (true) {
+        const uint64_t t = P.h->tail[P.rank].v.load(std::memory_order_relaxed);
+        if (P.h->head.v.load(std::memory_order_acquire) == t) {
+            if (nowait) return nullptr;
+            if (!sp.step()) { pib_set_error("pipe: no control record for too long (head gone?)"); return nullptr; }
+            continue;
+        }
+        const rec_hdr * h = (const rec_hdr *) (P.data + t % P.h->cap);
+        if (h->kind == REC_PAD) { P.h->tail[P.rank].v.store(t + h->bytes, std::memory_order_release); continue; }
+        return h;
+    }
+}
+static void rec_pop(const rec_hdr * h) {
+    const uint64_t t = P.h->tail[P.rank].v.load(std::memory_order_relaxed);
+    P.h->tail[P.rank].v.store(t + h->bytes, std::memory_order_release);
+}
+
+// ---- records written by the head (called from engine.cu) -------------------------------------------------------------
+bool pib_pipe_ring_active() { return P.h != nullptr && P.size > 1; }
+
+int pib_pipe_ship_decode(int batch_id, int n_tokens, int n_chunks, const uint8_t * const * descs, size_t desc_stride,
+                         const int * slots, const KvOp * ops, int n_ops) {
+    if (!pib_pipe_ring_active() || P.rank != 0) return PIB_OK;
+    const size_t payload = sizeof(rec_decode) + (size_t) n_chunks * desc_stride + (size_t) n_ops * sizeof(KvOp);
+    uint8_t * p = rec_begin(REC_DECODE, payload);
+    if (!p) return PIB_ERR_NOMEM;
+    rec_decode * d = (rec_decode *) p;
+    d->batch_id = batch_id; d->n_tokens = n_tokens; d->n_chunks = n_chunks; d->n_ops = n_ops; d->desc_stride = (uint32_t) desc_stride; d->pad = 0;
+    uint8_t * q = p + sizeof(rec_decode);
+    for (int ch = 0; ch < n_chunks; ch++, q += desc_stride) memcpy(q, descs[ch], desc_stride);
+    KvOp * o = (KvOp *) q;
+    for (int i = 0; i < n_ops; i++) {
+        o[i] = ops[i];
+        if (o[i].op == KVOP_ALLOC) {                 // descriptor slot of the head -> chunk index inside this record
+            int ch = 0;
+            while (ch < n_chunks && slots[ch] != ops[i].p1) ch++;
+            o[i].p1 = ch;
+        }
+    }
+    rec_commit();
+    return PIB_OK;
+}
+
+int pib_pipe_ship_ints(int kind, int tag, const int32_t * vals, int n) {
+    if (!pib_pipe_ring_active() || P.rank != 0) return PIB_OK;
+    uint8_t * p = rec_begin((uint32_t) kind, sizeof(int32_t) * (size_t) (n + 2));
+    if (!p) return PIB_ERR_NOMEM;
+    int32_t * q = (int32_t *) p;
+    q[0] = tag; q[1] = n;
+    if (n) memcpy(q + 2, vals, sizeof(int32_t) * (size_t) n);
+    rec_commit();
+    return PIB_OK;
+}
+
+int pib_pipe_ship_bias(const int32_t * ids, const float * vals, int n) {
+    if (!pib_pipe_ring_active() || P.rank != 0) return PIB_OK;
+    uint8_t * p = rec_begin(REC_BIAS, sizeof(int32_t) * (size_t) (2 * n + 2));
+    if (!p) return PIB_ERR_NOMEM;
+    int32_t * q = (int32_t *) p;
+    q[0] = 0; q[1] = n;
+    memcpy(q + 2, ids, sizeof(int32_t) * (size_t) n);
+    memcpy(q + 2 + n, vals, sizeof(float) * (size_t) n);
+    rec_commit();
+    return PIB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// NCCL, resolved at run time (the process may already have torch's copy of libnccl.so.2 loaded; dlopen returns that one)
+struct nccl_fns {
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *);
+    ncclResult_t (*CommInitRankConfig)(ncclComm_t *, int, ncclUniqueId, int, ncclConfig_t *);
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int);
+    ncclResult_t (*CommDestroy)(ncclComm_t);
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    ncclResult_t (*GroupStart)(void);
+    ncclResult_t (*GroupEnd)(void);
+    const char * (*GetErrorString)(ncclResult_t);
+};
+static nccl_fns N;
+
+static int nccl_load() {
+    if (P.nccl_lib) return PIB_OK;
+    const char * path = getenv("PIB_NCCL_LIB");
+    void * lib = dlopen(path ? path : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) { pib_set_error("pipe: cannot load NCCL (%s); set PIB_NCCL_LIB", dlerror()); return PIB_ERR_UNSUPP; }
+#define SYM(field, name) do { *(void **) &N.field = dlsym(lib, name); if (!N.field) { pib_set_error("pipe: NCCL symbol %s missing", name); return PIB_ERR_UNSUPP; } } while (0)
+    SYM(GetUniqueId, "ncclGetUniqueId"); SYM(CommInitRank, "ncclCommInitRank"); SYM(CommDestroy, "ncclCommDestroy");
+    SYM(Send, "ncclSend"); SYM(Recv, "ncclRecv"); SYM(GroupStart, "ncclGroupStart"); SYM(GroupEnd, "ncclGroupEnd");
+    SYM(GetErrorString, "ncclGetErrorString");
+#undef SYM
+    *(void **) &N.CommInitRankConfig = dlsym(lib, "ncclCommInitRankConfig");
+    P.nccl_lib = lib;
+    return PIB_OK;
+}
+#define NCCL_CHECK(expr) do { ncclResult_t r__ = (expr); if (r__ != ncclSuccess) { pib_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #expr, N.GetErrorString(r__)); return PIB_ERR_CUDA; } } while (0)
+
+extern "C" int pib_pipe_unique_id(uint8_t * out128) {
+    if (nccl_load() != PIB_OK) return PIB_ERR_UNSUPP;
+    ncclUniqueId id;
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    NCCL_CHECK(N.GetUniqueId(&id));
+    memcpy(out128, &id, 128);
+    return PIB_OK;
+}
+
+// both communicators span all ranks; call after pib_init on every rank, collectively
+extern "C" int pib_pipe_nccl_init(int rank, int size, const uint8_t * id_fwd, const uint8_t * id_back) {
+    if (nccl_load() != PIB_OK) return PIB_ERR_UNSUPP;
+    if (P.h && (P.rank != rank || P.size != size)) { pib_set_error("pipe: NCCL rank/size differ from the control ring's"); return PIB_ERR_ARG; }
+    P.rank = rank; P.size = size;
+    ncclUniqueId a, b;
+    memcpy(&a, id_fwd, 128); memcpy(&b, id_back, 128);
+    // one CTA per transfer: the messages are small (<= 512 KiB) and a receive that waits for the pipeline should not hold
+    // more than one SM slot of the head GPU
+    if (N.CommInitRankConfig) {
+        ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+        cfg.minCTAs = 1; cfg.maxCTAs = 1;
+        NCCL_CHECK(N.CommInitRankConfig(&P.fwd, size, a, rank, &cfg));
+        ncclConfig_t cfg2 = NCCL_CONFIG_INITIALIZER;
+        cfg2.minCTAs = 1; cfg2.maxCTAs = 1;
+        NCCL_CHECK(N.CommInitRankConfig(&P.back, size, b, rank, &cfg2));
+    } else {
+        NCCL_CHECK(N.CommInitRank(&P.fwd, size, a, rank));
+        NCCL_CHECK(N.CommInitRank(&P.back, size, b, rank));
+    }
+    int lo, hi;
+    PIB_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    PIB_CHECK(cudaStreamCreateWithPriority(&P.res_stream, cudaStreamNonBlocking, hi));
+    return PIB_OK;
+}
+
+extern "C" void pib_pipe_nccl_free(void) {
+    if (P.fwd) N.CommDestroy(P.fwd);
+    if (P.back) N.CommDestroy(P.back);
+    if (P.res_stream) cudaStreamDestroy(P.res_stream);
+    P.fwd = P.back = nullptr; P.res_stream = nullptr;
+}
+
+extern "C" void pib_pipe_traffic(uint64_t * hop_bytes, uint64_t * hop_msgs, uint64_t * back_bytes) {
+    if (hop_bytes) *hop_bytes = P.hop_bytes;
+    if (hop_msgs) *hop_msgs = P.hop_msgs;
+    if (back_bytes) *back_bytes = P.back_bytes;
+}
+
+bool pib_pipe_nccl_active() { return P.fwd != nullptr && P.size > 1; }
+
+// engine hooks ---------------------------------------------------------------------------------------------------------
+static int hop_recv(pib_context * c, float * x, int n_tokens, const int * cancel) {
+    (void) cancel;
+    const size_t n = (size_t) n_tokens * c->model->n_embd;
+    NCCL_CHECK(N.Recv(x, n, ncclFloat, P.rank - 1, P.fwd, c->stream));
+    return PIB_OK;
+}
+static int hop_send(pib_context * c, const float * x, int n_tokens, const int * cancel) {
+    (void) cancel;
+    const size_t n = (size_t) n_tokens * c->model->n_embd;
+    NCCL_CHECK(N.Send(x, n, ncclFloat, P.rank + 1, P.fwd, c->stream));
+    P.hop_bytes += n * 4; P.hop_msgs++;
+    return PIB_OK;
+}
+int pib_pipe_send_results(pib_context * c, pib_run & run) {
+    const size_t bytes = sizeof(pib_row_result) * (size_t) run.n_tokens;
+    NCCL_CHECK(N.Send(run.res_dev, bytes, ncclUint8, 0, P.back, c->stream));
+    P.back_bytes += bytes;
+    return PIB_OK;
+}
+int pib_pipe_post_result_recv(pib_context * c, pib_run & run) {
+    const size_t bytes = sizeof(pib_row_result) * (size_t) run.n_tokens;
+    NCCL_CHECK(N.Recv(run.res_dev, bytes, ncclUint8, P.size - 1, P.back, P.res_stream));
+    PIB_CHECK(cudaMemcpyAsync(run.res_host, run.res_dev, bytes, cudaMemcpyDeviceToHost, P.res_stream));
+    c->d2h_bytes += bytes;
+    PIB_CHECK(cudaEventRecord(run.done, P.res_stream));
+    return PIB_OK;
+}
+void pib_pipe_install_hooks() {
+    pib_hop_recv = hop_recv;
+    pib_hop_send = hop_send;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// the stage loop of ranks > 0 (reference worker loop: llama.cpp:9941-9977 llama_process_mpi_worker + the transaction
+// switch at :9944-9976).  Returns 0 when the head paused the pipeline (REC_RETURN; stream drained), 1 on shutdown.
+int pib_stage_serve(pib_context * c) {
+    if (!P.h || P.rank == 0) { pib_set_error("pipe: serve is for ranks > 0 of an open pipeline"); return -1; }
+    while (true) {
+        const rec_hdr * h = rec_peek(false);
+        if (!h) return -1;
+        const uint8_t * p = (const uint8_t *) (h + 1);
+        int rc = PIB_OK, ret = -2;
+        switch (h->kind) {
+            case REC_DECODE: {
+                const rec_decode * d = (const rec_decode *) p;
+                const uint8_t * descs = p + sizeof(rec_decode);
+                const KvOp *    ops   = (const KvOp *) (descs + (size_t) d->n_chunks * d->desc_stride);
+                rc = pib_decode_replay(c, d->batch_id, d->n_tokens, d->n_chunks, descs, d->desc_stride, ops, d->n_ops);
+            } break;
+            case REC_FINISH: { const int32_t * q = (const int32_t *) p; for (int i = 0; i < q[1]; i++) pib_stage_finish(c, q[2 + i]); } break;
+            case REC_CANCEL: { const int32_t * q = (const int32_t *) p; pib_cancel(c, q + 2, q[1]); } break;
+            case REC_BIAS:   { const int32_t * q = (const int32_t *) p; pib_set_logit_bias(c, q + 2, (const float *) (q + 2 + q[1]), q[1]); } break;
+            case REC_INTS:   { const int32_t * q = (const int32_t *) p; P.last_tag = q[0]; P.last_count = q[1]; } break;
+            case REC_RETURN:   ret = 0; break;
+            case REC_SHUTDOWN: ret = 1; break;
+            default: pib_set_error("pipe: unknown control record %u", h->kind); rc = PIB_ERR_ARG;
+        }
+        rec_pop(h);
+        if (rc != PIB_OK) return -1;
+        if (ret >= 0) {
+            if (cudaStreamSynchronize(c->stream) != cudaSuccess) { pib_set_error("pipe: stage stream failed: %s", cudaGetErrorString(cudaGetLastError())); return -1; }
+            return ret;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// CPU-only test hooks: the same records, applied to a host mirror instead of a GPU replica (tests/test_pipeline_cpu.py)
+void pib_kvtest_ship_decode(pib_kvtest * t, int n_tokens, const int32_t * pos, const uint32_t * tokbits) {
+    const int    W = t->kv.n_words, n_chunks = (n_tokens + PIB_CHUNK - 1) / PIB_CHUNK;
+    const size_t stride = pib_desc_stride(W);
+    std::vector<uint8_t>         buf((size_t) n_chunks * stride, 0);
+    std::vector<const uint8_t *> dp(n_chunks);
+    std::vector<int>             slots(n_chunks);
+    const uint32_t head = t->kv.head;
+    for (int ch = 0; ch < n_chunks; ch++) {
+        const int t0 = ch * PIB_CHUNK, nt = std::min(PIB_CHUNK, n_tokens - t0);
+        uint8_t * d  = buf.data() + (size_t) ch * stride;
+        int32_t * hdr = reinterpret_cast<int32_t *>(d + PIB_DESC_HDR_OFF);
+        hdr[PIB_DH_NTOK] = nt; hdr[PIB_DH_KVHEAD] = (int32_t) (head + t0); hdr[PIB_DH_NKV] = (int32_t) t->kv.n;
+        memcpy(d + PIB_DESC_POS_OFF, pos + t0, sizeof(int32_t) * nt);
+        memcpy(d + PIB_DESC_BITS_OFF, tokbits + (size_t) t0 * W, sizeof(uint32_t) * (size_t) nt * W);
+        dp[ch] = d; slots[ch] = ch;
+        t->devops.push_back({ KVOP_ALLOC, (int32_t) (head + t0), nt, (int32_t) t->kv.n, ch, 0 });
+    }
+    t->devops.push_back({ KVOP_ADVANCE, n_tokens, 0, 0, 0, 0 });
+    pib_pipe_ship_decode(0, n_tokens, n_chunks, dp.data(), stride, slots.data(), t->devops.data(), (int) t->devops.size());
+    t->devops.clear();
+}
+
+extern "C" void pib_kvtest_ship(void * h, int enable) { ((pib_kvtest *) h)->ship = enable != 0; }
+// head: publish whatever the op-log still holds (ops issued after the last decode), then let the stages return
+extern "C" int  pib_kvtest_pause(void * hh) {
+    pib_kvtest * t = (pib_kvtest *) hh;
+    if (t) {
+        kvlog_flush(t->kv, t->pending, t->devops);
+        if (!t->devops.empty()) pib_pipe_ship_decode(0, 0, 0, nullptr, pib_desc_stride(t->kv.n_words), nullptr, t->devops.data(), (int) t->devops.size());
+        t->devops.clear();
+    }
+    return pib_pipe_ship_ints(REC_RETURN, 0, nullptr, 0);
+}
+extern "C" int  pib_kvtest_replay(void * hh) {
+    pib_kvtest * t = (pib_kvtest *) hh;
+    while (true) {
+        const rec_hdr * h = rec_peek(false);
+        if (!h) return -1;
+        const uint8_t * p = (const uint8_t *) (h + 1);
+        int ret = -2;
+        if (h->kind == REC_DECODE) {
+            const rec_decode * d = (const rec_decode *) p;
+            const uint8_t * descs = p + sizeof(rec_decode);
+            const KvOp *    ops   = (const KvOp *) (descs + (size_t) d->n_chunks * d->desc_stride);
+            for (int i = 0; i < d->n_ops; i++) {
+                const uint8_t * dd = ops[i].op == KVOP_ALLOC ? descs + (size_t) ops[i].p1 * d->desc_stride : descs;
+                t->kv.apply(ops[i], reinterpret_cast<const int32_t *>(dd + PIB_DESC_POS_OFF), reinterpret_cast<const uint32_t *>(dd + PIB_DESC_BITS_OFF));
+            }
+        } else if (h->kind == REC_RETURN) ret = 0;
+        else if (h->kind == REC_SHUTDOWN) ret = 1;
+        rec_pop(h);
+        if (ret >= 0) return ret;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// layer partition: reference ggml_mpi_split_range (ggml-mpi.c:523-559), called with start = 0, end = n_layer - 1
+// (llama.cpp:8922-8936): range_length = end - start + 1; ranges[i] = [next, min(end, next + w_i * range_length + start)]
+// in float arithmetic truncated to uint16, next = ranges[i][1]; the last stage gets [next, end].  Stage i then runs layers
+// [ranges[i][0], ranges[i][1]) and the last stage runs to the end of the graph (ggml-mpi.c:640-650).
+extern "C" void pib_split_range(int n_stages, int start, int end, const float * weights, uint16_t * out_pairs) {
+    const uint16_t range_length = (uint16_t) (end - start + 1);
+    uint16_t       next_layer   = 0;
+    for (int i = 0; i < n_stages - 1; i++) {
+        out_pairs[2 * i] = next_layer;
+        const float hi = (float) out_pairs[2 * i] + weights[i] * (float) range_length + (float) start;
+        const uint16_t e = (uint16_t) ((float) end < hi ? (float) end : hi);
+        out_pairs[2 * i + 1] = e;
+        next_layer = e;
+    }
+    out_pairs[2 * (n_stages - 1)]     = next_layer;
+    out_pairs[2 * (n_stages - 1) + 1] = (uint16_t) end;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// ggml_mpi_* entry points kept for callers of the reference's transport API (ggml-mpi.h:70-301), mapped onto the ring and
+// NCCL.  Tensors and graphs do not exist here; the graph hooks (graph_creation_post / graph_compute_pre / _post) are what
+// run_chunk does with pib_hop_recv / pib_hop_send.
+struct ggml_mpi_context { int rank, size; int trans_id, recv_trans_id; uint16_t layer_start, layer_end; };
+
+extern "C" {
+void ggml_mpi_backend_init(void) {}                                          // ggml-mpi.c:58 (MPI_Init_thread): the launcher did it
+void ggml_mpi_backend_free(void) {}
+struct ggml_mpi_context * ggml_mpi_init(void) {                              // ggml-mpi.c:67
+    ggml_mpi_context * ctx = new ggml_mpi_context();
+    ctx->rank = P.rank; ctx->size = P.size; ctx->trans_id = 0; ctx->recv_trans_id = 0; ctx->layer_start = 0; ctx->layer_end = 0;
+    return ctx;
+}
+void   ggml_mpi_free(struct ggml_mpi_context * ctx) { delete ctx; }          // :100
+int    ggml_mpi_rank(struct ggml_mpi_context * ctx) { return ctx->rank; }   // :128
+size_t ggml_mpi_size(struct ggml_mpi_context * ctx) { return (size_t) ctx->size; }
+int    ggml_mpi_next_node(struct ggml_mpi_context * ctx) { return (ctx->rank + 1) % ctx->size; }      // :164
+int    ggml_mpi_prev_node(struct ggml_mpi_context * ctx) { const int t = ctx->rank - 1; return t >= 0 ? t : ctx->size - 1; }
+void   ggml_mpi_barrier(struct ggml_mpi_context * ctx) { (void) ctx; pib_pipe_barrier(); }           // :136
+int    ggml_mpi_trans_id(struct ggml_mpi_context * ctx) { return ctx->trans_id; }                     // :38-48
+int    ggml_mpi_recv_trans_id(struct ggml_mpi_context * ctx) { return ctx->recv_trans_id; }
+void   ggml_mpi_inc_trans_id(struct ggml_mpi_context * ctx) { ctx->trans_id++; }
+
+// :349-373: the head publishes `count` ints under `tag`; every other stage receives them in order
+void ggml_mpi_sync_ints_pipelined(struct ggml_mpi_context * ctx, int32_t * vals, int count, int tag) {
+    if (ctx->size < 2) return;
+    if (ctx->rank == 0) { pib_pipe_ship_ints(REC_INTS, tag, vals, count); return; }
+    const rec_hdr * h = rec_peek(false);
+    if (!h || h->kind != REC_INTS) return;
+    const int32_t * q = (const int32_t *) (h + 1);
+    if (q[0] == tag) memcpy(vals, q + 2, sizeof(int32_t) * (size_t) (q[1] < count ? q[1] : count));
+    P.last_tag = q[0]; P.last_count = q[1];
+    rec_pop(h);
+}
+// :140-162
+int ggml_mpi_iprobe(struct ggml_mpi_context * ctx, int src, int tag) {
+    (void) src;
+    if (ctx->rank == 0) return 0;
+    const rec_hdr * h = rec_peek(true);
+    if (!h || h->kind != REC_INTS) return 0;
+    const int32_t * q = (const int32_t *) (h + 1);
+    P.last_tag = q[0]; P.last_count = q[1];
+    return tag < 0 || q[0] == tag;
+}
+void ggml_mpi_probe(struct ggml_mpi_context * ctx, int src, int tag) {
+    (void) src; (void) tag;
+    if (ctx->rank == 0) return;
+    const rec_hdr * h = rec_peek(false);
+    if (h && h->kind == REC_INTS) { const int32_t * q = (const int32_t *) (h + 1); P.last_tag = q[0]; P.last_count = q[1]; }
+}
+int ggml_mpi_status_tag(struct ggml_mpi_context * ctx) { (void) ctx; return P.last_tag; }
+int ggml_mpi_status_count_int32(struct ggml_mpi_context * ctx) { (void) ctx; return P.last_count; }
+
+// :399-421 -- `val` is a DEVICE pointer here; the transfer is enqueued on the NCCL forward communicator's result stream
+void ggml_mpi_send_float_array_async(struct ggml_mpi_context * ctx, float * val, int arr_size, int dest, int tag) {
+    (void) ctx; (void) tag;
+    if (!pib_pipe_nccl_active()) return;
+    N.Send(val, (size_t) arr_size, ncclFloat, dest, P.back, P.res_stream);
+}
+void ggml_mpi_recv_float_array(struct ggml_mpi_context * ctx, float * val, int arr_size, int src, int tag) {
+    (void) ctx; (void) tag;
+    if (!pib_pipe_nccl_active()) return;
+    N.Recv(val, (size_t) arr_size, ncclFloat, src, P.back, P.res_stream);
+    cudaStreamSynchronize(P.res_stream);
+}
+
+// :523-559; the outer array and the rows are malloc'd, the caller frees the outer array (llama.cpp:8934-8936)
+uint16_t ** ggml_mpi_split_range(struct ggml_mpi_context * ctx, uint16_t start, uint16_t end, float node_weights[]) {
+    if (ctx->rank != 0) return nullptr;                                      // only the head computes the split (:536-538)
+    uint16_t ** ranges = (uint16_t **) malloc(sizeof(uint16_t *) * (size_t) ctx->size);
+    std::vector<uint16_t> flat((size_t) ctx->size * 2);
+    pib_split_range(ctx->size, start, end, node_weights, flat.data());
+    for (int i = 0; i < ctx->size; i++) {
+        ranges[i]    = (uint16_t *) malloc(sizeof(uint16_t) * 2);
+        ranges[i][0] = flat[2 * i]; ranges[i][1] = flat[2 * i + 1];
+    }
+    return ranges;
+}
+// :561-589: every stage learns its own range (MPI_Scatter in the reference; here each rank indexes the same table)
+void ggml_mpi_scatter_layers(struct ggml_mpi_context * ctx, uint16_t ** layer_ranges) {
+    int32_t flat[2 * PIPE_MAX_RANKS] = { 0 };
+    if (ctx->rank == 0 && layer_ranges) for (int i = 0; i < ctx->size; i++) { flat[2 * i] = layer_ranges[i][0]; flat[2 * i + 1] = layer_ranges[i][1]; }
+    ggml_mpi_sync_ints_pipelined(ctx, flat, 2 * ctx->size, 7 /* GGML_MPI_TRANSFER_TENSORS slot reused for the layer table */);
+    ctx->layer_start = (uint16_t) flat[2 * ctx->rank]; ctx->layer_end = (uint16_t) flat[2 * ctx->rank + 1];
+}
+void ggml_mpi_layer_range(struct ggml_mpi_context * ctx, uint16_t * start, uint16_t * end) { *start = ctx->layer_start; *end = ctx->layer_end; }
+}
