@@ -348,10 +348,11 @@ pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_st
     c->cancel_one = c->cancel_table + 65536;
     { int one = 1; CK(cudaMemcpy(c->cancel_one, &one, 4, cudaMemcpyHostToDevice)); }
     c->desc_stride = pib_desc_stride(c->n_words);
-    c->desc_slots  = 256;
-    CK(cudaMallocHost(&c->desc_host, c->desc_stride * c->desc_slots));
-    CK(cudaMalloc(&c->desc_dev, c->desc_stride * c->desc_slots));
-    c->desc_ev.assign(c->desc_slots, nullptr);
+    c->desc_slots  = 256;                  // ring; slots [256, 256 + 64) are bound to the run slots (single-chunk decodes)
+    CK(cudaMallocHost(&c->desc_host, c->desc_stride * (c->desc_slots + 64)));
+    CK(cudaMalloc(&c->desc_dev, c->desc_stride * (c->desc_slots + 64)));
+    c->desc_ev.assign(c->desc_slots + 64, nullptr);
+    { const char * g = getenv("PIB_GRAPHS"); c->use_graphs = !g || atoi(g) != 0; }
     c->ops_cap = 1 << 16;
     CK(cudaMallocHost(&c->ops_host, sizeof(KvOp) * c->ops_cap));
     CK(cudaMalloc(&c->ops_dev, sizeof(KvOp) * c->ops_cap));
@@ -379,6 +380,7 @@ void pib_context_free(pib_context * c) {
         if (r.res_host) cudaFreeHost(r.res_host);
     }
     for (auto e : c->desc_ev) if (e) cudaEventDestroy(e);
+    for (auto & g : c->graphs) if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->ctrl) cudaStreamDestroy(c->ctrl);
     delete c;
@@ -392,9 +394,10 @@ static std::vector<KvOp> & devq(pib_context * c) { return c->devops; }
 
 // ---------------------------------------------------------------------------------------------------------------------
 // decode
-static int take_desc_slot(pib_context * c) {
-    const int s = c->desc_next;
-    c->desc_next = (c->desc_next + 1) % c->desc_slots;
+static int take_desc_slot(pib_context * c, const pib_run * run, int n_chunks) {
+    int s;
+    if (run && n_chunks == 1) s = c->desc_slots + run->id;        // fixed address per run slot (see run_chunk)
+    else { s = c->desc_next; c->desc_next = (c->desc_next + 1) % c->desc_slots; }
     if (c->desc_ev[s]) cudaEventSynchronize(c->desc_ev[s]);
     else cudaEventCreateWithFlags(&c->desc_ev[s], cudaEventDisableTiming);
     return s;
@@ -411,12 +414,11 @@ __global__ void add_kernel(const float * __restrict__ a, const float * __restric
 int (*pib_hop_recv)(pib_context * c, float * x, int n_tokens, const int * cancel) = nullptr;
 int (*pib_hop_send)(pib_context * c, const float * x, int n_tokens, const int * cancel) = nullptr;
 
-static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int slot) {
+static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, int slot, const int * cancel) {
     pib_model *    m    = c->model;
     const int      E = m->n_embd, GQA = m->n_embd_gqa(), FF = m->n_ff, hd = m->head_dim(), wt = m->wtype, var = c->gemv_variant;
     cudaStream_t   st   = c->stream;
     const uint8_t * desc = c->desc_dev + (size_t) slot * c->desc_stride;
-    const int *    cancel = c->cancel_table + (run.batch_id & 0xffff);
     const int32_t * tok  = reinterpret_cast<const int32_t *>(desc + PIB_DESC_TOK_OFF);
     const int32_t * tpos = reinterpret_cast<const int32_t *>(desc + PIB_DESC_POS_OFF);
     const uint32_t * tbits = reinterpret_cast<const uint32_t *>(desc + PIB_DESC_BITS_OFF);
@@ -424,7 +426,7 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
 #define RC(e) do { rc = (e); if (rc != PIB_OK) return rc; c->n_kernels++; } while (0)
     // matmul launch, optionally bracketed by events (kind: 0 qkv, 1 o, 2 gate|up, 3 down, 4 lm_head)
 #define GEMV(kind, il_, w, out) do {                                                                                   \
-        const bool pr__ = (il_) == c->prof_layer && c->prof.size() < 8192;                                             \
+        const bool pr__ = c->prof_now && (il_) == c->prof_layer && c->prof.size() < 8192;                                             \
         pib_context::ProfRec r__ = { (kind), ntok, nullptr, nullptr };                                                 \
         if (pr__) { cudaEventCreate(&r__.e0); cudaEventCreate(&r__.e1); cudaEventRecord(r__.e0, st); }                 \
         RC(pib_gemv_internal((w), c->act, ntok, (out), var, cancel, st));                                              \
@@ -434,7 +436,7 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
     // any other launch of the profiled layer, bracketed the same way (kind: 5 attn-norm+quant, 6 rope+kv store, 7 attention,
     // 8 quant of the attention output, 9 residual+ffn-norm+quant, 10 silu*up+quant)
 #define TL(kind, il_, call) do {                                                                                       \
-        const bool pr__ = (il_) == c->prof_layer && c->prof.size() < 8192;                                             \
+        const bool pr__ = c->prof_now && (il_) == c->prof_layer && c->prof.size() < 8192;                                             \
         pib_context::ProfRec r__ = { (kind), ntok, nullptr, nullptr };                                                 \
         if (pr__) { cudaEventCreate(&r__.e0); cudaEventCreate(&r__.e1); cudaEventRecord(r__.e0, st); }                 \
         RC(call);                                                                                                      \
@@ -442,7 +444,6 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
     } while (0)
     RC(kv_device_mask(&c->kvd, tpos, tbits, ntok, c->mask, st));
     if (c->stage.first()) RC(pib_get_rows(m->tok_embd, tok, ntok, c->x, st));
-    else if (pib_hop_recv) RC(pib_hop_recv(c, c->x, ntok, cancel));
     // x holds layer_inp; `pending_add` = a down-projection result still to be added to x2 (ffn_inp) to form the next x
     bool pending_add = false;
     for (int il = m->layer_begin; il < m->layer_end; il++) {
@@ -475,11 +476,52 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
             add_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(c->proj, c->x2, c->x, n, cancel);
             c->n_kernels++;
         }
-        if (pib_hop_send) RC(pib_hop_send(c, c->x, ntok, cancel));
     }
 #undef TL
 #undef GEMV
 #undef RC
+    return PIB_OK;
+}
+
+// One chunk on this stage: receive the activations (stages > 0), run the layers, send them on (stages < last).  The
+// layer part of a single-chunk decode is replayed from a CUDA graph captured on the second use of its (run slot, n_tokens)
+// pair: every address a kernel gets is fixed per run slot (descriptor slot, cancel word, logits and result rows) and
+// everything that varies between decodes lives in the descriptor, which is device memory.  One graph launch replaces
+// ~10 launches per layer on the host, which is what bounds the small draft model.
+static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int slot) {
+    const int * cancel = c->cancel_table + run.id;
+    int rc;
+    if (!c->stage.first() && pib_hop_recv && (rc = pib_hop_recv(c, c->x, ntok, cancel)) != PIB_OK) return rc;
+    // per-launch event timing (bench.py roofline) samples one decode in eight, launched directly; the others keep their graphs
+    c->prof_now = c->prof_layer >= 0 && (c->n_decode & 7) == 0;
+    const bool graphable = c->use_graphs && !c->prof_now && slot >= c->desc_slots;          // reserved slot <=> single-chunk decode
+    bool done = false;
+    if (graphable) {
+        pib_context::GraphEntry & g = c->graphs[run.id * 32 + ntok];
+        g.uses++;
+        if (!g.exec && !g.failed && g.uses >= 2 && c->graphs.size() <= 512) {
+            const uint64_t k0 = c->n_kernels;
+            cudaGraph_t graph = nullptr;
+            bool ok = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeRelaxed) == cudaSuccess;
+            if (ok) {
+                rc = run_chunk_body(c, run, chunk, ntok, slot, cancel);
+                ok = cudaStreamEndCapture(c->stream, &graph) == cudaSuccess && rc == PIB_OK && graph != nullptr;
+            }
+            if (ok) ok = cudaGraphInstantiate(&g.exec, graph, 0) == cudaSuccess;
+            if (graph) cudaGraphDestroy(graph);
+            g.n_kernels = (int) (c->n_kernels - k0);
+            c->n_kernels = k0;
+            if (!ok) { cudaGetLastError(); g.exec = nullptr; g.failed = true; }
+        }
+        if (g.exec) {
+            if (cudaGraphLaunch(g.exec, c->stream) != cudaSuccess) { pib_set_error("decode: graph launch failed: %s", cudaGetErrorString(cudaGetLastError())); return PIB_ERR_CUDA; }
+            c->n_kernels += (uint64_t) g.n_kernels;
+            c->n_graph_launches++;
+            done = true;
+        }
+    }
+    if (!done && (rc = run_chunk_body(c, run, chunk, ntok, slot, cancel)) != PIB_OK) return rc;
+    if (!c->stage.last() && pib_hop_send && (rc = pib_hop_send(c, c->x, ntok, cancel)) != PIB_OK) return rc;
     return PIB_OK;
 }
 
@@ -535,7 +577,7 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
     std::vector<int> slots(n_chunks);
     for (int ch = 0; ch < n_chunks; ch++) {
         const int t0 = ch * PIB_CHUNK, nt = std::min(PIB_CHUNK, n_tokens - t0);
-        const int s  = take_desc_slot(c);
+        const int s  = take_desc_slot(c, run, n_chunks);
         slots[ch]    = s;
         uint8_t * d  = c->desc_host + (size_t) s * c->desc_stride;
         int32_t * hdr = reinterpret_cast<int32_t *>(d + PIB_DESC_HDR_OFF);
@@ -626,7 +668,7 @@ int pib_decode_replay(pib_context * c, int batch_id, int n_tokens, int n_chunks,
     if (!run) return PIB_ERR_NOMEM;
     std::vector<int> slots(n_chunks);
     for (int ch = 0; ch < n_chunks; ch++) {
-        const int s = take_desc_slot(c);
+        const int s = take_desc_slot(c, run, n_chunks);
         slots[ch]   = s;
         uint8_t * d = c->desc_host + (size_t) s * c->desc_stride;
         memcpy(d, descs + (size_t) ch * desc_stride, desc_stride);
@@ -649,7 +691,7 @@ void pib_stage_finish(pib_context * c, int batch_id) {
     for (auto it = c->inflight.begin(); it != c->inflight.end(); ++it) {
         pib_run & r = c->runs[*it];
         if (r.in_use && r.batch_id == batch_id) {
-            cudaMemsetAsync(c->cancel_table + (batch_id & 0xffff), 0, sizeof(int), c->stream);
+            cudaMemsetAsync(c->cancel_table + r.id, 0, sizeof(int), c->stream);
             r.in_use = false;
             c->inflight.erase(it);
             return;
@@ -666,8 +708,8 @@ int pib_run_finish(pib_context * c, int run) {
     if (run < 0 || run >= (int) c->runs.size() || !c->runs[run].in_use) { pib_set_error("finish: bad run handle"); return -1; }
     pib_run & r = c->runs[run];
     if (cudaEventSynchronize(r.done) != cudaSuccess) { pib_set_error("finish: %s", cudaGetErrorString(cudaGetLastError())); return -1; }
-    // the batch id may be reused from here on: drop its cancel flag (ordered after every kernel of the run)
-    cudaMemsetAsync(c->cancel_table + (r.batch_id & 0xffff), 0, sizeof(int), c->stream);
+    // the run slot may be reused from here on: drop its cancel flag (ordered after every kernel of the run)
+    cudaMemsetAsync(c->cancel_table + r.id, 0, sizeof(int), c->stream);
     if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_ints(2, 0, &r.batch_id, 1);
     for (auto it = c->inflight.begin(); it != c->inflight.end(); ++it) if (*it == run) { c->inflight.erase(it); break; }
     r.in_use         = false;
@@ -699,15 +741,22 @@ const float * pib_logits_row(pib_context * c, int i) {
 }
 
 void pib_cancel(pib_context * c, const int32_t * batch_ids, int n) {
+    // one cancel word per run slot (fixed addresses, so that captured graphs of a slot stay valid); the word is cleared when
+    // the run is finished, in stream order after its last kernel
     for (int i = 0; i < n; i++)
-        if (batch_ids[i] >= 0)
-            cudaMemcpyAsync(c->cancel_table + (batch_ids[i] & 0xffff), c->cancel_one, sizeof(int), cudaMemcpyDeviceToDevice, c->ctrl);
+        for (int id : c->inflight) {
+            pib_run & r = c->runs[id];
+            if (r.in_use && r.batch_id == batch_ids[i])
+                cudaMemcpyAsync(c->cancel_table + r.id, c->cancel_one, sizeof(int), cudaMemcpyDeviceToDevice, c->ctrl);
+        }
     if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_ints(3, 0, batch_ids, n);
 }
 
 void pib_set_logit_bias(pib_context * c, const int32_t * ids, const float * vals, int n) {
     if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_bias(ids, vals, n);
     cudaStreamSynchronize(c->stream);
+    for (auto & g : c->graphs) if (g.second.exec) cudaGraphExecDestroy(g.second.exec);       // they hold the old bias pointers
+    c->graphs.clear();
     if (c->bias_ids_dev) cudaFree(c->bias_ids_dev);
     if (c->bias_val_dev) cudaFree(c->bias_val_dev);
     c->bias_ids_dev = nullptr; c->bias_val_dev = nullptr; c->n_bias = 0;

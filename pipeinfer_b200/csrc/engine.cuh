@@ -7,6 +7,7 @@
 #include "kv_meta.cuh"
 
 #include <deque>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -118,8 +119,14 @@ struct pib_context {
     // optional per-launch timing of the matmuls of one layer (bench.py roofline): CUDA events on the launching stream
     struct ProfRec { int kind, b; cudaEvent_t e0, e1; };
     int                  prof_layer = -1;
+    bool                 prof_now   = false;
     std::vector<ProfRec> prof;
     uint64_t             n_decode  = 0;
+    // CUDA graphs of single-chunk decodes, keyed by run slot * 32 + n_tokens (engine.cu: run_chunk)
+    struct GraphEntry { cudaGraphExec_t exec = nullptr; int uses = 0; int n_kernels = 0; bool failed = false; };
+    std::map<int, GraphEntry> graphs;
+    bool                 use_graphs = true;
+    uint64_t             n_graph_launches = 0;
     int64_t              t_start_us = 0;
 };
 

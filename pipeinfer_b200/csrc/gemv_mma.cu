@@ -19,6 +19,9 @@
 // k-slot 16+4t+i <-> element 8t+4+i" (the activations use the same permutation, so every B fragment is one contiguous
 // 8-byte load).  Then the 16 row headers {fp16 d, fp16 dmin, scales[12]}.  2304 bytes per (T, S), consecutive S
 // contiguous: every warp-wide load instruction reads 512 contiguous bytes.
+#include <map>
+#include <mutex>
+#include <utility>
 #include "pib_common.cuh"
 
 #define MM_WARPS   4
@@ -482,23 +485,30 @@ gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K
 }
 
 // ---- launcher -----------------------------------------------------------------------------------------------------------
-// scratch for the k-split path: partial sums [split][b][N] + one counter per row tile; owned by the caller (the engine
-// keeps one per context; the stateless C ABI allocates it per device on first use)
-struct mm_scratch { float * partial; unsigned int * counters; size_t partial_floats; size_t n_counters; };
-static mm_scratch g_scratch[16];
+// scratch for the k-split path: partial sums [split][b][N] + one counter per row tile.  One set per (device, stream):
+// launches on one stream are serialised, so they can share it; two contexts (target and draft) running on their own
+// streams at the same time must not.  Allocated on first use, grown on demand, never shrunk.
+struct mm_scratch { float * partial = nullptr; unsigned int * counters = nullptr; size_t partial_floats = 0; size_t n_counters = 0; };
+static std::map<std::pair<int, cudaStream_t>, mm_scratch> g_scratch;
+static std::mutex                                        g_scratch_mu;
 
-static int ensure_scratch(size_t floats, size_t counters, mm_scratch ** out) {
+static int ensure_scratch(size_t floats, size_t counters, cudaStream_t st, mm_scratch ** out) {
     int dev = 0;
     cudaGetDevice(&dev);
-    mm_scratch & s = g_scratch[dev & 15];
+    std::lock_guard<std::mutex> lock(g_scratch_mu);
+    mm_scratch & s = g_scratch[std::make_pair(dev, st)];
+    // sized once for every shape the split rules can produce (a split is used only while tiles x splits stays below a few
+    // CTAs per SM): captured CUDA graphs keep these addresses, so growing later must not happen in practice
+    if (floats < ((size_t) 1 << 20)) floats = (size_t) 1 << 20;
+    if (counters < 4096) counters = 4096;
     if (s.partial_floats < floats) {
-        if (s.partial) cudaFree(s.partial);
+        if (s.partial) { cudaStreamSynchronize(st); cudaFree(s.partial); }
         s.partial = nullptr; s.partial_floats = 0;
         if (cudaMalloc(&s.partial, floats * sizeof(float)) != cudaSuccess) { cudaGetLastError(); return PIB_ERR_NOMEM; }
         s.partial_floats = floats;
     }
     if (s.n_counters < counters) {
-        if (s.counters) cudaFree(s.counters);
+        if (s.counters) { cudaStreamSynchronize(st); cudaFree(s.counters); }
         s.counters = nullptr; s.n_counters = 0;
         if (cudaMalloc(&s.counters, counters * sizeof(unsigned int)) != cudaSuccess) { cudaGetLastError(); return PIB_ERR_NOMEM; }
         cudaMemset(s.counters, 0, counters * sizeof(unsigned int));
@@ -576,7 +586,7 @@ int pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y
     const int split = choose_split_direct(n_tiles, nsb);
     mm_scratch * s = nullptr;
     if (split > 1) {
-        if (ensure_scratch((size_t) split * b * w->N, (size_t) n_tiles, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
+        if (ensure_scratch((size_t) split * b * w->N, (size_t) n_tiles, st, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
     }
     return pib_gemv_direct_launch(w, act_dev, b, y_dev, split, s ? s->partial : nullptr, s ? s->counters : nullptr, cancel, st);
 }
@@ -588,7 +598,7 @@ int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_de
     const int split = choose_lg_split(n_tiles, nsb);
     mm_scratch * s = nullptr;
     if (split > 0) {
-        if (ensure_scratch(((size_t) b << split) * w->N, (size_t) n_tiles, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
+        if (ensure_scratch(((size_t) b << split) * w->N, (size_t) n_tiles, st, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
     }
     return pib_gemv_mma_launch(w, act_dev, b, y_dev, split, s ? s->partial : nullptr, s ? s->counters : nullptr, cancel, st);
 }
