@@ -58,6 +58,8 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
                                                                const uint16_t * __restrict__ lut,
                                                                const float * __restrict__ addend, float * sum_out,
                                                                const int * __restrict__ cancel, int64_t xstride) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
     if (cancel && *cancel) return;
     const int     row  = blockIdx.x;
     const float * xr   = x + (size_t) row * xstride;
@@ -197,8 +199,8 @@ static int launch_aq(int wtype, const float * x, const float * x2, int x2_per_ro
     const int64_t units = wtype == PIB_TYPE_Q4_K ? K / PIB_QK_K : K / PIB_QK / 4;        // super-blocks, or groups of 4 blocks
     const int     parts = (int) max((int64_t) 1, min((int64_t) 32, units / (AQ_THREADS / 32)));
     const dim3    grid(b, parts);
-    if (wtype == PIB_TYPE_Q4_K) act_quant_kernel<true, PRO><<<grid, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride);
-    else                        act_quant_kernel<false, PRO><<<grid, AQ_THREADS, 0, st>>>(x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride);
+    if (wtype == PIB_TYPE_Q4_K) pib_launch(act_quant_kernel<true, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride);
+    else                        pib_launch(act_quant_kernel<false, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }

@@ -47,6 +47,8 @@ __global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8
                                      __half * __restrict__ q16, __half * __restrict__ kcache, __half * __restrict__ vcache,
                                      const int * __restrict__ cancel) {
     const int32_t * hdr = reinterpret_cast<const int32_t *>(desc + PIB_DESC_HDR_OFF);
+    pib_pdl_wait();
+    pib_pdl_trigger();
     if (cancel && *cancel) return;
     const int       t    = blockIdx.x;
     const int       pos  = reinterpret_cast<const int32_t *>(desc + PIB_DESC_POS_OFF)[t];
@@ -90,6 +92,8 @@ __global__ void __launch_bounds__(ATT_THREADS) attention_kernel(const __half * _
                                                                 const uint8_t * __restrict__ desc, const uint16_t * __restrict__ exp_lut,
                                                                 int E, int GQA, int n_ctx, float kq_scale, float * __restrict__ out,
                                                                 const int * __restrict__ cancel, int gdiv) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
     if (cancel && *cancel) return;
     (void) desc;
     extern __shared__ float smem[];
@@ -213,6 +217,8 @@ __global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half 
                                                                    const int32_t * __restrict__ scalars, const uint16_t * __restrict__ exp_lut,
                                                                    int E, int GQA, int n_ctx, float kq_scale, float * __restrict__ out,
                                                                    const int * __restrict__ cancel, int gdiv) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
     if (cancel && *cancel) return;
     extern __shared__ float smem[];
     __shared__ float  sq[HD];
@@ -311,7 +317,7 @@ template <int HD>
 static int launch_att_qh(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
                          int E, int GQA, int n_ctx, int n_tokens, int n_head, int gdiv, float * out, const int * cancel, cudaStream_t st) {
     const size_t smem = (size_t) std::max(n_ctx, (ATQ_THREADS / (HD / 2)) * HD) * sizeof(float);
-    attention_qh_kernel<HD><<<dim3(n_head, n_tokens), ATQ_THREADS, smem, st>>>(q16, kc, vc, mask, scalars, pib_get_luts().exp_f16, E, GQA,
+    pib_launch(attention_qh_kernel<HD>, dim3(n_head, n_tokens), dim3(ATQ_THREADS), smem, st, q16, kc, vc, mask, scalars, pib_get_luts().exp_f16, E, GQA,
                                                                                n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
@@ -327,7 +333,7 @@ static int launch_att(const __half * q16, const __half * kc, const __half * vc, 
         PIB_CHECK(cudaFuncSetAttribute(attention_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         configured = smem;
     }
-    attention_kernel<HD, G><<<dim3(n_blocks_x, n_tokens), ATT_THREADS, smem, st>>>(
+    pib_launch(attention_kernel<HD, G>, dim3(n_blocks_x, n_tokens), dim3(ATT_THREADS), smem, st, 
         q16, kc, vc, mask, scalars, desc, pib_get_luts().exp_f16, E, GQA, n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
@@ -336,7 +342,7 @@ static int launch_att(const __half * q16, const __half * kc, const __half * vc, 
 int pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * rope, int rope_n_pos, int n_tokens, int E, int GQA,
                       int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st) {
     const int parts = max(1, min(16, (E / 2 + GQA / 2 + 511) / 512));
-    rope_kv_store_kernel<<<dim3(n_tokens, parts), 256, 0, st>>>(qkv, desc, rope, rope_n_pos, E, GQA, hd, mode, q16, kc, vc, cancel);
+    pib_launch(rope_kv_store_kernel, dim3(n_tokens, parts), dim3(256), 0, st, qkv, desc, rope, rope_n_pos, E, GQA, hd, mode, q16, kc, vc, cancel);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }

@@ -405,6 +405,8 @@ static int take_desc_slot(pib_context * c, const pib_run * run, int n_chunks) {
 
 __global__ void add_kernel(const float * __restrict__ a, const float * __restrict__ b, float * __restrict__ o, int64_t n,
                            const int * __restrict__ cancel) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
     if (cancel && *cancel) return;
     const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) o[i] = __fadd_rn(a[i], b[i]);
@@ -473,7 +475,7 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
     } else {
         if (pending_add) {
             const int64_t n = (int64_t) ntok * E;
-            add_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(c->proj, c->x2, c->x, n, cancel);
+            pib_launch(add_kernel, dim3((unsigned) ((n + 255) / 256)), dim3(256), 0, st, c->proj, c->x2, c->x, n, cancel);
             c->n_kernels++;
         }
     }

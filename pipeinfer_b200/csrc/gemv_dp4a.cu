@@ -29,6 +29,8 @@ template <int B>
 __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q8_0_kernel(const int8_t * __restrict__ wqs, const uint16_t * __restrict__ wd,
                                                                   const int8_t * __restrict__ aqs, const float * __restrict__ ad,
                                                                   float * __restrict__ y, int N, int K, const int * __restrict__ cancel) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
     if (cancel && *cancel) return;
     const int lane = threadIdx.x & 31;
     const int row  = blockIdx.x * GV_WARPS + (threadIdx.x >> 5);
@@ -63,6 +65,8 @@ template <int B>
 __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q4_0_kernel(const uint8_t * __restrict__ wqs, const uint16_t * __restrict__ wd,
                                                                   const int8_t * __restrict__ aqs, const float * __restrict__ ad,
                                                                   float * __restrict__ y, int N, int K, const int * __restrict__ cancel) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
     if (cancel && *cancel) return;
     const int lane = threadIdx.x & 31;
     const int row  = blockIdx.x * GV_WARPS + (threadIdx.x >> 5);
@@ -114,6 +118,8 @@ __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q4_K_kernel(const uint8_t 
                                                                   const int8_t * __restrict__ aqs, const float * __restrict__ ad,
                                                                   const int16_t * __restrict__ absum, float * __restrict__ y,
                                                                   int N, int K, const int * __restrict__ cancel) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
     if (cancel && *cancel) return;
     const int lane = threadIdx.x & 31;
     const int row  = blockIdx.x * GV_WARPS + (threadIdx.x >> 5);
@@ -174,14 +180,14 @@ static void launch_b(const pib_weight * w, const uint8_t * act, const pib_act_la
     (void) b_total;
     if (w->type == PIB_TYPE_Q8_0) {
         const float * ad = (const float *) (act + L.d_off) + (size_t) t0 * (K / 32);
-        gemv_q8_0_kernel<B><<<grid, block, 0, st>>>((const int8_t *) w->qs, w->d, aqs, ad, yo, N, K, cancel);
+        pib_launch(gemv_q8_0_kernel<B>, grid, block, 0, st, (const int8_t *) w->qs, w->d, aqs, ad, yo, N, K, cancel);
     } else if (w->type == PIB_TYPE_Q4_0) {
         const float * ad = (const float *) (act + L.d_off) + (size_t) t0 * (K / 32);
-        gemv_q4_0_kernel<B><<<grid, block, 0, st>>>(w->qs, w->d, aqs, ad, yo, N, K, cancel);
+        pib_launch(gemv_q4_0_kernel<B>, grid, block, 0, st, w->qs, w->d, aqs, ad, yo, N, K, cancel);
     } else {
         const float *   ad = (const float *) (act + L.d_off) + (size_t) t0 * (K / 256);
         const int16_t * bs = (const int16_t *) (act + L.bs_off) + (size_t) t0 * (K / 16);
-        gemv_q4_K_kernel<B><<<grid, block, 0, st>>>(w->qs, (const uint8_t *) w->d, aqs, ad, bs, yo, N, K, cancel);
+        pib_launch(gemv_q4_K_kernel<B>, grid, block, 0, st, w->qs, (const uint8_t *) w->d, aqs, ad, bs, yo, N, K, cancel);
     }
 }
 

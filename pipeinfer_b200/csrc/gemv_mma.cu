@@ -340,7 +340,7 @@ __global__ void __launch_bounds__(MM_THREADS, NT == 1 ? 4 : 3)
 gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, const int8_t * __restrict__ aqs,
                        const float * __restrict__ ad, const int8_t * __restrict__ abs8, int b, float * __restrict__ y,
                        float * __restrict__ partial, unsigned int * __restrict__ counters, const int * __restrict__ cancel) {
-    if (cancel && *cancel) return;
+    if (cancel && *cancel) { pib_pdl_wait(); return; }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
     const int T = blockIdx.x;
     const int nsplit = gridDim.y, split = blockIdx.y;
@@ -372,6 +372,9 @@ gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K
         hq[0] = ld_stream_v4(hbase + (size_t) s * MM_TILE_BYTES);
         hq[1] = ld_stream_v4(hbase + (size_t) s * MM_TILE_BYTES + 128);
     }
+    // the weights above are immutable, so their loads were issued before waiting for the kernel that produces the activations
+    pib_pdl_wait();
+    pib_pdl_trigger();
     for (; s < sb1; s += MM_WARPS) {
         int4 wn[4], hn[2];
         const int sn = s + MM_WARPS;
@@ -550,8 +553,8 @@ int pib_gemv_direct_launch(const pib_weight * w, const void * act_dev, int b, fl
     const int8_t *       aqs = (const int8_t *) (act + L.qsp_off);
     const float *        ad  = (const float *) (act + L.d_off);
     const int8_t *       bs  = (const int8_t *) (act + L.bs8_off);
-    if (b <= 8) gemv_q4k_direct_kernel<1><<<grid, MM_THREADS, 0, st>>>(w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev, partial, counters, cancel);
-    else        gemv_q4k_direct_kernel<2><<<grid, MM_THREADS, 0, st>>>(w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev, partial, counters, cancel);
+    if (b <= 8) pib_launch(gemv_q4k_direct_kernel<1>, grid, dim3(MM_THREADS), 0, st, w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev, partial, counters, cancel);
+    else        pib_launch(gemv_q4k_direct_kernel<2>, grid, dim3(MM_THREADS), 0, st, w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev, partial, counters, cancel);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }

@@ -333,6 +333,8 @@ __global__ void __launch_bounds__(KVT) kv_apply_kernel(int32_t * __restrict__ po
 __global__ void kv_mask_kernel(const int32_t * __restrict__ pos, const uint32_t * __restrict__ bits,
                                const int32_t * __restrict__ scalars, int W, const int32_t * __restrict__ tpos,
                                const uint32_t * __restrict__ tokbits, int n_ctx, uint8_t * __restrict__ mask) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
     const int t  = blockIdx.y;
     const int n  = scalars[2];
     const int tp = tpos[t];
@@ -376,7 +378,7 @@ int kv_device_apply(const KvDevice * kv, const KvOp * ops_dev, int n_ops, const 
 int kv_device_mask(const KvDevice * kv, const int32_t * tpos_dev, const uint32_t * tokbits_dev, int n_tokens,
                    uint8_t * mask_dev, cudaStream_t st) {
     dim3 grid((kv->size + 255) / 256, n_tokens);
-    kv_mask_kernel<<<grid, 256, 0, st>>>(kv->pos, kv->bits, kv->scalars, kv->n_words, tpos_dev, tokbits_dev,
+    pib_launch(kv_mask_kernel, grid, dim3(256), 0, st, kv->pos, kv->bits, kv->scalars, kv->n_words, tpos_dev, tokbits_dev,
                                           (int) kv->size, mask_dev);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;

@@ -71,6 +71,12 @@ const pib_luts & pib_get_luts() {
     return g_luts[dev];
 }
 
+bool pib_pdl_enabled() {
+    static int on = -1;
+    if (on < 0) { const char * e = getenv("PIB_PDL"); on = (!e || atoi(e) != 0) ? 1 : 0; }
+    return on != 0;
+}
+
 int pib_num_sms() {
     int dev = 0;
     cudaGetDevice(&dev);
@@ -150,6 +156,8 @@ extern "C" int pib_mul_mat_host(const pib_weight * w, const float * x_host, int 
 // every element is one fp32 multiply (and one subtract for Q4_K), so results are bit-exact)
 __global__ void get_rows_kernel(int type, const uint8_t * __restrict__ qs, const uint16_t * __restrict__ d, int64_t K,
                                 const int32_t * __restrict__ ids, float * __restrict__ out) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
     const int64_t row = ids[blockIdx.x];
     float *       o   = out + (size_t) blockIdx.x * K;
     if (type == PIB_TYPE_Q8_0) {
@@ -189,7 +197,7 @@ __global__ void get_rows_kernel(int type, const uint8_t * __restrict__ qs, const
 
 extern "C" int pib_get_rows(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, pib_stream s) {
     if (!w || !ids_dev || !out_dev || n < 1) { pib_set_error("pib_get_rows: bad arguments"); return PIB_ERR_ARG; }
-    get_rows_kernel<<<n, 256, 0, (cudaStream_t) s>>>(w->type, w->qs, w->d, w->K, ids_dev, out_dev);
+    pib_launch(get_rows_kernel, dim3(n), dim3(256), 0, (cudaStream_t) s, w->type, w->qs, w->d, w->K, ids_dev, out_dev);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }

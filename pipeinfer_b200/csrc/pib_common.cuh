@@ -6,6 +6,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "../../include/pipeinfer_b200.h"
 
@@ -63,6 +64,14 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
+// Programmatic dependent launch (PDL): a kernel launched with pib_launch may become resident while its predecessor in
+// the stream is still running; it must call pib_pdl_wait() before it touches anything the predecessor wrote (or before it
+// exits: a cancelled kernel that returned without waiting would let ITS successor overtake the predecessor).  Only
+// immutable data (weights, tables) may be read before the wait.  pib_pdl_trigger() lets the successor start its own
+// prologue; it is issued after the wait, so at most two kernels overlap.
+__device__ __forceinline__ void pib_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pib_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // 128-bit read-only streaming load that does not allocate in L1 (weights are read exactly once per launch)
 __device__ __forceinline__ int4 ld_stream_v4(const void * p) {
     int4 r;
@@ -75,6 +84,21 @@ __device__ __forceinline__ int2 ld_stream_v2(const void * p) {
     int2 r;
     asm volatile("ld.global.nc.L1::no_allocate.v2.s32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
     return r;
+}
+
+// launch with the PDL attribute (env PIB_PDL=0 turns it off: plain stream order)
+bool pib_pdl_enabled();
+template <typename... KArgs, typename... Args>
+static inline cudaError_t pib_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr;
+    memset(&attr, 0, sizeof(attr));
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &attr; cfg.numAttrs = pib_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 // device view of a repacked weight matrix (see weights.cu for the layouts)

@@ -19,45 +19,71 @@ __global__ void __launch_bounds__(SMP_THREADS) sample_topk_kernel(float * __rest
                                                                   int n_bias, pib_row_result * __restrict__ out,
                                                                   const uint8_t * __restrict__ desc, const int * __restrict__ cancel) {
     (void) desc;
+    pib_pdl_wait();
+    pib_pdl_trigger();
     if (cancel && *cancel) return;
     __shared__ float  s_val[SMP_THREADS / 32];
     __shared__ int    s_idx[SMP_THREADS / 32];
     __shared__ double s_sum[SMP_THREADS / 32];
     __shared__ float  s_best;
     __shared__ int    s_besti;
-    __shared__ int    s_taken[SMP_TOPK];
     float *   l    = logits + (size_t) blockIdx.x * n_vocab;
     const int tid  = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int k = tid; k < n_bias; k += SMP_THREADS) l[bias_ids[k]] += bias_val[k];
     __syncthreads();
+    // one pass: every thread keeps the 8 largest of its strided elements, sorted (value descending, index ascending: the
+    // indices a thread sees only grow, so strict comparisons keep the earlier one of two equal values in front)
+    float tv[SMP_TOPK];
+    int   ti[SMP_TOPK];
+#pragma unroll
+    for (int j = 0; j < SMP_TOPK; j++) { tv[j] = -INFINITY; ti[j] = 0x7fffffff; }
+#pragma unroll 4
+    for (int i = tid; i < n_vocab; i += SMP_THREADS) {
+        const float v = l[i];
+        if (v > tv[SMP_TOPK - 1] || ti[SMP_TOPK - 1] == 0x7fffffff) {
+            tv[SMP_TOPK - 1] = v; ti[SMP_TOPK - 1] = i;
+#pragma unroll
+            for (int j = SMP_TOPK - 1; j > 0; j--) {
+                if (tv[j] > tv[j - 1] || ti[j - 1] == 0x7fffffff) {
+                    const float fv = tv[j]; tv[j] = tv[j - 1]; tv[j - 1] = fv;
+                    const int   fi = ti[j]; ti[j] = ti[j - 1]; ti[j - 1] = fi;
+                }
+            }
+        }
+    }
+    // eight rounds over the heads of the per-thread lists (std::max_element semantics: first index of the maximum)
     float max_l = 0.f;
     for (int k = 0; k < SMP_TOPK; k++) {
-        float bv = -INFINITY;
-        int   bi = 0x7fffffff;
-        for (int i = tid; i < n_vocab; i += SMP_THREADS) {
-            bool taken = false;
-            for (int j = 0; j < k; j++) taken |= (s_taken[j] == i);
-            const float v = l[i];
-            if (!taken && (v > bv || (v == bv && i < bi))) { bv = v; bi = i; }
-        }
+        float bv = tv[0];
+        int   bi = ti[0];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
             const int   oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+            if (oi != 0x7fffffff && (bi == 0x7fffffff || ov > bv || (ov == bv && oi < bi))) { bv = ov; bi = oi; }
         }
         if (lane == 0) { s_val[warp] = bv; s_idx[warp] = bi; }
         __syncthreads();
-        if (tid == 0) {
-            float v = s_val[0];
-            int   i = s_idx[0];
-            for (int w = 1; w < SMP_THREADS / 32; w++)
-                if (s_val[w] > v || (s_val[w] == v && s_idx[w] < i)) { v = s_val[w]; i = s_idx[w]; }
-            s_best = v; s_besti = i; s_taken[k] = i;
-            out[blockIdx.x].id[k] = i;
-            out[blockIdx.x].logit[k] = v;
+        if (warp == 0) {
+            bv = s_val[lane]; bi = s_idx[lane];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                const int   oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (oi != 0x7fffffff && (bi == 0x7fffffff || ov > bv || (ov == bv && oi < bi))) { bv = ov; bi = oi; }
+            }
+            if (lane == 0) {
+                s_best = bv; s_besti = bi;
+                out[blockIdx.x].id[k]    = bi == 0x7fffffff ? 0 : bi;
+                out[blockIdx.x].logit[k] = bv;
+            }
         }
         __syncthreads();
+        if (ti[0] == s_besti && s_besti != 0x7fffffff) {          // the winner pops its head
+#pragma unroll
+            for (int j = 0; j < SMP_TOPK - 1; j++) { tv[j] = tv[j + 1]; ti[j] = ti[j + 1]; }
+            tv[SMP_TOPK - 1] = -INFINITY; ti[SMP_TOPK - 1] = 0x7fffffff;
+        }
         if (k == 0) max_l = s_best;
     }
     double sum = 0.0;
@@ -74,7 +100,7 @@ __global__ void __launch_bounds__(SMP_THREADS) sample_topk_kernel(float * __rest
 
 int pib_sample_topk(float * logits_dev, int n_rows, int n_vocab, const int32_t * bias_ids_dev, const float * bias_val_dev,
                     int n_bias, void * out_dev, const uint8_t * desc, const int * cancel, cudaStream_t st) {
-    sample_topk_kernel<<<n_rows, SMP_THREADS, 0, st>>>(logits_dev, n_vocab, bias_ids_dev, bias_val_dev, n_bias,
+    pib_launch(sample_topk_kernel, dim3(n_rows), dim3(SMP_THREADS), 0, st, logits_dev, n_vocab, bias_ids_dev, bias_val_dev, n_bias,
                                                        (pib_row_result *) out_dev, desc, cancel);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
