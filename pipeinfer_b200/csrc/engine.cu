@@ -522,7 +522,14 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
             done = true;
         }
     }
-    if (!done && (rc = run_chunk_body(c, run, chunk, ntok, slot, cancel)) != PIB_OK) return rc;
+    if (!done) {
+        // a decode whose launches are timed with events runs in plain stream order: with PDL a kernel starts (and prefetches
+        // weights) before the event in front of it fires, and the event pair would under-report its duration
+        if (c->prof_now) pib_pdl_suspend(true);
+        rc = run_chunk_body(c, run, chunk, ntok, slot, cancel);
+        if (c->prof_now) pib_pdl_suspend(false);
+        if (rc != PIB_OK) return rc;
+    }
     if (!c->stage.last() && pib_hop_send && (rc = pib_hop_send(c, c->x, ntok, cancel)) != PIB_OK) return rc;
     return PIB_OK;
 }

@@ -335,6 +335,9 @@ gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int n_tiles, in
 
 // ---- direct variant: one CTA per (row tile, k split), the four warps interleave the super-blocks, weights prefetched one
 // super-block ahead into registers with streaming 128-bit loads (no shared-memory staging); same arithmetic core -------------
+#ifndef MM_L2_AHEAD
+#define MM_L2_AHEAD 0
+#endif
 template <int NT>
 __global__ void __launch_bounds__(MM_THREADS, NT == 1 ? 4 : 3)
 gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, const int8_t * __restrict__ aqs,
@@ -378,6 +381,13 @@ gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K
     for (; s < sb1; s += MM_WARPS) {
         int4 wn[4], hn[2];
         const int sn = s + MM_WARPS;
+#if MM_L2_AHEAD > 0
+        {   // keep more bytes in flight than the registers can hold: pull the record MM_L2_AHEAD iterations ahead into L2
+            const int sp = s + (1 + MM_L2_AHEAD) * MM_WARPS;
+            if (sp < sb1 && lane < MM_TILE_BYTES / 128)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(tiles + ((size_t) T * nsb + sp) * MM_TILE_BYTES + lane * 128));
+        }
+#endif
         if (sn < sb1) {
 #pragma unroll
             for (int c = 0; c < 4; c++) wn[c] = ld_stream_v4(tbase + (size_t) sn * MM_TILE_BYTES + c * 512);

@@ -71,10 +71,12 @@ const pib_luts & pib_get_luts() {
     return g_luts[dev];
 }
 
+static int g_pdl_suspended = 0;
+void pib_pdl_suspend(bool suspend) { g_pdl_suspended = suspend ? 1 : 0; }
 bool pib_pdl_enabled() {
     static int on = -1;
     if (on < 0) { const char * e = getenv("PIB_PDL"); on = (!e || atoi(e) != 0) ? 1 : 0; }
-    return on != 0;
+    return on != 0 && !g_pdl_suspended;
 }
 
 int pib_num_sms() {

@@ -88,6 +88,7 @@ __device__ __forceinline__ int2 ld_stream_v2(const void * p) {
 
 // launch with the PDL attribute (env PIB_PDL=0 turns it off: plain stream order)
 bool pib_pdl_enabled();
+void pib_pdl_suspend(bool suspend);   // event-timed launches must not overlap their predecessor
 template <typename... KArgs, typename... Args>
 static inline cudaError_t pib_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&... args) {
     cudaLaunchConfig_t cfg;
