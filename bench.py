@@ -160,16 +160,22 @@ def main():
     ap.add_argument("--np", type=int, default=3)
     ap.add_argument("--pa", type=float, default=0.1)
     ap.add_argument("--ps", type=float, default=0.9)
+    ap.add_argument("--max-spec-runs", type=int, default=-1,
+                    help="bound on target runs in flight: 0 = the reference's behaviour (unbounded), -1 = number of pipeline stages + 1")
+    ap.add_argument("--no-draft-priority", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layer-split", default="", help="comma-separated per-stage weights, as the reference's --mpi-layer-split")
     ap.add_argument("--head-share", type=float, default=None, help="share of the target's layers on the head GPU (which also runs the draft)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.max_spec_runs < 0:
+        args.max_spec_runs = world + 1
     (L, E, H, HKV, FF, V, wt), dshape, label = CONFIGS[args.config]
     config = {"workload": "%s, random-init (bigram flavour, draft agreement %.2f), %d-token synthetic prompt, greedy, "
-                          "--draft %d -np %d -pa %g -ps %g -n %d -c 1024, layer split over %d GPU(s)"
-                          % (label, args.agree, args.prompt_len, args.draft, args.np, args.pa, args.ps, args.n_predict, args.gpus),
+                          "--draft %d -np %d -pa %g -ps %g -n %d -c 1024, at most %s runs in flight, layer split over %d GPU(s)"
+                          % (label, args.agree, args.prompt_len, args.draft, args.np, args.pa, args.ps, args.n_predict,
+                             args.max_spec_runs or "unbounded", args.gpus),
               "l2_policy": "inputs larger than L2: every pass streams the target's weights (38.8 GB >> 126 MB)"}
 
     if args.impl == "reference":
@@ -222,10 +228,12 @@ def main():
     else:
         tgt = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=(L, E, H, HKV, FF, V, wt, 1, 1, 1.0))
     dft = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=dshape + (2, 1, args.agree)) if rank == 0 else None
+    if dft is not None and not args.no_draft_priority:
+        dft.set_priority(True)                           # the draft sits on the scheduler's critical path
     ctxs = [c for c in (tgt, dft) if c is not None]
     t_load = time.time() - t_load
     prompt = [1] + [3 + (i * 7919) % (V - 3) for i in range(args.prompt_len - 1)]
-    params = llama.spec_params(n_draft=args.draft, n_parallel=args.np, p_accept=args.pa, p_split=args.ps, n_predict=args.n_predict)
+    params = llama.spec_params(n_draft=args.draft, n_parallel=args.np, p_accept=args.pa, p_split=args.ps, n_predict=args.n_predict, max_spec_runs=args.max_spec_runs)
 
     def io(ctx):
         a, b = C.c_uint64(), C.c_uint64()

@@ -192,6 +192,8 @@ struct llama_context * llama_pib_new_context_stage(struct llama_model * model, u
 int  llama_pib_stage_serve(struct llama_context * ctx);
 int  llama_pib_pipe_pause(struct llama_context * ctx);
 int  llama_pib_pipe_shutdown(struct llama_context * ctx);
+/* 1 = this context's kernels run on a higher-priority stream than other contexts' (draft model next to a target stage) */
+int  llama_pib_set_priority(struct llama_context * ctx, int high);
 /* context with an explicit sequence-id capacity (the reference sizes std::set on demand) */
 struct llama_context * llama_pib_new_context(struct llama_model * model, uint32_t n_ctx, int32_t max_seq_ids);
 /* KV bookkeeping probes for parity tests: head / used / n, cell positions and sequence bitset rows, host mirror (0)

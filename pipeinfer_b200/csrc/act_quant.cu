@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
                                                                const int * __restrict__ cancel, int64_t xstride) {
     pib_pdl_wait();
     pib_pdl_trigger();
-    if (cancel && *cancel) return;
+    if (PIB_CANCELLED(cancel)) return;
     const int     row  = blockIdx.x;
     const float * xr   = x + (size_t) row * xstride;
     const float * x2r  = x2 ? (x2_per_row ? x2 + (size_t) row * xstride : x2) : nullptr;

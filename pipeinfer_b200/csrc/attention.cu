@@ -49,7 +49,7 @@ __global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8
     const int32_t * hdr = reinterpret_cast<const int32_t *>(desc + PIB_DESC_HDR_OFF);
     pib_pdl_wait();
     pib_pdl_trigger();
-    if (cancel && *cancel) return;
+    if (PIB_CANCELLED(cancel)) return;
     const int       t    = blockIdx.x;
     const int       pos  = reinterpret_cast<const int32_t *>(desc + PIB_DESC_POS_OFF)[t];
     const int       cell = hdr[PIB_DH_KVHEAD] + t;
@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attention_kernel(const __half * _
                                                                 const int * __restrict__ cancel, int gdiv) {
     pib_pdl_wait();
     pib_pdl_trigger();
-    if (cancel && *cancel) return;
+    if (PIB_CANCELLED(cancel)) return;
     (void) desc;
     extern __shared__ float smem[];
     // gdiv == 1: blockIdx.x is a KV head serving its G query heads (K/V read once per token; best at long contexts).
@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half 
                                                                    const int * __restrict__ cancel, int gdiv) {
     pib_pdl_wait();
     pib_pdl_trigger();
-    if (cancel && *cancel) return;
+    if (PIB_CANCELLED(cancel)) return;
     extern __shared__ float smem[];
     __shared__ float  sq[HD];
     __shared__ float  s_redf[ATQ_THREADS / 32];

@@ -343,15 +343,19 @@ pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_st
     rope_table_build(tab, c->rope_n_pos, m->n_rot, 0, m->rope_freq_base, m->rope_freq_scale);
     CK(cudaMalloc(&c->rope, tab.size() * sizeof(float2)));
     CK(cudaMemcpy(c->rope, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice));
-    CK(cudaMalloc(&c->cancel_table, 65536 * sizeof(int) + 16));
-    CK(cudaMemset(c->cancel_table, 0, 65536 * sizeof(int) + 16));
-    c->cancel_one = c->cancel_table + 65536;
+    CK(cudaMalloc(&c->cancel_table, 128 * sizeof(int)));          // [0] current run slot, [1..64] flags, [100] the constant 1
+    CK(cudaMemset(c->cancel_table, 0, 128 * sizeof(int)));
+    c->cancel_one = c->cancel_table + 100;
     { int one = 1; CK(cudaMemcpy(c->cancel_one, &one, 4, cudaMemcpyHostToDevice)); }
+    CK(cudaMallocHost(&c->run_id_host, 64 * sizeof(int)));
+    for (int i = 0; i < 64; i++) c->run_id_host[i] = i;
     c->desc_stride = pib_desc_stride(c->n_words);
-    c->desc_slots  = 256;                  // ring; slots [256, 256 + 64) are bound to the run slots (single-chunk decodes)
-    CK(cudaMallocHost(&c->desc_host, c->desc_stride * (c->desc_slots + 64)));
-    CK(cudaMalloc(&c->desc_dev, c->desc_stride * (c->desc_slots + 64)));
-    c->desc_ev.assign(c->desc_slots + 64, nullptr);
+    // ring of 256 slots for multi-chunk decodes; a single-chunk decode stages its descriptor in host slot 257 + run slot and
+    // always lands in device slot 256: one fixed address, ordered by the stream, so that its CUDA graph serves every run
+    c->desc_slots  = 256;
+    CK(cudaMallocHost(&c->desc_host, c->desc_stride * (c->desc_slots + 65)));
+    CK(cudaMalloc(&c->desc_dev, c->desc_stride * (c->desc_slots + 65)));
+    c->desc_ev.assign(c->desc_slots + 65, nullptr);
     { const char * g = getenv("PIB_GRAPHS"); c->use_graphs = !g || atoi(g) != 0; }
     c->ops_cap = 1 << 16;
     CK(cudaMallocHost(&c->ops_host, sizeof(KvOp) * c->ops_cap));
@@ -372,6 +376,7 @@ void pib_context_free(pib_context * c) {
                       c->cancel_table, c->desc_dev, c->ops_dev, c->bias_ids_dev, c->bias_val_dev };
     for (void * b : bufs) if (b) cudaFree(b);
     if (c->desc_host) cudaFreeHost(c->desc_host);
+    if (c->run_id_host) cudaFreeHost(c->run_id_host);
     if (c->ops_host) cudaFreeHost(c->ops_host);
     for (auto & r : c->runs) {
         if (r.done) cudaEventDestroy(r.done);
@@ -394,9 +399,11 @@ static std::vector<KvOp> & devq(pib_context * c) { return c->devops; }
 
 // ---------------------------------------------------------------------------------------------------------------------
 // decode
+static inline int dev_slot(const pib_context * c, int host_slot) { return host_slot > c->desc_slots ? c->desc_slots : host_slot; }
+
 static int take_desc_slot(pib_context * c, const pib_run * run, int n_chunks) {
     int s;
-    if (run && n_chunks == 1) s = c->desc_slots + run->id;        // fixed address per run slot (see run_chunk)
+    if (run && n_chunks == 1) return c->desc_slots + 1 + run->id;  // host staging of the run slot (free: its last run has finished)
     else { s = c->desc_next; c->desc_next = (c->desc_next + 1) % c->desc_slots; }
     if (c->desc_ev[s]) cudaEventSynchronize(c->desc_ev[s]);
     else cudaEventCreateWithFlags(&c->desc_ev[s], cudaEventDisableTiming);
@@ -407,7 +414,7 @@ __global__ void add_kernel(const float * __restrict__ a, const float * __restric
                            const int * __restrict__ cancel) {
     pib_pdl_wait();
     pib_pdl_trigger();
-    if (cancel && *cancel) return;
+    if (PIB_CANCELLED(cancel)) return;
     const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) o[i] = __fadd_rn(a[i], b[i]);
 }
@@ -416,11 +423,13 @@ __global__ void add_kernel(const float * __restrict__ a, const float * __restric
 int (*pib_hop_recv)(pib_context * c, float * x, int n_tokens, const int * cancel) = nullptr;
 int (*pib_hop_send)(pib_context * c, const float * x, int n_tokens, const int * cancel) = nullptr;
 
-static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, int slot, const int * cancel) {
+// `part`: 1 = embedding + layers (everything whose addresses are the same for every run: graph material), 2 = the last
+// stage's tail (final norm, lm_head, sampling: writes the run's own logits / result rows), 3 = both
+static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, int slot, const int * cancel, int part) {
     pib_model *    m    = c->model;
     const int      E = m->n_embd, GQA = m->n_embd_gqa(), FF = m->n_ff, hd = m->head_dim(), wt = m->wtype, var = c->gemv_variant;
     cudaStream_t   st   = c->stream;
-    const uint8_t * desc = c->desc_dev + (size_t) slot * c->desc_stride;
+    const uint8_t * desc = c->desc_dev + (size_t) dev_slot(c, slot) * c->desc_stride;
     const int32_t * tok  = reinterpret_cast<const int32_t *>(desc + PIB_DESC_TOK_OFF);
     const int32_t * tpos = reinterpret_cast<const int32_t *>(desc + PIB_DESC_POS_OFF);
     const uint32_t * tbits = reinterpret_cast<const uint32_t *>(desc + PIB_DESC_BITS_OFF);
@@ -444,11 +453,13 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
         RC(call);                                                                                                      \
         if (pr__) { cudaEventRecord(r__.e1, st); c->prof.push_back(r__); }                                             \
     } while (0)
-    RC(kv_device_mask(&c->kvd, tpos, tbits, ntok, c->mask, st));
-    if (c->stage.first()) RC(pib_get_rows(m->tok_embd, tok, ntok, c->x, st));
+    if (part & 1) {
+        RC(kv_device_mask(&c->kvd, tpos, tbits, ntok, c->mask, st));
+        if (c->stage.first()) RC(pib_get_rows(m->tok_embd, tok, ntok, c->x, st));
+    }
     // x holds layer_inp; `pending_add` = a down-projection result still to be added to x2 (ffn_inp) to form the next x
-    bool pending_add = false;
-    for (int il = m->layer_begin; il < m->layer_end; il++) {
+    bool pending_add = (part & 1) ? false : m->layer_end > m->layer_begin;
+    for (int il = m->layer_begin; (part & 1) && il < m->layer_end; il++) {
         const pib_layer & L  = m->layers[il];
         const size_t      lo = (size_t) (il - m->layer_begin) * c->n_ctx * GQA;
         if (pending_add) TL(5, il, pib_add_rmsnorm_quantize_act(wt, c->proj, c->x2, c->x, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
@@ -465,6 +476,8 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
         GEMV(3, il, L.wdown, c->proj);
         pending_add = true;
     }
+    if (c->stage.last() && !(part & 2)) return PIB_OK;
+    if (!c->stage.last() && !(part & 1)) return PIB_OK;
     if (c->stage.last()) {
         if (pending_add) RC(pib_add_rmsnorm_quantize_act(wt, c->proj, c->x2, c->x, m->output_norm, m->rms_eps, ntok, E, c->act, cancel, st));
         else             RC(pib_add_rmsnorm_quantize_act(wt, c->x, nullptr, nullptr, m->output_norm, m->rms_eps, ntok, E, c->act, cancel, st));
@@ -486,27 +499,27 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
 }
 
 // One chunk on this stage: receive the activations (stages > 0), run the layers, send them on (stages < last).  The
-// layer part of a single-chunk decode is replayed from a CUDA graph captured on the second use of its (run slot, n_tokens)
-// pair: every address a kernel gets is fixed per run slot (descriptor slot, cancel word, logits and result rows) and
-// everything that varies between decodes lives in the descriptor, which is device memory.  One graph launch replaces
+// layer part of a single-chunk decode is replayed from a CUDA graph captured on the second use of its n_tokens: every
+// address a kernel of that part gets is the same for every run (one device descriptor slot, the cancel block, the work
+// buffers) and everything that varies between decodes lives in the descriptor, which is device memory.  One graph launch replaces
 // ~10 launches per layer on the host, which is what bounds the small draft model.
 static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int slot) {
-    const int * cancel = c->cancel_table + run.id;
+    const int * cancel = c->cancel_table;            // block address (see PIB_CANCELLED); the current-run cell was set by enqueue_decode
     int rc;
     if (!c->stage.first() && pib_hop_recv && (rc = pib_hop_recv(c, c->x, ntok, cancel)) != PIB_OK) return rc;
     // per-launch event timing (bench.py roofline) samples one decode in eight, launched directly; the others keep their graphs
     c->prof_now = c->prof_layer >= 0 && (c->n_decode & 7) == 0;
-    const bool graphable = c->use_graphs && !c->prof_now && slot >= c->desc_slots;          // reserved slot <=> single-chunk decode
+    const bool graphable = c->use_graphs && !c->prof_now && slot > c->desc_slots;           // single-chunk decode: fixed device slot
     bool done = false;
     if (graphable) {
-        pib_context::GraphEntry & g = c->graphs[run.id * 32 + ntok];
+        pib_context::GraphEntry & g = c->graphs[ntok];
         g.uses++;
-        if (!g.exec && !g.failed && g.uses >= 2 && c->graphs.size() <= 512) {
+        if (!g.exec && !g.failed && g.uses >= 2) {
             const uint64_t k0 = c->n_kernels;
             cudaGraph_t graph = nullptr;
             bool ok = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeRelaxed) == cudaSuccess;
             if (ok) {
-                rc = run_chunk_body(c, run, chunk, ntok, slot, cancel);
+                rc = run_chunk_body(c, run, chunk, ntok, slot, cancel, 1);
                 ok = cudaStreamEndCapture(c->stream, &graph) == cudaSuccess && rc == PIB_OK && graph != nullptr;
             }
             if (ok) ok = cudaGraphInstantiate(&g.exec, graph, 0) == cudaSuccess;
@@ -519,6 +532,7 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
             if (cudaGraphLaunch(g.exec, c->stream) != cudaSuccess) { pib_set_error("decode: graph launch failed: %s", cudaGetErrorString(cudaGetLastError())); return PIB_ERR_CUDA; }
             c->n_kernels += (uint64_t) g.n_kernels;
             c->n_graph_launches++;
+            if ((rc = run_chunk_body(c, run, chunk, ntok, slot, cancel, 2)) != PIB_OK) return rc;
             done = true;
         }
     }
@@ -526,7 +540,7 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
         // a decode whose launches are timed with events runs in plain stream order: with PDL a kernel starts (and prefetches
         // weights) before the event in front of it fires, and the event pair would under-report its duration
         if (c->prof_now) pib_pdl_suspend(true);
-        rc = run_chunk_body(c, run, chunk, ntok, slot, cancel);
+        rc = run_chunk_body(c, run, chunk, ntok, slot, cancel, 3);
         if (c->prof_now) pib_pdl_suspend(false);
         if (rc != PIB_OK) return rc;
     }
@@ -559,11 +573,16 @@ static pib_run * take_run(pib_context * c, int n_tokens) {
     return nullptr;
 }
 
+static bool slow_trace() { static int on = -1; if (on < 0) on = getenv("PIB_TRACE_SLOW") ? 1 : 0; return on != 0; }
+#define SLOW_MARK(tag) do { if (slow_trace()) { const int64_t n__ = now_us(); if (n__ - t_mark > 500) fprintf(stderr, "[slow] rank-stage %d batch %d: %s took %lld us\n", c->stage.rank, batch_id, tag, (long long) (n__ - t_mark)); t_mark = n__; } } while (0)
+
 int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const int32_t * pos, const int32_t * n_seq_id,
                      const int32_t * const * seq_id, int batch_id) {
     if (n_tokens <= 0) { pib_set_error("decode: n_tokens == 0"); return -1; }
+    int64_t t_mark = slow_trace() ? now_us() : 0;
     pib_model * m = c->model;
     pib_kv_flush_host(c);
+    SLOW_MARK("kv flush (host mirror)");
     std::vector<KvOp> & dq = devq(c);
     const int W = c->n_words;
     // per-token sequence bitsets (the reference's SEQ_IDS message, ggml-mpi.c:318-334, as rows of n_words words)
@@ -578,7 +597,9 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
         if (c->stage.first() && (token[i] < 0 || token[i] >= m->n_vocab)) { pib_set_error("decode: token id %d out of range", token[i]); return -1; }
     // llama.cpp:5548-5571: head-reset heuristic, find_slot, attended range n
     const bool found = kvlog_decode_begin(c->kv, dq, n_tokens, pos, tb.data());
+    SLOW_MARK("find slot");
     pib_run *  run   = found ? take_run(c, n_tokens) : nullptr;
+    SLOW_MARK("take run");
     if (!found) pib_set_error("decode: no KV slot for %d tokens", n_tokens);
     if (!run) return -1;      // bookkeeping done so far (flushed ops, head moves) stays queued for the device
     const uint32_t head = c->kv.head;
@@ -596,17 +617,21 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
         memcpy(d + PIB_DESC_POS_OFF, pos + t0, sizeof(int32_t) * nt);
         memcpy(d + PIB_DESC_BITS_OFF, tb.data() + (size_t) t0 * W, sizeof(uint32_t) * (size_t) nt * W);
         dq.push_back({ KVOP_ALLOC, (int32_t) (head + t0), nt, (int32_t) c->kv.n, s, 0 });
-        cudaMemcpyAsync(c->desc_dev + (size_t) s * c->desc_stride, d, c->desc_stride, cudaMemcpyHostToDevice, c->stream);
+        cudaMemcpyAsync(c->desc_dev + (size_t) dev_slot(c, s) * c->desc_stride, d, c->desc_stride, cudaMemcpyHostToDevice, c->stream);
         c->h2d_bytes += c->desc_stride;
     }
     dq.push_back({ KVOP_ADVANCE, n_tokens, 0, 0, 0, 0 });
     kvlog_decode_end(c->kv, n_tokens);                                    // llama.cpp:5708-5713
+    SLOW_MARK("descriptors");
     if (c->stage.size > 1 && c->stage.first()) {          // tell the other stages first, so that their receives are posted early
         std::vector<const uint8_t *> dp(n_chunks);
         for (int ch = 0; ch < n_chunks; ch++) dp[ch] = c->desc_host + (size_t) slots[ch] * c->desc_stride;
         if (pib_pipe_ship_decode(batch_id, n_tokens, n_chunks, dp.data(), c->desc_stride, slots.data(), dq.data(), (int) dq.size()) != PIB_OK) return -1;
     }
-    return enqueue_decode(c, run, n_tokens, batch_id, slots);
+    SLOW_MARK("ship record");
+    const int rid = enqueue_decode(c, run, n_tokens, batch_id, slots);
+    SLOW_MARK("enqueue");
+    return rid;
 }
 
 // ship the queued device-level op-log to the GPU and replay it on the KV replica
@@ -617,6 +642,8 @@ int pib_apply_devops(pib_context * c) {
     if (n > c->ops_cap) { pib_set_error("decode: KV op-log overflow (%d ops)", n); return PIB_ERR_ARG; }
     if (c->ops_next + n > c->ops_cap) { cudaStreamSynchronize(c->stream); c->ops_next = 0; }
     memcpy(c->ops_host + c->ops_next, dq.data(), sizeof(KvOp) * n);
+    for (int i = 0; i < n; i++)                               // the log names host staging slots; the kernel reads device slots
+        if (c->ops_host[c->ops_next + i].op == KVOP_ALLOC) c->ops_host[c->ops_next + i].p1 = dev_slot(c, c->ops_host[c->ops_next + i].p1);
     cudaMemcpyAsync(c->ops_dev + c->ops_next, c->ops_host + c->ops_next, sizeof(KvOp) * n, cudaMemcpyHostToDevice, c->stream);
     c->h2d_bytes += sizeof(KvOp) * n;
     if (kv_device_apply(&c->kvd, c->ops_dev + c->ops_next, n, c->desc_dev, c->desc_stride, c->stream) != PIB_OK) return PIB_ERR_CUDA;
@@ -640,13 +667,17 @@ int pib_kv_sync_replicas(pib_context * c) {
 // hand the sampled rows to whoever needs them
 static int enqueue_decode(pib_context * c, pib_run * run, int n_tokens, int batch_id, const std::vector<int> & slots) {
     const int n_chunks = (int) slots.size();
+    int64_t t_mark = slow_trace() ? now_us() : 0;
     if (pib_apply_devops(c) != PIB_OK) return -1;
+    SLOW_MARK("  apply ops");
     run->in_use = true; run->batch_id = batch_id; run->n_tokens = n_tokens; run->failed = false;
+    cudaMemcpyAsync(c->cancel_table, c->run_id_host + run->id, sizeof(int), cudaMemcpyHostToDevice, c->stream);   // "this run executes now"
     for (int ch = 0; ch < n_chunks; ch++) {
         const int nt = std::min(PIB_CHUNK, n_tokens - ch * PIB_CHUNK);
         if (run_chunk(c, *run, ch, nt, slots[ch]) != PIB_OK) { run->failed = true; break; }
-        cudaEventRecord(c->desc_ev[slots[ch]], c->stream);
+        if (c->desc_ev[slots[ch]]) cudaEventRecord(c->desc_ev[slots[ch]], c->stream);
     }
+    SLOW_MARK("  chunks");
     if (c->stage.last() && !run->failed) {
         if (c->stage.size > 1) {
             if (pib_pipe_send_results(c, *run) != PIB_OK) run->failed = true;
@@ -660,6 +691,7 @@ static int enqueue_decode(pib_context * c, pib_run * run, int n_tokens, int batc
         // the rows come back from the last stage on the result stream; `done` then means "rows are in pinned host memory"
         if (pib_pipe_post_result_recv(c, *run) != PIB_OK) run->failed = true;
     }
+    SLOW_MARK("  result recv post");
     c->inflight.push_back(run->id);
     c->n_decode++;
     return run->id;
@@ -681,7 +713,7 @@ int pib_decode_replay(pib_context * c, int batch_id, int n_tokens, int n_chunks,
         slots[ch]   = s;
         uint8_t * d = c->desc_host + (size_t) s * c->desc_stride;
         memcpy(d, descs + (size_t) ch * desc_stride, desc_stride);
-        cudaMemcpyAsync(c->desc_dev + (size_t) s * c->desc_stride, d, c->desc_stride, cudaMemcpyHostToDevice, c->stream);
+        cudaMemcpyAsync(c->desc_dev + (size_t) dev_slot(c, s) * c->desc_stride, d, c->desc_stride, cudaMemcpyHostToDevice, c->stream);
         c->h2d_bytes += c->desc_stride;
     }
     std::vector<KvOp> & dq = devq(c);
@@ -700,7 +732,7 @@ void pib_stage_finish(pib_context * c, int batch_id) {
     for (auto it = c->inflight.begin(); it != c->inflight.end(); ++it) {
         pib_run & r = c->runs[*it];
         if (r.in_use && r.batch_id == batch_id) {
-            cudaMemsetAsync(c->cancel_table + r.id, 0, sizeof(int), c->stream);
+            cudaMemsetAsync(c->cancel_table + 1 + r.id, 0, sizeof(int), c->stream);
             r.in_use = false;
             c->inflight.erase(it);
             return;
@@ -718,7 +750,7 @@ int pib_run_finish(pib_context * c, int run) {
     pib_run & r = c->runs[run];
     if (cudaEventSynchronize(r.done) != cudaSuccess) { pib_set_error("finish: %s", cudaGetErrorString(cudaGetLastError())); return -1; }
     // the run slot may be reused from here on: drop its cancel flag (ordered after every kernel of the run)
-    cudaMemsetAsync(c->cancel_table + r.id, 0, sizeof(int), c->stream);
+    cudaMemsetAsync(c->cancel_table + 1 + r.id, 0, sizeof(int), c->stream);
     if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_ints(2, 0, &r.batch_id, 1);
     for (auto it = c->inflight.begin(); it != c->inflight.end(); ++it) if (*it == run) { c->inflight.erase(it); break; }
     r.in_use         = false;
@@ -756,7 +788,7 @@ void pib_cancel(pib_context * c, const int32_t * batch_ids, int n) {
         for (int id : c->inflight) {
             pib_run & r = c->runs[id];
             if (r.in_use && r.batch_id == batch_ids[i])
-                cudaMemcpyAsync(c->cancel_table + r.id, c->cancel_one, sizeof(int), cudaMemcpyDeviceToDevice, c->ctrl);
+                cudaMemcpyAsync(c->cancel_table + 1 + r.id, c->cancel_one, sizeof(int), cudaMemcpyDeviceToDevice, c->ctrl);
         }
     if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_ints(3, 0, batch_ids, n);
 }

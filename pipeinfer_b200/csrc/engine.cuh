@@ -92,7 +92,8 @@ struct pib_context {
     void *  act = nullptr;
     float2 * rope = nullptr;
     int      rope_n_pos = 0;
-    int *    cancel_table = nullptr;       // device int[65536], indexed by batch_id & 0xffff
+    int *    cancel_table = nullptr;       // device cancellation block: see PIB_CANCELLED (pib_common.cuh)
+    int *    run_id_host  = nullptr;       // pinned {0, 1, ..., 63}: sources of the current-run writes
     int *    cancel_one   = nullptr;       // device int {1}: source of the cancel writes
 
     // host->device staging rings (pinned host + device copies)
@@ -122,7 +123,7 @@ struct pib_context {
     bool                 prof_now   = false;
     std::vector<ProfRec> prof;
     uint64_t             n_decode  = 0;
-    // CUDA graphs of single-chunk decodes, keyed by run slot * 32 + n_tokens (engine.cu: run_chunk)
+    // CUDA graphs of the layer part of single-chunk decodes, keyed by n_tokens (engine.cu: run_chunk)
     struct GraphEntry { cudaGraphExec_t exec = nullptr; int uses = 0; int n_kernels = 0; bool failed = false; };
     std::map<int, GraphEntry> graphs;
     bool                 use_graphs = true;

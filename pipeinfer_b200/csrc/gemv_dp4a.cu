@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q8_0_kernel(const int8_t *
                                                                   float * __restrict__ y, int N, int K, const int * __restrict__ cancel) {
     pib_pdl_wait();
     pib_pdl_trigger();
-    if (cancel && *cancel) return;
+    if (PIB_CANCELLED(cancel)) return;
     const int lane = threadIdx.x & 31;
     const int row  = blockIdx.x * GV_WARPS + (threadIdx.x >> 5);
     if (row >= N) return;
@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q4_0_kernel(const uint8_t 
                                                                   float * __restrict__ y, int N, int K, const int * __restrict__ cancel) {
     pib_pdl_wait();
     pib_pdl_trigger();
-    if (cancel && *cancel) return;
+    if (PIB_CANCELLED(cancel)) return;
     const int lane = threadIdx.x & 31;
     const int row  = blockIdx.x * GV_WARPS + (threadIdx.x >> 5);
     if (row >= N) return;
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(GV_WARPS * 32) gemv_q4_K_kernel(const uint8_t 
                                                                   int N, int K, const int * __restrict__ cancel) {
     pib_pdl_wait();
     pib_pdl_trigger();
-    if (cancel && *cancel) return;
+    if (PIB_CANCELLED(cancel)) return;
     const int lane = threadIdx.x & 31;
     const int row  = blockIdx.x * GV_WARPS + (threadIdx.x >> 5);
     if (row >= N) return;

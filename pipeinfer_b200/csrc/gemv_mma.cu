@@ -143,7 +143,7 @@ gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int n_tiles, in
                     const int8_t * __restrict__ aqs, const float * __restrict__ ad, const int8_t * __restrict__ abs8, int b,
                     float * __restrict__ y, float * __restrict__ partial, unsigned int * __restrict__ counters,
                     const int * __restrict__ cancel) {
-    if (cancel && *cancel) return;
+    if (PIB_CANCELLED(cancel)) return;
     extern __shared__ __align__(128) uint8_t dsm[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
     uint8_t *      ring = dsm + (size_t) warp * MM_STAGES * MM_STAGE_BYTES;
@@ -343,7 +343,7 @@ __global__ void __launch_bounds__(MM_THREADS, NT == 1 ? 4 : 3)
 gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, const int8_t * __restrict__ aqs,
                        const float * __restrict__ ad, const int8_t * __restrict__ abs8, int b, float * __restrict__ y,
                        float * __restrict__ partial, unsigned int * __restrict__ counters, const int * __restrict__ cancel) {
-    if (cancel && *cancel) { pib_pdl_wait(); return; }
+    if (PIB_CANCELLED(cancel)) { pib_pdl_wait(); return; }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
     const int T = blockIdx.x;
     const int nsplit = gridDim.y, split = blockIdx.y;

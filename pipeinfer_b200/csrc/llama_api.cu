@@ -136,6 +136,23 @@ struct llama_context * llama_new_context_with_model(struct llama_model * model, 
     return lc;
 }
 
+// 1 = run this context's kernels on a higher-priority stream than other contexts' (the draft model shares the head GPU
+// with the first target stage and sits on the scheduler's critical path).  Call right after creating the context.
+int llama_pib_set_priority(struct llama_context * ctx, int high) {
+    pib_context * c = ctx->c;
+    int lo, hi;
+    if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess) return -1;
+    cudaStreamSynchronize(c->stream);
+    for (auto & g : c->graphs) if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
+    c->graphs.clear();
+    cudaStream_t ns = nullptr;
+    const int pr = high ? (hi < lo ? hi + 1 <= lo ? hi + 1 : hi : hi) : lo;      // one step below the control stream's priority
+    if (cudaStreamCreateWithPriority(&ns, cudaStreamNonBlocking, pr) != cudaSuccess) return -1;
+    cudaStreamDestroy(c->stream);
+    c->stream = ns;
+    return 0;
+}
+
 int llama_pib_stage_serve(struct llama_context * ctx) { return pib_stage_serve(ctx->c); }
 // head: let every stage drain its stream and return from llama_pib_stage_serve (kind 5), or end for good (kind 6)
 int llama_pib_pipe_pause(struct llama_context * ctx) {

@@ -72,6 +72,11 @@ __device__ __forceinline__ float warp_max(float v) {
 __device__ __forceinline__ void pib_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pib_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// Cancellation block of a context (device): int cur = run slot whose kernels are executing on the context's stream (set in
+// stream order in front of every run), then one flag per run slot.  Kernels get the block's address, which never
+// changes, so a captured CUDA graph serves every run; a null pointer means "not cancellable".
+#define PIB_CANCELLED(cancel) ((cancel) != nullptr && (cancel)[1 + (cancel)[0]] != 0)
+
 // 128-bit read-only streaming load that does not allocate in L1 (weights are read exactly once per launch)
 __device__ __forceinline__ int4 ld_stream_v4(const void * p) {
     int4 r;

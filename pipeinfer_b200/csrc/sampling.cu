@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(SMP_THREADS) sample_topk_kernel(float * __rest
     (void) desc;
     pib_pdl_wait();
     pib_pdl_trigger();
-    if (cancel && *cancel) return;
+    if (PIB_CANCELLED(cancel)) return;
     __shared__ float  s_val[SMP_THREADS / 32];
     __shared__ int    s_idx[SMP_THREADS / 32];
     __shared__ double s_sum[SMP_THREADS / 32];

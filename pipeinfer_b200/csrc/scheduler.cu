@@ -86,6 +86,21 @@ class Scheduler {
     Run current;                          // the run whose logits are being verified (only the scalar fields are used)
     Batch batch_tgt, batch_dft;
 
+    // optional event trace (env PIB_TRACE=<file>): time in us since the start of the generation, event, a, b, c
+    struct Ev { int64_t t; const char * what; int a, b, c; };
+    std::vector<Ev> trace;
+    bool            tracing = getenv("PIB_TRACE") != nullptr;
+    int64_t         t_trace0 = 0;
+    void ev(const char * what, int a = 0, int b = 0, int c = 0) { if (tracing) trace.push_back({ llama_time_us() - t_trace0, what, a, b, c }); }
+    void dump_trace() {
+        if (!tracing) return;
+        FILE * f = fopen(getenv("PIB_TRACE"), "a");
+        if (!f) return;
+        fprintf(f, "# generation\n");
+        for (const Ev & e : trace) fprintf(f, "%lld %s %d %d %d\n", (long long) e.t, e.what, e.a, e.b, e.c);
+        fclose(f);
+    }
+
     static llama_token greedy(llama_context * c, int row) { llama_token_data t[8]; llama_pib_get_top8(c, row, t); return t[0].id; }
 
     void check_for_cancel();
@@ -124,7 +139,7 @@ void Scheduler::check_for_cancel() {
             run.canceled = true;
         }
     }
-    if (!ids.empty()) { n_cancel += (int) ids.size(); llama_cancel_run(ctx_tgt, ids.data(), (int) ids.size()); }
+    if (!ids.empty()) { n_cancel += (int) ids.size(); llama_cancel_run(ctx_tgt, ids.data(), (int) ids.size()); ev("cancel", (int) ids.size(), ids[0]); }
 }
 
 // :1182-1275
@@ -141,6 +156,7 @@ void Scheduler::begin_async_run(llama_context * ctx, std::deque<Run> & q, const 
     if (!is_spec) { for (int i = 0; i <= max_seq; i++) llama_kv_cache_seq_rm(ctx, i, n_past, n_past + 1); }        // :1252-1255
     else          { for (int i = 0; i < np; i++) llama_kv_cache_seq_rm(ctx, i + seq_offset, n_past, n_past + 1); } // :1256-1260
     run.handle = llama_start_async_decode(*ctx, run.batch.view(max_seq + 1));                                      // :1261
+    if (ctx == ctx_tgt) ev(is_spec ? "start_spec" : "start_nonspec", batch_id, (int) run.batch.size(), n_past);
     if (!run.handle) failed = true;     // no KV slot left: the reference would spin forever here
     q.push_front(std::move(run));
     if (!is_spec) for (int i = 1; i <= max_seq; i++) llama_kv_cache_seq_cp(ctx, 0, i, n_past, n_past + 1);         // :1264-1268
@@ -221,6 +237,7 @@ bool Scheduler::start_spec_run(int prefix_n_past, int n_past_dft_arg, int orig_o
         }
         if (batch_dft.size() == 0) break;
         llama_decode(ctx_dft, batch_dft.view(max_seq + 1));                                              // :1090 synchronous draft step
+        ev("draft_step", (int) batch_dft.size());
         ++n_past_cur;
         ++n_drafted;
         max_ran_seq = n_seq_cur;
@@ -256,6 +273,7 @@ void Scheduler::speculation_loop() {
     int   iter = 0;
     float p_adjust;
     while (!is_waiting && P.p_accept + (p_adjust = p_adjust_of(iter)) < 1.0f) {
+        if (P.max_spec_runs > 0 && (int) tgt_runs.size() >= P.max_spec_runs) break;   // optional bound (0 = reference behaviour)
         const int orig_offset = current.seq_offset;
         bool should_run = true;
         do {                                                                                             // :791-807
@@ -275,7 +293,6 @@ void Scheduler::speculation_loop() {
         is_waiting = llama_mpi_iprobe(ctx_tgt);
         first_run  = false;
         iter++;
-        if (P.max_spec_runs > 0 && (int) tgt_runs.size() >= P.max_spec_runs) break;   // optional bound (0 = reference behaviour)
     }
 }
 
@@ -307,6 +324,7 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
     int64_t ttft = llama_time_us(), itt_start = 0;
     std::vector<int64_t> itl;
     const int64_t t_dec_start = llama_time_us();
+    t_trace0 = t_dec_start;
     first_run = true;
     int n_out = 0;
 
@@ -318,6 +336,7 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
             Run & run = tgt_runs.back();
             if (run.canceled) {
                 llama_finish_async_decode(*ctx_tgt, run.batch.view(max_seq + 1), run.handle);           // drain (:366)
+                ev("finish_cancelled", run.batch.batch_id);
                 if (run.speculative) free_offsets.push_back(run.seq_offset);
                 tgt_runs.pop_back();
                 continue;
@@ -328,6 +347,7 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
             s_keep = run.s_keep;
             for (int s = 0; s < np; ++s) if (drafts[s].active) drafts[s].tokens.erase(drafts[s].tokens.begin());
             llama_finish_async_decode(*ctx_tgt, run.batch.view(max_seq + 1), run.handle);
+            ev("finish", run.batch.batch_id, run.speculative ? 1 : 0, (int) run.batch.size());
             tgt_runs.pop_back();
             spec_past_tgt = n_past_tgt; spec_past_dft = n_past_dft;
             first_run = true;
@@ -373,10 +393,12 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
             }
         }
         if (!any_match) {                                                                                // :569-577
+            ev("no_new_token", current.n_past_tgt, i_dft);
             if (current.speculative) free_offsets.push_back(current.seq_offset);
             continue;
         }
         n_rejected = 0;
+        ev("accepted", n_past_tgt, i_dft, current.speculative ? 1 : 0);
         check_for_cancel();                                                                              // :581
 
         if (current.speculative) {                                                                       // :585-628 KV commit
@@ -417,6 +439,8 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
         if (n_predict > P.n_predict || has_eos || failed) break;                                         // :672
     }
     const int64_t t_dec_end = llama_time_us();
+    ev("end", n_predict);
+    dump_trace();
     for (int i = (int) tgt_runs.size() - 1; i >= 0; i--) llama_finish_async_decode(*ctx_tgt, tgt_runs[i].batch.view(max_seq + 1), tgt_runs[i].handle);
     tgt_runs.clear();
     if (res) {

@@ -93,6 +93,7 @@ def api():
     L.llama_pib_kv_words.argtypes = [C.c_void_p]
     L.llama_pib_kernel_launches.restype = C.c_uint64
     L.llama_pib_kernel_launches.argtypes = [C.c_void_p]
+    L.llama_pib_set_priority.argtypes = [C.c_void_p, C.c_int]
     L.llama_pib_weight_bytes.restype = C.c_size_t
     L.llama_pib_weight_bytes.argtypes = [C.c_void_p]
     _bound = True
@@ -139,6 +140,10 @@ class Context:
         self.n_ctx = n_ctx
         self.max_seq = max_seq
         self._bid = 0
+
+    def set_priority(self, high=True):
+        if self.L.llama_pib_set_priority(self.ctx, 1 if high else 0) != 0:
+            raise PibError("llama_pib_set_priority failed")
 
     def decode(self, tokens, pos, seq_lists):
         b, keep = make_batch(tokens, pos, seq_lists, self._bid, self.max_seq)
