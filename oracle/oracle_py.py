@@ -39,7 +39,10 @@ class Model(C.Structure):
                 ("wo", C.POINTER(C.c_void_p)),
                 ("ffn_norm", C.POINTER(C.c_void_p)),
                 ("ffn_gate", C.POINTER(C.c_void_p)), ("ffn_down", C.POINTER(C.c_void_p)),
-                ("ffn_up", C.POINTER(C.c_void_p))]
+                ("ffn_up", C.POINTER(C.c_void_p)),
+                ("arch", C.c_int32), ("norm_eps", C.c_float),
+                ("attn_norm_b", C.POINTER(C.c_void_p)), ("attn_norm2", C.POINTER(C.c_void_p)),
+                ("attn_norm2_b", C.POINTER(C.c_void_p)), ("output_norm_b", C.c_void_p)]
 
 
 class KvMeta(C.Structure):
@@ -246,6 +249,22 @@ def load_gguf_model(path):
     m.tok_embd = p("token_embd.weight")
     m.output_norm = p("output_norm.weight")
     m.output = p("output.weight")
+    if arch == "falcon":
+        m.arch = 1
+        m.norm_eps = float(kv.get(arch + ".attention.layer_norm_epsilon", 1e-5))
+        m.output_norm_b = p("output_norm.bias")
+        m.attn_norm = arr("blk.%d.attn_norm.weight")
+        m.attn_norm_b = arr("blk.%d.attn_norm.bias")
+        if "blk.0.attn_norm_2.weight" in t:
+            m.attn_norm2 = arr("blk.%d.attn_norm_2.weight")
+            m.attn_norm2_b = arr("blk.%d.attn_norm_2.bias")
+        m.wq = arr("blk.%d.attn_qkv.weight")
+        m.wo = arr("blk.%d.attn_output.weight")
+        m.ffn_down = arr("blk.%d.ffn_down.weight")
+        m.ffn_up = arr("blk.%d.ffn_up.weight")
+        m._keep = keep
+        m._reader = r
+        return m
     m.attn_norm = arr("blk.%d.attn_norm.weight")
     m.wq = arr("blk.%d.attn_q.weight")
     m.wk = arr("blk.%d.attn_k.weight")

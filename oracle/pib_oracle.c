@@ -568,6 +568,98 @@ static void dequant_row(int type, const void * w, int64_t row, int64_t k, float 
     }
 }
 
+/* llm_build_norm with LLM_NORM (llama.cpp:3578-3600): ggml_norm, then ggml_mul by the weight, then ggml_add of the bias */
+static void layer_norm_rows(const float * x, float * y, int T, int E, float eps, const float * w, const float * b) {
+    for (int t = 0; t < T; t++) {
+        po_norm(x + (size_t) t * E, y + (size_t) t * E, E, eps);
+        for (int i = 0; i < E; i++) y[(size_t) t * E + i] = y[(size_t) t * E + i] * w[i];
+        for (int i = 0; i < E; i++) y[(size_t) t * E + i] = y[(size_t) t * E + i] + b[i];
+    }
+}
+
+/* masked multi-sequence attention of one layer (llm_build_kqv llama.cpp:3698): shared by both architectures */
+static void attention_rows(const po_context * c, int il, int T, int n_kv, const uint8_t * mask, const float * q, float * att,
+                           float * kq, po_fp16 * q16, po_fp16 * p16) {
+    const po_model * m = c->model;
+    const int E = m->n_embd, H = m->n_head, HKV = m->n_head_kv, hd = E / H, GQA = hd * HKV, NC = (int) c->n_ctx;
+    const po_fp16 * kl = c->k + (size_t) il * NC * GQA;
+    const po_fp16 * vl = c->v + (size_t) il * NC * GQA;
+    const float kq_scale = 1.0f / sqrtf((float) hd);
+    for (int t = 0; t < T; t++) {
+        for (int h = 0; h < H; h++) {
+            const int hk = h / (H / HKV);
+            for (int i = 0; i < hd; i++) q16[i] = po_fp32_to_fp16(q[(size_t) t * E + h * hd + i]);
+            for (int i = 0; i < n_kv; i++) {
+                float s;
+                po_vec_dot_f16(hd, &s, kl + (size_t) i * GQA + hk * hd, q16);
+                s *= kq_scale;
+                kq[i] = mask[(size_t) t * n_kv + i] ? -INFINITY : s + 0.0f;
+            }
+            po_soft_max(kq, n_kv);
+            for (int i = 0; i < n_kv; i++) p16[i] = po_fp32_to_fp16(kq[i]);
+            for (int d = 0; d < hd; d++) {
+                float s;
+                po_vec_dot_f16(n_kv, &s, vl + (size_t) (hk * hd + d) * NC, p16);
+                att[(size_t) t * E + h * hd + d] = s;
+            }
+        }
+    }
+}
+
+/* build_falcon (llama.cpp:4106-4225) inside the decode of :5461-5726 */
+static int decode_falcon(po_context * c, int T, const int32_t * token, const int32_t * pos, int n_kv, uint32_t kv_head,
+                         const uint8_t * mask, float * logits) {
+    const po_model * m = c->model;
+    const int E = m->n_embd, H = m->n_head, HKV = m->n_head_kv, hd = E / H, GQA = hd * HKV, FF = m->n_ff, NC = (int) c->n_ctx;
+    const int NQKV = E + 2 * GQA;
+    float * inpL = (float *) malloc(4 * (size_t) T * E);
+    float * an   = (float *) malloc(4 * (size_t) T * E);      /* attn_norm output: feeds the MLP (and QKV in the 7B layout) */
+    float * an2  = (float *) malloc(4 * (size_t) T * E);
+    float * qkv  = (float *) malloc(4 * (size_t) T * NQKV);
+    float * q    = (float *) malloc(4 * (size_t) T * E);
+    float * kc   = (float *) malloc(4 * (size_t) T * GQA);
+    float * att  = (float *) malloc(4 * (size_t) T * E);
+    float * ao   = (float *) malloc(4 * (size_t) T * E);
+    float * up   = (float *) malloc(4 * (size_t) T * FF);
+    float * fo   = (float *) malloc(4 * (size_t) T * E);
+    float * kq   = (float *) malloc(4 * (size_t) n_kv);
+    po_fp16 * q16 = (po_fp16 *) malloc(2 * (size_t) hd);
+    po_fp16 * p16 = (po_fp16 *) malloc(2 * (size_t) n_kv);
+    for (int t = 0; t < T; t++) dequant_row(m->wtype, m->tok_embd, token[t], E, inpL + (size_t) t * E);
+    for (int il = 0; il < m->n_layer; il++) {
+        po_fp16 * kl = c->k + (size_t) il * NC * GQA;
+        po_fp16 * vl = c->v + (size_t) il * NC * GQA;
+        layer_norm_rows(inpL, an, T, E, m->norm_eps, m->attn_norm[il], m->attn_norm_b[il]);
+        const float * qin = an;
+        if (m->attn_norm2 && m->attn_norm2[il]) {                                            /* Falcon-40B :4137-4147 */
+            layer_norm_rows(inpL, an2, T, E, m->norm_eps, m->attn_norm2[il], m->attn_norm2_b[il]);
+            qin = an2;
+        }
+        po_mul_mat(m->wtype, m->wq[il], NQKV, E, qin, T, qkv);                                /* wqkv :4149 */
+        for (int t = 0; t < T; t++) {                                                        /* ggml_cont of the three views */
+            memcpy(q + (size_t) t * E, qkv + (size_t) t * NQKV, 4 * (size_t) E);
+            memcpy(kc + (size_t) t * GQA, qkv + (size_t) t * NQKV + E, 4 * (size_t) GQA);
+            po_rope(q + (size_t) t * E, H, hd, hd, pos[t], 2, m->rope_freq_base, m->rope_freq_scale);      /* NeoX :4163-4173 */
+            po_rope(kc + (size_t) t * GQA, HKV, hd, hd, pos[t], 2, m->rope_freq_base, m->rope_freq_scale);
+            for (int i = 0; i < GQA; i++) {
+                kl[(size_t) (kv_head + t) * GQA + i] = po_fp32_to_fp16(kc[(size_t) t * GQA + i]);
+                vl[(size_t) i * NC + kv_head + t]    = po_fp32_to_fp16(qkv[(size_t) t * NQKV + E + GQA + i]);
+            }
+        }
+        attention_rows(c, il, T, n_kv, mask, q, att, kq, q16, p16);
+        po_mul_mat(m->wtype, m->wo[il], E, E, att, T, ao);                                    /* kqv_out */
+        po_mul_mat(m->wtype, m->ffn_up[il], FF, E, an, T, up);                                /* the MLP reads attn_norm :4187 */
+        po_gelu(up, T * FF);
+        po_mul_mat(m->wtype, m->ffn_down[il], E, FF, up, T, fo);
+        for (size_t i = 0; i < (size_t) T * E; i++) fo[i] = fo[i] + ao[i];                    /* :4197 */
+        for (size_t i = 0; i < (size_t) T * E; i++) inpL[i] = fo[i] + inpL[i];                /* :4200 */
+    }
+    layer_norm_rows(inpL, an, T, E, m->norm_eps, m->output_norm, m->output_norm_b);
+    po_mul_mat(m->wtype, m->output, m->n_vocab, E, an, T, logits);
+    free(inpL); free(an); free(an2); free(qkv); free(q); free(kc); free(att); free(ao); free(up); free(fo); free(kq); free(q16); free(p16);
+    return 0;
+}
+
 /* llama.cpp:5461-5726 (phase 0) + build_llama :3872-3980 + llm_build_kv_store :3546 + llm_build_kqv :3698 */
 int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t * pos, const int32_t * n_seq_id,
               const int32_t * const * seq_id, float * logits) {
@@ -588,6 +680,13 @@ int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t
     uint8_t *      mask    = (uint8_t *) malloc((size_t) T * n_kv);
     po_kv_mask(kv, T, n_kv, pos, n_seq_id, seq_id, mask);
     const float kq_scale = 1.0f / sqrtf((float) hd);                                /* :5189 */
+    if (m->arch == 1) {
+        const int rc = decode_falcon(c, T, token, pos, n_kv, kv_head, mask, logits);
+        kv->head += (uint32_t) T;
+        if (kv->head >= kv->size) kv->head = 0;
+        free(mask);
+        return rc;
+    }
 
     float * inpL = (float *) malloc(4 * (size_t) T * E);
     float * cur  = (float *) malloc(4 * (size_t) T * E);

@@ -95,6 +95,12 @@ typedef struct {
     const void **  wq, ** wk, ** wv, ** wo;
     const float ** ffn_norm;
     const void **  ffn_gate, ** ffn_down, ** ffn_up;
+    /* falcon architecture (build_falcon llama.cpp:4106): arch = 1.  wq[il] then holds the fused attn_qkv matrix
+     * [n_embd + 2 n_embd_gqa][n_embd]; attn_norm2 entries are NULL in the 7B layout */
+    int32_t        arch;
+    float          norm_eps;
+    const float ** attn_norm_b, ** attn_norm2, ** attn_norm2_b;
+    const float *  output_norm_b;
 } po_model;
 
 typedef struct {

@@ -14,15 +14,18 @@
 //   PRO_GELU      v = gelu_f16lut(x)                             (ggml.c:1433; falcon MLP)
 #include "pib_common.cuh"
 
-enum { PRO_PLAIN = 0, PRO_RMSNORM = 1, PRO_SILU_MUL = 2, PRO_GELU = 3 };
+enum { PRO_PLAIN = 0, PRO_RMSNORM = 1, PRO_SILU_MUL = 2, PRO_GELU = 3, PRO_LAYERNORM = 4 };
 
 #define AQ_THREADS 256
 
 template <int PRO>
 __device__ __forceinline__ float aq_value(const float * xr, const float * __restrict__ x2r, float scale,
-                                          const uint16_t * __restrict__ lut, int64_t i) {
+                                          const uint16_t * __restrict__ lut, int64_t i, float mean = 0.f,
+                                          const float * __restrict__ biasr = nullptr) {
     const float x = xr[i];
     if (PRO == PRO_RMSNORM) return __fmul_rn(__fmul_rn(x, scale), x2r[i]);
+    // reference norm_f32 (ggml.c:8959-9020): y = (x - mean) * scale, then ggml_mul by the weight, ggml_add of the bias
+    if (PRO == PRO_LAYERNORM) return __fadd_rn(__fmul_rn(__fmul_rn(__fsub_rn(x, mean), scale), x2r[i]), biasr[i]);
     if (PRO == PRO_SILU_MUL) return __fmul_rn(pib_h2f(lut[pib_f2h(x)]), x2r[i]);
     if (PRO == PRO_GELU) return pib_h2f(lut[pib_f2h(x)]);
     return x;
@@ -31,17 +34,19 @@ __device__ __forceinline__ float aq_value(const float * xr, const float * __rest
 // eight consecutive values (32-byte aligned) with two 128-bit loads per operand
 template <int PRO>
 __device__ __forceinline__ void aq_value8(const float * xr, const float * __restrict__ x2r, float scale,
-                                          const uint16_t * __restrict__ lut, int64_t i0, float * v) {
+                                          const uint16_t * __restrict__ lut, int64_t i0, float * v, float mean = 0.f,
+                                          const float * __restrict__ biasr = nullptr) {
     const float4 xa = *reinterpret_cast<const float4 *>(xr + i0), xb = *reinterpret_cast<const float4 *>(xr + i0 + 4);
     const float  x[8] = { xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w };
     float        w[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
-    if (PRO == PRO_RMSNORM || PRO == PRO_SILU_MUL) {
+    if (PRO == PRO_RMSNORM || PRO == PRO_SILU_MUL || PRO == PRO_LAYERNORM) {
         const float4 wa = *reinterpret_cast<const float4 *>(x2r + i0), wb = *reinterpret_cast<const float4 *>(x2r + i0 + 4);
         w[0] = wa.x; w[1] = wa.y; w[2] = wa.z; w[3] = wa.w; w[4] = wb.x; w[5] = wb.y; w[6] = wb.z; w[7] = wb.w;
     }
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         if (PRO == PRO_RMSNORM)       v[j] = __fmul_rn(__fmul_rn(x[j], scale), w[j]);
+        else if (PRO == PRO_LAYERNORM) v[j] = __fadd_rn(__fmul_rn(__fmul_rn(__fsub_rn(x[j], mean), scale), w[j]), biasr[i0 + j]);
         else if (PRO == PRO_SILU_MUL) v[j] = __fmul_rn(pib_h2f(lut[pib_f2h(x[j])]), w[j]);
         else if (PRO == PRO_GELU)     v[j] = pib_h2f(lut[pib_f2h(x[j])]);
         else                          v[j] = x[j];
@@ -57,7 +62,8 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
                                                                float * __restrict__ vout,
                                                                const uint16_t * __restrict__ lut,
                                                                const float * __restrict__ addend, float * sum_out,
-                                                               const int * __restrict__ cancel, int64_t xstride) {
+                                                               const int * __restrict__ cancel, int64_t xstride,
+                                                               const float * __restrict__ bias, const float * __restrict__ addend2) {
     pib_pdl_wait();
     pib_pdl_trigger();
     if (PIB_CANCELLED(cancel)) return;
@@ -67,8 +73,8 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
     const int     lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int     nwarp = AQ_THREADS / 32;
 
-    float scale = 1.0f;
-    if (PRO == PRO_RMSNORM) {
+    float scale = 1.0f, mean = 0.0f;
+    if (PRO == PRO_RMSNORM || PRO == PRO_LAYERNORM) {
         __shared__ double red[AQ_THREADS / 32];
         __shared__ float  s_scale;
         double            s = 0.0;
@@ -77,6 +83,7 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
         //  write the same sums, so pass 2 never depends on another CTA).  128-bit loads, four in flight per thread.
         const float4 * __restrict__ x4 = reinterpret_cast<const float4 *>(xr);
         const float4 * __restrict__ a4 = addend ? reinterpret_cast<const float4 *>(addend + (size_t) row * K) : nullptr;
+        const float4 * __restrict__ b4 = addend2 ? reinterpret_cast<const float4 *>(addend2 + (size_t) row * K) : nullptr;   // (x + addend) + addend2
         float4 *                    o4 = sum_out ? reinterpret_cast<float4 *>(sum_out + (size_t) row * K) : nullptr;
         const int n4 = (int) (K / 4);
 #pragma unroll 4
@@ -85,33 +92,75 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
             if (a4) {
                 const float4 a = a4[i];
                 v.x = __fadd_rn(v.x, a.x); v.y = __fadd_rn(v.y, a.y); v.z = __fadd_rn(v.z, a.z); v.w = __fadd_rn(v.w, a.w);
+                if (b4) {
+                    const float4 c2 = b4[i];
+                    v.x = __fadd_rn(v.x, c2.x); v.y = __fadd_rn(v.y, c2.y); v.z = __fadd_rn(v.z, c2.z); v.w = __fadd_rn(v.w, c2.w);
+                }
                 o4[i] = v;
             }
-            s += (double) __fmul_rn(v.x, v.x);
-            s += (double) __fmul_rn(v.y, v.y);
-            s += (double) __fmul_rn(v.z, v.z);
-            s += (double) __fmul_rn(v.w, v.w);
+            if (PRO == PRO_LAYERNORM) {
+                s += (double) v.x; s += (double) v.y; s += (double) v.z; s += (double) v.w;
+            } else {
+                s += (double) __fmul_rn(v.x, v.x);
+                s += (double) __fmul_rn(v.y, v.y);
+                s += (double) __fmul_rn(v.z, v.z);
+                s += (double) __fmul_rn(v.w, v.w);
+            }
         }
         if (a4) xr = sum_out + (size_t) row * K;     // pass 2 re-reads the sums (visible CTA-wide after the barrier below)
         s = warp_sum_d(s);
         if (lane == 0) red[warp] = s;
         __syncthreads();
-        if (threadIdx.x == 0) {
-            double t = 0.0;
-            for (int w = 0; w < nwarp; w++) t += red[w];
-            const float mean = (float) (t / (double) K);
-            s_scale          = 1.0f / sqrtf(mean + eps);
+        if (PRO == PRO_RMSNORM) {
+            if (threadIdx.x == 0) {
+                double t = 0.0;
+                for (int w = 0; w < nwarp; w++) t += red[w];
+                const float ms = (float) (t / (double) K);
+                s_scale        = 1.0f / sqrtf(ms + eps);
+            }
+            __syncthreads();
+            scale = s_scale;
+        } else {
+            // LayerNorm (reference norm_f32, ggml.c:8959-9020): mean from the double sum, then the double sum of the float
+            // squares of (x - mean), scale = 1 / sqrtf(variance + eps)
+            __shared__ float s_mean;
+            if (threadIdx.x == 0) {
+                double t = 0.0;
+                for (int w = 0; w < nwarp; w++) t += red[w];
+                s_mean = (float) (t / (double) K);
+            }
+            __syncthreads();
+            mean = s_mean;
+            double s2 = 0.0;
+            const float4 * v4 = reinterpret_cast<const float4 *>(xr);
+#pragma unroll 4
+            for (int i = threadIdx.x; i < n4; i += AQ_THREADS) {
+                const float4 v = v4[i];
+                const float  d0 = __fsub_rn(v.x, mean), d1 = __fsub_rn(v.y, mean), d2 = __fsub_rn(v.z, mean), d3 = __fsub_rn(v.w, mean);
+                s2 += (double) __fmul_rn(d0, d0); s2 += (double) __fmul_rn(d1, d1); s2 += (double) __fmul_rn(d2, d2); s2 += (double) __fmul_rn(d3, d3);
+            }
+            s2 = warp_sum_d(s2);
+            __syncthreads();
+            if (lane == 0) red[warp] = s2;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                double t = 0.0;
+                for (int w = 0; w < nwarp; w++) t += red[w];
+                const float var = (float) (t / (double) K);
+                s_scale         = 1.0f / sqrtf(var + eps);
+            }
+            __syncthreads();
+            scale = s_scale;
         }
-        __syncthreads();
-        scale = s_scale;
     }
+    const float * biasr = bias;
 
     if (!Q8K) {
         // one warp per 32-element block, lane == element
         const int64_t nb = K / PIB_QK;
         for (int64_t blk = (int64_t) blockIdx.y * nwarp + warp; blk < nb; blk += (int64_t) gridDim.y * nwarp) {
             const int64_t i    = blk * PIB_QK + lane;
-            const float   v    = aq_value<PRO>(xr, x2r, scale, lut, i);
+            const float   v    = aq_value<PRO>(xr, x2r, scale, lut, i, mean, biasr);
             const float   amax = warp_max(fabsf(v));
             const float   d    = amax / 127.f;
             const float   id   = (amax != 0.0f) ? 127.f / amax : 0.0f;
@@ -133,7 +182,7 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
         for (int64_t sb = (int64_t) blockIdx.y * nwarp + warp; sb < nsb; sb += (int64_t) gridDim.y * nwarp) {
             const int64_t i0 = sb * PIB_QK_K + lane * 8;
             float v[8];
-            aq_value8<PRO>(xr, x2r, scale, lut, i0, v);
+            aq_value8<PRO>(xr, x2r, scale, lut, i0, v, mean, biasr);
             // first element (in index order) with the largest |x|: strict '>' scan, ties keep the lower index
             float amax = 0.0f, mx = 0.0f;
             int   idx  = 1 << 30;
@@ -188,7 +237,8 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
 template <int PRO>
 static int launch_aq(int wtype, const float * x, const float * x2, int x2_per_row, float eps, int b, int64_t K, void * act,
                      float * vout, const uint16_t * lut, cudaStream_t st, const float * addend = nullptr,
-                     float * sum_out = nullptr, const int * cancel = nullptr, int64_t xstride = 0) {
+                     float * sum_out = nullptr, const int * cancel = nullptr, int64_t xstride = 0, const float * bias = nullptr,
+                     const float * addend2 = nullptr) {
     if (xstride == 0) xstride = K;
     const pib_act_layout L = pib_act_layout_of(wtype, K, b);
     int8_t * qs = (int8_t *) act + L.qs_off;
@@ -199,8 +249,8 @@ static int launch_aq(int wtype, const float * x, const float * x2, int x2_per_ro
     const int64_t units = wtype == PIB_TYPE_Q4_K ? K / PIB_QK_K : K / PIB_QK / 4;        // super-blocks, or groups of 4 blocks
     const int     parts = (int) max((int64_t) 1, min((int64_t) 32, units / (AQ_THREADS / 32)));
     const dim3    grid(b, parts);
-    if (wtype == PIB_TYPE_Q4_K) pib_launch(act_quant_kernel<true, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride);
-    else                        pib_launch(act_quant_kernel<false, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride);
+    if (wtype == PIB_TYPE_Q4_K) pib_launch(act_quant_kernel<true, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride, bias, addend2);
+    else                        pib_launch(act_quant_kernel<false, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride, bias, addend2);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }
@@ -249,6 +299,21 @@ int pib_add_rmsnorm_quantize_act(int wtype, const float * x_dev, const float * a
     if (check_args(wtype, b, K) != PIB_OK) return PIB_ERR_ARG;
     return launch_aq<PRO_RMSNORM>(wtype, x_dev, norm_w_dev, 0, eps, b, K, act_dev, nullptr, nullptr, st, addend_dev, sum_out_dev,
                                   cancel);
+}
+
+// falcon: [sum_out = (x + addend) + addend2;] act = quantise(layernorm(sum or x) * w + bias)
+int pib_add_layernorm_quantize_act(int wtype, const float * x_dev, const float * addend_dev, const float * addend2_dev,
+                                   float * sum_out_dev, const float * norm_w_dev, const float * norm_b_dev, float eps, int b,
+                                   int64_t K, void * act_dev, const int * cancel, cudaStream_t st) {
+    if (check_args(wtype, b, K) != PIB_OK) return PIB_ERR_ARG;
+    return launch_aq<PRO_LAYERNORM>(wtype, x_dev, norm_w_dev, 0, eps, b, K, act_dev, nullptr, nullptr, st, addend_dev, sum_out_dev,
+                                    cancel, 0, norm_b_dev, addend2_dev);
+}
+
+// falcon: act = quantise(gelu(x)) through the reference's fp16 table (ggml.c:8676)
+int pib_gelu_quantize_act(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, const int * cancel, cudaStream_t st) {
+    if (check_args(wtype, b, K) != PIB_OK) return PIB_ERR_ARG;
+    return launch_aq<PRO_GELU>(wtype, x_dev, nullptr, 0, 0.f, b, K, act_dev, nullptr, pib_get_luts().gelu_f16, st, nullptr, nullptr, cancel);
 }
 
 extern "C" int pib_act_to_blocks(int wtype, const void * act_dev, int b, int64_t K, void * out) {

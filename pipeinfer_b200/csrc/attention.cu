@@ -351,6 +351,7 @@ bool pib_attention_supported(int hd, int n_head, int n_head_kv, int n_ctx) {
     if (hd != 64 && hd != 128) return false;
     if (n_head % n_head_kv) return false;
     const int G = n_head / n_head_kv;
+    if (n_ctx <= 4096) return true;                       // per-query-head kernel: any group size (falcon-7B: 71 heads on one KV head)
     if (G != 1 && G != 2 && G != 4 && G != 8) return false;
     const size_t smem = ((size_t) G * n_ctx + (size_t) (ATT_THREADS / (hd / 2)) * G * hd) * sizeof(float);
     return smem <= 220 * 1024;

@@ -27,6 +27,10 @@ int  pib_silu_mul_quantize_act(int wtype, const float * gate_dev, const float * 
 int  pib_quantize_act_c(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, const int * cancel, cudaStream_t st);
 int  pib_add_rmsnorm_quantize_act(int wtype, const float * x_dev, const float * addend_dev, float * sum_out_dev,
                                   const float * norm_w_dev, float eps, int b, int64_t K, void * act_dev, const int * cancel, cudaStream_t st);
+int  pib_add_layernorm_quantize_act(int wtype, const float * x_dev, const float * addend_dev, const float * addend2_dev,
+                                    float * sum_out_dev, const float * norm_w_dev, const float * norm_b_dev, float eps, int b,
+                                    int64_t K, void * act_dev, const int * cancel, cudaStream_t st);
+int  pib_gelu_quantize_act(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, const int * cancel, cudaStream_t st);
 void rope_table_build(std::vector<float2> & tab, int n_pos, int n_dims, int mode, float freq_base, float freq_scale);
 int  pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * rope, int rope_n_pos, int n_tokens, int E, int GQA,
                        int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st);
@@ -83,8 +87,9 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
     GgufFile g;
     if (!g.open(path)) { pib_set_error("gguf: %s", g.error.c_str()); return nullptr; }
     const std::string arch = g.get_s("general.architecture", "");
-    if (arch != "llama") { pib_set_error("gguf: architecture '%s' not supported (llama only)", arch.c_str()); return nullptr; }
+    if (arch != "llama" && arch != "falcon") { pib_set_error("gguf: architecture '%s' not supported (llama, falcon)", arch.c_str()); return nullptr; }
     pib_model * m = new pib_model();
+    m->arch = arch == "falcon" ? 1 : 0;
     m->name        = g.get_s("general.name", "");
     m->n_layer     = (int) g.get_i(arch + ".block_count", 0);
     m->n_embd      = (int) g.get_i(arch + ".embedding_length", 0);
@@ -94,6 +99,7 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
     m->n_ctx_train = (int) g.get_i(arch + ".context_length", 2048);
     m->n_rot       = (int) g.get_i(arch + ".rope.dimension_count", m->n_head ? m->n_embd / m->n_head : 0);
     m->rms_eps        = (float) g.get_f(arch + ".attention.layer_norm_rms_epsilon", 1e-5);
+    m->norm_eps       = (float) g.get_f(arch + ".attention.layer_norm_epsilon", 1e-5);
     m->rope_freq_base = (float) g.get_f(arch + ".rope.freq_base", 10000.0);
     m->tok_bos = (int) g.get_i("tokenizer.ggml.bos_token_id", 1);
     m->tok_eos = (int) g.get_i("tokenizer.ggml.eos_token_id", 2);
@@ -109,6 +115,7 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
         delete m;
         return nullptr;
     }
+    if (m->n_ff <= 0) { const GgufTensor * up = g.tensor("blk.0.ffn_up.weight"); if (up) m->n_ff = (int) up->ne[1]; }
     if (layer_end <= 0 || layer_end > m->n_layer) layer_end = m->n_layer;
     m->layer_begin = layer_begin;
     m->layer_end   = layer_end;
@@ -120,10 +127,27 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
         m->output_norm = upload_f32(g.tensor("output_norm.weight"), E);
         m->output      = upload_concat({ g.tensor("output.weight") }, m->wtype, E);
         ok = ok && m->output_norm && m->output;
+        if (m->arch == 1) { m->output_norm_b = upload_f32(g.tensor("output_norm.bias"), E); ok = ok && m->output_norm_b; }
     }
     for (int il = layer_begin; il < layer_end && ok; il++) {
         const std::string p = "blk." + std::to_string(il) + ".";
         pib_layer & L = m->layers[il];
+        if (m->arch == 1) {                                   // falcon tensor table (reference llama.cpp:2769-2811)
+            L.attn_norm   = upload_f32(g.tensor(p + "attn_norm.weight"), E);
+            L.attn_norm_b = upload_f32(g.tensor(p + "attn_norm.bias"), E);
+            if (g.tensor(p + "attn_norm_2.weight")) {
+                L.attn_norm2   = upload_f32(g.tensor(p + "attn_norm_2.weight"), E);
+                L.attn_norm2_b = upload_f32(g.tensor(p + "attn_norm_2.bias"), E);
+                ok = ok && L.attn_norm2 && L.attn_norm2_b;
+            }
+            L.wqkv  = upload_concat({ g.tensor(p + "attn_qkv.weight") }, m->wtype, E);
+            L.wo    = upload_concat({ g.tensor(p + "attn_output.weight") }, m->wtype, E);
+            L.wgu   = upload_concat({ g.tensor(p + "ffn_up.weight") }, m->wtype, E);
+            L.wdown = upload_concat({ g.tensor(p + "ffn_down.weight") }, m->wtype, FF);
+            ok = ok && L.attn_norm && L.attn_norm_b && L.wqkv && L.wo && L.wgu && L.wdown;
+            if (ok) m->weight_bytes += pib_weight_bytes(L.wqkv) + pib_weight_bytes(L.wo) + pib_weight_bytes(L.wgu) + pib_weight_bytes(L.wdown);
+            continue;
+        }
         L.attn_norm = upload_f32(g.tensor(p + "attn_norm.weight"), E);
         L.ffn_norm  = upload_f32(g.tensor(p + "ffn_norm.weight"), E);
         L.wqkv  = upload_concat({ g.tensor(p + "attn_q.weight"), g.tensor(p + "attn_k.weight"), g.tensor(p + "attn_v.weight") }, m->wtype, E);
@@ -293,7 +317,9 @@ void pib_model_free(pib_model * m) {
     pib_weight_free(m->tok_embd);
     pib_weight_free(m->output);
     if (m->output_norm) cudaFree(m->output_norm);
+    if (m->output_norm_b) cudaFree(m->output_norm_b);
     for (auto & L : m->layers) {
+        for (float * f : { L.attn_norm_b, L.attn_norm2, L.attn_norm2_b }) if (f) cudaFree(f);
         if (L.attn_norm) cudaFree(L.attn_norm);
         if (L.ffn_norm) cudaFree(L.ffn_norm);
         pib_weight_free(L.wqkv); pib_weight_free(L.wo); pib_weight_free(L.wgu); pib_weight_free(L.wdown);
@@ -340,7 +366,7 @@ pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_st
     actb = std::max(pib_act_bytes(m->wtype, E, B), pib_act_bytes(m->wtype, FF, B));
     CK(cudaMalloc(&c->act, actb));
     c->rope_n_pos = (int) std::max<uint32_t>(n_ctx, (uint32_t) m->n_ctx_train) + 64;
-    rope_table_build(tab, c->rope_n_pos, m->n_rot, 0, m->rope_freq_base, m->rope_freq_scale);
+    rope_table_build(tab, c->rope_n_pos, m->n_rot, m->arch == 1 ? 2 : 0, m->rope_freq_base, m->rope_freq_scale);    // falcon: NeoX pairs
     CK(cudaMalloc(&c->rope, tab.size() * sizeof(float2)));
     CK(cudaMemcpy(c->rope, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice));
     CK(cudaMalloc(&c->cancel_table, 128 * sizeof(int)));          // [0] current run slot, [1..64] flags, [100] the constant 1
@@ -419,6 +445,15 @@ __global__ void add_kernel(const float * __restrict__ a, const float * __restric
     if (i < n) o[i] = __fadd_rn(a[i], b[i]);
 }
 
+// falcon: l_out = (ffn_out + attn_out) + layer input, in the reference's order (llama.cpp:4197-4201); o may alias c
+__global__ void add3_kernel(const float * a, const float * b, const float * c, float * o, int64_t n, const int * __restrict__ cancel) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
+    if (PIB_CANCELLED(cancel)) return;
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) o[i] = __fadd_rn(__fadd_rn(a[i], b[i]), c[i]);
+}
+
 // hooks installed by pipeline.cu on multi-GPU runs (nullptr on a single GPU)
 int (*pib_hop_recv)(pib_context * c, float * x, int n_tokens, const int * cancel) = nullptr;
 int (*pib_hop_send)(pib_context * c, const float * x, int n_tokens, const int * cancel) = nullptr;
@@ -456,6 +491,52 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
     if (part & 1) {
         RC(kv_device_mask(&c->kvd, tpos, tbits, ntok, c->mask, st));
         if (c->stage.first()) RC(pib_get_rows(m->tok_embd, tok, ntok, c->x, st));
+    }
+    if (m->arch == 1) {
+        // ---- falcon (reference build_falcon, llama.cpp:4106-4225) ----------------------------------------------------------
+        //   [x = (ffn_out + attn_out) + x_prev] -> LayerNorm*w+b -> quantise      (attn_norm_2 when the layer has one, else attn_norm)
+        //   Wqkv GEMV; [LayerNorm(attn_norm) -> quantise;] Wup GEMV               the MLP reads the attention norm's output
+        //   NeoX RoPE, K/V store, attention, quantise, Wo GEMV -> attn_out
+        //   gelu(up) -> quantise -> Wdown GEMV -> ffn_out
+        // The layer input lives in `cur`; the attention output and then the next layer's input go to `other` (ping-pong), so
+        // that no kernel reads a buffer another CTA of the same launch is rewriting.
+        const int nl = m->layer_end - m->layer_begin;
+        float *   cur = c->x, * other = c->att;
+        bool      pend = false;
+        if (!(part & 1)) { pend = nl > 0; if (nl > 0 && ((nl - 1) & 1)) std::swap(cur, other); }     // the state the layer loop leaves behind
+        for (int il = m->layer_begin; (part & 1) && il < m->layer_end; il++) {
+            const pib_layer & L  = m->layers[il];
+            const size_t      lo = (size_t) (il - m->layer_begin) * c->n_ctx * GQA;
+            const float *     nw = L.attn_norm2 ? L.attn_norm2 : L.attn_norm, * nb = L.attn_norm2 ? L.attn_norm2_b : L.attn_norm_b;
+            if (pend) { TL(5, il, pib_add_layernorm_quantize_act(wt, c->x2, c->proj, cur, other, nw, nb, m->norm_eps, ntok, E, c->act, cancel, st)); std::swap(cur, other); }
+            else      { TL(5, il, pib_add_layernorm_quantize_act(wt, cur, nullptr, nullptr, nullptr, nw, nb, m->norm_eps, ntok, E, c->act, cancel, st)); }
+            GEMV(0, il, L.wqkv, c->qkv);
+            if (L.attn_norm2) TL(9, il, pib_add_layernorm_quantize_act(wt, cur, nullptr, nullptr, nullptr, L.attn_norm, L.attn_norm_b, m->norm_eps, ntok, E, c->act, cancel, st));
+            GEMV(2, il, L.wgu, c->gu);
+            TL(6, il, pib_rope_kv_store(c->qkv, desc, c->rope, c->rope_n_pos, ntok, E, GQA, hd, 2, c->q16, c->kcache + lo, c->vcache + lo, cancel, st));
+            TL(7, il, pib_attention(c->q16, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, desc, ntok, m->n_head, m->n_head_kv, hd,
+                                    (int) c->n_ctx, other, cancel, st));
+            TL(8, il, pib_quantize_act_c(wt, other, ntok, E, c->act, cancel, st));
+            GEMV(1, il, L.wo, c->proj);
+            TL(10, il, pib_gelu_quantize_act(wt, c->gu, ntok, FF, c->act, cancel, st));
+            GEMV(3, il, L.wdown, c->x2);
+            pend = true;
+        }
+        if (c->stage.last() && !(part & 2)) return PIB_OK;
+        if (!c->stage.last() && !(part & 1)) return PIB_OK;
+        if (c->stage.last()) {
+            if (pend) RC(pib_add_layernorm_quantize_act(wt, c->x2, c->proj, cur, other, m->output_norm, m->output_norm_b, m->norm_eps, ntok, E, c->act, cancel, st));
+            else      RC(pib_add_layernorm_quantize_act(wt, cur, nullptr, nullptr, nullptr, m->output_norm, m->output_norm_b, m->norm_eps, ntok, E, c->act, cancel, st));
+            float * lg = run.logits + (size_t) chunk * PIB_CHUNK * m->n_vocab;
+            GEMV(4, c->prof_layer >= 0 ? c->prof_layer : -2, m->output, lg);
+            RC(pib_sample_topk(lg, ntok, m->n_vocab, c->bias_ids_dev, c->bias_val_dev, c->n_bias, run.res_dev + (size_t) chunk * PIB_CHUNK,
+                               desc, cancel, st));
+        } else if (pend) {
+            const int64_t n = (int64_t) ntok * E;
+            pib_launch(add3_kernel, dim3((unsigned) ((n + 255) / 256)), dim3(256), 0, st, c->x2, c->proj, cur, c->x, n, cancel);
+            c->n_kernels++;
+        }
+        return PIB_OK;
     }
     // x holds layer_inp; `pending_add` = a down-projection result still to be added to x2 (ffn_inp) to form the next x
     bool pending_add = (part & 1) ? false : m->layer_end > m->layer_begin;

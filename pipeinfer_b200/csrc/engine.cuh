@@ -20,10 +20,12 @@ struct pib_row_result {            // per logits row: sorted top-8 {id, logit, p
 
 struct pib_layer {
     float *      attn_norm = nullptr;   // [n_embd]
+    float *      attn_norm_b = nullptr; // falcon: LayerNorm bias
+    float *      attn_norm2 = nullptr, * attn_norm2_b = nullptr;   // falcon 40B/180B layout: the norm that feeds QKV
     pib_weight * wqkv      = nullptr;   // rows: Wq (n_embd) | Wk (n_embd_gqa) | Wv (n_embd_gqa)
     pib_weight * wo        = nullptr;
     float *      ffn_norm  = nullptr;
-    pib_weight * wgu       = nullptr;   // rows: gate (n_ff) | up (n_ff)
+    pib_weight * wgu       = nullptr;   // llama rows: gate (n_ff) | up (n_ff); falcon: up (n_ff) only
     pib_weight * wdown     = nullptr;
 };
 
@@ -32,11 +34,14 @@ struct pib_model {
     int   n_layer = 0, n_embd = 0, n_head = 0, n_head_kv = 0, n_ff = 0, n_vocab = 0, n_rot = 0, n_ctx_train = 0;
     float rms_eps = 1e-5f, rope_freq_base = 10000.f, rope_freq_scale = 1.f;
     int   wtype = 0;
+    int   arch = 0;                      // 0 llama (build_llama, llama.cpp:3872), 1 falcon (build_falcon, :4106)
+    float norm_eps = 1e-5f;              // falcon: f_norm_eps
     int   tok_bos = 1, tok_eos = 2, tok_nl = 13;
     // tensors (only those of the layer range this process owns are resident)
     int          layer_begin = 0, layer_end = 0;
     pib_weight * tok_embd    = nullptr;
     float *      output_norm = nullptr;
+    float *      output_norm_b = nullptr;
     pib_weight * output      = nullptr;
     std::vector<pib_layer> layers;
     // vocabulary (for llama_token_to_piece / the char-level prompt path)

@@ -62,7 +62,8 @@ def build(args):
     rng = np.random.default_rng(args.seed)
     E, L, H, HKV, FF, V = args.n_embd, args.n_layer, args.n_head, args.n_head_kv, args.n_ff, args.n_vocab
     hd = E // H
-    w = gguf.GGUFWriter(args.out if args.quant == "f32" else args.out + ".f32.gguf", "llama")
+    falcon = args.arch == "falcon"
+    w = gguf.GGUFWriter(args.out if args.quant == "f32" else args.out + ".f32.gguf", args.arch)
     w.add_name(args.name)
     w.add_context_length(args.n_ctx_train)
     w.add_embedding_length(E)
@@ -71,7 +72,10 @@ def build(args):
     w.add_rope_dimension_count(hd)
     w.add_head_count(H)
     w.add_head_count_kv(HKV)
-    w.add_layer_norm_rms_eps(1e-5)
+    if falcon:
+        w.add_layer_norm_eps(1e-5)
+    else:
+        w.add_layer_norm_rms_eps(1e-5)
     w.add_file_type(0)
     toks, scores, types = synth_vocab(V)
     w.add_tokenizer_model("llama")
@@ -102,7 +106,30 @@ def build(args):
         out = mat(V, E, 0.02)
         std = 0.02
     w.add_tensor("token_embd.weight", emb)
-    for il in range(L):
+
+    def norm_w():
+        return rng.uniform(0.5, 1.5, E).astype(np.float32)
+
+    def norm_b():
+        return (rng.standard_normal(E) * 0.02).astype(np.float32)
+
+    for il in range(L if falcon else 0):
+        # tensor table of the falcon architecture (reference llama.cpp:2769-2811): LayerNorm with bias, fused QKV,
+        # optional second norm (Falcon-40B/180B), GELU MLP without gate
+        pre = "blk.%d." % il
+        w.add_tensor(pre + "attn_norm.weight", norm_w())
+        w.add_tensor(pre + "attn_norm.bias", norm_b())
+        if args.norm2:
+            w.add_tensor(pre + "attn_norm_2.weight", norm_w())
+            w.add_tensor(pre + "attn_norm_2.bias", norm_b())
+        w.add_tensor(pre + "attn_qkv.weight", mat(E + 2 * hd * HKV, E, std))
+        w.add_tensor(pre + "attn_output.weight", mat(E, E, std))
+        w.add_tensor(pre + "ffn_down.weight", mat(E, FF, std))
+        w.add_tensor(pre + "ffn_up.weight", mat(FF, E, std))
+    if falcon:
+        w.add_tensor("output_norm.weight", norm_w())
+        w.add_tensor("output_norm.bias", norm_b())
+    for il in range(0 if falcon else L):
         pre = "blk.%d." % il
         w.add_tensor(pre + "attn_norm.weight", np.ones(E, dtype=np.float32))
         w.add_tensor(pre + "attn_q.weight", mat(E, E, std))
@@ -113,7 +140,8 @@ def build(args):
         w.add_tensor(pre + "ffn_gate.weight", mat(FF, E, std))
         w.add_tensor(pre + "ffn_down.weight", mat(E, FF, std))
         w.add_tensor(pre + "ffn_up.weight", mat(FF, E, std))
-    w.add_tensor("output_norm.weight", np.ones(E, dtype=np.float32))
+    if not falcon:
+        w.add_tensor("output_norm.weight", np.ones(E, dtype=np.float32))
     w.add_tensor("output.weight", out)
     w.write_header_to_file()
     w.write_kv_data_to_file()
@@ -225,6 +253,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", required=True)
     ap.add_argument("--name", default="random-llama")
+    ap.add_argument("--arch", default="llama", choices=["llama", "falcon"])
+    ap.add_argument("--norm2", action="store_true", help="falcon: second attention norm per layer (the 40B/180B layout)")
     ap.add_argument("--n-layer", type=int, default=2)
     ap.add_argument("--n-embd", type=int, default=512)
     ap.add_argument("--n-head", type=int, default=8)
