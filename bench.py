@@ -37,8 +37,15 @@ CONFIGS = {
             "Llama-2-70B-arch Q4_K target + TinyLlama-1.1B-arch Q4_K draft"),
     "7b": ((32, 4096, 32, 32, 11008, 32000, Q4_0), (22, 2048, 32, 4, 5632, 32000, Q4_0),
            "Llama-2-7B-arch Q4_0 target + TinyLlama-1.1B-arch Q4_0 draft"),
+    "120b": ((137, 8192, 64, 8, 28672, 32000, Q4_K), (32, 4096, 32, 32, 11008, 32000, Q4_K),
+             "Goliath-120B-arch Q4_K target + XWin-7B-arch Q4_K draft"),
+    "180b": ((80, 14848, 232, 8, 59392, 65024, Q4_0), (32, 4544, 71, 1, 18176, 65024, Q4_0),
+             "Falcon-180B-arch Q4_0 target + Falcon-7B-arch Q4_0 draft"),
     "tiny": ((8, 1024, 8, 2, 2048, 4096, Q4_K), (2, 512, 8, 2, 1024, 4096, Q4_K), "8-layer 1024-wide target + 2-layer draft (smoke)"),
+    "tiny-falcon": ((8, 1024, 16, 2, 4096, 4096, Q4_0), (2, 512, 8, 1, 2048, 4096, Q4_0), "8-layer falcon-arch target + 2-layer falcon-arch draft (smoke)"),
 }
+# synthetic-model flavour of (target, draft): bigram (1) [+ 0x10 falcon architecture, + 0x20 second attention norm]
+FLAVOUR = {"180b": (0x31, 0x11), "tiny-falcon": (0x31, 0x11)}
 TYPE_NAME = {Q4_K: "q4_k", Q4_0: "q4_0", Q8_0: "q8_0"}
 BPW = {Q4_K: 4.5, Q4_0: 4.5, Q8_0: 8.5}
 KIND = {0: "qkv", 1: "attn_out", 2: "gate_up", 3: "down", 4: "lm_head", 5: "attn_norm_quant", 6: "rope_kv_store", 7: "attention",
@@ -221,13 +228,14 @@ def main():
     cap = 1000 * args.np + 2
     t_load = time.time()
     weights = [float(x) for x in args.layer_split.split(",")] if args.layer_split else pipeline.default_weights(world, args.head_share)
+    fl_t, fl_d = FLAVOUR.get(args.config, (1, 1))
     ranges = pipeline.split_layers(L, weights) if world > 1 else [(0, L)]
     config["layer_ranges"] = ranges
     if world > 1:
-        tgt = pipeline.StageContext(rank, world, ranges, 1024, cap, synthetic=(L, E, H, HKV, FF, V, wt, 1, 1, 1.0))
+        tgt = pipeline.StageContext(rank, world, ranges, 1024, cap, synthetic=(L, E, H, HKV, FF, V, wt, 1, fl_t, 1.0))
     else:
-        tgt = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=(L, E, H, HKV, FF, V, wt, 1, 1, 1.0))
-    dft = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=dshape + (2, 1, args.agree)) if rank == 0 else None
+        tgt = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=(L, E, H, HKV, FF, V, wt, 1, fl_t, 1.0))
+    dft = llama.Context(None, n_ctx=1024, max_seq=cap, synthetic=dshape + (2, fl_d, args.agree)) if rank == 0 else None
     if dft is not None and not args.no_draft_priority:
         dft.set_priority(True)                           # the draft sits on the scheduler's critical path
     ctxs = [c for c in (tgt, dft) if c is not None]

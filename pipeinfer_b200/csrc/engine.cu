@@ -246,7 +246,11 @@ pib_model * pib_model_synthetic(int n_layer, int n_embd, int n_head, int n_head_
                                 int flavour, float agree, int layer_begin, int layer_end, bool want_embd, bool want_output) {
     const int blk = wtype == PIB_TYPE_Q4_K ? 256 : 32;
     if (n_embd % blk || n_ff % blk || n_embd % n_head || n_head % n_head_kv) { pib_set_error("synthetic model: bad shape"); return nullptr; }
+    // flavour: low nibble 0 iid / 1 bigram; 0x10 = falcon architecture, 0x20 = with the second attention norm (40B/180B layout)
+    const bool falcon = (flavour & 0x10) != 0, norm2 = (flavour & 0x20) != 0;
+    flavour &= 0xF;
     pib_model * m = new pib_model();
+    m->arch = falcon ? 1 : 0;
     m->name = "synthetic";
     m->n_layer = n_layer; m->n_embd = n_embd; m->n_head = n_head; m->n_head_kv = n_head_kv; m->n_ff = n_ff; m->n_vocab = n_vocab;
     m->n_rot = n_embd / n_head; m->n_ctx_train = 4096; m->wtype = wtype;
@@ -286,6 +290,7 @@ pib_model * pib_model_synthetic(int n_layer, int n_embd, int n_head, int n_head_
     if (want_embd) { m->tok_embd = synth_weight(wtype, n_vocab, E, embseed, nullptr, flavour == 1 ? 1.0f : 0.02f); ok = ok && m->tok_embd; }
     if (want_output) {
         m->output_norm = const_f32(E, 1.0f);
+        if (falcon) { m->output_norm_b = const_f32(E, 0.0f); ok = ok && m->output_norm_b; }
         m->output = flavour == 1 ? synth_weight(wtype, n_vocab, E, embseed, inv_dev, 1.0f) : synth_weight(wtype, n_vocab, E, s32 ^ 0x22222222u, nullptr, 0.02f);
         ok = ok && m->output && m->output_norm;
     }
@@ -293,12 +298,15 @@ pib_model * pib_model_synthetic(int n_layer, int n_embd, int n_head, int n_head_
         pib_layer & L = m->layers[il];
         const uint32_t ls = s32 ^ (uint32_t) (il * 7919 + 13);
         L.attn_norm = const_f32(E, 1.0f);
-        L.ffn_norm  = const_f32(E, 1.0f);
+        if (falcon) {
+            L.attn_norm_b = const_f32(E, 0.0f);
+            if (norm2) { L.attn_norm2 = const_f32(E, 1.0f); L.attn_norm2_b = const_f32(E, 0.0f); }
+        } else L.ffn_norm = const_f32(E, 1.0f);
         L.wqkv  = synth_weight(wtype, E + 2 * GQA, E, ls ^ 0x1u, nullptr, lstdE);
         L.wo    = synth_weight(wtype, E, E, ls ^ 0x2u, nullptr, lstdE);
-        L.wgu   = synth_weight(wtype, 2 * FF, E, ls ^ 0x3u, nullptr, lstdE);
+        L.wgu   = synth_weight(wtype, (falcon ? 1 : 2) * FF, E, ls ^ 0x3u, nullptr, lstdE);
         L.wdown = synth_weight(wtype, E, FF, ls ^ 0x4u, nullptr, lstdF);
-        ok = L.attn_norm && L.ffn_norm && L.wqkv && L.wo && L.wgu && L.wdown;
+        ok = L.attn_norm && (falcon ? (L.attn_norm_b && (!norm2 || (L.attn_norm2 && L.attn_norm2_b))) : L.ffn_norm != nullptr) && L.wqkv && L.wo && L.wgu && L.wdown;
         if (ok) m->weight_bytes += pib_weight_bytes(L.wqkv) + pib_weight_bytes(L.wo) + pib_weight_bytes(L.wgu) + pib_weight_bytes(L.wdown);
     }
     cudaDeviceSynchronize();
