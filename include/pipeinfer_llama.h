@@ -189,6 +189,7 @@ struct llama_model * llama_pib_synthetic_model_slice(int n_layer, int n_embd, in
                                                      int layer_end, int want_embd, int want_output);
 struct llama_model * llama_pib_load_model_slice(const char * path_model, int layer_begin, int layer_end, int want_embd, int want_output);
 struct llama_context * llama_pib_new_context_stage(struct llama_model * model, uint32_t n_ctx, int32_t max_seq_ids, int rank, int size);
+int  llama_pib_n_layer(const struct llama_model * model);
 int  llama_pib_stage_serve(struct llama_context * ctx);
 int  llama_pib_pipe_pause(struct llama_context * ctx);
 int  llama_pib_pipe_shutdown(struct llama_context * ctx);

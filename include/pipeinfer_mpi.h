@@ -27,6 +27,9 @@ int  pib_pipe_size(void);
 int  pib_pipe_unique_id(uint8_t * out128);
 int  pib_pipe_nccl_init(int rank, int size, const uint8_t * id_fwd, const uint8_t * id_back);
 void pib_pipe_nccl_free(void);
+/* all of the above from the launcher's environment (RANK, WORLD_SIZE, LOCAL_RANK, MASTER_PORT): ring named after the port,
+ * NCCL ids handed over through the ring's header page; returns the world size (1 = not a multi-process launch), < 0 on error */
+int  pib_pipe_open_env(void);
 /* bytes / messages of activations this rank sent to its next stage, and bytes of sampled rows it sent to the head */
 void pib_pipe_traffic(uint64_t * hop_bytes, uint64_t * hop_msgs, uint64_t * back_bytes);
 /* layer partition rule of ggml_mpi_split_range (ggml-mpi.c:523-559) without a context: out_pairs[2*i], [2*i+1] */

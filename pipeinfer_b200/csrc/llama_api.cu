@@ -184,6 +184,7 @@ void llama_set_n_threads(struct llama_context * ctx, uint32_t a, uint32_t b) { (
 const struct llama_model * llama_get_model(const struct llama_context * ctx) { return ctx->model; }
 int llama_n_ctx(const struct llama_context * ctx) { return (int) ctx->c->n_ctx; }
 int llama_n_vocab(const struct llama_model * model) { return model->m->n_vocab; }
+int llama_pib_n_layer(const struct llama_model * model) { return model->m->n_layer; }
 int llama_n_ctx_train(const struct llama_model * model) { return model->m->n_ctx_train; }
 int llama_n_embd(const struct llama_model * model) { return model->m->n_embd; }
 llama_token llama_token_bos(const struct llama_model * model) { return model->m->tok_bos; }

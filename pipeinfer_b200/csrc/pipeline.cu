@@ -48,6 +48,8 @@ struct ring_hdr {
     uint64_t  cap;
     uint32_t  n_ranks;
     std::atomic<uint32_t> magic;
+    uint8_t   nccl_ids[256];             // the two ncclUniqueIds, published by rank 0 (launchers without a store of their own)
+    std::atomic<uint32_t> ids_ready;
 };
 struct rec_hdr { uint32_t bytes, kind; };
 struct rec_decode { int32_t batch_id, n_tokens, n_chunks, n_ops; uint32_t desc_stride, pad; };
@@ -116,7 +118,7 @@ extern "C" int pib_pipe_ring_open(const char * name, int rank, int n_ranks, size
     P.h = (ring_hdr *) p; P.data = (uint8_t *) p + 4096; P.map_bytes = total; P.rank = rank; P.size = n_ranks; P.name = name; P.wpos = 0;
     if (rank == 0) {
         P.h->cap = cap_bytes; P.h->n_ranks = (uint32_t) n_ranks;
-        P.h->head.v.store(0); P.h->bar_count.v.store(0); P.h->bar_gen.v.store(0);
+        P.h->head.v.store(0); P.h->bar_count.v.store(0); P.h->bar_gen.v.store(0); P.h->ids_ready.store(0);
         for (int i = 0; i < PIPE_MAX_RANKS; i++) P.h->tail[i].v.store(0);
         P.h->magic.store(PIPE_MAGIC, std::memory_order_release);
     } else {
@@ -275,6 +277,7 @@ static nccl_fns N;
 
 static int nccl_load() {
     if (P.nccl_lib) return PIB_OK;
+    setenv("NCCL_DEBUG_FILE", "/dev/stderr", 0);      // NCCL's banner / debug lines must not land in a CLI's stdout (generated text only)
     const char * path = getenv("PIB_NCCL_LIB");
     void * lib = dlopen(path ? path : "libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
     if (!lib) { pib_set_error("pipe: cannot load NCCL (%s); set PIB_NCCL_LIB", dlerror()); return PIB_ERR_UNSUPP; }
@@ -322,6 +325,30 @@ extern "C" int pib_pipe_nccl_init(int rank, int size, const uint8_t * id_fwd, co
     PIB_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     PIB_CHECK(cudaStreamCreateWithPriority(&P.res_stream, cudaStreamNonBlocking, hi));
     return PIB_OK;
+}
+
+// Everything from the launcher's environment (RANK, WORLD_SIZE, LOCAL_RANK, MASTER_PORT as torchrun / mpirun-style
+// launchers set them): control ring named after the port, NCCL ids handed over through the ring's header page.  For
+// programs that have no rendezvous store of their own (the `speculative` CLI); returns the world size, < 0 on error.
+extern "C" int pib_pipe_open_env(void) {
+    const char * r = getenv("RANK"), * w = getenv("WORLD_SIZE"), * lr = getenv("LOCAL_RANK"), * port = getenv("MASTER_PORT");
+    const int rank = r ? atoi(r) : 0, world = w ? atoi(w) : 1;
+    if (world <= 1) return 1;
+    if (pib_init(lr ? atoi(lr) : rank) != PIB_OK) return PIB_ERR_CUDA;
+    const std::string name = std::string("/pib_ring_") + (port ? port : "29500");
+    int rc = pib_pipe_ring_open(name.c_str(), rank, world, (size_t) 64 << 20);
+    if (rc != PIB_OK) return rc;
+    if (rank == 0) {
+        if ((rc = pib_pipe_unique_id(P.h->nccl_ids)) != PIB_OK || (rc = pib_pipe_unique_id(P.h->nccl_ids + 128)) != PIB_OK) return rc;
+        P.h->ids_ready.store(1, std::memory_order_release);
+    } else {
+        spinner sp;
+        while (P.h->ids_ready.load(std::memory_order_acquire) != 1) if (!sp.step()) { pib_set_error("pipe: NCCL ids never published"); return PIB_ERR_ARG; }
+    }
+    uint8_t ids[256];
+    memcpy(ids, P.h->nccl_ids, 256);
+    if ((rc = pib_pipe_nccl_init(rank, world, ids, ids + 128)) != PIB_OK) return rc;
+    return world;
 }
 
 extern "C" void pib_pipe_nccl_free(void) {
