@@ -156,25 +156,35 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
     const float * biasr = bias;
 
     if (!Q8K) {
-        // one warp per 32-element block, lane == element
-        const int64_t nb = K / PIB_QK;
-        for (int64_t blk = (int64_t) blockIdx.y * nwarp + warp; blk < nb; blk += (int64_t) gridDim.y * nwarp) {
-            const int64_t i    = blk * PIB_QK + lane;
-            const float   v    = aq_value<PRO>(xr, x2r, scale, lut, i, mean, biasr);
-            const float   amax = warp_max(fabsf(v));
-            const float   d    = amax / 127.f;
-            const float   id   = (amax != 0.0f) ? 127.f / amax : 0.0f;
-            int           q    = __float2int_rn(__fmul_rn(v, id));
-            q                  = max(-128, min(127, q));
-            qs[(size_t) row * K + i] = (int8_t) q;
-            if (vout) vout[(size_t) row * K + i] = v;
-            int sum = q;
+        // one warp per 32-element block, lane == element.  Blocks nb .. nbp - 1 are the zero padding of the last group of
+        // eight (K not a multiple of 256): only their fragment-order copies exist.
+        const int64_t nb = K / PIB_QK, nbp = ((K + 255) / 256) * 8;
+        __half *      dxp = reinterpret_cast<__half *>(bs8plane);
+        for (int64_t blk = (int64_t) blockIdx.y * nwarp + warp; blk < nbp; blk += (int64_t) gridDim.y * nwarp) {
+            int   q = 0;
+            float d = 0.0f;
+            if (blk < nb) {
+                const int64_t i    = blk * PIB_QK + lane;
+                const float   v    = aq_value<PRO>(xr, x2r, scale, lut, i, mean, biasr);
+                const float   amax = warp_max(fabsf(v));
+                d                  = amax / 127.f;
+                const float   id   = (amax != 0.0f) ? 127.f / amax : 0.0f;
+                q                  = __float2int_rn(__fmul_rn(v, id));
+                q                  = max(-128, min(127, q));
+                qs[(size_t) row * K + i] = (int8_t) q;
+                if (vout) vout[(size_t) row * K + i] = v;
+                int sum = q;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-            if (lane == 0) {
-                dplane[(size_t) row * nb + blk]            = pib_h2f(pib_f2h(d));   // the reference stores d as fp16
-                ((int32_t *) bsplane)[(size_t) row * nb + blk] = sum;
+                for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                if (lane == 0) {
+                    dplane[(size_t) row * nb + blk]            = pib_h2f(pib_f2h(d));   // the reference stores d as fp16
+                    ((int32_t *) bsplane)[(size_t) row * nb + blk] = sum;
+                }
             }
+            // fragment-order copy for the tensor-core GEMV (gemv_blk32.cu): element e = 16 h + 4 t + i of block j of a group
+            // of eight goes to 64 t + 8 j + 4 h + i, so that a lane's B operands of a whole group are 64 contiguous bytes
+            qsp[(size_t) row * nbp * 32 + (blk >> 3) * 256 + ((lane & 15) >> 2) * 64 + (blk & 7) * 8 + (lane >> 4) * 4 + (lane & 3)] = (int8_t) q;
+            if (lane == 0) dxp[(size_t) row * nbp + blk] = __float2half_rn(d);
         }
     } else {
         // one warp per 256-element super-block, lane owns 8 consecutive elements

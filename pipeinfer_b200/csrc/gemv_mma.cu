@@ -52,7 +52,10 @@ __global__ void q4k_tiles_kernel(const uint8_t * __restrict__ qs, const uint8_t 
     *reinterpret_cast<uint4 *>(tiles + i * 16) = v;
 }
 
+int pib_weight_build_tiles_blk32(pib_weight * w);     // gemv_blk32.cu
+
 int pib_weight_build_tiles(pib_weight * w) {
+    if (w->type == PIB_TYPE_Q4_0 || w->type == PIB_TYPE_Q8_0) return pib_weight_build_tiles_blk32(w);
     if (w->type != PIB_TYPE_Q4_K || w->tiles) return PIB_OK;
     const int64_t nsb = w->K / 256, n_tiles = (w->N + 15) / 16;
     const size_t  bytes = (size_t) n_tiles * nsb * MM_TILE_BYTES;

@@ -114,12 +114,15 @@ int pib_gemv_dp4a(const pib_weight * w, const void * act_dev, int b, float * y_d
 int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 bool pib_gemv_mma_supported(const pib_weight * w, int b);
+bool pib_gemv_blk32_supported(const pib_weight * w, int b);
+int  pib_gemv_blk32(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 
 int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, const int * cancel,
                       cudaStream_t st) {
     const bool tc = pib_gemv_mma_supported(w, b);
     if (variant == 3 && tc) return pib_gemv_mma(w, act_dev, b, y_dev, cancel, st);
     if ((variant == 2 || variant == 0) && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);
+    if ((variant == 2 || variant == 0) && pib_gemv_blk32_supported(w, b)) return pib_gemv_blk32(w, act_dev, b, y_dev, cancel, st);
     return pib_gemv_dp4a(w, act_dev, b, y_dev, cancel, st);
 }
 
@@ -128,8 +131,8 @@ extern "C" int pib_gemv(const pib_weight * w, const void * act_dev, int b, float
         pib_set_error("pib_gemv: bad arguments (b = %d, limit %d)", b, PIB_MAX_BATCH);
         return PIB_ERR_ARG;
     }
-    if ((variant == 2 || variant == 3) && !pib_gemv_mma_supported(w, b)) {
-        pib_set_error("pib_gemv: variants 2 / 3 need Q4_K weights");
+    if ((variant == 3 && !pib_gemv_mma_supported(w, b)) || (variant == 2 && !pib_gemv_mma_supported(w, b) && !pib_gemv_blk32_supported(w, b))) {
+        pib_set_error("pib_gemv: variant 2 needs tiles (Q4_K, Q4_0, Q8_0), variant 3 Q4_K");
         return PIB_ERR_UNSUPP;
     }
     return pib_gemv_internal(w, act_dev, b, y_dev, variant, nullptr, (cudaStream_t) s);

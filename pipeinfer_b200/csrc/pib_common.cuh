@@ -145,8 +145,11 @@ __host__ __device__ inline pib_act_layout pib_act_layout_of(int wtype, int64_t K
     L.bs_off = (L.d_off + nd * 4 + 255) & ~(size_t) 255;
     size_t nbs = (wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / 16) * 2 : (size_t) b * (K / PIB_QK) * 4;
     L.bs8_off = (L.bs_off + nbs + 255) & ~(size_t) 255;
-    size_t nbs8 = (wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / PIB_QK_K) * 16 : 0;
+    // 32-element block formats: bs8 holds the "dxp" plane (fp16 block scales [b][ngr * 8], ngr = groups of 8 blocks, zero
+    // padded) and qsp the fragment-order quants [b][ngr * 256] of gemv_blk32.cu
+    const size_t ngr = (size_t) ((K + 255) / 256);
+    size_t nbs8 = (wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / PIB_QK_K) * 16 : (size_t) b * ngr * 8 * 2;
     L.qsp_off = (L.bs8_off + nbs8 + 255) & ~(size_t) 255;
-    L.total  = (L.qsp_off + ((wtype == PIB_TYPE_Q4_K) ? qs : 0) + 255) & ~(size_t) 255;
+    L.total  = (L.qsp_off + ((wtype == PIB_TYPE_Q4_K) ? qs : (size_t) b * ngr * 256) + 255) & ~(size_t) 255;
     return L;
 }

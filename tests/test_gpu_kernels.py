@@ -90,14 +90,15 @@ def test_get_rows_bit_exact(lib, kern, name, wt):
 
 
 def variants(wt):
-    return [1, 2, 3] if wt == op.TYPE_Q4_K else [1]      # variants 2 (direct) and 3 (TMA-staged) exist for Q4_K
+    # 1 = dp4a (all types), 2 = tensor-core kernel with register-prefetched tiles (all types), 3 = TMA-staged (Q4_K only)
+    return [1, 2, 3] if wt == op.TYPE_Q4_K else [1, 2]
 
 
 @pytest.mark.parametrize("variant", [1, 2, 3])
 @pytest.mark.parametrize("name,wt", TYPES)
 def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
     if variant not in variants(wt):
-        pytest.skip("variants 2 and 3 are Q4_K only")
+        pytest.skip("variant 3 is Q4_K only")
     w, x, y = kern[name + "_w"], kern[name + "_x"], kern[name + "_y"]
     h = lib.weight_upload(wt, w, x.shape[1])
     got = lib.mul_mat(h, x, w.shape[0], variant)
@@ -110,7 +111,7 @@ def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
 @pytest.mark.parametrize("b", [1, 2, 5, 8, 9, 16])
 def test_mul_mat_vs_oracle_batches(lib, oracle, name, wt, b, variant):
     if variant not in variants(wt):
-        pytest.skip("variants 2 and 3 are Q4_K only")
+        pytest.skip("variant 3 is Q4_K only")
     rng = np.random.default_rng(100 + b)
     N, K = 96, 2048
     w = rand_blocks(rng, wt, N, K)
@@ -137,21 +138,37 @@ def test_mul_mat_ragged_rows_and_long_k(lib, oracle, name, wt):
     lib.L.pib_weight_free(h)
 
 
+@pytest.mark.parametrize("name,wt", TYPES)
 @pytest.mark.parametrize("N,K,b", [(2560, 2048, 3), (48, 8192, 16), (200, 1024, 1)])
-def test_mul_mat_tensor_core_k_split_path(lib, oracle, N, K, b):
+def test_mul_mat_tensor_core_k_split_path(lib, oracle, N, K, b, name, wt):
     # few row tiles -> the kernel splits K over several CTAs and reduces partial sums through scratch memory in a fixed order;
     # run twice: the per-tile arrival counters must be left clean
     rng = np.random.default_rng(N)
-    wt = op.TYPE_Q4_K
     w = rand_blocks(rng, wt, N, K)
     x = rng.standard_normal((b, K)).astype(np.float32)
     h = lib.weight_upload(wt, w, K)
     ref = oracle.mul_mat(wt, w, x)
-    for variant in (2, 3):
+    for variant in variants(wt)[1:]:
         a1 = lib.mul_mat(h, x, N, variant)
         a2 = lib.mul_mat(h, x, N, variant)
         assert np.array_equal(a1, a2)                      # deterministic
         assert np.abs(a1 - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max())
+    lib.L.pib_weight_free(h)
+
+
+@pytest.mark.parametrize("wt", [op.TYPE_Q4_0, op.TYPE_Q8_0])
+@pytest.mark.parametrize("b", [1, 7, 12])
+def test_mul_mat_width_not_a_multiple_of_256(lib, oracle, wt, b):
+    # Falcon-7B: n_embd = 4544 = 142 blocks of 32; the tensor-core kernel pads the last group of eight blocks with zeros
+    rng = np.random.default_rng(b)
+    N, K = 100, 4544
+    w = rand_blocks(rng, wt, N, K)
+    x = rng.standard_normal((b, K)).astype(np.float32)
+    h = lib.weight_upload(wt, w, K)
+    ref = oracle.mul_mat(wt, w, x)
+    for variant in (1, 2):
+        got = lib.mul_mat(h, x, N, variant)
+        assert np.abs(got - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max()), variant
     lib.L.pib_weight_free(h)
 
 
