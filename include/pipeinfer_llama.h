@@ -154,6 +154,11 @@ void llama_kv_cache_clear(struct llama_context * ctx);
 void llama_kv_cache_seq_rm(struct llama_context * ctx, llama_seq_id seq_id, llama_pos p0, llama_pos p1);
 void llama_kv_cache_seq_cp(struct llama_context * ctx, llama_seq_id seq_id_src, llama_seq_id seq_id_dst, llama_pos p0, llama_pos p1);
 void llama_kv_cache_seq_keep(struct llama_context * ctx, llama_seq_id seq_id);
+/* llama.cpp:9310 / :9263: seq_cp issued from the other end of the reference's MPI ring; here every op comes from the head */
+void llama_kv_cache_seq_cp_back(struct llama_context * ctx, llama_seq_id seq_id_src, llama_seq_id seq_id_dst, llama_pos p0, llama_pos p1);
+void llama_kv_cache_seq_cp_sync_bi(struct llama_context * ctx, llama_seq_id seq_id_src, llama_seq_id seq_id_dst, llama_pos p0, llama_pos p1);
+/* llama.cpp:9348 (context shifting of `main`, not on the speculation path): refused with an error, the cache is left unchanged */
+void llama_kv_cache_seq_shift(struct llama_context * ctx, llama_seq_id seq_id, llama_pos p0, llama_pos p1, llama_pos delta);
 int  llama_get_kv_cache_token_count(const struct llama_context * ctx);
 int  llama_get_kv_cache_used_cells(const struct llama_context * ctx);
 struct llama_kv_cache_view llama_kv_cache_view_init(const struct llama_context * ctx, int32_t n_max_seq);
@@ -172,6 +177,16 @@ int  llama_node_id(struct llama_context * ctx);
 /* ---- samplers used under greedy decoding (llama.cpp:7019, 7496) ---- */
 void        llama_sample_softmax(struct llama_context * ctx, llama_token_data_array * candidates);
 llama_token llama_sample_token_greedy(struct llama_context * ctx, llama_token_data_array * candidates);
+void        llama_sample_repetition_penalties(struct llama_context * ctx, llama_token_data_array * candidates,
+                                              const llama_token * last_tokens, size_t penalty_last_n, float penalty_repeat,
+                                              float penalty_freq, float penalty_present);                  /* llama.cpp:7286 */
+
+/* ---- reporting (llama.h:323, 860-872; llama.cpp:10182-10240) ---- */
+int          llama_vocab_type(const struct llama_model * model);           /* 0 = SPM */
+void         llama_print_timings(struct llama_context * ctx);
+void         llama_reset_timings(struct llama_context * ctx);
+const char * llama_print_system_info(void);
+void         llama_log_set(void (*log_callback)(int level, const char * text, void * user_data), void * user_data);
 
 /* ---- additive extensions (no counterpart in llama.h; needed for device-side acceptance) ---- */
 /* sorted top-8 {id, logit, p} of logits row i of the last finished run: 96 bytes instead of n_vocab floats */

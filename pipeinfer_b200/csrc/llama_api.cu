@@ -11,6 +11,12 @@
 #include <string>
 #include <vector>
 
+static int64_t now_us_api() {
+    struct timeval tv;
+    gettimeofday(&tv, nullptr);
+    return (int64_t) tv.tv_sec * 1000000 + tv.tv_usec;
+}
+
 struct llama_model {
     pib_model * m = nullptr;
     std::map<std::string, int32_t> tok_index;     // piece text -> id (built on first tokenize)
@@ -152,6 +158,66 @@ int llama_pib_set_priority(struct llama_context * ctx, int high) {
     c->stream = ns;
     return 0;
 }
+
+// ---- the rest of the llama.h surface that speculative.cpp / main.cpp / common reference (llama.h:323, 472-500, 760-800, 860-872) ----
+int llama_vocab_type(const struct llama_model * model) { (void) model; return 0; }      // LLAMA_VOCAB_TYPE_SPM (llama.h:70-73)
+
+// llama.cpp:9263 / :9310: in the reference these differ from seq_cp only in the direction the op travels along the MPI
+// ring; every stage here receives every op from the head, so both are seq_cp (with the reference's src == dst shortcut)
+void llama_kv_cache_seq_cp_back(struct llama_context * ctx, llama_seq_id src, llama_seq_id dst, llama_pos p0, llama_pos p1) {
+    if (src == dst) return;
+    llama_kv_cache_seq_cp(ctx, src, dst, p0, p1);
+}
+void llama_kv_cache_seq_cp_sync_bi(struct llama_context * ctx, llama_seq_id src, llama_seq_id dst, llama_pos p0, llama_pos p1) {
+    if (src == dst) return;
+    llama_kv_cache_seq_cp(ctx, src, dst, p0, p1);
+}
+// llama.cpp:1736 / :9348: position shift with re-rotation of the cached K (context shifting of `main`).  Not on the
+// speculation path and not implemented: the call is refused loudly instead of leaving K rotated for the old positions.
+void llama_kv_cache_seq_shift(struct llama_context * ctx, llama_seq_id seq_id, llama_pos p0, llama_pos p1, llama_pos delta) {
+    (void) ctx;
+    pib_set_error("llama_kv_cache_seq_shift(seq %d, [%d, %d), %+d): K-cache re-rotation is not implemented", seq_id, p0, p1, delta);
+    fprintf(stderr, "libpipeinfer_b200: %s\n", pib_last_error());
+}
+
+// llama.cpp:7286-7335
+void llama_sample_repetition_penalties(struct llama_context * ctx, llama_token_data_array * candidates, const llama_token * last_tokens,
+                                       size_t penalty_last_n, float penalty_repeat, float penalty_freq, float penalty_present) {
+    (void) ctx;
+    if (penalty_last_n == 0 || (penalty_repeat == 1.0f && penalty_freq == 0.0f && penalty_present == 0.0f)) return;
+    std::map<llama_token, int> token_count;
+    for (size_t i = 0; i < penalty_last_n; ++i) token_count[last_tokens[i]]++;
+    for (size_t i = 0; i < candidates->size; ++i) {
+        const auto it = token_count.find(candidates->data[i].id);
+        if (it == token_count.end()) continue;
+        const int count = it->second;
+        if (candidates->data[i].logit <= 0) candidates->data[i].logit *= penalty_repeat;
+        else                                candidates->data[i].logit /= penalty_repeat;
+        candidates->data[i].logit -= float(count) * penalty_freq + float(count > 0) * penalty_present;
+    }
+    candidates->sorted = false;
+}
+
+void llama_print_timings(struct llama_context * ctx) {                                  // llama.cpp:10182-10200 (what there is to report here)
+    const pib_context * c = ctx->c;
+    const double wall_ms = (now_us_api() - c->t_start_us) / 1000.0;
+    fprintf(stderr, "\nllama_print_timings:      decodes = %llu, kernel launches = %llu (graph launches %llu), h2d %llu B, d2h %llu B, total time = %10.2f ms\n",
+            (unsigned long long) c->n_decode, (unsigned long long) c->n_kernels, (unsigned long long) c->n_graph_launches,
+            (unsigned long long) c->h2d_bytes, (unsigned long long) c->d2h_bytes, wall_ms);
+}
+void llama_reset_timings(struct llama_context * ctx) { ctx->c->t_start_us = now_us_api(); ctx->c->n_decode = 0; }
+const char * llama_print_system_info(void) {
+    static char buf[160];
+    int dev = 0, sms = 0, cc_major = 0, cc_minor = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, dev);
+    cudaDeviceGetAttribute(&cc_minor, cudaDevAttrComputeCapabilityMinor, dev);
+    snprintf(buf, sizeof(buf), "CUDA = 1 | sm = %d%d | SMs = %d | PDL = %d | pipeline stages = %d | ", cc_major, cc_minor, sms,
+             pib_pdl_enabled() ? 1 : 0, pib_pipe_ring_active() ? 2 : 1);
+    return buf;
+}
+void llama_log_set(void (*log_callback)(int level, const char * text, void * user_data), void * user_data) { (void) log_callback; (void) user_data; }
 
 int llama_pib_stage_serve(struct llama_context * ctx) { return pib_stage_serve(ctx->c); }
 // head: let every stage drain its stream and return from llama_pib_stage_serve (kind 5), or end for good (kind 6)
