@@ -157,7 +157,8 @@ void llama_kv_cache_seq_keep(struct llama_context * ctx, llama_seq_id seq_id);
 /* llama.cpp:9310 / :9263: seq_cp issued from the other end of the reference's MPI ring; here every op comes from the head */
 void llama_kv_cache_seq_cp_back(struct llama_context * ctx, llama_seq_id seq_id_src, llama_seq_id seq_id_dst, llama_pos p0, llama_pos p1);
 void llama_kv_cache_seq_cp_sync_bi(struct llama_context * ctx, llama_seq_id seq_id_src, llama_seq_id seq_id_dst, llama_pos p0, llama_pos p1);
-/* llama.cpp:9348 (context shifting of `main`, not on the speculation path): refused with an error, the cache is left unchanged */
+/* llama.cpp:9348 (context shifting of `main`, not on the speculation path): refused with an error, the cache is left
+ * unchanged.  The reference's MPI build aborts at the next decode instead (ggml-mpi.c:610 asserts with K_shift nodes present). */
 void llama_kv_cache_seq_shift(struct llama_context * ctx, llama_seq_id seq_id, llama_pos p0, llama_pos p1, llama_pos delta);
 int  llama_get_kv_cache_token_count(const struct llama_context * ctx);
 int  llama_get_kv_cache_used_cells(const struct llama_context * ctx);

@@ -174,6 +174,8 @@ void llama_kv_cache_seq_cp_sync_bi(struct llama_context * ctx, llama_seq_id src,
 }
 // llama.cpp:1736 / :9348: position shift with re-rotation of the cached K (context shifting of `main`).  Not on the
 // speculation path and not implemented: the call is refused loudly instead of leaving K rotated for the old positions.
+// (The reference cannot do it on this path either: with GGML_USE_MPI -- which this fork needs to compile -- the decode that
+// follows a shift aborts on GGML_ASSERT(inp0 == gf->nodes[0]), ggml-mpi.c:610, because the K_shift nodes come first.)
 void llama_kv_cache_seq_shift(struct llama_context * ctx, llama_seq_id seq_id, llama_pos p0, llama_pos p1, llama_pos delta) {
     (void) ctx;
     pib_set_error("llama_kv_cache_seq_shift(seq %d, [%d, %d), %+d): K-cache re-rotation is not implemented", seq_id, p0, p1, delta);
