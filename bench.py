@@ -37,6 +37,8 @@ CONFIGS = {
             "Llama-2-70B-arch Q4_K target + TinyLlama-1.1B-arch Q4_K draft"),
     "7b": ((32, 4096, 32, 32, 11008, 32000, Q4_0), (22, 2048, 32, 4, 5632, 32000, Q4_0),
            "Llama-2-7B-arch Q4_0 target + TinyLlama-1.1B-arch Q4_0 draft"),
+    "1b": ((22, 2048, 32, 4, 5632, 32000, Q8_0), (2, 512, 8, 8, 1408, 32000, Q8_0),
+           "TinyLlama-1.1B-arch Q8_0 target + 2-layer Llama-arch Q8_0 draft"),
     "120b": ((137, 8192, 64, 8, 28672, 32000, Q4_K), (32, 4096, 32, 32, 11008, 32000, Q4_K),
              "Goliath-120B-arch Q4_K target + XWin-7B-arch Q4_K draft"),
     "180b": ((80, 14848, 232, 8, 59392, 65024, Q4_0), (32, 4544, 71, 1, 18176, 65024, Q4_0),
@@ -50,6 +52,16 @@ TYPE_NAME = {Q4_K: "q4_k", Q4_0: "q4_0", Q8_0: "q8_0"}
 BPW = {Q4_K: 4.5, Q4_0: 4.5, Q8_0: 8.5}
 KIND = {0: "qkv", 1: "attn_out", 2: "gate_up", 3: "down", 4: "lm_head", 5: "attn_norm_quant", 6: "rope_kv_store", 7: "attention",
         8: "attn_out_quant", 9: "resid_ffn_norm_quant", 10: "silu_mul_quant"}
+
+
+def nvlink_tx_kib(gpu):
+    """sum of the per-link NVLink transmit counters of one GPU (`nvidia-smi nvlink -gt d`), or None where unsupported"""
+    try:
+        out = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(gpu)], capture_output=True, text=True, timeout=20).stdout
+        vals = [int(x) for x in re.findall(r"Data Tx:\s*(\d+)\s*KiB", out)]
+        return sum(vals) if vals else None
+    except Exception:
+        return None
 
 
 def measured_peaks():
@@ -278,6 +290,7 @@ def main():
     k0 = launches()
     io0 = [io(c) for c in ctxs]
     tr0 = pipeline.traffic()
+    nv0 = nvlink_tx_kib(dev) if world > 1 else None
     clocks = ClockSampler(dev)
     clocks.start()
     allreduce([0.0])                                    # barrier
@@ -300,15 +313,17 @@ def main():
     k1 = launches()
     io1 = [io(c) for c in ctxs]
     tr1 = pipeline.traffic()
+    nv1 = nvlink_tx_kib(dev) if world > 1 else None
     h2d_all, d2h_all, launches_all, wbytes_all = allreduce([
         sum(io1[i][0] - io0[i][0] for i in range(len(ctxs))), sum(io1[i][1] - io0[i][1] for i in range(len(ctxs))), k1 - k0,
         sum(lib.llama_pib_weight_bytes(c.model) for c in ctxs)])
     hops = None
     if world > 1:
-        per_rank = [torch.zeros(3, dtype=torch.float64) for _ in range(world)]
-        dist.all_gather(per_rank, torch.tensor([tr1[i] - tr0[i] for i in range(3)], dtype=torch.float64))
-        hops = [{"rank": r, "activation_bytes_to_next_stage": int(t[0]), "messages": int(t[1]), "result_bytes_to_head": int(t[2])}
-                for r, t in enumerate(per_rank)]
+        per_rank = [torch.zeros(4, dtype=torch.float64) for _ in range(world)]
+        nv = float((nv1 - nv0) * 1024) if (nv0 is not None and nv1 is not None) else -1.0
+        dist.all_gather(per_rank, torch.tensor([tr1[i] - tr0[i] for i in range(3)] + [nv], dtype=torch.float64))
+        hops = [{"rank": r, "activation_bytes_to_next_stage": int(t[0]), "messages": int(t[1]), "result_bytes_to_head": int(t[2]),
+                 "nvlink_tx_bytes_counter": (int(t[3]) if t[3] >= 0 else None)} for r, t in enumerate(per_rank)]
         if rank == 0:
             tgt.shutdown()
         else:
