@@ -597,7 +597,7 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
     int rc;
     if (!c->stage.first() && pib_hop_recv && (rc = pib_hop_recv(c, c->x, ntok, cancel)) != PIB_OK) return rc;
     // per-launch event timing (bench.py roofline) samples one decode in eight, launched directly; the others keep their graphs
-    c->prof_now = c->prof_layer >= 0 && (c->n_decode & 7) == 0;
+    c->prof_now = c->prof_layer >= 0 && (c->n_decode & 7) == 0 && slot > c->desc_slots;      // verification batches only (single chunk), not prompt chunks
     const bool graphable = c->use_graphs && !c->prof_now && slot > c->desc_slots;           // single-chunk decode: fixed device slot
     bool done = false;
     if (graphable) {
