@@ -116,7 +116,7 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
         return nullptr;
     }
     if (m->n_ff <= 0) { const GgufTensor * up = g.tensor("blk.0.ffn_up.weight"); if (up) m->n_ff = (int) up->ne[1]; }
-    if (layer_end <= 0 || layer_end > m->n_layer) layer_end = m->n_layer;
+    if (layer_end < 0 || layer_end > m->n_layer) layer_end = m->n_layer;        // < 0: all layers; begin == end: none (a head stage that only embeds)
     m->layer_begin = layer_begin;
     m->layer_end   = layer_end;
     m->layers.resize(m->n_layer);
@@ -254,7 +254,7 @@ pib_model * pib_model_synthetic(int n_layer, int n_embd, int n_head, int n_head_
     m->name = "synthetic";
     m->n_layer = n_layer; m->n_embd = n_embd; m->n_head = n_head; m->n_head_kv = n_head_kv; m->n_ff = n_ff; m->n_vocab = n_vocab;
     m->n_rot = n_embd / n_head; m->n_ctx_train = 4096; m->wtype = wtype;
-    if (layer_end <= 0 || layer_end > n_layer) layer_end = n_layer;
+    if (layer_end < 0 || layer_end > n_layer) layer_end = n_layer;              // < 0: all layers; begin == end: none
     m->layer_begin = layer_begin; m->layer_end = layer_end;
     m->layers.resize(n_layer);
     const int E = n_embd, GQA = m->n_embd_gqa(), FF = n_ff;

@@ -65,7 +65,7 @@ void llama_backend_free(void) {}
 struct llama_model * llama_load_model_from_file(const char * path_model, struct llama_model_params params) {
     (void) params;
     ensure_init();
-    pib_model * m = pib_model_load_gguf(path_model, 0, 0, true, true);
+    pib_model * m = pib_model_load_gguf(path_model, 0, -1, true, true);
     if (!m) { fprintf(stderr, "llama_load_model_from_file: %s\n", pib_last_error()); return nullptr; }
     llama_model * lm = new llama_model();
     lm->m = m;
@@ -75,7 +75,7 @@ struct llama_model * llama_load_model_from_file(const char * path_model, struct 
 struct llama_model * llama_pib_synthetic_model(int n_layer, int n_embd, int n_head, int n_head_kv, int n_ff, int n_vocab,
                                                int wtype, uint64_t seed, int flavour, float agree) {
     ensure_init();
-    pib_model * m = pib_model_synthetic(n_layer, n_embd, n_head, n_head_kv, n_ff, n_vocab, wtype, seed, flavour, agree, 0, 0, true, true);
+    pib_model * m = pib_model_synthetic(n_layer, n_embd, n_head, n_head_kv, n_ff, n_vocab, wtype, seed, flavour, agree, 0, -1, true, true);
     if (!m) { fprintf(stderr, "llama_pib_synthetic_model: %s\n", pib_last_error()); return nullptr; }
     llama_model * lm = new llama_model();
     lm->m = m;

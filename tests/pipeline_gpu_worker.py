@@ -22,7 +22,7 @@ def main():
     torch.cuda.set_device(dev)
     dist.init_process_group("cpu:gloo,cuda:nccl")
     pipeline.open_pipeline(rank, world, dev)
-    ranges = pipeline.split_layers(TGT[0], pipeline.default_weights(world, 0.25))
+    ranges = pipeline.split_layers(TGT[0], pipeline.default_weights(world, float(os.environ.get("PIB_TEST_HEAD_SHARE", "0.25"))))
     assert ranges[0][0] == 0 and ranges[-1][1] == TGT[0] and all(ranges[i][1] == ranges[i + 1][0] for i in range(world - 1)), ranges
     cap = 1000 * 2 + 2
     tgt = pipeline.StageContext(rank, world, ranges, 512, cap, synthetic=TGT + (1, 1, 1.0))

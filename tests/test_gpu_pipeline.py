@@ -20,11 +20,12 @@ def n_gpus():
         return 0
 
 
-@pytest.mark.parametrize("world", [2, 4])
-def test_layer_split_target_matches_single_gpu(world):
+# head share 0: the head GPU keeps no target layer (it embeds the tokens and runs the draft), the reference's topology
+@pytest.mark.parametrize("world,head_share", [(2, 0.25), (4, 0.25), (2, 0.0)])
+def test_layer_split_target_matches_single_gpu(world, head_share):
     if n_gpus() < world:
         pytest.skip("needs %d GPUs" % world)
-    env = dict(os.environ, PIB_PIPE_TIMEOUT="120")
+    env = dict(os.environ, PIB_PIPE_TIMEOUT="120", PIB_TEST_HEAD_SHARE=str(head_share))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
            "--master-port", str(free_port()), os.path.join(ROOT, "tests", "pipeline_gpu_worker.py")]
     r = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
