@@ -181,7 +181,7 @@ def main():
     ap.add_argument("--ps", type=float, default=0.9)
     ap.add_argument("--max-spec-runs", type=int, default=-1,
                     help="bound on target runs in flight: 0 = the reference's behaviour (unbounded), -1 = number of pipeline stages + 1")
-    ap.add_argument("--mode", default="speculative", choices=["speculative", "plain"],
+    ap.add_argument("--mode", default="speculative", choices=["speculative", "plain", "classic"],
                     help="plain = non-speculative greedy decoding through the same pipeline (the reference's `main`): the second denominator")
     ap.add_argument("--no-draft-priority", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -272,7 +272,7 @@ def main():
             out = llama.plain_generate(tgt, prompt, args.n_predict)
             out[1].update(n_drafted=0, n_accept=0, n_cancelled=0, n_spec_runs=0)
         else:
-            out = llama.speculative_generate(tgt, dft, prompt, params)
+            out = llama.speculative_generate(tgt, dft, prompt, params, classic=args.mode == "classic")
         if world > 1:
             tgt.pause()
         return out
@@ -386,6 +386,8 @@ def main():
     acc = sum(r["n_accept"] for r in results) / max(1, sum(r["n_drafted"] for r in results))
     if args.mode == "plain":
         config["workload"] = config["workload"].replace("greedy,", "greedy, NON-SPECULATIVE pipelined decode (reference `main`),")
+    if args.mode == "classic":
+        config["workload"] = config["workload"].replace("greedy,", "greedy, CLASSIC synchronous speculation (reference `speculative_orig`),")
     line = {"metric": "accepted tokens/sec", "value": n_tok / t_dec, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": wall_ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 x int4 blocks (Q4_K x Q8_K), fp32 accumulate", "data": "synthetic", "config": config,

@@ -53,6 +53,14 @@ int pib_speculative_generate(struct llama_context * ctx_tgt, struct llama_contex
 int pib_plain_generate(struct llama_context * ctx, const llama_token * prompt, int n_prompt, int n_predict,
                        llama_token * out_tokens, pib_spec_result * result, double * itl_us, int itl_cap);
 
+/* Classic synchronous speculative decoding: draft a tree of up to n_draft tokens over n_parallel sequences, verify it with
+ * one target decode, keep the matching prefix.  Replaces: the loop of examples/speculative_orig/speculative.cpp:222-505
+ * (the "Speculative" bar next to "Sequential" and PipeInfer in plot.py).  Same parameters and result as above; the
+ * contexts need a sequence-id capacity of n_parallel + 1. */
+int pib_speculative_orig_generate(struct llama_context * ctx_tgt, struct llama_context * ctx_dft, const llama_token * prompt,
+                                  int n_prompt, const pib_spec_params * params, llama_token * out_tokens, int out_cap,
+                                  pib_spec_result * result, double * itl_us, int itl_cap);
+
 #ifdef __cplusplus
 }
 #endif

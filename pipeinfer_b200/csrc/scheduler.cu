@@ -533,4 +533,156 @@ int pib_plain_generate(struct llama_context * ctx, const llama_token * prompt, i
     return n_out;
 }
 
+// classic synchronous speculative decoding: the reference's examples/speculative_orig (the "Speculative" bar of plot.py).
+// Draft up to n_draft tokens as a tree over n_parallel sequences, verify them with ONE target decode, keep the matching
+// prefix, repeat (speculative_orig/speculative.cpp:222-505; cited lines are of that file).  Greedy only, like the rest.
+int pib_speculative_orig_generate(struct llama_context * ctx_tgt, struct llama_context * ctx_dft, const llama_token * prompt, int n_prompt,
+                                  const pib_spec_params * params, llama_token * out_tokens, int out_cap, pib_spec_result * result,
+                                  double * itl_us, int itl_cap) {
+    if (!ctx_tgt || !ctx_dft || !prompt || !params || n_prompt < 2) { pib_set_error("pib_speculative_orig_generate: bad arguments"); return -1; }
+    const pib_spec_params & P = *params;
+    const int n_seq_dft = std::max(1, P.n_parallel), n_draft = P.n_draft;
+    if (llama_pib_kv_words(ctx_tgt) * 32 < n_seq_dft + 1 || llama_pib_kv_words(ctx_dft) * 32 < n_seq_dft + 1) {
+        pib_set_error("pib_speculative_orig_generate: contexts need a sequence-id capacity of %d", n_seq_dft + 1);
+        return -1;
+    }
+    if (P.ignore_eos) {
+        const llama_token e_t = llama_token_eos(llama_get_model(ctx_tgt)), e_d = llama_token_eos(llama_get_model(ctx_dft));
+        const float ninf = -INFINITY;
+        llama_pib_set_logit_bias(ctx_tgt, &e_t, &ninf, 1);
+        llama_pib_set_logit_bias(ctx_dft, &e_d, &ninf, 1);
+    }
+    const int M = n_seq_dft + 1;
+    auto top8 = [](llama_context * c, int row, llama_token_data * t) { llama_pib_get_top8(c, row, t); };
+    const int64_t t_enc_start = llama_time_us();
+    std::vector<llama_seq_id> seq_ids(M);
+    for (int i = 0; i < M; i++) seq_ids[i] = i;
+    Batch batch_dft, batch_tgt;
+    {   // :172-184 prompt: every token in every sequence; the target decodes n-1 tokens, then the last one
+        for (int i = 0; i < n_prompt - 1; i++) { batch_dft.add(prompt[i], i, seq_ids); batch_tgt.add(prompt[i], i, seq_ids); }
+        if (llama_decode(ctx_tgt, batch_tgt.view(M)) != 0) return -1;
+        batch_tgt.clear();
+        batch_dft.add(prompt[n_prompt - 1], n_prompt - 1, seq_ids);
+        batch_tgt.add(prompt[n_prompt - 1], n_prompt - 1, seq_ids);
+        if (llama_decode(ctx_tgt, batch_tgt.view(M)) != 0) return -1;
+        if (llama_decode(ctx_dft, batch_dft.view(M)) != 0) return -1;
+    }
+    const int64_t t_enc_end = llama_time_us();
+    int n_predict = 0, n_drafted = 0, n_accept = 0, n_past_tgt = n_prompt, n_past_dft = n_prompt, n_out = 0, n_runs = 0;
+    bool has_eos = false, first_token = false, has_run_first_token = false;
+    std::vector<Draft> drafts(n_seq_dft);
+    drafts[0].i_batch_tgt = { 0 };                                                                        // :222-224
+    int64_t ttft = llama_time_us(), itt_start = 0;
+    std::vector<int64_t> itl;
+    const int64_t t_dec_start = llama_time_us();
+    llama_token_data t8[8];
+    while (true) {
+        int i_dft = 0, s_keep = 0;
+        while (true) {                                                                                    // :247-339 verification walk
+            top8(ctx_tgt, drafts[s_keep].i_batch_tgt[i_dft], t8);
+            const llama_token id = t8[0].id;
+            if (has_run_first_token) {
+                if (first_token) { ttft = llama_time_us() - ttft; first_token = false; }
+                else itl.push_back(llama_time_us() - itt_start);
+                itt_start = llama_time_us();
+            }
+            if (n_out < out_cap) out_tokens[n_out] = id;
+            n_out++;
+            if (id == llama_token_eos(llama_get_model(ctx_tgt)) && !P.ignore_eos) has_eos = true;
+            ++n_predict;
+            bool matches = false;
+            for (int s = 0; s < n_seq_dft; ++s) {
+                if (!drafts[s].active) continue;
+                if (i_dft < (int) drafts[s].tokens.size() && id == drafts[s].tokens[i_dft]) { s_keep = s; matches = true; }
+                else drafts[s].active = false;
+            }
+            if (matches) { ++n_accept; ++n_past_tgt; ++n_past_dft; ++i_dft; continue; }
+            // :305-338 keep the winning branch, feed the new token to the draft
+            llama_kv_cache_seq_keep(ctx_dft, s_keep);
+            llama_kv_cache_seq_cp(ctx_dft, s_keep, 0, -1, -1);
+            llama_kv_cache_seq_keep(ctx_dft, 0);
+            llama_kv_cache_seq_rm(ctx_tgt, s_keep, n_past_tgt, -1);
+            llama_kv_cache_seq_keep(ctx_tgt, s_keep);
+            llama_kv_cache_seq_cp(ctx_tgt, s_keep, 0, -1, -1);
+            llama_kv_cache_seq_keep(ctx_tgt, 0);
+            for (int s = 0; s < n_seq_dft; ++s) { drafts[s].active = false; drafts[s].tokens.clear(); drafts[s].i_batch_tgt.clear(); }
+            drafts[0].tokens.push_back(id);
+            drafts[0].i_batch_tgt.push_back(0);
+            batch_dft.clear();
+            batch_dft.add(id, n_past_dft, { 0 });
+            llama_kv_cache_seq_rm(ctx_dft, -1, n_past_dft, -1);
+            if (llama_decode(ctx_dft, batch_dft.view(M)) != 0) return -1;
+            ++n_past_dft;
+            break;
+        }
+        if (n_predict > P.n_predict || has_eos) break;                                                    // :341-343
+        int n_seq_cur = 1, n_past_cur = n_past_dft;
+        for (int s = 0; s < n_seq_dft; ++s) { drafts[s].active = false; drafts[s].drafting = false; }
+        drafts[0].active = true; drafts[0].drafting = true; drafts[0].i_batch_dft = 0;
+        batch_tgt.clear();
+        batch_tgt.add(drafts[0].tokens[0], n_past_tgt, { 0 });
+        for (int i = 0; i < n_draft; ++i) {                                                               // :362-475 tree drafting
+            batch_dft.clear();
+            for (int s = 0; s < n_seq_dft; ++s) drafts[s].skip = false;
+            for (int s = 0; s < n_seq_dft; ++s) {
+                if (!drafts[s].drafting || drafts[s].skip) continue;
+                top8(ctx_dft, drafts[s].i_batch_dft, t8);
+                if (t8[0].p < P.p_accept) { drafts[s].drafting = false; continue; }                      // :389-393
+                std::vector<int> sa(1, s);
+                for (int f = 1; f < 8; ++f) {                                                             // :398-441 branch splitting
+                    if (n_seq_cur < n_seq_dft && t8[f].p > P.p_split) {
+                        llama_kv_cache_seq_rm(ctx_dft, n_seq_cur, -1, -1);
+                        llama_kv_cache_seq_cp(ctx_dft, s, n_seq_cur, -1, -1);
+                        for (int t = 0; t < batch_tgt.size(); ++t)
+                            for (size_t p = 0; p < batch_tgt.seq[t].size(); ++p)
+                                if (batch_tgt.seq[t][p] == s) { batch_tgt.seq[t].push_back(n_seq_cur); break; }
+                        drafts[n_seq_cur].active = true; drafts[n_seq_cur].drafting = true; drafts[n_seq_cur].skip = true;
+                        drafts[n_seq_cur].tokens = drafts[s].tokens;
+                        drafts[n_seq_cur].i_batch_dft = drafts[s].i_batch_dft;
+                        drafts[n_seq_cur].i_batch_tgt = drafts[s].i_batch_tgt;
+                        sa.push_back(n_seq_cur);
+                        n_seq_cur++;
+                    } else break;
+                }
+                for (int is = 0; is < (int) sa.size(); ++is) {                                            // :444-465
+                    const llama_token id = t8[is].id;
+                    const int sq = sa[is];
+                    drafts[sq].tokens.push_back(id);
+                    drafts[sq].i_batch_tgt.push_back(batch_tgt.size());
+                    batch_tgt.add(id, n_past_tgt + i + 1, { sq });
+                    drafts[sq].i_batch_dft = batch_dft.size();
+                    batch_dft.add(id, n_past_cur, { sq });
+                    if (batch_tgt.size() > n_draft) drafts[sq].drafting = false;
+                }
+            }
+            if (batch_dft.size() == 0) break;
+            if (llama_decode(ctx_dft, batch_dft.view(M)) != 0) return -1;
+            ++n_past_cur;
+            ++n_drafted;
+            if (batch_tgt.size() > n_draft) break;
+        }
+        llama_kv_cache_seq_keep(ctx_tgt, 0);                                                              // :478-495 verify
+        for (int s = 1; s < n_seq_dft; ++s) llama_kv_cache_seq_cp(ctx_tgt, 0, s, -1, -1);
+        if (!has_run_first_token) { has_run_first_token = true; first_token = true; }
+        if (llama_decode(ctx_tgt, batch_tgt.view(M)) != 0) return -1;
+        ++n_past_tgt;
+        ++n_runs;
+        for (int s = 0; s < n_seq_dft; ++s) if (drafts[s].active) drafts[s].tokens.erase(drafts[s].tokens.begin());   // :498-504
+    }
+    const int64_t t_dec_end = llama_time_us();
+    if (result) {
+        memset(result, 0, sizeof(*result));
+        result->n_predict = n_predict; result->n_drafted = n_drafted; result->n_accept = n_accept; result->n_spec_runs = n_runs;
+        result->t_encode_s = (t_enc_end - t_enc_start) / 1e6; result->t_decode_s = (t_dec_end - t_dec_start) / 1e6;
+        result->decode_tok_per_s = n_predict / std::max(1e-9, result->t_decode_s);
+        result->ttft_s = ttft / 1e6; result->n_itl = (int) itl.size();
+        double sum = 0; for (int64_t v : itl) sum += (double) v;
+        result->itl_mean_s = itl.empty() ? 0 : sum / itl.size() / 1e6;
+        std::vector<int64_t> srt = itl; std::sort(srt.begin(), srt.end());
+        result->itl_p50_s = srt.empty() ? 0 : srt[srt.size() / 2] / 1e6;
+    }
+    for (int i = 0; i < (int) itl.size() && i < itl_cap; i++) itl_us[i] = (double) itl[i];
+    return std::min(n_out, out_cap);
+}
+
 }   // extern "C"

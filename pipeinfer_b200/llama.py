@@ -237,6 +237,7 @@ def _bind_sched(L):
     L.pib_spec_default_params.restype = SpecParams
     L.pib_speculative_generate.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int, C.POINTER(SpecParams),
                                            C.POINTER(C.c_int32), C.c_int, C.POINTER(SpecResult), C.POINTER(C.c_double), C.c_int]
+    L.pib_speculative_orig_generate.argtypes = L.pib_speculative_generate.argtypes
     L.pib_plain_generate.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int, C.c_int, C.POINTER(C.c_int32),
                                      C.POINTER(SpecResult), C.POINTER(C.c_double), C.c_int]
     L._pib_sched_bound = True
@@ -251,8 +252,9 @@ def spec_params(**kw):
     return p
 
 
-def speculative_generate(tgt, dft, prompt_ids, params):
-    """tgt / dft: Context objects created with max_seq >= 1000 * n_parallel + 2.  Returns (token ids, result dict, itl_us)."""
+def speculative_generate(tgt, dft, prompt_ids, params, classic=False):
+    """tgt / dft: Context objects created with max_seq >= 1000 * n_parallel + 2.  Returns (token ids, result dict, itl_us).
+    classic=True runs the synchronous speculative_orig loop instead of PipeInfer's asynchronous one."""
     L = api()
     _bind_sched(L)
     n = len(prompt_ids)
@@ -261,7 +263,8 @@ def speculative_generate(tgt, dft, prompt_ids, params):
     out = (C.c_int32 * cap)()
     itl = (C.c_double * cap)()
     res = SpecResult()
-    k = L.pib_speculative_generate(tgt.ctx, dft.ctx, pr, n, C.byref(params), out, cap, C.byref(res), itl, cap)
+    fn = L.pib_speculative_orig_generate if classic else L.pib_speculative_generate
+    k = fn(tgt.ctx, dft.ctx, pr, n, C.byref(params), out, cap, C.byref(res), itl, cap)
     if k < 0:
         raise PibError(L.pib_last_error().decode())
     return list(out[:min(k, cap)]), res.as_dict(), list(itl[:res.n_itl])
