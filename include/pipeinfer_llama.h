@@ -146,7 +146,8 @@ int                  llama_finish_async_decode(struct llama_context * lctx, stru
 #endif
 bool llama_mpi_iprobe(struct llama_context * lctx);
 void llama_cancel_run(struct llama_context * ctx, int32_t * canceled, int count);
-float * llama_get_logits(struct llama_context * ctx);                      /* lazy device->host copy */
+float * llama_get_logits(struct llama_context * ctx);                      /* lazy device->host copy; on the head of a
+                                                                             * pipeline each row is fetched from the last stage */
 float * llama_get_logits_ith(struct llama_context * ctx, int32_t i);       /* llama.cpp:10019-10025 */
 
 /* ---- KV cache sequence ops (llama.cpp:9238-9359 wrappers over :1657-1734) ---- */

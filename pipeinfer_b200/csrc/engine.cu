@@ -407,7 +407,7 @@ void pib_context_free(pib_context * c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     kv_device_free(&c->kvd);
     void * bufs[] = { c->kcache, c->vcache, c->x, c->x2, c->qkv, c->att, c->proj, c->gu, c->q16, c->mask, c->act, c->rope,
-                      c->cancel_table, c->desc_dev, c->ops_dev, c->bias_ids_dev, c->bias_val_dev };
+                      c->cancel_table, c->desc_dev, c->ops_dev, c->bias_ids_dev, c->bias_val_dev, c->logits_fetch_dev };
     for (void * b : bufs) if (b) cudaFree(b);
     if (c->desc_host) cudaFreeHost(c->desc_host);
     if (c->run_id_host) cudaFreeHost(c->run_id_host);
@@ -823,6 +823,7 @@ void pib_stage_finish(pib_context * c, int batch_id) {
         if (r.in_use && r.batch_id == batch_id) {
             cudaMemsetAsync(c->cancel_table + 1 + r.id, 0, sizeof(int), c->stream);
             r.in_use = false;
+            c->last_finished = r.id;     // its logits stay reserved until the next finish, as on the head (llama_get_logits_ith)
             c->inflight.erase(it);
             return;
         }
@@ -855,16 +856,19 @@ const pib_row_result * pib_last_results(pib_context * c) {
 const float * pib_logits_row(pib_context * c, int i) {
     if (c->last_finished < 0) return nullptr;
     pib_run & r = c->runs[c->last_finished];
-    if (i < 0 || i >= r.n_tokens || !r.logits) {
-        if (!r.logits) pib_set_error("logits: full rows live on the last pipeline stage; the head receives the top-8 of every row");
-        return nullptr;
-    }
+    const bool remote = !r.logits && c->stage.size > 1 && c->stage.first();       // the rows live on the last pipeline stage
+    if (i < 0 || i >= r.n_tokens || (!r.logits && !remote)) return nullptr;
     const size_t V = (size_t) c->model->n_vocab;
     if (c->logits_host.size() < (size_t) r.n_tokens * V) c->logits_host.resize((size_t) r.n_tokens * V);
     if (!c->logits_row_valid[i]) {
-        cudaMemcpyAsync(c->logits_host.data() + (size_t) i * V, r.logits + (size_t) i * V, V * 4, cudaMemcpyDeviceToHost, c->stream);
-        cudaStreamSynchronize(c->stream);
-        c->d2h_bytes += V * 4;
+        if (remote) {
+            if (!c->logits_fetch_dev && cudaMalloc(&c->logits_fetch_dev, V * 4) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+            if (pib_pipe_fetch_logits(c, i, c->logits_fetch_dev, c->logits_host.data() + (size_t) i * V) != PIB_OK) return nullptr;
+        } else {
+            cudaMemcpyAsync(c->logits_host.data() + (size_t) i * V, r.logits + (size_t) i * V, V * 4, cudaMemcpyDeviceToHost, c->stream);
+            cudaStreamSynchronize(c->stream);
+            c->d2h_bytes += V * 4;
+        }
         c->logits_row_valid[i] = 1;
     }
     return c->logits_host.data() + (size_t) i * V;

@@ -117,6 +117,7 @@ struct pib_context {
     std::vector<pib_run> runs;
     std::deque<int>      inflight;        // run ids in issue order
     int                  last_finished = -1;
+    float *              logits_fetch_dev = nullptr;   // head of a pipeline: staging for one row fetched from the last stage
     std::vector<float>   logits_host;     // lazily filled rows of the last finished run
     std::vector<uint8_t> logits_row_valid;
     bool                 logits_all = true;
@@ -171,6 +172,7 @@ int  pib_pipe_ship_ints(int kind, int tag, const int32_t * vals, int n);      //
 int  pib_pipe_ship_bias(const int32_t * ids, const float * vals, int n);
 int  pib_pipe_send_results(pib_context * c, pib_run & run);
 int  pib_pipe_post_result_recv(pib_context * c, pib_run & run);
+int  pib_pipe_fetch_logits(pib_context * c, int row, float * dev_staging, float * host_dst);
 int  pib_stage_serve(pib_context * c);
 extern int (*pib_hop_recv)(pib_context * c, float * x, int n_tokens, const int * cancel);
 extern int (*pib_hop_send)(pib_context * c, const float * x, int n_tokens, const int * cancel);

@@ -38,7 +38,7 @@
 // control ring
 #define PIPE_MAX_RANKS 16
 #define PIPE_MAGIC     0x31424950u
-enum { REC_PAD = 0, REC_DECODE = 1, REC_FINISH = 2, REC_CANCEL = 3, REC_BIAS = 4, REC_RETURN = 5, REC_SHUTDOWN = 6, REC_INTS = 7 };
+enum { REC_PAD = 0, REC_DECODE = 1, REC_FINISH = 2, REC_CANCEL = 3, REC_BIAS = 4, REC_RETURN = 5, REC_SHUTDOWN = 6, REC_INTS = 7, REC_LOGITS = 8 };
 
 struct alignas(64) ring_word { std::atomic<uint64_t> v; char pad[56]; };
 struct ring_hdr {
@@ -394,6 +394,31 @@ int pib_pipe_post_result_recv(pib_context * c, pib_run & run) {
     PIB_CHECK(cudaEventRecord(run.done, P.res_stream));
     return PIB_OK;
 }
+// head: one full logits row of the last finished run, from the last stage (llama_get_logits_ith for callers that still read
+// n_vocab floats, e.g. the reference's common/sampling.cpp:131).  Ordered behind the result rows of the runs in flight.
+int pib_pipe_fetch_logits(pib_context * c, int row, float * dev_staging, float * host_dst) {
+    const int32_t r = row;
+    int rc = pib_pipe_ship_ints(REC_LOGITS, 0, &r, 1);
+    if (rc != PIB_OK) return rc;
+    const size_t V = (size_t) c->model->n_vocab;
+    NCCL_CHECK(N.Recv(dev_staging, V, ncclFloat, P.size - 1, P.back, P.res_stream));
+    PIB_CHECK(cudaMemcpyAsync(host_dst, dev_staging, V * 4, cudaMemcpyDeviceToHost, P.res_stream));
+    PIB_CHECK(cudaStreamSynchronize(P.res_stream));
+    c->d2h_bytes += V * 4;
+    return PIB_OK;
+}
+// last stage: answer it
+static int send_logits_row(pib_context * c, int row) {
+    if (!c->stage.last()) return PIB_OK;
+    if (c->last_finished < 0) { pib_set_error("stage: logits requested before any run finished"); return PIB_ERR_ARG; }
+    pib_run & r = c->runs[c->last_finished];
+    if (row < 0 || row >= r.n_tokens || !r.logits) { pib_set_error("stage: bad logits row %d", row); return PIB_ERR_ARG; }
+    const size_t V = (size_t) c->model->n_vocab;
+    NCCL_CHECK(N.Send(r.logits + (size_t) row * V, V, ncclFloat, 0, P.back, c->stream));
+    P.back_bytes += V * 4;
+    return PIB_OK;
+}
+
 void pib_pipe_install_hooks() {
     pib_hop_recv = hop_recv;
     pib_hop_send = hop_send;
@@ -420,6 +445,7 @@ int pib_stage_serve(pib_context * c) {
             case REC_CANCEL: { const int32_t * q = (const int32_t *) p; pib_cancel(c, q + 2, q[1]); } break;
             case REC_BIAS:   { const int32_t * q = (const int32_t *) p; pib_set_logit_bias(c, q + 2, (const float *) (q + 2 + q[1]), q[1]); } break;
             case REC_INTS:   { const int32_t * q = (const int32_t *) p; P.last_tag = q[0]; P.last_count = q[1]; } break;
+            case REC_LOGITS: { const int32_t * q = (const int32_t *) p; rc = send_logits_row(c, q[2]); } break;
             case REC_RETURN:   ret = 0; break;
             case REC_SHUTDOWN: ret = 1; break;
             default: pib_set_error("pipe: unknown control record %u", h->kind); rc = PIB_ERR_ARG;

@@ -27,6 +27,16 @@ def main():
     cap = 1000 * 2 + 2
     tgt = pipeline.StageContext(rank, world, ranges, 512, cap, synthetic=TGT + (1, 1, 1.0))
     prompt = [1] + [3 + (i * 7919) % (TGT[5] - 3) for i in range(40)]
+    # full logits rows through the llama.h calls the reference's sampling code uses (llama_decode + llama_get_logits_ith):
+    # on the head of a pipeline every row is fetched from the last stage
+    full_logits = None
+    if rank == 0:
+        rc, full_logits = tgt.decode(prompt[:5], list(range(5)), [[0]] * 5)
+        assert rc == 0 and full_logits is not None and np.isfinite(full_logits).all()
+        tgt.L.llama_kv_cache_clear(tgt.ctx)
+        tgt.pause()
+    else:
+        assert tgt.serve() == 0
     results = {}
     for n_draft, n_par in ((3, 2), (4, 1)):
         if rank == 0:
@@ -52,6 +62,9 @@ def main():
         tgt.shutdown()
         # the same model on this GPU alone: plain greedy decoding is the ground truth of speculative decoding
         one = llama.Context(None, n_ctx=512, max_seq=8, synthetic=TGT + (1, 1, 1.0))
+        rc, lg1 = one.decode(prompt[:5], list(range(5)), [[0]] * 5)
+        assert rc == 0 and np.array_equal(lg1, full_logits), float(np.abs(lg1 - full_logits).max())     # same kernels, same order
+        one.L.llama_kv_cache_clear(one.ctx)
         ref, _, _ = llama.plain_generate(one, prompt, 48)
         for key, (toks, res) in results.items():
             n = min(len(ref), len(toks))
@@ -63,7 +76,7 @@ def main():
         assert tgt.serve() == 1
         hop_bytes, hop_msgs, back = pipeline.traffic()
         if rank == world - 1:
-            assert hop_msgs == 0 and back > 0 and back % 96 == 0
+            assert hop_msgs == 0 and back > 0 and (back - 5 * TGT[5] * 4) % 96 == 0          # result rows + the five fetched logits rows
     pipeline.close_pipeline()
     dist.destroy_process_group()
     print("PIPELINE_GPU_OK rank %d" % rank)
