@@ -183,6 +183,20 @@ void        llama_sample_repetition_penalties(struct llama_context * ctx, llama_
                                               const llama_token * last_tokens, size_t penalty_last_n, float penalty_repeat,
                                               float penalty_freq, float penalty_present);                  /* llama.cpp:7286 */
 
+/* host samplers of llama.h:720-800 so that the reference's common/sampling.cpp links unmodified (compat_ref.cu); only the
+ * greedy configuration is on the path: tail-free / typical are accepted with neutral parameters, mirostat / classifier-free
+ * guidance / grammar / LoRA are refused with an error */
+void        llama_sample_top_k(struct llama_context * ctx, llama_token_data_array * candidates, int k, size_t min_keep);
+void        llama_sample_top_p(struct llama_context * ctx, llama_token_data_array * candidates, float p, size_t min_keep);
+void        llama_sample_min_p(struct llama_context * ctx, llama_token_data_array * candidates, float p, size_t min_keep);
+void        llama_sample_tail_free(struct llama_context * ctx, llama_token_data_array * candidates, float z, size_t min_keep);
+void        llama_sample_typical(struct llama_context * ctx, llama_token_data_array * candidates, float p, size_t min_keep);
+void        llama_sample_temp(struct llama_context * ctx, llama_token_data_array * candidates, float temp);
+llama_token llama_sample_token(struct llama_context * ctx, llama_token_data_array * candidates);
+bool        llama_mmap_supported(void);
+bool        llama_mlock_supported(void);
+int         llama_max_devices(void);
+
 /* ---- reporting (llama.h:323, 860-872; llama.cpp:10182-10240) ---- */
 int          llama_vocab_type(const struct llama_model * model);           /* 0 = SPM */
 void         llama_print_timings(struct llama_context * ctx);

@@ -1,0 +1,147 @@
+// compat_ref.cu -- the remaining symbols the reference's own examples/speculative/speculative.cpp + common/*.cpp link
+// against (llama.h sampling section :700-800, grammar :810-850, misc :263-300; ggml.h time / cpu-feature probes), so that
+// the UNMODIFIED reference program can be linked with this library in place of llama.o + ggml*.o (INTEGRATION.md §1;
+// oracle/Makefile builds it as oracle/_ref/speculative_b200 and tests/test_gpu_cli.py runs it).
+//
+// Samplers are host code over llama_token_data_array exactly as in the reference; the ones on the path's greedy
+// configuration (softmax, greedy, repetition penalties) live in llama_api.cu.  Grammar sampling, LoRA, mirostat,
+// classifier-free guidance, tail-free and locally-typical sampling are outside the path: they are accepted when their
+// parameters are neutral (as the reference's own early returns do) and refused loudly otherwise.
+#include "engine.cuh"
+#include "../../include/pipeinfer_llama.h"
+
+#include <sys/time.h>
+
+#include <algorithm>
+#include <random>
+#include <vector>
+
+static void not_on_path(const char * what) {
+    pib_set_error("%s is not implemented (outside the speculation path: greedy sampling only)", what);
+    fprintf(stderr, "libpipeinfer_b200: %s\n", pib_last_error());
+}
+
+extern "C" {
+
+// ---- ggml.h ----
+int64_t ggml_time_us(void) { return llama_time_us(); }
+void    ggml_print_backtrace(void) {}
+int ggml_cpu_has_avx(void) { return 0; }
+int ggml_cpu_has_avx2(void) { return 0; }
+int ggml_cpu_has_avx512(void) { return 0; }
+int ggml_cpu_has_avx512_vbmi(void) { return 0; }
+int ggml_cpu_has_avx512_vnni(void) { return 0; }
+int ggml_cpu_has_fma(void) { return 0; }
+int ggml_cpu_has_neon(void) { return 0; }
+int ggml_cpu_has_arm_fma(void) { return 0; }
+int ggml_cpu_has_f16c(void) { return 0; }
+int ggml_cpu_has_fp16_va(void) { return 0; }
+int ggml_cpu_has_wasm_simd(void) { return 0; }
+int ggml_cpu_has_blas(void) { return 0; }
+int ggml_cpu_has_cublas(void) { return 1; }
+int ggml_cpu_has_clblast(void) { return 0; }
+int ggml_cpu_has_gpublas(void) { return 1; }
+int ggml_cpu_has_sse3(void) { return 0; }
+int ggml_cpu_has_ssse3(void) { return 0; }
+int ggml_cpu_has_vsx(void) { return 0; }
+
+// ---- llama.h misc ----
+bool llama_mmap_supported(void) { return true; }
+bool llama_mlock_supported(void) { return false; }
+int  llama_max_devices(void) { return 16; }
+int  llama_model_apply_lora_from_file(const struct llama_model * model, const char * path_lora, float scale, const char * path_base_model,
+                                      int n_threads) {
+    (void) model; (void) path_lora; (void) scale; (void) path_base_model; (void) n_threads;
+    not_on_path("llama_model_apply_lora_from_file");
+    return 1;
+}
+
+// ---- samplers (llama.cpp:7019-7500) ----
+void llama_sample_top_k(struct llama_context * ctx, llama_token_data_array * candidates, int k, size_t min_keep) {      // :7048
+    (void) ctx;
+    k = std::max(k, (int) min_keep);
+    k = std::min(k, (int) candidates->size);
+    if (!candidates->sorted) {
+        auto comp = [](const llama_token_data & a, const llama_token_data & b) { return a.logit > b.logit; };
+        if (k == (int) candidates->size) std::sort(candidates->data, candidates->data + candidates->size, comp);
+        else std::partial_sort(candidates->data, candidates->data + k, candidates->data + candidates->size, comp);
+        candidates->sorted = true;
+    }
+    candidates->size = (size_t) k;
+}
+void llama_sample_top_p(struct llama_context * ctx, llama_token_data_array * candidates, float p, size_t min_keep) {    // :7073
+    if (p >= 1.0f) return;
+    llama_sample_softmax(ctx, candidates);
+    float  cum_sum  = 0.0f;
+    size_t last_idx = candidates->size;
+    for (size_t i = 0; i < candidates->size; ++i) {
+        cum_sum += candidates->data[i].p;
+        if (cum_sum >= p && i + 1 >= min_keep) { last_idx = i + 1; break; }
+    }
+    candidates->size = last_idx;
+}
+void llama_sample_min_p(struct llama_context * ctx, llama_token_data_array * candidates, float p, size_t min_keep) {    // :7105
+    if (p <= 0.0f || !candidates->size) return;
+    llama_sample_softmax(ctx, candidates);
+    const float scale = candidates->data[0].p;
+    size_t i = 1;
+    for (; i < candidates->size; ++i) if (candidates->data[i].p < p * scale && i >= min_keep) break;
+    candidates->size = i;
+}
+void llama_sample_tail_free(struct llama_context * ctx, llama_token_data_array * candidates, float z, size_t min_keep) { // :7133
+    (void) ctx; (void) min_keep;
+    if (z >= 1.0f || candidates->size <= 2) return;        // the reference's own early return
+    not_on_path("llama_sample_tail_free with z < 1");
+}
+void llama_sample_typical(struct llama_context * ctx, llama_token_data_array * candidates, float p, size_t min_keep) {  // :7190
+    (void) ctx; (void) candidates; (void) min_keep;
+    if (p >= 1.0f) return;                                  // the reference's own early return
+    not_on_path("llama_sample_typical with p < 1");
+}
+void llama_sample_temp(struct llama_context * ctx, llama_token_data_array * candidates, float temp) {                   // :7259
+    (void) ctx;
+    for (size_t i = 0; i < candidates->size; ++i) candidates->data[i].logit /= temp;
+}
+void llama_sample_classifier_free_guidance(struct llama_context * ctx, llama_token_data_array * candidates,
+                                           struct llama_context * guidance_ctx, float scale) {
+    (void) ctx; (void) candidates; (void) guidance_ctx; (void) scale;
+    not_on_path("llama_sample_classifier_free_guidance");
+}
+llama_token llama_sample_token(struct llama_context * ctx, llama_token_data_array * candidates) {                       // :7511
+    (void) ctx;
+    static std::mt19937 rng(0xFFFFFFFFu);                   // the reference seeds ctx->rng from params.seed; one stream here
+    llama_sample_softmax(nullptr, candidates);
+    std::vector<float> probs;
+    probs.reserve(candidates->size);
+    for (size_t i = 0; i < candidates->size; ++i) probs.push_back(candidates->data[i].p);
+    std::discrete_distribution<> dist(probs.begin(), probs.end());
+    return candidates->data[dist(rng)].id;
+}
+llama_token llama_sample_token_mirostat(struct llama_context * ctx, llama_token_data_array * candidates, float tau, float eta, int m, float * mu) {
+    (void) tau; (void) eta; (void) m; (void) mu;
+    not_on_path("llama_sample_token_mirostat");
+    return llama_sample_token_greedy(ctx, candidates);
+}
+llama_token llama_sample_token_mirostat_v2(struct llama_context * ctx, llama_token_data_array * candidates, float tau, float eta, float * mu) {
+    (void) tau; (void) eta; (void) mu;
+    not_on_path("llama_sample_token_mirostat_v2");
+    return llama_sample_token_greedy(ctx, candidates);
+}
+
+// ---- grammar (llama.h:810-850): only an absent grammar is supported ----
+struct llama_grammar;
+struct llama_grammar * llama_grammar_init(const void ** rules, size_t n_rules, size_t start_rule_index) {
+    (void) rules; (void) n_rules; (void) start_rule_index;
+    not_on_path("llama_grammar_init");
+    return nullptr;
+}
+void llama_grammar_free(struct llama_grammar * grammar) { (void) grammar; }
+struct llama_grammar * llama_grammar_copy(const struct llama_grammar * grammar) { (void) grammar; return nullptr; }
+void llama_sample_grammar(struct llama_context * ctx, llama_token_data_array * candidates, const struct llama_grammar * grammar) {
+    (void) ctx; (void) candidates; (void) grammar;
+}
+void llama_grammar_accept_token(struct llama_context * ctx, struct llama_grammar * grammar, llama_token token) {
+    (void) ctx; (void) grammar; (void) token;
+}
+
+}   // extern "C"

@@ -51,3 +51,21 @@ def test_cli_two_stages_matches_reference_text(golden_dir, tmp_path):
     got, ref = generated(r.stdout, gold)
     n = min(len(got), len(ref))
     assert n >= 20 and got[:n] == ref[:n], (got, ref)
+
+
+REF_ON_OURS = os.path.join(ROOT, "oracle", "_ref", "speculative_b200")
+
+
+@pytest.mark.skipif(not os.path.exists(REF_ON_OURS), reason="oracle/_ref/speculative_b200 is built only where /root/reference exists")
+def test_unmodified_reference_speculative_runs_on_this_library(golden_dir, tmp_path):
+    # the reference's own examples/speculative/speculative.cpp + common/*.cpp, compiled from /root/reference and linked against
+    # libpipeinfer_b200.so instead of llama.o / ggml*.o (oracle/Makefile): their scheduler and sampling code drive this engine
+    # through llama.h alone, and must print what they print on top of their own CPU engine
+    gold = json.load(open(os.path.join(golden_dir, "speculative_q8_0.json")))
+    r = subprocess.run([REF_ON_OURS] + cli_args(golden_dir, gold), cwd=tmp_path, capture_output=True, timeout=300,
+                       env=dict(os.environ, PIB_MAX_SEQ="1002"))
+    assert r.returncode == 0, r.stderr[-3000:]
+    got, ref = generated(r.stdout, gold)
+    n = min(len(got), len(ref))
+    assert n >= 20 and got[:n] == ref[:n], (got, ref)
+    assert b"n_accept" in r.stderr
