@@ -10,6 +10,7 @@
 #include "engine.cuh"
 #include "../../include/pipeinfer_llama.h"
 
+#include <string.h>
 #include <sys/time.h>
 
 #include <algorithm>
@@ -54,6 +55,35 @@ int  llama_model_apply_lora_from_file(const struct llama_model * model, const ch
     (void) model; (void) path_lora; (void) scale; (void) path_base_model; (void) n_threads;
     not_on_path("llama_model_apply_lora_from_file");
     return 1;
+}
+
+// ---- what examples/main/main.cpp needs on top (llama.h:249-260, 350, 524-540, 692, 860-872) ----
+int64_t ggml_time_ms(void) { return llama_time_us() / 1000; }
+void    llama_set_rng_seed(struct llama_context * ctx, uint32_t seed) { (void) ctx; (void) seed; }      // greedy path: no RNG in use
+int     llama_model_desc(const struct llama_model * model, char * buf, size_t buf_size) {
+    return snprintf(buf, buf_size, "pipeinfer_b200 model, %d layers, n_embd %d, n_vocab %d", llama_pib_n_layer(model), llama_n_embd(model), llama_n_vocab(model));
+}
+struct llama_timings { double t_start_ms, t_end_ms, t_load_ms, t_sample_ms, t_p_eval_ms, t_eval_ms; int32_t n_sample, n_p_eval, n_eval; };
+struct llama_timings llama_get_timings(struct llama_context * ctx) {
+    (void) ctx;
+    struct llama_timings t;
+    memset(&t, 0, sizeof(t));
+    t.t_end_ms = (double) llama_time_us() / 1000.0;
+    return t;
+}
+void llama_dump_timing_info_yaml(FILE * stream, const struct llama_context * ctx) { (void) ctx; fprintf(stream, "\n# timings: see llama_print_timings\n"); }
+// session files (prompt caches) are outside the path: loading reports "no session", saving reports failure
+bool llama_load_session_file(struct llama_context * ctx, const char * path_session, llama_token * tokens_out, size_t n_token_capacity,
+                             size_t * n_token_count_out) {
+    (void) ctx; (void) path_session; (void) tokens_out; (void) n_token_capacity;
+    if (n_token_count_out) *n_token_count_out = 0;
+    not_on_path("llama_load_session_file");
+    return false;
+}
+bool llama_save_session_file(struct llama_context * ctx, const char * path_session, const llama_token * tokens, size_t n_token_count) {
+    (void) ctx; (void) path_session; (void) tokens; (void) n_token_count;
+    not_on_path("llama_save_session_file");
+    return false;
 }
 
 // ---- samplers (llama.cpp:7019-7500) ----

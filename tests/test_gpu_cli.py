@@ -69,3 +69,19 @@ def test_unmodified_reference_speculative_runs_on_this_library(golden_dir, tmp_p
     n = min(len(got), len(ref))
     assert n >= 20 and got[:n] == ref[:n], (got, ref)
     assert b"n_accept" in r.stderr
+
+
+MAIN_ON_OURS = os.path.join(ROOT, "oracle", "_ref", "main_b200")
+
+
+@pytest.mark.skipif(not os.path.exists(MAIN_ON_OURS), reason="oracle/_ref/main_b200 is built only where /root/reference exists")
+def test_unmodified_reference_main_runs_on_this_library(golden_dir, tmp_path):
+    # examples/main/main.cpp (plain greedy decoding, the paper's "sequential" baseline), same treatment
+    gold = json.load(open(os.path.join(golden_dir, "speculative_q8_0.json")))
+    args = ["-m", os.path.join(golden_dir, "tiny_q8_0.gguf"), "-p", gold["prompt"], "-n", "24", "-c", "256", "--temp", "-1",
+            "--repeat-last-n", "0", "--ignore-eos", "-t", "2"]
+    r = subprocess.run([MAIN_ON_OURS] + args, cwd=tmp_path, capture_output=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-3000:]
+    got, ref = r.stdout.decode("utf-8", "replace"), gold["main_text"]
+    n = min(len(got), len(ref))
+    assert n >= 20 and got[:n] == ref[:n], (got, ref)
