@@ -193,11 +193,14 @@ def main():
     if args.max_spec_runs < 0:
         args.max_spec_runs = world + 1
     (L, E, H, HKV, FF, V, wt), dshape, label = CONFIGS[args.config]
+    wbytes = L * (E * (E + 2 * (E // H) * HKV) + E * E + 3 * E * FF) * BPW[wt] / 8
+    l2_policy = ("inputs larger than L2: every pass streams the target's weights (%.1f GB >> 126 MB)" % (wbytes / 1e9)) if wbytes > 1e9 else \
+                ("smoke configuration: the target's weights (%.0f MB) fit in the 126 MB L2 -- not a bandwidth measurement" % (wbytes / 1e6))
     config = {"workload": "%s, random-init (bigram flavour, draft agreement %.2f), %d-token synthetic prompt, greedy, "
                           "--draft %d -np %d -pa %g -ps %g -n %d -c 1024, at most %s runs in flight, layer split over %d GPU(s)"
                           % (label, args.agree, args.prompt_len, args.draft, args.np, args.pa, args.ps, args.n_predict,
                              args.max_spec_runs or "unbounded", args.gpus),
-              "l2_policy": "inputs larger than L2: every pass streams the target's weights (38.8 GB >> 126 MB)"}
+              "l2_policy": l2_policy}
 
     if args.impl == "reference":
         if rank != 0:
