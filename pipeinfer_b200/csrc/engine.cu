@@ -41,6 +41,15 @@ int  pib_attention(const __half * q16, const __half * kc, const __half * vc, con
 int  pib_sample_topk(float * logits_dev, int n_rows, int n_vocab, const int32_t * bias_ids_dev, const float * bias_val_dev, int n_bias,
                      void * out_dev, const uint8_t * desc, const int * cancel, cudaStream_t st);
 pib_weight * pib_weight_alloc(int type, int64_t N, int64_t K);
+void pib_weight_drop_planes(pib_weight * w);
+
+// matrices the engine only multiplies with keep just their tiles (PIB_KEEP_PLANES=1: keep both forms, e.g. to run variant 1)
+static void drop_planes_of(pib_model * m) {
+    const char * keep = getenv("PIB_KEEP_PLANES");
+    if (keep && atoi(keep) != 0) return;
+    if (m->output) pib_weight_drop_planes(m->output);
+    for (auto & L : m->layers) for (pib_weight * w : { L.wqkv, L.wo, L.wgu, L.wdown }) if (w) pib_weight_drop_planes(w);
+}
 int pib_weight_build_tiles(pib_weight * w);
 
 static int64_t now_us() {
@@ -163,6 +172,7 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
         return nullptr;
     }
     if (m->output) m->weight_bytes += pib_weight_bytes(m->output);
+    drop_planes_of(m);
     return m;
 }
 
@@ -317,6 +327,7 @@ pib_model * pib_model_synthetic(int n_layer, int n_embd, int n_head, int n_head_
         return nullptr;
     }
     if (m->output) m->weight_bytes += pib_weight_bytes(m->output);
+    drop_planes_of(m);
     return m;
 }
 

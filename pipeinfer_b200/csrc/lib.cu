@@ -202,6 +202,7 @@ __global__ void get_rows_kernel(int type, const uint8_t * __restrict__ qs, const
 
 extern "C" int pib_get_rows(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, pib_stream s) {
     if (!w || !ids_dev || !out_dev || n < 1) { pib_set_error("pib_get_rows: bad arguments"); return PIB_ERR_ARG; }
+    if (!w->qs) { pib_set_error("pib_get_rows: this matrix keeps only its tensor-core tiles"); return PIB_ERR_UNSUPP; }
     pib_launch(get_rows_kernel, dim3(n), dim3(256), 0, (cudaStream_t) s, w->type, w->qs, w->d, w->K, ids_dev, out_dev);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
