@@ -124,3 +124,62 @@ def test_non_spec_run_loops_are_coalesced_and_identical(oracle):
         assert np.array_equal(st["pos"], np.ctypeslib.as_array(o.pos, shape=(n_ctx,)))
         assert np.array_equal(st["bits"], np.ctypeslib.as_array(o.bits, shape=(n_ctx, o.n_words)))
         oracle.L.po_kv_free(okv)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_random_long_traces_match_the_oracle_cell_for_cell(oracle, seed):
+    # differential test of the lazy, coalescing op-log front end + host mirror against the plain restatement of the reference's
+    # llama_kv_cache_* (oracle, itself pinned on the reference's KV view): 1500 random ops with scheduler-sized id ranges, runs
+    # of consecutive ids (which the log turns into ranged ops / sweeps), failed decodes, clears; state compared all along
+    rng = np.random.default_rng(1000 + seed)
+    n_ctx, max_seq = 96, 1002
+    kv = KvTest(n_ctx, max_seq)
+    okv = oracle.L.po_kv_new(n_ctx, max_seq)
+    pos_next = 0
+
+    def check():
+        st, o = kv.state(), okv.contents
+        assert (st["head"], st["used"]) == (o.head, o.used)
+        assert np.array_equal(st["pos"], np.ctypeslib.as_array(o.pos, shape=(n_ctx,)))
+        assert np.array_equal(st["bits"], np.ctypeslib.as_array(o.bits, shape=(n_ctx, o.n_words)))
+
+    for it in range(1500):
+        c = int(rng.integers(0, 12))
+        if c < 4:                                                   # decode (with the reference's head heuristic and head advance)
+            n = int(rng.integers(1, 9))
+            seqs = [sorted(set(rng.integers(0, max_seq, int(rng.integers(1, 4))).tolist())) for _ in range(n)]
+            ps = np.arange(pos_next, pos_next + n, dtype=np.int32)
+            ns, ptrs, keep = op.seq_ptrs(seqs)
+            o = okv.contents
+            if o.head > o.used + 2 * n:
+                o.head = 0
+            ok_ref = oracle.L.po_kv_find_slot(okv, n, ps.ctypes.data, ns.ctypes.data, ptrs)
+            rc, _ = kv.decode([0] * n, ps.tolist(), seqs)
+            assert (rc == 0) == bool(ok_ref)
+            if ok_ref:
+                o.head = (o.head + n) % n_ctx if o.head + n < n_ctx else 0
+                pos_next += n
+        elif c < 7:                                                 # a run of consecutive ids: rm then cp (the commit pattern)
+            a = int(rng.integers(0, max_seq - 40)); b = a + int(rng.integers(0, 40))
+            p0 = int(rng.integers(-1, max(1, pos_next))); p1 = int(rng.integers(-1, pos_next + 2))
+            src = int(rng.integers(0, 3))
+            for i in range(a, b + 1):
+                kv.seq_rm(i, p0, p1); oracle.L.po_kv_seq_rm(okv, i, p0, p1)
+                if rng.random() < 0.8 or True:
+                    kv.seq_cp(src, i, p0, p1); oracle.L.po_kv_seq_cp(okv, src, i, p0, p1)
+        elif c < 9:
+            s = int(rng.integers(-1, max_seq)); p0 = int(rng.integers(-1, max(1, pos_next))); p1 = int(rng.integers(-1, pos_next + 2))
+            kv.seq_rm(s, p0, p1); oracle.L.po_kv_seq_rm(okv, s, p0, p1)
+        elif c < 10:
+            a, b = int(rng.integers(0, max_seq)), int(rng.integers(0, max_seq))
+            kv.seq_cp(a, b, -1, -1); oracle.L.po_kv_seq_cp(okv, a, b, -1, -1)
+        elif c < 11:
+            s = int(rng.integers(0, 4))
+            kv.seq_keep(s); oracle.L.po_kv_seq_keep(okv, s)
+        else:
+            kv.seq_rm(-1, -1, -1); oracle.L.po_kv_seq_rm(okv, -1, -1, -1)
+            pos_next = 0
+        if it % 7 == 0:
+            check()
+    check()
+    oracle.L.po_kv_free(okv)
