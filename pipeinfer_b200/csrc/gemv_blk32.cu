@@ -17,6 +17,8 @@
 #include <mutex>
 #include <utility>
 
+#include <math.h>
+
 #include "pib_common.cuh"
 
 #define BK_WARPS   4
@@ -237,15 +239,17 @@ static int bk_ensure_scratch(cudaStream_t st, bk_scratch ** out) {
     std::lock_guard<std::mutex> lock(g_bk_mu);
     bk_scratch & s = g_bk_scratch[std::make_pair(dev, st)];
     if (!s.partial) {
-        if (cudaMalloc(&s.partial, (size_t) 4 << 20) != cudaSuccess || cudaMalloc(&s.counters, 4096 * sizeof(unsigned int)) != cudaSuccess) {
+        if (cudaMalloc(&s.partial, (size_t) 32 << 20) != cudaSuccess || cudaMalloc(&s.counters, 8192 * sizeof(unsigned int)) != cudaSuccess) {
             cudaGetLastError();
             return PIB_ERR_NOMEM;
         }
-        cudaMemset(s.counters, 0, 4096 * sizeof(unsigned int));
+        cudaMemset(s.counters, 0, 8192 * sizeof(unsigned int));
     }
     *out = &s;
     return PIB_OK;
 }
+
+int pib_split_fill_target();         // gemv_mma.cu: CTA count below which a k split is worth its second phase
 
 bool pib_gemv_blk32_supported(const pib_weight * w, int b) {
     return w && (w->type == PIB_TYPE_Q4_0 || w->type == PIB_TYPE_Q8_0) && w->tiles != nullptr && b >= 1 && b <= PIB_MAX_BATCH;
@@ -258,8 +262,8 @@ int pib_gemv_blk32(const pib_weight * w, const void * act_dev, int b, float * y_
     const int            ngr = (int) ((w->K + 255) / 256), n_tiles = (int) ((w->N + 15) / 16);
     // k splits: enough CTAs to fill the machine when there are few row tiles; at least two records per warp
     int split = 1;
-    while (n_tiles * split < 4 * pib_num_sms() && split * 2 * BK_WARPS <= ngr && split < 16) split *= 2;
-    while (split > 1 && ((size_t) split * b * w->N * sizeof(float) > ((size_t) 4 << 20) || n_tiles > 4096)) split /= 2;
+    while (n_tiles * split < pib_split_fill_target() && split * 2 * BK_WARPS <= ngr && split < 16) split *= 2;     // see gemv_mma.cu
+    while (split > 1 && ((size_t) split * b * w->N * sizeof(float) > ((size_t) 32 << 20) || n_tiles > 8192)) split /= 2;
     bk_scratch * s = nullptr;
     if (split > 1 && bk_ensure_scratch(st, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
     const dim3     grid(n_tiles, split);
