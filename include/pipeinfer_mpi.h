@@ -61,6 +61,19 @@ uint16_t ** ggml_mpi_split_range(struct ggml_mpi_context * ctx_mpi, uint16_t sta
 void   ggml_mpi_scatter_layers(struct ggml_mpi_context * ctx_mpi, uint16_t ** layer_ranges);                               /* :561 */
 /* additive: the range ggml_mpi_scatter_layers delivered to this rank */
 void   ggml_mpi_layer_range(struct ggml_mpi_context * ctx_mpi, uint16_t * start, uint16_t * end);
+struct ggml_cgraph;
+void   ggml_mpi_synch_int(struct ggml_mpi_context * ctx_mpi, int32_t * val, int root);                                     /* :375, root 0 only */
+void   ggml_mpi_synch_float(struct ggml_mpi_context * ctx_mpi, float * val, int root);                                     /* :387 */
+void   ggml_mpi_sync_ints_pipelined_back(struct ggml_mpi_context * ctx_mpi, int32_t * vals, int count, int tag);           /* :361, no-op */
+bool   ggml_mpi_is_decoding(struct ggml_mpi_context * ctx_mpi);                                                            /* :50 */
+void   ggml_mpi_wait_recv(struct ggml_mpi_context * ctx_mpi);                                                              /* :516 */
+/* the batch of a decode from the head to every stage, in the reference's message order (ggml-mpi.c:236-347) */
+bool   ggml_mpi_eval_init(struct ggml_mpi_context * ctx_mpi, int32_t * n_tokens, int32_t ** tokens, int32_t ** pos, int32_t ** n_seq_ids,
+                          int32_t *** seq_id, int8_t ** logits, int32_t * batch_id, bool receive_only);
+/* graph hooks (:591, :683, :710): no ggml graph exists here, the hop is done inside the engine; kept so that callers link */
+void   ggml_mpi_graph_creation_post(struct ggml_mpi_context * ctx_mpi, struct ggml_cgraph * cgraph, int n_layers);
+bool   ggml_mpi_graph_compute_pre(struct ggml_mpi_context * ctx_mpi, struct ggml_cgraph * gf);
+void   ggml_mpi_graph_compute_post(struct ggml_mpi_context * ctx_mpi, struct ggml_cgraph * gf);
 
 /* ---- CPU-only test hooks: KV bookkeeping replicated through the control ring (no CUDA call) ---- */
 void pib_kvtest_ship(void * kvtest, int enable);                 /* head: pib_kvtest_decode also publishes its record */

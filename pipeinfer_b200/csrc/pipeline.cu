@@ -33,6 +33,7 @@
 #include <algorithm>
 #include <atomic>
 #include <string>
+#include <vector>
 
 // ---------------------------------------------------------------------------------------------------------------------
 // control ring
@@ -622,4 +623,59 @@ void ggml_mpi_scatter_layers(struct ggml_mpi_context * ctx, uint16_t ** layer_ra
     ctx->layer_start = (uint16_t) flat[2 * ctx->rank]; ctx->layer_end = (uint16_t) flat[2 * ctx->rank + 1];
 }
 void ggml_mpi_layer_range(struct ggml_mpi_context * ctx, uint16_t * start, uint16_t * end) { *start = ctx->layer_start; *end = ctx->layer_end; }
+
+// :375-397: one value from `root` to everybody.  Only the head can publish on the ring, so root must be 0.
+void ggml_mpi_synch_int(struct ggml_mpi_context * ctx, int32_t * val, int root) {
+    if (ctx->size < 2) return;
+    if (root != 0) { pib_set_error("ggml_mpi_synch_int: only root 0 (the head) can publish"); return; }
+    ggml_mpi_sync_ints_pipelined(ctx, val, 1, 100);
+}
+void ggml_mpi_synch_float(struct ggml_mpi_context * ctx, float * val, int root) {
+    int32_t bits;
+    memcpy(&bits, val, 4);
+    ggml_mpi_synch_int(ctx, &bits, root);
+    memcpy(val, &bits, 4);
+}
+// :361-373: the reverse direction (last stage -> head) carries no host records here: sampled rows and logits come back over
+// NCCL, KV ops originate on the head only.  Kept as a no-op so that callers link.
+void ggml_mpi_sync_ints_pipelined_back(struct ggml_mpi_context * ctx, int32_t * vals, int count, int tag) { (void) ctx; (void) vals; (void) count; (void) tag; }
+bool ggml_mpi_is_decoding(struct ggml_mpi_context * ctx) { (void) ctx; return false; }          // :50-56 (state of the reference's async recv)
+void ggml_mpi_wait_recv(struct ggml_mpi_context * ctx) { (void) ctx; }                            // :516-521: receives complete in stream order
+
+// :236-347: the head publishes a batch (batch id, n_tokens, logits mask, tokens, n_seq_id, positions, flattened sequence ids,
+// in the reference's message order and with its tags); every other stage receives it into the caller's pre-allocated
+// arrays (the reference makes the same assumption, :293-300).  On stages the logits mask replaces *logits as in :270-290.
+bool ggml_mpi_eval_init(struct ggml_mpi_context * ctx, int32_t * n_tokens, int32_t ** tokens, int32_t ** pos, int32_t ** n_seq_ids,
+                        int32_t *** seq_id, int8_t ** logits, int32_t * batch_id, bool receive_only) {
+    (void) receive_only;
+    if (ctx->size < 2) return true;
+    ggml_mpi_sync_ints_pipelined(ctx, batch_id, 1, 12 /* GGML_MPI_BATCH_ID */);
+    ggml_mpi_sync_ints_pipelined(ctx, n_tokens, 1, 13 /* GGML_MPI_N_TOKENS */);
+    const int n = *n_tokens;
+    std::vector<int32_t> lg((size_t) n, 0);
+    if (ctx->rank == 0 && *logits) for (int i = 0; i < n; i++) lg[i] = (*logits)[i];
+    ggml_mpi_sync_ints_pipelined(ctx, lg.data(), n, 20 /* GGML_MPI_BATCH_LOGITS */);
+    if (ctx->rank != 0) {
+        bool any = false;
+        for (int i = 0; i < n; i++) any = any || lg[i];
+        if (*logits) { free(*logits); *logits = nullptr; }
+        if (any) { *logits = (int8_t *) calloc((size_t) n, 1); for (int i = 0; i < n; i++) (*logits)[i] = (int8_t) lg[i]; }
+    }
+    ggml_mpi_sync_ints_pipelined(ctx, *tokens, n, 14 /* GGML_MPI_TOKENS */);
+    ggml_mpi_sync_ints_pipelined(ctx, *n_seq_ids, n, 15 /* GGML_MPI_N_SEQ_IDS */);
+    int total = 0;
+    for (int i = 0; i < n; i++) total += (*n_seq_ids)[i];
+    std::vector<int32_t> flat((size_t) total, 0);
+    if (ctx->rank == 0) { int k = 0; for (int i = 0; i < n; i++) for (int j = 0; j < (*n_seq_ids)[i]; j++) flat[k++] = (*seq_id)[i][j]; }
+    ggml_mpi_sync_ints_pipelined(ctx, *pos, n, 17 /* GGML_MPI_POS */);
+    ggml_mpi_sync_ints_pipelined(ctx, flat.data(), total, 16 /* GGML_MPI_SEQ_IDS */);
+    { int k = 0; for (int i = 0; i < n; i++) for (int j = 0; j < (*n_seq_ids)[i]; j++) (*seq_id)[i][j] = flat[k++]; }
+    return true;
+}
+
+// :591-720 graph hooks: there is no ggml graph here; run_chunk (engine.cu) receives before the first local layer and sends
+// after the last one through pib_hop_recv / pib_hop_send.  Present so that callers link.
+void ggml_mpi_graph_creation_post(struct ggml_mpi_context * ctx, struct ggml_cgraph * gf, int n_layers) { (void) ctx; (void) gf; (void) n_layers; }
+bool ggml_mpi_graph_compute_pre(struct ggml_mpi_context * ctx, struct ggml_cgraph * gf) { (void) ctx; (void) gf; return true; }
+void ggml_mpi_graph_compute_post(struct ggml_mpi_context * ctx, struct ggml_cgraph * gf) { (void) ctx; (void) gf; }
 }

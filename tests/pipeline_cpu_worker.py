@@ -63,6 +63,39 @@ def main():
         buf = np.array(vals if rank == 0 else [0] * len(vals), dtype=np.int32)
         L.ggml_mpi_sync_ints_pipelined(ctx, buf.ctypes.data, len(vals), tag)
         assert buf.tolist() == vals, (rank, tag, buf)
+    # ggml_mpi_eval_init: the batch of a decode, head -> stages, into the stages' pre-allocated arrays
+    libc = C.CDLL(None)
+    libc.calloc.restype = C.c_void_p
+    libc.calloc.argtypes = [C.c_size_t, C.c_size_t]
+    L.ggml_mpi_eval_init.restype = C.c_bool
+    L.ggml_mpi_eval_init.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.POINTER(C.c_int32)),
+                                     C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.POINTER(C.POINTER(C.c_int32))),
+                                     C.POINTER(C.POINTER(C.c_int8)), C.POINTER(C.c_int32), C.c_bool]
+    L.ggml_mpi_synch_float.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.c_int]
+    cap, max_ids = 16, 4
+    want_tok, want_pos = [11, 22, 33, 44, 55], [7, 8, 9, 8, 9]
+    want_seq = [[1, 2], [1], [1], [2], [2, 3, 0]]
+    want_lg = [0, 0, 1, 0, 1]
+    tok = (C.c_int32 * cap)(*(want_tok if rank == 0 else []))
+    pos = (C.c_int32 * cap)(*(want_pos if rank == 0 else []))
+    nsq = (C.c_int32 * cap)(*([len(x) for x in want_seq] if rank == 0 else []))
+    rows = [(C.c_int32 * max_ids)(*(want_seq[i] if rank == 0 and i < len(want_seq) else [])) for i in range(cap)]
+    sid = (C.POINTER(C.c_int32) * cap)(*[C.cast(r, C.POINTER(C.c_int32)) for r in rows])
+    lgp = C.cast(libc.calloc(cap, 1), C.POINTER(C.c_int8))            # malloc'd: stages free and replace it (ggml-mpi.c:270-290)
+    if rank == 0:
+        for i, v in enumerate(want_lg):
+            lgp[i] = v
+    n_tok, bid = C.c_int32(len(want_tok) if rank == 0 else 0), C.c_int32(77 if rank == 0 else 0)
+    ptok, ppos, pnsq = C.cast(tok, C.POINTER(C.c_int32)), C.cast(pos, C.POINTER(C.c_int32)), C.cast(nsq, C.POINTER(C.c_int32))
+    psid = C.cast(sid, C.POINTER(C.POINTER(C.c_int32)))
+    assert L.ggml_mpi_eval_init(ctx, C.byref(n_tok), C.byref(ptok), C.byref(ppos), C.byref(pnsq), C.byref(psid), C.byref(lgp), C.byref(bid), False)
+    assert (n_tok.value, bid.value) == (5, 77)
+    assert list(tok[:5]) == want_tok and list(pos[:5]) == want_pos and list(nsq[:5]) == [len(x) for x in want_seq]
+    assert [list(rows[i][:len(want_seq[i])]) for i in range(5)] == want_seq
+    assert [int(lgp[i]) for i in range(5)] == want_lg
+    f = C.c_float(3.25 if rank == 0 else 0.0)
+    L.ggml_mpi_synch_float(ctx, C.byref(f), 0)
+    assert f.value == 3.25
     L.ggml_mpi_barrier(ctx)
 
     # ---- KV bookkeeping replicated through decode records ----------------------------------------------------------------
