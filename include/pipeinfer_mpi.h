@@ -41,6 +41,7 @@ void   ggml_mpi_backend_init(void);                                             
 void   ggml_mpi_backend_free(void);                                                        /* :63  */
 struct ggml_mpi_context * ggml_mpi_init(void);                                             /* :67  */
 void   ggml_mpi_free(struct ggml_mpi_context * ctx);                                       /* :100 */
+struct ggml_mpi_context * ggml_mpi_split_comm(struct ggml_mpi_context * ctx, int color, int key);   /* :84 */
 int    ggml_mpi_rank(struct ggml_mpi_context * ctx);                                       /* :128 */
 size_t ggml_mpi_size(struct ggml_mpi_context * ctx);                                       /* :132 */
 void   ggml_mpi_barrier(struct ggml_mpi_context * ctx);                                    /* :136 */

@@ -551,6 +551,14 @@ struct ggml_mpi_context * ggml_mpi_init(void) {                              // 
     return ctx;
 }
 void   ggml_mpi_free(struct ggml_mpi_context * ctx) { delete ctx; }          // :100
+// :84-98 MPI_Comm_split: the reference uses it to separate the target pipeline's ranks from the draft pipeline's.  Both
+// pipelines' heads live in rank 0's process here, so a split keeps the stage set (colour >= 0) or yields a lone context
+struct ggml_mpi_context * ggml_mpi_split_comm(struct ggml_mpi_context * ctx, int color, int key) {
+    (void) key;
+    ggml_mpi_context * n = new ggml_mpi_context(*ctx);
+    if (color < 0) { n->rank = 0; n->size = 1; }
+    return n;
+}
 int    ggml_mpi_rank(struct ggml_mpi_context * ctx) { return ctx->rank; }   // :128
 size_t ggml_mpi_size(struct ggml_mpi_context * ctx) { return (size_t) ctx->size; }
 int    ggml_mpi_next_node(struct ggml_mpi_context * ctx) { return (ctx->rank + 1) % ctx->size; }      // :164
