@@ -393,7 +393,7 @@ def main():
         config["workload"] = config["workload"].replace("greedy,", "greedy, CLASSIC synchronous speculation (reference `speculative_orig`),")
     line = {"metric": "accepted tokens/sec", "value": n_tok / t_dec, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": wall_ms / args.steps, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "int8 x int4 blocks (Q4_K x Q8_K), fp32 accumulate", "data": "synthetic", "config": config,
+            "vs_baseline": None, "dtype": {Q4_K: "int8 x int4 blocks (Q4_K x Q8_K), fp32 accumulate", Q4_0: "int8 x int4 blocks (Q4_0 x Q8_0), fp32 accumulate", Q8_0: "int8 x int8 blocks (Q8_0 x Q8_0), fp32 accumulate"}[wt], "data": "synthetic", "config": config,
             "latency_p50_ms": p50, "latency_mean_ms": sum(itls_ms) / len(itls_ms) if itls_ms else None,
             "ttft_ms": 1000.0 * results[-1]["ttft_s"], "accept_rate": acc,
             "spec": {k: sum(r[k] for r in results) / len(results) for k in ("n_predict", "n_drafted", "n_accept", "n_cancelled", "n_spec_runs")},
