@@ -55,6 +55,7 @@ typedef struct { po_fp16 d; uint8_t qs[QK / 2]; } blk_q4_0;                     
 typedef struct { po_fp16 d; int8_t qs[QK]; } blk_q8_0;                                        /* 34 B */
 typedef struct { po_fp16 d; po_fp16 dmin; uint8_t scales[12]; uint8_t qs[QK_K / 2]; } blk_q4_K; /* 144 B */
 typedef struct { float d; int8_t qs[QK_K]; int16_t bsums[QK_K / 16]; } blk_q8_K;              /* 292 B */
+typedef struct { uint8_t ql[QK_K / 2]; uint8_t qh[QK_K / 4]; int8_t scales[QK_K / 16]; po_fp16 d; } blk_q6_K;   /* 210 B, ggml-quants.h:152-157 */
 #pragma pack(pop)
 
 /* hsum_float_8, ggml-quants.c:67-73: (hi128 + lo128) -> (x + movehl) -> (x + movehdup) */
@@ -269,6 +270,68 @@ void po_vec_dot_q4_K_q8_K(int n, float * s, const void * vx, const void * vy) {
     *s = hsum8(acc) + (m0 + m1);
 }
 
+/* ggml-quants.c:1994-2040 */
+void po_dequantize_row_q6_K(const void * vx, float * y, int k) {
+    const blk_q6_K * x = (const blk_q6_K *) vx;
+    const int nb = k / QK_K;
+    for (int i = 0; i < nb; i++) {
+        const float     d  = po_fp16_to_fp32(x[i].d);
+        const uint8_t * ql = x[i].ql;
+        const uint8_t * qh = x[i].qh;
+        const int8_t *  sc = x[i].scales;
+        for (int n = 0; n < QK_K; n += 128) {
+            for (int l = 0; l < 32; ++l) {
+                const int    is = l / 16;
+                const int8_t q1 = (int8_t) ((ql[l + 0] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
+                const int8_t q2 = (int8_t) ((ql[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
+                const int8_t q3 = (int8_t) ((ql[l + 0] >> 4) | (((qh[l] >> 4) & 3) << 4)) - 32;
+                const int8_t q4 = (int8_t) ((ql[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+                y[l + 0]  = d * sc[is + 0] * q1;
+                y[l + 32] = d * sc[is + 2] * q2;
+                y[l + 64] = d * sc[is + 4] * q3;
+                y[l + 96] = d * sc[is + 6] * q4;
+            }
+            y += 128; ql += 64; qh += 32; sc += 8;
+        }
+    }
+}
+
+/* ggml-quants.c:6739-6812 (AVX2).  Per super-block d = y.d * fp16(x.d).  The 256 values are 2 halves x 4 groups of 32
+ * (group g of half j: ql nibbles low/high of bytes [0,32) / [32,64), 2 bits of qh, y[128 j + 32 g ..]).  maddubs gives int16
+ * pair sums q*y (no saturation: 63*127*2), minus 32*(y pair sum); madd with the group's two int8 scales (first 16 values /
+ * last 16) gives 8 int32 lanes, lane m = elements 4m..4m+3 of the group; the lanes add up over the 8 groups, then
+ * acc = fma(d, float(sumi), acc) and hsum_float_8. */
+void po_vec_dot_q6_K_q8_K(int n, float * s, const void * vx, const void * vy) {
+    const blk_q6_K * x  = (const blk_q6_K *) vx;
+    const blk_q8_K * y  = (const blk_q8_K *) vy;
+    const int        nb = n / QK_K;
+    float acc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    for (int i = 0; i < nb; ++i) {
+        const float     d  = y[i].d * po_fp16_to_fp32(x[i].d);
+        const uint8_t * ql = x[i].ql;
+        const uint8_t * qh = x[i].qh;
+        const int8_t *  q8 = y[i].qs;
+        int32_t sumi[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+        for (int j = 0; j < QK_K / 128; ++j) {
+            for (int g = 0; g < 4; g++) {
+                for (int m = 0; m < 8; m++) {
+                    int dot = 0;
+                    for (int t = 0; t < 4; t++) {
+                        const int l  = 4 * m + t;
+                        const int lo = (g & 1) ? ql[32 + l] : ql[l];
+                        const int q  = ((g < 2) ? (lo & 0xF) : (lo >> 4)) | (((qh[l] >> (2 * g)) & 3) << 4);
+                        dot += (q - 32) * (int) q8[32 * g + l];
+                    }
+                    sumi[m] += (int) x[i].scales[8 * j + 2 * g + (m >= 4)] * dot;
+                }
+            }
+            ql += 64; qh += 32; q8 += 128;
+        }
+        for (int l = 0; l < 8; l++) acc[l] = fmaf(d, (float) sumi[l], acc[l]);
+    }
+    *s = hsum8(acc);
+}
+
 /* ggml.c:1200-1235 with GGML_F16_STEP 32, GGML_F16_EPR 8, GGML_F16_ARR 4 (F16C + FMA), reduce macro ggml.c:772-790 */
 void po_vec_dot_f16(int n, float * s, const po_fp16 * x, const po_fp16 * y) {
     double    sumf = 0.0;
@@ -294,6 +357,7 @@ size_t po_row_size(int type, int64_t k) {
         case PO_TYPE_Q4_0: return (size_t) (k / QK) * sizeof(blk_q4_0);
         case PO_TYPE_Q8_0: return (size_t) (k / QK) * sizeof(blk_q8_0);
         case PO_TYPE_Q4_K: return (size_t) (k / QK_K) * sizeof(blk_q4_K);
+        case PO_TYPE_Q6_K: return (size_t) (k / QK_K) * sizeof(blk_q6_K);
         case PO_TYPE_F32:  return (size_t) k * 4;
     }
     return 0;
@@ -303,10 +367,11 @@ size_t po_row_size(int type, int64_t k) {
  * weights, Q8_K for Q4_K: ggml.c:455-465, 541-548), then dst[i1][ir0] = vec_dot(ne00, src0 row ir0, src1 row i1). */
 void po_mul_mat(int type, const void * w, int64_t N, int64_t K, const float * x, int b, float * y) {
     const size_t wrow = po_row_size(type, K);
-    const size_t arow = (type == PO_TYPE_Q4_K) ? (size_t) (K / QK_K) * sizeof(blk_q8_K) : (size_t) (K / QK) * sizeof(blk_q8_0);
+    const int    kq   = type == PO_TYPE_Q4_K || type == PO_TYPE_Q6_K;             /* K-quants multiply with Q8_K activations */
+    const size_t arow = kq ? (size_t) (K / QK_K) * sizeof(blk_q8_K) : (size_t) (K / QK) * sizeof(blk_q8_0);
     char * act = (char *) malloc(arow * (size_t) b);
     for (int t = 0; t < b; t++) {
-        if (type == PO_TYPE_Q4_K) po_quantize_row_q8_K(x + (size_t) t * K, act + arow * t, (int) K);
+        if (kq) po_quantize_row_q8_K(x + (size_t) t * K, act + arow * t, (int) K);
         else                      po_quantize_row_q8_0(x + (size_t) t * K, act + arow * t, (int) K);
     }
     for (int t = 0; t < b; t++) {
@@ -317,6 +382,7 @@ void po_mul_mat(int type, const void * w, int64_t N, int64_t K, const float * x,
                 case PO_TYPE_Q4_0: po_vec_dot_q4_0_q8_0((int) K, o, wr, act + arow * t); break;
                 case PO_TYPE_Q8_0: po_vec_dot_q8_0_q8_0((int) K, o, wr, act + arow * t); break;
                 case PO_TYPE_Q4_K: po_vec_dot_q4_K_q8_K((int) K, o, wr, act + arow * t); break;
+                case PO_TYPE_Q6_K: po_vec_dot_q6_K_q8_K((int) K, o, wr, act + arow * t); break;
             }
         }
     }
@@ -564,6 +630,7 @@ static void dequant_row(int type, const void * w, int64_t row, int64_t k, float 
         case PO_TYPE_Q4_0: po_dequantize_row_q4_0(p, out, (int) k); break;
         case PO_TYPE_Q8_0: po_dequantize_row_q8_0(p, out, (int) k); break;
         case PO_TYPE_Q4_K: po_dequantize_row_q4_K(p, out, (int) k); break;
+        case PO_TYPE_Q6_K: po_dequantize_row_q6_K(p, out, (int) k); break;
         case PO_TYPE_F32:  memcpy(out, p, 4 * (size_t) k); break;
     }
 }

@@ -139,3 +139,13 @@ def test_split_range_examples(oracle):
     r = r.reshape(8, 2)
     assert r[0].tolist() == [0, 8] and r[1].tolist() == [8, 20] and r[7].tolist() == [r[6][1], 79]
     assert all(r[i][1] == r[i + 1][0] for i in range(7))
+
+
+def test_q6_k_matches_reference_golden(oracle, golden_dir):
+    # Q6_K: the type Q4_K_M files keep output.weight and part of attn_v / ffn_down in (reference ggml-quants.c:1994, :6594)
+    g = np.load(os.path.join(golden_dir, "kernels_q6k.npz"))
+    wt = op.TYPE_Q6_K
+    K = g["x"].shape[1]
+    assert np.array_equal(oracle.dequantize(wt, g["w"], K).view(np.uint32), g["deq"].view(np.uint32))
+    assert np.array_equal(oracle.quantize_act(wt, g["x"]), g["act"])
+    assert np.array_equal(oracle.mul_mat(wt, g["w"], g["x"]).view(np.uint32), g["y"].view(np.uint32))
