@@ -122,6 +122,10 @@ struct pib_weight {
     int       owns;
 };
 
+// activation format a weight type multiplies with, named by the weight type that owns the layout below: the K-quants share
+// Q8_K (reference type_traits[].vec_dot_type, ggml.c:455-560)
+static inline int pib_act_family(int wtype) { return wtype == PIB_TYPE_Q6_K ? PIB_TYPE_Q4_K : wtype; }
+
 // byte layout of a quantised-activation buffer for `b` tokens (device, produced by act_quant.cu)
 struct pib_act_layout {
     size_t qs_off;     // int8  [b][K]

@@ -7,6 +7,7 @@
 //   Q8_0:  qs  int8  [N][K]          d   fp16 [N][K/32]
 //   Q4_0:  qs  uint8 [N][K/2]        d   fp16 [N][K/32]      (byte j of a block = element j low nibble, j+16 high)
 //   Q4_K:  qs  uint8 [N][K/2]        hdr 16 B [N][K/256]     {fp16 d, fp16 dmin, uint8 scales[12]}
+//   Q6_K:  qs  192 B [N][K/256]      hdr 32 B [N][K/256]     {ql[128], qh[64]} and {int8 scales[16], fp16 d, pad}
 //
 // The tensor-core GEMV additionally builds fragment-major tiles from these planes (gemv_mma.cu).
 #include "pib_common.cuh"
@@ -46,11 +47,24 @@ static __global__ void repack_q4_K(const uint8_t * __restrict__ src, uint8_t * _
     else        *reinterpret_cast<int4 *>(qs + blk * 128 + (p - 1) * 16) = v;
 }
 
+// block_q6_K (ggml-quants.h:152-157): ql[128], qh[64], scales[16], d -- 210 bytes, not even 4-byte aligned in a row
+static __global__ void repack_q6_K(const uint8_t * __restrict__ src, uint8_t * __restrict__ qs, uint8_t * __restrict__ hdr, int64_t nblk) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nblk * 16) return;                // 16 threads per super-block: 12 x 16 quant bytes, 1 x scales, 1 x d, 2 idle
+    const int64_t blk = i / 16;
+    const int     p   = (int) (i % 16);
+    const uint8_t * b = src + blk * 210;
+    if (p < 12) { for (int k = 0; k < 16; k++) qs[blk * 192 + p * 16 + k] = b[p * 16 + k]; }
+    else if (p == 12) { for (int k = 0; k < 16; k++) hdr[blk * 32 + k] = b[192 + k]; }
+    else if (p == 13) { hdr[blk * 32 + 16] = b[208]; hdr[blk * 32 + 17] = b[209]; for (int k = 18; k < 32; k++) hdr[blk * 32 + k] = 0; }
+}
+
 static int block_geom(int type, int * elems, int * bytes) {
     switch (type) {
         case PIB_TYPE_Q4_0: *elems = 32;  *bytes = 18;  return 0;
         case PIB_TYPE_Q8_0: *elems = 32;  *bytes = 34;  return 0;
         case PIB_TYPE_Q4_K: *elems = 256; *bytes = 144; return 0;
+        case PIB_TYPE_Q6_K: *elems = 256; *bytes = 210; return 0;
     }
     return -1;
 }
@@ -66,8 +80,9 @@ static pib_weight * alloc_weight(int type, int64_t N, int64_t K) {
     w->N     = N;
     w->K     = K;
     w->bytes = (size_t) N * (K / be) * bb;
-    size_t qs_bytes = (type == PIB_TYPE_Q8_0) ? (size_t) N * K : (size_t) N * K / 2;
-    size_t d_bytes  = (type == PIB_TYPE_Q4_K) ? (size_t) N * (K / 256) * 16 : (size_t) N * (K / 32) * 2;
+    size_t qs_bytes = (type == PIB_TYPE_Q8_0) ? (size_t) N * K : (type == PIB_TYPE_Q6_K) ? (size_t) N * (K / 256) * 192 : (size_t) N * K / 2;
+    size_t d_bytes  = (type == PIB_TYPE_Q4_K) ? (size_t) N * (K / 256) * 16 : (type == PIB_TYPE_Q6_K) ? (size_t) N * (K / 256) * 32
+                                                                            : (size_t) N * (K / 32) * 2;
     size_t d_off    = (qs_bytes + 255) & ~(size_t) 255;
     if (cudaMalloc(&w->base, d_off + d_bytes + 256) != cudaSuccess) {
         pib_set_error("pib_weight: cudaMalloc of %zu bytes failed", d_off + d_bytes);
@@ -94,6 +109,9 @@ static int repack_from_device(pib_weight * w, const uint8_t * src, int64_t row0,
             break;
         case PIB_TYPE_Q4_0:
             repack_q4_0<<<(unsigned) ((nblk + T - 1) / T), T, 0, st>>>(src, w->qs + blk0 * 16, w->d + blk0, nblk);
+            break;
+        case PIB_TYPE_Q6_K:
+            repack_q6_K<<<(unsigned) ((nblk * 16 + T - 1) / T), T, 0, st>>>(src, w->qs + blk0 * 192, (uint8_t *) w->d + blk0 * 32, nblk);
             break;
         case PIB_TYPE_Q4_K:
             repack_q4_K<<<(unsigned) ((nblk * 9 + T - 1) / T), T, 0, st>>>(src, w->qs + blk0 * 128,
@@ -175,6 +193,14 @@ extern "C" int pib_weight_row_blocks(const pib_weight * w, int64_t row, void * o
     if (!w || row < 0 || row >= w->N) { pib_set_error("pib_weight_row_blocks: bad row"); return PIB_ERR_ARG; }
     if (!w->qs) { pib_set_error("pib_weight_row_blocks: this matrix keeps only its tensor-core tiles"); return PIB_ERR_UNSUPP; }
     uint8_t * o = (uint8_t *) out;
+    if (w->type == PIB_TYPE_Q6_K) {
+        const int64_t nsb = w->K / 256;
+        for (int64_t s = 0; s < nsb; s++) {
+            PIB_CHECK(cudaMemcpy(o + s * 210, w->qs + (row * nsb + s) * 192, 192, cudaMemcpyDeviceToHost));
+            PIB_CHECK(cudaMemcpy(o + s * 210 + 192, (uint8_t *) w->d + (row * nsb + s) * 32, 18, cudaMemcpyDeviceToHost));
+        }
+        return PIB_OK;
+    }
     if (w->type == PIB_TYPE_Q4_K) {
         const int64_t nsb = w->K / 256;
         for (int64_t s = 0; s < nsb; s++) {

@@ -172,6 +172,30 @@ def test_mul_mat_width_not_a_multiple_of_256(lib, oracle, wt, b):
     lib.L.pib_weight_free(h)
 
 
+@pytest.mark.parametrize("b", [1, 3, 8, 9, 16])
+def test_q6_k_mul_mat(lib, oracle, golden_dir, b):
+    # Q6_K: output.weight and part of attn_v / ffn_down of Q4_K_M files.  Block round trip, the reference's golden, random raw blocks
+    wt = op.TYPE_Q6_K
+    g = np.load(os.path.join(golden_dir, "kernels_q6k.npz"))
+    K = g["x"].shape[1]
+    h = lib.weight_upload(wt, g["w"], K)
+    assert np.array_equal(lib.weight_rows(h, wt, g["w"].shape[0], K), g["w"])
+    got = lib.mul_mat(h, g["x"], g["w"].shape[0], 0)
+    assert np.abs(got - g["y"]).max() <= REL_TOL * max(1.0, np.abs(g["y"]).max())
+    lib.L.pib_weight_free(h)
+    rng = np.random.default_rng(60 + b)
+    N, K = 77, 2048
+    w = rng.integers(0, 256, (N, K // 256, 210), dtype=np.uint8)
+    w[:, :, 208:210] = (rng.uniform(0.5, 1.5, (N, K // 256)) * 0.001).astype(np.float16).view(np.uint8).reshape(N, K // 256, 2)
+    w = w.reshape(N, -1)
+    x = (rng.standard_normal((b, K)) * 2).astype(np.float32)
+    h = lib.weight_upload(wt, w, K)
+    ref = oracle.mul_mat(wt, w, x)
+    got = lib.mul_mat(h, x, N, 0)
+    assert np.abs(got - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max())
+    lib.L.pib_weight_free(h)
+
+
 def test_bad_arguments_are_rejected(lib):
     import ctypes as C
     assert lib.L.pib_gemv(None, None, 1, None, 0, None) < 0
