@@ -45,7 +45,7 @@ void rope_table_build(std::vector<float2> & tab, int n_pos, int n_dims, int mode
 __global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8_t * __restrict__ desc,
                                      const float2 * __restrict__ rope, int rope_n_pos, int E, int GQA, int hd, int mode,
                                      __half * __restrict__ q16, __half * __restrict__ kcache, __half * __restrict__ vcache,
-                                     const int * __restrict__ cancel) {
+                                     const int * __restrict__ cancel, const float * __restrict__ vsep) {
     const int32_t * hdr = reinterpret_cast<const int32_t *>(desc + PIB_DESC_HDR_OFF);
     pib_pdl_wait();
     pib_pdl_trigger();
@@ -53,7 +53,8 @@ __global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8
     const int       t    = blockIdx.x;
     const int       pos  = reinterpret_cast<const int32_t *>(desc + PIB_DESC_POS_OFF)[t];
     const int       cell = hdr[PIB_DH_KVHEAD] + t;
-    const float *   row  = qkv + (size_t) t * (E + 2 * GQA);
+    // vsep != null: V comes from its own matmul ([b][GQA]; Wv of another weight type than Wq|Wk) and qkv rows hold Q|K only
+    const float *   row  = qkv + (size_t) t * (E + (vsep ? 1 : 2) * GQA);
     const int       half = hd / 2;
     const float2 *  cs   = rope + (size_t) min(pos, rope_n_pos - 1) * half;
     const int       nq = E / 2, nk = GQA / 2;
@@ -74,7 +75,7 @@ __global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8
         dst[i0] = __float2half_rn(y0);
         dst[i1] = __float2half_rn(y1);
     }
-    const float * v = row + E + GQA;
+    const float * v = vsep ? vsep + (size_t) t * GQA : row + E + GQA;
     for (int i = tid0; i < GQA; i += nthr) vcache[(size_t) cell * GQA + i] = __float2half_rn(v[i]);
 }
 
@@ -340,9 +341,9 @@ static int launch_att(const __half * q16, const __half * kc, const __half * vc, 
 }
 
 int pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * rope, int rope_n_pos, int n_tokens, int E, int GQA,
-                      int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st) {
+                      int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st, const float * vsep) {
     const int parts = max(1, min(16, (E / 2 + GQA / 2 + 511) / 512));
-    pib_launch(rope_kv_store_kernel, dim3(n_tokens, parts), dim3(256), 0, st, qkv, desc, rope, rope_n_pos, E, GQA, hd, mode, q16, kc, vc, cancel);
+    pib_launch(rope_kv_store_kernel, dim3(n_tokens, parts), dim3(256), 0, st, qkv, desc, rope, rope_n_pos, E, GQA, hd, mode, q16, kc, vc, cancel, vsep);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }

@@ -33,7 +33,8 @@ int  pib_add_layernorm_quantize_act(int wtype, const float * x_dev, const float 
 int  pib_gelu_quantize_act(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, const int * cancel, cudaStream_t st);
 void rope_table_build(std::vector<float2> & tab, int n_pos, int n_dims, int mode, float freq_base, float freq_scale);
 int  pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * rope, int rope_n_pos, int n_tokens, int E, int GQA,
-                       int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st);
+                       int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st,
+                       const float * vsep = nullptr);
 bool pib_attention_supported(int hd, int n_head, int n_head_kv, int n_ctx);
 int  pib_attention(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
                    const uint8_t * desc, int n_tokens, int n_head, int n_head_kv, int hd, int n_ctx, float * out, const int * cancel,
@@ -48,7 +49,7 @@ static void drop_planes_of(pib_model * m) {
     const char * keep = getenv("PIB_KEEP_PLANES");
     if (keep && atoi(keep) != 0) return;
     if (m->output) pib_weight_drop_planes(m->output);
-    for (auto & L : m->layers) for (pib_weight * w : { L.wqkv, L.wo, L.wgu, L.wdown }) if (w) pib_weight_drop_planes(w);
+    for (auto & L : m->layers) for (pib_weight * w : { L.wqkv, L.wv, L.wo, L.wgu, L.wdown }) if (w) pib_weight_drop_planes(w);
 }
 int pib_weight_build_tiles(pib_weight * w);
 
@@ -78,8 +79,12 @@ static size_t row_bytes_of(int type, int64_t K) {
 }
 
 // upload the row-wise concatenation of several [N_i][K] tensors as one matrix
-static pib_weight * upload_concat(const std::vector<const GgufTensor *> & ts, int wtype, int64_t K) {
+// (all of one type; `family` = the activation format the model multiplies with: a K-quant file may mix Q4_K and Q6_K)
+static pib_weight * upload_concat(const std::vector<const GgufTensor *> & ts, int family, int64_t K) {
     int64_t N = 0;
+    if (ts.empty() || !ts[0]) return nullptr;
+    const int wtype = ts[0]->type;
+    if (pib_act_family(wtype) != family) { pib_set_error("gguf: tensor type %d does not multiply with the activations of type %d", wtype, family); return nullptr; }
     for (auto t : ts) {
         if (!t || t->type != wtype || t->ne[0] != K) return nullptr;
         N += t->ne[1];
@@ -120,7 +125,7 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
     m->n_vocab = (int) emb->ne[1];
     m->wtype   = emb->type;
     if (m->wtype != PIB_TYPE_Q4_0 && m->wtype != PIB_TYPE_Q8_0 && m->wtype != PIB_TYPE_Q4_K) {
-        pib_set_error("gguf: tensor type %d not supported (Q4_0, Q8_0, Q4_K; make the file with quantize --pure)", m->wtype);
+        pib_set_error("gguf: token_embd of type %d not supported (Q4_0, Q8_0, Q4_K; other matrices may also be Q6_K)", m->wtype);
         delete m;
         return nullptr;
     }
@@ -159,7 +164,15 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
         }
         L.attn_norm = upload_f32(g.tensor(p + "attn_norm.weight"), E);
         L.ffn_norm  = upload_f32(g.tensor(p + "ffn_norm.weight"), E);
-        L.wqkv  = upload_concat({ g.tensor(p + "attn_q.weight"), g.tensor(p + "attn_k.weight"), g.tensor(p + "attn_v.weight") }, m->wtype, E);
+        {
+            const GgufTensor * tq = g.tensor(p + "attn_q.weight"), * tk = g.tensor(p + "attn_k.weight"), * tv = g.tensor(p + "attn_v.weight");
+            if (tq && tk && tv && tv->type != tq->type) {       // Q4_K_M: attn_v in Q6_K (or Q5_K) next to Q4_K attn_q / attn_k
+                L.wqkv = upload_concat({ tq, tk }, m->wtype, E);
+                L.wv   = upload_concat({ tv }, m->wtype, E);
+                ok = ok && L.wv;
+                if (L.wv) m->weight_bytes += pib_weight_bytes(L.wv);
+            } else L.wqkv = upload_concat({ tq, tk, tv }, m->wtype, E);
+        }
         L.wo    = upload_concat({ g.tensor(p + "attn_output.weight") }, m->wtype, E);
         L.wgu   = upload_concat({ g.tensor(p + "ffn_gate.weight"), g.tensor(p + "ffn_up.weight") }, m->wtype, E);
         L.wdown = upload_concat({ g.tensor(p + "ffn_down.weight") }, m->wtype, FF);
@@ -341,7 +354,7 @@ void pib_model_free(pib_model * m) {
         for (float * f : { L.attn_norm_b, L.attn_norm2, L.attn_norm2_b }) if (f) cudaFree(f);
         if (L.attn_norm) cudaFree(L.attn_norm);
         if (L.ffn_norm) cudaFree(L.ffn_norm);
-        pib_weight_free(L.wqkv); pib_weight_free(L.wo); pib_weight_free(L.wgu); pib_weight_free(L.wdown);
+        pib_weight_free(L.wqkv); pib_weight_free(L.wv); pib_weight_free(L.wo); pib_weight_free(L.wgu); pib_weight_free(L.wdown);
     }
     delete m;
 }
@@ -377,6 +390,7 @@ pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_st
     CK(cudaMalloc(&c->x, (size_t) B * E * 4));
     CK(cudaMalloc(&c->x2, (size_t) B * E * 4));
     CK(cudaMalloc(&c->qkv, (size_t) B * (E + 2 * GQA) * 4));
+    CK(cudaMalloc(&c->vsep, (size_t) B * GQA * 4));
     CK(cudaMalloc(&c->att, (size_t) B * E * 4));
     CK(cudaMalloc(&c->proj, (size_t) B * E * 4));
     CK(cudaMalloc(&c->gu, (size_t) B * 2 * FF * 4));
@@ -417,7 +431,7 @@ void pib_context_free(pib_context * c) {
     if (!c) return;
     if (c->stream) cudaStreamSynchronize(c->stream);
     kv_device_free(&c->kvd);
-    void * bufs[] = { c->kcache, c->vcache, c->x, c->x2, c->qkv, c->att, c->proj, c->gu, c->q16, c->mask, c->act, c->rope,
+    void * bufs[] = { c->vsep, c->kcache, c->vcache, c->x, c->x2, c->qkv, c->att, c->proj, c->gu, c->q16, c->mask, c->act, c->rope,
                       c->cancel_table, c->desc_dev, c->ops_dev, c->bias_ids_dev, c->bias_val_dev, c->logits_fetch_dev };
     for (void * b : bufs) if (b) cudaFree(b);
     if (c->desc_host) cudaFreeHost(c->desc_host);
@@ -565,7 +579,9 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
         if (pending_add) TL(5, il, pib_add_rmsnorm_quantize_act(wt, c->proj, c->x2, c->x, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
         else             TL(5, il, pib_add_rmsnorm_quantize_act(wt, c->x, nullptr, nullptr, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
         GEMV(0, il, L.wqkv, c->qkv);
-        TL(6, il, pib_rope_kv_store(c->qkv, desc, c->rope, c->rope_n_pos, ntok, E, GQA, hd, 0, c->q16, c->kcache + lo, c->vcache + lo, cancel, st));
+        if (L.wv) GEMV(0, il, L.wv, c->vsep);
+        TL(6, il, pib_rope_kv_store(c->qkv, desc, c->rope, c->rope_n_pos, ntok, E, GQA, hd, 0, c->q16, c->kcache + lo, c->vcache + lo, cancel, st,
+                                    L.wv ? c->vsep : nullptr));
         TL(7, il, pib_attention(c->q16, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, desc, ntok, m->n_head, m->n_head_kv, hd,
                                 (int) c->n_ctx, c->att, cancel, st));
         TL(8, il, pib_quantize_act_c(wt, c->att, ntok, E, c->act, cancel, st));

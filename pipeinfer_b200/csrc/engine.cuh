@@ -23,6 +23,7 @@ struct pib_layer {
     float *      attn_norm_b = nullptr; // falcon: LayerNorm bias
     float *      attn_norm2 = nullptr, * attn_norm2_b = nullptr;   // falcon 40B/180B layout: the norm that feeds QKV
     pib_weight * wqkv      = nullptr;   // rows: Wq (n_embd) | Wk (n_embd_gqa) | Wv (n_embd_gqa)
+    pib_weight * wv        = nullptr;   // only when Wv has another weight type than Wq / Wk (Q4_K_M files): then wqkv = Wq | Wk
     pib_weight * wo        = nullptr;
     float *      ffn_norm  = nullptr;
     pib_weight * wgu       = nullptr;   // llama rows: gate (n_ff) | up (n_ff); falcon: up (n_ff) only
@@ -91,6 +92,7 @@ struct pib_context {
     __half * kcache = nullptr, * vcache = nullptr;     // [n_layer_local][n_ctx][n_embd_gqa]
 
     // per-chunk work buffers
+    float * vsep = nullptr;               // [chunk][n_embd_gqa]: V of a layer whose Wv is a separate matrix
     float * x = nullptr, * x2 = nullptr, * qkv = nullptr, * att = nullptr, * proj = nullptr, * gu = nullptr;
     __half * q16 = nullptr;
     uint8_t * mask = nullptr;

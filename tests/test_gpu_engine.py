@@ -25,7 +25,8 @@ def llama():
 
 # llama architecture in the three weight types; falcon architecture (LayerNorm + bias, NeoX RoPE, fused QKV, GELU MLP in
 # parallel with attention) in its 7B layout (multi-query, one norm) and its 40B/180B layout (two norms per layer)
-@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0"])
+# q4_k_m: a file as the reference's quantize makes it without --pure (Q4_K with Q6_K output.weight and some attn_v / ffn_down)
+@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m"])
 def test_decode_trace_vs_reference(llama, golden_dir, q):
     ctx = llama.Context(os.path.join(golden_dir, "tiny_%s.gguf" % q), n_ctx=48, max_seq=8)
     errs, row_errs = [], []
