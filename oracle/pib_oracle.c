@@ -55,6 +55,7 @@ typedef struct { po_fp16 d; uint8_t qs[QK / 2]; } blk_q4_0;                     
 typedef struct { po_fp16 d; int8_t qs[QK]; } blk_q8_0;                                        /* 34 B */
 typedef struct { po_fp16 d; po_fp16 dmin; uint8_t scales[12]; uint8_t qs[QK_K / 2]; } blk_q4_K; /* 144 B */
 typedef struct { float d; int8_t qs[QK_K]; int16_t bsums[QK_K / 16]; } blk_q8_K;              /* 292 B */
+typedef struct { po_fp16 d; po_fp16 dmin; uint8_t scales[12]; uint8_t qh[QK_K / 8]; uint8_t qs[QK_K / 2]; } blk_q5_K;   /* 176 B, ggml-quants.h:138-145 */
 typedef struct { uint8_t ql[QK_K / 2]; uint8_t qh[QK_K / 4]; int8_t scales[QK_K / 16]; po_fp16 d; } blk_q6_K;   /* 210 B, ggml-quants.h:152-157 */
 #pragma pack(pop)
 
@@ -270,6 +271,72 @@ void po_vec_dot_q4_K_q8_K(int n, float * s, const void * vx, const void * vy) {
     *s = hsum8(acc) + (m0 + m1);
 }
 
+/* ggml-quants.c:1917-1960 */
+void po_dequantize_row_q5_K(const void * vx, float * y, int k) {
+    const blk_q5_K * x = (const blk_q5_K *) vx;
+    const int nb = k / QK_K;
+    for (int i = 0; i < nb; i++) {
+        const uint8_t * ql = x[i].qs;
+        const uint8_t * qh = x[i].qh;
+        const float d = po_fp16_to_fp32(x[i].d), min = po_fp16_to_fp32(x[i].dmin);
+        int     is = 0;
+        uint8_t sc, m, u1 = 1, u2 = 2;
+        for (int j = 0; j < QK_K; j += 64) {
+            get_scale_min_k4(is + 0, x[i].scales, &sc, &m);
+            const float d1 = d * sc, m1 = min * m;
+            get_scale_min_k4(is + 1, x[i].scales, &sc, &m);
+            const float d2 = d * sc, m2 = min * m;
+            for (int l = 0; l < 32; ++l) *y++ = d1 * ((ql[l] & 0xF) + (qh[l] & u1 ? 16 : 0)) - m1;
+            for (int l = 0; l < 32; ++l) *y++ = d2 * ((ql[l] >> 4) + (qh[l] & u2 ? 16 : 0)) - m2;
+            ql += 32; is += 2;
+            u1 <<= 2; u2 <<= 2;
+        }
+    }
+}
+
+/* ggml-quants.c:5773-5850 (AVX2).  As q4_K with a fifth bit per value (qh bit 2j for the low nibbles of chunk j, bit 2j+1 for
+ * the high nibbles); the mins go through a SCALAR float: summs += dmin * (int) sum_j m_j (bsums[2j] + bsums[2j+1]) (mul then
+ * add, no contraction); result = hsum_float_8(acc) + summs. */
+void po_vec_dot_q5_K_q8_K(int n, float * s, const void * vx, const void * vy) {
+    const blk_q5_K * x  = (const blk_q5_K *) vx;
+    const blk_q8_K * y  = (const blk_q8_K *) vy;
+    const int        nb = n / QK_K;
+    float acc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    float summs  = 0.f;
+    for (int i = 0; i < nb; ++i) {
+        const float d    = y[i].d * po_fp16_to_fp32(x[i].d);
+        const float dmin = -y[i].d * po_fp16_to_fp32(x[i].dmin);
+        uint8_t sc[8], mn[8];
+        for (int j = 0; j < 8; j++) get_scale_min_k4(j, x[i].scales, &sc[j], &mn[j]);
+        int prod = 0;
+        for (int j = 0; j < 8; j++) prod += (int) mn[j] * (int) (int16_t) (y[i].bsums[2 * j] + y[i].bsums[2 * j + 1]);
+        {
+            const float t = dmin * (float) prod;
+            summs = summs + t;
+        }
+        int32_t sumi[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+        const uint8_t * q5 = x[i].qs;
+        const int8_t *  q8 = y[i].qs;
+        for (int j = 0; j < QK_K / 64; ++j) {
+            for (int l = 0; l < 8; l++) {
+                int lo = 0, hi = 0;
+                for (int t = 0; t < 4; t++) {
+                    const int e  = 4 * l + t;
+                    const int ql = (q5[e] & 0xF) + (((x[i].qh[e] >> (2 * j)) & 1) << 4);
+                    const int qu = (q5[e] >> 4) + (((x[i].qh[e] >> (2 * j + 1)) & 1) << 4);
+                    lo += ql * (int) q8[e];
+                    hi += qu * (int) q8[32 + e];
+                }
+                sumi[l] += (int) sc[2 * j] * lo + (int) sc[2 * j + 1] * hi;
+            }
+            q5 += 32;
+            q8 += 64;
+        }
+        for (int l = 0; l < 8; l++) acc[l] = fmaf(d, (float) sumi[l], acc[l]);
+    }
+    *s = hsum8(acc) + summs;
+}
+
 /* ggml-quants.c:1994-2040 */
 void po_dequantize_row_q6_K(const void * vx, float * y, int k) {
     const blk_q6_K * x = (const blk_q6_K *) vx;
@@ -357,6 +424,7 @@ size_t po_row_size(int type, int64_t k) {
         case PO_TYPE_Q4_0: return (size_t) (k / QK) * sizeof(blk_q4_0);
         case PO_TYPE_Q8_0: return (size_t) (k / QK) * sizeof(blk_q8_0);
         case PO_TYPE_Q4_K: return (size_t) (k / QK_K) * sizeof(blk_q4_K);
+        case PO_TYPE_Q5_K: return (size_t) (k / QK_K) * sizeof(blk_q5_K);
         case PO_TYPE_Q6_K: return (size_t) (k / QK_K) * sizeof(blk_q6_K);
         case PO_TYPE_F32:  return (size_t) k * 4;
     }
@@ -367,7 +435,7 @@ size_t po_row_size(int type, int64_t k) {
  * weights, Q8_K for Q4_K: ggml.c:455-465, 541-548), then dst[i1][ir0] = vec_dot(ne00, src0 row ir0, src1 row i1). */
 void po_mul_mat(int type, const void * w, int64_t N, int64_t K, const float * x, int b, float * y) {
     const size_t wrow = po_row_size(type, K);
-    const int    kq   = type == PO_TYPE_Q4_K || type == PO_TYPE_Q6_K;             /* K-quants multiply with Q8_K activations */
+    const int    kq   = type == PO_TYPE_Q4_K || type == PO_TYPE_Q5_K || type == PO_TYPE_Q6_K;             /* K-quants multiply with Q8_K activations */
     const size_t arow = kq ? (size_t) (K / QK_K) * sizeof(blk_q8_K) : (size_t) (K / QK) * sizeof(blk_q8_0);
     char * act = (char *) malloc(arow * (size_t) b);
     for (int t = 0; t < b; t++) {
@@ -382,6 +450,7 @@ void po_mul_mat(int type, const void * w, int64_t N, int64_t K, const float * x,
                 case PO_TYPE_Q4_0: po_vec_dot_q4_0_q8_0((int) K, o, wr, act + arow * t); break;
                 case PO_TYPE_Q8_0: po_vec_dot_q8_0_q8_0((int) K, o, wr, act + arow * t); break;
                 case PO_TYPE_Q4_K: po_vec_dot_q4_K_q8_K((int) K, o, wr, act + arow * t); break;
+                case PO_TYPE_Q5_K: po_vec_dot_q5_K_q8_K((int) K, o, wr, act + arow * t); break;
                 case PO_TYPE_Q6_K: po_vec_dot_q6_K_q8_K((int) K, o, wr, act + arow * t); break;
             }
         }
@@ -630,6 +699,7 @@ static void dequant_row(int type, const void * w, int64_t row, int64_t k, float 
         case PO_TYPE_Q4_0: po_dequantize_row_q4_0(p, out, (int) k); break;
         case PO_TYPE_Q8_0: po_dequantize_row_q8_0(p, out, (int) k); break;
         case PO_TYPE_Q4_K: po_dequantize_row_q4_K(p, out, (int) k); break;
+        case PO_TYPE_Q5_K: po_dequantize_row_q5_K(p, out, (int) k); break;
         case PO_TYPE_Q6_K: po_dequantize_row_q6_K(p, out, (int) k); break;
         case PO_TYPE_F32:  memcpy(out, p, 4 * (size_t) k); break;
     }

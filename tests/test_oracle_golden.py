@@ -141,10 +141,10 @@ def test_split_range_examples(oracle):
     assert all(r[i][1] == r[i + 1][0] for i in range(7))
 
 
-def test_q6_k_matches_reference_golden(oracle, golden_dir):
-    # Q6_K: the type Q4_K_M files keep output.weight and part of attn_v / ffn_down in (reference ggml-quants.c:1994, :6594)
-    g = np.load(os.path.join(golden_dir, "kernels_q6k.npz"))
-    wt = op.TYPE_Q6_K
+@pytest.mark.parametrize("wt,fname", [(op.TYPE_Q6_K, "kernels_q6k.npz"), (op.TYPE_Q5_K, "kernels_q5k.npz")])
+def test_q6_k_q5_k_match_reference_golden(oracle, golden_dir, wt, fname):
+    # the types Q4_K_M files keep output.weight, attn_v and part of ffn_down in (reference ggml-quants.c:1917, 1994, 5680, 6594)
+    g = np.load(os.path.join(golden_dir, fname))
     K = g["x"].shape[1]
     assert np.array_equal(oracle.dequantize(wt, g["w"], K).view(np.uint32), g["deq"].view(np.uint32))
     assert np.array_equal(oracle.quantize_act(wt, g["x"]), g["act"])
