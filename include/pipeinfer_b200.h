@@ -31,6 +31,7 @@ extern "C" {
 #define PIB_TYPE_Q4_0  2
 #define PIB_TYPE_Q8_0  8
 #define PIB_TYPE_Q4_K 12
+#define PIB_TYPE_Q5_K 13   /* matmul only (attn_v of 70B-class Q4_K_M files) */
 #define PIB_TYPE_Q6_K 14   /* matmul only (output.weight / attn_v / ffn_down of Q4_K_M files); activations as for Q4_K (Q8_K) */
 
 #define PIB_MAX_BATCH 16          /* verification batch handled by the dequant-GEMV path (north_star: batch 1-16) */

@@ -192,7 +192,7 @@ static void launch_b(const pib_weight * w, const uint8_t * act, const pib_act_la
 }
 
 int pib_gemv_dp4a(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
-    if (w->type == PIB_TYPE_Q6_K) { pib_set_error("pib_gemv: Q6_K has its own kernel"); return PIB_ERR_UNSUPP; }
+    if (w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K) { pib_set_error("pib_gemv: Q5_K / Q6_K have their own kernels"); return PIB_ERR_UNSUPP; }
     if (!w->qs) { pib_set_error("pib_gemv: variant 1 needs the plane form, which this matrix dropped (set PIB_KEEP_PLANES=1 before loading the model)"); return PIB_ERR_UNSUPP; }
     const pib_act_layout L   = pib_act_layout_of(w->type, w->K, b);
     const uint8_t *      act = (const uint8_t *) act_dev;

@@ -115,12 +115,14 @@ int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_de
 int pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 bool pib_gemv_mma_supported(const pib_weight * w, int b);
 bool pib_gemv_blk32_supported(const pib_weight * w, int b);
+int  pib_gemv_q5k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_q6k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_blk32(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 
 int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, const int * cancel,
                       cudaStream_t st) {
     if (w->type == PIB_TYPE_Q6_K) return pib_gemv_q6k(w, act_dev, b, y_dev, cancel, st);
+    if (w->type == PIB_TYPE_Q5_K) return pib_gemv_q5k(w, act_dev, b, y_dev, cancel, st);
     const bool tc = pib_gemv_mma_supported(w, b);
     if (variant == 3 && tc) return pib_gemv_mma(w, act_dev, b, y_dev, cancel, st);
     if ((variant == 2 || variant == 0) && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);
@@ -133,7 +135,7 @@ extern "C" int pib_gemv(const pib_weight * w, const void * act_dev, int b, float
         pib_set_error("pib_gemv: bad arguments (b = %d, limit %d)", b, PIB_MAX_BATCH);
         return PIB_ERR_ARG;
     }
-    if (w->type == PIB_TYPE_Q6_K) variant = 0;            // one kernel for this type
+    if (w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K) variant = 0;            // one kernel for these types
     if ((variant == 3 && !pib_gemv_mma_supported(w, b)) || (variant == 2 && !pib_gemv_mma_supported(w, b) && !pib_gemv_blk32_supported(w, b))) {
         pib_set_error("pib_gemv: variant 2 needs tiles (Q4_K, Q4_0, Q8_0), variant 3 Q4_K");
         return PIB_ERR_UNSUPP;
@@ -206,7 +208,7 @@ __global__ void get_rows_kernel(int type, const uint8_t * __restrict__ qs, const
 extern "C" int pib_get_rows(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, pib_stream s) {
     if (!w || !ids_dev || !out_dev || n < 1) { pib_set_error("pib_get_rows: bad arguments"); return PIB_ERR_ARG; }
     if (!w->qs) { pib_set_error("pib_get_rows: this matrix keeps only its tensor-core tiles"); return PIB_ERR_UNSUPP; }
-    if (w->type == PIB_TYPE_Q6_K) { pib_set_error("pib_get_rows: Q6_K embeddings are not supported (Q4_K_M files keep token_embd in Q4_K)"); return PIB_ERR_UNSUPP; }
+    if (w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K) { pib_set_error("pib_get_rows: Q5_K / Q6_K embeddings are not supported (Q4_K_M files keep token_embd in Q4_K)"); return PIB_ERR_UNSUPP; }
     pib_launch(get_rows_kernel, dim3(n), dim3(256), 0, (cudaStream_t) s, w->type, w->qs, w->d, w->K, ids_dev, out_dev);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;

@@ -7,6 +7,7 @@
 //   Q8_0:  qs  int8  [N][K]          d   fp16 [N][K/32]
 //   Q4_0:  qs  uint8 [N][K/2]        d   fp16 [N][K/32]      (byte j of a block = element j low nibble, j+16 high)
 //   Q4_K:  qs  uint8 [N][K/2]        hdr 16 B [N][K/256]     {fp16 d, fp16 dmin, uint8 scales[12]}
+//   Q5_K:  qs  160 B [N][K/256]      hdr 16 B [N][K/256]     {qs[128], qh[32]} and {fp16 d, fp16 dmin, uint8 scales[12]}
 //   Q6_K:  qs  192 B [N][K/256]      hdr 32 B [N][K/256]     {ql[128], qh[64]} and {int8 scales[16], fp16 d, pad}
 //
 // The tensor-core GEMV additionally builds fragment-major tiles from these planes (gemv_mma.cu).
@@ -47,6 +48,18 @@ static __global__ void repack_q4_K(const uint8_t * __restrict__ src, uint8_t * _
     else        *reinterpret_cast<int4 *>(qs + blk * 128 + (p - 1) * 16) = v;
 }
 
+// block_q5_K (ggml-quants.h:138-145): d, dmin, scales[12], qh[32], qs[128] -- 176 bytes = 11 x 16
+static __global__ void repack_q5_K(const uint8_t * __restrict__ src, uint8_t * __restrict__ qs, uint8_t * __restrict__ hdr, int64_t nblk) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nblk * 11) return;
+    const int64_t blk = i / 11;
+    const int     p   = (int) (i % 11);
+    const int4    v   = *reinterpret_cast<const int4 *>(src + blk * 176 + p * 16);
+    if (p == 0)     *reinterpret_cast<int4 *>(hdr + blk * 16) = v;
+    else if (p < 3) *reinterpret_cast<int4 *>(qs + blk * 160 + 128 + (p - 1) * 16) = v;
+    else            *reinterpret_cast<int4 *>(qs + blk * 160 + (p - 3) * 16) = v;
+}
+
 // block_q6_K (ggml-quants.h:152-157): ql[128], qh[64], scales[16], d -- 210 bytes, not even 4-byte aligned in a row
 static __global__ void repack_q6_K(const uint8_t * __restrict__ src, uint8_t * __restrict__ qs, uint8_t * __restrict__ hdr, int64_t nblk) {
     const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -64,6 +77,7 @@ static int block_geom(int type, int * elems, int * bytes) {
         case PIB_TYPE_Q4_0: *elems = 32;  *bytes = 18;  return 0;
         case PIB_TYPE_Q8_0: *elems = 32;  *bytes = 34;  return 0;
         case PIB_TYPE_Q4_K: *elems = 256; *bytes = 144; return 0;
+        case PIB_TYPE_Q5_K: *elems = 256; *bytes = 176; return 0;
         case PIB_TYPE_Q6_K: *elems = 256; *bytes = 210; return 0;
     }
     return -1;
@@ -80,8 +94,8 @@ static pib_weight * alloc_weight(int type, int64_t N, int64_t K) {
     w->N     = N;
     w->K     = K;
     w->bytes = (size_t) N * (K / be) * bb;
-    size_t qs_bytes = (type == PIB_TYPE_Q8_0) ? (size_t) N * K : (type == PIB_TYPE_Q6_K) ? (size_t) N * (K / 256) * 192 : (size_t) N * K / 2;
-    size_t d_bytes  = (type == PIB_TYPE_Q4_K) ? (size_t) N * (K / 256) * 16 : (type == PIB_TYPE_Q6_K) ? (size_t) N * (K / 256) * 32
+    size_t qs_bytes = (type == PIB_TYPE_Q8_0) ? (size_t) N * K : (type == PIB_TYPE_Q6_K) ? (size_t) N * (K / 256) * 192 : (type == PIB_TYPE_Q5_K) ? (size_t) N * (K / 256) * 160 : (size_t) N * K / 2;
+    size_t d_bytes  = (type == PIB_TYPE_Q4_K || type == PIB_TYPE_Q5_K) ? (size_t) N * (K / 256) * 16 : (type == PIB_TYPE_Q6_K) ? (size_t) N * (K / 256) * 32
                                                                             : (size_t) N * (K / 32) * 2;
     size_t d_off    = (qs_bytes + 255) & ~(size_t) 255;
     if (cudaMalloc(&w->base, d_off + d_bytes + 256) != cudaSuccess) {
@@ -109,6 +123,9 @@ static int repack_from_device(pib_weight * w, const uint8_t * src, int64_t row0,
             break;
         case PIB_TYPE_Q4_0:
             repack_q4_0<<<(unsigned) ((nblk + T - 1) / T), T, 0, st>>>(src, w->qs + blk0 * 16, w->d + blk0, nblk);
+            break;
+        case PIB_TYPE_Q5_K:
+            repack_q5_K<<<(unsigned) ((nblk * 11 + T - 1) / T), T, 0, st>>>(src, w->qs + blk0 * 160, (uint8_t *) w->d + blk0 * 16, nblk);
             break;
         case PIB_TYPE_Q6_K:
             repack_q6_K<<<(unsigned) ((nblk * 16 + T - 1) / T), T, 0, st>>>(src, w->qs + blk0 * 192, (uint8_t *) w->d + blk0 * 32, nblk);
@@ -193,6 +210,15 @@ extern "C" int pib_weight_row_blocks(const pib_weight * w, int64_t row, void * o
     if (!w || row < 0 || row >= w->N) { pib_set_error("pib_weight_row_blocks: bad row"); return PIB_ERR_ARG; }
     if (!w->qs) { pib_set_error("pib_weight_row_blocks: this matrix keeps only its tensor-core tiles"); return PIB_ERR_UNSUPP; }
     uint8_t * o = (uint8_t *) out;
+    if (w->type == PIB_TYPE_Q5_K) {
+        const int64_t nsb = w->K / 256;
+        for (int64_t s = 0; s < nsb; s++) {
+            PIB_CHECK(cudaMemcpy(o + s * 176, (uint8_t *) w->d + (row * nsb + s) * 16, 16, cudaMemcpyDeviceToHost));
+            PIB_CHECK(cudaMemcpy(o + s * 176 + 16, w->qs + (row * nsb + s) * 160 + 128, 32, cudaMemcpyDeviceToHost));
+            PIB_CHECK(cudaMemcpy(o + s * 176 + 48, w->qs + (row * nsb + s) * 160, 128, cudaMemcpyDeviceToHost));
+        }
+        return PIB_OK;
+    }
     if (w->type == PIB_TYPE_Q6_K) {
         const int64_t nsb = w->K / 256;
         for (int64_t s = 0; s < nsb; s++) {

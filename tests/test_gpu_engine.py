@@ -26,7 +26,7 @@ def llama():
 # llama architecture in the three weight types; falcon architecture (LayerNorm + bias, NeoX RoPE, fused QKV, GELU MLP in
 # parallel with attention) in its 7B layout (multi-query, one norm) and its 40B/180B layout (two norms per layer)
 # q4_k_m: a file as the reference's quantize makes it without --pure (Q4_K with Q6_K output.weight and some attn_v / ffn_down)
-@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m"])
+@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m", "q4_k_s"])
 def test_decode_trace_vs_reference(llama, golden_dir, q):
     ctx = llama.Context(os.path.join(golden_dir, "tiny_%s.gguf" % q), n_ctx=48, max_seq=8)
     errs, row_errs = [], []
@@ -63,6 +63,9 @@ def test_decode_trace_vs_reference(llama, golden_dir, q):
         # it.  The first decode (fresh cache) and the later rows that cannot see the cell must still be exact.
         assert errs[0] < LOGIT_TOL_TYPICAL
         assert row_errs[3][2] < LOGIT_TOL_TYPICAL and row_errs[6][3] < LOGIT_TOL_TYPICAL
+    elif q == "q4_k_s":
+        # same story: one flip in the second decode (4 layers of Q5_K attn_v / ffn_down) that the cache then carries along
+        assert errs[0] < LOGIT_TOL_TYPICAL
     else:
         assert np.median(errs) < LOGIT_TOL_TYPICAL
     ctx.close()

@@ -172,11 +172,11 @@ def test_mul_mat_width_not_a_multiple_of_256(lib, oracle, wt, b):
     lib.L.pib_weight_free(h)
 
 
+@pytest.mark.parametrize("wt,fname,bb,dpos", [(op.TYPE_Q6_K, "kernels_q6k.npz", 210, 208), (op.TYPE_Q5_K, "kernels_q5k.npz", 176, 0)])
 @pytest.mark.parametrize("b", [1, 3, 8, 9, 16])
-def test_q6_k_mul_mat(lib, oracle, golden_dir, b):
-    # Q6_K: output.weight and part of attn_v / ffn_down of Q4_K_M files.  Block round trip, the reference's golden, random raw blocks
-    wt = op.TYPE_Q6_K
-    g = np.load(os.path.join(golden_dir, "kernels_q6k.npz"))
+def test_q6_k_q5_k_mul_mat(lib, oracle, golden_dir, b, wt, fname, bb, dpos):
+    # Q6_K / Q5_K: output.weight, attn_v and part of ffn_down of Q4_K_M files.  Block round trip, the reference's golden, random raw blocks
+    g = np.load(os.path.join(golden_dir, fname))
     K = g["x"].shape[1]
     h = lib.weight_upload(wt, g["w"], K)
     assert np.array_equal(lib.weight_rows(h, wt, g["w"].shape[0], K), g["w"])
@@ -185,8 +185,10 @@ def test_q6_k_mul_mat(lib, oracle, golden_dir, b):
     lib.L.pib_weight_free(h)
     rng = np.random.default_rng(60 + b)
     N, K = 77, 2048
-    w = rng.integers(0, 256, (N, K // 256, 210), dtype=np.uint8)
-    w[:, :, 208:210] = (rng.uniform(0.5, 1.5, (N, K // 256)) * 0.001).astype(np.float16).view(np.uint8).reshape(N, K // 256, 2)
+    w = rng.integers(0, 256, (N, K // 256, bb), dtype=np.uint8)
+    w[:, :, dpos:dpos + 2] = (rng.uniform(0.5, 1.5, (N, K // 256)) * 0.001).astype(np.float16).view(np.uint8).reshape(N, K // 256, 2)
+    if wt == op.TYPE_Q5_K:
+        w[:, :, 2:4] = (rng.uniform(0.5, 1.5, (N, K // 256)) * 0.0005).astype(np.float16).view(np.uint8).reshape(N, K // 256, 2)
     w = w.reshape(N, -1)
     x = (rng.standard_normal((b, K)) * 2).astype(np.float32)
     h = lib.weight_upload(wt, w, K)
