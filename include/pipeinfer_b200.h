@@ -8,7 +8,8 @@
  * PIB_ERR_* code; pib_last_error() gives the message.  There is no CPU fallback: without a CUDA device every entry
  * point fails with PIB_ERR_CUDA.
  *
- * The model/runtime level (llama_decode, llama_batch, llama_kv_cache_seq_*, ggml_mpi_*) is in pipeinfer_llama.h.
+ * The model/runtime level (llama_decode, llama_batch, llama_kv_cache_seq_*) is in pipeinfer_llama.h, the transport level
+ * (ggml_mpi_*, pipeline bring-up) in pipeinfer_mpi.h, the scheduler in pipeinfer_sched.h.
  */
 #ifndef PIPEINFER_B200_H
 #define PIPEINFER_B200_H
@@ -51,8 +52,8 @@ int          pib_memcpy_d2h(void * host, const void * dev, size_t bytes, pib_str
 int          pib_stream_sync(pib_stream s);
 
 /* ---- weights ------------------------------------------------------------------------------------------------- */
-/* Upload an [N][K] matrix given in the reference's block layout (block_q4_0 / block_q8_0 / block_q4_K rows,
- * ggml-quants.h:10-15, 42-47, 116-122) and repack it for the GEMV kernels.  Layout-only: no value changes.
+/* Upload an [N][K] matrix given in the reference's block layout (block_q4_0 / block_q8_0 / block_q4_K / block_q5_K /
+ * block_q6_K rows, ggml-quants.h:10-15, 42-47, 116-122, 138-157) and repack it for the GEMV kernels.  Layout-only: no value changes.
  * Replaces: the mmap'ed tensor data that ggml_compute_forward_mul_mat reads as src0 (ggml.c:9388). */
 pib_weight * pib_weight_upload(int type, const void * host_blocks, int64_t N, int64_t K);
 /* Same, for blocks that are already in device memory (used by the synthetic-model generator). */
@@ -64,7 +65,7 @@ int          pib_weight_row_blocks(const pib_weight * w, int64_t row, void * hos
 
 /* ---- K2: activation quantisation ------------------------------------------------------------------------------ */
 /* Bytes of the device buffer that holds `b` quantised activation rows of length K for weights of `wtype`. */
-size_t pib_act_bytes(int wtype, int64_t K, int b);
+size_t pib_act_bytes(int wtype, int64_t K, int b);          /* wtype: Q4_0 / Q8_0 / Q4_K; Q5_K and Q6_K weights use Q4_K's */
 /* x_dev float [b][K] -> act_dev.  Q8_0 blocks for Q4_0/Q8_0 weights, Q8_K super-blocks for Q4_K weights, with the
  * rounding of the reference's x86 build.  Replaces: quantize_row_q8_0 (ggml-quants.c:632, AVX2 branch :701-760) and
  * quantize_row_q8_K (ggml-quants.c:2329), called from the INIT phase of mul_mat (ggml.c:9493-9509). */
