@@ -51,6 +51,7 @@ struct ring_hdr {
     std::atomic<uint32_t> magic;
     uint8_t   nccl_ids[256];             // the two ncclUniqueIds, published by rank 0 (launchers without a store of their own)
     std::atomic<uint32_t> ids_ready;
+    uint64_t  created_us;                // wall clock of the creation: lets a stage tell a fresh ring from one a crashed run left behind
 };
 struct rec_hdr { uint32_t bytes, kind; };
 struct rec_decode { int32_t batch_id, n_tokens, n_chunks, n_ops; uint32_t desc_stride, pad; };
@@ -91,6 +92,8 @@ struct spinner {
     }
 };
 
+static uint64_t g_ring_min_created_us = 0;      // pib_pipe_open_env: refuse rings older than this (same name = same MASTER_PORT)
+
 extern "C" int pib_pipe_ring_open(const char * name, int rank, int n_ranks, size_t cap_bytes) {
     if (P.h) { pib_set_error("pipe: ring already open"); return PIB_ERR_ARG; }
     if (n_ranks < 1 || n_ranks > PIPE_MAX_RANKS || rank < 0 || rank >= n_ranks) { pib_set_error("pipe: bad rank %d / %d", rank, n_ranks); return PIB_ERR_ARG; }
@@ -120,11 +123,21 @@ extern "C" int pib_pipe_ring_open(const char * name, int rank, int n_ranks, size
     if (rank == 0) {
         P.h->cap = cap_bytes; P.h->n_ranks = (uint32_t) n_ranks;
         P.h->head.v.store(0); P.h->bar_count.v.store(0); P.h->bar_gen.v.store(0); P.h->ids_ready.store(0);
+        P.h->created_us = (uint64_t) (now_s() * 1e6);
         for (int i = 0; i < PIPE_MAX_RANKS; i++) P.h->tail[i].v.store(0);
         P.h->magic.store(PIPE_MAGIC, std::memory_order_release);
     } else {
         spinner sp;
         while (P.h->magic.load(std::memory_order_acquire) != PIPE_MAGIC) if (!sp.step()) { pib_set_error("pipe: ring %s never initialised", name); return PIB_ERR_ARG; }
+        if (P.h->created_us < g_ring_min_created_us) {
+            // a segment of this name left behind by a run that died: the head is about to unlink and re-create it
+            munmap((void *) P.h, P.map_bytes);
+            P.h = nullptr; P.data = nullptr;
+            usleep(20000);
+            static int retries = 0;
+            if (++retries > 3000) { pib_set_error("pipe: only a stale ring %s is there", name); return PIB_ERR_ARG; }
+            return pib_pipe_ring_open(name, rank, n_ranks, cap_bytes);
+        }
     }
     return PIB_OK;
 }
@@ -337,6 +350,7 @@ extern "C" int pib_pipe_open_env(void) {
     if (world <= 1) return 1;
     if (pib_init(lr ? atoi(lr) : rank) != PIB_OK) return PIB_ERR_CUDA;
     const std::string name = std::string("/pib_ring_") + (port ? port : "29500");
+    g_ring_min_created_us = (uint64_t) (now_s() * 1e6) - 120ull * 1000000ull;       // the ranks of one launch start within two minutes
     int rc = pib_pipe_ring_open(name.c_str(), rank, world, (size_t) 64 << 20);
     if (rc != PIB_OK) return rc;
     if (rank == 0) {
