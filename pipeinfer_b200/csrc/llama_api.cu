@@ -63,9 +63,9 @@ void llama_backend_init(bool numa) { (void) numa; ensure_init(); }
 void llama_backend_free(void) {}
 
 struct llama_model * llama_load_model_from_file(const char * path_model, struct llama_model_params params) {
-    (void) params;
-    ensure_init();
-    pib_model * m = pib_model_load_gguf(path_model, 0, -1, true, true);
+    // vocab_only (llama.h:176): hyper-parameters and vocabulary, no tensor, no CUDA call -- the tokenizer works without a GPU
+    if (!params.vocab_only) ensure_init();
+    pib_model * m = params.vocab_only ? pib_model_load_gguf(path_model, 0, 0, false, false) : pib_model_load_gguf(path_model, 0, -1, true, true);
     if (!m) { fprintf(stderr, "llama_load_model_from_file: %s\n", pib_last_error()); return nullptr; }
     llama_model * lm = new llama_model();
     lm->m = m;
