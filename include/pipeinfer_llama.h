@@ -115,10 +115,19 @@ int   llama_n_embd(const struct llama_model * model);
 llama_token llama_token_bos(const struct llama_model * model);
 llama_token llama_token_eos(const struct llama_model * model);
 llama_token llama_token_nl(const struct llama_model * model);
-int   llama_add_bos_token(const struct llama_model * model);
+int   llama_add_bos_token(const struct llama_model * model);   /* tokenizer.ggml.add_bos_token: 0 / 1, -1 when absent (llama.cpp:2521-2525) */
+/* Text -> ids with the model's own vocabulary kind: SentencePiece-style merging by score (llama.cpp:5970-6110) or GPT-2
+ * byte-level BPE (pre-tokenizer :6249-6386, merging by rank :6117-6219); with `special`, occurrences of special tokens
+ * are cut out first and emitted as their ids (:6431-6524).  Returns the count, or -needed when n_max_tokens is too
+ * small (:10079-10093).  Where the reference throws out of its C API (text that is not UTF-8 for a BPE vocabulary, a
+ * byte without a token) this returns INT32_MIN and pib_last_error() says why.  Host only: works on a vocab_only model
+ * without a GPU. */
 int   llama_tokenize(const struct llama_model * model, const char * text, int text_len, llama_token * tokens,
-                     int n_max_tokens, bool add_bos, bool special);                       /* SPM, llama.cpp:5970-6110 */
-int   llama_token_to_piece(const struct llama_model * model, llama_token token, char * buf, int length);
+                     int n_max_tokens, bool add_bos, bool special);
+int   llama_token_to_piece(const struct llama_model * model, llama_token token, char * buf, int length);   /* llama.cpp:10111-10166 */
+/* class the BPE pre-tokenizer sees for a codepoint: 1 digit, 2 letter, 3 whitespace, 0 anything else (the reference's
+ * codepoint_type, unicode.h:351-403, folded to the three classes llama.cpp:6317-6353 asks about).  For the tests. */
+int   pib_tokenizer_codepoint_class(uint32_t cp);
 
 /* ---- batches (llama.cpp:9839-9898) ---- */
 struct llama_batch llama_batch_get_one(llama_token * tokens, int32_t n_tokens, llama_pos pos_0, llama_seq_id seq_id);
@@ -198,7 +207,7 @@ bool        llama_mlock_supported(void);
 int         llama_max_devices(void);
 
 /* ---- reporting (llama.h:323, 860-872; llama.cpp:10182-10240) ---- */
-int          llama_vocab_type(const struct llama_model * model);           /* 0 = SPM */
+int          llama_vocab_type(const struct llama_model * model);           /* 0 = SPM, 1 = BPE (llama.h:70-73) */
 void         llama_print_timings(struct llama_context * ctx);
 void         llama_reset_timings(struct llama_context * ctx);
 const char * llama_print_system_info(void);

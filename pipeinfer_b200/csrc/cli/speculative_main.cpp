@@ -118,8 +118,11 @@ int main(int argc, char ** argv) {
     llama_pib_set_priority(c_dft, 1);
     if (llama_n_vocab(m_tgt) != llama_n_vocab(m_dft)) { fprintf(stderr, "speculative: draft and target vocabularies differ\n"); return 1; }   // speculative.cpp:186-200
 
+    // BOS in front unless the file says otherwise; without a say, SPM vocabularies get one (common.cpp llama_should_add_bos_token)
+    auto wants_bos = [](const llama_model * m) { const int a = llama_add_bos_token(m); return a != -1 ? a != 0 : llama_vocab_type(m) == 0; };
+    if (wants_bos(m_tgt) != wants_bos(m_dft)) { fprintf(stderr, "speculative: draft and target disagree about a leading BOS token\n"); return 1; }   // speculative.cpp:181-192
     std::vector<llama_token> inp(prompt.size() + 8);
-    const int n_inp = llama_tokenize(m_tgt, prompt.c_str(), (int) prompt.size(), inp.data(), (int) inp.size(), true, true);
+    const int n_inp = llama_tokenize(m_tgt, prompt.c_str(), (int) prompt.size(), inp.data(), (int) inp.size(), wants_bos(m_tgt), true);
     if (n_inp < 2) { fprintf(stderr, "speculative: the prompt needs at least 2 tokens\n"); return 1; }
     inp.resize(n_inp);
     if (n_inp > n_ctx - 4) { fprintf(stderr, "speculative: the prompt exceeds the context size\n"); return 1; }   // :212-216

@@ -115,15 +115,30 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
     m->rms_eps        = (float) g.get_f(arch + ".attention.layer_norm_rms_epsilon", 1e-5);
     m->norm_eps       = (float) g.get_f(arch + ".attention.layer_norm_epsilon", 1e-5);
     m->rope_freq_base = (float) g.get_f(arch + ".rope.freq_base", 10000.0);
-    m->tok_bos = (int) g.get_i("tokenizer.ggml.bos_token_id", 1);
-    m->tok_eos = (int) g.get_i("tokenizer.ggml.eos_token_id", 2);
     if (g.kv.count("tokenizer.ggml.tokens")) m->tok_text = g.kv["tokenizer.ggml.tokens"].arr_s;
+    // vocabulary kind and its default special ids (llama.cpp:2413-2468); an id outside the vocabulary falls back to the
+    // default (:2505-2519)
+    m->tok_model = g.get_s("tokenizer.ggml.model", "llama");
+    const bool bpe = m->tok_model == "gpt2";
+    if (bpe) {
+        if (!g.kv.count("tokenizer.ggml.merges")) { pib_set_error("gguf: a gpt2 vocabulary without tokenizer.ggml.merges"); delete m; return nullptr; }
+        m->tok_merges = g.kv["tokenizer.ggml.merges"].arr_s;
+    }
+    auto special_id = [&](const char * key, int def) {
+        const int32_t id = (int32_t) g.get_i(key, def);                  // a u32 in the file, an int32 in the vocabulary
+        return !m->tok_text.empty() && (size_t) ((int64_t) id + 1) > m->tok_text.size() ? def : (int) id;
+    };
+    m->tok_bos = special_id("tokenizer.ggml.bos_token_id", bpe ? 11 : 1);
+    m->tok_eos = special_id("tokenizer.ggml.eos_token_id", bpe ? 11 : 2);
+    { auto it = g.kv.find("tokenizer.ggml.add_bos_token"); if (it != g.kv.end() && it->second.type == 7) m->tok_add_bos = (int) it->second.u; }
     if (g.kv.count("tokenizer.ggml.scores")) for (double f : g.kv["tokenizer.ggml.scores"].arr_f) m->tok_score.push_back((float) f);
     if (g.kv.count("tokenizer.ggml.token_type")) for (int64_t i : g.kv["tokenizer.ggml.token_type"].arr_i) m->tok_type.push_back((int32_t) i);
     const GgufTensor * emb = g.tensor("token_embd.weight");
-    if (!emb || m->n_layer <= 0 || m->n_embd <= 0 || m->n_head <= 0) { pib_set_error("gguf: missing hyper-parameters / token_embd"); delete m; return nullptr; }
-    m->n_vocab = (int) emb->ne[1];
-    m->wtype   = emb->type;
+    // a vocabulary-only load (nothing resident) also accepts a file without tensors, like the reference's vocab_only
+    const bool nothing_resident = !want_embd && !want_output && layer_begin == layer_end && layer_end >= 0;
+    if ((!emb && !nothing_resident) || m->n_layer <= 0 || m->n_embd <= 0 || m->n_head <= 0) { pib_set_error("gguf: missing hyper-parameters / token_embd"); delete m; return nullptr; }
+    m->n_vocab = emb ? (int) emb->ne[1] : (int) m->tok_text.size();
+    m->wtype   = emb ? emb->type : PIB_TYPE_Q8_0;
     if (m->wtype != PIB_TYPE_Q4_0 && m->wtype != PIB_TYPE_Q8_0 && m->wtype != PIB_TYPE_Q4_K) {
         pib_set_error("gguf: token_embd of type %d not supported (Q4_0, Q8_0, Q4_K; other matrices may also be Q6_K)", m->wtype);
         delete m;

@@ -37,7 +37,7 @@ struct pib_model {
     int   wtype = 0;
     int   arch = 0;                      // 0 llama (build_llama, llama.cpp:3872), 1 falcon (build_falcon, :4106)
     float norm_eps = 1e-5f;              // falcon: f_norm_eps
-    int   tok_bos = 1, tok_eos = 2, tok_nl = 13;
+    int   tok_bos = 1, tok_eos = 2;
     // tensors (only those of the layer range this process owns are resident)
     int          layer_begin = 0, layer_end = 0;
     pib_weight * tok_embd    = nullptr;
@@ -49,6 +49,9 @@ struct pib_model {
     std::vector<std::string> tok_text;
     std::vector<float>       tok_score;
     std::vector<int32_t>     tok_type;
+    std::string              tok_model = "llama";  // tokenizer.ggml.model: "llama" (SPM) or "gpt2" (byte-level BPE)
+    std::vector<std::string> tok_merges;           // BPE merges "left right", rank = position
+    int                      tok_add_bos = -1;     // tokenizer.ggml.add_bos_token: 0 / 1, -1 = not in the file
     std::string              name;
     size_t                   weight_bytes = 0;     // algorithmic bytes of all resident matrices
 

@@ -1,5 +1,6 @@
 // llama_api.cu -- the llama.h-compatible C ABI (include/pipeinfer_llama.h) on top of the engine.
 #include "engine.cuh"
+#include "tokenizer.cuh"
 #include "../../include/pipeinfer_llama.h"
 
 #include <string.h>
@@ -7,7 +8,7 @@
 
 #include <algorithm>
 #include <map>
-#include <queue>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -19,7 +20,8 @@ static int64_t now_us_api() {
 
 struct llama_model {
     pib_model * m = nullptr;
-    std::map<std::string, int32_t> tok_index;     // piece text -> id (built on first tokenize)
+    pib_vocab *    vocab = nullptr;               // built on first use (tokenize / piece / nl / vocab_type)
+    std::once_flag vocab_once;
 };
 
 struct llama_context {
@@ -108,6 +110,7 @@ struct llama_model * llama_pib_load_model_slice(const char * path_model, int lay
 
 void llama_free_model(struct llama_model * model) {
     if (!model) return;
+    pib_vocab_free(model->vocab);
     pib_model_free(model->m);
     delete model;
 }
@@ -160,7 +163,6 @@ int llama_pib_set_priority(struct llama_context * ctx, int high) {
 }
 
 // ---- the rest of the llama.h surface that speculative.cpp / main.cpp / common reference (llama.h:323, 472-500, 760-800, 860-872) ----
-int llama_vocab_type(const struct llama_model * model) { (void) model; return 0; }      // LLAMA_VOCAB_TYPE_SPM (llama.h:70-73)
 
 // llama.cpp:9263 / :9310: in the reference these differ from seq_cp only in the direction the op travels along the MPI
 // ring; every stage here receives every op from the head, so both are seq_cp (with the reference's src == dst shortcut)
@@ -257,64 +259,27 @@ int llama_n_ctx_train(const struct llama_model * model) { return model->m->n_ctx
 int llama_n_embd(const struct llama_model * model) { return model->m->n_embd; }
 llama_token llama_token_bos(const struct llama_model * model) { return model->m->tok_bos; }
 llama_token llama_token_eos(const struct llama_model * model) { return model->m->tok_eos; }
-llama_token llama_token_nl(const struct llama_model * model) { return model->m->tok_nl; }
-int llama_add_bos_token(const struct llama_model * model) { (void) model; return -1; }
 size_t llama_pib_weight_bytes(const struct llama_model * model) { return model->m->weight_bytes; }
 
-// ---- tokenizer: SentencePiece-style bigram merging (reference llm_tokenizer_spm, llama.cpp:5970-6110) ----------------
-static size_t utf8_len(unsigned char c) { return c < 0x80 ? 1 : (c >> 5) == 6 ? 2 : (c >> 4) == 14 ? 3 : (c >> 3) == 30 ? 4 : 1; }
+// ---- tokenizer (tokenizer.cu): SPM and byte-level BPE, special tokens cut out first when `special` ------------------
+static const pib_vocab * vocab_of(const llama_model * model) {
+    llama_model * lm = const_cast<llama_model *>(model);
+    std::call_once(lm->vocab_once, [lm] { lm->vocab = pib_vocab_build(lm->m); });
+    return lm->vocab;
+}
 
+int llama_vocab_type(const struct llama_model * model) { return pib_vocab_type(vocab_of(model)); }      // llama.h:70-73
+llama_token llama_token_nl(const struct llama_model * model) { return pib_vocab_linefeed(vocab_of(model)); }
+int llama_add_bos_token(const struct llama_model * model) { return model->m->tok_add_bos; }
+
+// returns the number of tokens, -needed when n_max_tokens is too small (llama.cpp:10079-10093); INT32_MIN when the text
+// cannot be tokenized at all (invalid UTF-8 for a BPE vocabulary, a byte without a token) -- the reference throws there
 int llama_tokenize(const struct llama_model * model, const char * text, int text_len, llama_token * tokens, int n_max_tokens,
                    bool add_bos, bool special) {
-    (void) special;
-    llama_model * lm = const_cast<llama_model *>(model);
-    const pib_model * m = lm->m;
-    if (lm->tok_index.empty()) for (size_t i = 0; i < m->tok_text.size(); i++) lm->tok_index.emplace(m->tok_text[i], (int32_t) i);
-    std::vector<llama_token> out;
-    if (add_bos) out.push_back(m->tok_bos);
-    std::string s = " " + std::string(text, (size_t) text_len);        // SPM space prefix, then ' ' -> U+2581
-    std::string esc;
-    for (char ch : s) { if (ch == ' ') esc += "\xe2\x96\x81"; else esc += ch; }
-    if (text_len > 0) {
-        struct sym { size_t off, n; int prev, next; };
-        std::vector<sym> syms;
-        for (size_t off = 0; off < esc.size();) {
-            size_t n = std::min(utf8_len((unsigned char) esc[off]), esc.size() - off);
-            syms.push_back({ off, n, (int) syms.size() - 1, off + n >= esc.size() ? -1 : (int) syms.size() + 1 });
-            off += n;
-        }
-        struct bigram { int left, right; float score; size_t size; };
-        auto cmp = [](const bigram & a, const bigram & b) { return a.score < b.score || (a.score == b.score && a.left > b.left); };
-        std::priority_queue<bigram, std::vector<bigram>, decltype(cmp)> q(cmp);
-        auto try_add = [&](int l, int r) {
-            if (l < 0 || r < 0) return;
-            const std::string piece = esc.substr(syms[l].off, syms[l].n + syms[r].n);
-            auto it = lm->tok_index.find(piece);
-            if (it == lm->tok_index.end()) return;
-            q.push({ l, r, (size_t) it->second < m->tok_score.size() ? m->tok_score[it->second] : 0.f, piece.size() });
-        };
-        for (int i = 1; i < (int) syms.size(); i++) try_add(i - 1, i);
-        while (!q.empty()) {
-            bigram b = q.top(); q.pop();
-            sym & L = syms[b.left]; sym & R = syms[b.right];
-            if (L.n == 0 || R.n == 0 || L.n + R.n != b.size) continue;
-            L.n += R.n; R.n = 0;
-            L.next = R.next;
-            if (R.next >= 0) syms[R.next].prev = b.left;
-            try_add(L.prev, b.left);
-            try_add(b.left, L.next);
-        }
-        for (int i = 0; i != -1; i = syms[i].next) {
-            const std::string piece = esc.substr(syms[i].off, syms[i].n);
-            auto it = lm->tok_index.find(piece);
-            if (it != lm->tok_index.end()) { out.push_back(it->second); continue; }
-            for (unsigned char ch : piece) {                                  // byte fallback <0xXX>
-                char buf[8];
-                snprintf(buf, sizeof(buf), "<0x%02X>", ch);
-                auto bt = lm->tok_index.find(buf);
-                out.push_back(bt != lm->tok_index.end() ? bt->second : 0);
-            }
-        }
+    std::vector<int32_t> out;
+    if (pib_vocab_tokenize(vocab_of(model), std::string(text, (size_t) (text_len > 0 ? text_len : 0)), add_bos, special, out) != 0) {
+        fprintf(stderr, "llama_tokenize: %s\n", pib_last_error());
+        return PIB_TOKENIZE_INVALID;
     }
     if ((int) out.size() > n_max_tokens) return -(int) out.size();
     for (size_t i = 0; i < out.size(); i++) tokens[i] = out[i];
@@ -322,21 +287,8 @@ int llama_tokenize(const struct llama_model * model, const char * text, int text
 }
 
 int llama_token_to_piece(const struct llama_model * model, llama_token token, char * buf, int length) {
-    const pib_model * m = model->m;
-    if (token < 0 || (size_t) token >= m->tok_text.size()) return 0;
-    const int ty = (size_t) token < m->tok_type.size() ? m->tok_type[token] : 1;
     std::string r;
-    if (ty == 1) {                       // normal: U+2581 -> ' '
-        const std::string & t = m->tok_text[token];
-        for (size_t i = 0; i < t.size();) {
-            if (i + 2 < t.size() && (unsigned char) t[i] == 0xE2 && (unsigned char) t[i + 1] == 0x96 && (unsigned char) t[i + 2] == 0x81) { r += ' '; i += 3; }
-            else r += t[i++];
-        }
-    } else if (ty == 6) {                // byte token <0xXX>
-        r = std::string(1, (char) strtol(m->tok_text[token].substr(3, 2).c_str(), nullptr, 16));
-    } else if (ty == 2) {
-        r = "\xe2\x96\x85";
-    }
+    if (!pib_vocab_piece(vocab_of(model), token, r)) return 0;
     if ((int) r.size() > length) return -(int) r.size();
     memcpy(buf, r.data(), r.size());
     return (int) r.size();

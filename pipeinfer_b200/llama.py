@@ -289,6 +289,8 @@ def tokenize(ctx, text, add_bos=True):
     buf = (C.c_int32 * (len(text) * 4 + 8))()
     raw = text.encode()
     n = L.llama_tokenize(ctx.model, raw, len(raw), buf, len(buf), add_bos, True)
+    if n < 0:
+        raise PibError("llama_tokenize: " + (L.pib_last_error().decode() if n == -2**31 else "needs %d tokens" % -n))
     return list(buf[:n])
 
 
