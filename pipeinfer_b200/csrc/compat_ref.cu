@@ -5,7 +5,7 @@
 //
 // Samplers are host code over llama_token_data_array exactly as in the reference; the ones on the path's greedy
 // configuration (softmax, greedy, repetition penalties) live in llama_api.cu.  Grammar sampling, LoRA, mirostat,
-// classifier-free guidance, tail-free and locally-typical sampling are outside the path: they are accepted when their
+// classifier-free guidance are outside the path: they are accepted when their
 // parameters are neutral (as the reference's own early returns do) and refused loudly otherwise.
 #include "engine.cuh"
 #include "../../include/pipeinfer_llama.h"
@@ -118,15 +118,48 @@ void llama_sample_min_p(struct llama_context * ctx, llama_token_data_array * can
     for (; i < candidates->size; ++i) if (candidates->data[i].p < p * scale && i >= min_keep) break;
     candidates->size = i;
 }
-void llama_sample_tail_free(struct llama_context * ctx, llama_token_data_array * candidates, float z, size_t min_keep) { // :7133
-    (void) ctx; (void) min_keep;
-    if (z >= 1.0f || candidates->size <= 2) return;        // the reference's own early return
-    not_on_path("llama_sample_tail_free with z < 1");
+// tail-free sampling: cut the candidates where the cumulated, normalised |second difference| of the sorted probabilities passes z
+void llama_sample_tail_free(struct llama_context * ctx, llama_token_data_array * candidates, float z, size_t min_keep) { // :7131
+    if (z >= 1.0f || candidates->size <= 2) return;
+    llama_sample_softmax(ctx, candidates);
+    const llama_token_data * c = candidates->data;
+    const size_t n2 = candidates->size - 2;
+    std::vector<float> curv(n2);
+    float total = 0.0f;                                    // summed left to right in fp32, like std::accumulate there
+    for (size_t i = 0; i < n2; ++i) {
+        const float d0 = c[i].p - c[i + 1].p, d1 = c[i + 1].p - c[i + 2].p;
+        curv[i] = std::fabs(d0 - d1);
+        total += curv[i];
+    }
+    for (float & v : curv) v = total > 1e-6f ? v / total : 1.0f / (float) n2;
+    float run = 0.0f;
+    for (size_t i = 0; i < n2; ++i) {
+        run += curv[i];
+        if (run > z && i >= min_keep) { candidates->size = i; return; }
+    }
 }
+// locally typical sampling: keep the candidates whose surprise is closest to the entropy until their mass passes p
 void llama_sample_typical(struct llama_context * ctx, llama_token_data_array * candidates, float p, size_t min_keep) {  // :7190
-    (void) ctx; (void) candidates; (void) min_keep;
-    if (p >= 1.0f) return;                                  // the reference's own early return
-    not_on_path("llama_sample_typical with p < 1");
+    if (p >= 1.0f) return;
+    llama_sample_softmax(ctx, candidates);
+    const size_t n = candidates->size;
+    float entropy = 0.0f;
+    for (size_t i = 0; i < n; ++i) entropy += -candidates->data[i].p * logf(candidates->data[i].p);
+    std::vector<float> dist(n);
+    for (size_t i = 0; i < n; ++i) dist[i] = fabsf(-logf(candidates->data[i].p) - entropy);
+    std::vector<size_t> order(n);
+    for (size_t i = 0; i < n; ++i) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](size_t a, size_t b) { return dist[a] < dist[b]; });
+    float  mass = 0.0f;
+    size_t keep = n;
+    for (size_t i = 0; i < n; ++i) {
+        mass += candidates->data[order[i]].p;
+        if (mass > p && i >= min_keep - 1) { keep = i + 1; break; }      // min_keep == 0 wraps and keeps everything, as there
+    }
+    std::vector<llama_token_data> kept(keep);
+    for (size_t i = 0; i < keep; ++i) kept[i] = candidates->data[order[i]];
+    std::copy(kept.begin(), kept.end(), candidates->data);
+    candidates->size = keep;
 }
 void llama_sample_temp(struct llama_context * ctx, llama_token_data_array * candidates, float temp) {                   // :7259
     (void) ctx;
