@@ -90,6 +90,9 @@ class Scheduler {
     struct Ev { int64_t t; const char * what; int a, b, c; };
     std::vector<Ev> trace;
     bool            tracing = getenv("PIB_TRACE") != nullptr;
+    // PIB_REFERENCE_HAZARDS=1 restores the two behaviours of the reference that can make the text differ from the greedy
+    // text (see check_for_cancel and speculation_loop); for A/B runs only
+    bool            reference_hazards = getenv("PIB_REFERENCE_HAZARDS") != nullptr && atoi(getenv("PIB_REFERENCE_HAZARDS")) != 0;
     int64_t         t_trace0 = 0;
     void ev(const char * what, int a = 0, int b = 0, int c = 0) { if (tracing) trace.push_back({ llama_time_us() - t_trace0, what, a, b, c }); }
     void dump_trace() {
@@ -135,7 +138,12 @@ void Scheduler::check_for_cancel() {
             }
         }
         if (run.n_past_max < n_past_tgt || !correct_prefix) {
-            if (run.speculative) ids.push_back(run.batch.batch_id);
+            // A run that is merely stale (everything it covers has been verified by other runs, its own draft tokens were
+            // right) is dropped from the bookkeeping but NOT stopped on the GPUs: a run chained behind it attends to its
+            // KV cells, and cells of a run that was stopped before it got through every stage hold garbage.  Only runs with
+            // a wrong prefix are stopped -- whatever is chained behind those has the same wrong prefix.  The reference
+            // stops both kinds (speculative.cpp:1344-1356); tests/test_scheduler_sim.py shows the text that costs.
+            if (run.speculative && (!correct_prefix || reference_hazards)) ids.push_back(run.batch.batch_id);
             run.canceled = true;
         }
     }
@@ -287,6 +295,11 @@ void Scheduler::speculation_loop() {
             }
         } while (!should_run && !free_offsets.empty());
         if (!should_run) break;
+        // A chained run seeds its partition from the partition of the run before it (start_spec_run).  If that run has been
+        // cancelled and retired meanwhile, the partition handed out here is that same one: the reference then clears it and
+        // copies it onto itself (speculative.cpp:891-905 with orig_offset == seq_offset), which leaves the new run without
+        // the positions from prefix - 1 on.  Stop speculating instead; the next verified run restarts the chain.
+        if (!first_run && current.seq_offset == orig_offset && !reference_hazards) break;
         auto it = std::find(free_offsets.begin(), free_offsets.end(), current.seq_offset);
         if (it != free_offsets.end()) free_offsets.erase(it);
         if (start_spec_run(n_past_tgt, n_past_dft, orig_offset, p_adjust)) break;

@@ -1,0 +1,88 @@
+"""CPU-only: the scheduler object that ships in libpipeinfer_b200.so (scheduler.o) driven by a virtual-clock model of the
+engine (tests/sched_sim).  The model predicts every row from the context the KV metadata lets that row see, poisons the
+cells of runs cancelled in flight and fails decodes when the real KV bookkeeping finds no slot -- so "the generated text
+is the greedy text" here means the scheduler's sequence partitions, commits, cancels and draft trees were right under
+that timing.  Timings, agreement and flags are drawn at random: the interleavings differ from case to case."""
+import random
+
+import pytest
+
+from tests.sched_sim import sim
+
+
+def check(r, n_predict):
+    assert r["error"] == "" or "no slot" in r["error"] or r["target"]["refused"] + r["draft"]["refused"] > 0, r["error"]
+    assert r["tokens"] == r["truth"], [i for i, (a, b) in enumerate(zip(r["tokens"], r["truth"])) if a != b][:4]
+    assert r["target"]["read_cancelled_rows"] == 0          # the scheduler never samples from a run it cancelled
+    if r["target"]["refused"] + r["draft"]["refused"] == 0:
+        assert r["n"] >= n_predict
+    # else: the KV cache filled up (cells of retired speculative runs stay allocated until their partition is used again,
+    # as in the reference); the scheduler stopped and what it produced until then is still the greedy text
+
+
+@pytest.mark.parametrize("mode", ["plain", "classic", "speculative"])
+def test_default_timing_8_stages(mode):
+    r = sim.run(sim.default_config(), mode=mode, max_spec_runs=9 if mode == "speculative" else 0)
+    check(r, 128)
+    if mode == "plain":
+        # 8 stages of 1.4 ms + hops: the model is calibrated on the measured plain decode (89 tok/s at 8 GPUs)
+        assert 80 < r["result"]["decode_tok_per_s"] < 100
+    else:
+        assert r["result"]["n_accept"] > 0 and r["result"]["decode_tok_per_s"] > 120
+
+
+@pytest.mark.parametrize("block", range(6))
+def test_random_timings_flags_and_agreement(block):
+    rnd = random.Random(1000 + block)
+    for trial in range(25):
+        cfg = sim.default_config(n_stages=rnd.choice([1, 2, 4, 8]), jitter=rnd.choice([0, 0.3, 0.8]), agree=rnd.choice([0.0, 0.3, 0.6, 0.8, 0.95, 1.0]),
+                                 p_top=0.6, p_second=rnd.choice([0.05, 0.3]), share_gpu0=rnd.choice([0, 1]), seed=block * 100 + trial,
+                                 draft_us=rnd.choice([100, 800, 3000]), stage_us=rnd.choice([200, 1350]), skip_us=rnd.choice([5, 150]))
+        kw = dict(mode=rnd.choice(["speculative", "speculative", "classic"]), n_draft=rnd.choice([2, 3, 5, 8]), n_parallel=rnd.choice([1, 2, 3]),
+                  p_accept=rnd.choice([0.1, 0.5]), p_split=rnd.choice([0.2, 0.9]), p_recovery=rnd.choice([0.0, 0.05]), p_decay=rnd.choice([0.0, 0.1]),
+                  max_spec_runs=rnd.choice([0, 4, 9]), n_predict=96, n_ctx=4096, prompt_seed=trial)
+        check(sim.run(cfg, **kw), 96)
+
+
+HAZARD_CASES = [
+    # a perfect draft whose runs get overtaken: stale runs stopped on the GPUs leave garbage KV behind for the run chained behind them
+    (dict(n_stages=4, jitter=0, agree=1.0, p_top=0.6, p_second=0.3, share_gpu0=1, seed=17, draft_us=800, stage_us=200, skip_us=5),
+     dict(n_draft=3, n_parallel=1, p_accept=0.1, p_split=0.2, p_recovery=0.05, p_decay=0.0, max_spec_runs=9, n_predict=96, n_ctx=4096, prompt_seed=17)),
+    # a poor, fast draft: a chained run is handed the partition of its cancelled predecessor and copies it onto itself
+    (dict(n_stages=8, jitter=0, agree=0.3, p_top=0.6, p_second=0.3, share_gpu0=1, seed=524, draft_us=100, stage_us=1350, skip_us=5),
+     dict(n_draft=2, n_parallel=1, p_accept=0.1, p_split=0.2, p_recovery=0.05, p_decay=0.1, max_spec_runs=0, n_predict=96, n_ctx=4096, prompt_seed=24)),
+]
+
+
+@pytest.mark.parametrize("case", range(len(HAZARD_CASES)))
+def test_the_two_reference_behaviours_that_corrupt_context_are_fixed(case, monkeypatch):
+    """Found with this simulator.  With PIB_REFERENCE_HAZARDS=1 the scheduler does what speculative.cpp does (stops stale
+    runs on the GPUs, :1344-1356; re-seeds a partition from itself, :891-905) and an accepted row has attended to garbage or
+    to a context with a hole: the text is not the greedy text.  The default avoids both."""
+    c, kw = HAZARD_CASES[case]
+    monkeypatch.setenv("PIB_REFERENCE_HAZARDS", "1")
+    r = sim.run(sim.default_config(**c), **kw)
+    assert r["tokens"] != r["truth"]
+    monkeypatch.delenv("PIB_REFERENCE_HAZARDS")
+    check(sim.run(sim.default_config(**c), **kw), 96)
+
+
+def test_tree_branches_are_exercised():
+    """a second candidate above p_split opens a branch (speculative.cpp:1009-1050); with a draft that is wrong half of the
+    time and whose runner-up is then right, accepted tokens must come from branches other than 0 as well"""
+    cfg = sim.default_config(agree=0.5, p_top=0.55, p_second=0.4, seed=3)
+    one = sim.run(cfg, n_parallel=1, p_split=0.3, n_draft=4, max_spec_runs=9, n_ctx=4096)
+    three = sim.run(cfg, n_parallel=3, p_split=0.3, n_draft=4, max_spec_runs=9, n_ctx=4096)
+    check(one, 128)
+    check(three, 128)
+    assert three["result"]["n_accept"] > one["result"]["n_accept"]
+
+
+def test_unbounded_speculation_exhausts_a_small_cache_like_the_reference():
+    """cells of cancelled runs stay allocated until their partition is used again (llama.cpp:5700-5714): with 1024 cells, a
+    poor draft and nothing bounding the runs in flight the cache fills; the scheduler then stops instead of spinning"""
+    cfg = sim.default_config(n_stages=1, jitter=0.3, agree=0.6, p_top=0.6, seed=53, draft_us=100, stage_us=1350)
+    r = sim.run(cfg, n_draft=5, n_parallel=2, p_decay=0.1, n_predict=400, n_ctx=512, prompt_seed=53)
+    assert r["tokens"] == r["truth"]                        # whatever was produced is right
+    if r["n"] < 400:
+        assert r["target"]["refused"] + r["draft"]["refused"] > 0
