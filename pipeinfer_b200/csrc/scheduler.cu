@@ -93,6 +93,19 @@ class Scheduler {
     // PIB_REFERENCE_HAZARDS=1 restores the two behaviours of the reference that can make the text differ from the greedy
     // text (see check_for_cancel and speculation_loop); for A/B runs only
     bool            reference_hazards = getenv("PIB_REFERENCE_HAZARDS") != nullptr && atoi(getenv("PIB_REFERENCE_HAZARDS")) != 0;
+    // PIB_SCHED_CHAIN=1 (experimental, off by default): keep the chain of speculative runs alive across a verification.  The
+    // reference restarts drafting from the last verified token after EVERY run it verifies (speculative.cpp:392-394), so when
+    // the draft was right the runs already in flight are drafted and verified a second time and later dropped as stale.  With
+    // this policy drafting resumes at the tip of the chain whenever the newest speculative run in flight is still consistent
+    // with what has been generated; a rejection restarts the chain as before.  The text is the greedy text either way.
+    bool            chain_policy = getenv("PIB_SCHED_CHAIN") != nullptr && atoi(getenv("PIB_SCHED_CHAIN")) != 0;
+    int             chain_start_tgt = 0, chain_start_dft = 0;      // n_past at which the current chain began: prefix of all its links
+    llama_token_data tip_top8[8];                                   // the draft's candidates after the tip of branch 0
+    bool            have_tip = false;
+    struct Tip { std::vector<Draft> drafts; int spec_past_tgt = 0, spec_past_dft = 0, seq_offset = 0; llama_token id = 0; bool first_run = true; } tip;
+    int             n_chain_resumed = 0;
+    void save_tip() { tip.drafts = drafts; tip.spec_past_tgt = spec_past_tgt; tip.spec_past_dft = spec_past_dft; tip.seq_offset = current.seq_offset; tip.id = id; tip.first_run = first_run; }
+    bool resume_chain(int verified_offset, bool verified_spec);
     int64_t         t_trace0 = 0;
     void ev(const char * what, int a = 0, int b = 0, int c = 0) { if (tracing) trace.push_back({ llama_time_us() - t_trace0, what, a, b, c }); }
     void dump_trace() {
@@ -215,7 +228,8 @@ bool Scheduler::start_spec_run(int prefix_n_past, int n_past_dft_arg, int orig_o
         for (int s = 0; s <= max_ran_seq; ++s) {
             if (!drafts[s].drafting || drafts[s].skip) continue;
             llama_token_data cur_p[8];
-            llama_pib_get_top8(ctx_dft, drafts[s].i_batch_dft, cur_p);                                   // :975-983
+            if (chain_policy && !first_run && have_tip && i == 0 && s == 0) memcpy(cur_p, tip_top8, sizeof(cur_p));
+            else llama_pib_get_top8(ctx_dft, drafts[s].i_batch_dft, cur_p);                              // :975-983
             if (cur_p[0].p < P.p_accept + p_adjust) { drafts[s].drafting = false; continue; }           // :998-1003
             std::vector<int> sa(1, s);
             for (int f = 1; f < 8; ++f) {                                                                // :1009-1050 branch split
@@ -271,7 +285,26 @@ bool Scheduler::start_spec_run(int prefix_n_past, int n_past_dft_arg, int orig_o
     spec_past_dft += (int) drafts[0].tokens.size();
     id = drafts[0].tokens.back();
     first_run = false;
+    if (chain_policy) have_tip = llama_pib_get_top8(ctx_dft, drafts[0].i_batch_dft, tip_top8) == 0;   // what the next link starts from
     return false;
+}
+
+// after a verification: is the newest speculative run in flight still consistent with the text (check_for_cancel has just
+// run) and does it reach beyond what is verified?  Then go on drafting from its end instead of from the verified token.
+bool Scheduler::resume_chain(int verified_offset, bool verified_spec) {
+    if (!chain_policy || tip.first_run || !have_tip) return false;
+    const Run * newest = nullptr;
+    for (const Run & r : tgt_runs) if (r.speculative) { newest = &r; break; }      // front() is the newest
+    if (!newest || newest->canceled || newest->seq_offset != tip.seq_offset || newest->n_past_max <= n_past_tgt) return false;
+    if (verified_spec) free_offsets.push_back(verified_offset);                   // its partition is not reused by a restart
+    drafts = tip.drafts;
+    spec_past_tgt = tip.spec_past_tgt; spec_past_dft = tip.spec_past_dft;
+    id = tip.id;
+    current.seq_offset = tip.seq_offset;
+    first_run = false;
+    n_chain_resumed++;
+    ev("resume_chain", spec_past_tgt, n_past_tgt);
+    return true;
 }
 
 // :765-844
@@ -302,7 +335,8 @@ void Scheduler::speculation_loop() {
         if (!first_run && current.seq_offset == orig_offset && !reference_hazards) break;
         auto it = std::find(free_offsets.begin(), free_offsets.end(), current.seq_offset);
         if (it != free_offsets.end()) free_offsets.erase(it);
-        if (start_spec_run(n_past_tgt, n_past_dft, orig_offset, p_adjust)) break;
+        if (first_run || !chain_policy) { chain_start_tgt = n_past_tgt; chain_start_dft = n_past_dft; }
+        if (start_spec_run(chain_start_tgt, chain_start_dft, orig_offset, p_adjust)) break;
         is_waiting = llama_mpi_iprobe(ctx_tgt);
         first_run  = false;
         iter++;
@@ -354,6 +388,7 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
                 tgt_runs.pop_back();
                 continue;
             }
+            if (chain_policy) save_tip();
             drafts = run.drafts;
             current.speculative = run.speculative; current.n_past_max = run.n_past_max; current.n_past_tgt = run.n_past_tgt;
             current.n_past_dft = run.n_past_dft; current.seq_offset = run.seq_offset;
@@ -407,6 +442,7 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
         }
         if (!any_match) {                                                                                // :569-577
             ev("no_new_token", current.n_past_tgt, i_dft);
+            if (resume_chain(current.seq_offset, current.speculative)) continue;
             if (current.speculative) free_offsets.push_back(current.seq_offset);
             continue;
         }
@@ -443,6 +479,11 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
             dft_runs.pop_back();
         }
         spec_past_tgt = n_past_tgt; spec_past_dft = n_past_dft;
+        if (resume_chain(current.seq_offset, current.speculative)) {
+            speculation_loop();
+            if (n_predict > P.n_predict || has_eos || failed) break;
+            continue;
+        }
         if (!current.speculative) {                                                                      // :653-662
             if (free_offsets.empty()) continue;
             current.seq_offset = free_offsets.front();

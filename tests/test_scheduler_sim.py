@@ -31,9 +31,12 @@ def test_default_timing_8_stages(mode):
         assert r["result"]["n_accept"] > 0 and r["result"]["decode_tok_per_s"] > 120
 
 
+@pytest.mark.parametrize("chain", [0, 1])
 @pytest.mark.parametrize("block", range(6))
-def test_random_timings_flags_and_agreement(block):
-    rnd = random.Random(1000 + block)
+def test_random_timings_flags_and_agreement(block, chain, monkeypatch):
+    # chain = 1: the experimental policy that resumes drafting at the tip of the chain after a verification (PIB_SCHED_CHAIN)
+    monkeypatch.setenv("PIB_SCHED_CHAIN", str(chain))
+    rnd = random.Random(1000 + block + 50 * chain)
     for trial in range(25):
         cfg = sim.default_config(n_stages=rnd.choice([1, 2, 4, 8]), jitter=rnd.choice([0, 0.3, 0.8]), agree=rnd.choice([0.0, 0.3, 0.6, 0.8, 0.95, 1.0]),
                                  p_top=0.6, p_second=rnd.choice([0.05, 0.3]), share_gpu0=rnd.choice([0, 1]), seed=block * 100 + trial,
@@ -60,6 +63,7 @@ def test_the_two_reference_behaviours_that_corrupt_context_are_fixed(case, monke
     runs on the GPUs, :1344-1356; re-seeds a partition from itself, :891-905) and an accepted row has attended to garbage or
     to a context with a hole: the text is not the greedy text.  The default avoids both."""
     c, kw = HAZARD_CASES[case]
+    c = dict(c, hop_us=20, ret_us=30, stage_tok_us=50, draft_tok_us=50, enqueue_us=60, call_us=0.3)     # pins the interleaving
     monkeypatch.setenv("PIB_REFERENCE_HAZARDS", "1")
     r = sim.run(sim.default_config(**c), **kw)
     assert r["tokens"] != r["truth"]
@@ -86,3 +90,17 @@ def test_unbounded_speculation_exhausts_a_small_cache_like_the_reference():
     assert r["tokens"] == r["truth"]                        # whatever was produced is right
     if r["n"] < 400:
         assert r["target"]["refused"] + r["draft"]["refused"] > 0
+
+
+def test_chain_policy_resumes_and_pays_with_a_good_draft(monkeypatch):
+    """with a draft that is right 95 % of the time the reference's restart-after-every-verification re-drafts what is already
+    in flight; resuming at the tip of the chain must be clearly faster in the model, with the same text"""
+    cfg = sim.default_config(agree=0.95, seed=2)
+    kw = dict(n_draft=3, max_spec_runs=9, n_prompt=64, n_predict=192, n_ctx=2048)
+    monkeypatch.setenv("PIB_SCHED_CHAIN", "0")
+    ref = sim.run(cfg, **kw)
+    monkeypatch.setenv("PIB_SCHED_CHAIN", "1")
+    chained = sim.run(cfg, **kw)
+    check(ref, 192)
+    check(chained, 192)
+    assert chained["result"]["decode_tok_per_s"] > 1.08 * ref["result"]["decode_tok_per_s"]
