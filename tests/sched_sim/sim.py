@@ -82,13 +82,17 @@ def default_config(**kw):
 
 
 def run(cfg, mode="speculative", n_prompt=24, n_predict=128, n_ctx=1024, n_draft=3, n_parallel=3, p_accept=0.1, p_split=0.9,
-        p_recovery=0.0, p_decay=0.0, max_spec_runs=0, prompt_seed=5):
+        p_recovery=0.0, p_decay=0.0, max_spec_runs=0, prompt_seed=5, prompt=None):
     L = lib()
     L.sim_configure(C.byref(cfg))
     max_seq = 1000 * max(1, n_parallel) + 2 if mode == "speculative" else max(1, n_parallel) + 2
     tgt = L.sim_new_context(n_ctx, max_seq, 1)
     dft = L.sim_new_context(n_ctx, max_seq, 0)
-    prompt = (C.c_int32 * n_prompt)(*([1] + [3 + (i * 7919 + prompt_seed * 104729) % 30000 for i in range(n_prompt - 1)]))
+    if prompt is not None:
+        n_prompt = len(prompt)
+    else:
+        prompt = [1] + [3 + (i * 7919 + prompt_seed * 104729) % 30000 for i in range(n_prompt - 1)]
+    prompt = (C.c_int32 * n_prompt)(*prompt)
     cap = n_predict + 64
     out = (C.c_int32 * cap)()
     res = SpecResult()
@@ -124,3 +128,41 @@ if __name__ == "__main__":
     r["ok"] = r["tokens"] == r["truth"]
     del r["tokens"], r["truth"]
     print(json.dumps(r, indent=1))
+
+
+# ---- the reference's own scheduler on the same model (oracle/_ref/speculative_sim, built by oracle/Makefile) ----------------
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "speculative_sim")
+
+
+def run_reference(cfg_fields, text, n_predict=128, n_ctx=1024, n_draft=3, n_parallel=3, p_accept=0.1, p_split=0.9, p_recovery=0.0,
+                  p_decay=0.0, trace=None, workdir="/tmp"):
+    """plays examples/speculative/speculative.cpp (unmodified) against the simulator; returns tokens, counters, tok/s"""
+    import json
+    import tempfile
+    d = tempfile.mkdtemp(dir=workdir)
+    env = dict(os.environ, SIM_CFG=",".join("%s=%s" % kv for kv in cfg_fields.items()), SIM_OUT=os.path.join(d, "out.json"))
+    if trace:
+        env["SIM_TRACE"] = trace
+    args = [REF_BIN, "-m", "sim:target", "-md", "sim:draft", "-p", text, "-n", str(n_predict), "-c", str(n_ctx), "--draft", str(n_draft),
+            "-np", str(n_parallel), "-pa", str(p_accept), "-ps", str(p_split), "-pr", str(p_recovery), "-pd", str(p_decay), "--temp", "-1",
+            "--repeat-last-n", "0", "--ignore-eos"]
+    p = subprocess.run(args, cwd=d, env=env, capture_output=True, text=True, timeout=int(os.environ.get("SIM_REF_TIMEOUT", "120")))
+    if p.returncode != 0:
+        raise RuntimeError("speculative_sim failed: %s" % p.stderr[-2000:])
+    toks = [int(x) for x in p.stdout.split()]
+    stats = json.load(open(os.path.join(d, "out.json")))
+    row = open(os.path.join(d, "results.csv")).read().strip().splitlines()[-1].split(",")
+    return {"tokens": toks, "stats": stats, "decode_tok_per_s": float(row[1])}
+
+
+def text_prompt(text):
+    return [1] + [3 + b for b in text.encode()]
+
+
+def truth_of(cfg, prompt, n):
+    L = lib()
+    L.sim_configure(C.byref(cfg))
+    P = (C.c_int32 * len(prompt))(*prompt)
+    T = (C.c_int32 * n)()
+    L.sim_truth(P, len(prompt), T, n)
+    return list(T)

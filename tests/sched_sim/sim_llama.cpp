@@ -63,6 +63,14 @@ static uint64_t g_rng = 88172645463325252ull;
 static std::vector<std::pair<double, double>> g_draft_busy;      // GPU-0 intervals taken by the draft
 static long g_bad_context = 0, g_read_cancelled = 0;
 
+// optional log of what the scheduler asked of the TARGET context (env SIM_TRACE=<file>): issue order, batch contents, finishes
+// and cancels -- the logical schedule, comparable between two schedulers driven with the same clock
+static FILE * g_trace = nullptr;
+static void trace_open() {
+    if (g_trace) { fclose(g_trace); g_trace = nullptr; }
+    if (getenv("SIM_TRACE")) g_trace = fopen(getenv("SIM_TRACE"), "w");
+}
+
 static uint64_t mix(uint64_t x) { x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33; return x; }
 static double noise() {
     if (G.jitter <= 0) return 1.0;
@@ -85,7 +93,7 @@ struct sim_run {
     std::vector<double>  dur;       // per stage, drawn at issue time
 };
 
-struct llama_model { int dummy; };
+struct llama_model { bool is_target = false; };
 struct llama_context {
     llama_model           model;
     bool                  is_target = false;
@@ -203,6 +211,15 @@ static bool issue(llama_context * c, const llama_batch & b, sim_run & run) {
     kvlog_decode_end(c->kv, b.n_tokens);
     c->devops.clear();
     run.batch_id = b.batch_id; run.n_tokens = b.n_tokens;
+    if (g_trace && c->is_target) {
+        fprintf(g_trace, "D %d %d", b.batch_id, b.n_tokens);
+        for (int i = 0; i < b.n_tokens; i++) {
+            uint64_t hs = 0;
+            for (int j = 0; j < b.n_seq_id[i]; j++) hs = mix(hs ^ (uint64_t) (b.seq_id[i][j] + 1));
+            fprintf(g_trace, " %d@%d/%d:%d:%04x", b.token[i], b.pos[i], b.n_seq_id[i], b.seq_id[i][0], (unsigned) (hs & 0xffff));
+        }
+        fprintf(g_trace, " # t=%.0f cell=%u\n", g_now, run.cell0);
+    }
     return true;
 }
 
@@ -244,6 +261,7 @@ int llama_finish_async_decode(struct llama_context & c, struct llama_batch b, st
     sim_run & r = c.flight.front();                             // runs finish in issue order
     if (r.batch_id != b.batch_id) { pib_set_error("sim: finish of batch %d but the oldest run is %d", b.batch_id, r.batch_id); return -1; }
     g_now = std::max(g_now, r.t_done) + G.call_us;
+    if (g_trace && c.is_target) fprintf(g_trace, "F %d%s # t=%.0f\n", r.batch_id, r.t_cancel >= 0 ? " cancelled" : "", g_now);
     c.rows = std::move(r.rows);
     if (r.t_cancel >= 0) for (sim_row & row : c.rows) row.valid = false;
     if (r.skipped) c.skipped.push_back(r.ticket);
@@ -266,7 +284,7 @@ int llama_decode(struct llama_context * ctx, struct llama_batch b) {
 }
 
 bool llama_mpi_iprobe(struct llama_context * c) {
-    g_now += G.call_us;
+    g_now += std::max(G.call_us, 0.2);        // polling takes time even when the other calls are modelled as free: a scheduler that spins on it must see the clock move
     if (c->flight.empty()) return false;
     if (c->is_target) resolve(c, false);
     return c->flight.front().t_done <= g_now;
@@ -275,6 +293,7 @@ bool llama_mpi_iprobe(struct llama_context * c) {
 void llama_cancel_run(struct llama_context * c, int32_t * ids, int count) {
     g_now += G.call_us;
     if (c->is_target) resolve(c, false);
+    if (g_trace && c->is_target) { fprintf(g_trace, "C"); for (int i = 0; i < count; i++) fprintf(g_trace, " %d", ids[i]); fprintf(g_trace, " # t=%.0f\n", g_now); }
     for (sim_run & r : c->flight)
         for (int i = 0; i < count; i++)
             if (r.batch_id == ids[i] && r.t_cancel < 0) {
@@ -298,7 +317,7 @@ int llama_pib_get_top8(struct llama_context * c, int32_t i, llama_token_data * o
 }
 
 // ---- the harness's own entry points ------------------------------------------------------------------------------------------
-void sim_configure(const sim_config * cfg) { G = *cfg; g_now = 0; g_rng = 88172645463325252ull ^ mix(cfg->seed); g_draft_busy.clear(); g_bad_context = 0; g_read_cancelled = 0; }
+void sim_configure(const sim_config * cfg) { trace_open(); G = *cfg; g_now = 0; g_rng = 88172645463325252ull ^ mix(cfg->seed); g_draft_busy.clear(); g_bad_context = 0; g_read_cancelled = 0; }
 void sim_default_config(sim_config * cfg) { *cfg = DEFAULTS; }
 double sim_now_us(void) { return g_now; }
 
@@ -316,6 +335,7 @@ void sim_free_context(struct llama_context * c) { delete c; }
 // counters: decodes issued, decodes refused (no KV slot), runs cancelled, rows predicted from a broken context, rows of a
 // cancelled run that the scheduler read, cells in use
 void sim_stats(const struct llama_context * c, int64_t * out6) {
+    if (g_trace) fflush(g_trace);
     out6[0] = c->n_decodes; out6[1] = c->n_failed; out6[2] = c->n_cancelled_runs; out6[3] = g_bad_context; out6[4] = g_read_cancelled; out6[5] = c->kv.used;
 }
 

@@ -104,3 +104,72 @@ def test_chain_policy_resumes_and_pays_with_a_good_draft(monkeypatch):
     check(ref, 192)
     check(chained, 192)
     assert chained["result"]["decode_tok_per_s"] > 1.08 * ref["result"]["decode_tok_per_s"]
+
+
+# ---- differential: the reference's own scheduler (speculative.cpp, unmodified) on the same model --------------------------
+import os
+
+needs_ref = pytest.mark.skipif(not os.path.exists(sim.REF_BIN), reason="oracle/_ref/speculative_sim is built only where /root/reference exists")
+
+DIFF_CASES = [
+    # (model fields, flags)
+    (dict(n_stages=8, seed=1), dict(n_draft=3, n_parallel=3, p_accept=0.1, p_split=0.9)),                       # the benchmark's flags
+    (dict(n_stages=4, seed=2, agree=0.6, p_top=0.6, p_second=0.3), dict(n_draft=5, n_parallel=3, p_accept=0.1, p_split=0.2)),   # tree branches
+    (dict(n_stages=1, seed=3, agree=0.95), dict(n_draft=8, n_parallel=2, p_accept=0.5, p_split=0.2, p_recovery=0.05, p_decay=0.1)),
+    (dict(n_stages=2, seed=4, agree=0.3, jitter=0.3), dict(n_draft=2, n_parallel=1, p_accept=0.1, p_split=0.9, p_recovery=0.05)),
+    (dict(n_stages=8, seed=5, agree=1.0, draft_us=300, stage_us=400), dict(n_draft=3, n_parallel=1, p_accept=0.1, p_split=0.9)),
+    (dict(n_stages=8, seed=6, agree=0.8, p_top=0.5, p_second=0.45, jitter=0.8), dict(n_draft=4, n_parallel=3, p_accept=0.3, p_split=0.4, p_decay=0.05)),
+]
+
+
+@needs_ref
+@pytest.mark.parametrize("case", range(len(DIFF_CASES)))
+def test_schedule_is_the_reference_schedule(case, monkeypatch, tmp_path):
+    """Same clock, same model, same flags: every target decode (batch id, tokens, positions, sequence sets, KV cell), every
+    finish and every cancel this scheduler issues is the one examples/speculative/speculative.cpp issues, at the same virtual
+    time -- rows S1-S6 of SURVEY.md §8a.  (PIB_REFERENCE_HAZARDS=1: the two deliberate deviations are switched off.)"""
+    fields, flags = DIFF_CASES[case]
+    fields = dict(fields, n_vocab=4096, call_us=0)
+    text = "".join(chr(33 + (i * (7 + case)) % 90) for i in range(47))
+    ref_trace, my_trace = str(tmp_path / "ref.txt"), str(tmp_path / "mine.txt")
+    ref = sim.run_reference(fields, text, n_predict=96, n_ctx=4096, trace=ref_trace, workdir=str(tmp_path), **flags)
+    monkeypatch.setenv("PIB_REFERENCE_HAZARDS", "1")
+    monkeypatch.setenv("SIM_TRACE", my_trace)
+    mine = sim.run(sim.default_config(**fields), prompt=sim.text_prompt(text), n_predict=96, n_ctx=4096, **flags)
+    assert ref["stats"]["target"]["refused"] == 0 and mine["target"]["refused"] == 0
+    a, b = open(ref_trace).read().splitlines(), open(my_trace).read().splitlines()
+    assert len(a) > 100
+    for i, (x, y) in enumerate(zip(a, b)):
+        assert x == y, "event %d differs:\n reference: %s\n here:      %s" % (i, x[:300], y[:300])
+    assert len(a) == len(b)
+    assert mine["tokens"][:len(ref["tokens"])] == ref["tokens"] and len(ref["tokens"]) >= 96
+    assert abs(mine["result"]["decode_tok_per_s"] - ref["decode_tok_per_s"]) < 1e-2 * ref["decode_tok_per_s"]
+    assert mine["target"]["cancelled_runs"] == ref["stats"]["target"]["cancelled_runs"]
+    assert mine["draft"]["decodes"] == ref["stats"]["draft"]["decodes"]
+
+
+REF_HAZARD_CASES = [
+    ({'n_stages': 4, 'agree': 0.95, 'p_top': 0.6, 'p_second': 0.05, 'seed': 183, 'draft_us': 100, 'stage_us': 1350, 'skip_us': 5, 'call_us': 0, 'enqueue_us': 60,
+      'draft_tok_us': 50, 'jitter': 0, 'n_vocab': 4096},
+     {'n_draft': 2, 'n_parallel': 1, 'p_accept': 0.5, 'p_split': 0.9, 'p_recovery': 0.05, 'p_decay': 0.1}, '!+5?IS]gq!+5?IS]gq!+5?IS]gq!+5?IS]gq!+5?'),
+    ({'n_stages': 1, 'agree': 1.0, 'p_top': 0.6, 'p_second': 0.3, 'seed': 266, 'draft_us': 100, 'stage_us': 1350, 'skip_us': 5, 'call_us': 0, 'enqueue_us': 60,
+      'draft_tok_us': 0, 'jitter': 0, 'n_vocab': 4096},
+     {'n_draft': 3, 'n_parallel': 2, 'p_accept': 0.1, 'p_split': 0.2, 'p_recovery': 0.05, 'p_decay': 0.1}, "!$'*-0369<?BEHKNQTWZ]`cfilorux!$'*-0369<"),
+]
+
+
+@needs_ref
+@pytest.mark.parametrize("case", range(len(REF_HAZARD_CASES)))
+def test_the_reference_scheduler_itself_leaves_the_greedy_text(case, monkeypatch, tmp_path):
+    """The two context-corrupting behaviours are the reference's, not artefacts of the restatement: speculative.cpp itself,
+    on this model, accepts a row that attended to garbage / a hole and prints a text that is not the greedy text; this
+    scheduler with PIB_REFERENCE_HAZARDS=1 prints the same wrong text, and by default the greedy one."""
+    fields, flags, text = REF_HAZARD_CASES[case]
+    ref = sim.run_reference(fields, text, n_predict=96, n_ctx=2048, workdir=str(tmp_path), **flags)
+    truth = sim.truth_of(sim.default_config(**fields), sim.text_prompt(text), len(ref["tokens"]))
+    assert ref["tokens"] != truth
+    monkeypatch.setenv("PIB_REFERENCE_HAZARDS", "1")
+    same = sim.run(sim.default_config(**fields), prompt=sim.text_prompt(text), n_predict=96, n_ctx=2048, **flags)
+    assert same["tokens"][:len(ref["tokens"])] == ref["tokens"]
+    monkeypatch.setenv("PIB_REFERENCE_HAZARDS", "0")
+    check(sim.run(sim.default_config(**fields), prompt=sim.text_prompt(text), n_predict=96, n_ctx=2048, **flags), 96)
