@@ -132,10 +132,11 @@ if __name__ == "__main__":
 
 # ---- the reference's own scheduler on the same model (oracle/_ref/speculative_sim, built by oracle/Makefile) ----------------
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "speculative_sim")
+REF_BIN_CLASSIC = os.path.join(ROOT, "oracle", "_ref", "speculative_orig_sim")     # examples/speculative_orig
 
 
 def run_reference(cfg_fields, text, n_predict=128, n_ctx=1024, n_draft=3, n_parallel=3, p_accept=0.1, p_split=0.9, p_recovery=0.0,
-                  p_decay=0.0, trace=None, workdir="/tmp"):
+                  p_decay=0.0, trace=None, workdir="/tmp", classic=False):
     """plays examples/speculative/speculative.cpp (unmodified) against the simulator; returns tokens, counters, tok/s"""
     import json
     import tempfile
@@ -143,13 +144,13 @@ def run_reference(cfg_fields, text, n_predict=128, n_ctx=1024, n_draft=3, n_para
     env = dict(os.environ, SIM_CFG=",".join("%s=%s" % kv for kv in cfg_fields.items()), SIM_OUT=os.path.join(d, "out.json"))
     if trace:
         env["SIM_TRACE"] = trace
-    args = [REF_BIN, "-m", "sim:target", "-md", "sim:draft", "-p", text, "-n", str(n_predict), "-c", str(n_ctx), "--draft", str(n_draft),
+    args = [REF_BIN_CLASSIC if classic else REF_BIN, "-m", "sim:target", "-md", "sim:draft", "-p", text, "-n", str(n_predict), "-c", str(n_ctx), "--draft", str(n_draft),
             "-np", str(n_parallel), "-pa", str(p_accept), "-ps", str(p_split), "-pr", str(p_recovery), "-pd", str(p_decay), "--temp", "-1",
-            "--repeat-last-n", "0", "--ignore-eos"]
+            "--repeat-last-n", "0", "--ignore-eos", "--mpi-layer-split", "1.0/1.0"]
     p = subprocess.run(args, cwd=d, env=env, capture_output=True, text=True, timeout=int(os.environ.get("SIM_REF_TIMEOUT", "120")))
     if p.returncode != 0:
         raise RuntimeError("speculative_sim failed: %s" % p.stderr[-2000:])
-    toks = [int(x) for x in p.stdout.split()]
+    toks = [int(x) for line in p.stdout.splitlines() if not line.startswith("Size of") for x in line.split()]
     stats = json.load(open(os.path.join(d, "out.json")))
     row = open(os.path.join(d, "results.csv")).read().strip().splitlines()[-1].split(",")
     return {"tokens": toks, "stats": stats, "decode_tok_per_s": float(row[1])}

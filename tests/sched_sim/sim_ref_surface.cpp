@@ -150,6 +150,15 @@ struct llama_kv_cache_view llama_kv_cache_view_init(const struct llama_context *
     return v;
 }
 
+// examples/speculative_orig times itself in "cycles"
+int64_t ggml_cycles(void) { return (int64_t) g_now; }
+int64_t ggml_cycles_per_ms(void) { return 1000; }
+void llama_batch_free(struct llama_batch & b) {
+    free(b.token); free(b.pos); free(b.n_seq_id);
+    if (b.seq_id) { for (int i = 0; i < b.n_tokens; ++i) free(b.seq_id[i]); free(b.seq_id); }
+    free(b.logits);
+}
+
 // one process, no communicators
 int  llama_node_id(struct llama_context *) { return 0; }
 void llama_split_comm(struct llama_context *, int) {}

@@ -173,3 +173,32 @@ def test_the_reference_scheduler_itself_leaves_the_greedy_text(case, monkeypatch
     assert same["tokens"][:len(ref["tokens"])] == ref["tokens"]
     monkeypatch.setenv("PIB_REFERENCE_HAZARDS", "0")
     check(sim.run(sim.default_config(**fields), prompt=sim.text_prompt(text), n_predict=96, n_ctx=2048, **flags), 96)
+
+
+CLASSIC_CASES = [
+    (dict(seed=1), dict(n_draft=3, n_parallel=1, p_split=0.9)),
+    (dict(seed=2, agree=0.6, p_top=0.5, p_second=0.4, n_stages=2), dict(n_draft=5, n_parallel=3, p_split=0.2)),      # tree drafting
+    (dict(seed=3, agree=0.95), dict(n_draft=8, n_parallel=2, p_split=0.3)),
+    (dict(seed=4, agree=0.0, n_stages=1), dict(n_draft=4, n_parallel=2, p_split=0.04)),                              # nothing is ever accepted
+]
+
+
+@pytest.mark.skipif(not os.path.exists(sim.REF_BIN_CLASSIC), reason="oracle/_ref/speculative_orig_sim is built only where /root/reference exists")
+@pytest.mark.parametrize("case", range(len(CLASSIC_CASES)))
+def test_classic_speculation_is_the_reference_schedule(case, monkeypatch, tmp_path):
+    """pib_speculative_orig_generate against examples/speculative_orig/speculative.cpp (unmodified) on the same model: same
+    target batches in the same order at the same virtual time, same text, same tokens/s"""
+    fields, flags = CLASSIC_CASES[case]
+    fields = dict(fields, n_vocab=4096, call_us=0)
+    text = "".join(chr(33 + (i * (11 + case)) % 90) for i in range(47))
+    ref_trace, my_trace = str(tmp_path / "ref.txt"), str(tmp_path / "mine.txt")
+    ref = sim.run_reference(fields, text, n_predict=96, trace=ref_trace, workdir=str(tmp_path), classic=True, **flags)
+    monkeypatch.setenv("SIM_TRACE", my_trace)
+    mine = sim.run(sim.default_config(**fields), mode="classic", prompt=sim.text_prompt(text), n_predict=96, **flags)
+    a, b = open(ref_trace).read().splitlines(), open(my_trace).read().splitlines()
+    for i, (x, y) in enumerate(zip(a, b)):
+        assert x == y, "event %d differs:\n reference: %s\n here:      %s" % (i, x[:300], y[:300])
+    assert len(a) == len(b) and len(a) > 20
+    assert mine["tokens"][:len(ref["tokens"])] == ref["tokens"] == mine["truth"][:len(ref["tokens"])]
+    assert abs(mine["result"]["decode_tok_per_s"] - ref["decode_tok_per_s"]) < 1e-2 * ref["decode_tok_per_s"]
+    assert mine["draft"]["decodes"] == ref["stats"]["draft"]["decodes"]
