@@ -1,0 +1,59 @@
+#!/usr/bin/env python
+"""TEST INFRASTRUCTURE: the what-if runs behind DESIGN.md §9 (scheduler simulator).
+
+  python tests/sched_sim/explore.py calibrate    model against the measured 8-GPU numbers in profiles/
+  python tests/sched_sim/explore.py sensitivity  tokens/s in the model when the draft step / the stage time / the agreement change,
+                                                 under the reference policy and under PIB_SCHED_CHAIN=1
+  python tests/sched_sim/explore.py scaling      1, 2, 4, 8 stages
+
+Every run also checks that the text is the greedy text.  Numbers are means over 6 prompts / model seeds.
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.abspath(os.path.join(os.path.dirname(__file__), "..", "..")))
+from tests.sched_sim import sim  # noqa: E402
+
+MEASURED_8 = {"d3": 206.4, "d2": 203.7, "d5": 184.2, "d8": 163.4, "d3np1": 210.3, "classic": 182.1, "plain": 89.0}   # profiles/r1_bench_*_n8.json
+MEASURED_N = {1: 97.2, 2: 142.0, 4: 194.0, 8: 206.4}
+
+
+def mean_tps(cfg=None, seeds=6, **kw):
+    out = []
+    for seed in range(seeds):
+        r = sim.run(sim.default_config(seed=seed, **(cfg or {})), prompt_seed=seed, n_prompt=64, n_predict=128, n_ctx=1024, **kw)
+        assert r["tokens"] == r["truth"] and r["n"] >= 128, (cfg, kw, r["error"])
+        out.append(r["result"]["decode_tok_per_s"])
+    return sum(out) / len(out)
+
+
+def calibrate():
+    runs = {"d3": dict(n_draft=3, max_spec_runs=9), "d2": dict(n_draft=2, max_spec_runs=9), "d5": dict(n_draft=5, max_spec_runs=9),
+            "d8": dict(n_draft=8, max_spec_runs=9), "d3np1": dict(n_draft=3, n_parallel=1, max_spec_runs=9),
+            "classic": dict(mode="classic", n_draft=3), "plain": dict(mode="plain")}
+    for k, kw in runs.items():
+        v = mean_tps(**kw)
+        print("%-8s measured %6.1f   model %6.1f   (%+.0f %%)" % (k, MEASURED_8[k], v, 100 * (v / MEASURED_8[k] - 1)))
+
+
+def sensitivity():
+    rows = [("as measured", {}), ("draft step 0.35 ms", dict(draft_us=200)), ("draft step 0.10 ms", dict(draft_us=0, enqueue_us=100)),
+            ("stage 0.90 ms", dict(stage_us=900)), ("stage 0.90 ms + draft 0.35 ms", dict(stage_us=900, draft_us=200)),
+            ("agreement 0.6", dict(agree=0.6)), ("agreement 0.9", dict(agree=0.9)), ("agreement 0.95", dict(agree=0.95))]
+    for chain in ("0", "1"):
+        os.environ["PIB_SCHED_CHAIN"] = chain
+        print("PIB_SCHED_CHAIN=%s" % chain)
+        for name, cfg in rows:
+            print("  %-32s --draft 3: %5.0f   --draft 5: %5.0f   classic: %5.0f" %
+                  (name, mean_tps(cfg, n_draft=3, max_spec_runs=9), mean_tps(cfg, n_draft=5, max_spec_runs=9), mean_tps(cfg, mode="classic", n_draft=3)))
+
+
+def scaling():
+    for stages in (1, 2, 4, 8):
+        cfg = dict(n_stages=stages, stage_us=10320.0 / stages, stage_tok_us=480.0 / stages)
+        print("%d stage(s): measured %5.1f   model PipeInfer %5.1f   classic %5.1f   plain %5.1f" %
+              (stages, MEASURED_N[stages], mean_tps(cfg, n_draft=3, max_spec_runs=stages + 1), mean_tps(cfg, mode="classic", n_draft=3), mean_tps(cfg, mode="plain")))
+
+
+if __name__ == "__main__":
+    {"calibrate": calibrate, "sensitivity": sensitivity, "scaling": scaling}[sys.argv[1] if len(sys.argv) > 1 else "calibrate"]()
