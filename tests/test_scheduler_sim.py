@@ -202,3 +202,33 @@ def test_classic_speculation_is_the_reference_schedule(case, monkeypatch, tmp_pa
     assert mine["tokens"][:len(ref["tokens"])] == ref["tokens"] == mine["truth"][:len(ref["tokens"])]
     assert abs(mine["result"]["decode_tok_per_s"] - ref["decode_tok_per_s"]) < 1e-2 * ref["decode_tok_per_s"]
     assert mine["draft"]["decodes"] == ref["stats"]["draft"]["decodes"]
+
+
+@needs_ref
+@pytest.mark.parametrize("block", range(4))
+def test_random_configurations_give_the_reference_schedule(block, monkeypatch, tmp_path):
+    """the comparison of test_schedule_is_the_reference_schedule over drawn timings, agreement, tree and threshold flags"""
+    rnd = random.Random(4242 + block)
+    monkeypatch.setenv("PIB_REFERENCE_HAZARDS", "1")
+    compared = 0
+    for trial in range(8):
+        p_top = rnd.choice([0.5, 0.6, 0.9])
+        fields = dict(n_stages=rnd.choice([1, 2, 4, 8]), agree=rnd.choice([0.3, 0.6, 0.8, 0.95, 1.0]), p_top=p_top, p_second=rnd.choice([0.04, 0.3 if p_top < 0.7 else 0.08]),
+                      seed=100 * block + trial, draft_us=rnd.choice([100, 710, 3000]), stage_us=rnd.choice([200, 1290]), skip_us=rnd.choice([5, 150]),
+                      jitter=rnd.choice([0, 0.3]), enqueue_us=rnd.choice([60, 150]), n_vocab=4096, call_us=0)
+        flags = dict(n_draft=rnd.choice([2, 3, 5, 8]), n_parallel=rnd.choice([1, 2, 3]), p_accept=rnd.choice([0.1, 0.45]), p_split=rnd.choice([0.2, 0.85]),
+                     p_recovery=rnd.choice([0.0, 0.05]), p_decay=rnd.choice([0.0, 0.1]))
+        text = "".join(chr(33 + (i * (7 + trial + 10 * block)) % 90) for i in range(40))
+        ref_trace, my_trace = str(tmp_path / "ref.txt"), str(tmp_path / "mine.txt")
+        ref = sim.run_reference(fields, text, n_predict=64, n_ctx=4096, trace=ref_trace, workdir=str(tmp_path), **flags)
+        if ref["stats"]["target"]["refused"] or ref["stats"]["draft"]["refused"]:
+            continue                      # the reference carries on with a NULL run handle there; this scheduler stops
+        monkeypatch.setenv("SIM_TRACE", my_trace)
+        mine = sim.run(sim.default_config(**fields), prompt=sim.text_prompt(text), n_predict=64, n_ctx=4096, **flags)
+        a, b = open(ref_trace).read().splitlines(), open(my_trace).read().splitlines()
+        for i, (x, y) in enumerate(zip(a, b)):
+            assert x == y, "%s %s\nevent %d differs:\n reference: %s\n here:      %s" % (fields, flags, i, x[:300], y[:300])
+        assert len(a) == len(b)
+        assert mine["tokens"][:len(ref["tokens"])] == ref["tokens"]
+        compared += 1
+    assert compared >= 6
