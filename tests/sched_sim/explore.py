@@ -27,17 +27,21 @@ def mean_tps(cfg=None, seeds=6, **kw):
     return sum(out) / len(out)
 
 
+BEFORE_FIX = dict(spec_issue_extra_us=900, nonspec_issue_extra_us=500)    # host KV-mirror cost per run issue when profiles/ was measured
+
+
 def calibrate():
+    """the measurements in profiles/ predate the host KV-mirror fix: compare them with the model carrying that cost"""
     runs = {"d3": dict(n_draft=3, max_spec_runs=9), "d2": dict(n_draft=2, max_spec_runs=9), "d5": dict(n_draft=5, max_spec_runs=9),
             "d8": dict(n_draft=8, max_spec_runs=9), "d3np1": dict(n_draft=3, n_parallel=1, max_spec_runs=9),
             "classic": dict(mode="classic", n_draft=3), "plain": dict(mode="plain")}
     for k, kw in runs.items():
-        v = mean_tps(**kw)
-        print("%-8s measured %6.1f   model %6.1f   (%+.0f %%)" % (k, MEASURED_8[k], v, 100 * (v / MEASURED_8[k] - 1)))
+        b, a = mean_tps(BEFORE_FIX, **kw), mean_tps(**kw)
+        print("%-8s measured %6.1f   model (as measured) %6.1f (%+.0f %%)   model (after the fix) %6.1f" % (k, MEASURED_8[k], b, 100 * (b / MEASURED_8[k] - 1), a))
 
 
 def sensitivity():
-    rows = [("as measured", {}), ("draft step 0.35 ms", dict(draft_us=200)), ("draft step 0.10 ms", dict(draft_us=0, enqueue_us=100)),
+    rows = [("today", {}), ("draft step 0.35 ms", dict(draft_us=200)), ("draft step 0.10 ms", dict(draft_us=0, enqueue_us=100)),
             ("stage 0.90 ms", dict(stage_us=900)), ("stage 0.90 ms + draft 0.35 ms", dict(stage_us=900, draft_us=200)),
             ("agreement 0.6", dict(agree=0.6)), ("agreement 0.9", dict(agree=0.9)), ("agreement 0.95", dict(agree=0.95))]
     for chain in ("0", "1"):
@@ -51,8 +55,9 @@ def sensitivity():
 def scaling():
     for stages in (1, 2, 4, 8):
         cfg = dict(n_stages=stages, stage_us=10320.0 / stages, stage_tok_us=480.0 / stages)
-        print("%d stage(s): measured %5.1f   model PipeInfer %5.1f   classic %5.1f   plain %5.1f" %
-              (stages, MEASURED_N[stages], mean_tps(cfg, n_draft=3, max_spec_runs=stages + 1), mean_tps(cfg, mode="classic", n_draft=3), mean_tps(cfg, mode="plain")))
+        print("%d stage(s): measured %5.1f   model as measured %5.1f   after the fix %5.1f   classic %5.1f   plain %5.1f" %
+              (stages, MEASURED_N[stages], mean_tps(dict(cfg, **BEFORE_FIX), n_draft=3, max_spec_runs=stages + 1),
+               mean_tps(cfg, n_draft=3, max_spec_runs=stages + 1), mean_tps(cfg, mode="classic", n_draft=3), mean_tps(cfg, mode="plain")))
 
 
 if __name__ == "__main__":

@@ -19,7 +19,7 @@ class Config(C.Structure):
                 ("ret_us", C.c_double), ("skip_us", C.c_double), ("draft_us", C.c_double), ("draft_tok_us", C.c_double),
                 ("enqueue_us", C.c_double), ("call_us", C.c_double), ("agree", C.c_double), ("p_top", C.c_double),
                 ("p_second", C.c_double), ("jitter", C.c_double), ("share_gpu0", C.c_int32), ("n_vocab", C.c_int32),
-                ("seed", C.c_uint64)]
+                ("seed", C.c_uint64), ("spec_issue_extra_us", C.c_double), ("nonspec_issue_extra_us", C.c_double)]
 
 
 class SpecParams(C.Structure):

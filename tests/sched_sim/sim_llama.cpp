@@ -53,10 +53,12 @@ struct sim_config {
     int32_t share_gpu0;          // draft decodes delay stage-0 work
     int32_t n_vocab;
     uint64_t seed;
+    double  spec_issue_extra_us;     // extra host time to issue a speculative target run / a non-speculative one (the state of the
+    double  nonspec_issue_extra_us;  // library BEFORE the host KV-mirror fix: ~900 and ~500 us)
 };
 // defaults: fitted to the 8-GPU runs of the 70B / 1.1B pair in profiles/ (plain 89, classic 182, PipeInfer 206 / 204 / 184 / 163
 // tok/s at --draft 3 / 2 / 5 / 8): the model lands within 10 % of each
-static const sim_config DEFAULTS = { 8, 1290, 60, 20, 30, 150, 710, 0, 150, 1.5, 0.8, 0.9, 0.05, 0, 0, 32000, 1 };
+static const sim_config DEFAULTS = { 8, 1290, 60, 20, 30, 150, 710, 0, 150, 1.5, 0.8, 0.9, 0.05, 0, 0, 32000, 1, 0, 0 };
 static sim_config G = DEFAULTS;
 static double g_now = 0;
 static uint64_t g_rng = 88172645463325252ull;
@@ -238,6 +240,7 @@ void llama_kv_cache_seq_keep(struct llama_context * ctx, llama_seq_id seq) { kvl
 
 struct ggml_cgraph * llama_start_async_decode(struct llama_context & c, struct llama_batch b) {
     g_now += G.enqueue_us * noise();
+    if (c.is_target) g_now += (b.n_tokens == 1 && b.n_seq_id[0] == 1 && b.seq_id[0][0] == 0) ? G.nonspec_issue_extra_us : G.spec_issue_extra_us;
     sim_run run;
     const uint32_t head_before = c.kv.head;
     (void) head_before;
