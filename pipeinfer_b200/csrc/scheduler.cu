@@ -98,14 +98,19 @@ class Scheduler {
     // the draft was right the runs already in flight are drafted and verified a second time and later dropped as stale.  With
     // this policy drafting resumes at the tip of the chain whenever the newest speculative run in flight is still consistent
     // with what has been generated; a rejection restarts the chain as before.  The text is the greedy text either way.
-    bool            chain_policy = getenv("PIB_SCHED_CHAIN") != nullptr && atoi(getenv("PIB_SCHED_CHAIN")) != 0;
+    // PIB_SCHED_CHAIN=2 additionally skips, when the chain is resumed, the non-speculative run of the token just sampled (on
+    // both models): the next link in flight starts with exactly that token, so its first row yields the same logits and its
+    // KV cell is committed along with that link's accepted tokens.
+    int             chain_policy = getenv("PIB_SCHED_CHAIN") ? atoi(getenv("PIB_SCHED_CHAIN")) : 0;
     int             chain_start_tgt = 0, chain_start_dft = 0;      // n_past at which the current chain began: prefix of all its links
     llama_token_data tip_top8[8];                                   // the draft's candidates after the tip of branch 0
     bool            have_tip = false;
     struct Tip { std::vector<Draft> drafts; int spec_past_tgt = 0, spec_past_dft = 0, seq_offset = 0; llama_token id = 0; bool first_run = true; } tip;
     int             n_chain_resumed = 0;
     void save_tip() { tip.drafts = drafts; tip.spec_past_tgt = spec_past_tgt; tip.spec_past_dft = spec_past_dft; tip.seq_offset = current.seq_offset; tip.id = id; tip.first_run = first_run; }
+    bool chain_alive() const;
     bool resume_chain(int verified_offset, bool verified_spec);
+    int  pending_pos_tgt = -1, pending_pos_dft = -1;       // policy 2: position of a sampled token that lives only in the next link's partition
     int64_t         t_trace0 = 0;
     void ev(const char * what, int a = 0, int b = 0, int c = 0) { if (tracing) trace.push_back({ llama_time_us() - t_trace0, what, a, b, c }); }
     void dump_trace() {
@@ -291,11 +296,15 @@ bool Scheduler::start_spec_run(int prefix_n_past, int n_past_dft_arg, int orig_o
 
 // after a verification: is the newest speculative run in flight still consistent with the text (check_for_cancel has just
 // run) and does it reach beyond what is verified?  Then go on drafting from its end instead of from the verified token.
-bool Scheduler::resume_chain(int verified_offset, bool verified_spec) {
+bool Scheduler::chain_alive() const {
     if (!chain_policy || tip.first_run || !have_tip) return false;
     const Run * newest = nullptr;
     for (const Run & r : tgt_runs) if (r.speculative) { newest = &r; break; }      // front() is the newest
-    if (!newest || newest->canceled || newest->seq_offset != tip.seq_offset || newest->n_past_max <= n_past_tgt) return false;
+    return newest && !newest->canceled && newest->seq_offset == tip.seq_offset && newest->n_past_max > n_past_tgt;
+}
+
+bool Scheduler::resume_chain(int verified_offset, bool verified_spec) {
+    if (!chain_alive()) return false;
     if (verified_spec) free_offsets.push_back(verified_offset);                   // its partition is not reused by a restart
     drafts = tip.drafts;
     spec_past_tgt = tip.spec_past_tgt; spec_past_dft = tip.spec_past_dft;
@@ -451,24 +460,39 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
         check_for_cancel();                                                                              // :581
 
         if (current.speculative) {                                                                       // :585-628 KV commit
+            // policy 2: the token sampled by the previous verification sits in this run's first cell only
+            const int c0_tgt = pending_pos_tgt == current.n_past_tgt ? current.n_past_tgt : current.n_past_tgt + 1;
+            const int c0_dft = pending_pos_dft == current.n_past_dft ? current.n_past_dft : current.n_past_dft + 1;
+            pending_pos_tgt = pending_pos_dft = -1;
             for (int i = 0; i < np; i++) {
                 llama_kv_cache_seq_rm(ctx_tgt, i + current.seq_offset, n_past_tgt, -1);
                 llama_kv_cache_seq_rm(ctx_dft, i + current.seq_offset, n_past_dft, -1);
             }
-            llama_kv_cache_seq_rm(ctx_tgt, 0, current.n_past_tgt + 1, n_past_tgt);
-            llama_kv_cache_seq_rm(ctx_dft, 0, current.n_past_dft + 1, n_past_dft);
-            llama_kv_cache_seq_cp(ctx_tgt, s_keep + current.seq_offset, 0, current.n_past_tgt + 1, n_past_tgt);
-            llama_kv_cache_seq_cp(ctx_dft, s_keep + current.seq_offset, 0, current.n_past_dft + 1, n_past_dft);
+            llama_kv_cache_seq_rm(ctx_tgt, 0, c0_tgt, n_past_tgt);
+            llama_kv_cache_seq_rm(ctx_dft, 0, c0_dft, n_past_dft);
+            llama_kv_cache_seq_cp(ctx_tgt, s_keep + current.seq_offset, 0, c0_tgt, n_past_tgt);
+            llama_kv_cache_seq_cp(ctx_dft, s_keep + current.seq_offset, 0, c0_dft, n_past_dft);
             // the reference interleaves the two contexts inside one loop; the contexts are independent, so two loops
             // give the same per-context call order (and let the op-log collapse each into one KVOP_SWEEP)
             for (int i = 1; i <= max_seq; i++) {
-                llama_kv_cache_seq_rm(ctx_tgt, i, current.n_past_tgt + 1, n_past_tgt);
-                llama_kv_cache_seq_cp(ctx_tgt, 0, i, current.n_past_tgt + 1, n_past_tgt);
+                llama_kv_cache_seq_rm(ctx_tgt, i, c0_tgt, n_past_tgt);
+                llama_kv_cache_seq_cp(ctx_tgt, 0, i, c0_tgt, n_past_tgt);
             }
             for (int i = 1; i <= max_seq; i++) {
-                llama_kv_cache_seq_rm(ctx_dft, i, current.n_past_dft + 1, n_past_dft);
-                llama_kv_cache_seq_cp(ctx_dft, 0, i, current.n_past_dft + 1, n_past_dft);
+                llama_kv_cache_seq_rm(ctx_dft, i, c0_dft, n_past_dft);
+                llama_kv_cache_seq_cp(ctx_dft, 0, i, c0_dft, n_past_dft);
             }
+        }
+        if (chain_policy >= 2 && chain_alive()) {
+            // the next link in flight begins with `id` at this very position: no run of its own for it, on either model
+            pending_pos_tgt = n_past_tgt++;
+            pending_pos_dft = n_past_dft++;
+            if (!has_run_first_token) { has_run_first_token = true; first_token = true; }
+            ev("skip_nonspec", n_past_tgt);
+            resume_chain(current.seq_offset, current.speculative);
+            speculation_loop();
+            if (n_predict > P.n_predict || has_eos || failed) break;
+            continue;
         }
         begin_non_spec_run(ctx_tgt, tgt_runs, n_past_tgt, n_past_dft);                                   // :630 (async)
         begin_non_spec_run(ctx_dft, dft_runs, n_past_dft, n_past_dft);                                   // :633 (finished right away)

@@ -31,10 +31,11 @@ def test_default_timing_8_stages(mode):
         assert r["result"]["n_accept"] > 0 and r["result"]["decode_tok_per_s"] > 120
 
 
-@pytest.mark.parametrize("chain", [0, 1])
+@pytest.mark.parametrize("chain", [0, 1, 2])
 @pytest.mark.parametrize("block", range(6))
 def test_random_timings_flags_and_agreement(block, chain, monkeypatch):
-    # chain = 1: the experimental policy that resumes drafting at the tip of the chain after a verification (PIB_SCHED_CHAIN)
+    # chain = 1: the experimental policy that resumes drafting at the tip of the chain after a verification (PIB_SCHED_CHAIN);
+    # chain = 2: ... and does not run the token just sampled on its own when the next link in flight starts with it
     monkeypatch.setenv("PIB_SCHED_CHAIN", str(chain))
     rnd = random.Random(1000 + block + 50 * chain)
     for trial in range(25):
@@ -101,9 +102,14 @@ def test_chain_policy_resumes_and_pays_with_a_good_draft(monkeypatch):
     ref = sim.run(cfg, **kw)
     monkeypatch.setenv("PIB_SCHED_CHAIN", "1")
     chained = sim.run(cfg, **kw)
+    monkeypatch.setenv("PIB_SCHED_CHAIN", "2")
+    chained2 = sim.run(cfg, **kw)
     check(ref, 192)
     check(chained, 192)
+    check(chained2, 192)
     assert chained["result"]["decode_tok_per_s"] > 1.08 * ref["result"]["decode_tok_per_s"]
+    assert chained2["result"]["decode_tok_per_s"] > 1.05 * chained["result"]["decode_tok_per_s"]
+    assert chained2["target"]["decodes"] < chained["target"]["decodes"]          # the skipped non-speculative runs
 
 
 # ---- differential: the reference's own scheduler (speculative.cpp, unmodified) on the same model --------------------------
