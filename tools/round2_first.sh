@@ -1,0 +1,14 @@
+#!/bin/bash
+# First 8-GPU visit of the next round: what this round could not afford to re-measure.
+#   gpurun --gpus 8 --timeout 600 -- 'bash tools/round2_first.sh'
+# Each line is one bench run (--no-cpu-baseline, 3 + 3 steps, ~20 s): the default policy after the host KV-mirror fix, the two
+# experimental chain policies, the reference's cancel behaviour, and the same at a draft agreement of 0.9.
+set -u
+A="--no-cpu-baseline --steps 3 --warmup 3"
+bash tools/scale_run.sh 8 r2_default $A
+PIB_SCHED_CHAIN=1 bash tools/scale_run.sh 8 r2_chain1 $A
+PIB_SCHED_CHAIN=2 bash tools/scale_run.sh 8 r2_chain2 $A
+PIB_REFERENCE_HAZARDS=1 bash tools/scale_run.sh 8 r2_refcancel $A
+bash tools/scale_run.sh 8 r2_default_a90 $A --agree 0.9
+PIB_SCHED_CHAIN=1 bash tools/scale_run.sh 8 r2_chain1_a90 $A --agree 0.9
+PIB_SCHED_CHAIN=2 bash tools/scale_run.sh 8 r2_chain2_a90 $A --agree 0.9
