@@ -183,6 +183,8 @@ def main():
                     help="bound on target runs in flight: 0 = the reference's behaviour (unbounded), -1 = number of pipeline stages + 1")
     ap.add_argument("--mode", default="speculative", choices=["speculative", "plain", "classic"],
                     help="plain = non-speculative greedy decoding through the same pipeline (the reference's `main`): the second denominator")
+    ap.add_argument("--sched-policy", default="reference", choices=["reference", "chain1", "chain2"],
+                    help="scheduler policy: the reference's, or the experimental chain-continuation policies (PIB_SCHED_CHAIN, DESIGN.md §9)")
     ap.add_argument("--no-draft-priority", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--layer-split", default="", help="comma-separated per-stage weights, as the reference's --mpi-layer-split")
@@ -201,6 +203,9 @@ def main():
                           % (label, args.agree, args.prompt_len, args.draft, args.np, args.pa, args.ps, args.n_predict,
                              args.max_spec_runs or "unbounded", args.gpus),
               "l2_policy": l2_policy}
+    if args.sched_policy != "reference":
+        os.environ["PIB_SCHED_CHAIN"] = args.sched_policy[-1]          # read by the scheduler at every generation
+        config["workload"] += ", scheduler policy %s (experimental, DESIGN.md §9)" % args.sched_policy
 
     if args.impl == "reference":
         if rank != 0:

@@ -109,6 +109,7 @@ class Scheduler {
     int             n_chain_resumed = 0;
     void save_tip() { tip.drafts = drafts; tip.spec_past_tgt = spec_past_tgt; tip.spec_past_dft = spec_past_dft; tip.seq_offset = current.seq_offset; tip.id = id; tip.first_run = first_run; }
     bool chain_alive() const;
+    bool next_link_starts_with(llama_token tok) const;
     bool resume_chain(int verified_offset, bool verified_spec);
     int  pending_pos_tgt = -1, pending_pos_dft = -1;       // policy 2: position of a sampled token that lives only in the next link's partition
     int64_t         t_trace0 = 0;
@@ -303,6 +304,17 @@ bool Scheduler::chain_alive() const {
     return newest && !newest->canceled && newest->seq_offset == tip.seq_offset && newest->n_past_max > n_past_tgt;
 }
 
+// policy 2's precondition, checked explicitly: the oldest speculative run in flight that has not been cancelled begins at the
+// position the sampled token will take and its kept branch begins with that token
+bool Scheduler::next_link_starts_with(llama_token tok) const {
+    for (auto it = tgt_runs.rbegin(); it != tgt_runs.rend(); ++it) {                // back() is the oldest
+        if (!it->speculative || it->canceled) continue;
+        const Draft & d = it->drafts[it->s_keep];
+        return it->n_past_tgt == n_past_tgt && !d.tokens.empty() && d.tokens[0] == tok;
+    }
+    return false;
+}
+
 bool Scheduler::resume_chain(int verified_offset, bool verified_spec) {
     if (!chain_alive()) return false;
     if (verified_spec) free_offsets.push_back(verified_offset);                   // its partition is not reused by a restart
@@ -483,7 +495,7 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
                 llama_kv_cache_seq_cp(ctx_dft, 0, i, c0_dft, n_past_dft);
             }
         }
-        if (chain_policy >= 2 && chain_alive()) {
+        if (chain_policy >= 2 && chain_alive() && next_link_starts_with(id)) {
             // the next link in flight begins with `id` at this very position: no run of its own for it, on either model
             pending_pos_tgt = n_past_tgt++;
             pending_pos_dft = n_past_dft++;

@@ -6,9 +6,11 @@
 set -u
 A="--no-cpu-baseline --steps 3 --warmup 3"
 bash tools/scale_run.sh 8 r2_default $A
-PIB_SCHED_CHAIN=1 bash tools/scale_run.sh 8 r2_chain1 $A
-PIB_SCHED_CHAIN=2 bash tools/scale_run.sh 8 r2_chain2 $A
+bash tools/scale_run.sh 8 r2_chain1 $A --sched-policy chain1
+bash tools/scale_run.sh 8 r2_chain2 $A --sched-policy chain2
 PIB_REFERENCE_HAZARDS=1 bash tools/scale_run.sh 8 r2_refcancel $A
 bash tools/scale_run.sh 8 r2_default_a90 $A --agree 0.9
-PIB_SCHED_CHAIN=1 bash tools/scale_run.sh 8 r2_chain1_a90 $A --agree 0.9
-PIB_SCHED_CHAIN=2 bash tools/scale_run.sh 8 r2_chain2_a90 $A --agree 0.9
+bash tools/scale_run.sh 8 r2_chain1_a90 $A --agree 0.9 --sched-policy chain1
+bash tools/scale_run.sh 8 r2_chain2_a90 $A --agree 0.9 --sched-policy chain2
+# one GPU (the driver's headline bench): the model predicts 94 -> 115 tok/s for chain2
+# gpurun --timeout 300 -- 'bash tools/scale_run.sh 1 r2_n1 --no-cpu-baseline; bash tools/scale_run.sh 1 r2_n1_chain2 --no-cpu-baseline --sched-policy chain2'
