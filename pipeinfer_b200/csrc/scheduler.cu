@@ -101,6 +101,9 @@ class Scheduler {
     // PIB_SCHED_CHAIN=2 additionally skips, when the chain is resumed, the non-speculative run of the token just sampled (on
     // both models): the next link in flight starts with exactly that token, so its first row yields the same logits and its
     // KV cell is committed along with that link's accepted tokens.
+    // PIB_SCHED_CHAIN=3 additionally merges, when the chain has to be restarted, the target's non-speculative run of the sampled
+    // token into the first speculative run (the token becomes row 0 of that run, as in classic speculation): one pass of the
+    // target instead of two, which is what matters when there is no pipeline to hide the second one (one or two GPUs).
     int             chain_policy = getenv("PIB_SCHED_CHAIN") ? atoi(getenv("PIB_SCHED_CHAIN")) : 0;
     int             chain_start_tgt = 0, chain_start_dft = 0;      // n_past at which the current chain began: prefix of all its links
     llama_token_data tip_top8[8];                                   // the draft's candidates after the tip of branch 0
@@ -111,6 +114,7 @@ class Scheduler {
     bool chain_alive() const;
     bool next_link_starts_with(llama_token tok) const;
     bool resume_chain(int verified_offset, bool verified_spec);
+    bool merge_first = false;                              // policy 3: the next first link carries the sampled token itself
     int  pending_pos_tgt = -1, pending_pos_dft = -1;       // policy 2: position of a sampled token that lives only in the next link's partition
     int64_t         t_trace0 = 0;
     void ev(const char * what, int a = 0, int b = 0, int c = 0) { if (tracing) trace.push_back({ llama_time_us() - t_trace0, what, a, b, c }); }
@@ -224,6 +228,8 @@ bool Scheduler::start_spec_run(int prefix_n_past, int n_past_dft_arg, int orig_o
         drafts[s].i_batch_tgt.clear();
     }
     drafts[0].tokens.push_back(id);                                                                      // erased after drafting
+    const int merged = merge_first && first_run ? 1 : 0;                                                 // policy 3: `id` is row 0 of this run
+    if (merged) { drafts[0].i_batch_tgt.push_back(0); batch_tgt.add(id, spec_past_tgt, { off }); }
     batch_dft.clear();
     int n_seq_cur = 0, max_ran_seq = 0, n_past_cur = spec_past_dft;
     for (int s = 0; s < np; s++) { drafts[s].skip = true; drafts[s].active = false; drafts[s].drafting = false; }
@@ -257,10 +263,10 @@ bool Scheduler::start_spec_run(int prefix_n_past, int n_past_dft_arg, int orig_o
                 const int sq = sa[is];
                 drafts[sq].tokens.push_back(tok);
                 drafts[sq].i_batch_tgt.push_back(batch_tgt.size());
-                batch_tgt.add(tok, spec_past_tgt + i, { sq + off });
+                batch_tgt.add(tok, spec_past_tgt + merged + i, { sq + off });
                 drafts[sq].i_batch_dft = batch_dft.size();
                 batch_dft.add(tok, n_past_cur, { sq + off });
-                if (batch_tgt.size() > P.n_draft) drafts[sq].drafting = false;
+                if (batch_tgt.size() > P.n_draft + merged) drafts[sq].drafting = false;
             }
         }
         if (batch_dft.size() == 0) break;
@@ -270,27 +276,28 @@ bool Scheduler::start_spec_run(int prefix_n_past, int n_past_dft_arg, int orig_o
         ++n_drafted;
         max_ran_seq = n_seq_cur;
         batch_dft.clear();
-        if (batch_tgt.size() > P.n_draft) break;
+        if (batch_tgt.size() > P.n_draft + merged) break;
     }
     if (batch_dft.size() != 0) llama_decode(ctx_dft, batch_dft.view(max_seq + 1));                       // :1107-1113
 
-    if (batch_tgt.size() == 0) {                                                                         // :1129-1135
+    if (batch_tgt.size() == merged) {                                                                    // :1129-1135 (nothing drafted)
         free_offsets.push_back(off);
         n_rejected++;
         return true;
     }
-    for (int s = 0; s < np; ++s) {                                                                       // :1149-1157
+    for (int s = 0; s < np && !merged; ++s) {                                                            // :1149-1157
         if (!drafts[s].active) continue;
-        drafts[s].tokens.erase(drafts[s].tokens.begin());
+        drafts[s].tokens.erase(drafts[s].tokens.begin());                                                // (a merged run keeps `id` in front: it is in the batch)
     }
     if (first_run) ++n_drafted;
     n_spec_runs++;
     begin_async_run(ctx_tgt, tgt_runs, drafts, spec_past_tgt, n_past_dft_arg, true, batch_tgt,
                     spec_past_tgt + (int) drafts[0].tokens.size(), prefix_n_past, off);                 // :1163
     spec_past_tgt += (int) drafts[0].tokens.size();
-    spec_past_dft += (int) drafts[0].tokens.size();
+    spec_past_dft += (int) drafts[0].tokens.size() - merged;
     id = drafts[0].tokens.back();
     first_run = false;
+    merge_first = false;
     if (chain_policy) have_tip = llama_pib_get_top8(ctx_dft, drafts[0].i_batch_dft, tip_top8) == 0;   // what the next link starts from
     return false;
 }
@@ -356,7 +363,7 @@ void Scheduler::speculation_loop() {
         if (!first_run && current.seq_offset == orig_offset && !reference_hazards) break;
         auto it = std::find(free_offsets.begin(), free_offsets.end(), current.seq_offset);
         if (it != free_offsets.end()) free_offsets.erase(it);
-        if (first_run || !chain_policy) { chain_start_tgt = n_past_tgt; chain_start_dft = n_past_dft; }
+        if (first_run || !chain_policy) { chain_start_tgt = n_past_tgt - (merge_first ? 1 : 0); chain_start_dft = n_past_dft; }
         if (start_spec_run(chain_start_tgt, chain_start_dft, orig_offset, p_adjust)) break;
         is_waiting = llama_mpi_iprobe(ctx_tgt);
         first_run  = false;
@@ -506,7 +513,9 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
             if (n_predict > P.n_predict || has_eos || failed) break;
             continue;
         }
-        begin_non_spec_run(ctx_tgt, tgt_runs, n_past_tgt, n_past_dft);                                   // :630 (async)
+        const bool try_merge = chain_policy >= 3;
+        if (!try_merge) begin_non_spec_run(ctx_tgt, tgt_runs, n_past_tgt, n_past_dft);                   // :630 (async)
+        else { pending_pos_tgt = n_past_tgt++; merge_first = true; }                                     // `id` rides in the next first link
         begin_non_spec_run(ctx_dft, dft_runs, n_past_dft, n_past_dft);                                   // :633 (finished right away)
         if (!has_run_first_token) { has_run_first_token = true; first_token = true; }
         {
@@ -514,18 +523,27 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
             llama_finish_async_decode(*ctx_dft, dr.batch.view(max_seq + 1), dr.handle);
             dft_runs.pop_back();
         }
-        spec_past_tgt = n_past_tgt; spec_past_dft = n_past_dft;
-        if (resume_chain(current.seq_offset, current.speculative)) {
+        spec_past_tgt = n_past_tgt - (try_merge ? 1 : 0); spec_past_dft = n_past_dft;
+        if (try_merge) pending_pos_dft = n_past_dft;       // the merged run also verifies its FIRST drafted token: the draft's cell for it is committed from the partition
+        if (!try_merge && resume_chain(current.seq_offset, current.speculative)) {
             speculation_loop();
             if (n_predict > P.n_predict || has_eos || failed) break;
             continue;
         }
+        bool can_speculate = true;
         if (!current.speculative) {                                                                      // :653-662
-            if (free_offsets.empty()) continue;
-            current.seq_offset = free_offsets.front();
-            free_offsets.pop_front();
+            if (free_offsets.empty()) can_speculate = false;
+            else { current.seq_offset = free_offsets.front(); free_offsets.pop_front(); }
         }
-        speculation_loop();                                                                              // :666
+        if (can_speculate) speculation_loop();                                                           // :666
+        if (merge_first) {
+            // no first link was issued (the oldest run is already waiting, no partition or run slot free, nothing drafted):
+            // the sampled token gets its own run after all, as in the reference -- there must be a run in flight that yields the next token
+            merge_first = false; pending_pos_tgt = pending_pos_dft = -1; n_past_tgt--;
+            begin_non_spec_run(ctx_tgt, tgt_runs, n_past_tgt, n_past_dft);
+            spec_past_tgt = n_past_tgt;
+        }
+        if (!can_speculate) continue;
         if (n_predict > P.n_predict || has_eos || failed) break;                                         // :672
     }
     const int64_t t_dec_end = llama_time_us();

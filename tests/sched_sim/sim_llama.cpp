@@ -5,7 +5,7 @@
 // driven on the CPU:
 //   * time is virtual: llama_time_us() returns a clock that only the calls below advance (host cost per call, waiting
 //     for a run); a target decode occupies the S stages of a pipeline one after the other, runs queue behind each other
-//     per stage, a cancelled run takes (almost) no time in the stages it has not reached when the cancel is issued; the
+//     per stage, a cancelled run stops at the next kernel (it takes almost no time from the cancel on); the
 //     draft decodes synchronously and, if asked, steals GPU time from stage 0 (same GPU, higher priority);
 //   * KV bookkeeping is the real one: the same op-log front end and host mirror the engine uses (kv_meta.cu), so "no
 //     slot" failures happen where they would;
@@ -179,9 +179,13 @@ static void resolve(llama_context * c, bool retire) {
         double t = r.t_issue;
         for (int s = 0; s < G.n_stages; s++) {
             const double start = std::max(t, free_at[s]);
-            const bool   skip  = r.t_cancel >= 0 && start >= r.t_cancel;
-            const double d     = skip ? G.skip_us : r.dur[s];
-            if (skip) r.skipped = true;
+            // cancellation is kernel-granular in the engine (every kernel of the run tests the flag first): a stage that has not
+            // started is skipped, a stage in progress stops at the next kernel; either way the run's KV cells are not all written
+            double d = r.dur[s];
+            if (r.t_cancel >= 0 && start + d > r.t_cancel) {
+                d = std::max(0.0, r.t_cancel - start) + G.skip_us;
+                r.skipped = true;
+            }
             const double end   = s == 0 ? run_on_gpu0(start, d) : start + d;
             free_at[s] = end;
             t = end + (s + 1 < G.n_stages ? G.hop_us : G.ret_us);
