@@ -183,7 +183,7 @@ def main():
                     help="bound on target runs in flight: 0 = the reference's behaviour (unbounded), -1 = number of pipeline stages + 1")
     ap.add_argument("--mode", default="speculative", choices=["speculative", "plain", "classic"],
                     help="plain = non-speculative greedy decoding through the same pipeline (the reference's `main`): the second denominator")
-    ap.add_argument("--sched-policy", default="reference", choices=["reference", "chain1", "chain2"],
+    ap.add_argument("--sched-policy", default="reference", choices=["reference", "chain1", "chain2", "chain3"],
                     help="scheduler policy: the reference's, or the experimental chain-continuation policies (PIB_SCHED_CHAIN, DESIGN.md §9)")
     ap.add_argument("--no-draft-priority", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -13,4 +13,6 @@ bash tools/scale_run.sh 8 r2_default_a90 $A --agree 0.9
 bash tools/scale_run.sh 8 r2_chain1_a90 $A --agree 0.9 --sched-policy chain1
 bash tools/scale_run.sh 8 r2_chain2_a90 $A --agree 0.9 --sched-policy chain2
 # one GPU (the driver's headline bench): the model predicts 94 -> 115 tok/s for chain2
-# gpurun --timeout 300 -- 'bash tools/scale_run.sh 1 r2_n1 --no-cpu-baseline; bash tools/scale_run.sh 1 r2_n1_chain2 --no-cpu-baseline --sched-policy chain2'
+# gpurun --timeout 300 -- 'bash tools/scale_run.sh 1 r2_n1 --no-cpu-baseline; bash tools/scale_run.sh 1 r2_n1_chain2 --no-cpu-baseline --sched-policy chain2; python -m pytest tests/test_gpu_scheduler.py -q -m gpu'
+#   (and PIB_SCHED_CHAIN=2 python -m pytest tests/test_gpu_scheduler.py tests/test_gpu_cli.py -q -m gpu  before making it the default)
+# model: 102 -> 157 tok/s on one GPU, 168 -> 221 on two (gpurun --gpus 2 ... scale_run.sh 2 ...), 245 -> 260 on four
