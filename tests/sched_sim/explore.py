@@ -52,12 +52,21 @@ def sensitivity():
                   (name, mean_tps(cfg, n_draft=3, max_spec_runs=9), mean_tps(cfg, n_draft=5, max_spec_runs=9), mean_tps(cfg, mode="classic", n_draft=3)))
 
 
+SPLITS = {1: (0, 0), 2: (30 / 80, 50 / 80), 4: (15 / 80, 23 / 80), 8: (7 / 80, 13 / 80)}     # bench.py's default layer split: (head, tail) share
+
+
 def scaling():
+    """1, 2, 4, 8 stages with bench.py's layer split.  The draft shares GPU 0 with the first stage and has priority there: the
+    model brackets that with share_gpu0 = 1 (the target stands still while a draft decode runs) and 0 (no interference)."""
     for stages in (1, 2, 4, 8):
-        cfg = dict(n_stages=stages, stage_us=10320.0 / stages, stage_tok_us=480.0 / stages)
-        print("%d stage(s): measured %5.1f   model as measured %5.1f   after the fix %5.1f   classic %5.1f   plain %5.1f" %
-              (stages, MEASURED_N[stages], mean_tps(dict(cfg, **BEFORE_FIX), n_draft=3, max_spec_runs=stages + 1),
-               mean_tps(cfg, n_draft=3, max_spec_runs=stages + 1), mean_tps(cfg, mode="classic", n_draft=3), mean_tps(cfg, mode="plain")))
+        cfg = dict(n_stages=stages, stage_us=10320.0 / stages, stage_tok_us=480.0 / stages, head_frac=SPLITS[stages][0], tail_frac=SPLITS[stages][1])
+        band = lambda extra, **kw: "%5.1f..%5.1f" % tuple(mean_tps(dict(cfg, share_gpu0=sh, **extra), n_draft=3, max_spec_runs=stages + 1, **kw) for sh in (1.0, 0.0))
+        os.environ["PIB_SCHED_CHAIN"] = "0"
+        line = "%d stage(s): measured %5.1f   model as measured %s   after the host fix %s" % (stages, MEASURED_N[stages], band(BEFORE_FIX), band({}))
+        os.environ["PIB_SCHED_CHAIN"] = "2"
+        line += "   with policy 2 %s" % band({})
+        os.environ["PIB_SCHED_CHAIN"] = "0"
+        print(line)
 
 
 if __name__ == "__main__":

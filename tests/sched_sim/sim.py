@@ -18,8 +18,9 @@ class Config(C.Structure):
     _fields_ = [("n_stages", C.c_int32), ("stage_us", C.c_double), ("stage_tok_us", C.c_double), ("hop_us", C.c_double),
                 ("ret_us", C.c_double), ("skip_us", C.c_double), ("draft_us", C.c_double), ("draft_tok_us", C.c_double),
                 ("enqueue_us", C.c_double), ("call_us", C.c_double), ("agree", C.c_double), ("p_top", C.c_double),
-                ("p_second", C.c_double), ("jitter", C.c_double), ("share_gpu0", C.c_int32), ("n_vocab", C.c_int32),
-                ("seed", C.c_uint64), ("spec_issue_extra_us", C.c_double), ("nonspec_issue_extra_us", C.c_double)]
+                ("p_second", C.c_double), ("jitter", C.c_double), ("share_gpu0", C.c_double), ("n_vocab", C.c_int32),
+                ("seed", C.c_uint64), ("spec_issue_extra_us", C.c_double), ("nonspec_issue_extra_us", C.c_double),
+                ("head_frac", C.c_double), ("tail_frac", C.c_double)]
 
 
 class SpecParams(C.Structure):

@@ -50,15 +50,16 @@ struct sim_config {
     double  agree;               // probability that the draft's first candidate is the target's token
     double  p_top, p_second;     // probabilities the draft reports for its first / second candidate
     double  jitter;              // +- relative noise on every duration (deterministic in seed)
-    int32_t share_gpu0;          // draft decodes delay stage-0 work
+    double  share_gpu0;          // 0..1: how much of a draft decode's duration stage-0 work of the target loses (same GPU, the draft has priority)
     int32_t n_vocab;
     uint64_t seed;
     double  spec_issue_extra_us;     // extra host time to issue a speculative target run / a non-speculative one (the state of the
     double  nonspec_issue_extra_us;  // library BEFORE the host KV-mirror fix: ~900 and ~500 us)
+    double  head_frac, tail_frac;    // share of the target's layers on the first / last stage (0 = all stages equal); stage_us is the MEAN
 };
 // defaults: fitted to the 8-GPU runs of the 70B / 1.1B pair in profiles/ (plain 89, classic 182, PipeInfer 206 / 204 / 184 / 163
 // tok/s at --draft 3 / 2 / 5 / 8): the model lands within 10 % of each
-static const sim_config DEFAULTS = { 8, 1290, 60, 20, 30, 150, 710, 0, 150, 1.5, 0.8, 0.9, 0.05, 0, 0, 32000, 1, 0, 0 };
+static const sim_config DEFAULTS = { 8, 1290, 60, 20, 30, 150, 710, 0, 150, 1.5, 0.8, 0.9, 0.05, 0, 0.0, 32000, 1, 0, 0, 0, 0 };
 static sim_config G = DEFAULTS;
 static double g_now = 0;
 static uint64_t g_rng = 88172645463325252ull;
@@ -159,13 +160,17 @@ static void predict_rows(llama_context * c, const llama_batch & b, std::vector<s
 }
 
 // ---- the pipeline's timeline ---------------------------------------------------------------------------------------------
-static double run_on_gpu0(double start, double need) {      // stage-0 work that yields to the draft's intervals
-    if (!G.share_gpu0) return start + need;
+static double run_on_gpu0(double start, double need) {      // stage-0 work that yields (partly) to the draft's intervals
+    if (G.share_gpu0 <= 0) return start + need;
+    const double rate = std::max(0.0, 1.0 - G.share_gpu0);    // the target's speed while a draft decode runs on the same GPU
     double t = start;
     for (const auto & iv : g_draft_busy) {
         if (iv.second <= t) continue;
         if (iv.first >= t + need) break;
         if (iv.first > t) { need -= iv.first - t; t = iv.first; }
+        const double span = iv.second - t;
+        if (rate > 0 && need <= span * rate) return t + need / rate;
+        need -= span * rate;
         t = iv.second;
     }
     return t + need;
@@ -252,7 +257,15 @@ struct ggml_cgraph * llama_start_async_decode(struct llama_context & c, struct l
     run.t_issue = g_now;
     if (c.is_target) {
         run.dur.resize(G.n_stages);
-        for (int s = 0; s < G.n_stages; s++) run.dur[s] = (G.stage_us + G.stage_tok_us * b.n_tokens) * noise();
+        for (int s = 0; s < G.n_stages; s++) {
+            double w = 1.0;                                   // this stage's share of the layers, relative to an even split
+            if (G.n_stages > 1 && G.head_frac > 0) {
+                const double tail = G.tail_frac > 0 ? G.tail_frac : (1.0 - G.head_frac) / (G.n_stages - 1);
+                const double mid  = G.n_stages > 2 ? (1.0 - G.head_frac - tail) / (G.n_stages - 2) : 0.0;
+                w = (s == 0 ? G.head_frac : s == G.n_stages - 1 ? tail : mid) * G.n_stages;
+            }
+            run.dur[s] = (G.stage_us + G.stage_tok_us * b.n_tokens) * w * noise();
+        }
     } else {                                                    // the draft runs at once, on GPU 0, and the caller waits
         const double d = (G.draft_us + G.draft_tok_us * b.n_tokens) * noise(), t0 = std::max(g_now, c.draft_free);
         g_draft_busy.push_back({ t0, t0 + d });

@@ -29,7 +29,7 @@ static void apply_env_config() {
             const double v = atof(kv.c_str() + eq + 1);
 #define F(name) if (k == #name) cfg.name = (decltype(cfg.name)) v;
             F(n_stages) F(stage_us) F(stage_tok_us) F(hop_us) F(ret_us) F(skip_us) F(draft_us) F(draft_tok_us) F(enqueue_us) F(call_us)
-            F(agree) F(p_top) F(p_second) F(jitter) F(share_gpu0) F(n_vocab) F(seed) F(spec_issue_extra_us) F(nonspec_issue_extra_us)
+            F(agree) F(p_top) F(p_second) F(jitter) F(share_gpu0) F(n_vocab) F(seed) F(spec_issue_extra_us) F(nonspec_issue_extra_us) F(head_frac) F(tail_frac)
 #undef F
         }
         p = q + 1;
