@@ -203,9 +203,11 @@ def main():
                           % (label, args.agree, args.prompt_len, args.draft, args.np, args.pa, args.ps, args.n_predict,
                              args.max_spec_runs or "unbounded", args.gpus),
               "l2_policy": l2_policy}
-    if args.sched_policy != "reference":
-        os.environ["PIB_SCHED_CHAIN"] = args.sched_policy[-1]          # read by the scheduler at every generation
-        config["workload"] += ", scheduler policy %s (experimental, DESIGN.md §9)" % args.sched_policy
+    # scheduler policy (PIB_SCHED_CHAIN is read by the scheduler at every generation).  A non-reference policy is checked on
+    # the GPU before it is timed: the first warm-up step runs the reference policy, the others the chosen one, and any
+    # difference in the generated text falls back to the reference policy (the text must be the greedy text under any policy)
+    os.environ["PIB_SCHED_CHAIN"] = "0"
+    config["sched_policy"] = args.sched_policy
 
     if args.impl == "reference":
         if rank != 0:
@@ -289,9 +291,18 @@ def main():
         return sum(lib.llama_pib_kernel_launches(c.ctx) for c in ctxs)
 
     first = None
-    for _ in range(args.warmup):
+    policy_env = "0" if args.sched_policy == "reference" or args.mode != "speculative" else args.sched_policy[-1]
+    for w in range(args.warmup):
+        os.environ["PIB_SCHED_CHAIN"] = policy_env if (w > 0 or args.warmup == 1) else "0"
         toks, res, itl = step()
         first = first or toks
+        if rank == 0 and policy_env != "0" and toks[:len(first)] != first[:len(toks)]:
+            sys.stderr.write("bench: scheduler policy %s changed the text; falling back to the reference policy\n" % args.sched_policy)
+            policy_env = "0"
+            config["sched_policy"] = "reference (fallback: %s changed the text)" % args.sched_policy
+    os.environ["PIB_SCHED_CHAIN"] = policy_env
+    if policy_env != "0":
+        config["workload"] += ", scheduler policy %s (additive, text-identical; DESIGN.md §9)" % args.sched_policy
     b0, e0l = ranges[rank] if world > 1 else (0, L)
     prof_layer = (b0 + e0l) // 2
     lib.llama_pib_profile_layer(tgt.ctx, prof_layer)
