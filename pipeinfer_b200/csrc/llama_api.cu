@@ -159,6 +159,10 @@ int llama_pib_set_priority(struct llama_context * ctx, int high) {
     if (cudaStreamCreateWithPriority(&ns, cudaStreamNonBlocking, pr) != cudaSuccess) return -1;
     cudaStreamDestroy(c->stream);
     c->stream = ns;
+    // A/B switch for the draft's matmul kernel only (the context the scheduler marks high-priority): its matrices are small
+    // enough that the fixed cost of a launch, not bandwidth, sets the time; e.g. PIB_KEEP_PLANES=1 PIB_DRAFT_GEMV_VARIANT=1
+    const char * dv = high ? getenv("PIB_DRAFT_GEMV_VARIANT") : nullptr;
+    if (dv) c->gemv_variant = atoi(dv);
     return 0;
 }
 
