@@ -241,6 +241,14 @@ struct llama_context * llama_pib_new_context(struct llama_model * model, uint32_
  * or device replica (1) */
 int  llama_pib_kv_state(struct llama_context * ctx, int from_device, int32_t * scalars3, int32_t * pos, uint32_t * bits);
 int  llama_pib_kv_words(const struct llama_context * ctx);
+/* Ranged KV operations (no reference counterpart; the reference's scheduler loops over up to 3 000 sequence ids per operation,
+ * speculative.cpp:603-612, 1252-1268).  Same bookkeeping as the literal loops:
+ *   rm_range : for s in [first, last]: llama_kv_cache_seq_rm(ctx, s, p0, p1)
+ *   cp_range : for d in [dst_first, dst_last]: llama_kv_cache_seq_cp(ctx, src, d, p0, p1)
+ *   sweep    : for s in [first, last] (first >= 1): seq_rm(ctx, s, p0, p1); seq_cp(ctx, 0, s, p0, p1) */
+void llama_pib_kv_seq_rm_range(struct llama_context * ctx, llama_seq_id first, llama_seq_id last, llama_pos p0, llama_pos p1);
+void llama_pib_kv_seq_cp_range(struct llama_context * ctx, llama_seq_id src, llama_seq_id dst_first, llama_seq_id dst_last, llama_pos p0, llama_pos p1);
+void llama_pib_kv_seq_sweep(struct llama_context * ctx, llama_seq_id first, llama_seq_id last, llama_pos p0, llama_pos p1);
 uint64_t llama_pib_kernel_launches(const struct llama_context * ctx);
 size_t   llama_pib_weight_bytes(const struct llama_model * model);
 /* measurement hooks used by bench.py: host<->device bytes issued so far; CUDA-event timing of every matmul launch of

@@ -421,6 +421,19 @@ void kvlog_push(std::vector<KvOp> & q, const KvOp & op_in) {
     q.push_back(op);
 }
 
+// the ranged records the coalescing above arrives at, pushed directly: what the scheduler's per-id loops (3 000 ids, 12 000 calls
+// per accepted run) collapse to anyway.  kind = KVOP_RM: sequences [a, b]; KVOP_CP: a -> [b, c] (a outside [b, c]); KVOP_SWEEP: [a, b], a >= 1.
+void kvlog_push_ranged(std::vector<KvOp> & q, int kind, int32_t a, int32_t b, int32_t c, int32_t p0, int32_t p1) {
+    if (a > b && kind != KVOP_CP) return;
+    if (kind == KVOP_CP && b > c) return;
+    if (kind == KVOP_CP && a >= b && a <= c) {               // the source inside the destinations: the literal loop skips src == dst
+        if (a > b) kvlog_push_ranged(q, kind, a, b, a - 1, p0, p1);
+        if (a < c) kvlog_push_ranged(q, kind, a, a + 1, c, p0, p1);
+        return;
+    }
+    q.push_back({ kind, a, b, p0, p1, kind == KVOP_CP ? c : 0 });
+}
+
 void kvlog_flush(KvMirror & kv, std::vector<KvOp> & pending, std::vector<KvOp> & devops) {
     for (const KvOp & op : pending) {
         switch (op.op) {

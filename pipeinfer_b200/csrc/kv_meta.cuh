@@ -84,6 +84,7 @@ int kv_device_mask(const KvDevice * kv, const int32_t * tpos_dev, const uint32_t
 
 // op-log front end (kv_meta.cu)
 void kvlog_push(std::vector<KvOp> & pending, const KvOp & op);
+void kvlog_push_ranged(std::vector<KvOp> & pending, int kind, int32_t a, int32_t b, int32_t c, int32_t p0, int32_t p1);
 void kvlog_flush(KvMirror & kv, std::vector<KvOp> & pending, std::vector<KvOp> & devops);
 bool kvlog_decode_begin(KvMirror & kv, std::vector<KvOp> & devops, int n_tokens, const int32_t * pos, const uint32_t * tokbits);
 void kvlog_decode_end(KvMirror & kv, int n_tokens);

@@ -402,9 +402,20 @@ void llama_kv_cache_seq_rm(struct llama_context * ctx, llama_seq_id seq_id, llam
     pib_kv_push(ctx->c, { KVOP_RM, seq_id, 0, p0, p1, 0 });
 }
 void llama_kv_cache_seq_cp(struct llama_context * ctx, llama_seq_id src, llama_seq_id dst, llama_pos p0, llama_pos p1) {
+    if (src == dst) return;                    // the reference's wrapper returns before touching the cache (llama.cpp:9303-9305): head keeps its value
     pib_kv_push(ctx->c, { KVOP_CP, src, dst, p0, p1, 0 });
 }
 void llama_kv_cache_seq_keep(struct llama_context * ctx, llama_seq_id seq_id) { pib_kv_push(ctx->c, { KVOP_KEEP, seq_id, 0, 0, 0, 0 }); }
+// ranged forms (extension): exactly what the per-id loops of the scheduler collapse to in the op-log, without the 12 000 calls
+void llama_pib_kv_seq_rm_range(struct llama_context * ctx, llama_seq_id first, llama_seq_id last, llama_pos p0, llama_pos p1) {
+    kvlog_push_ranged(ctx->c->pending, KVOP_RM, first, last, 0, p0, p1);
+}
+void llama_pib_kv_seq_cp_range(struct llama_context * ctx, llama_seq_id src, llama_seq_id dst_first, llama_seq_id dst_last, llama_pos p0, llama_pos p1) {
+    kvlog_push_ranged(ctx->c->pending, KVOP_CP, src, dst_first, dst_last, p0, p1);
+}
+void llama_pib_kv_seq_sweep(struct llama_context * ctx, llama_seq_id first, llama_seq_id last, llama_pos p0, llama_pos p1) {
+    kvlog_push_ranged(ctx->c->pending, KVOP_SWEEP, first, last, 0, p0, p1);
+}
 
 int llama_get_kv_cache_used_cells(const struct llama_context * ctx) {
     pib_kv_flush_host(ctx->c);

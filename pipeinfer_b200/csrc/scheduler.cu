@@ -184,13 +184,13 @@ void Scheduler::begin_async_run(llama_context * ctx, std::deque<Run> & q, const 
     run.drafts = dr;
     run.n_past_tgt = n_past; run.prefix_n_past_tgt = prefix_n_past; run.n_past_max = n_past_max; run.n_past_dft = n_past_dft_arg;
     run.speculative = is_spec;
-    if (!is_spec) { for (int i = 0; i <= max_seq; i++) llama_kv_cache_seq_rm(ctx, i, n_past, n_past + 1); }        // :1252-1255
+    if (!is_spec) llama_pib_kv_seq_rm_range(ctx, 0, max_seq, n_past, n_past + 1);     // :1252-1255, for i in 0..max_seq: seq_rm(i, ...)
     else          { for (int i = 0; i < np; i++) llama_kv_cache_seq_rm(ctx, i + seq_offset, n_past, n_past + 1); } // :1256-1260
     run.handle = llama_start_async_decode(*ctx, run.batch.view(max_seq + 1));                                      // :1261
     if (ctx == ctx_tgt) ev(is_spec ? "start_spec" : "start_nonspec", batch_id, (int) run.batch.size(), n_past);
     if (!run.handle) failed = true;     // no KV slot left: the reference would spin forever here
     q.push_front(std::move(run));
-    if (!is_spec) for (int i = 1; i <= max_seq; i++) llama_kv_cache_seq_cp(ctx, 0, i, n_past, n_past + 1);         // :1264-1268
+    if (!is_spec) llama_pib_kv_seq_cp_range(ctx, 0, 1, max_seq, n_past, n_past + 1);  // :1264-1268, for i in 1..max_seq: seq_cp(0, i, ...)
 }
 
 // :850-879
@@ -491,16 +491,9 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
             llama_kv_cache_seq_rm(ctx_dft, 0, c0_dft, n_past_dft);
             llama_kv_cache_seq_cp(ctx_tgt, s_keep + current.seq_offset, 0, c0_tgt, n_past_tgt);
             llama_kv_cache_seq_cp(ctx_dft, s_keep + current.seq_offset, 0, c0_dft, n_past_dft);
-            // the reference interleaves the two contexts inside one loop; the contexts are independent, so two loops
-            // give the same per-context call order (and let the op-log collapse each into one KVOP_SWEEP)
-            for (int i = 1; i <= max_seq; i++) {
-                llama_kv_cache_seq_rm(ctx_tgt, i, c0_tgt, n_past_tgt);
-                llama_kv_cache_seq_cp(ctx_tgt, 0, i, c0_tgt, n_past_tgt);
-            }
-            for (int i = 1; i <= max_seq; i++) {
-                llama_kv_cache_seq_rm(ctx_dft, i, c0_dft, n_past_dft);
-                llama_kv_cache_seq_cp(ctx_dft, 0, i, c0_dft, n_past_dft);
-            }
+            // :603-612, for i in 1..max_seq: seq_rm(i, range); seq_cp(0, i, range) on both contexts -- one ranged record each
+            llama_pib_kv_seq_sweep(ctx_tgt, 1, max_seq, c0_tgt, n_past_tgt);
+            llama_pib_kv_seq_sweep(ctx_dft, 1, max_seq, c0_dft, n_past_dft);
         }
         if (chain_policy >= 2 && chain_alive() && next_link_starts_with(id)) {
             // the next link in flight begins with `id` at this very position: no run of its own for it, on either model

@@ -244,8 +244,12 @@ int  llama_pib_kv_words(const struct llama_context * ctx) { return ctx->kv.n_wor
 void llama_pib_set_logit_bias(struct llama_context *, const llama_token *, const float *, int) { g_now += G.call_us; }
 
 void llama_kv_cache_seq_rm(struct llama_context * ctx, llama_seq_id seq, llama_pos p0, llama_pos p1) { kvlog_push(ctx->pending, { KVOP_RM, seq, 0, p0, p1, 0 }); g_now += G.call_us * 0.02; }
-void llama_kv_cache_seq_cp(struct llama_context * ctx, llama_seq_id src, llama_seq_id dst, llama_pos p0, llama_pos p1) { kvlog_push(ctx->pending, { KVOP_CP, src, dst, p0, p1, 0 }); g_now += G.call_us * 0.02; }
+void llama_kv_cache_seq_cp(struct llama_context * ctx, llama_seq_id src, llama_seq_id dst, llama_pos p0, llama_pos p1) { if (src == dst) return; kvlog_push(ctx->pending, { KVOP_CP, src, dst, p0, p1, 0 }); g_now += G.call_us * 0.02; }
 void llama_kv_cache_seq_keep(struct llama_context * ctx, llama_seq_id seq) { kvlog_push(ctx->pending, { KVOP_KEEP, seq, 0, 0, 0, 0 }); g_now += G.call_us * 0.02; }
+
+void llama_pib_kv_seq_rm_range(struct llama_context * ctx, llama_seq_id first, llama_seq_id last, llama_pos p0, llama_pos p1) { kvlog_push_ranged(ctx->pending, KVOP_RM, first, last, 0, p0, p1); g_now += G.call_us * 0.02; }
+void llama_pib_kv_seq_cp_range(struct llama_context * ctx, llama_seq_id src, llama_seq_id d0, llama_seq_id d1, llama_pos p0, llama_pos p1) { kvlog_push_ranged(ctx->pending, KVOP_CP, src, d0, d1, p0, p1); g_now += G.call_us * 0.02; }
+void llama_pib_kv_seq_sweep(struct llama_context * ctx, llama_seq_id first, llama_seq_id last, llama_pos p0, llama_pos p1) { kvlog_push_ranged(ctx->pending, KVOP_SWEEP, first, last, 0, p0, p1); g_now += G.call_us * 0.02; }
 
 struct ggml_cgraph * llama_start_async_decode(struct llama_context & c, struct llama_batch b) {
     g_now += G.enqueue_us * noise();

@@ -49,13 +49,15 @@ def test_random_timings_flags_and_agreement(block, chain, monkeypatch):
         check(sim.run(cfg, **kw), 96)
 
 
-HAZARD_CASES = [
+HAZARD_CASES = [      # every timing field is given and API calls cost no virtual time: the interleaving does not depend on the defaults
     # a perfect draft whose runs get overtaken: stale runs stopped on the GPUs leave garbage KV behind for the run chained behind them
-    (dict(n_stages=4, jitter=0, agree=1.0, p_top=0.6, p_second=0.3, share_gpu0=1, seed=17, draft_us=800, stage_us=200, skip_us=5),
-     dict(n_draft=3, n_parallel=1, p_accept=0.1, p_split=0.2, p_recovery=0.05, p_decay=0.0, max_spec_runs=9, n_predict=96, n_ctx=4096, prompt_seed=17)),
-    # a poor, fast draft: a chained run is handed the partition of its cancelled predecessor and copies it onto itself
-    (dict(n_stages=8, jitter=0, agree=0.3, p_top=0.6, p_second=0.3, share_gpu0=1, seed=524, draft_us=100, stage_us=1350, skip_us=5),
-     dict(n_draft=2, n_parallel=1, p_accept=0.1, p_split=0.2, p_recovery=0.05, p_decay=0.1, max_spec_runs=0, n_predict=96, n_ctx=4096, prompt_seed=24)),
+    ({'n_stages': 8, 'agree': 1.0, 'p_top': 0.6, 'p_second': 0.3, 'jitter': 0, 'seed': 50, 'draft_us': 100, 'stage_us': 1350, 'skip_us': 150, 'call_us': 0,
+      'enqueue_us': 60, 'draft_tok_us': 0, 'stage_tok_us': 50, 'hop_us': 20, 'ret_us': 30},
+     {'n_draft': 3, 'n_parallel': 1, 'p_accept': 0.5, 'p_split': 0.9, 'p_recovery': 0.0, 'p_decay': 0.1, 'max_spec_runs': 0, 'n_predict': 96, 'n_ctx': 4096, 'prompt_seed': 50}),
+    # a poor, fast draft and nothing bounding the runs in flight
+    ({'n_stages': 8, 'agree': 0.6, 'p_top': 0.6, 'p_second': 0.3, 'jitter': 0, 'seed': 49, 'draft_us': 100, 'stage_us': 1350, 'skip_us': 150, 'call_us': 0,
+      'enqueue_us': 60, 'draft_tok_us': 0, 'stage_tok_us': 50, 'hop_us': 20, 'ret_us': 30},
+     {'n_draft': 2, 'n_parallel': 1, 'p_accept': 0.1, 'p_split': 0.2, 'p_recovery': 0.05, 'p_decay': 0.0, 'max_spec_runs': 0, 'n_predict': 96, 'n_ctx': 4096, 'prompt_seed': 49}),
 ]
 
 
@@ -65,7 +67,6 @@ def test_the_two_reference_behaviours_that_corrupt_context_are_fixed(case, monke
     runs on the GPUs, :1344-1356; re-seeds a partition from itself, :891-905) and an accepted row has attended to garbage or
     to a context with a hole: the text is not the greedy text.  The default avoids both."""
     c, kw = HAZARD_CASES[case]
-    c = dict(c, hop_us=20, ret_us=30, stage_tok_us=50, draft_tok_us=50, enqueue_us=60, call_us=0.3)     # pins the interleaving
     monkeypatch.setenv("PIB_REFERENCE_HAZARDS", "1")
     r = sim.run(sim.default_config(**c), **kw)
     assert r["tokens"] != r["truth"]
