@@ -480,6 +480,14 @@ extern "C" void * pib_kvtest_new(uint32_t n_ctx, int32_t max_seq) {
 extern "C" void pib_kvtest_free(void * h) { delete (pib_kvtest *) h; }
 extern "C" void pib_kvtest_op(void * h, int op, int a, int b, int p0, int p1) { kvlog_push(((pib_kvtest *) h)->pending, { op, a, b, p0, p1, 0 }); }
 extern "C" int pib_kvtest_pending(void * h) { return (int) ((pib_kvtest *) h)->pending.size(); }
+extern "C" void pib_kvtest_op_ranged(void * h, int kind, int a, int b, int c, int p0, int p1) { kvlog_push_ranged(((pib_kvtest *) h)->pending, kind, a, b, c, p0, p1); }
+// the pending (not yet flushed) records, 6 int32 each: op, a, b, p0, p1, pad
+extern "C" int pib_kvtest_dump_pending(void * h, int32_t * out, int cap_records) {
+    const std::vector<KvOp> & q = ((pib_kvtest *) h)->pending;
+    const int n = (int) q.size() < cap_records ? (int) q.size() : cap_records;
+    memcpy(out, q.data(), sizeof(KvOp) * (size_t) n);
+    return (int) q.size();
+}
 extern "C" int pib_kvtest_decode(void * h, int n_tokens, const int32_t * pos, const int32_t * n_seq_id, const int32_t * const * seq_id) {
     pib_kvtest * t = (pib_kvtest *) h;
     kvlog_flush(t->kv, t->pending, t->devops);

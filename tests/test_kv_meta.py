@@ -183,3 +183,50 @@ def test_random_long_traces_match_the_oracle_cell_for_cell(oracle, seed):
             check()
     check()
     oracle.L.po_kv_free(okv)
+
+
+def test_ranged_operations_are_the_records_the_literal_loops_collapse_to():
+    """llama_pib_kv_seq_rm_range / _cp_range / _sweep (what the scheduler issues) against the per-id loops of the reference's
+    scheduler (speculative.cpp:603-612, 1252-1268) pushed one call at a time: identical op-log records, hence identical
+    bookkeeping on the host mirror and on every device replica"""
+    L = C.CDLL(SO)
+    L.pib_kvtest_new.restype = C.c_void_p
+    L.pib_kvtest_new.argtypes = [C.c_uint32, C.c_int32]
+    L.pib_kvtest_op.argtypes = [C.c_void_p] + [C.c_int] * 5
+    L.pib_kvtest_op_ranged.argtypes = [C.c_void_p] + [C.c_int] * 6
+    L.pib_kvtest_dump_pending.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    L.pib_kvtest_free.argtypes = [C.c_void_p]
+    max_seq, n_past, c0 = 3001, 77, 71
+    lit, rng = L.pib_kvtest_new(256, max_seq + 1), L.pib_kvtest_new(256, max_seq + 1)
+
+    def pending(h):
+        out = np.zeros((64, 6), dtype=np.int32)
+        n = L.pib_kvtest_dump_pending(h, out.ctypes.data, 64)
+        return out[:n].tolist()
+
+    # commit of an accepted speculative run
+    for h in (lit, rng):
+        L.pib_kvtest_op(h, KVOP_RM, 0, 0, c0, n_past)
+        L.pib_kvtest_op(h, KVOP_CP, 1005, 0, c0, n_past)
+    for i in range(1, max_seq + 1):
+        L.pib_kvtest_op(lit, KVOP_RM, i, 0, c0, n_past)
+        L.pib_kvtest_op(lit, KVOP_CP, 0, i, c0, n_past)
+    L.pib_kvtest_op_ranged(rng, 7, 1, max_seq, 0, c0, n_past)                  # KVOP_SWEEP
+    # the non-speculative run that follows: remove the position from every sequence, (decode,) copy it to every sequence
+    for i in range(0, max_seq + 1):
+        L.pib_kvtest_op(lit, KVOP_RM, i, 0, n_past, n_past + 1)
+    L.pib_kvtest_op_ranged(rng, KVOP_RM, 0, max_seq, 0, n_past, n_past + 1)
+    a, b = pending(lit), pending(rng)
+    assert a == b and len(a) == 4, (a, b)
+    for h in (lit, rng):
+        L.pib_kvtest_free(h)
+    lit, rng = L.pib_kvtest_new(256, max_seq + 1), L.pib_kvtest_new(256, max_seq + 1)
+    for i in range(1, max_seq + 1):
+        L.pib_kvtest_op(lit, KVOP_CP, 0, i, n_past, n_past + 1)
+    L.pib_kvtest_op_ranged(rng, KVOP_CP, 0, 1, max_seq, n_past, n_past + 1)
+    assert pending(lit) == pending(rng) and len(pending(rng)) == 1
+    # a source inside the destination range: the literal loop skips src == dst (llama.cpp:9303-9305)
+    L.pib_kvtest_op_ranged(rng, KVOP_CP, 5, 3, 8, 0, 10)
+    assert [r[:3] + [r[5]] for r in pending(rng)[1:]] == [[KVOP_CP, 5, 3, 4], [KVOP_CP, 5, 6, 8]]
+    for h in (lit, rng):
+        L.pib_kvtest_free(h)
