@@ -98,6 +98,9 @@ int pib_gemv(const pib_weight * w, const void * act_dev, int b, float * y_dev, i
 #define PIB_GEMV_NOALLOC_SCRATCH_BYTES (2u * 1024u * 1024u)
 #define PIB_MAX_DEV_NOALLOC 64
 int pib_gemv_q4k_noalloc(const pib_weight * w, const void * act_dev, int b, float * y_dev, pib_stream s);
+/* Number of K splits pib_gemv_q4k_noalloc uses for an N x K matrix on the current device (1 = no scratch touched); lets a
+ * caller -- and the tests -- see which shapes go through the built-in array.  No counterpart in the reference. */
+int pib_gemv_direct_splits(int64_t N, int64_t K);
 /* Host-buffer convenience used by the parity tests and the end-to-end timing: x_host float [b][K] -> y_host [b][N];
  * includes the H2D copy of x, quantisation, GEMV and the D2H copy of y. */
 int pib_mul_mat_host(const pib_weight * w, const float * x_host, int b, float * y_host, int variant);

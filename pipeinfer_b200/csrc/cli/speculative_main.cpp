@@ -128,7 +128,7 @@ int main(int argc, char ** argv) {
     if (n_inp > n_ctx - 4) { fprintf(stderr, "speculative: the prompt exceeds the context size\n"); return 1; }   // :212-216
     fprintf(stderr, "\n\n");
     char piece[256];
-    for (llama_token t : inp) { const int n = llama_token_to_piece(m_tgt, t, piece, sizeof(piece)); fprintf(stderr, "%.*s", n, piece); }
+    for (llama_token t : inp) { const int n = llama_token_to_piece(m_tgt, t, piece, sizeof(piece)); if (n > 0) fprintf(stderr, "%.*s", n, piece); }
     fflush(stderr);
 
     std::vector<llama_token> out((size_t) n_predict + 64);
@@ -136,7 +136,10 @@ int main(int argc, char ** argv) {
     pib_spec_result          res;
     const int n_out = pib_speculative_generate(c_tgt, c_dft, inp.data(), n_inp, &P, out.data(), (int) out.size(), &res, itl.data(), (int) itl.size());
     if (n_out < 0) { fprintf(stderr, "speculative: %s\n", pib_last_error()); return 1; }
-    for (int i = 0; i < n_out; i++) { const int n = llama_token_to_piece(m_tgt, out[i], piece, sizeof(piece)); fwrite(piece, 1, (size_t) n, stdout); }
+    for (int i = 0; i < n_out && i < (int) out.size(); i++) {
+        const int n = llama_token_to_piece(m_tgt, out[i], piece, sizeof(piece));     // < 0: the piece does not fit (never with 256 bytes)
+        if (n > 0) fwrite(piece, 1, (size_t) n, stdout);
+    }
     fflush(stdout);
 
     const double encode_speed = res.t_encode_s > 0 ? n_inp / res.t_encode_s : 0.0;

@@ -396,6 +396,7 @@ pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_st
     CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CK(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, lo));
     CK(cudaStreamCreateWithPriority(&c->ctrl, cudaStreamNonBlocking, hi));
+    CK(cudaEventCreateWithFlags(&c->cancel_ev, cudaEventDisableTiming));
     c->kv.init(n_ctx, c->max_seq);
     if (kv_device_init(&c->kvd, n_ctx, c->n_words) != PIB_OK) goto fail;
     CK(cudaMalloc(&c->kcache, kvb ? kvb : 16));
@@ -459,6 +460,7 @@ void pib_context_free(pib_context * c) {
         if (r.res_host) cudaFreeHost(r.res_host);
     }
     for (auto e : c->desc_ev) if (e) cudaEventDestroy(e);
+    if (c->cancel_ev) cudaEventDestroy(c->cancel_ev);
     for (auto & g : c->graphs) if (g.second.exec) cudaGraphExecDestroy(g.second.exec);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->ctrl) cudaStreamDestroy(c->ctrl);
@@ -859,11 +861,18 @@ int pib_decode_replay(pib_context * c, int batch_id, int n_tokens, int n_chunks,
     return enqueue_decode(c, run, n_tokens, batch_id, slots) >= 0 ? PIB_OK : PIB_ERR_CUDA;
 }
 
+// Clear a run slot's cancel flag in stream order after the run's last kernel -- and after any cancel write still travelling on the
+// control stream: without the event a late cancel copy could land after the clear and poison the slot's next run.
+static void clear_cancel_flag(pib_context * c, int slot) {
+    if (c->cancel_ev_pending) { cudaStreamWaitEvent(c->stream, c->cancel_ev, 0); c->cancel_ev_pending = false; }
+    cudaMemsetAsync(c->cancel_table + 1 + slot, 0, sizeof(int), c->stream);
+}
+
 void pib_stage_finish(pib_context * c, int batch_id) {
     for (auto it = c->inflight.begin(); it != c->inflight.end(); ++it) {
         pib_run & r = c->runs[*it];
         if (r.in_use && r.batch_id == batch_id) {
-            cudaMemsetAsync(c->cancel_table + 1 + r.id, 0, sizeof(int), c->stream);
+            clear_cancel_flag(c, r.id);
             r.in_use = false;
             c->last_finished = r.id;     // its logits stay reserved until the next finish, as on the head (llama_get_logits_ith)
             c->inflight.erase(it);
@@ -882,7 +891,7 @@ int pib_run_finish(pib_context * c, int run) {
     pib_run & r = c->runs[run];
     if (cudaEventSynchronize(r.done) != cudaSuccess) { pib_set_error("finish: %s", cudaGetErrorString(cudaGetLastError())); return -1; }
     // the run slot may be reused from here on: drop its cancel flag (ordered after every kernel of the run)
-    cudaMemsetAsync(c->cancel_table + 1 + r.id, 0, sizeof(int), c->stream);
+    clear_cancel_flag(c, r.id);
     if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_ints(2, 0, &r.batch_id, 1);
     for (auto it = c->inflight.begin(); it != c->inflight.end(); ++it) if (*it == run) { c->inflight.erase(it); break; }
     r.in_use         = false;
@@ -919,12 +928,16 @@ const float * pib_logits_row(pib_context * c, int i) {
 void pib_cancel(pib_context * c, const int32_t * batch_ids, int n) {
     // one cancel word per run slot (fixed addresses, so that captured graphs of a slot stay valid); the word is cleared when
     // the run is finished, in stream order after its last kernel
+    bool wrote = false;
     for (int i = 0; i < n; i++)
         for (int id : c->inflight) {
             pib_run & r = c->runs[id];
-            if (r.in_use && r.batch_id == batch_ids[i])
+            if (r.in_use && r.batch_id == batch_ids[i]) {
                 cudaMemcpyAsync(c->cancel_table + 1 + r.id, c->cancel_one, sizeof(int), cudaMemcpyDeviceToDevice, c->ctrl);
+                wrote = true;
+            }
         }
+    if (wrote) { cudaEventRecord(c->cancel_ev, c->ctrl); c->cancel_ev_pending = true; }
     if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_ints(3, 0, batch_ids, n);
 }
 
@@ -937,9 +950,12 @@ void pib_set_logit_bias(pib_context * c, const int32_t * ids, const float * vals
     if (c->bias_val_dev) cudaFree(c->bias_val_dev);
     c->bias_ids_dev = nullptr; c->bias_val_dev = nullptr; c->n_bias = 0;
     if (n <= 0) return;
-    cudaMalloc(&c->bias_ids_dev, sizeof(int32_t) * n);
-    cudaMalloc(&c->bias_val_dev, sizeof(float) * n);
-    cudaMemcpy(c->bias_ids_dev, ids, sizeof(int32_t) * n, cudaMemcpyHostToDevice);
-    cudaMemcpy(c->bias_val_dev, vals, sizeof(float) * n, cudaMemcpyHostToDevice);
+    if (cudaMalloc(&c->bias_ids_dev, sizeof(int32_t) * n) != cudaSuccess || cudaMalloc(&c->bias_val_dev, sizeof(float) * n) != cudaSuccess ||
+        cudaMemcpy(c->bias_ids_dev, ids, sizeof(int32_t) * n, cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemcpy(c->bias_val_dev, vals, sizeof(float) * n, cudaMemcpyHostToDevice) != cudaSuccess) {
+        // greedy output with the bias silently dropped would be wrong (e.g. --ignore-eos): fail loudly, as the reference's GGML_ASSERTs do
+        fprintf(stderr, "pib_set_logit_bias: %s\n", cudaGetErrorString(cudaGetLastError()));
+        abort();
+    }
     c->n_bias = n;
 }

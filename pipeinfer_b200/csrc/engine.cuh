@@ -105,6 +105,8 @@ struct pib_context {
     int *    cancel_table = nullptr;       // device cancellation block: see PIB_CANCELLED (pib_common.cuh)
     int *    run_id_host  = nullptr;       // pinned {0, 1, ..., 63}: sources of the current-run writes
     int *    cancel_one   = nullptr;       // device int {1}: source of the cancel writes
+    cudaEvent_t cancel_ev = nullptr;       // recorded on `ctrl` after every cancel write: the clearing memset on `stream` waits for it
+    bool     cancel_ev_pending = false;
 
     // host->device staging rings (pinned host + device copies)
     uint8_t * desc_host = nullptr, * desc_dev = nullptr;

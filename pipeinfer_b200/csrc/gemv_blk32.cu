@@ -100,7 +100,13 @@ __global__ void __launch_bounds__(BK_THREADS, NT == 1 ? 4 : 3)
 gemv_blk32_kernel(const uint8_t * __restrict__ tiles, int ngr, int N, const int8_t * __restrict__ aqs, const __half * __restrict__ adx,
                   int b, float * __restrict__ y, float * __restrict__ partial, unsigned int * __restrict__ counters,
                   const int * __restrict__ cancel) {
-    if (PIB_CANCELLED(cancel)) { pib_pdl_wait(); return; }
+    if (PIB_CANCELLED(cancel)) {
+        pib_pdl_wait();
+        // cancelled: no math, but the arrival protocol of the k split still runs -- the flag can flip while the grid is starting,
+        // and a tile whose splits did not all arrive would leave its counter non-zero for the next launch
+        if (gridDim.y > 1 && threadIdx.x == 0 && atomicAdd(&counters[blockIdx.x], 1u) == gridDim.y - 1) counters[blockIdx.x] = 0;
+        return;
+    }
     constexpr int REC = WT == PIB_TYPE_Q4_0 ? 2304 : 4352;
     constexpr int NQ  = WT == PIB_TYPE_Q4_0 ? 4 : 8;            // 128-bit quant loads per lane and record
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;

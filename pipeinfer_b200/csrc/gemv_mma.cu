@@ -146,7 +146,16 @@ gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int n_tiles, in
                     const int8_t * __restrict__ aqs, const float * __restrict__ ad, const int8_t * __restrict__ abs8, int b,
                     float * __restrict__ y, float * __restrict__ partial, unsigned int * __restrict__ counters,
                     const int * __restrict__ cancel) {
-    if (PIB_CANCELLED(cancel)) return;
+    if (PIB_CANCELLED(cancel)) {
+        // A cancelled warp skips the math but still arrives for every item it owns: the flag can flip while the grid is
+        // starting, and a tile whose splits did not all arrive would leave its counter non-zero for the next launch.
+        if (lg_split > 0 && (threadIdx.x & 31) == 0) {
+            const unsigned nsp = 1u << lg_split;
+            for (int item = (int) blockIdx.x * MM_WARPS + (int) (threadIdx.x >> 5); item < (n_tiles << lg_split); item += (int) gridDim.x * MM_WARPS)
+                if (atomicAdd(&counters[item >> lg_split], 1u) == nsp - 1) counters[item >> lg_split] = 0;
+        }
+        return;
+    }
     extern __shared__ __align__(128) uint8_t dsm[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
     uint8_t *      ring = dsm + (size_t) warp * MM_STAGES * MM_STAGE_BYTES;
@@ -346,7 +355,12 @@ __global__ void __launch_bounds__(MM_THREADS, NT == 1 ? 4 : 3)
 gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, const int8_t * __restrict__ aqs,
                        const float * __restrict__ ad, const int8_t * __restrict__ abs8, int b, float * __restrict__ y,
                        float * __restrict__ partial, unsigned int * __restrict__ counters, const int * __restrict__ cancel) {
-    if (PIB_CANCELLED(cancel)) { pib_pdl_wait(); return; }
+    if (PIB_CANCELLED(cancel)) {
+        pib_pdl_wait();
+        // cancelled: no math, but the arrival protocol of the k split still runs (see the persistent kernel above)
+        if (gridDim.y > 1 && threadIdx.x == 0 && atomicAdd(&counters[blockIdx.x], 1u) == gridDim.y - 1) counters[blockIdx.x] = 0;
+        return;
+    }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
     const int T = blockIdx.x;
     const int nsplit = gridDim.y, split = blockIdx.y;
@@ -564,6 +578,11 @@ static int choose_split_direct(int n_tiles, int nsb) {
     int split = 1;
     while (n_tiles * split < target && split * 2 * MM_WARPS <= nsb && split < 16) split *= 2;
     return split;
+}
+
+extern "C" int pib_gemv_direct_splits(int64_t N, int64_t K) {
+    if (N <= 0 || K <= 0 || K % 256) return -1;
+    return choose_split_direct((int) ((N + 15) / 16), (int) (K / 256));
 }
 
 int pib_gemv_direct_launch(const pib_weight * w, const void * act_dev, int b, float * y_dev, int split, float * partial,

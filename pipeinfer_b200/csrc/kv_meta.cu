@@ -431,6 +431,14 @@ void kvlog_push_ranged(std::vector<KvOp> & q, int kind, int32_t a, int32_t b, in
         if (a < c) kvlog_push_ranged(q, kind, a, a + 1, c, p0, p1);
         return;
     }
+    if (kind == KVOP_SWEEP && a < 1) {
+        // the closed form of the sweep (host mirror and device kernel alike) assumes sequence 0 is the untouched source; ids
+        // below 1 take the literal per-id records instead, so that the mirror and the device replica cannot diverge
+        // (negative ids name no sequence; for id 0 the literal loop is seq_rm(0) followed by a copy onto itself, a no-op)
+        if (b >= 0) q.push_back({ KVOP_RM, 0, 0, p0, p1, 0 });
+        if (b < 1) return;
+        a = 1;
+    }
     q.push_back({ kind, a, b, p0, p1, kind == KVOP_CP ? c : 0 });
 }
 

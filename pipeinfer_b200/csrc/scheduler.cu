@@ -558,7 +558,7 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
         res->itl_p50_s = srt.empty() ? 0 : srt[srt.size() / 2] / 1e6;
     }
     for (int i = 0; i < (int) itl.size() && i < itl_cap; i++) itl_us[i] = (double) itl[i];
-    return n_out;
+    return std::min(n_out, out_cap);          // never more than was written (a run may accept past n_predict)
 }
 
 }   // namespace

@@ -1,9 +1,15 @@
 """GPU: the llama.h-compatible ABI (llama_decode, llama_kv_cache_seq_*, async decode, cancel) of libpipeinfer_b200.so
 against the reference's own llama_decode outputs (tests/golden/decode_*.logits.bin, *.kv.txt) and the oracle.
-Logits: north_star tolerance is 1e-2 max-abs; we assert 2e-3 and report the real figure.  KV bookkeeping: bit-exact,
-for the host mirror AND the device replica."""
+Logits: north_star's bound is 1e-2 max-abs.  It is asserted as such on the config-1 model at its real shape
+(test_config1_real_shape_trace) and on the fixtures with the benchmark's attention shapes; the 256-wide toy fixtures keep
+a wider envelope (LOGIT_TOL_FLIP) because one activation-rounding flip moves a logit further on a model that narrow,
+with the median still held to 1e-4.  KV bookkeeping: bit-exact, for the host mirror AND the device replica."""
 import ctypes as C
+import hashlib
+import json
 import os
+import subprocess
+import sys
 
 import numpy as np
 import pytest
@@ -53,8 +59,7 @@ def test_decode_trace_vs_reference(llama, golden_dir, q):
     n_dec, n_kv = replay(golden_dir, "decode_%s" % q, ctx.decode, ctx.seq_rm, ctx.seq_cp, ctx.seq_keep, cells, check)
     # The reference's arithmetic is discontinuous (int8 activation rounding, fp16 rounding of Q/K/V/P): a 1e-7 relative
     # difference in fp32 summation order occasionally flips one rounding, which moves a logit by ~1e-2 on these tiny
-    # models (the same happens between the reference's own AVX2 and scalar builds).  Typical decodes agree to ~1e-6;
-    # every decode must stay inside the flip envelope.
+    # models.  Typical decodes agree to ~1e-6; every decode must stay inside the flip envelope.
     print("max|logit - reference| per decode (%s): %s" % (q, " ".join("%.2g" % e for e in errs)))
     assert n_dec == 8 and max(errs) < LOGIT_TOL_FLIP
     if q == "falcon_q4_0":
@@ -69,6 +74,72 @@ def test_decode_trace_vs_reference(llama, golden_dir, q):
     else:
         assert np.median(errs) < LOGIT_TOL_TYPICAL
     ctx.close()
+
+
+def _replay_checked(llama, golden_dir, model_path, stem, n_ctx, max_seq):
+    """replay a reference trace; returns (per-decode max error, per-row max error, rows whose argmax is a logged near tie)"""
+    ctx = llama.Context(model_path, n_ctx=n_ctx, max_seq=max_seq)
+    errs, rows, ties = [], [], []
+
+    def check(got, ref):
+        d = np.abs(got - ref)
+        errs.append(float(d.max()))
+        rows.extend(d.max(1).tolist())
+        for i in np.nonzero(got.argmax(1) != ref.argmax(1))[0]:
+            top2 = np.sort(ref[i])[-2:]
+            assert top2[1] - top2[0] <= 2 * errs[-1], "argmax differs on a row that is not a near-tie"
+            ties.append((len(errs) - 1, int(i), float(top2[1] - top2[0])))
+
+    def cells():
+        used, c = ctx.kv_view()
+        st_h, st_d = ctx.kv_state(False), ctx.kv_state(True)
+        for k in ("head", "used", "n"):
+            assert st_h[k] == st_d[k], k
+        assert np.array_equal(st_h["pos"], st_d["pos"]) and np.array_equal(st_h["bits"], st_d["bits"])
+        assert op.kv_state_to_cells(st_d) == c
+        return used, c
+
+    n_dec, n_kv = replay(golden_dir, "decode_%s" % stem, ctx.decode, ctx.seq_rm, ctx.seq_cp, ctx.seq_keep, cells, check)
+    ctx.close()
+    return n_dec, errs, np.array(rows), ties
+
+
+# What the benchmark runs and the toy fixtures never reach: head_dim 128, eight query heads per KV head (70B / 120B) and one
+# (7B), 290 cells in use of a 1024-cell cache, 3002 sequence ids (94-word sets in the mask predicate), batches of 208 / 64
+# tokens (multi-chunk) and of 9 (two n-tiles), and -- wide_long -- a 6144-cell cache with 300+ cells attended (the
+# long-context attention path).  All compared with what the reference's CPU build returned for the same calls.
+@pytest.mark.parametrize("stem,model,n_ctx,max_seq,n_dec", [("wide_q4_k", "wide_q4_k.gguf", 1024, 3002, 9), ("wide_q4_0", "wide_q4_0.gguf", 1024, 3002, 9),
+                                                          ("wide_long", "wide_q4_k.gguf", 6144, 8, 3)])
+def test_decode_trace_at_benchmark_attention_shapes(llama, golden_dir, stem, model, n_ctx, max_seq, n_dec):
+    got_dec, errs, rows, ties = _replay_checked(llama, golden_dir, os.path.join(golden_dir, model), stem, n_ctx, max_seq)
+    print("%s: max|logit - reference| per decode: %s; rows above 1e-4: %d of %d; near ties: %s"
+          % (stem, " ".join("%.2g" % e for e in errs), int((rows > 1e-4).sum()), len(rows), ties))
+    assert got_dec == n_dec
+    assert np.median(rows) < LOGIT_TOL_TYPICAL and max(errs) <= 1e-2
+
+
+def test_config1_real_shape_trace(llama, golden_dir, tmp_path):
+    """BASELINE.json configs[0] at its real shape (TinyLlama-1.1B architecture, 22 layers, Q8_0, 32000-token vocabulary):
+    eight decodes -- prompt, single tokens, tree batches -- against the reference's CPU build, held to north_star's bound."""
+    meta = json.load(open(os.path.join(golden_dir, "c1_tinyllama_q8_0.json")))
+    sh = meta["shape"]
+    path = str(tmp_path / "c1.gguf")
+    subprocess.run([sys.executable, os.path.join(os.path.dirname(golden_dir), "..", "tools", "make_gguf.py"), "--direct", "--out", path,
+                    "--n-layer", str(sh["n_layer"]), "--n-embd", str(sh["n_embd"]), "--n-head", str(sh["n_head"]),
+                    "--n-head-kv", str(sh["n_head_kv"]), "--n-ff", str(sh["n_ff"]), "--n-vocab", str(sh["n_vocab"]),
+                    "--quant", sh["quant"], "--seed", str(sh["seed"]), "--emb-scale", str(sh["emb_scale"])], check=True)
+    h = hashlib.sha256()
+    with open(path, "rb") as f:
+        for blk in iter(lambda: f.read(1 << 24), b""):
+            h.update(blk)
+    assert h.hexdigest() == meta["sha256"], "the regenerated model file is not the one the golden logits were made with"
+    n_dec, errs, rows, ties = _replay_checked(llama, golden_dir, path, "c1_tinyllama_q8_0", 64, 8)
+    os.unlink(path)
+    flips = [(i, float(r)) for i, r in enumerate(rows) if r > 1e-4]
+    print("config 1 at its real shape: max|logit - reference| per decode: %s; rows above 1e-4 (rounding flips): %s; near ties: %s"
+          % (" ".join("%.2g" % e for e in errs), flips, ties))
+    assert n_dec == 8
+    assert np.median(rows) < LOGIT_TOL_TYPICAL and max(errs) <= 1e-2
 
 
 def test_kv_ops_device_replica_bit_exact(llama, golden_dir):
@@ -119,6 +190,40 @@ def test_async_decode_top8_and_cancel(llama, oracle, golden_dir):
     assert np.array_equal(st["pos"], ost["pos"]) and np.array_equal(st["bits"], ost["bits"])
     assert ctx.finish(None, b2) == -1                  # NULL handle -> -1 (llama.cpp:5866)
     ctx.close(); octx.close()
+
+
+@pytest.mark.parametrize("wt", [2, 12])
+def test_cancel_mid_flight_on_k_split_shapes_leaves_the_next_decode_intact(llama, wt):
+    """7B-width matrices (256 row tiles) are split over K: partial sums meet through scratch memory and a per-tile arrival
+    counter.  A cancel flag that lands while such a grid is half started must not leave a counter behind: cancel a run at 24
+    different moments of its flight and check every time that the next decode of the same token returns the very same logits."""
+    import time
+    ctx = llama.Context(None, n_ctx=128, max_seq=8, synthetic=(4, 4096, 32, 32, 11008 // 256 * 256, 2048, wt, 1, 1, 1.0))
+    toks = [3 + (i * 7919) % 2045 for i in range(9)]
+    rc, _ = ctx.decode(toks[:8], list(range(8)), [[0, 1, 2]] * 8)
+    assert rc == 0
+    for b in (1, 3):                                   # a single token and a small tree batch
+        tk, ps, sq = toks[8:9] * b, [8] * b, [[0]] + [[k] for k in range(1, b)]
+        rc, want = ctx.decode(tk, ps, sq)
+        assert rc == 0
+        for s_ in range(b):
+            ctx.seq_rm(s_, 8, -1)
+        for trial in range(24):
+            h, bt, keep = ctx.start(tk, ps, sq, batch_id=5000 + 100 * b + trial)
+            assert h is not None
+            t_end = time.perf_counter() + trial * 8e-6     # let the run get 0 .. 180 us into its ~150 us of kernels
+            while time.perf_counter() < t_end:
+                pass
+            ids = (C.c_int32 * 1)(5000 + 100 * b + trial)
+            ctx.L.llama_cancel_run(ctx.ctx, ids, 1)
+            assert ctx.finish(h, bt) == 1
+            for s_ in range(b):
+                ctx.seq_rm(s_, 8, -1)
+            rc, got = ctx.decode(tk, ps, sq)
+            assert rc == 0 and np.array_equal(got, want), "a cancelled run corrupted the decode after it (trial %d)" % trial
+            for s_ in range(b):
+                ctx.seq_rm(s_, 8, -1)
+    ctx.close()
 
 
 def test_synthetic_bigram_model_predicts_permutation(llama):

@@ -156,6 +156,34 @@ def test_mul_mat_tensor_core_k_split_path(lib, oracle, N, K, b, name, wt):
     lib.L.pib_weight_free(h)
 
 
+# the matrices bench.py times, at their full size: 70B gate|up, down, fused qkv, lm_head (Q4_K) and Falcon-180B up (Q4_0).
+# The oracle computes a sample of rows -- the first and last row tiles, the rows either side of every 1/8 of the matrix (where a
+# balanced partition of the weight stream changes hands) and 1024 drawn at random -- for b = 1, 4 and 16 tokens.
+@pytest.mark.parametrize("wt,N,K", [(op.TYPE_Q4_K, 57344, 8192), (op.TYPE_Q4_K, 8192, 28672), (op.TYPE_Q4_K, 10240, 8192),
+                                    (op.TYPE_Q4_K, 32000, 8192), (op.TYPE_Q4_0, 118784, 14848)])
+def test_mul_mat_benchmark_shapes_vs_oracle(lib, oracle, wt, N, K):
+    rng = np.random.default_rng(N + K)
+    w = rand_blocks(rng, wt, N, K)
+    rows = set(range(32)) | set(range(N - 32, N)) | set(int(r) for r in rng.integers(0, N, 1024))
+    for e in range(1, 8):
+        rows |= set(range(N * e // 8 - 20, N * e // 8 + 20))
+    rows = np.array(sorted(rows))
+    h = lib.weight_upload(wt, w, K)
+    wsub = np.ascontiguousarray(w[rows])
+    del w
+    for b in (1, 4, 16):
+        x = rng.standard_normal((b, K)).astype(np.float32)
+        ref = oracle.mul_mat(wt, wsub, x)
+        got = lib.mul_mat(h, x, N, 0)
+        assert np.isfinite(got).all()
+        assert np.abs(got[:, rows] - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max()), b
+        # every row, cheaply: the default kernel against the simple dp4a kernel (same integer sums, another fp32 order)
+        if wt == op.TYPE_Q4_0:
+            alt = lib.mul_mat(h, x, N, 1)
+            assert np.abs(got - alt).max() <= REL_TOL * max(1.0, np.abs(alt).max()), b
+    lib.L.pib_weight_free(h)
+
+
 @pytest.mark.parametrize("wt", [op.TYPE_Q4_0, op.TYPE_Q8_0])
 @pytest.mark.parametrize("b", [1, 7, 12])
 def test_mul_mat_width_not_a_multiple_of_256(lib, oracle, wt, b):

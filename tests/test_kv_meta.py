@@ -230,3 +230,29 @@ def test_ranged_operations_are_the_records_the_literal_loops_collapse_to():
     assert [r[:3] + [r[5]] for r in pending(rng)[1:]] == [[KVOP_CP, 5, 3, 4], [KVOP_CP, 5, 6, 8]]
     for h in (lit, rng):
         L.pib_kvtest_free(h)
+    # a sweep that starts below 1 (exported ABI; the scheduler never does it): the closed form assumes sequence 0 is the
+    # untouched source, so id 0 must travel as its literal records -- same state as the per-id loop, on mirror and log alike
+    L.pib_kvtest_state.argtypes = [C.c_void_p] * 4
+    lit, rng = L.pib_kvtest_new(64, 40), L.pib_kvtest_new(64, 40)
+    pos = (C.c_int32 * 6)(*range(6))
+    nsq = (C.c_int32 * 6)(*([2] * 6))
+    rows = [(C.c_int32 * 2)(0, 3) for _ in range(6)]
+    sid = (C.POINTER(C.c_int32) * 6)(*[C.cast(r, C.POINTER(C.c_int32)) for r in rows])
+    L.pib_kvtest_decode.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    for h in (lit, rng):
+        assert L.pib_kvtest_decode(h, 6, pos, nsq, sid) == 0
+    for i in range(0, 9):
+        L.pib_kvtest_op(lit, KVOP_RM, i, 0, 2, 5)
+        if i != 0:
+            L.pib_kvtest_op(lit, KVOP_CP, 0, i, 2, 5)        # llama_kv_cache_seq_cp returns early for src == dst
+    L.pib_kvtest_op_ranged(rng, 7, 0, 8, 0, 2, 5)
+    assert all(r[0] != 7 or r[1] >= 1 for r in pending(rng))
+
+    def state(h):
+        sc, ps, bt = np.zeros(3, np.int32), np.zeros(64, np.int32), np.zeros((64, 2), np.uint32)
+        L.pib_kvtest_state(h, sc.ctypes.data, ps.ctypes.data, bt.ctypes.data)
+        return sc.tolist(), ps.tolist(), bt.tolist()
+
+    assert state(lit) == state(rng)
+    for h in (lit, rng):
+        L.pib_kvtest_free(h)

@@ -99,6 +99,36 @@ def test_decode_trace_matches_reference_bit_exact(oracle, golden_dir, q):
     assert n_dec == 8 and n_kv >= 8
 
 
+# the benchmark's shapes: head_dim 128, grouped-query attention with 8 query heads per KV head (70B / 120B) and without
+# grouping (7B), 290 cells of a 1024-cell cache in use, 3002 sequence ids (94-word sets), 64- and 208-token batches
+@pytest.mark.parametrize("stem,model,n_ctx,max_seq,n_dec", [("wide_q4_k", "wide_q4_k.gguf", 1024, 3002, 9), ("wide_q4_0", "wide_q4_0.gguf", 1024, 3002, 9),
+                                                          ("wide_long", "wide_q4_k.gguf", 6144, 8, 3)])
+def test_decode_trace_at_benchmark_shapes_matches_reference_bit_exact(oracle, golden_dir, stem, model, n_ctx, max_seq, n_dec):
+    got_dec, n_kv = _replay(oracle, golden_dir, model, "decode_%s" % stem, n_ctx=n_ctx, max_seq=max_seq)
+    assert got_dec == n_dec and n_kv >= 3
+
+
+def test_config1_real_shape_trace_matches_reference_bit_exact(oracle, golden_dir, tmp_path):
+    # BASELINE.json configs[0] at its real shape (22 layers, 2048 wide, 32000 tokens, Q8_0): the model file is regenerated from
+    # its seed (1.17 GB, not committed) and must hash to what the reference was given
+    import hashlib, json, subprocess, sys
+    meta = json.load(open(os.path.join(golden_dir, "c1_tinyllama_q8_0.json")))
+    sh = meta["shape"]
+    path = str(tmp_path / "c1.gguf")
+    subprocess.run([sys.executable, os.path.join(golden_dir, "..", "..", "tools", "make_gguf.py"), "--direct", "--out", path,
+                    "--n-layer", str(sh["n_layer"]), "--n-embd", str(sh["n_embd"]), "--n-head", str(sh["n_head"]),
+                    "--n-head-kv", str(sh["n_head_kv"]), "--n-ff", str(sh["n_ff"]), "--n-vocab", str(sh["n_vocab"]),
+                    "--quant", sh["quant"], "--seed", str(sh["seed"]), "--emb-scale", str(sh["emb_scale"])], check=True)
+    h = hashlib.sha256()
+    with open(path, "rb") as f:
+        for blk in iter(lambda: f.read(1 << 24), b""):
+            h.update(blk)
+    assert h.hexdigest() == meta["sha256"]
+    n_dec, n_kv = _replay(oracle, golden_dir, path, "decode_c1_tinyllama_q8_0", n_ctx=64, max_seq=8)
+    os.unlink(path)
+    assert n_dec == 8 and n_kv == 2
+
+
 def test_kv_bookkeeping_random_ops_match_reference(oracle, golden_dir):
     # R6: 400 random seq_rm / seq_cp / seq_keep / decode ops, cell metadata compared after every op
     n_dec, n_kv = _replay(oracle, golden_dir, "tiny_q8_0.gguf", "kvops", check_logits=False)

@@ -1,6 +1,9 @@
-"""The allocation-free GEMV entry point (pib_gemv_q4k_noalloc) against the regular one (pib_gemv), through the C ABI.
+"""The allocation-free GEMV entry point (pib_gemv_q4k_noalloc) against the regular one (pib_gemv) and against the CPU
+oracle, through the C ABI.
 Collected last on purpose: it must give the same answers in a fresh process and after every other test has used the
 library (the built-in scratch array keeps the previous call's contents)."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
@@ -26,12 +29,19 @@ def rand_q4k(rng, N, K):
     return blk.reshape(N, nb * 144)
 
 
-# shapes the kernel splits over K (few row tiles) plus one it does not; the first is the 7B attention projection
-@pytest.mark.parametrize("N,K,b", [(4096, 4096, 4), (2048, 11008 // 256 * 256, 16), (200, 1024, 1), (8192, 8192, 16), (16384, 2048, 3)])
-def test_noalloc_matches_regular_entry_point_twice(lib, N, K, b):
+# (N, K, b, k splits the launcher picks on 148 SMs).  The first five go through the built-in scratch array: the 7B attention
+# projection (256 row tiles, 2 splits), a 128-tile matrix (4), the TinyLlama fused qkv (160 tiles, 2), a 64-tile matrix (8
+# splits of 4 super-blocks) and a ragged 13-tile one (2); the last has 512 row tiles and is not split (no scratch used).
+@pytest.mark.parametrize("N,K,b,splits", [(4096, 4096, 4, 2), (2048, 11008 // 256 * 256, 16, 4), (2560, 2048, 3, 2), (1024, 8192, 16, 8),
+                                          (200, 4096, 1, 2), (8192, 8192, 16, 1)])
+def test_noalloc_matches_regular_entry_point_and_oracle_twice(lib, oracle, N, K, b, splits):
     rng = np.random.default_rng(N + b)
     wt = op.TYPE_Q4_K
-    h = lib.weight_upload(wt, rand_q4k(rng, N, K), K)
+    w = rand_q4k(rng, N, K)
+    h = lib.weight_upload(wt, w, K)
+    lib.L.pib_gemv_direct_splits.argtypes = [C.c_int64, C.c_int64]
+    if lib.L.pib_device_sm_count() == 148:
+        assert lib.L.pib_gemv_direct_splits(N, K) == splits
     y_ref_d, y_d = lib.alloc(b * N * 4), lib.alloc(b * N * 4)
     act = lib.alloc(lib.L.pib_act_bytes(wt, K, b))
     for rep in range(2):                                    # two calls in a row, fresh inputs each time
@@ -47,6 +57,8 @@ def test_noalloc_matches_regular_entry_point_twice(lib, N, K, b):
         got = lib.to_host(y_d, (b, N), np.float32)
         assert np.isfinite(got).all()
         assert np.abs(got - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max())
+        cpu = oracle.mul_mat(wt, w, x)
+        assert np.abs(got - cpu).max() <= REL_TOL * max(1.0, np.abs(cpu).max())
         lib.free(xd)
     for d in (y_ref_d, y_d, act):
         lib.free(d)

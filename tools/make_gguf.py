@@ -220,7 +220,7 @@ def build_direct(args):
         return b, qt
 
     erng = np.random.default_rng(4242)                 # the same g_t for target and draft of one vocabulary / width
-    emb, qt = direct_blocks(erng, args.quant, V, E, 1.0)
+    emb, qt = direct_blocks(erng, args.quant, V, E, args.emb_scale)
     p = perm(V, 7)
     if args.agree < 1.0:
         flip = np.nonzero(np.random.default_rng(9).random(V) >= args.agree)[0]
