@@ -13,6 +13,7 @@
 
 #include <immintrin.h>
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -797,6 +798,16 @@ static int decode_falcon(po_context * c, int T, const int32_t * token, const int
     return 0;
 }
 
+/* debugging aid: with PO_DUMP_DIR set every intermediate of the llama graph is written to <dir>/<name>.<layer>.bin (float32) */
+static void po_dump(const char * name, int il, const float * p, size_t n) {
+    const char * dir = getenv("PO_DUMP_DIR");
+    if (!dir) return;
+    char path[512];
+    snprintf(path, sizeof(path), "%s/%s.%d.bin", dir, name, il);
+    FILE * f = fopen(path, "wb");
+    if (f) { fwrite(p, 4, n, f); fclose(f); }
+}
+
 /* llama.cpp:5461-5726 (phase 0) + build_llama :3872-3980 + llm_build_kv_store :3546 + llm_build_kqv :3698 */
 int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t * pos, const int32_t * n_seq_id,
               const int32_t * const * seq_id, float * logits) {
@@ -843,6 +854,7 @@ int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t
     for (int il = 0; il < m->n_layer; il++) {
         po_fp16 * kl = c->k + (size_t) il * NC * GQA;
         po_fp16 * vl = c->v + (size_t) il * NC * GQA;
+        po_dump("inp", il, inpL, (size_t) T * E);
         for (int t = 0; t < T; t++) {
             po_rms_norm(inpL + (size_t) t * E, cur + (size_t) t * E, E, m->rms_eps);
             for (int i = 0; i < E; i++) cur[(size_t) t * E + i] *= m->attn_norm[il][i];       /* ggml_mul :3593 */
@@ -850,6 +862,7 @@ int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t
         po_mul_mat(m->wtype, m->wq[il], E, E, cur, T, q);
         po_mul_mat(m->wtype, m->wk[il], GQA, E, cur, T, kc);
         po_mul_mat(m->wtype, m->wv[il], GQA, E, cur, T, vc);
+        po_dump("q", il, q, (size_t) T * E); po_dump("k", il, kc, (size_t) T * GQA); po_dump("v", il, vc, (size_t) T * GQA);
         for (int t = 0; t < T; t++) {
             po_rope(q + (size_t) t * E, H, hd, m->n_rot, pos[t], 0, m->rope_freq_base, m->rope_freq_scale);
             po_rope(kc + (size_t) t * GQA, HKV, hd, m->n_rot, pos[t], 0, m->rope_freq_base, m->rope_freq_scale);
@@ -879,17 +892,22 @@ int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t
                 }
             }
         }
+        po_dump("att", il, att, (size_t) T * E);
         po_mul_mat(m->wtype, m->wo[il], E, E, att, T, cur);
+        po_dump("o", il, cur, (size_t) T * E);
         for (size_t i = 0; i < (size_t) T * E; i++) ffi[i] = cur[i] + inpL[i];               /* ffn_inp :3944 */
+        po_dump("ffi", il, ffi, (size_t) T * E);
         for (int t = 0; t < T; t++) {
             po_rms_norm(ffi + (size_t) t * E, cur + (size_t) t * E, E, m->rms_eps);
             for (int i = 0; i < E; i++) cur[(size_t) t * E + i] *= m->ffn_norm[il][i];
         }
         po_mul_mat(m->wtype, m->ffn_up[il], FF, E, cur, T, up);                              /* llm_build_ffn :3611 */
         po_mul_mat(m->wtype, m->ffn_gate[il], FF, E, cur, T, gate);
+        po_dump("gate", il, gate, (size_t) T * FF); po_dump("up", il, up, (size_t) T * FF);
         po_silu(gate, T * FF);
         for (size_t i = 0; i < (size_t) T * FF; i++) gate[i] = gate[i] * up[i];
         po_mul_mat(m->wtype, m->ffn_down[il], E, FF, gate, T, cur);
+        po_dump("down", il, cur, (size_t) T * E);
         for (size_t i = 0; i < (size_t) T * E; i++) inpL[i] = cur[i] + ffi[i];               /* l_out :3962 */
     }
     for (int t = 0; t < T; t++) {

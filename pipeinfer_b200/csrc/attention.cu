@@ -234,25 +234,37 @@ __global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half 
     if (tid < HD) sq[tid] = __half2float(q16[(size_t) t * E + (size_t) head * HD + tid]);
     __syncthreads();
 
-    // phase 1: scores
+    // phase 1: scores, in the reference's order (ggml_vec_dot_f16, ggml.c:1200-1235 with the AVX2 reduce macro :772-790):
+    // 32 fp32 accumulators, element e of the head goes to accumulator e mod 32, then ((0+2)+(1+3)) over the four 8-lane
+    // vectors, low half + high half, two horizontal adds
     float lmax = -INFINITY;
     for (int i = tid; i < n; i += ATQ_THREADS) {
         float sc = -INFINITY;
         if (!mrow[i]) {
             const uint4 * kr = reinterpret_cast<const uint4 *>(kcache + (size_t) i * GQA + (size_t) kvh * HD);
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            float a[4][8];
 #pragma unroll
-            for (int v = 0; v < HD / 8; v++) {
-                const uint4   k8 = kr[v];
-                const __half2 h0 = *reinterpret_cast<const __half2 *>(&k8.x), h1 = *reinterpret_cast<const __half2 *>(&k8.y);
-                const __half2 h2 = *reinterpret_cast<const __half2 *>(&k8.z), h3 = *reinterpret_cast<const __half2 *>(&k8.w);
-                const float4  qa = *reinterpret_cast<const float4 *>(sq + v * 8), qb = *reinterpret_cast<const float4 *>(sq + v * 8 + 4);
-                a0 = fmaf(__low2float(h0), qa.x, a0); a1 = fmaf(__high2float(h0), qa.y, a1);
-                a2 = fmaf(__low2float(h1), qa.z, a2); a3 = fmaf(__high2float(h1), qa.w, a3);
-                a0 = fmaf(__low2float(h2), qb.x, a0); a1 = fmaf(__high2float(h2), qb.y, a1);
-                a2 = fmaf(__low2float(h3), qb.z, a2); a3 = fmaf(__high2float(h3), qb.w, a3);
-            }
-            sc = __fmul_rn((a0 + a1) + (a2 + a3), kq_scale);
+            for (int j = 0; j < 4; j++)
+#pragma unroll
+                for (int l = 0; l < 8; l++) a[j][l] = 0.f;
+#pragma unroll
+            for (int st = 0; st < HD / 32; st++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint4   k8 = kr[st * 4 + j];
+                    const __half2 h0 = *reinterpret_cast<const __half2 *>(&k8.x), h1 = *reinterpret_cast<const __half2 *>(&k8.y);
+                    const __half2 h2 = *reinterpret_cast<const __half2 *>(&k8.z), h3 = *reinterpret_cast<const __half2 *>(&k8.w);
+                    const float * q  = sq + st * 32 + j * 8;
+                    a[j][0] = fmaf(__low2float(h0), q[0], a[j][0]); a[j][1] = fmaf(__high2float(h0), q[1], a[j][1]);
+                    a[j][2] = fmaf(__low2float(h1), q[2], a[j][2]); a[j][3] = fmaf(__high2float(h1), q[3], a[j][3]);
+                    a[j][4] = fmaf(__low2float(h2), q[4], a[j][4]); a[j][5] = fmaf(__high2float(h2), q[5], a[j][5]);
+                    a[j][6] = fmaf(__low2float(h3), q[6], a[j][6]); a[j][7] = fmaf(__high2float(h3), q[7], a[j][7]);
+                }
+            float r[8];
+#pragma unroll
+            for (int l = 0; l < 8; l++) r[l] = __fadd_rn(__fadd_rn(a[0][l], a[2][l]), __fadd_rn(a[1][l], a[3][l]));
+            const float t0 = __fadd_rn(r[0], r[4]), t1 = __fadd_rn(r[1], r[5]), t2 = __fadd_rn(r[2], r[6]), t3 = __fadd_rn(r[3], r[7]);
+            sc = __fmul_rn(__fadd_rn(__fadd_rn(t0, t1), __fadd_rn(t2, t3)), kq_scale);
         }
         s[i] = sc;
         lmax = fmaxf(lmax, sc);
@@ -281,43 +293,52 @@ __global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half 
     for (int i = tid; i < n; i += ATQ_THREADS) s[i] = __half2float(__float2half_rn(__fmul_rn(s[i], inv)));
     __syncthreads();
 
-    // phase 3: O = V . P
-    constexpr int TPR = HD / 2, NGR = ATQ_THREADS / TPR;
+    // phase 3: O = V . P in the reference's order (the same ggml_vec_dot_f16, now over the cells): cell c < np = n & ~31 goes
+    // to accumulator c mod 32, each accumulator a sequential fma chain over its cells; then the same tree per output element;
+    // the n - np cells left over are added one by one in double.  A thread owns a pair of output dims and APG of the 32
+    // accumulators; the 32 x HD partial sums meet in shared memory.
+    constexpr int TPR = HD / 2, NGR = ATQ_THREADS / TPR, APG = 32 / NGR;      // hd 128: 4 groups x 8 accumulators; hd 64: 8 x 4
     const int grp = tid / TPR, dp = tid % TPR;
+    const int np  = n & ~31;
     const __half * vb = vcache + (size_t) kvh * HD + dp * 2;
-    float o0 = 0.f, o1 = 0.f;
-    int i = grp;
-    for (; i + 7 * NGR < n; i += 8 * NGR) {
-        __half2 vv[8];
-        float   pp[8];
+    float o0[APG], o1[APG];
 #pragma unroll
-        for (int u = 0; u < 8; u++) { vv[u] = *reinterpret_cast<const __half2 *>(vb + (size_t) (i + u * NGR) * GQA); pp[u] = s[i + u * NGR]; }
+    for (int u = 0; u < APG; u++) { o0[u] = 0.f; o1[u] = 0.f; }
+    for (int base = 0; base < np; base += 32) {
+        __half2 vv[APG];
+        float   pp[APG];
 #pragma unroll
-        for (int u = 0; u < 8; u++) { o0 = fmaf(__low2float(vv[u]), pp[u], o0); o1 = fmaf(__high2float(vv[u]), pp[u], o1); }
-    }
-    for (; i < n; i += NGR) {
-        const float p = s[i];
-        if (p != 0.f) {
-            const __half2 vv = *reinterpret_cast<const __half2 *>(vb + (size_t) i * GQA);
-            o0 = fmaf(__low2float(vv), p, o0); o1 = fmaf(__high2float(vv), p, o1);
+        for (int u = 0; u < APG; u++) {
+            const int c = base + grp * APG + u;
+            pp[u] = s[c];
+            vv[u] = pp[u] != 0.f ? *reinterpret_cast<const __half2 *>(vb + (size_t) c * GQA) : __half2();     // p == 0: the fma leaves the accumulator as it is
         }
+#pragma unroll
+        for (int u = 0; u < APG; u++) { o0[u] = fmaf(__low2float(vv[u]), pp[u], o0[u]); o1[u] = fmaf(__high2float(vv[u]), pp[u], o1[u]); }
     }
-    __syncthreads();
-    float * red = smem;                                 // reuse: [NGR][HD]
-    red[grp * HD + dp * 2] = o0; red[grp * HD + dp * 2 + 1] = o1;
+    float * red = smem + n_ctx;                         // [32 accumulators][HD]
+#pragma unroll
+    for (int u = 0; u < APG; u++) { red[(grp * APG + u) * HD + dp * 2] = o0[u]; red[(grp * APG + u) * HD + dp * 2 + 1] = o1[u]; }
     __syncthreads();
     if (tid < HD) {
-        float a = 0.f;
+        float r[8];
 #pragma unroll
-        for (int r = 0; r < NGR; r++) a += red[r * HD + tid];
-        out[(size_t) t * E + (size_t) head * HD + tid] = a;
+        for (int l = 0; l < 8; l++)
+            r[l] = __fadd_rn(__fadd_rn(red[(0 * 8 + l) * HD + tid], red[(2 * 8 + l) * HD + tid]), __fadd_rn(red[(1 * 8 + l) * HD + tid], red[(3 * 8 + l) * HD + tid]));
+        const float t0 = __fadd_rn(r[0], r[4]), t1 = __fadd_rn(r[1], r[5]), t2 = __fadd_rn(r[2], r[6]), t3 = __fadd_rn(r[3], r[7]);
+        double sumf = (double) __fadd_rn(__fadd_rn(t0, t1), __fadd_rn(t2, t3));
+        for (int c = np; c < n; c++) {
+            const float p = s[c];
+            if (p != 0.f) sumf += (double) __fmul_rn(__half2float(vcache[(size_t) c * GQA + (size_t) kvh * HD + tid]), p);
+        }
+        out[(size_t) t * E + (size_t) head * HD + tid] = (float) sumf;
     }
 }
 
 template <int HD>
 static int launch_att_qh(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
                          int E, int GQA, int n_ctx, int n_tokens, int n_head, int gdiv, float * out, const int * cancel, cudaStream_t st) {
-    const size_t smem = (size_t) std::max(n_ctx, (ATQ_THREADS / (HD / 2)) * HD) * sizeof(float);
+    const size_t smem = ((size_t) n_ctx + 32 * HD) * sizeof(float);          // scores / probabilities + the 32 x HD partial sums
     pib_launch(attention_qh_kernel<HD>, dim3(n_head, n_tokens), dim3(ATQ_THREADS), smem, st, q16, kc, vc, mask, scalars, pib_get_luts().exp_f16, E, GQA,
                                                                                n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv);
     PIB_CHECK(cudaGetLastError());

@@ -508,6 +508,19 @@ __global__ void add3_kernel(const float * a, const float * b, const float * c, f
 int (*pib_hop_recv)(pib_context * c, float * x, int n_tokens, const int * cancel) = nullptr;
 int (*pib_hop_send)(pib_context * c, const float * x, int n_tokens, const int * cancel) = nullptr;
 
+// debugging aid (PIB_DUMP_DIR=<dir>, graphs off): every intermediate of the llama graph goes to <dir>/<name>.<layer>.bin as float32,
+// under the names the oracle uses for the same tensors (PO_DUMP_DIR, oracle/pib_oracle.c), so the two can be compared step by step
+static void dump_dev(const pib_context * c, const char * name, int il, const float * dev, size_t rows, size_t cols, size_t ld) {
+    static const char * dir = getenv("PIB_DUMP_DIR");
+    if (!dir) return;
+    cudaStreamSynchronize(c->stream);
+    std::vector<float> h(rows * cols);
+    cudaMemcpy2D(h.data(), cols * 4, dev, ld * 4, cols * 4, rows, cudaMemcpyDeviceToHost);
+    char path[512];
+    snprintf(path, sizeof(path), "%s/%s.%d.bin", dir, name, il);
+    if (FILE * f = fopen(path, "wb")) { fwrite(h.data(), 4, h.size(), f); fclose(f); }
+}
+
 // `part`: 1 = embedding + layers (everything whose addresses are the same for every run: graph material), 2 = the last
 // stage's tail (final norm, lm_head, sampling: writes the run's own logits / result rows), 3 = both
 static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, int slot, const int * cancel, int part) {
@@ -597,16 +610,26 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
         else             TL(5, il, pib_add_rmsnorm_quantize_act(wt, c->x, nullptr, nullptr, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
         GEMV(0, il, L.wqkv, c->qkv);
         if (L.wv) GEMV(0, il, L.wv, c->vsep);
+        dump_dev(c, "inp", il, c->x, ntok, E, E);
+        dump_dev(c, "q", il, c->qkv, ntok, E, E + (L.wv ? 1 : 2) * GQA);
+        dump_dev(c, "k", il, c->qkv + E, ntok, GQA, E + (L.wv ? 1 : 2) * GQA);
+        if (!L.wv) dump_dev(c, "v", il, c->qkv + E + GQA, ntok, GQA, E + 2 * GQA);
         TL(6, il, pib_rope_kv_store(c->qkv, desc, c->rope, c->rope_n_pos, ntok, E, GQA, hd, 0, c->q16, c->kcache + lo, c->vcache + lo, cancel, st,
                                     L.wv ? c->vsep : nullptr));
         TL(7, il, pib_attention(c->q16, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, desc, ntok, m->n_head, m->n_head_kv, hd,
                                 (int) c->n_ctx, c->att, cancel, st));
+        dump_dev(c, "att", il, c->att, ntok, E, E);
         TL(8, il, pib_quantize_act_c(wt, c->att, ntok, E, c->act, cancel, st));
         GEMV(1, il, L.wo, c->proj);
+        dump_dev(c, "o", il, c->proj, ntok, E, E);
         TL(9, il, pib_add_rmsnorm_quantize_act(wt, c->proj, c->x, c->x2, L.ffn_norm, m->rms_eps, ntok, E, c->act, cancel, st));   // x2 = ffn_inp
+        dump_dev(c, "ffi", il, c->x2, ntok, E, E);
         GEMV(2, il, L.wgu, c->gu);
+        dump_dev(c, "gate", il, c->gu, ntok, FF, 2 * (size_t) FF);
+        dump_dev(c, "up", il, c->gu + FF, ntok, FF, 2 * (size_t) FF);
         TL(10, il, pib_silu_mul_quantize_act(wt, c->gu, c->gu + FF, 2 * (int64_t) FF, ntok, FF, c->act, cancel, st));
         GEMV(3, il, L.wdown, c->proj);
+        dump_dev(c, "down", il, c->proj, ntok, E, E);
         pending_add = true;
     }
     if (c->stage.last() && !(part & 2)) return PIB_OK;
@@ -753,7 +776,7 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
         cudaMemcpyAsync(c->desc_dev + (size_t) dev_slot(c, s) * c->desc_stride, d, c->desc_stride, cudaMemcpyHostToDevice, c->stream);
         c->h2d_bytes += c->desc_stride;
     }
-    dq.push_back({ KVOP_ADVANCE, n_tokens, 0, 0, 0, 0 });
+    dq.push_back({ KVOP_ADVANCE, n_tokens, (int32_t) head, 0, 0, 0 });
     kvlog_decode_end(c->kv, n_tokens);                                    // llama.cpp:5708-5713
     SLOW_MARK("descriptors");
     if (c->stage.size > 1 && c->stage.first()) {          // tell the other stages first, so that their receives are posted early

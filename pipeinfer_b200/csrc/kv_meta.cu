@@ -182,7 +182,7 @@ void KvMirror::apply(const KvOp & op, const int32_t * tpos, const uint32_t * tok
             used += (uint32_t) op.b;
             n = (uint32_t) op.p0;
             break;
-        case KVOP_ADVANCE: head += (uint32_t) op.a; if (head >= size) head = 0; break;
+        case KVOP_ADVANCE: head = (uint32_t) (op.b + op.a); if (head >= size) head = 0; break;
         default: break;
     }
 }
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(KVT) kv_apply_kernel(int32_t * __restrict__ po
             else if (op.op == KVOP_CP) s_head = 0;
             else if (op.op == KVOP_SETHEAD) s_head = op.a;
             else if (op.op == KVOP_ALLOC) { s_head = op.a; s_used += op.b; s_n = op.p0; }
-            else if (op.op == KVOP_ADVANCE) { s_head += op.a; if (s_head >= size) s_head = 0; }
+            else if (op.op == KVOP_ADVANCE) { s_head = op.b + op.a; if (s_head >= size) s_head = 0; }
         }
         __syncthreads();   // also orders this op's global writes before the next op's reads (same CTA)
     }

@@ -23,7 +23,8 @@ enum {
     KVOP_KEEP  = 4,     // a=seq                                     llama_kv_cache_seq_keep
     KVOP_ALLOC = 5,     // a=head, b=n_tokens, p0=n (attended range), p1=descriptor slot: cells [head, head+n_tokens)
                         //   take pos / seq bits of the batch         llama_kv_cache_find_slot (resolved on the host)
-    KVOP_ADVANCE = 6,   // a=n_tokens: head += n_tokens, wrap to 0    llama.cpp:5708-5713
+    KVOP_ADVANCE = 6,   // a=n_tokens, b=first cell of the decode: head = b + a, wrap to 0 (a multi-chunk decode issues one ALLOC
+                        //   per chunk, each moving head to its own first cell)        llama.cpp:5708-5713
     KVOP_SWEEP = 7,     // a=first seq, b=last seq, p0, p1: for i in [a, b]: RM(i, p0, p1); CP(0, i, p0, p1)
                         //   the per-sequence commit loop of speculative.cpp:603-612 collapsed into one op
     KVOP_SETHEAD = 8,   // a=head: the pre-decode heuristic (llama.cpp:5548-5550) resolved on the host

@@ -118,11 +118,13 @@ bool pib_gemv_blk32_supported(const pib_weight * w, int b);
 int  pib_gemv_q5k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_q6k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_blk32(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
+int  pib_gemv_exact_ref(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 
 int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, const int * cancel,
                       cudaStream_t st) {
     if (w->type == PIB_TYPE_Q6_K) return pib_gemv_q6k(w, act_dev, b, y_dev, cancel, st);
     if (w->type == PIB_TYPE_Q5_K) return pib_gemv_q5k(w, act_dev, b, y_dev, cancel, st);
+    if (variant == 4) return pib_gemv_exact_ref(w, act_dev, b, y_dev, cancel, st);
     const bool tc = pib_gemv_mma_supported(w, b);
     if (variant == 3 && tc) return pib_gemv_mma(w, act_dev, b, y_dev, cancel, st);
     if ((variant == 2 || variant == 0) && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);

@@ -493,7 +493,7 @@ void pib_kvtest_ship_decode(pib_kvtest * t, int n_tokens, const int32_t * pos, c
         dp[ch] = d; slots[ch] = ch;
         t->devops.push_back({ KVOP_ALLOC, (int32_t) (head + t0), nt, (int32_t) t->kv.n, ch, 0 });
     }
-    t->devops.push_back({ KVOP_ADVANCE, n_tokens, 0, 0, 0, 0 });
+    t->devops.push_back({ KVOP_ADVANCE, n_tokens, (int32_t) head, 0, 0, 0 });
     pib_pipe_ship_decode(0, n_tokens, n_chunks, dp.data(), stride, slots.data(), t->devops.data(), (int) t->devops.size());
     t->devops.clear();
 }
