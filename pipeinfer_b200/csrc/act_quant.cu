@@ -58,7 +58,8 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
                                                                int x2_per_row, float eps, int64_t K,
                                                                int8_t * __restrict__ qs, float * __restrict__ dplane,
                                                                void * __restrict__ bsplane, int8_t * __restrict__ bs8plane,
-                                                               int8_t * __restrict__ qsp,
+                                                               int8_t * __restrict__ qsp, int2 * __restrict__ qsl,
+                                                               int16_t * __restrict__ sbs,
                                                                float * __restrict__ vout,
                                                                const uint16_t * __restrict__ lut,
                                                                const float * __restrict__ addend, float * sum_out,
@@ -238,6 +239,13 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
                 int8_t * o = bs8plane + ((size_t) row * nsb + sb) * 16 + (lane >> 2);
                 o[0] = (int8_t) (s32 >> 6);
                 o[8] = (int8_t) (s32 & 63);
+                sbs[((size_t) row * nsb + sb) * 8 + (lane >> 2)] = (int16_t) s32;
+            }
+            // lane-group copy for the lane-exact kernel: this lane holds lane groups 2 (lane % 4) and 2 (lane % 4) + 1 of sub-block lane / 4
+            {
+                int2 * o = qsl + (((size_t) row * nsb + sb) * 8 + 2 * (lane & 3)) * 8 + (lane >> 2);
+                o[0] = make_int2(packed.x, 0);
+                o[8] = make_int2(0, packed.y);
             }
             if (lane == 0) dplane[(size_t) row * nsb + sb] = dval;
         }
@@ -256,11 +264,13 @@ static int launch_aq(int wtype, const float * x, const float * x2, int x2_per_ro
     void *   bs = (uint8_t *) act + L.bs_off;
     int8_t * b8 = (int8_t *) act + L.bs8_off;
     int8_t * qp = (int8_t *) act + L.qsp_off;
+    int2 *    ql = (int2 *) ((uint8_t *) act + L.qsl_off);
+    int16_t * sb = (int16_t *) ((uint8_t *) act + L.sbs_off);
     const int64_t units = wtype == PIB_TYPE_Q4_K ? K / PIB_QK_K : K / PIB_QK / 4;        // super-blocks, or groups of 4 blocks
     const int     parts = (int) max((int64_t) 1, min((int64_t) 32, units / (AQ_THREADS / 32)));
     const dim3    grid(b, parts);
-    if (wtype == PIB_TYPE_Q4_K) pib_launch(act_quant_kernel<true, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride, bias, addend2);
-    else                        pib_launch(act_quant_kernel<false, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, vout, lut, addend, sum_out, cancel, xstride, bias, addend2);
+    if (wtype == PIB_TYPE_Q4_K) pib_launch(act_quant_kernel<true, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, ql, sb, vout, lut, addend, sum_out, cancel, xstride, bias, addend2);
+    else                        pib_launch(act_quant_kernel<false, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, ql, sb, vout, lut, addend, sum_out, cancel, xstride, bias, addend2);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }

@@ -118,6 +118,7 @@ bool pib_gemv_blk32_supported(const pib_weight * w, int b);
 int  pib_gemv_q5k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_q6k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_blk32(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
+int  pib_gemv_q4k_lane(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_exact_ref(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 
 int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, const int * cancel,
@@ -127,7 +128,8 @@ int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float *
     if (variant == 4) return pib_gemv_exact_ref(w, act_dev, b, y_dev, cancel, st);
     const bool tc = pib_gemv_mma_supported(w, b);
     if (variant == 3 && tc) return pib_gemv_mma(w, act_dev, b, y_dev, cancel, st);
-    if ((variant == 2 || variant == 0) && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);
+    if ((variant == 2 || variant == 0) && tc) return pib_gemv_q4k_lane(w, act_dev, b, y_dev, cancel, st);
+    if (variant == 5 && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);      // round-1 kernel (fp32 terms added in another order)
     if ((variant == 2 || variant == 0) && pib_gemv_blk32_supported(w, b)) return pib_gemv_blk32(w, act_dev, b, y_dev, cancel, st);
     return pib_gemv_dp4a(w, act_dev, b, y_dev, cancel, st);
 }

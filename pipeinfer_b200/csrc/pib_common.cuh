@@ -138,6 +138,9 @@ struct pib_act_layout {
     size_t qsp_off;    // Q8_K family: int8 [b][K], the same quants as qs_off in tensor-core fragment order: inside each
                        //   super-block, element e = 64c + 32h + 8t + i (chunk c, low/high-nibble half h, lane quarter t) is
                        //   stored at 64t + 16c + 8h + i, so a lane's B fragments for all four chunks are 64 contiguous bytes
+    size_t qsl_off;    // Q8_K family: int2 [b][K/256][8 lane groups g][8 sub-blocks j]: {x if g even else 0, x if g odd else 0} with x =
+                       //   the four quants 4g .. 4g+3 of sub-block j -- the two B registers of the lane-exact kernel (gemv_q4k_lane.cu)
+    size_t sbs_off;    // Q8_K family: int16 [b][K/32] sub-block sums bsums[2j] + bsums[2j+1]
     size_t total;
 };
 __host__ __device__ inline pib_act_layout pib_act_layout_of(int wtype, int64_t K, int b) {
@@ -154,6 +157,8 @@ __host__ __device__ inline pib_act_layout pib_act_layout_of(int wtype, int64_t K
     const size_t ngr = (size_t) ((K + 255) / 256);
     size_t nbs8 = (wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / PIB_QK_K) * 16 : (size_t) b * ngr * 8 * 2;
     L.qsp_off = (L.bs8_off + nbs8 + 255) & ~(size_t) 255;
-    L.total  = (L.qsp_off + ((wtype == PIB_TYPE_Q4_K) ? qs : (size_t) b * ngr * 256) + 255) & ~(size_t) 255;
+    L.qsl_off = (L.qsp_off + ((wtype == PIB_TYPE_Q4_K) ? qs : (size_t) b * ngr * 256) + 255) & ~(size_t) 255;
+    L.sbs_off = (L.qsl_off + ((wtype == PIB_TYPE_Q4_K) ? 2 * qs : 0) + 255) & ~(size_t) 255;
+    L.total   = (L.sbs_off + ((wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / 32) * 2 : 0) + 255) & ~(size_t) 255;
     return L;
 }

@@ -1,0 +1,39 @@
+#!/usr/bin/env python
+"""Isolated timing of one quantised matmul shape through the C ABI (pib_gemv), weights generated on the device:
+  python tools/gemv_bench.py --type q4_k --N 57344 --K 8192 --b 1,4 --variant 0,5 [--reps 50]
+Rotates over enough copies of the matrix to exceed the 126 MB L2."""
+import argparse, ctypes as C, os, sys, time
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+import numpy as np
+from pipeinfer_b200 import load
+ap = argparse.ArgumentParser()
+ap.add_argument("--type", default="q4_k"); ap.add_argument("--N", type=int, default=57344); ap.add_argument("--K", type=int, default=8192)
+ap.add_argument("--b", default="1,4"); ap.add_argument("--variant", default="0"); ap.add_argument("--reps", type=int, default=50)
+a = ap.parse_args()
+wt = {"q4_k": 12, "q4_0": 2, "q8_0": 8}[a.type]
+bb = {12: 144, 2: 18, 8: 34}[wt]; be = {12: 256, 2: 32, 8: 32}[wt]
+lib = load(); lib.init(0)
+rng = np.random.default_rng(0)
+wbytes = a.N * a.K // be * bb
+ncopies = max(1, int(300e6 // wbytes) + 1)
+blk = rng.integers(0, 256, (a.N, a.K // be, bb), dtype=np.uint8)
+blk[:, :, 0:2] = (rng.uniform(0.5, 1.5, (a.N, a.K // be)) * 0.0025).astype(np.float16).view(np.uint8).reshape(a.N, a.K // be, 2)
+if wt == 12:
+    blk[:, :, 2:4] = (rng.uniform(0.5, 1.5, (a.N, a.K // be)) * 0.001).astype(np.float16).view(np.uint8).reshape(a.N, a.K // be, 2)
+hs = [lib.weight_upload(wt, blk.reshape(a.N, -1), a.K) for _ in range(ncopies)]
+for b in [int(x) for x in a.b.split(",")]:
+    x = rng.standard_normal((b, a.K)).astype(np.float32)
+    xd = lib.to_device(x)
+    act = lib.alloc(lib.L.pib_act_bytes(wt, a.K, b))
+    yd = lib.alloc(b * a.N * 4)
+    lib.check(lib.L.pib_quantize_act(wt, xd, b, a.K, act, None))
+    for v in [int(x) for x in a.variant.split(",")]:
+        for i in range(5):
+            lib.check(lib.L.pib_gemv(hs[i % ncopies], act, b, yd, v, None))
+        lib.check(lib.L.pib_stream_sync(None))
+        t0 = time.perf_counter()
+        for i in range(a.reps):
+            lib.L.pib_gemv(hs[i % ncopies], act, b, yd, v, None)
+        lib.check(lib.L.pib_stream_sync(None))
+        dt = (time.perf_counter() - t0) / a.reps
+        print("%s %dx%d b=%d variant %d: %.2f us  %.0f GB/s" % (a.type, a.N, a.K, b, v, dt * 1e6, wbytes / dt / 1e9), flush=True)
