@@ -80,137 +80,11 @@ __global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8
 }
 
 // ---- attention ------------------------------------------------------------------------------------------------------
-// grid (n_head_kv, n_tokens); one CTA serves the G = n_head / n_head_kv query heads that share a KV head, for one
-// token, over all n cells: K and V of that head are read once per token (GQA broadcast, ggml.c:9567 i02 = i12 / r2).
-// Masked cells are skipped entirely (no K/V load): in a speculative run most cells of other partitions are masked.
-#define ATT_THREADS 256
-#define ATT_WARPS   (ATT_THREADS / 32)
-
-template <int HD, int G>
-__global__ void __launch_bounds__(ATT_THREADS) attention_kernel(const __half * __restrict__ q16, const __half * __restrict__ kcache,
-                                                                const __half * __restrict__ vcache,
-                                                                const uint8_t * __restrict__ mask, const int32_t * __restrict__ scalars,
-                                                                const uint8_t * __restrict__ desc, const uint16_t * __restrict__ exp_lut,
-                                                                int E, int GQA, int n_ctx, float kq_scale, float * __restrict__ out,
-                                                                const int * __restrict__ cancel, int gdiv) {
-    pib_pdl_wait();
-    pib_pdl_trigger();
-    if (PIB_CANCELLED(cancel)) return;
-    (void) desc;
-    extern __shared__ float smem[];
-    // gdiv == 1: blockIdx.x is a KV head serving its G query heads (K/V read once per token; best at long contexts).
-    // gdiv  > 1: blockIdx.x is a query head (template G == 1) reading KV head blockIdx.x / gdiv: G times more CTAs,
-    //            K/V re-read through L2 -- the better trade at the short contexts of verification batches.
-    const int qh0 = blockIdx.x * G, kvh = blockIdx.x / gdiv, t = blockIdx.y;
-    const int n   = scalars[2];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int DPL = HD / 32;                 // dims per lane: 4 (hd 128) or 2 (hd 64)
-    float * s = smem;                            // [G][n] scores, then probabilities (fp16-rounded values)
-    const uint8_t * mrow = mask + (size_t) t * n_ctx;
-
-    // the lane's slice of the G query vectors, already rounded to fp16 by rope_kv_store
-    float q[G][DPL];
-#pragma unroll
-    for (int g = 0; g < G; g++)
-#pragma unroll
-        for (int j = 0; j < DPL; j++) q[g][j] = __half2float(q16[(size_t) t * E + (size_t) (qh0 + g) * HD + lane * DPL + j]);
-
-    // phase 1: scores
-    for (int i = warp; i < n; i += ATT_WARPS) {
-        if (mrow[i]) {
-            if (lane < G) s[(size_t) lane * n + i] = -INFINITY;
-            continue;
-        }
-        const __half * kr = kcache + (size_t) i * GQA + (size_t) kvh * HD + lane * DPL;
-        float kf[DPL];
-        if (DPL == 4) {
-            const uint2 raw = *reinterpret_cast<const uint2 *>(kr);
-            const __half2 h0 = *reinterpret_cast<const __half2 *>(&raw.x), h1 = *reinterpret_cast<const __half2 *>(&raw.y);
-            kf[0] = __low2float(h0); kf[1] = __high2float(h0); kf[2] = __low2float(h1); kf[3] = __high2float(h1);
-        } else {
-            const __half2 h0 = *reinterpret_cast<const __half2 *>(kr);
-            kf[0] = __low2float(h0); kf[1] = __high2float(h0);
-        }
-        float acc[G];
-#pragma unroll
-        for (int g = 0; g < G; g++) {
-            float a = 0.f;
-#pragma unroll
-            for (int j = 0; j < DPL; j++) a = fmaf(kf[j], q[g][j], a);
-            acc[g] = a;
-        }
-#pragma unroll
-        for (int g = 0; g < G; g++) {
-            const float v = warp_sum(acc[g]);
-            if (lane == g) s[(size_t) g * n + i] = __fmul_rn(v, kq_scale);
-        }
-    }
-    __syncthreads();
-
-    // phase 2: softmax per query head (warp g -> head g, looping when G > ATT_WARPS is impossible: G <= 8)
-    for (int g = warp; g < G; g += ATT_WARPS) {
-        float * sg = s + (size_t) g * n;
-        float   mx = -INFINITY;
-        for (int i = lane; i < n; i += 32) mx = fmaxf(mx, sg[i]);
-        mx = warp_max(mx);
-        double sum = 0.0;
-        for (int i = lane; i < n; i += 32) {
-            const float x = sg[i];
-            float       v = 0.0f;
-            if (x != -INFINITY) {
-                v = pib_h2f(exp_lut[pib_f2h(__fsub_rn(x, mx))]);
-                sum += (double) v;
-            }
-            sg[i] = v;
-        }
-        sum = warp_sum_d(sum);                   // exact: fp16 values, <= 2^12 terms
-        const float inv = (float) (1.0 / sum);
-        for (int i = lane; i < n; i += 32) sg[i] = __half2float(__float2half_rn(__fmul_rn(sg[i], inv)));
-    }
-    __syncthreads();
-
-    // phase 3: O = V . P ; thread -> (cell group, pair of dims), fp32 accumulate, cross-group reduce in smem
-    constexpr int TPR = HD / 2;                  // threads per cell row (half2 each)
-    constexpr int NGR = ATT_THREADS / TPR;       // cell groups: 4 (hd 128) or 8 (hd 64)
-    const int grp = tid / TPR, dp = tid % TPR;
-    float o[G][2];
-#pragma unroll
-    for (int g = 0; g < G; g++) { o[g][0] = 0.f; o[g][1] = 0.f; }
-    for (int i = grp; i < n; i += NGR) {
-        if (mrow[i]) continue;
-        const __half2 vv = *reinterpret_cast<const __half2 *>(vcache + (size_t) i * GQA + (size_t) kvh * HD + dp * 2);
-        const float   v0 = __low2float(vv), v1 = __high2float(vv);
-#pragma unroll
-        for (int g = 0; g < G; g++) {
-            const float p = s[(size_t) g * n + i];
-            o[g][0] = fmaf(v0, p, o[g][0]);
-            o[g][1] = fmaf(v1, p, o[g][1]);
-        }
-    }
-    __syncthreads();
-    float * red = smem;                          // reuse: [NGR][G][HD]   (needs NGR*G*HD <= G*n floats or the extra tail)
-    float * redbuf = smem + (size_t) G * n;      // separate region sized by the launcher
-    (void) red;
-#pragma unroll
-    for (int g = 0; g < G; g++) {
-        redbuf[((size_t) grp * G + g) * HD + dp * 2]     = o[g][0];
-        redbuf[((size_t) grp * G + g) * HD + dp * 2 + 1] = o[g][1];
-    }
-    __syncthreads();
-    for (int j = tid; j < G * HD; j += ATT_THREADS) {
-        float a = 0.f;
-#pragma unroll
-        for (int r = 0; r < NGR; r++) a += redbuf[(size_t) r * G * HD + j];
-        const int g = j / HD, d = j % HD;
-        out[(size_t) t * E + (size_t) (qh0 + g) * HD + d] = a;
-    }
-}
-
-// ---- per-query-head variant (short contexts: verification batches) -----------------------------------------------------
-// grid (n_head, n_tokens), 256 threads.  Phase 1 gives every thread whole cells: a lane reads one K row with 128-bit loads
-// and keeps the dot product in four independent fp32 accumulators (no shuffles); phase 3 gives every thread a pair of
-// output dims over a slice of the cells, eight V loads in flight.  K/V of a KV head are re-read by its G query heads
-// through L2 -- a few MB per layer at these context lengths.
+// grid (n_head, n_tokens), 256 threads; one CTA per (query head, token).  Every fp32 sum is formed in the reference's order
+// (ggml_vec_dot_f16 for both K.Q and V.P), so the output is bit-identical to the CPU's: phase 1 gives every thread whole cells
+// (a K row in 128-bit loads, the 32 lane accumulators of the reference in registers); phase 3 gives every thread a pair of
+// output dims and a share of the 32 accumulators, each a sequential chain over its cells.  K/V of a KV head are re-read by its
+// G query heads through L2 -- a few MB per layer at these context lengths.  Masked cells are never loaded.
 #define ATQ_THREADS 256
 template <int HD>
 __global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half * __restrict__ q16, const __half * __restrict__ kcache,
@@ -339,24 +213,13 @@ template <int HD>
 static int launch_att_qh(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
                          int E, int GQA, int n_ctx, int n_tokens, int n_head, int gdiv, float * out, const int * cancel, cudaStream_t st) {
     const size_t smem = ((size_t) n_ctx + 32 * HD) * sizeof(float);          // scores / probabilities + the 32 x HD partial sums
-    pib_launch(attention_qh_kernel<HD>, dim3(n_head, n_tokens), dim3(ATQ_THREADS), smem, st, q16, kc, vc, mask, scalars, pib_get_luts().exp_f16, E, GQA,
-                                                                               n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv);
-    PIB_CHECK(cudaGetLastError());
-    return PIB_OK;
-}
-
-template <int HD, int G>
-static int launch_att(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
-                      const uint8_t * desc, int E, int GQA, int n_ctx, int n_tokens, int n_blocks_x, int gdiv, float * out,
-                      const int * cancel, cudaStream_t st) {
-    const size_t smem = ((size_t) G * n_ctx + (size_t) (ATT_THREADS / (HD / 2)) * G * HD) * sizeof(float);
-    static size_t configured = 0;
+    static size_t configured = 48 * 1024;
     if (smem > configured) {
-        PIB_CHECK(cudaFuncSetAttribute(attention_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        PIB_CHECK(cudaFuncSetAttribute(attention_qh_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         configured = smem;
     }
-    pib_launch(attention_kernel<HD, G>, dim3(n_blocks_x, n_tokens), dim3(ATT_THREADS), smem, st, 
-        q16, kc, vc, mask, scalars, desc, pib_get_luts().exp_f16, E, GQA, n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv);
+    pib_launch(attention_qh_kernel<HD>, dim3(n_head, n_tokens), dim3(ATQ_THREADS), smem, st, q16, kc, vc, mask, scalars, pib_get_luts().exp_f16, E, GQA,
+                                                                               n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }
@@ -372,27 +235,16 @@ int pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * ro
 bool pib_attention_supported(int hd, int n_head, int n_head_kv, int n_ctx) {
     if (hd != 64 && hd != 128) return false;
     if (n_head % n_head_kv) return false;
-    const int G = n_head / n_head_kv;
-    if (n_ctx <= 4096) return true;                       // per-query-head kernel: any group size (falcon-7B: 71 heads on one KV head)
-    if (G != 1 && G != 2 && G != 4 && G != 8) return false;
-    const size_t smem = ((size_t) G * n_ctx + (size_t) (ATT_THREADS / (hd / 2)) * G * hd) * sizeof(float);
-    return smem <= 220 * 1024;
+    return ((size_t) n_ctx + 32 * hd) * sizeof(float) <= 220 * 1024;      // the scores of one (head, token) live in shared memory
 }
 
 int pib_attention(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
                   const uint8_t * desc, int n_tokens, int n_head, int n_head_kv, int hd, int n_ctx, float * out,
                   const int * cancel, cudaStream_t st) {
+    (void) desc;
     const int E = n_head * hd, GQA = n_head_kv * hd, G = n_head / n_head_kv;
-    // per-query-head CTAs unless the context is long enough for the G-fold K/V re-reads to matter
-    if (n_ctx <= 4096) {
-        if (hd == 128) return launch_att_qh<128>(q16, kc, vc, mask, scalars, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
-        if (hd == 64)  return launch_att_qh<64>(q16, kc, vc, mask, scalars, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
-    }
-#define ATT_CASE(HDv, Gv) \
-    if (hd == HDv && G == Gv) return launch_att<HDv, Gv>(q16, kc, vc, mask, scalars, desc, E, GQA, n_ctx, n_tokens, n_head_kv, 1, out, cancel, st);
-    ATT_CASE(128, 1) ATT_CASE(128, 2) ATT_CASE(128, 4) ATT_CASE(128, 8)
-    ATT_CASE(64, 1) ATT_CASE(64, 2) ATT_CASE(64, 4) ATT_CASE(64, 8)
-#undef ATT_CASE
-    pib_set_error("attention: unsupported head_dim %d / group %d", hd, G);
+    if (hd == 128) return launch_att_qh<128>(q16, kc, vc, mask, scalars, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
+    if (hd == 64)  return launch_att_qh<64>(q16, kc, vc, mask, scalars, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
+    pib_set_error("attention: unsupported head_dim %d", hd);
     return PIB_ERR_UNSUPP;
 }

@@ -45,9 +45,14 @@ pib_weight * pib_weight_alloc(int type, int64_t N, int64_t K);
 void pib_weight_drop_planes(pib_weight * w);
 
 // matrices the engine only multiplies with keep just their tiles (PIB_KEEP_PLANES=1: keep both forms, e.g. to run variant 1)
+// exact mode (PIB_EXACT=1, read when a model is loaded and when a context is created): every matmul keeps the reference's
+// summation order, so that logits are bit-identical to the CPU build's; the 32-element block types do that from the plane form
+bool pib_exact_mode() { const char * e = getenv("PIB_EXACT"); return e && atoi(e) != 0; }
+
 static void drop_planes_of(pib_model * m) {
     const char * keep = getenv("PIB_KEEP_PLANES");
     if (keep && atoi(keep) != 0) return;
+    if (pib_exact_mode() && m->wtype != PIB_TYPE_Q4_K) return;
     if (m->output) pib_weight_drop_planes(m->output);
     for (auto & L : m->layers) for (pib_weight * w : { L.wqkv, L.wv, L.wo, L.wgu, L.wdown }) if (w) pib_weight_drop_planes(w);
 }

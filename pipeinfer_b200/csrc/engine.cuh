@@ -145,6 +145,7 @@ struct pib_context {
 };
 
 // engine.cu
+bool          pib_exact_mode();      // PIB_EXACT=1
 pib_model *   pib_model_load_gguf(const char * path, int layer_begin, int layer_end, bool want_embd, bool want_output);
 pib_model *   pib_model_synthetic(int n_layer, int n_embd, int n_head, int n_head_kv, int n_ff, int n_vocab, int wtype,
                                   uint64_t seed, int flavour, float agree, int layer_begin, int layer_end, bool want_embd,

@@ -36,6 +36,7 @@
 #define LX_TILE_BYTES 2304
 #define LX_STAGES 3                 // records per warp ring: two in flight while one is multiplied
 #define LX_MAX_SEGS 24              // a CTA never gets more than ~8 tiles (tiles / slots + 2 pieces)
+#define LX_MAXB_W 8                 // largest batch of the warp-per-tile variant
 #define LX_TERMS 12                 // 8 lane sums + 4 min products per (row, token, super-block)
 
 __device__ __forceinline__ void lx_mma_u8s8(int (&c)[4], int a0, int a1, int a2, int a3, int b0, int b1) {
@@ -339,6 +340,215 @@ gemv_q4k_lane_kernel(const uint8_t * __restrict__ tiles, int nsb, int n_tiles, i
     }
 }
 
+// ---- warp-per-tile variant (many row tiles: gate|up, lm_head, qkv) ------------------------------------------------------------
+// Same arithmetic, other decomposition: a warp walks ITS tiles' super-blocks in order, so the twelve chains of an output stay in
+// that warp's registers (thread (g, t): lanes 2t, 2t+1 and min t of rows g and g + 8) -- no terms through shared memory, no CTA
+// barrier.  The weight stream is cut per WARP into equal pieces of records; a tile cut in two is started by the warp holding
+// its head (first thing it does) and finished by the next warp (last thing it does), the chain state (6 floats per thread and
+// token) going through global memory.  Needs at least as many tiles as warps in the grid, else every warp simply takes one tile.
+template <int BMAX>
+__global__ void __launch_bounds__(LX_THREADS, BMAX <= 2 ? 5 : (BMAX <= 4 ? 4 : 3))
+gemv_q4k_lanew_kernel(const uint8_t * __restrict__ tiles, int nsb, int n_tiles, int N, int K, const int2 * __restrict__ aqsl,
+                      const float * __restrict__ ad, const int16_t * __restrict__ asbs, int b, float * __restrict__ y,
+                      float * __restrict__ handoff, unsigned int * __restrict__ flags, lx_sync * __restrict__ sync,
+                      const int * __restrict__ cancel) {
+    extern __shared__ __align__(16) int lx_smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const int fstage_bytes = b * 512 + b * 16 + ((b * 4 + 15) & ~15);
+    uint8_t * W = reinterpret_cast<uint8_t *>(lx_smem) + warp * (LX_STAGES * LX_TILE_BYTES + 2 * fstage_bytes);   // this warp's rings
+    uint8_t * F = W + LX_STAGES * LX_TILE_BYTES;
+
+    // ---- this warp's piece of the weight stream, in records -------------------------------------------------------------------
+    const int       Wn = gridDim.x * LX_WARPS, gw = blockIdx.x * LX_WARPS + warp;
+    const long long U  = (long long) n_tiles * nsb;
+    const long long u0 = U * gw / Wn, u1 = U * (gw + 1) / Wn;
+    const int X = (int) (u0 / nsb), a = (int) (u0 % nsb);
+    const int Y = u1 > u0 ? (int) ((u1 - 1) / nsb) : X, e = u1 > u0 ? (int) (u1 - (long long) Y * nsb) : nsb;
+    const bool has_tail = a > 0 && u1 > u0, has_head = e < nsb && u1 > u0;
+    const int  F0 = has_tail ? X + 1 : X, F1 = has_head ? Y : Y + 1;
+    const int  nfull = u1 > u0 ? (F1 > F0 ? F1 - F0 : 0) : 0;
+    const int  nseg = (has_head ? 1 : 0) + nfull + (has_tail ? 1 : 0);
+    auto seg_of = [&](int i, int & tile, int & s0, int & s1, int & kind) {
+        if (has_head) { if (i == 0) { tile = Y; s0 = 0; s1 = e; kind = 0; return; } i--; }
+        if (i < nfull) { tile = F0 + i; s0 = 0; s1 = nsb; kind = 1; return; }
+        tile = X; s0 = a; s1 = nsb; kind = 2;
+    };
+    // prefetch cursors: weights (LX_STAGES - 1 records ahead) and activations (one ahead)
+    int pseg = 0, ps = 0, pend = 0, qseg = 0, qs = 0, qend = 0;
+    const uint8_t * nrec = tiles;
+    auto pseg_load = [&]() { if (pseg < nseg) { int tl, k; seg_of(pseg, tl, ps, pend, k); nrec = tiles + ((size_t) tl * nsb + ps) * LX_TILE_BYTES + lane * 16; } };
+    auto qseg_load = [&]() { if (qseg < nseg) { int tl, k; seg_of(qseg, tl, qs, qend, k); } };
+    pseg_load();
+    qseg_load();
+    const uint32_t ring  = (uint32_t) __cvta_generic_to_shared(W) + lane * 16;
+    const uint32_t fring = (uint32_t) __cvta_generic_to_shared(F);
+    auto issue = [&](int stage) {
+        if (pseg < nseg) {
+            const uint32_t dst = ring + stage * LX_TILE_BYTES;
+#pragma unroll
+            for (int ch = 0; ch < 4; ch++) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + ch * 512), "l"(nrec + ch * 512) : "memory");
+            if (lane < 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 2048), "l"(nrec + 2048) : "memory");
+            if (++ps < pend) nrec += LX_TILE_BYTES; else { pseg++; pseg_load(); }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    const uint8_t * xsrc = reinterpret_cast<const uint8_t *>(aqsl) + lane * 16;
+    auto issue_act = [&](int fstage) {
+        if (qseg < nseg) {
+            const uint32_t dst = fring + fstage * fstage_bytes;
+            for (int k = 0; k < b; k++)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + k * 512 + lane * 16), "l"(xsrc + ((size_t) k * nsb + qs) * 512) : "memory");
+            if (lane < b) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + b * 512 + lane * 16), "l"(asbs + ((size_t) lane * nsb + qs) * 8) : "memory");
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + b * 528 + lane * 4), "l"(ad + (size_t) lane * nsb + qs) : "memory");
+            }
+            if (++qs >= qend) { qseg++; qseg_load(); }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#pragma unroll
+    for (int i = 0; i < LX_STAGES - 1; i++) issue(i);          // weights are immutable: before the wait on the producer kernel
+    pib_pdl_wait();
+    pib_pdl_trigger();
+    issue_act(0);
+    const unsigned int ready = sync->epoch + 1;
+    const bool cancelled = PIB_CANCELLED(cancel);
+
+    const int b_active = (t == (g >> 1)) ? 1 : 0;
+    float acc[BMAX][4], accm[BMAX][2];
+    int   fbuf = 0, stage = 0;
+    bool  first_unit = true;
+    float * hbase = handoff + ((size_t) gw * LX_MAXB_W * 32 + lane) * 6;          // [warp][token][lane][6]
+
+    for (int seg = 0; seg < nseg && !cancelled; seg++) {
+        int tile, s0, s1, kind;
+        seg_of(seg, tile, s0, s1, kind);
+        if (kind == 2) {
+            const volatile unsigned int * f = flags + (gw - 1);
+            while (*f != ready) { if (PIB_CANCELLED(cancel)) break; }
+            __threadfence();
+            const float * hin = hbase - (size_t) LX_MAXB_W * 32 * 6;
+#pragma unroll
+            for (int k = 0; k < BMAX; k++)
+                if (k < b) {
+                    const float2 v0 = __ldcg(reinterpret_cast<const float2 *>(hin + k * 192)), v1 = __ldcg(reinterpret_cast<const float2 *>(hin + k * 192 + 2)),
+                                 v2 = __ldcg(reinterpret_cast<const float2 *>(hin + k * 192 + 4));
+                    acc[k][0] = v0.x; acc[k][1] = v0.y; acc[k][2] = v1.x; acc[k][3] = v1.y; accm[k][0] = v2.x; accm[k][1] = v2.y;
+                }
+        } else {
+#pragma unroll
+            for (int k = 0; k < BMAX; k++) { acc[k][0] = acc[k][1] = acc[k][2] = acc[k][3] = 0.f; accm[k][0] = accm[k][1] = 0.f; }
+        }
+        for (int s = s0; s < s1; s++) {
+            __syncwarp();                         // every lane is done with the stages about to be refilled
+            issue_act(fbuf ^ 1);
+            issue((stage + LX_STAGES - 1) % LX_STAGES);
+            if (first_unit) { asm volatile("cp.async.wait_group 2;" ::: "memory"); first_unit = false; }
+            else asm volatile("cp.async.wait_group 3;" ::: "memory");
+            __syncwarp();
+            const uint8_t * rs = W + stage * LX_TILE_BYTES;
+            int4 wq[4];
+#pragma unroll
+            for (int ch = 0; ch < 4; ch++) wq[ch] = *reinterpret_cast<const int4 *>(rs + ch * 512 + lane * 16);
+            const lx_hdr H0 = lx_decode(*reinterpret_cast<const int4 *>(rs + 2048 + g * 16)), H1 = lx_decode(*reinterpret_cast<const int4 *>(rs + 2048 + (g + 8) * 16));
+            const int mw0 = (int) (((t < 2 ? H0.m_lo : H0.m_hi) >> (16 * (t & 1))) & 0xffffu);
+            const int mw1 = (int) (((t < 2 ? H1.m_lo : H1.m_hi) >> (16 * (t & 1))) & 0xffffu);
+            const uint8_t * fs = F + fbuf * fstage_bytes;
+            const uint8_t * xs = fs + g * 64;
+            const int *     ss = reinterpret_cast<const int *>(fs + b * 512) + t;
+            const float *   dxs = reinterpret_cast<const float *>(fs + b * 528);
+#pragma unroll
+            for (int k0 = 0; k0 < BMAX; k0 += 2) {
+                if (k0 < b) {
+                    constexpr int TB = BMAX > 1 ? 2 : 1;
+                    int sumi[TB][4], sumh[TB][4];
+#pragma unroll
+                    for (int k = 0; k < TB; k++)
+#pragma unroll
+                        for (int i = 0; i < 4; i++) { sumi[k][i] = 0; sumh[k][i] = 0; }
+                    const int xk1 = (TB > 1 && k0 + 1 < b) ? 512 : 0;        // an odd batch repeats its last token (computed, not used)
+#pragma unroll
+                    for (int ch = 0; ch < 4; ch++) {
+                        const uint32_t wx = (uint32_t) wq[ch].x, wy = (uint32_t) wq[ch].y, wz = (uint32_t) wq[ch].z, ww = (uint32_t) wq[ch].w;
+                        const int al0 = (int) (wx & 0x0F0F0F0Fu), al1 = (int) (wz & 0x0F0F0F0Fu), al2 = (int) (wy & 0x0F0F0F0Fu), al3 = (int) (ww & 0x0F0F0F0Fu);
+                        const int ah0 = (int) (wx & 0xF0F0F0F0u), ah1 = (int) (wz & 0xF0F0F0F0u), ah2 = (int) (wy & 0xF0F0F0F0u), ah3 = (int) (ww & 0xF0F0F0F0u);
+                        const int j0 = 2 * ch, j1 = 2 * ch + 1;
+                        const int sc0_lo = (int) __byte_perm(j0 < 4 ? H0.sc_lo : H0.sc_hi, 0, 0x4440 + (j0 & 3));
+                        const int sc1_lo = (int) __byte_perm(j0 < 4 ? H1.sc_lo : H1.sc_hi, 0, 0x4440 + (j0 & 3));
+                        const int sc0_hi = (int) __byte_perm(j1 < 4 ? H0.sc_lo : H0.sc_hi, 0, 0x4440 + (j1 & 3));
+                        const int sc1_hi = (int) __byte_perm(j1 < 4 ? H1.sc_lo : H1.sc_hi, 0, 0x4440 + (j1 & 3));
+#pragma unroll
+                        for (int k = 0; k < TB; k++) {
+                            int4 xq = *reinterpret_cast<const int4 *>(xs + k0 * 512 + (k ? xk1 : 0) + ch * 16);
+                            if (!b_active) xq = make_int4(0, 0, 0, 0);
+                            int c_lo[4] = { 0, 0, 0, 0 }, c_hi[4] = { 0, 0, 0, 0 };
+                            lx_mma_u8s8(c_lo, al0, al1, al2, al3, xq.x, xq.y);
+                            lx_mma_u8s8(c_hi, ah0, ah1, ah2, ah3, xq.z, xq.w);
+                            sumi[k][0] += sc0_lo * c_lo[0]; sumh[k][0] += sc0_hi * c_hi[0];
+                            sumi[k][1] += sc0_lo * c_lo[1]; sumh[k][1] += sc0_hi * c_hi[1];
+                            sumi[k][2] += sc1_lo * c_lo[2]; sumh[k][2] += sc1_hi * c_hi[2];
+                            sumi[k][3] += sc1_lo * c_lo[3]; sumh[k][3] += sc1_hi * c_hi[3];
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < TB; k++) {
+                        if (k0 + k < BMAX && (k == 0 || k0 + k < b)) {
+                            const float dx = dxs[k0 + k];
+                            const float d0 = __fmul_rn(dx, H0.d), d1 = __fmul_rn(dx, H1.d);
+                            acc[k0 + k][0] = fmaf(d0, (float) (sumi[k][0] + (sumh[k][0] >> 4)), acc[k0 + k][0]);
+                            acc[k0 + k][1] = fmaf(d0, (float) (sumi[k][1] + (sumh[k][1] >> 4)), acc[k0 + k][1]);
+                            acc[k0 + k][2] = fmaf(d1, (float) (sumi[k][2] + (sumh[k][2] >> 4)), acc[k0 + k][2]);
+                            acc[k0 + k][3] = fmaf(d1, (float) (sumi[k][3] + (sumh[k][3] >> 4)), acc[k0 + k][3]);
+                            const int q8 = ss[(k0 + k) * 4];
+                            accm[k0 + k][0] = fmaf(__fmul_rn(-dx, H0.dmin), (float) __dp2a_lo(q8, mw0, 0), accm[k0 + k][0]);
+                            accm[k0 + k][1] = fmaf(__fmul_rn(-dx, H1.dmin), (float) __dp2a_lo(q8, mw1, 0), accm[k0 + k][1]);
+                        }
+                    }
+                }
+            }
+            fbuf ^= 1;
+            stage = stage + 1 == LX_STAGES ? 0 : stage + 1;
+        }
+        if (kind == 0) {
+#pragma unroll
+            for (int k = 0; k < BMAX; k++)
+                if (k < b) {
+                    __stcg(reinterpret_cast<float2 *>(hbase + k * 192), make_float2(acc[k][0], acc[k][1]));
+                    __stcg(reinterpret_cast<float2 *>(hbase + k * 192 + 2), make_float2(acc[k][2], acc[k][3]));
+                    __stcg(reinterpret_cast<float2 *>(hbase + k * 192 + 4), make_float2(accm[k][0], accm[k][1]));
+                }
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) { __threadfence(); *(volatile unsigned int *) (flags + gw) = ready; }
+        } else {
+            // hsum_float_8 over the quad: thread t holds lanes 2t, 2t+1; ((a0+a4)+(a2+a6)) + ((a1+a5)+(a3+a7)), then the mins ((m0+m2)+(m1+m3))
+            const int r0 = tile * 16 + g, r1 = r0 + 8;
+#pragma unroll
+            for (int k = 0; k < BMAX; k++)
+                if (k < b) {
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        float p = acc[k][2 * h], q = acc[k][2 * h + 1], m = accm[k][h];
+                        p = __fadd_rn(p, __shfl_xor_sync(0xffffffffu, p, 2));
+                        q = __fadd_rn(q, __shfl_xor_sync(0xffffffffu, q, 2));
+                        p = __fadd_rn(p, __shfl_xor_sync(0xffffffffu, p, 1));
+                        q = __fadd_rn(q, __shfl_xor_sync(0xffffffffu, q, 1));
+                        m = __fadd_rn(m, __shfl_xor_sync(0xffffffffu, m, 2));
+                        m = __fadd_rn(m, __shfl_xor_sync(0xffffffffu, m, 1));
+                        const int row = h ? r1 : r0;
+                        if (t == 0 && row < N) y[(size_t) k * N + row] = __fadd_rn(__fadd_rn(p, q), m);
+                    }
+                }
+        }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        if (atomicAdd(&sync->ticket, 1u) == gridDim.x - 1) { sync->ticket = 0; __threadfence(); atomicAdd(&sync->epoch, 1u); }
+    }
+}
+
 // ---- launcher -----------------------------------------------------------------------------------------------------------
 struct lx_scratch { float * handoff = nullptr; unsigned int * flags = nullptr; lx_sync * sync = nullptr; int max_ctas = 0; };
 static std::map<std::pair<int, cudaStream_t>, lx_scratch> g_lx;
@@ -358,10 +568,11 @@ static int lx_get_scratch(cudaStream_t st, lx_scratch ** out) {
     lx_scratch & s = g_lx[std::make_pair(dev, st)];
     if (!s.sync) {
         const int max_ctas = 5 * pib_num_sms();
-        const size_t hb = (size_t) max_ctas * PIB_MAX_BATCH * LX_THREADS * sizeof(float2);     // [cta][token][thread] {lane acc, min acc}
-        if (cudaMalloc(&s.handoff, hb) != cudaSuccess || cudaMalloc(&s.flags, (size_t) max_ctas * 4) != cudaSuccess ||
+        // [cta][token][thread] {lane acc, min acc} for the CTA-per-tile kernel, [warp][token][lane][6] for the warp-per-tile one
+        const size_t hb = (size_t) max_ctas * LX_WARPS * (PIB_MAX_BATCH * 32 * sizeof(float2) > LX_MAXB_W * 32 * 6 * sizeof(float) ? PIB_MAX_BATCH * 32 * sizeof(float2) : LX_MAXB_W * 32 * 6 * sizeof(float));
+        if (cudaMalloc(&s.handoff, hb) != cudaSuccess || cudaMalloc(&s.flags, (size_t) max_ctas * LX_WARPS * 4) != cudaSuccess ||
             cudaMalloc(&s.sync, sizeof(lx_sync)) != cudaSuccess) { cudaGetLastError(); return PIB_ERR_NOMEM; }
-        cudaMemset(s.flags, 0, (size_t) max_ctas * 4);
+        cudaMemset(s.flags, 0, (size_t) max_ctas * LX_WARPS * 4);
         cudaMemset(s.sync, 0, sizeof(lx_sync));
         s.max_ctas = max_ctas;
     }
@@ -397,13 +608,50 @@ static int lx_launch(const pib_weight * w, const void * act_dev, int b, float * 
     return PIB_OK;
 }
 
+static size_t lxw_smem_bytes(int b) { return (size_t) LX_WARPS * (LX_STAGES * LX_TILE_BYTES + 2 * (b * 512 + b * 16 + ((b * 4 + 15) & ~15))); }
+
+template <int BMAX>
+static int lxw_launch(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st, lx_scratch * s) {
+    const size_t smem = lxw_smem_bytes(b);
+    static bool configured = false;
+    static int  per_sm_of[PIB_MAX_BATCH + 1];
+    if (!configured) {
+        PIB_CHECK(cudaFuncSetAttribute(gemv_q4k_lanew_kernel<BMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) lxw_smem_bytes(LX_MAXB_W)));
+        for (int i = 0; i <= PIB_MAX_BATCH; i++) per_sm_of[i] = 0;
+        configured = true;
+    }
+    if (!per_sm_of[b]) PIB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_of[b], gemv_q4k_lanew_kernel<BMAX>, LX_THREADS, smem));
+    int per_sm = per_sm_of[b];
+    if (per_sm < 1) { pib_set_error("pib_gemv: warp-per-tile kernel does not fit (b = %d)", b); return PIB_ERR_UNSUPP; }
+    if (per_sm > 5) per_sm = 5;
+    const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    const int slots = per_sm * pib_num_sms();                           // CTAs; 4 warps each
+    // balanced pieces need a tile or more per warp; with fewer tiles every warp takes one tile
+    const int grid = n_tiles >= slots * LX_WARPS ? slots : n_tiles / LX_WARPS;        // never more warps than tiles: a piece is a tile or more
+    const pib_act_layout L   = pib_act_layout_of(w->type, w->K, b);
+    const uint8_t *      act = (const uint8_t *) act_dev;
+    pib_launch(gemv_q4k_lanew_kernel<BMAX>, dim3(grid), dim3(LX_THREADS), smem, st, w->tiles, nsb, n_tiles, (int) w->N, (int) w->K,
+               (const int2 *) (act + L.qsl_off), (const float *) (act + L.d_off), (const int16_t *) (act + L.sbs_off), b, y_dev,
+               s->handoff, s->flags, s->sync, cancel);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+
 bool pib_gemv_mma_supported(const pib_weight * w, int b);
+static int lx_mode() { static int m = -1; if (m < 0) { const char * e = getenv("PIB_Q4K_MODE"); m = e ? atoi(e) : 0; } return m; }     // 1: CTA-per-tile always, 2: warp-per-tile whenever b <= 8
 
 // variant 2 / default for Q4_K
 int pib_gemv_q4k_lane(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
     if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: the Q4_K kernel needs Q4_K weights with tiles"); return PIB_ERR_UNSUPP; }
     lx_scratch * s = nullptr;
     if (lx_get_scratch(st, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
+    const int n_tiles = (int) ((w->N + 15) / 16);
+    if (b <= LX_MAXB_W && lx_mode() != 1 && n_tiles >= LX_WARPS && (n_tiles >= 600 || lx_mode() == 2)) {
+        if (b <= 1) return lxw_launch<1>(w, act_dev, b, y_dev, cancel, st, s);
+        if (b <= 2) return lxw_launch<2>(w, act_dev, b, y_dev, cancel, st, s);
+        if (b <= 4) return lxw_launch<4>(w, act_dev, b, y_dev, cancel, st, s);
+        return lxw_launch<8>(w, act_dev, b, y_dev, cancel, st, s);
+    }
     if (b <= 1) return lx_launch<1, 1>(w, act_dev, b, y_dev, cancel, st, s);
     if (b <= 2) return lx_launch<2, 2>(w, act_dev, b, y_dev, cancel, st, s);
     if (b <= 4) return lx_launch<4, 2>(w, act_dev, b, y_dev, cancel, st, s);

@@ -125,11 +125,15 @@ int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float *
                       cudaStream_t st) {
     if (w->type == PIB_TYPE_Q6_K) return pib_gemv_q6k(w, act_dev, b, y_dev, cancel, st);
     if (w->type == PIB_TYPE_Q5_K) return pib_gemv_q5k(w, act_dev, b, y_dev, cancel, st);
+    // variants: 0 / 2 the fast tensor-core kernels (fp32 block terms added in the kernel's own order), 1 dp4a, 3 TMA-staged persistent
+    // (Q4_K), 4 the reference's summation order restated literally (one thread per output; bit-identical to the CPU, slow), 6 the
+    // tensor-core kernel that keeps the reference's order (Q4_K; bit-identical to the CPU).  7 = "exact mode": 6 where it exists, else 4.
+    if (variant == 7) variant = (w->type == PIB_TYPE_Q4_K && pib_gemv_mma_supported(w, b)) ? 6 : 4;
     if (variant == 4) return pib_gemv_exact_ref(w, act_dev, b, y_dev, cancel, st);
     const bool tc = pib_gemv_mma_supported(w, b);
+    if (variant == 6 && tc) return pib_gemv_q4k_lane(w, act_dev, b, y_dev, cancel, st);
     if (variant == 3 && tc) return pib_gemv_mma(w, act_dev, b, y_dev, cancel, st);
-    if ((variant == 2 || variant == 0) && tc) return pib_gemv_q4k_lane(w, act_dev, b, y_dev, cancel, st);
-    if (variant == 5 && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);      // round-1 kernel (fp32 terms added in another order)
+    if ((variant == 2 || variant == 0) && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);
     if ((variant == 2 || variant == 0) && pib_gemv_blk32_supported(w, b)) return pib_gemv_blk32(w, act_dev, b, y_dev, cancel, st);
     return pib_gemv_dp4a(w, act_dev, b, y_dev, cancel, st);
 }
@@ -140,8 +144,8 @@ extern "C" int pib_gemv(const pib_weight * w, const void * act_dev, int b, float
         return PIB_ERR_ARG;
     }
     if (w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K) variant = 0;            // one kernel for these types
-    if ((variant == 3 && !pib_gemv_mma_supported(w, b)) || (variant == 2 && !pib_gemv_mma_supported(w, b) && !pib_gemv_blk32_supported(w, b))) {
-        pib_set_error("pib_gemv: variant 2 needs tiles (Q4_K, Q4_0, Q8_0), variant 3 Q4_K");
+    if (((variant == 3 || variant == 6) && !pib_gemv_mma_supported(w, b)) || (variant == 2 && !pib_gemv_mma_supported(w, b) && !pib_gemv_blk32_supported(w, b))) {
+        pib_set_error("pib_gemv: variant 2 needs tiles (Q4_K, Q4_0, Q8_0), variants 3 and 6 Q4_K");
         return PIB_ERR_UNSUPP;
     }
     return pib_gemv_internal(w, act_dev, b, y_dev, variant, nullptr, (cudaStream_t) s);

@@ -133,6 +133,7 @@ struct llama_context * llama_pib_new_context_stage(struct llama_model * model, u
     lc->model = model;
     lc->c     = c;
     const char * v = getenv("PIB_GEMV_VARIANT");
+    if (pib_exact_mode()) c->gemv_variant = 7;          // the kernels that keep the reference's summation order
     if (v) c->gemv_variant = atoi(v);
     return lc;
 }

@@ -14,7 +14,7 @@ TYPES = list(op.TYPE_NAMES.items())
 REL_TOL = 3e-5     # of max|y|: fp32 reassociation over <= 896 block terms (the kernels that add the block terms in their own order)
 # kernels that keep the reference's summation order (eight fp32 lane accumulators per output, block after block, then its
 # reduction tree) return the oracle's bits: (weight type, variant) pairs held to np.array_equal
-EXACT = {(op.TYPE_Q4_K, 0), (op.TYPE_Q4_K, 2), (op.TYPE_Q4_K, 4), (op.TYPE_Q4_0, 4), (op.TYPE_Q8_0, 4)}
+EXACT = {(op.TYPE_Q4_K, 6), (op.TYPE_Q4_K, 4), (op.TYPE_Q4_0, 4), (op.TYPE_Q8_0, 4), (op.TYPE_Q4_K, 7), (op.TYPE_Q4_0, 7), (op.TYPE_Q8_0, 7)}
 
 
 def check(got, ref, wt, variant, what=None):
@@ -101,15 +101,16 @@ def test_get_rows_bit_exact(lib, kern, name, wt):
 
 def variants(wt):
     # 1 = dp4a (all types), 2 = the default tensor-core kernel (all types), 3 = TMA-staged persistent kernel (Q4_K only),
-    # 4 = the reference's summation order restated literally, one thread per output (all types)
-    return [1, 2, 3, 4] if wt == op.TYPE_Q4_K else [1, 2, 4]
+    # 4 = the reference's summation order restated literally, one thread per output (all types), 6 = the tensor-core kernel that
+    # keeps the reference's order (Q4_K only)
+    return [1, 2, 3, 4, 6] if wt == op.TYPE_Q4_K else [1, 2, 4]
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 6])
 @pytest.mark.parametrize("name,wt", TYPES)
 def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
     if variant not in variants(wt):
-        pytest.skip("variant 3 is Q4_K only")
+        pytest.skip("variants 3 and 6 are Q4_K only")
     w, x, y = kern[name + "_w"], kern[name + "_x"], kern[name + "_y"]
     h = lib.weight_upload(wt, w, x.shape[1])
     got = lib.mul_mat(h, x, w.shape[0], variant)
@@ -117,12 +118,12 @@ def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
     lib.L.pib_weight_free(h)
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 6])
 @pytest.mark.parametrize("name,wt", TYPES)
 @pytest.mark.parametrize("b", [1, 2, 5, 8, 9, 16])
 def test_mul_mat_vs_oracle_batches(lib, oracle, name, wt, b, variant):
     if variant not in variants(wt):
-        pytest.skip("variant 3 is Q4_K only")
+        pytest.skip("variants 3 and 6 are Q4_K only")
     rng = np.random.default_rng(100 + b)
     N, K = 96, 2048
     w = rand_blocks(rng, wt, N, K)
@@ -188,6 +189,10 @@ def test_mul_mat_benchmark_shapes_vs_oracle(lib, oracle, wt, N, K):
         got = lib.mul_mat(h, x, N, 0)
         assert np.isfinite(got).all()
         check(np.ascontiguousarray(got[:, rows]), ref, wt, 0, b)
+        if wt == op.TYPE_Q4_K:          # the order-keeping kernel, both decompositions (PIB_Q4K_MODE picks; default by shape)
+            ex = lib.mul_mat(h, x, N, 6)
+            check(np.ascontiguousarray(ex[:, rows]), ref, wt, 6, b)
+            assert np.abs(ex - got).max() <= REL_TOL * max(1.0, np.abs(got).max())
         # every row, cheaply: the default kernel against the simple dp4a kernel (same integer sums, another fp32 order)
         if wt == op.TYPE_Q4_0:
             alt = lib.mul_mat(h, x, N, 1)
