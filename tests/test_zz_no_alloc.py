@@ -31,9 +31,9 @@ def rand_q4k(rng, N, K):
 
 # (N, K, b, k splits the launcher picks on 148 SMs).  The first five go through the built-in scratch array: the 7B attention
 # projection (256 row tiles, 2 splits), a 128-tile matrix (4), the TinyLlama fused qkv (160 tiles, 2), a 64-tile matrix (8
-# splits of 4 super-blocks) and a ragged 13-tile one (2); the last has 512 row tiles and is not split (no scratch used).
+# splits of 4 super-blocks) and a ragged 13-tile one (4); the last has 512 row tiles and is not split (no scratch used).
 @pytest.mark.parametrize("N,K,b,splits", [(4096, 4096, 4, 2), (2048, 11008 // 256 * 256, 16, 4), (2560, 2048, 3, 2), (1024, 8192, 16, 8),
-                                          (200, 4096, 1, 2), (8192, 8192, 16, 1)])
+                                          (200, 4096, 1, 4), (8192, 8192, 16, 1)])
 def test_noalloc_matches_regular_entry_point_and_oracle_twice(lib, oracle, N, K, b, splits):
     rng = np.random.default_rng(N + b)
     wt = op.TYPE_Q4_K
