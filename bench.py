@@ -55,7 +55,25 @@ KIND = {0: "qkv", 1: "attn_out", 2: "gate_up", 3: "down", 4: "lm_head", 5: "attn
 
 
 def nvlink_tx_kib(gpu):
-    """sum of the per-link NVLink transmit counters of one GPU (`nvidia-smi nvlink -gt d`), or None where unsupported"""
+    """NVLink transmit counter of one GPU in KiB (all links), or None where the driver exposes none: NVML field values first
+    (NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, KiB since driver load), then the per-link table of `nvidia-smi nvlink -gt d`"""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu)
+        fid = getattr(pynvml, "NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX", 138)
+        try:
+            vals = pynvml.nvmlDeviceGetFieldValues(h, [(fid, 0xFFFFFFFF)])      # scope: all links
+        except TypeError:
+            vals = pynvml.nvmlDeviceGetFieldValues(h, [fid])
+        v = vals[0]
+        if v.nvmlReturn == 0:
+            for name in ("ullVal", "ulVal", "uiVal"):
+                x = getattr(v.value, name, None)
+                if x:
+                    return int(x)
+    except Exception:
+        pass
     try:
         out = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(gpu)], capture_output=True, text=True, timeout=20).stdout
         vals = [int(x) for x in re.findall(r"Data Tx:\s*(\d+)\s*KiB", out)]
@@ -117,10 +135,10 @@ def run_reference_sample(cfg_name, args, budget="small"):
     cores = os.cpu_count() or 1
     n_tgt_ranks = 2
     threads = max(1, cores // (n_tgt_ranks + 1))
-    depths = (2, 4) if budget == "small" else (2, 6)
-    n_pred = 12 if budget == "small" else 24
+    depths = (2, 4) if budget == "small" else (2, 4, 6)
+    n_pred = 24 if budget == "small" else 64
     if cfg_name == "tiny":
-        depths = (2, 4)
+        depths = (2, 4) if budget == "small" else (2, 3, 4)
     tmp = "/tmp/pib_ref_%d" % os.getpid()
     os.makedirs(tmp, exist_ok=True)
     mk = [sys.executable, os.path.join(ROOT, "tools", "make_gguf.py"), "--direct", "--quant", TYPE_NAME[wt]]
@@ -151,17 +169,22 @@ def run_reference_sample(cfg_name, args, budget="small"):
                       wall_s=time.time() - t0)
         os.unlink(tgt)
     os.unlink(dft)
-    d0, d1 = depths
-    t0_tok, t1_tok = res[d0]["seconds"] / res[d0]["tokens"], res[d1]["seconds"] / res[d1]["tokens"]
-    per_layer = max(0.0, (t1_tok - t0_tok) / (d1 - d0))
-    fixed = max(0.0, t0_tok - per_layer * d0)
+    # seconds per accepted token as a straight line in the number of target layers (least squares over the depths run)
+    xs = [float(d) for d in depths]
+    ys = [res[d]["seconds"] / res[d]["tokens"] for d in depths]
+    n  = len(xs)
+    mx, my = sum(xs) / n, sum(ys) / n
+    per_layer = max(0.0, sum((x - mx) * (y - my) for x, y in zip(xs, ys)) / sum((x - mx) ** 2 for x in xs))
+    fixed = max(0.0, my - per_layer * mx)
     full = fixed + per_layer * L
+    resid = max(abs(fixed + per_layer * x - y) / y for x, y in zip(xs, ys))
     sample = ("reference `speculative` (oracle/_ref) under the mini-MPI shim, 2 target ranks + 1 draft rank x %d threads, "
-              "same flags; %s-width target at %d and %d layers (%.3f / %.3f s per accepted token), full draft; value = "
-              "1 / (%.4f + %d * %.4f) s extrapolated to %d layers" % (threads, "x".join(map(str, (E, FF))), d0, d1, t0_tok, t1_tok,
-                                                                     fixed, L, per_layer, L))
+              "same flags, %d tokens predicted; %s-width target at %s layers (%s s per accepted token), full draft; value = "
+              "1 / (%.4f + %d * %.4f) s extrapolated to %d layers, worst relative residual of the fit %.3f"
+              % (threads, n_pred, "x".join(map(str, (E, FF))), "/".join(str(d) for d in depths), " / ".join("%.3f" % y for y in ys),
+                 fixed, L, per_layer, L, resid))
     return dict(value=1.0 / full if full > 0 else None, unit="tokens/s", cores=cores, kind="reference", sample=sample,
-                raw={str(k): v for k, v in res.items()}, itl_est_s=full)
+                raw={str(k): v for k, v in res.items()}, itl_est_s=full, fit_residual=resid)
 
 
 # --------------------------------------------------------------------------------------------------------------------
@@ -183,10 +206,12 @@ def main():
                     help="bound on target runs in flight: 0 = the reference's behaviour (unbounded), -1 = number of pipeline stages + 1")
     ap.add_argument("--mode", default="speculative", choices=["speculative", "plain", "classic"],
                     help="plain = non-speculative greedy decoding through the same pipeline (the reference's `main`): the second denominator")
-    ap.add_argument("--sched-policy", default="reference", choices=["reference", "chain1", "chain2", "chain3"],
-                    help="scheduler policy: the reference's, or the experimental chain-continuation policies (PIB_SCHED_CHAIN, DESIGN.md §9)")
+    ap.add_argument("--sched-policy", default="chain2", choices=["reference", "chain1", "chain2", "chain3"],
+                    help="scheduler policy: chain2 (the library's default: text-identical to the reference's policy, checked in the first "
+                         "warm-up step), the reference's own, or the other chain-continuation policies (PIB_SCHED_CHAIN, DESIGN.md §9)")
     ap.add_argument("--no-draft-priority", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-plain", action="store_true", help="skip the non-speculative generation after the timed steps (plain_tok_s, plain_tokens_sha)")
     ap.add_argument("--layer-split", default="", help="comma-separated per-stage weights, as the reference's --mpi-layer-split")
     ap.add_argument("--head-share", type=float, default=None, help="share of the target's layers on the head GPU (which also runs the draft)")
     args = ap.parse_args()
@@ -330,6 +355,18 @@ def main():
     clk = clocks.stop()
     lib.llama_pib_profile_layer(tgt.ctx, -1)
     k1 = launches()
+    # outside the timed region: one NON-SPECULATIVE greedy generation through the same pipeline (the reference's `main`): the second
+    # denominator of north_star, measured in the same run, and the text every speculative step must reproduce
+    plain = None
+    if args.mode == "speculative" and not args.no_plain:
+        if rank != 0:
+            tgt.serve()
+        else:
+            lib.llama_kv_cache_clear(tgt.ctx)
+            ptoks, pres, pitl = llama.plain_generate(tgt, prompt, args.n_predict)
+            if world > 1:
+                tgt.pause()
+            plain = {"tokens": ptoks, "tok_s": pres["n_predict"] / pres["t_decode_s"]}
     io1 = [io(c) for c in ctxs]
     tr1 = pipeline.traffic()
     nv1 = nvlink_tx_kib(dev) if world > 1 else None
@@ -417,6 +454,19 @@ def main():
             "e2e": {"value": n_tok / (wall_ms / 1000.0), "unit": "tokens/s", "h2d_bytes_per_step": h2d // args.steps,
                     "d2h_bytes_per_step": d2h // args.steps},
             "gpu_launches": int(launches_all), "weights_gb": wbytes_all / 1e9, "model_build_s": t_load}
+    # the generated ids, hashed: the same value at every N (and equal to the plain-greedy hash) shows that the N-stage pipeline and
+    # the speculative scheduler produce the text of single-GPU greedy decoding
+    import hashlib
+
+    def sha(ids):
+        return hashlib.sha256(b"".join(int(t).to_bytes(4, "little", signed=True) for t in ids)).hexdigest()[:16]
+
+    line["tokens_sha"] = sha(toks[:args.n_predict])
+    if plain is not None:
+        line["plain_tokens_sha"] = sha(plain["tokens"][:args.n_predict])
+        line["plain_tok_s"] = plain["tok_s"]
+        line["speedup_over_plain"] = line["value"] / plain["tok_s"]
+        line["text_equals_plain_greedy"] = toks[:args.n_predict] == plain["tokens"][:args.n_predict]
     if hops is not None:
         line["nvlink_hops"] = {"per_rank_over_timed_steps": hops, "formula": "n_tokens * n_embd * 4 B of fp32 activations per hop (%d B per token) + 96 B per sampled row back to the head" % (E * 4)}
     print(json.dumps(line))

@@ -10,6 +10,13 @@ import pytest
 from tests.sched_sim import sim
 
 
+
+@pytest.fixture(autouse=True)
+def _reference_policy_unless_a_test_says_otherwise(monkeypatch):
+    """the differential tests compare with the reference's own scheduler, i.e. policy 0; the library's default is chain policy 2"""
+    monkeypatch.setenv("PIB_SCHED_CHAIN", "0")
+
+
 def check(r, n_predict):
     assert r["error"] == "" or "no slot" in r["error"] or r["target"]["refused"] + r["draft"]["refused"] > 0, r["error"]
     assert r["tokens"] == r["truth"], [i for i, (a, b) in enumerate(zip(r["tokens"], r["truth"])) if a != b][:4]
@@ -68,9 +75,12 @@ def test_the_two_reference_behaviours_that_corrupt_context_are_fixed(case, monke
     to a context with a hole: the text is not the greedy text.  The default avoids both."""
     c, kw = HAZARD_CASES[case]
     monkeypatch.setenv("PIB_REFERENCE_HAZARDS", "1")
+    monkeypatch.setenv("PIB_SCHED_CHAIN", "0")            # the reference's policy (the library's default is chain policy 2)
     r = sim.run(sim.default_config(**c), **kw)
     assert r["tokens"] != r["truth"]
     monkeypatch.delenv("PIB_REFERENCE_HAZARDS")
+    check(sim.run(sim.default_config(**c), **kw), 96)
+    monkeypatch.delenv("PIB_SCHED_CHAIN")
     check(sim.run(sim.default_config(**c), **kw), 96)
 
 
