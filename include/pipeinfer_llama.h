@@ -216,6 +216,16 @@ void         llama_log_set(void (*log_callback)(int level, const char * text, vo
 /* ---- additive extensions (no counterpart in llama.h; needed for device-side acceptance) ---- */
 /* sorted top-8 {id, logit, p} of logits row i of the last finished run: 96 bytes instead of n_vocab floats */
 int  llama_pib_get_top8(struct llama_context * ctx, int32_t i, llama_token_data * out8);
+/* Draft-vs-target acceptance on the device (the walk of examples/speculative/speculative.cpp:439-560 under greedy sampling).
+ * set_accept_table describes the verification batch that the NEXT llama_start_async_decode / llama_decode on `ctx` starts: for
+ * each of n_branches (<= 8) draft branches its length len[s] (-1: inactive), and for depth i the batch row rows[s*stride+i] whose
+ * logits are sampled at that depth (i <= len[s]) and the drafted token toks[s*stride+i] it is compared with (i < len[s]); `keep`
+ * = the branch the walk starts on, `speculative` = 0 stops after the first sample.  The last pipeline stage then runs the walk
+ * right after sampling, and after llama_finish_async_decode llama_pib_get_accepted returns the ids sampled along it (count
+ * returned; -1 if the run had no table) and the branch kept: 8 + 4 n bytes cross to the host instead of 96 bytes per row. */
+void    llama_pib_set_accept_table(struct llama_context * ctx, int32_t n_branches, int32_t keep, int32_t speculative, const int32_t * len,
+                                   const int32_t * rows, const int32_t * toks, int32_t depth_stride);
+int32_t llama_pib_get_accepted(struct llama_context * ctx, int32_t * ids, int32_t cap, int32_t * s_keep);
 /* logit bias applied on the device before argmax (the reference adds it on the host, common/sampling.cpp:134-136) */
 void llama_pib_set_logit_bias(struct llama_context * ctx, const llama_token * ids, const float * bias, int n);
 /* random-init model of the llama architecture generated directly in HBM (no file); flavour 0 iid, 1 bigram */

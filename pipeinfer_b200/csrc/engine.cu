@@ -41,6 +41,7 @@ int  pib_attention(const __half * q16, const __half * kc, const __half * vc, con
                    cudaStream_t st);
 int  pib_sample_topk(float * logits_dev, int n_rows, int n_vocab, const int32_t * bias_ids_dev, const float * bias_val_dev, int n_bias,
                      void * out_dev, const uint8_t * desc, const int * cancel, cudaStream_t st);
+int  pib_accept_walk(const void * rows_dev, const uint8_t * desc, void * out_dev, const int * cancel, cudaStream_t st);
 pib_weight * pib_weight_alloc(int type, int64_t N, int64_t K);
 void pib_weight_drop_planes(pib_weight * w);
 
@@ -442,6 +443,7 @@ pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_st
     CK(cudaMalloc(&c->ops_dev, sizeof(KvOp) * c->ops_cap));
     c->runs.resize(64);
     for (int i = 0; i < (int) c->runs.size(); i++) c->runs[i].id = i;
+    if (stage.size > 1 && pib_pipe_hop_setup(c) != PIB_OK) goto fail;
     return c;
 fail:
     pib_context_free(c);
@@ -451,6 +453,7 @@ fail:
 void pib_context_free(pib_context * c) {
     if (!c) return;
     if (c->stream) cudaStreamSynchronize(c->stream);
+    pib_pipe_hop_free(c);
     kv_device_free(&c->kvd);
     void * bufs[] = { c->vsep, c->kcache, c->vcache, c->x, c->x2, c->qkv, c->att, c->proj, c->gu, c->q16, c->mask, c->act, c->rope,
                       c->cancel_table, c->desc_dev, c->ops_dev, c->bias_ids_dev, c->bias_val_dev, c->logits_fetch_dev };
@@ -463,6 +466,8 @@ void pib_context_free(pib_context * c) {
         if (r.logits) cudaFree(r.logits);
         if (r.res_dev) cudaFree(r.res_dev);
         if (r.res_host) cudaFreeHost(r.res_host);
+        if (r.acc_dev) cudaFree(r.acc_dev);
+        if (r.acc_host) cudaFreeHost(r.acc_host);
     }
     for (auto e : c->desc_ev) if (e) cudaEventDestroy(e);
     if (c->cancel_ev) cudaEventDestroy(c->cancel_ev);
@@ -557,6 +562,7 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
         if (pr__) { cudaEventRecord(r__.e1, st); c->prof.push_back(r__); }                                             \
     } while (0)
     if (part & 1) {
+        if (c->hop_peer && !c->stage.first()) RC(pib_hop_recv_launch(c, ntok, st));
         RC(kv_device_mask(&c->kvd, tpos, tbits, ntok, c->mask, st));
         if (c->stage.first()) RC(pib_get_rows(m->tok_embd, tok, ntok, c->x, st));
     }
@@ -599,6 +605,10 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
             GEMV(4, c->prof_layer >= 0 ? c->prof_layer : -2, m->output, lg);
             RC(pib_sample_topk(lg, ntok, m->n_vocab, c->bias_ids_dev, c->bias_val_dev, c->n_bias, run.res_dev + (size_t) chunk * PIB_CHUNK,
                                desc, cancel, st));
+            if (run.has_walk) RC(pib_accept_walk(run.res_dev, desc, run.acc_dev, cancel, st));
+        } else if (c->hop_peer) {
+            if (pend) RC(pib_hop_send_launch(c, c->x2, c->proj, cur, ntok, st));
+            else      RC(pib_hop_send_launch(c, cur, nullptr, nullptr, ntok, st));
         } else if (pend) {
             const int64_t n = (int64_t) ntok * E;
             pib_launch(add3_kernel, dim3((unsigned) ((n + 255) / 256)), dim3(256), 0, st, c->x2, c->proj, cur, c->x, n, cancel);
@@ -646,6 +656,11 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
         GEMV(4, c->prof_layer >= 0 ? c->prof_layer : -2, m->output, lg);
         RC(pib_sample_topk(lg, ntok, m->n_vocab, c->bias_ids_dev, c->bias_val_dev, c->n_bias, run.res_dev + (size_t) chunk * PIB_CHUNK,
                            desc, cancel, st));
+        if (run.has_walk) RC(pib_accept_walk(run.res_dev, desc, run.acc_dev, cancel, st));
+    } else if (c->hop_peer) {
+        // the stage's output goes straight into the next stage's input slot: residual add fused with the store over NVLink
+        if (pending_add) RC(pib_hop_send_launch(c, c->proj, c->x2, nullptr, ntok, st));
+        else             RC(pib_hop_send_launch(c, c->x, nullptr, nullptr, ntok, st));
     } else {
         if (pending_add) {
             const int64_t n = (int64_t) ntok * E;
@@ -667,7 +682,7 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
 static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int slot) {
     const int * cancel = c->cancel_table;            // block address (see PIB_CANCELLED); the current-run cell was set by enqueue_decode
     int rc;
-    if (!c->stage.first() && pib_hop_recv && (rc = pib_hop_recv(c, c->x, ntok, cancel)) != PIB_OK) return rc;
+    if (!c->hop_peer && !c->stage.first() && pib_hop_recv && (rc = pib_hop_recv(c, c->x, ntok, cancel)) != PIB_OK) return rc;
     // per-launch event timing (bench.py roofline) samples one decode in eight, launched directly; the others keep their graphs
     c->prof_now = c->prof_layer >= 0 && (c->n_decode & 7) == 0 && slot > c->desc_slots;      // verification batches only (single chunk), not prompt chunks
     const bool graphable = c->use_graphs && !c->prof_now && slot > c->desc_slots;           // single-chunk decode: fixed device slot
@@ -705,7 +720,8 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
         if (c->prof_now) pib_pdl_suspend(false);
         if (rc != PIB_OK) return rc;
     }
-    if (!c->stage.last() && pib_hop_send && (rc = pib_hop_send(c, c->x, ntok, cancel)) != PIB_OK) return rc;
+    if (!c->hop_peer && !c->stage.last() && pib_hop_send && (rc = pib_hop_send(c, c->x, ntok, cancel)) != PIB_OK) return rc;
+    if (c->hop_peer && !c->stage.last()) pib_pipe_hop_account((size_t) ntok * c->model->n_embd * 4);
     return PIB_OK;
 }
 
@@ -715,6 +731,11 @@ static pib_run * take_run(pib_context * c, int n_tokens) {
     for (auto & r : c->runs) {
         if (r.in_use || r.id == c->last_finished) continue;
         if (!r.done) cudaEventCreateWithFlags(&r.done, cudaEventDisableTiming);
+        if (!r.acc_dev && (cudaMalloc(&r.acc_dev, sizeof(pib_accept_result)) != cudaSuccess || cudaMallocHost(&r.acc_host, sizeof(pib_accept_result)) != cudaSuccess)) {
+            pib_set_error("decode: out of memory for a run slot");
+            cudaGetLastError();
+            return nullptr;
+        }
         const int cap = ((n_tokens + PIB_CHUNK - 1) / PIB_CHUNK) * PIB_CHUNK;
         if ((c->stage.last() || c->stage.first()) && r.cap_tokens < cap) {
             if (r.res_dev) { cudaStreamSynchronize(c->stream); cudaFree(r.logits); cudaFree(r.res_dev); cudaFreeHost(r.res_host); }
@@ -777,6 +798,14 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
         memcpy(d + PIB_DESC_TOK_OFF, token + t0, sizeof(int32_t) * nt);
         memcpy(d + PIB_DESC_POS_OFF, pos + t0, sizeof(int32_t) * nt);
         memcpy(d + PIB_DESC_BITS_OFF, tb.data() + (size_t) t0 * W, sizeof(uint32_t) * (size_t) nt * W);
+        if (ch == 0 && n_chunks == 1 && c->tree_pending.n_branches > 0) {           // the acceptance table rides in the descriptor
+            const pib_accept_table & T = c->tree_pending;
+            hdr[PIB_DH_TREE_NP] = T.n_branches; hdr[PIB_DH_TREE_KEEP] = T.keep; hdr[PIB_DH_TREE_SPEC] = T.speculative;
+            int32_t * tl = reinterpret_cast<int32_t *>(d + PIB_DESC_TREE_OFF);
+            memcpy(tl, T.len, sizeof(T.len));
+            memcpy(tl + PIB_TREE_NP, T.rows, sizeof(T.rows));
+            memcpy(tl + PIB_TREE_NP + PIB_TREE_NP * PIB_TREE_DEPTH, T.toks, sizeof(T.toks));
+        }
         dq.push_back({ KVOP_ALLOC, (int32_t) (head + t0), nt, (int32_t) c->kv.n, s, 0 });
         cudaMemcpyAsync(c->desc_dev + (size_t) dev_slot(c, s) * c->desc_stride, d, c->desc_stride, cudaMemcpyHostToDevice, c->stream);
         c->h2d_bytes += c->desc_stride;
@@ -790,6 +819,8 @@ int pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, const
         if (pib_pipe_ship_decode(batch_id, n_tokens, n_chunks, dp.data(), c->desc_stride, slots.data(), dq.data(), (int) dq.size()) != PIB_OK) return -1;
     }
     SLOW_MARK("ship record");
+    run->has_walk = n_chunks == 1 && c->tree_pending.n_branches > 0;
+    c->tree_pending.n_branches = 0;
     const int rid = enqueue_decode(c, run, n_tokens, batch_id, slots);
     SLOW_MARK("enqueue");
     return rid;
@@ -843,8 +874,16 @@ static int enqueue_decode(pib_context * c, pib_run * run, int n_tokens, int batc
         if (c->stage.size > 1) {
             if (pib_pipe_send_results(c, *run) != PIB_OK) run->failed = true;
         } else {
-            cudaMemcpyAsync(run->res_host, run->res_dev, sizeof(pib_row_result) * (size_t) n_tokens, cudaMemcpyDeviceToHost, c->stream);
-            c->d2h_bytes += sizeof(pib_row_result) * (size_t) n_tokens;
+            // with an acceptance table only the walk's result crosses to the host; the rows stay on the device (fetched on demand)
+            if (run->has_walk) {
+                cudaMemcpyAsync(run->acc_host, run->acc_dev, sizeof(pib_accept_result), cudaMemcpyDeviceToHost, c->stream);
+                c->d2h_bytes += sizeof(pib_accept_result);
+                run->rows_on_host = false;
+            } else {
+                cudaMemcpyAsync(run->res_host, run->res_dev, sizeof(pib_row_result) * (size_t) n_tokens, cudaMemcpyDeviceToHost, c->stream);
+                c->d2h_bytes += sizeof(pib_row_result) * (size_t) n_tokens;
+                run->rows_on_host = true;
+            }
         }
     }
     cudaEventRecord(run->done, c->stream);
@@ -877,6 +916,7 @@ int pib_decode_replay(pib_context * c, int batch_id, int n_tokens, int n_chunks,
         cudaMemcpyAsync(c->desc_dev + (size_t) dev_slot(c, s) * c->desc_stride, d, c->desc_stride, cudaMemcpyHostToDevice, c->stream);
         c->h2d_bytes += c->desc_stride;
     }
+    run->has_walk = n_chunks == 1 && reinterpret_cast<const int32_t *>(descs + PIB_DESC_HDR_OFF)[PIB_DH_TREE_NP] > 0;
     std::vector<KvOp> & dq = devq(c);
     for (int i = 0; i < n_ops; i++) {
         KvOp op = ops[i];
@@ -929,7 +969,22 @@ int pib_run_finish(pib_context * c, int run) {
 }
 
 const pib_row_result * pib_last_results(pib_context * c) {
-    return c->last_finished >= 0 ? c->runs[c->last_finished].res_host : nullptr;
+    if (c->last_finished < 0) return nullptr;
+    pib_run & r = c->runs[c->last_finished];
+    if (!r.rows_on_host) {
+        // a run whose acceptance was walked on the device: its rows were not copied; a caller that asks for them gets them now
+        if (c->stage.size > 1) return nullptr;                 // they live on the last pipeline stage
+        cudaMemcpyAsync(r.res_host, r.res_dev, sizeof(pib_row_result) * (size_t) r.n_tokens, cudaMemcpyDeviceToHost, c->stream);
+        cudaStreamSynchronize(c->stream);
+        c->d2h_bytes += sizeof(pib_row_result) * (size_t) r.n_tokens;
+        r.rows_on_host = true;
+    }
+    return r.res_host;
+}
+
+const pib_accept_result * pib_last_accept(pib_context * c) {
+    if (c->last_finished < 0 || !c->runs[c->last_finished].has_walk) return nullptr;
+    return c->runs[c->last_finished].acc_host;
 }
 
 const float * pib_logits_row(pib_context * c, int i) {

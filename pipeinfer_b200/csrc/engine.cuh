@@ -18,6 +18,17 @@ struct pib_row_result {            // per logits row: sorted top-8 {id, logit, p
     float   p[PIB_TOPK];
 };
 
+struct pib_accept_result {         // what the device-side acceptance walk returns for one verification batch
+    int32_t n_ids;                 // target tokens sampled along the walk (1 .. depth + 1)
+    int32_t s_keep;                // branch the walk ended on
+    int32_t ids[PIB_CHUNK + 2];
+};
+struct pib_accept_table {          // host form of the table in the descriptor (desc.cuh)
+    int32_t n_branches = 0, keep = 0, speculative = 0;
+    int32_t len[PIB_TREE_NP];
+    int32_t rows[PIB_TREE_NP][PIB_TREE_DEPTH], toks[PIB_TREE_NP][PIB_TREE_DEPTH];
+};
+
 struct pib_layer {
     float *      attn_norm = nullptr;   // [n_embd]
     float *      attn_norm_b = nullptr; // falcon: LayerNorm bias
@@ -70,6 +81,9 @@ struct pib_run {                   // one (possibly still executing) decode: the
     pib_row_result * res_dev  = nullptr;  // device [n_tokens]
     pib_row_result * res_host = nullptr;  // pinned [n_tokens]
     int          cap_tokens = 0;
+    bool         has_walk  = false;       // the batch came with an acceptance table: only the walk's result crosses to the host
+    bool         rows_on_host = false;
+    pib_accept_result * acc_dev = nullptr, * acc_host = nullptr;
 };
 
 struct pib_stage {                 // pipeline position of this process (1-GPU: first && last)
@@ -108,6 +122,11 @@ struct pib_context {
     cudaEvent_t cancel_ev = nullptr;       // recorded on `ctrl` after every cancel write: the clearing memset on `stream` waits for it
     bool     cancel_ev_pending = false;
 
+    // peer-store hop (pipeline.cu): this stage's exported buffer, the next stage's (mapped), the previous stage's (mapped)
+    void *   hop_mine = nullptr, * hop_next = nullptr, * hop_prev = nullptr;
+    size_t   hop_slot_f4 = 0;
+    bool     hop_peer = false;
+
     // host->device staging rings (pinned host + device copies)
     uint8_t * desc_host = nullptr, * desc_dev = nullptr;
     size_t    desc_stride = 0;
@@ -121,6 +140,7 @@ struct pib_context {
     float *   bias_val_dev = nullptr;
     int       n_bias = 0;
 
+    pib_accept_table     tree_pending;     // set by llama_pib_set_accept_table, consumed by the next decode started
     std::vector<pib_run> runs;
     std::deque<int>      inflight;        // run ids in issue order
     int                  last_finished = -1;
@@ -161,6 +181,7 @@ int  pib_decode_start(pib_context * c, int n_tokens, const int32_t * token, cons
 bool pib_run_ready(pib_context * c, int run);
 int  pib_run_finish(pib_context * c, int run);                         // waits; makes results available; frees the slot
 const pib_row_result * pib_last_results(pib_context * c);
+const pib_accept_result * pib_last_accept(pib_context * c);
 const float *          pib_logits_row(pib_context * c, int i);         // lazy D2H of one row of the last finished run
 void pib_cancel(pib_context * c, const int32_t * batch_ids, int n);
 // stages > 0: replay one decode record of the head (descriptors + resolved KV op-log) / release a finished run
@@ -182,6 +203,11 @@ int  pib_pipe_send_results(pib_context * c, pib_run & run);
 int  pib_pipe_post_result_recv(pib_context * c, pib_run & run);
 int  pib_pipe_fetch_logits(pib_context * c, int row, float * dev_staging, float * host_dst);
 int  pib_stage_serve(pib_context * c);
+int  pib_pipe_hop_setup(pib_context * c);
+void pib_pipe_hop_free(pib_context * c);
+void pib_pipe_hop_account(size_t bytes);
+int  pib_hop_recv_launch(pib_context * c, int n_tokens, cudaStream_t st);
+int  pib_hop_send_launch(pib_context * c, const float * a, const float * b, const float * c3, int n_tokens, cudaStream_t st);
 extern int (*pib_hop_recv)(pib_context * c, float * x, int n_tokens, const int * cancel);
 extern int (*pib_hop_send)(pib_context * c, const float * x, int n_tokens, const int * cancel);
 void pib_set_logit_bias(pib_context * c, const int32_t * ids, const float * vals, int n);

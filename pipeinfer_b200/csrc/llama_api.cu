@@ -391,6 +391,31 @@ int llama_pib_get_top8(struct llama_context * ctx, int32_t i, llama_token_data *
     return 0;
 }
 
+// acceptance on the device (north_star item 4): the table of the NEXT decode started on this context
+void llama_pib_set_accept_table(struct llama_context * ctx, int32_t n_branches, int32_t keep, int32_t speculative, const int32_t * len,
+                                const int32_t * rows, const int32_t * toks, int32_t depth_stride) {
+    pib_accept_table & T = ctx->c->tree_pending;
+    T.n_branches = 0;
+    if (n_branches < 1 || n_branches > PIB_TREE_NP || depth_stride < 1) return;       // too wide for the device table: the caller walks the rows itself
+    memset(T.rows, 0, sizeof(T.rows)); memset(T.toks, 0, sizeof(T.toks));
+    for (int s = 0; s < PIB_TREE_NP; s++) T.len[s] = -1;
+    for (int s = 0; s < n_branches; s++) {
+        if (len[s] > PIB_TREE_DEPTH - 1) return;
+        T.len[s] = len[s];
+        for (int i = 0; i < PIB_TREE_DEPTH && i < depth_stride; i++) { T.rows[s][i] = rows[s * depth_stride + i]; T.toks[s][i] = toks[s * depth_stride + i]; }
+    }
+    T.keep = keep; T.speculative = speculative; T.n_branches = n_branches;
+}
+
+// after llama_finish_async_decode of a run that carried a table: the ids sampled along the walk, and the branch kept
+int32_t llama_pib_get_accepted(struct llama_context * ctx, int32_t * ids, int32_t cap, int32_t * s_keep) {
+    const pib_accept_result * r = pib_last_accept(ctx->c);
+    if (!r) return -1;
+    for (int i = 0; i < r->n_ids && i < cap; i++) ids[i] = r->ids[i];
+    if (s_keep) *s_keep = r->s_keep;
+    return r->n_ids;
+}
+
 void llama_pib_set_logit_bias(struct llama_context * ctx, const llama_token * ids, const float * bias, int n) {
     pib_set_logit_bias(ctx->c, ids, bias, n);
 }

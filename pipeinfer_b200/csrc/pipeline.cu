@@ -52,6 +52,11 @@ struct ring_hdr {
     uint8_t   nccl_ids[256];             // the two ncclUniqueIds, published by rank 0 (launchers without a store of their own)
     std::atomic<uint32_t> ids_ready;
     uint64_t  created_us;                // wall clock of the creation: lets a stage tell a fresh ring from one a crashed run left behind
+    // peer-store hop: every stage publishes the IPC handle of its hop buffer here (generation = how many pipelines' worth of
+    // contexts this ring has seen, so that a handle of an earlier context is never taken for the current one)
+    cudaIpcMemHandle_t    hop_ipc[PIPE_MAX_RANKS];
+    std::atomic<uint32_t> hop_gen[PIPE_MAX_RANKS];
+    uint32_t              hop_embd[PIPE_MAX_RANKS];
 };
 struct rec_hdr { uint32_t bytes, kind; };
 struct rec_decode { int32_t batch_id, n_tokens, n_chunks, n_ops; uint32_t desc_stride, pad; };
@@ -124,7 +129,7 @@ extern "C" int pib_pipe_ring_open(const char * name, int rank, int n_ranks, size
         P.h->cap = cap_bytes; P.h->n_ranks = (uint32_t) n_ranks;
         P.h->head.v.store(0); P.h->bar_count.v.store(0); P.h->bar_gen.v.store(0); P.h->ids_ready.store(0);
         P.h->created_us = (uint64_t) (now_s() * 1e6);
-        for (int i = 0; i < PIPE_MAX_RANKS; i++) P.h->tail[i].v.store(0);
+        for (int i = 0; i < PIPE_MAX_RANKS; i++) { P.h->tail[i].v.store(0); P.h->hop_gen[i].store(0); }
         P.h->magic.store(PIPE_MAGIC, std::memory_order_release);
     } else {
         spinner sp;
@@ -381,6 +386,135 @@ extern "C" void pib_pipe_traffic(uint64_t * hop_bytes, uint64_t * hop_msgs, uint
 
 bool pib_pipe_nccl_active() { return P.fwd != nullptr && P.size > 1; }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// peer-store hop (reference: ggml_mpi_tensor_send / _recv of the layer output, ggml-mpi.c:451-503, 710-721).  Every stage but the
+// first owns a ring of HOP_SLOTS activation slots + one flag per slot in ITS OWN memory, exported with cudaIpc and mapped by the
+// stage in front of it.  The last kernel of a stage forms the stage's output (residual add) and stores it straight into the next
+// stage's slot with ordinary st.global over NVLink, then releases the slot's flag (system scope); the first kernel of the next
+// stage acquires the flag, copies the slot into its work buffer and acknowledges into the SENDER's memory (back pressure: the
+// sender never runs more than HOP_SLOTS chunks ahead).  Both kernels take everything that varies from device memory (sequence
+// counters), so they live inside the stage's captured CUDA graph: no ncclSend / ncclRecv launch pair per stage.  Plain loads and
+// stores only.
+#define HOP_SLOTS 32
+struct hop_dev {                          // first 256 bytes of a stage's exported allocation
+    unsigned int flags[HOP_SLOTS];        // written by the PREVIOUS stage: 1 + sequence number of the chunk in the slot
+    unsigned int ack;                     // written by the NEXT stage: chunks it has consumed
+    unsigned int send_seq, recv_seq;      // this stage's own counters (chunks sent on / received)
+    unsigned int pad[64 - HOP_SLOTS - 3];
+};
+static_assert(sizeof(hop_dev) == 256, "hop header");
+
+__device__ __forceinline__ unsigned int hop_ld_acquire(const unsigned int * p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void hop_st_release(unsigned int * p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// out = a [+ b [+ c3]] written into the next stage's slot; one CTA (the payload is 32 KiB per token)
+__global__ void __launch_bounds__(1024) hop_send_kernel(const float4 * __restrict__ a, const float4 * __restrict__ b, const float4 * __restrict__ c3,
+                                                        int n4, hop_dev * mine, hop_dev * peer, size_t slot_f4) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
+    const unsigned int seq = mine->send_seq, slot = seq % HOP_SLOTS;
+    if (threadIdx.x == 0) while ((int) (seq - hop_ld_acquire(&mine->ack)) >= HOP_SLOTS) { }
+    __syncthreads();
+    float4 * dst = reinterpret_cast<float4 *>(reinterpret_cast<uint8_t *>(peer) + 256) + (size_t) slot * slot_f4;
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+        float4 v = a[i];
+        if (b) { const float4 w = b[i]; v.x = __fadd_rn(v.x, w.x); v.y = __fadd_rn(v.y, w.y); v.z = __fadd_rn(v.z, w.z); v.w = __fadd_rn(v.w, w.w); }
+        if (c3) { const float4 w = c3[i]; v.x = __fadd_rn(v.x, w.x); v.y = __fadd_rn(v.y, w.y); v.z = __fadd_rn(v.z, w.z); v.w = __fadd_rn(v.w, w.w); }
+        dst[i] = v;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) { hop_st_release(&peer->flags[slot], seq + 1); mine->send_seq = seq + 1; }
+}
+
+__global__ void __launch_bounds__(1024) hop_recv_kernel(float4 * __restrict__ x, int n4, hop_dev * mine, hop_dev * peer_prev, size_t slot_f4) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
+    const unsigned int seq = mine->recv_seq, slot = seq % HOP_SLOTS;
+    if (threadIdx.x == 0) while (hop_ld_acquire(&mine->flags[slot]) != seq + 1) { }
+    __syncthreads();
+    const float4 * src = reinterpret_cast<const float4 *>(reinterpret_cast<const uint8_t *>(mine) + 256) + (size_t) slot * slot_f4;
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) x[i] = __ldcv(src + i);       // the slot was written from outside this GPU: not through L1
+    __syncthreads();
+    if (threadIdx.x == 0) { mine->recv_seq = seq + 1; hop_st_release(&peer_prev->ack, seq + 1); }
+}
+
+static uint32_t g_hop_generation = 0;
+
+// collective over the stages of the pipeline (each creates its target context at the same point of the program)
+int pib_pipe_hop_setup(pib_context * c) {
+    const char * mode = getenv("PIB_HOP");
+    if (!P.h || c->stage.size <= 1 || (mode && !strcmp(mode, "nccl"))) return PIB_OK;
+    const int      r = c->stage.rank, n = c->stage.size;
+    const uint32_t gen = ++g_hop_generation;
+    const size_t   slot_bytes = (size_t) PIB_CHUNK * c->model->n_embd * sizeof(float);
+    const size_t   bytes = 256 + (r > 0 ? (size_t) HOP_SLOTS * slot_bytes : 0);
+    int dev = 0;
+    PIB_CHECK(cudaGetDevice(&dev));
+    PIB_CHECK(cudaMalloc(&c->hop_mine, bytes));
+    PIB_CHECK(cudaMemset(c->hop_mine, 0, bytes));
+    PIB_CHECK(cudaDeviceSynchronize());
+    PIB_CHECK(cudaIpcGetMemHandle(&P.h->hop_ipc[r], c->hop_mine));
+    P.h->hop_embd[r] = (uint32_t) c->model->n_embd;
+    P.h->hop_gen[r].store(gen, std::memory_order_release);
+    auto open_peer = [&](int peer, void ** out) -> int {
+        spinner sp;
+        while (P.h->hop_gen[peer].load(std::memory_order_acquire) != gen) if (!sp.step()) { pib_set_error("pipe: stage %d never published its hop buffer", peer); return PIB_ERR_ARG; }
+        if (P.h->hop_embd[peer] != (uint32_t) c->model->n_embd) { pib_set_error("pipe: stage %d runs another model width", peer); return PIB_ERR_ARG; }
+        cudaIpcMemHandle_t hnd = P.h->hop_ipc[peer];
+        const cudaError_t e = cudaIpcOpenMemHandle(out, hnd, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) { cudaGetLastError(); *out = nullptr; pib_set_error("pipe: cannot map stage %d's hop buffer: %s", peer, cudaGetErrorString(e)); return PIB_ERR_CUDA; }
+        return PIB_OK;
+    };
+    int rc = PIB_OK;
+    if (r + 1 < n) rc = open_peer(r + 1, &c->hop_next);
+    if (rc == PIB_OK && r > 0) rc = open_peer(r - 1, &c->hop_prev);
+    c->hop_slot_f4 = slot_bytes / 16;
+    // every stage reports through the ring header (a stage that failed publishes generation | 0x80000000): if any mapping failed
+    // -- no peer access between two of the GPUs -- ALL stages fall back to the NCCL hop
+    P.h->hop_gen[r].store(rc == PIB_OK ? gen : (gen | 0x80000000u), std::memory_order_release);
+    pib_pipe_barrier();
+    bool all_ok = true;
+    for (int i = 0; i < n; i++) if (P.h->hop_gen[i].load(std::memory_order_acquire) != gen) all_ok = false;
+    pib_pipe_barrier();
+    c->hop_peer = all_ok;
+    if (!all_ok && r == 0) fprintf(stderr, "pipe: peer mapping unavailable (%s); the hop uses ncclSend / ncclRecv\n", pib_last_error());
+    return PIB_OK;
+}
+
+void pib_pipe_hop_free(pib_context * c) {
+    if (c->hop_next) cudaIpcCloseMemHandle(c->hop_next);
+    if (c->hop_prev) cudaIpcCloseMemHandle(c->hop_prev);
+    if (c->hop_mine) cudaFree(c->hop_mine);
+    c->hop_next = c->hop_prev = c->hop_mine = nullptr;
+    c->hop_peer = false;
+}
+
+// first kernel of a stage > 0: the previous stage's output -> c->x
+int pib_hop_recv_launch(pib_context * c, int n_tokens, cudaStream_t st) {
+    const int n4 = n_tokens * c->model->n_embd / 4;
+    pib_launch(hop_recv_kernel, dim3(1), dim3(1024), 0, st, reinterpret_cast<float4 *>(c->x), n4, (hop_dev *) c->hop_mine, (hop_dev *) c->hop_prev, c->hop_slot_f4);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+// last kernel of a stage < last: a [+ b [+ c3]] -> the next stage's slot
+int pib_hop_send_launch(pib_context * c, const float * a, const float * b, const float * c3, int n_tokens, cudaStream_t st) {
+    const int n4 = n_tokens * c->model->n_embd / 4;
+    pib_launch(hop_send_kernel, dim3(1), dim3(1024), 0, st, reinterpret_cast<const float4 *>(a), reinterpret_cast<const float4 *>(b),
+               reinterpret_cast<const float4 *>(c3), n4, (hop_dev *) c->hop_mine, (hop_dev *) c->hop_next, c->hop_slot_f4);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+// bytes this stage stores into the next stage's memory: counted where the chunk is enqueued (a graph replay does not pass through
+// the launch function above)
+void pib_pipe_hop_account(size_t bytes) { P.hop_bytes += bytes; P.hop_msgs++; }
+
 // engine hooks ---------------------------------------------------------------------------------------------------------
 static int hop_recv(pib_context * c, float * x, int n_tokens, const int * cancel) {
     (void) cancel;
@@ -395,16 +529,20 @@ static int hop_send(pib_context * c, const float * x, int n_tokens, const int * 
     P.hop_bytes += n * 4; P.hop_msgs++;
     return PIB_OK;
 }
+// what comes back from the last stage: the result of the device-side acceptance walk when the batch carried a table (72 bytes),
+// else the sampled rows (96 bytes per row).  Both ends know which: the table travels in the descriptor.
 int pib_pipe_send_results(pib_context * c, pib_run & run) {
-    const size_t bytes = sizeof(pib_row_result) * (size_t) run.n_tokens;
-    NCCL_CHECK(N.Send(run.res_dev, bytes, ncclUint8, 0, P.back, c->stream));
+    const size_t bytes = run.has_walk ? sizeof(pib_accept_result) : sizeof(pib_row_result) * (size_t) run.n_tokens;
+    NCCL_CHECK(N.Send(run.has_walk ? (const void *) run.acc_dev : (const void *) run.res_dev, bytes, ncclUint8, 0, P.back, c->stream));
     P.back_bytes += bytes;
     return PIB_OK;
 }
 int pib_pipe_post_result_recv(pib_context * c, pib_run & run) {
-    const size_t bytes = sizeof(pib_row_result) * (size_t) run.n_tokens;
-    NCCL_CHECK(N.Recv(run.res_dev, bytes, ncclUint8, P.size - 1, P.back, P.res_stream));
-    PIB_CHECK(cudaMemcpyAsync(run.res_host, run.res_dev, bytes, cudaMemcpyDeviceToHost, P.res_stream));
+    const size_t bytes = run.has_walk ? sizeof(pib_accept_result) : sizeof(pib_row_result) * (size_t) run.n_tokens;
+    void * dev = run.has_walk ? (void *) run.acc_dev : (void *) run.res_dev, * host = run.has_walk ? (void *) run.acc_host : (void *) run.res_host;
+    run.rows_on_host = !run.has_walk;
+    NCCL_CHECK(N.Recv(dev, bytes, ncclUint8, P.size - 1, P.back, P.res_stream));
+    PIB_CHECK(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, P.res_stream));
     c->d2h_bytes += bytes;
     PIB_CHECK(cudaEventRecord(run.done, P.res_stream));
     return PIB_OK;

@@ -105,3 +105,44 @@ int pib_sample_topk(float * logits_dev, int n_rows, int n_vocab, const int32_t *
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }
+
+// ---- acceptance walk (reference speculative.cpp:439-560, greedy) ----------------------------------------------------------------
+// The verification loop of the scheduler, on the device that holds the sampled rows: start on branch `keep` at depth 0; sample the
+// target's token at that branch's row; every active branch whose drafted token at this depth differs is dropped, the first that
+// agrees becomes the branch to follow; stop at the first depth where none agrees.  Only the ids sampled along the way (and the
+// branch kept) cross to the host: 8 + 4 * n_ids bytes instead of 96 bytes per row.
+__global__ void accept_walk_kernel(const pib_row_result * __restrict__ rows, const uint8_t * __restrict__ desc, pib_accept_result * __restrict__ out,
+                                   const int * __restrict__ cancel) {
+    pib_pdl_wait();
+    pib_pdl_trigger();
+    if (threadIdx.x != 0) return;
+    const int32_t * hdr = reinterpret_cast<const int32_t *>(desc + PIB_DESC_HDR_OFF);
+    const int np = hdr[PIB_DH_TREE_NP];
+    if (np <= 0 || PIB_CANCELLED(cancel)) { out->n_ids = 0; out->s_keep = 0; return; }
+    const int32_t * len = reinterpret_cast<const int32_t *>(desc + PIB_DESC_TREE_OFF);
+    const int32_t * trow = len + PIB_TREE_NP, * ttok = trow + PIB_TREE_NP * PIB_TREE_DEPTH;
+    int  keep = hdr[PIB_DH_TREE_KEEP], n = 0, i = 0;
+    bool act[PIB_TREE_NP];
+    for (int s = 0; s < PIB_TREE_NP; s++) act[s] = s < np && len[s] >= 0;
+    while (n < PIB_CHUNK + 2 && i < PIB_TREE_DEPTH) {
+        const int id = rows[trow[keep * PIB_TREE_DEPTH + i]].id[0];
+        out->ids[n++] = id;
+        if (!hdr[PIB_DH_TREE_SPEC]) break;
+        bool matches = false;
+        for (int s = 0; s < np; s++) {
+            if (!act[s]) continue;
+            if (i < len[s] && id == ttok[s * PIB_TREE_DEPTH + i]) { if (!matches) keep = s; matches = true; }
+            else act[s] = false;
+        }
+        if (!matches) break;
+        i++;
+    }
+    out->n_ids = n;
+    out->s_keep = keep;
+}
+
+int pib_accept_walk(const void * rows_dev, const uint8_t * desc, void * out_dev, const int * cancel, cudaStream_t st) {
+    pib_launch(accept_walk_kernel, dim3(1), dim3(32), 0, st, (const pib_row_result *) rows_dev, desc, (pib_accept_result *) out_dev, cancel);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}

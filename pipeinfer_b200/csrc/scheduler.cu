@@ -107,6 +107,8 @@ class Scheduler {
     // token into the first speculative run (the token becomes row 0 of that run, as in classic speculation): one pass of the
     // target instead of two, which is what matters when there is no pipeline to hide the second one (one or two GPUs).
     int             chain_policy = getenv("PIB_SCHED_CHAIN") ? atoi(getenv("PIB_SCHED_CHAIN")) : 2;
+    // acceptance walked on the device that holds the logits (PIB_DEVICE_WALK=0: the host walks the sampled rows, 96 bytes each)
+    bool            device_walk = !(getenv("PIB_DEVICE_WALK") && atoi(getenv("PIB_DEVICE_WALK")) == 0);
     int             chain_start_tgt = 0, chain_start_dft = 0;      // n_past at which the current chain began: prefix of all its links
     llama_token_data tip_top8[8];                                   // the draft's candidates after the tip of branch 0
     bool            have_tip = false;
@@ -188,6 +190,21 @@ void Scheduler::begin_async_run(llama_context * ctx, std::deque<Run> & q, const 
     run.speculative = is_spec;
     if (!is_spec) llama_pib_kv_seq_rm_range(ctx, 0, max_seq, n_past, n_past + 1);     // :1252-1255, for i in 0..max_seq: seq_rm(i, ...)
     else          { for (int i = 0; i < np; i++) llama_kv_cache_seq_rm(ctx, i + seq_offset, n_past, n_past + 1); } // :1256-1260
+    if (ctx == ctx_tgt && device_walk && np <= 8) {
+        // the acceptance table of this batch, indexed as the verification walk will see the drafts (first token of every branch
+        // erased, :431): the last stage's device walks it right after sampling and only the ids sampled on the way come back
+        int32_t len[8], rows[8][17], toks[8][17];
+        bool fits = true;
+        memset(rows, 0, sizeof(rows)); memset(toks, 0, sizeof(toks));
+        for (int s = 0; s < np && fits; s++) {
+            const int nt = (int) dr[s].tokens.size() - 1, nr = (int) dr[s].i_batch_tgt.size();
+            len[s] = dr[s].active ? nt : -1;                                   // an inactive branch is never compared, but may be the one sampled from
+            if (nt > 16 || nr > 17) { fits = false; break; }
+            for (int i = 0; i < nr; i++) rows[s][i] = dr[s].i_batch_tgt[i];
+            for (int i = 0; i < nt; i++) toks[s][i] = dr[s].tokens[i + 1];
+        }
+        if (fits) llama_pib_set_accept_table(ctx, np, run.s_keep, is_spec ? 1 : 0, len, &rows[0][0], &toks[0][0], 17);
+    }
     run.handle = llama_start_async_decode(*ctx, run.batch.view(max_seq + 1));                                      // :1261
     if (ctx == ctx_tgt) ev(is_spec ? "start_spec" : "start_nonspec", batch_id, (int) run.batch.size(), n_past);
     if (!run.handle) failed = true;     // no KV slot left: the reference would spin forever here
@@ -435,11 +452,16 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
         }
 
         // ---- verification walk (:439-560) ----
+        int32_t walk_ids[18];
+        int     walk_n = -1, walk_pos = 0;
         bool any_match = false;
         int  keep0 = s_keep;
         bool keeps_nonempty = true;
         while (keeps_nonempty) {
-            id = greedy(ctx_tgt, drafts[keep0].i_batch_tgt[i_dft]);                                      // :448
+            // :448 -- from the device's walk of this batch when it carried a table (same loop, same order), else from the row
+            if (walk_n < 0) walk_n = device_walk ? llama_pib_get_accepted(ctx_tgt, walk_ids, 18, nullptr) : 0;
+            if (walk_n > 0 && walk_pos < walk_n) id = walk_ids[walk_pos++];
+            else id = greedy(ctx_tgt, drafts[keep0].i_batch_tgt[i_dft]);
             if (current.n_past_tgt + i_dft == n_past_tgt - 1) {                                          // a token nobody has seen yet (:465)
                 any_match = true;
                 ++n_predict;

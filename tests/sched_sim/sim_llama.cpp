@@ -331,6 +331,10 @@ void llama_cancel_run(struct llama_context * c, int32_t * ids, int count) {
             }
 }
 
+// the virtual engine has no device to walk on: the scheduler falls back to walking the sampled rows
+void    llama_pib_set_accept_table(struct llama_context *, int32_t, int32_t, int32_t, const int32_t *, const int32_t *, const int32_t *, int32_t) {}
+int32_t llama_pib_get_accepted(struct llama_context *, int32_t *, int32_t, int32_t *) { return -1; }
+
 int llama_pib_get_top8(struct llama_context * c, int32_t i, llama_token_data * out8) {
     g_now += G.call_us;
     if (i < 0 || i >= (int) c->rows.size()) return -1;

@@ -264,6 +264,81 @@ def test_cancel_mid_flight_on_k_split_shapes_leaves_the_next_decode_intact(llama
     ctx.close()
 
 
+def test_device_acceptance_walk_matches_the_host_walk(llama, golden_dir):
+    """north_star item 4: the draft-vs-target comparison of speculative.cpp:439-560 runs on the device right after sampling.  A
+    5-row tree batch (trunk + two branches) is decoded twice: once plainly (rows read back, walked in Python as the reference's
+    loop does), once with the acceptance table (only the walk's result comes back).  Drafted tokens are chosen from the first
+    pass so that the walk follows branch 1 for two steps and then fails -- and, second case, fails at once."""
+    L = llama.api()
+    L.llama_pib_set_accept_table.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
+    L.llama_pib_get_accepted.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
+    ctx = llama.Context(os.path.join(golden_dir, "tiny_q8_0.gguf"), n_ctx=64, max_seq=8)
+    rng = np.random.default_rng(3)
+    prompt = rng.integers(3, ctx.n_vocab, 6).tolist()
+    assert ctx.decode(prompt, list(range(6)), [[0, 1, 2]] * 6)[0] == 0
+    # rows: 0 trunk (seqs 1,2) pos 6 | 1, 2: branch 1 at pos 7, 8 | 3, 4: branch 2 at pos 7, 8
+    pos, seqs = [6, 7, 8, 7, 8], [[1, 2], [1], [1], [2], [2]]
+
+    def run(tokens, table):
+        if table is not None:
+            ln, rows, toks = table
+            a = lambda x: np.ascontiguousarray(x, dtype=np.int32)
+            ln, rows, toks = a(ln), a(rows), a(toks)
+            L.llama_pib_set_accept_table(ctx.ctx, 2, 0, 1, ln.ctypes.data, rows.ctypes.data, toks.ctypes.data, 17)
+        h, b, keep = ctx.start(tokens, pos, seqs)
+        assert ctx.finish(h, b) == 1
+        out = None
+        if table is not None:
+            ids, sk = (C.c_int32 * 18)(), C.c_int32()
+            n = L.llama_pib_get_accepted(ctx.ctx, ids, 18, C.byref(sk))
+            out = (list(ids[:n]), sk.value)
+        arg = [ctx.top8(i)[0][0] for i in range(5)]
+        for s_ in (1, 2):
+            ctx.seq_rm(s_, 6, -1)
+        return arg, out
+
+    toks0 = rng.integers(3, ctx.n_vocab, 5).tolist()
+    arg, _ = run(toks0, None)
+    for case in range(2):
+        tk = list(toks0)
+        if case == 0:
+            tk[3] = arg[0]                 # branch index 1 (rows 0, 3, 4) drafted the target's token after the trunk ...
+            tk[1] = (arg[0] + 1) % ctx.n_vocab   # ... branch index 0 (rows 0, 1, 2) did not
+        else:
+            tk[1] = (arg[0] + 1) % ctx.n_vocab
+            tk[3] = (arg[0] + 2) % ctx.n_vocab
+        arg2, _ = run(tk, None)            # the argmax of every row for THESE tokens
+        if case == 0:
+            tk[4] = arg2[3]                # and its second token as well; the third sample then has nothing to match
+            arg2, _ = run(tk, None)
+        # table: branch s, depth i -> row, drafted token (first token of the branch = the trunk token, erased as in :431)
+        rows = np.zeros((8, 17), np.int32); tt = np.zeros((8, 17), np.int32)
+        rows[0, :3] = [0, 1, 2]; rows[1, :3] = [0, 3, 4]
+        tt[0, :2] = [tk[1], tk[2]]; tt[1, :2] = [tk[3], tk[4]]
+        ln = [2, 2] + [-1] * 6
+        # host walk (the reference's loop)
+        keep, i, act, want = 0, 0, [True, True], []
+        while True:
+            want.append(arg2[rows[keep, i]])
+            m = False
+            for s_ in range(2):
+                if act[s_]:
+                    if i < ln[s_] and want[-1] == tt[s_, i]:
+                        if not m:
+                            keep = s_
+                        m = True
+                    else:
+                        act[s_] = False
+            if not m:
+                break
+            i += 1
+        arg3, got = run(tk, (ln, rows, tt))
+        assert arg3 == arg2
+        assert got == (want, keep), (case, got, want, keep)
+        assert len(want) == (3 if case == 0 else 1)
+    ctx.close()
+
+
 def test_synthetic_bigram_model_predicts_permutation(llama):
     # random-init weights generated in HBM; with the bigram flavour target and draft agree on most tokens
     for wt in (8, 2, 12):
