@@ -375,11 +375,14 @@ def main():
         sum(lib.llama_pib_weight_bytes(c.model) for c in ctxs)])
     hops = None
     if world > 1:
-        per_rank = [torch.zeros(4, dtype=torch.float64) for _ in range(world)]
         nv = float((nv1 - nv0) * 1024) if (nv0 is not None and nv1 is not None) else -1.0
-        dist.all_gather(per_rank, torch.tensor([tr1[i] - tr0[i] for i in range(3)] + [nv], dtype=torch.float64))
+        per_rank = [torch.zeros(9, dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(per_rank, torch.tensor([tr1[i] - tr0[i] for i in range(3)] + [nv] + list(pipeline.cancel_stats()), dtype=torch.float64))
         hops = [{"rank": r, "activation_bytes_to_next_stage": int(t[0]), "messages": int(t[1]), "result_bytes_to_head": int(t[2]),
-                 "nvlink_tx_bytes_counter": (int(t[3]) if t[3] >= 0 else None)} for r, t in enumerate(per_rank)]
+                 "nvlink_tx_bytes_counter": (int(t[3]) if t[3] >= 0 else None),
+                 "cancel_records": int(t[4]), "cancel_to_stage_host_us": {"mean": float(t[5]), "max": float(t[6])},
+                 "cancel_to_device_flag_us": ({"mean": float(t[7]), "max": float(t[8])} if os.environ.get("PIB_CANCEL_TIMING") == "1" else None)}
+                for r, t in enumerate(per_rank)]
         if rank == 0:
             tgt.shutdown()
         else:
@@ -468,7 +471,12 @@ def main():
         line["speedup_over_plain"] = line["value"] / plain["tok_s"]
         line["text_equals_plain_greedy"] = toks[:args.n_predict] == plain["tokens"][:args.n_predict]
     if hops is not None:
-        line["nvlink_hops"] = {"per_rank_over_timed_steps": hops, "formula": "n_tokens * n_embd * 4 B of fp32 activations per hop (%d B per token) + 96 B per sampled row back to the head" % (E * 4)}
+        line["nvlink_hops"] = {"per_rank_over_timed_steps": hops,
+                               "formula": "n_tokens * n_embd * 4 B of fp32 activations per hop (%d B per token), stored by the sending stage's last kernel into the "
+                                          "next stage's memory; 72 B per verification batch (device-side acceptance walk) back to the head" % (E * 4),
+                               "nvlink_tx_bytes_counter": "not exposed on this driver: NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX returns NVML_ERROR_NOT_SUPPORTED and "
+                                                          "`nvidia-smi nvlink -gt d` prints N/A (tools/nvlink_probe.py); the byte counts above are counted at the "
+                                                          "point where each transfer is enqueued" if all(h["nvlink_tx_bytes_counter"] is None for h in hops) else "KiB counters read around the timed steps"}
     print(json.dumps(line))
     return 0
 

@@ -105,6 +105,17 @@ int pib_gemv_direct_splits(int64_t N, int64_t K);
  * includes the H2D copy of x, quantisation, GEMV and the D2H copy of y. */
 int pib_mul_mat_host(const pib_weight * w, const float * x_host, int b, float * y_host, int variant);
 
+/* The same product for a WIDE batch (prompt ingestion; 1 <= b <= 256 tokens at once) on the tcgen05 tensor cores: the Q4_K weights
+ * are dequantised tile by tile to fp16, the Q8_K-quantised activations likewise, fp32 accumulation in tensor memory.  Replaces
+ * ggml_compute_forward_mul_mat at large ne11 (ggml.c:9388) / ggml_cuda_op_mul_mat_cublas (ggml-cuda.cu:6562).  Tolerance-checked
+ * against the oracle (fp16 operand rounding, another summation order), not bit-exact.  Host buffers in and out. */
+int pib_gemm_host(const pib_weight * w, const float * x_host, int b, float * y_host);
+/* Device-buffer form: act_dev = activation planes of b rows (pib_quantize_act_rows), scratch_dev = pib_gemm_scratch_bytes(K, b) bytes
+ * (the fp16 copy of the activations the TMA loads from). */
+size_t pib_gemm_scratch_bytes(int64_t K, int b);
+int    pib_gemm(const pib_weight * w, const void * act_dev, int b, float * y_dev, void * scratch_dev, pib_stream s);
+int    pib_quantize_act_rows(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, pib_stream s);
+
 /* ---- K3: embedding rows ---------------------------------------------------------------------------------------- */
 /* out_dev float [n][K] = dequantised rows `ids` of W.  Replaces: ggml_compute_forward_get_rows_q (ggml.c:10161) with
  * dequantize_row_q4_0 / q8_0 / q4_K (ggml-quants.c:1074, 1168, 1917). */

@@ -41,6 +41,9 @@ int  pib_attention(const __half * q16, const __half * kc, const __half * vc, con
                    cudaStream_t st);
 int  pib_sample_topk(float * logits_dev, int n_rows, int n_vocab, const int32_t * bias_ids_dev, const float * bias_val_dev, int n_bias,
                      void * out_dev, const uint8_t * desc, const int * cancel, cudaStream_t st);
+int  pib_gemm_q4k_tc(const pib_weight * w, const void * act_dev, int b, float * y_dev, void * xhat_dev, cudaStream_t st);
+size_t pib_gemm_xhat_bytes(int64_t K, int b);
+int  kv_device_mask(const KvDevice * kv, const int32_t * tpos_dev, const uint32_t * tokbits_dev, int n_tokens, uint8_t * mask_dev, cudaStream_t st);
 int  pib_accept_walk(const void * rows_dev, const uint8_t * desc, void * out_dev, const int * cancel, cudaStream_t st);
 pib_weight * pib_weight_alloc(int type, int64_t N, int64_t K);
 void pib_weight_drop_planes(pib_weight * w);
@@ -438,6 +441,7 @@ pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_st
     CK(cudaMalloc(&c->desc_dev, c->desc_stride * (c->desc_slots + 65)));
     c->desc_ev.assign(c->desc_slots + 65, nullptr);
     { const char * g = getenv("PIB_GRAPHS"); c->use_graphs = !g || atoi(g) != 0; }
+    { const char * g = getenv("PIB_PROMPT_GEMM"); c->prompt_gemm = (g && atoi(g) == 0) || pib_exact_mode() ? 0 : 1; }
     c->ops_cap = 1 << 16;
     CK(cudaMallocHost(&c->ops_host, sizeof(KvOp) * c->ops_cap));
     CK(cudaMalloc(&c->ops_dev, sizeof(KvOp) * c->ops_cap));
@@ -454,6 +458,8 @@ void pib_context_free(pib_context * c) {
     if (!c) return;
     if (c->stream) cudaStreamSynchronize(c->stream);
     pib_pipe_hop_free(c);
+    for (void * b : { (void *) c->pb.x, (void *) c->pb.x2, (void *) c->pb.qkv, (void *) c->pb.att, (void *) c->pb.proj, (void *) c->pb.gu, (void *) c->pb.q16,
+                      (void *) c->pb.mask, c->pb.act, c->pb.xhat }) if (b) cudaFree(b);
     kv_device_free(&c->kvd);
     void * bufs[] = { c->vsep, c->kcache, c->vcache, c->x, c->x2, c->qkv, c->att, c->proj, c->gu, c->q16, c->mask, c->act, c->rope,
                       c->cancel_table, c->desc_dev, c->ops_dev, c->bias_ids_dev, c->bias_val_dev, c->logits_fetch_dev };
@@ -727,6 +733,112 @@ static int run_chunk(pib_context * c, pib_run & run, int chunk, int ntok, int sl
 
 static int enqueue_decode(pib_context * c, pib_run * run, int n_tokens, int batch_id, const std::vector<int> & slots);
 
+// ---- wide batches (prompt ingestion): the matmuls of up to PIB_PROMPT_MAX tokens at once on the tcgen05 GEMM -----------------------
+// The reference takes a prompt of up to n_batch = 512 tokens in one ggml_compute_forward_mul_mat per matrix (common.h:52, ggml.c:9388).
+// Here the per-token kernels (norm / quantise, RoPE + KV store, attention, ...) keep their 16-token descriptors, but every matmul of a
+// layer runs once for the whole pass.  Used for llama-architecture models whose matrices are all Q4_K, for decodes of more than two
+// chunks, outside exact mode (the GEMM is tolerance-checked, not bit-exact: gemm_q4k_tc.cu).
+static bool prompt_gemm_ok(const pib_context * c, int n_tokens) {
+    const pib_model * m = c->model;
+    if (!c->prompt_gemm || c->gemv_variant != 0 || m->arch != 0 || m->wtype != PIB_TYPE_Q4_K || n_tokens <= 2 * PIB_CHUNK) return false;
+    for (int il = m->layer_begin; il < m->layer_end; il++) {
+        const pib_layer & L = m->layers[il];
+        if (L.wv) return false;
+        for (const pib_weight * w : { L.wqkv, L.wo, L.wgu, L.wdown }) if (!w || w->type != PIB_TYPE_Q4_K || !w->tiles) return false;
+    }
+    if (c->stage.last() && (!m->output || m->output->type != PIB_TYPE_Q4_K || !m->output->tiles)) return false;
+    return true;
+}
+
+static int prompt_bufs(pib_context * c) {
+    if (c->pb.ready) return PIB_OK;
+    const pib_model * m = c->model;
+    const size_t P = PIB_PROMPT_MAX, E = m->n_embd, GQA = m->n_embd_gqa(), FF = m->n_ff, KM = std::max(E, FF);
+    auto & b = c->pb;
+    if (cudaMalloc(&b.x, P * E * 4) != cudaSuccess || cudaMalloc(&b.x2, P * E * 4) != cudaSuccess || cudaMalloc(&b.qkv, P * (E + 2 * GQA) * 4) != cudaSuccess ||
+        cudaMalloc(&b.att, P * E * 4) != cudaSuccess || cudaMalloc(&b.proj, P * E * 4) != cudaSuccess || cudaMalloc(&b.gu, P * 2 * FF * 4) != cudaSuccess ||
+        cudaMalloc(&b.q16, P * E * 2) != cudaSuccess || cudaMalloc(&b.mask, P * c->n_ctx) != cudaSuccess ||
+        cudaMalloc(&b.act, pib_act_bytes(PIB_TYPE_Q4_K, (int64_t) KM, (int) P)) != cudaSuccess || cudaMalloc(&b.xhat, pib_gemm_xhat_bytes((int64_t) KM, (int) P)) != cudaSuccess) {
+        cudaGetLastError();
+        pib_set_error("decode: out of memory for the prompt path's work buffers");
+        return PIB_ERR_NOMEM;
+    }
+    b.ready = true;
+    return PIB_OK;
+}
+
+// one pass of `ntok` tokens = chunks [ch0, ch0 + nch) of the run
+static int run_prompt_pass(pib_context * c, pib_run & run, int ch0, int nch, int ntok, const std::vector<int> & slots) {
+    pib_model *  m  = c->model;
+    const int    E = m->n_embd, GQA = m->n_embd_gqa(), FF = m->n_ff, hd = m->head_dim(), wt = m->wtype;
+    cudaStream_t st = c->stream;
+    const int *  cancel = c->cancel_table;
+    auto & B = c->pb;
+    int rc;
+#define RC(e) do { rc = (e); if (rc != PIB_OK) return rc; c->n_kernels++; } while (0)
+    auto desc_of = [&](int k) { return c->desc_dev + (size_t) dev_slot(c, slots[ch0 + k]) * c->desc_stride; };
+    auto nt_of   = [&](int k) { return std::min(PIB_CHUNK, ntok - k * PIB_CHUNK); };
+    for (int k = 0; k < nch; k++) {
+        const uint8_t * desc = desc_of(k);
+        const size_t    off  = (size_t) k * PIB_CHUNK;
+        if (c->stage.first()) RC(pib_get_rows(m->tok_embd, reinterpret_cast<const int32_t *>(desc + PIB_DESC_TOK_OFF), nt_of(k), B.x + off * E, st));
+        else if (c->hop_peer) { RC(pib_hop_recv_launch(c, nt_of(k), st)); cudaMemcpyAsync(B.x + off * E, c->x, (size_t) nt_of(k) * E * 4, cudaMemcpyDeviceToDevice, st); }
+        else if (pib_hop_recv) RC(pib_hop_recv(c, B.x + off * E, nt_of(k), cancel));
+        RC(kv_device_mask(&c->kvd, reinterpret_cast<const int32_t *>(desc + PIB_DESC_POS_OFF), reinterpret_cast<const uint32_t *>(desc + PIB_DESC_BITS_OFF), nt_of(k),
+                          B.mask + off * c->n_ctx, st));
+    }
+    bool pending_add = false;
+    for (int il = m->layer_begin; il < m->layer_end; il++) {
+        const pib_layer & L  = m->layers[il];
+        const size_t      lo = (size_t) (il - m->layer_begin) * c->n_ctx * GQA;
+        if (pending_add) RC(pib_add_rmsnorm_quantize_act(wt, B.proj, B.x2, B.x, L.attn_norm, m->rms_eps, ntok, E, B.act, cancel, st));
+        else             RC(pib_add_rmsnorm_quantize_act(wt, B.x, nullptr, nullptr, L.attn_norm, m->rms_eps, ntok, E, B.act, cancel, st));
+        RC(pib_gemm_q4k_tc(L.wqkv, B.act, ntok, B.qkv, B.xhat, st));
+        for (int k = 0; k < nch; k++) {
+            const size_t off = (size_t) k * PIB_CHUNK;
+            RC(pib_rope_kv_store(B.qkv + off * (E + 2 * GQA), desc_of(k), c->rope, c->rope_n_pos, nt_of(k), E, GQA, hd, 0, B.q16 + off * E, c->kcache + lo, c->vcache + lo, cancel, st));
+        }
+        for (int k = 0; k < nch; k++) {
+            const size_t off = (size_t) k * PIB_CHUNK;
+            RC(pib_attention(B.q16 + off * E, c->kcache + lo, c->vcache + lo, B.mask + off * c->n_ctx, c->kvd.scalars, desc_of(k), nt_of(k), m->n_head, m->n_head_kv, hd,
+                             (int) c->n_ctx, B.att + off * E, cancel, st));
+        }
+        RC(pib_quantize_act_c(wt, B.att, ntok, E, B.act, cancel, st));
+        RC(pib_gemm_q4k_tc(L.wo, B.act, ntok, B.proj, B.xhat, st));
+        RC(pib_add_rmsnorm_quantize_act(wt, B.proj, B.x, B.x2, L.ffn_norm, m->rms_eps, ntok, E, B.act, cancel, st));
+        RC(pib_gemm_q4k_tc(L.wgu, B.act, ntok, B.gu, B.xhat, st));
+        RC(pib_silu_mul_quantize_act(wt, B.gu, B.gu + FF, 2 * (int64_t) FF, ntok, FF, B.act, cancel, st));
+        RC(pib_gemm_q4k_tc(L.wdown, B.act, ntok, B.proj, B.xhat, st));
+        pending_add = true;
+    }
+    if (c->stage.last()) {
+        if (pending_add) RC(pib_add_rmsnorm_quantize_act(wt, B.proj, B.x2, B.x, m->output_norm, m->rms_eps, ntok, E, B.act, cancel, st));
+        else             RC(pib_add_rmsnorm_quantize_act(wt, B.x, nullptr, nullptr, m->output_norm, m->rms_eps, ntok, E, B.act, cancel, st));
+        float * lg = run.logits + (size_t) ch0 * PIB_CHUNK * m->n_vocab;
+        RC(pib_gemm_q4k_tc(m->output, B.act, ntok, lg, B.xhat, st));
+        RC(pib_sample_topk(lg, ntok, m->n_vocab, c->bias_ids_dev, c->bias_val_dev, c->n_bias, run.res_dev + (size_t) ch0 * PIB_CHUNK, desc_of(0), cancel, st));
+    } else {
+        // the stage's output, chunk by chunk, to the next stage (its hop slots hold one 16-token chunk each)
+        for (int k = 0; k < nch; k++) {
+            const size_t off = (size_t) k * PIB_CHUNK * E;
+            if (c->hop_peer) {
+                if (pending_add) RC(pib_hop_send_launch(c, B.proj + off, B.x2 + off, nullptr, nt_of(k), st));
+                else             RC(pib_hop_send_launch(c, B.x + off, nullptr, nullptr, nt_of(k), st));
+                pib_pipe_hop_account((size_t) nt_of(k) * E * 4);
+            } else if (pib_hop_send) {
+                if (pending_add) {
+                    const int64_t n = (int64_t) nt_of(k) * E;
+                    pib_launch(add_kernel, dim3((unsigned) ((n + 255) / 256)), dim3(256), 0, st, B.proj + off, B.x2 + off, B.x + off, n, cancel);
+                    c->n_kernels++;
+                }
+                RC(pib_hop_send(c, B.x + off, nt_of(k), cancel));
+            }
+        }
+    }
+#undef RC
+    return PIB_OK;
+}
+
 static pib_run * take_run(pib_context * c, int n_tokens) {
     for (auto & r : c->runs) {
         if (r.in_use || r.id == c->last_finished) continue;
@@ -864,6 +976,14 @@ static int enqueue_decode(pib_context * c, pib_run * run, int n_tokens, int batc
     SLOW_MARK("  apply ops");
     run->in_use = true; run->batch_id = batch_id; run->n_tokens = n_tokens; run->failed = false;
     cudaMemcpyAsync(c->cancel_table, c->run_id_host + run->id, sizeof(int), cudaMemcpyHostToDevice, c->stream);   // "this run executes now"
+    if (prompt_gemm_ok(c, n_tokens) && prompt_bufs(c) == PIB_OK) {
+        const int per = PIB_PROMPT_MAX / PIB_CHUNK;
+        for (int ch0 = 0; ch0 < n_chunks && !run->failed; ch0 += per) {
+            const int nch = std::min(per, n_chunks - ch0), ntok = std::min(PIB_PROMPT_MAX, n_tokens - ch0 * PIB_CHUNK);
+            if (run_prompt_pass(c, *run, ch0, nch, ntok, slots) != PIB_OK) run->failed = true;
+        }
+        for (int ch = 0; ch < n_chunks; ch++) if (c->desc_ev[slots[ch]]) cudaEventRecord(c->desc_ev[slots[ch]], c->stream);
+    } else
     for (int ch = 0; ch < n_chunks; ch++) {
         const int nt = std::min(PIB_CHUNK, n_tokens - ch * PIB_CHUNK);
         if (run_chunk(c, *run, ch, nt, slots[ch]) != PIB_OK) { run->failed = true; break; }
@@ -1021,7 +1141,7 @@ void pib_cancel(pib_context * c, const int32_t * batch_ids, int n) {
             }
         }
     if (wrote) { cudaEventRecord(c->cancel_ev, c->ctrl); c->cancel_ev_pending = true; }
-    if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_ints(3, 0, batch_ids, n);
+    if (c->stage.size > 1 && c->stage.first()) pib_pipe_ship_cancel(batch_ids, n);
 }
 
 void pib_set_logit_bias(pib_context * c, const int32_t * ids, const float * vals, int n) {

@@ -12,6 +12,7 @@
 #include <vector>
 
 #define PIB_TOPK 8
+#define PIB_PROMPT_MAX 256           // tokens per pass of the tensor-core prompt path (gemm_q4k_tc.cu)
 struct pib_row_result {            // per logits row: sorted top-8 {id, logit, p}; entry 0 is the greedy token
     int32_t id[PIB_TOPK];
     float   logit[PIB_TOPK];
@@ -122,6 +123,11 @@ struct pib_context {
     cudaEvent_t cancel_ev = nullptr;       // recorded on `ctrl` after every cancel write: the clearing memset on `stream` waits for it
     bool     cancel_ev_pending = false;
 
+    // wide-batch (prompt) path: work buffers for up to PIB_PROMPT_MAX tokens at once, allocated on the first prompt that uses them
+    struct PromptBufs { float * x = nullptr, * x2 = nullptr, * qkv = nullptr, * att = nullptr, * proj = nullptr, * gu = nullptr; __half * q16 = nullptr;
+                        uint8_t * mask = nullptr; void * act = nullptr, * xhat = nullptr; bool ready = false; } pb;
+    int      prompt_gemm = 1;              // 0: prompts go through the GEMV kernels in chunks of 16 (PIB_PROMPT_GEMM=0, and always in exact mode)
+
     // peer-store hop (pipeline.cu): this stage's exported buffer, the next stage's (mapped), the previous stage's (mapped)
     void *   hop_mine = nullptr, * hop_next = nullptr, * hop_prev = nullptr;
     size_t   hop_slot_f4 = 0;
@@ -199,6 +205,7 @@ int  pib_pipe_ship_decode(int batch_id, int n_tokens, int n_chunks, const uint8_
                           const int * slots, const KvOp * ops, int n_ops);
 int  pib_pipe_ship_ints(int kind, int tag, const int32_t * vals, int n);      // kind: 2 finish, 3 cancel, 5 return, 6 shutdown
 int  pib_pipe_ship_bias(const int32_t * ids, const float * vals, int n);
+int  pib_pipe_ship_cancel(const int32_t * batch_ids, int n);
 int  pib_pipe_send_results(pib_context * c, pib_run & run);
 int  pib_pipe_post_result_recv(pib_context * c, pib_run & run);
 int  pib_pipe_fetch_logits(pib_context * c, int row, float * dev_staging, float * host_dst);

@@ -28,6 +28,7 @@
 #include <sys/mman.h>
 #include <sys/stat.h>
 #include <sys/time.h>
+#include <time.h>
 #include <unistd.h>
 
 #include <algorithm>
@@ -265,6 +266,29 @@ int pib_pipe_ship_ints(int kind, int tag, const int32_t * vals, int n) {
     if (n) memcpy(q + 2, vals, sizeof(int32_t) * (size_t) n);
     rec_commit();
     return PIB_OK;
+}
+
+// cancel record: the batch ids, then the head's monotonic clock (ns) at the moment of the decision, for the latency statistics below
+static int64_t mono_ns() { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return (int64_t) ts.tv_sec * 1000000000ll + ts.tv_nsec; }
+int pib_pipe_ship_cancel(const int32_t * batch_ids, int n) {
+    if (!pib_pipe_ring_active() || P.rank != 0) return PIB_OK;
+    uint8_t * p = rec_begin(REC_CANCEL, sizeof(int32_t) * (size_t) (n + 4));
+    if (!p) return PIB_ERR_NOMEM;
+    int32_t * q = (int32_t *) p;
+    q[0] = 0; q[1] = n;
+    memcpy(q + 2, batch_ids, sizeof(int32_t) * (size_t) n);
+    const int64_t t = mono_ns();
+    memcpy(q + 2 + n, &t, 8);
+    rec_commit();
+    return PIB_OK;
+}
+// stage side: head decision -> record seen by this stage's host -> cancel word written on this stage's GPU (the latter only with
+// PIB_CANCEL_TIMING=1: it synchronises the control stream after every cancel)
+static struct { uint64_t n = 0; double host_sum = 0, host_max = 0, dev_sum = 0, dev_max = 0; uint64_t n_dev = 0; } g_cancel_stats;
+extern "C" void pib_pipe_cancel_stats(uint64_t * n, double * host_mean_us, double * host_max_us, double * dev_mean_us, double * dev_max_us) {
+    *n = g_cancel_stats.n;
+    *host_mean_us = g_cancel_stats.n ? g_cancel_stats.host_sum / g_cancel_stats.n : 0; *host_max_us = g_cancel_stats.host_max;
+    *dev_mean_us = g_cancel_stats.n_dev ? g_cancel_stats.dev_sum / g_cancel_stats.n_dev : 0; *dev_max_us = g_cancel_stats.dev_max;
 }
 
 int pib_pipe_ship_bias(const int32_t * ids, const float * vals, int n) {
@@ -595,7 +619,20 @@ int pib_stage_serve(pib_context * c) {
                 rc = pib_decode_replay(c, d->batch_id, d->n_tokens, d->n_chunks, descs, d->desc_stride, ops, d->n_ops);
             } break;
             case REC_FINISH: { const int32_t * q = (const int32_t *) p; for (int i = 0; i < q[1]; i++) pib_stage_finish(c, q[2 + i]); } break;
-            case REC_CANCEL: { const int32_t * q = (const int32_t *) p; pib_cancel(c, q + 2, q[1]); } break;
+            case REC_CANCEL: {
+                const int32_t * q = (const int32_t *) p;
+                int64_t t0;
+                memcpy(&t0, q + 2 + q[1], 8);
+                const double host_us = (mono_ns() - t0) / 1000.0;
+                g_cancel_stats.n++; g_cancel_stats.host_sum += host_us; g_cancel_stats.host_max = std::max(g_cancel_stats.host_max, host_us);
+                pib_cancel(c, q + 2, q[1]);
+                static const bool timing = getenv("PIB_CANCEL_TIMING") && atoi(getenv("PIB_CANCEL_TIMING")) != 0;
+                if (timing) {
+                    cudaStreamSynchronize(c->ctrl);
+                    const double dev_us = (mono_ns() - t0) / 1000.0;
+                    g_cancel_stats.n_dev++; g_cancel_stats.dev_sum += dev_us; g_cancel_stats.dev_max = std::max(g_cancel_stats.dev_max, dev_us);
+                }
+            } break;
             case REC_BIAS:   { const int32_t * q = (const int32_t *) p; pib_set_logit_bias(c, q + 2, (const float *) (q + 2 + q[1]), q[1]); } break;
             case REC_INTS:   { const int32_t * q = (const int32_t *) p; P.last_tag = q[0]; P.last_count = q[1]; } break;
             case REC_LOGITS: { const int32_t * q = (const int32_t *) p; rc = send_logits_row(c, q[2]); } break;

@@ -131,6 +131,16 @@ class StageContext(llama.Context):
         self.L.llama_pib_pipe_shutdown(self.ctx)
 
 
+def cancel_stats():
+    """this stage's cancel-path latencies: (records, mean / max us head decision -> record seen by the stage's host, mean / max us
+    head decision -> cancel word written on the stage's GPU; the latter only when PIB_CANCEL_TIMING=1)"""
+    L = llama.api()
+    n = C.c_uint64()
+    v = [C.c_double() for _ in range(4)]
+    L.pib_pipe_cancel_stats(C.byref(n), *[C.byref(x) for x in v])
+    return (n.value,) + tuple(x.value for x in v)
+
+
 def traffic():
     L = llama.api()
     _bind(L)

@@ -139,8 +139,9 @@ def _replay_checked(llama, golden_dir, model_path, stem, n_ctx, max_seq, exact=F
 # (7B), 290 cells in use of a 1024-cell cache, 3002 sequence ids (94-word sets in the mask predicate), batches of 208 / 64
 # tokens (multi-chunk) and of 9 (two n-tiles), and -- wide_long -- a 6144-cell cache with 300+ cells attended.  All compared
 # with what the reference's CPU build returned for the same calls.  These two-layer models have large weights on purpose
-# (every layer matters, attention included), which also makes them amplify a rounding flip ~50x: the fast mode is held to
-# 2e-1 here and the point of the fixture is the exact mode.
+# (every layer matters, attention included), which also makes them amplify a rounding flip ~50x: the fast mode -- whose 208- and
+# 64-token batches go through the fp16 tensor-core GEMM -- is held to 3e-1 here (logit scale 4.8) and the point of the fixture
+# is the exact mode.
 WIDE = [("wide_q4_k", "wide_q4_k.gguf", 1024, 3002, 9), ("wide_q4_0", "wide_q4_0.gguf", 1024, 3002, 9), ("wide_long", "wide_q4_k.gguf", 6144, 8, 3)]
 
 
@@ -151,7 +152,7 @@ def test_decode_trace_at_benchmark_attention_shapes(llama, golden_dir, stem, mod
     print("%s (%s): max|logit - reference| per decode: %s; rows above 1e-4: %d of %d; near ties: %s"
           % (stem, "exact" if exact else "fast", " ".join("%.2g" % e for e in errs), int((rows > 1e-4).sum()), len(rows), ties))
     assert got_dec == n_dec
-    assert max(errs) == 0.0 if exact else max(errs) <= 2e-1
+    assert max(errs) == 0.0 if exact else max(errs) <= 3e-1
 
 
 @pytest.mark.parametrize("exact", [True, False])
@@ -262,6 +263,34 @@ def test_cancel_mid_flight_on_k_split_shapes_leaves_the_next_decode_intact(llama
             for s_ in range(b):
                 ctx.seq_rm(s_, 8, -1)
     ctx.close()
+
+
+def test_prompt_through_the_tensor_core_gemm_matches_the_chunked_path(llama):
+    """north_star item 2: prompts (> 32 tokens) run their matmuls on the tcgen05 GEMM, 256 tokens per pass; verification batches keep the
+    GEMV.  Same model, same 300-token prompt, both ways: logits within 2e-2 of each other (fp16 operands against int8 x int4 integer
+    arithmetic, on a model whose top logits are ~10), same argmax on every row that is not a near tie; and the KV cache the GEMM pass
+    leaves behind serves a following single-token decode equally well."""
+    shape = (4, 2048, 16, 2, 5632 // 256 * 256, 4096, 12, 1, 1, 1.0)
+    toks = [3 + (i * 7919) % 4093 for i in range(301)]
+    out = {}
+    for mode in ("1", "0"):
+        os.environ["PIB_PROMPT_GEMM"] = mode
+        ctx = llama.Context(None, n_ctx=512, max_seq=4, synthetic=shape)
+        rc, lg = ctx.decode(toks[:300], list(range(300)), [[0]] * 300)
+        assert rc == 0
+        rc, nxt = ctx.decode(toks[300:], [300], [[0]])
+        assert rc == 0
+        out[mode] = (lg, nxt)
+        ctx.close()
+    os.environ.pop("PIB_PROMPT_GEMM")
+    for a, b in zip(out["1"], out["0"]):
+        d = np.abs(a - b).max(1)
+        scale = np.abs(b).max()
+        print("tensor-core prompt path vs chunked GEMV: max|diff| %.3g (logit scale %.3g), rows above 1e-2: %d of %d" % (d.max(), scale, int((d > 1e-2).sum()), len(d)))
+        assert d.max() <= 2e-2 * max(1.0, scale / 10)
+        for i in np.nonzero(a.argmax(1) != b.argmax(1))[0]:
+            top2 = np.sort(b[i])[-2:]
+            assert top2[1] - top2[0] <= 2 * d[i]
 
 
 def test_device_acceptance_walk_matches_the_host_walk(llama, golden_dir):

@@ -21,7 +21,26 @@ blk[:, :, 0:2] = (rng.uniform(0.5, 1.5, (a.N, a.K // be)) * 0.0025).astype(np.fl
 if wt == 12:
     blk[:, :, 2:4] = (rng.uniform(0.5, 1.5, (a.N, a.K // be)) * 0.001).astype(np.float16).view(np.uint8).reshape(a.N, a.K // be, 2)
 hs = [lib.weight_upload(wt, blk.reshape(a.N, -1), a.K) for _ in range(ncopies)]
+lib.L.pib_gemm_scratch_bytes.restype = C.c_size_t
+lib.L.pib_gemm_scratch_bytes.argtypes = [C.c_int64, C.c_int]
+lib.L.pib_gemm.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+lib.L.pib_quantize_act_rows.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p]
 for b in [int(x) for x in a.b.split(",")]:
+    if b > 16:                                   # wide batches: the tcgen05 GEMM (Q4_K)
+        x = rng.standard_normal((b, a.K)).astype(np.float32)
+        xd = lib.to_device(x)
+        act = lib.alloc(lib.L.pib_act_bytes(wt, a.K, b)); yd = lib.alloc(b * a.N * 4); sc = lib.alloc(lib.L.pib_gemm_scratch_bytes(a.K, b))
+        lib.check(lib.L.pib_quantize_act_rows(wt, xd, b, a.K, act, None))
+        for i in range(3):
+            lib.check(lib.L.pib_gemm(hs[i % ncopies], act, b, yd, sc, None))
+        lib.check(lib.L.pib_stream_sync(None))
+        t0 = time.perf_counter()
+        for i in range(a.reps):
+            lib.L.pib_gemm(hs[i % ncopies], act, b, yd, sc, None)
+        lib.check(lib.L.pib_stream_sync(None))
+        dt = (time.perf_counter() - t0) / a.reps
+        print("%s %dx%d b=%d tcgen05 gemm: %.1f us  %.1f TFLOP/s  (weights at %.0f GB/s)" % (a.type, a.N, a.K, b, dt * 1e6, 2.0 * a.N * a.K * b / dt / 1e12, wbytes / dt / 1e9), flush=True)
+        continue
     x = rng.standard_normal((b, a.K)).astype(np.float32)
     xd = lib.to_device(x)
     act = lib.alloc(lib.L.pib_act_bytes(wt, a.K, b))
