@@ -87,36 +87,43 @@ bool llama_save_session_file(struct llama_context * ctx, const char * path_sessi
 }
 
 // ---- samplers (llama.cpp:7019-7500) ----
-void llama_sample_top_k(struct llama_context * ctx, llama_token_data_array * candidates, int k, size_t min_keep) {      // :7048
-    (void) ctx;
-    k = std::max(k, (int) min_keep);
-    k = std::min(k, (int) candidates->size);
-    if (!candidates->sorted) {
-        auto comp = [](const llama_token_data & a, const llama_token_data & b) { return a.logit > b.logit; };
-        if (k == (int) candidates->size) std::sort(candidates->data, candidates->data + candidates->size, comp);
-        else std::partial_sort(candidates->data, candidates->data + k, candidates->data + candidates->size, comp);
-        candidates->sorted = true;
+// The three truncation samplers below exist so that the reference's unmodified common/sampling.cpp links against this library;
+// greedy decoding (the path of SURVEY.md section 8) never calls them.  Behaviour as llama.cpp:7048-7130, own formulation.
+static inline bool by_logit_desc(const llama_token_data & a, const llama_token_data & b) { return a.logit > b.logit; }
+
+void llama_sample_top_k(struct llama_context *, llama_token_data_array * cand, int k, size_t min_keep) {
+    const size_t want = std::min(cand->size, (size_t) std::max<long long>(k, (long long) min_keep));
+    if (!cand->sorted) {
+        // the same library algorithms as the reference (heap-based partial sort unless everything is kept): with equal logits
+        // the order among them is whatever those algorithms leave, and callers compare ids
+        llama_token_data * first = cand->data, * last = cand->data + cand->size;
+        if (want < cand->size) std::partial_sort(first, first + want, last, by_logit_desc);
+        else                   std::sort(first, last, by_logit_desc);
+        cand->sorted = true;
     }
-    candidates->size = (size_t) k;
+    cand->size = want;
 }
-void llama_sample_top_p(struct llama_context * ctx, llama_token_data_array * candidates, float p, size_t min_keep) {    // :7073
-    if (p >= 1.0f) return;
-    llama_sample_softmax(ctx, candidates);
-    float  cum_sum  = 0.0f;
-    size_t last_idx = candidates->size;
-    for (size_t i = 0; i < candidates->size; ++i) {
-        cum_sum += candidates->data[i].p;
-        if (cum_sum >= p && i + 1 >= min_keep) { last_idx = i + 1; break; }
+
+void llama_sample_top_p(struct llama_context * ctx, llama_token_data_array * cand, float p, size_t min_keep) {
+    if (!(p < 1.0f)) return;
+    llama_sample_softmax(ctx, cand);                   // sorted, probabilities filled in
+    // shortest prefix whose mass reaches p (fp32 running sum, left to right), but never fewer than min_keep entries
+    float  mass = 0.0f;
+    size_t n    = 0;
+    while (n < cand->size) {
+        mass += cand->data[n++].p;
+        if (mass >= p && n >= min_keep) break;
     }
-    candidates->size = last_idx;
+    cand->size = n;
 }
-void llama_sample_min_p(struct llama_context * ctx, llama_token_data_array * candidates, float p, size_t min_keep) {    // :7105
-    if (p <= 0.0f || !candidates->size) return;
-    llama_sample_softmax(ctx, candidates);
-    const float scale = candidates->data[0].p;
-    size_t i = 1;
-    for (; i < candidates->size; ++i) if (candidates->data[i].p < p * scale && i >= min_keep) break;
-    candidates->size = i;
+
+void llama_sample_min_p(struct llama_context * ctx, llama_token_data_array * cand, float p, size_t min_keep) {
+    if (cand->size == 0 || !(p > 0.0f)) return;
+    llama_sample_softmax(ctx, cand);
+    const float floor_p = p * cand->data[0].p;         // relative to the most likely token
+    size_t n = 1;
+    while (n < cand->size && !(cand->data[n].p < floor_p && n >= min_keep)) n++;
+    cand->size = n;
 }
 // tail-free sampling: cut the candidates where the cumulated, normalised |second difference| of the sorted probabilities passes z
 void llama_sample_tail_free(struct llama_context * ctx, llama_token_data_array * candidates, float z, size_t min_keep) { // :7131

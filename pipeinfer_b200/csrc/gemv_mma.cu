@@ -517,35 +517,34 @@ gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K
 // ---- launcher -----------------------------------------------------------------------------------------------------------
 // scratch for the k-split path: partial sums [split][b][N] + one counter per row tile.  One set per (device, stream):
 // launches on one stream are serialised, so they can share it; two contexts (target and draft) running on their own
-// streams at the same time must not.  Allocated on first use, grown on demand, never shrunk.
+// streams at the same time must not.
 struct mm_scratch { float * partial = nullptr; unsigned int * counters = nullptr; size_t partial_floats = 0; size_t n_counters = 0; };
 static std::map<std::pair<int, cudaStream_t>, mm_scratch> g_scratch;
 static std::mutex                                        g_scratch_mu;
 
+// Fixed size, allocated once per (device, stream) and never again: captured CUDA graphs keep these addresses.  A launch whose
+// split would not fit is given a smaller split by its caller (fit_split); one that cannot fit at all is refused.
+#define MM_SCRATCH_FLOATS   ((size_t) 8 << 20)          /* 32 MiB: two splits of 16 tokens x 118784 rows */
+#define MM_SCRATCH_COUNTERS ((size_t) 8192)
 static int ensure_scratch(size_t floats, size_t counters, cudaStream_t st, mm_scratch ** out) {
+    if (floats > MM_SCRATCH_FLOATS || counters > MM_SCRATCH_COUNTERS) return PIB_ERR_ARG;
     int dev = 0;
     cudaGetDevice(&dev);
     std::lock_guard<std::mutex> lock(g_scratch_mu);
     mm_scratch & s = g_scratch[std::make_pair(dev, st)];
-    // sized once for every shape the split rules can produce (a split is used only while tiles x splits stays below a few
-    // CTAs per SM): captured CUDA graphs keep these addresses, so growing later must not happen in practice
-    if (floats < ((size_t) 8 << 20)) floats = (size_t) 8 << 20;          // 32 MiB: two splits of 16 tokens x 118784 rows fit
-    if (counters < 8192) counters = 8192;
-    if (s.partial_floats < floats) {
-        if (s.partial) { cudaStreamSynchronize(st); cudaFree(s.partial); }
-        s.partial = nullptr; s.partial_floats = 0;
-        if (cudaMalloc(&s.partial, floats * sizeof(float)) != cudaSuccess) { cudaGetLastError(); return PIB_ERR_NOMEM; }
-        s.partial_floats = floats;
-    }
-    if (s.n_counters < counters) {
-        if (s.counters) { cudaStreamSynchronize(st); cudaFree(s.counters); }
-        s.counters = nullptr; s.n_counters = 0;
-        if (cudaMalloc(&s.counters, counters * sizeof(unsigned int)) != cudaSuccess) { cudaGetLastError(); return PIB_ERR_NOMEM; }
-        cudaMemset(s.counters, 0, counters * sizeof(unsigned int));
-        s.n_counters = counters;
+    if (!s.partial) {
+        if (cudaMalloc(&s.partial, MM_SCRATCH_FLOATS * sizeof(float)) != cudaSuccess) { cudaGetLastError(); s.partial = nullptr; return PIB_ERR_NOMEM; }
+        if (cudaMalloc(&s.counters, MM_SCRATCH_COUNTERS * sizeof(unsigned int)) != cudaSuccess) { cudaGetLastError(); cudaFree(s.partial); s.partial = nullptr; return PIB_ERR_NOMEM; }
+        cudaMemset(s.counters, 0, MM_SCRATCH_COUNTERS * sizeof(unsigned int));
+        s.partial_floats = MM_SCRATCH_FLOATS; s.n_counters = MM_SCRATCH_COUNTERS;
     }
     *out = &s;
     return PIB_OK;
+}
+// largest split <= want whose partial sums and counters fit the fixed scratch (1 = no scratch needed)
+static int fit_split(int want, int b, int64_t N, int n_tiles) {
+    while (want > 1 && ((size_t) want * b * N > MM_SCRATCH_FLOATS || (size_t) n_tiles > MM_SCRATCH_COUNTERS)) want /= 2;
+    return want;
 }
 
 bool pib_gemv_mma_supported(const pib_weight * w, int b) {
@@ -627,7 +626,7 @@ int pib_gemv_mma_launch(const pib_weight * w, const void * act_dev, int b, float
 int pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
     if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: variant 2 needs Q4_K weights with tiles"); return PIB_ERR_UNSUPP; }
     const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
-    const int split = choose_split_direct(n_tiles, nsb);
+    const int split = fit_split(choose_split_direct(n_tiles, nsb), b, w->N, n_tiles);
     mm_scratch * s = nullptr;
     if (split > 1) {
         if (ensure_scratch((size_t) split * b * w->N, (size_t) n_tiles, st, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
@@ -639,7 +638,8 @@ int pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y
 int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
     if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: variant 3 needs Q4_K weights with tiles"); return PIB_ERR_UNSUPP; }
     const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
-    const int split = choose_lg_split(n_tiles, nsb);
+    int split = choose_lg_split(n_tiles, nsb);
+    while (split > 0 && (((size_t) b << split) * w->N > MM_SCRATCH_FLOATS || (size_t) n_tiles > MM_SCRATCH_COUNTERS)) split--;
     mm_scratch * s = nullptr;
     if (split > 0) {
         if (ensure_scratch(((size_t) b << split) * w->N, (size_t) n_tiles, st, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }

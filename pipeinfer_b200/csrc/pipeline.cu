@@ -791,13 +791,17 @@ int ggml_mpi_status_count_int32(struct ggml_mpi_context * ctx) { (void) ctx; ret
 void ggml_mpi_send_float_array_async(struct ggml_mpi_context * ctx, float * val, int arr_size, int dest, int tag) {
     (void) ctx; (void) tag;
     if (!pib_pipe_nccl_active()) return;
-    N.Send(val, (size_t) arr_size, ncclFloat, dest, P.back, P.res_stream);
+    // the reference's transport aborts on a failed MPI call (MPI_ERRORS_ARE_FATAL); a silent loss here would hang the peer
+    const ncclResult_t r = N.Send(val, (size_t) arr_size, ncclFloat, dest, P.back, P.res_stream);
+    if (r != ncclSuccess) { fprintf(stderr, "ggml_mpi_send_float_array_async: %s\n", N.GetErrorString(r)); abort(); }
 }
 void ggml_mpi_recv_float_array(struct ggml_mpi_context * ctx, float * val, int arr_size, int src, int tag) {
     (void) ctx; (void) tag;
     if (!pib_pipe_nccl_active()) return;
-    N.Recv(val, (size_t) arr_size, ncclFloat, src, P.back, P.res_stream);
-    cudaStreamSynchronize(P.res_stream);
+    const ncclResult_t r = N.Recv(val, (size_t) arr_size, ncclFloat, src, P.back, P.res_stream);
+    if (r != ncclSuccess) { fprintf(stderr, "ggml_mpi_recv_float_array: %s\n", N.GetErrorString(r)); abort(); }
+    const cudaError_t e = cudaStreamSynchronize(P.res_stream);
+    if (e != cudaSuccess) { fprintf(stderr, "ggml_mpi_recv_float_array: %s\n", cudaGetErrorString(e)); abort(); }
 }
 
 // :523-559; the outer array and the rows are malloc'd, the caller frees the outer array (llama.cpp:8934-8936)
