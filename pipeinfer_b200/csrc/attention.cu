@@ -86,9 +86,16 @@ __global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8
 // output dims and a share of the 32 accumulators, each a sequential chain over its cells.  K/V of a KV head are re-read by its
 // G query heads through L2 -- a few MB per layer at these context lengths.  Masked cells are never loaded.
 #define ATQ_THREADS 256
+// RoPE, KV store and attention in one launch.  A CTA rotates its own query head itself, rotates / converts the K and V rows of
+// ALL tokens of the batch for its KV head into shared memory (<= 16 rows: the batch's cells are the contiguous range starting at
+// the descriptor's kv head, and a token of a tree batch attends to earlier tokens of the same batch), and the first query head
+// of each KV group also writes its token's K / V row to the cache.  Cells of the batch are therefore never read from global
+// memory, cells outside it never written: no ordering between CTAs is needed.  Values and roundings are those of the separate
+// rope_kv_store_kernel (reference rope_f32 ggml.c:11006, dup f32 -> f16 :6528).
 template <int HD>
-__global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half * __restrict__ q16, const __half * __restrict__ kcache,
-                                                                   const __half * __restrict__ vcache, const uint8_t * __restrict__ mask,
+__global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const float * __restrict__ qkv, const float * __restrict__ vsep,
+                                                                   const uint8_t * __restrict__ desc, const float2 * __restrict__ rope, int rope_n_pos, int mode,
+                                                                   __half * __restrict__ kcache, __half * __restrict__ vcache, const uint8_t * __restrict__ mask,
                                                                    const int32_t * __restrict__ scalars, const uint16_t * __restrict__ exp_lut,
                                                                    int E, int GQA, int n_ctx, float kq_scale, float * __restrict__ out,
                                                                    const int * __restrict__ cancel, int gdiv) {
@@ -100,13 +107,42 @@ __global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half 
     __shared__ float  s_redf[ATQ_THREADS / 32];
     __shared__ double s_redd[ATQ_THREADS / 32];
     __shared__ float  s_max, s_inv;
+    __shared__ __align__(16) __half kb[PIB_CHUNK][HD], vb[PIB_CHUNK][HD];      // this KV head's rows of the batch's tokens
     const int head = blockIdx.x, kvh = head / gdiv, t = blockIdx.y;
     const int n = scalars[2];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float *         s    = smem;                       // [n] scores -> probabilities
     const uint8_t * mrow = mask + (size_t) t * n_ctx;
-    if (tid < HD) sq[tid] = __half2float(q16[(size_t) t * E + (size_t) head * HD + tid]);
+    const int32_t * hdr  = reinterpret_cast<const int32_t *>(desc + PIB_DESC_HDR_OFF);
+    const int32_t * tpos = reinterpret_cast<const int32_t *>(desc + PIB_DESC_POS_OFF);
+    const int       ntok = hdr[PIB_DH_NTOK], cell0 = hdr[PIB_DH_KVHEAD];
+    const int       rstride = E + (vsep ? 1 : 2) * GQA, half = HD / 2;
+    {
+        // rotate: pair j of a head = elements (2j, 2j+1), or (j, j + HD/2) in NeoX mode; unfused multiplies as the reference (-std=c11)
+        for (int i = tid; i < (ntok + 1) * half; i += ATQ_THREADS) {
+            const int     r = i / half, j = i - r * half;              // r < ntok: K row of batch token r; r == ntok: this CTA's query
+            const int     tok = r < ntok ? r : t;
+            const float * src = qkv + (size_t) tok * rstride + (r < ntok ? E + (size_t) kvh * HD : (size_t) head * HD);
+            const float2  cs  = rope[(size_t) min(tpos[tok], rope_n_pos - 1) * half + j];
+            const int     i0 = (mode & 2) ? j : 2 * j, i1 = (mode & 2) ? j + half : 2 * j + 1;
+            const float   x0 = src[i0], x1 = src[i1];
+            const __half  y0 = __float2half_rn(__fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y)));
+            const __half  y1 = __float2half_rn(__fadd_rn(__fmul_rn(x0, cs.y), __fmul_rn(x1, cs.x)));
+            if (r < ntok) { kb[r][i0] = y0; kb[r][i1] = y1; }
+            else          { sq[i0] = __half2float(y0); sq[i1] = __half2float(y1); }
+        }
+        for (int i = tid; i < ntok * HD; i += ATQ_THREADS) {
+            const int r = i / HD, d = i - r * HD;
+            const float * v = vsep ? vsep + (size_t) r * GQA : qkv + (size_t) r * rstride + E + GQA;
+            vb[r][d] = __float2half_rn(v[(size_t) kvh * HD + d]);
+        }
+    }
     __syncthreads();
+    if (head == kvh * gdiv) {                           // first query head of the group: this token's K / V row goes to the cache
+        const size_t co = (size_t) (cell0 + t) * GQA + (size_t) kvh * HD;
+        if (tid < HD / 8) reinterpret_cast<uint4 *>(kcache + co)[tid] = reinterpret_cast<const uint4 *>(kb[t])[tid];
+        else if (tid < HD / 4) reinterpret_cast<uint4 *>(vcache + co)[tid - HD / 8] = reinterpret_cast<const uint4 *>(vb[t])[tid - HD / 8];
+    }
 
     // phase 1: scores, in the reference's order (ggml_vec_dot_f16, ggml.c:1200-1235 with the AVX2 reduce macro :772-790):
     // 32 fp32 accumulators, element e of the head goes to accumulator e mod 32, then ((0+2)+(1+3)) over the four 8-lane
@@ -115,7 +151,9 @@ __global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half 
     for (int i = tid; i < n; i += ATQ_THREADS) {
         float sc = -INFINITY;
         if (!mrow[i]) {
-            const uint4 * kr = reinterpret_cast<const uint4 *>(kcache + (size_t) i * GQA + (size_t) kvh * HD);
+            const int     bi = i - cell0;
+            const uint4 * kr = (bi >= 0 && bi < ntok) ? reinterpret_cast<const uint4 *>(kb[bi])
+                                                      : reinterpret_cast<const uint4 *>(kcache + (size_t) i * GQA + (size_t) kvh * HD);
             float a[4][8];
 #pragma unroll
             for (int j = 0; j < 4; j++)
@@ -174,7 +212,7 @@ __global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half 
     constexpr int TPR = HD / 2, NGR = ATQ_THREADS / TPR, APG = 32 / NGR;      // hd 128: 4 groups x 8 accumulators; hd 64: 8 x 4
     const int grp = tid / TPR, dp = tid % TPR;
     const int np  = n & ~31;
-    const __half * vb = vcache + (size_t) kvh * HD + dp * 2;
+    const __half * vg = vcache + (size_t) kvh * HD + dp * 2;
     float o0[APG], o1[APG];
 #pragma unroll
     for (int u = 0; u < APG; u++) { o0[u] = 0.f; o1[u] = 0.f; }
@@ -185,7 +223,9 @@ __global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half 
         for (int u = 0; u < APG; u++) {
             const int c = base + grp * APG + u;
             pp[u] = s[c];
-            vv[u] = pp[u] != 0.f ? *reinterpret_cast<const __half2 *>(vb + (size_t) c * GQA) : __half2();     // p == 0: the fma leaves the accumulator as it is
+            const int bi = c - cell0;
+            vv[u] = pp[u] == 0.f ? __half2()                                                               // p == 0: the fma leaves the accumulator as it is
+                  : (bi >= 0 && bi < ntok) ? *reinterpret_cast<const __half2 *>(&vb[bi][dp * 2]) : *reinterpret_cast<const __half2 *>(vg + (size_t) c * GQA);
         }
 #pragma unroll
         for (int u = 0; u < APG; u++) { o0[u] = fmaf(__low2float(vv[u]), pp[u], o0[u]); o1[u] = fmaf(__high2float(vv[u]), pp[u], o1[u]); }
@@ -203,23 +243,25 @@ __global__ void __launch_bounds__(ATQ_THREADS) attention_qh_kernel(const __half 
         double sumf = (double) __fadd_rn(__fadd_rn(t0, t1), __fadd_rn(t2, t3));
         for (int c = np; c < n; c++) {
             const float p = s[c];
-            if (p != 0.f) sumf += (double) __fmul_rn(__half2float(vcache[(size_t) c * GQA + (size_t) kvh * HD + tid]), p);
+            const int bi = c - cell0;
+            if (p != 0.f) sumf += (double) __fmul_rn(__half2float((bi >= 0 && bi < ntok) ? vb[bi][tid] : vcache[(size_t) c * GQA + (size_t) kvh * HD + tid]), p);
         }
         out[(size_t) t * E + (size_t) head * HD + tid] = (float) sumf;
     }
 }
 
 template <int HD>
-static int launch_att_qh(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
-                         int E, int GQA, int n_ctx, int n_tokens, int n_head, int gdiv, float * out, const int * cancel, cudaStream_t st) {
+static int launch_att_qh(const float * qkv, const float * vsep, const uint8_t * desc, const float2 * rope, int rope_n_pos, int mode, __half * kc, __half * vc,
+                         const uint8_t * mask, const int32_t * scalars, int E, int GQA, int n_ctx, int n_tokens, int n_head, int gdiv, float * out,
+                         const int * cancel, cudaStream_t st) {
     const size_t smem = ((size_t) n_ctx + 32 * HD) * sizeof(float);          // scores / probabilities + the 32 x HD partial sums
-    static size_t configured = 48 * 1024;
+    static size_t configured = 32 * 1024;
     if (smem > configured) {
         PIB_CHECK(cudaFuncSetAttribute(attention_qh_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         configured = smem;
     }
-    pib_launch(attention_qh_kernel<HD>, dim3(n_head, n_tokens), dim3(ATQ_THREADS), smem, st, q16, kc, vc, mask, scalars, pib_get_luts().exp_f16, E, GQA,
-                                                                               n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv);
+    pib_launch(attention_qh_kernel<HD>, dim3(n_head, n_tokens), dim3(ATQ_THREADS), smem, st, qkv, vsep, desc, rope, rope_n_pos, mode, kc, vc, mask, scalars,
+               pib_get_luts().exp_f16, E, GQA, n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }
@@ -235,16 +277,17 @@ int pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * ro
 bool pib_attention_supported(int hd, int n_head, int n_head_kv, int n_ctx) {
     if (hd != 64 && hd != 128) return false;
     if (n_head % n_head_kv) return false;
-    return ((size_t) n_ctx + 32 * hd) * sizeof(float) <= 220 * 1024;      // the scores of one (head, token) live in shared memory
+    return ((size_t) n_ctx + 32 * hd) * sizeof(float) <= 200 * 1024;      // the scores of one (head, token) live in shared memory
 }
 
-int pib_attention(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
-                  const uint8_t * desc, int n_tokens, int n_head, int n_head_kv, int hd, int n_ctx, float * out,
+// RoPE (mode 0: adjacent pairs, 2: NeoX) + KV store + attention of one chunk: qkv = the fused projection's output [n_tokens][E + 2 GQA]
+// (or [E + GQA] with V in vsep)
+int pib_attention(const float * qkv, const float * vsep, const uint8_t * desc, const float2 * rope, int rope_n_pos, int mode, __half * kc, __half * vc,
+                  const uint8_t * mask, const int32_t * scalars, int n_tokens, int n_head, int n_head_kv, int hd, int n_ctx, float * out,
                   const int * cancel, cudaStream_t st) {
-    (void) desc;
     const int E = n_head * hd, GQA = n_head_kv * hd, G = n_head / n_head_kv;
-    if (hd == 128) return launch_att_qh<128>(q16, kc, vc, mask, scalars, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
-    if (hd == 64)  return launch_att_qh<64>(q16, kc, vc, mask, scalars, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
+    if (hd == 128) return launch_att_qh<128>(qkv, vsep, desc, rope, rope_n_pos, mode, kc, vc, mask, scalars, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
+    if (hd == 64)  return launch_att_qh<64>(qkv, vsep, desc, rope, rope_n_pos, mode, kc, vc, mask, scalars, E, GQA, n_ctx, n_tokens, n_head, G, out, cancel, st);
     pib_set_error("attention: unsupported head_dim %d", hd);
     return PIB_ERR_UNSUPP;
 }

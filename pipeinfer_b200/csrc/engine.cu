@@ -32,13 +32,10 @@ int  pib_add_layernorm_quantize_act(int wtype, const float * x_dev, const float 
                                     int64_t K, void * act_dev, const int * cancel, cudaStream_t st);
 int  pib_gelu_quantize_act(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, const int * cancel, cudaStream_t st);
 void rope_table_build(std::vector<float2> & tab, int n_pos, int n_dims, int mode, float freq_base, float freq_scale);
-int  pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * rope, int rope_n_pos, int n_tokens, int E, int GQA,
-                       int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st,
-                       const float * vsep = nullptr);
 bool pib_attention_supported(int hd, int n_head, int n_head_kv, int n_ctx);
-int  pib_attention(const __half * q16, const __half * kc, const __half * vc, const uint8_t * mask, const int32_t * scalars,
-                   const uint8_t * desc, int n_tokens, int n_head, int n_head_kv, int hd, int n_ctx, float * out, const int * cancel,
-                   cudaStream_t st);
+int  pib_attention(const float * qkv, const float * vsep, const uint8_t * desc, const float2 * rope, int rope_n_pos, int mode, __half * kc, __half * vc,
+                   const uint8_t * mask, const int32_t * scalars, int n_tokens, int n_head, int n_head_kv, int hd, int n_ctx, float * out,
+                   const int * cancel, cudaStream_t st);
 int  pib_sample_topk(float * logits_dev, int n_rows, int n_vocab, const int32_t * bias_ids_dev, const float * bias_val_dev, int n_bias,
                      void * out_dev, const uint8_t * desc, const int * cancel, cudaStream_t st);
 int  pib_gemm_q4k_tc(const pib_weight * w, const void * act_dev, int b, float * y_dev, void * xhat_dev, cudaStream_t st);
@@ -593,9 +590,8 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
             GEMV(0, il, L.wqkv, c->qkv);
             if (L.attn_norm2) TL(9, il, pib_add_layernorm_quantize_act(wt, cur, nullptr, nullptr, nullptr, L.attn_norm, L.attn_norm_b, m->norm_eps, ntok, E, c->act, cancel, st));
             GEMV(2, il, L.wgu, c->gu);
-            TL(6, il, pib_rope_kv_store(c->qkv, desc, c->rope, c->rope_n_pos, ntok, E, GQA, hd, 2, c->q16, c->kcache + lo, c->vcache + lo, cancel, st));
-            TL(7, il, pib_attention(c->q16, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, desc, ntok, m->n_head, m->n_head_kv, hd,
-                                    (int) c->n_ctx, other, cancel, st));
+            TL(7, il, pib_attention(c->qkv, nullptr, desc, c->rope, c->rope_n_pos, 2, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, ntok, m->n_head,
+                                    m->n_head_kv, hd, (int) c->n_ctx, other, cancel, st));
             TL(8, il, pib_quantize_act_c(wt, other, ntok, E, c->act, cancel, st));
             GEMV(1, il, L.wo, c->proj);
             TL(10, il, pib_gelu_quantize_act(wt, c->gu, ntok, FF, c->act, cancel, st));
@@ -635,10 +631,8 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
         dump_dev(c, "q", il, c->qkv, ntok, E, E + (L.wv ? 1 : 2) * GQA);
         dump_dev(c, "k", il, c->qkv + E, ntok, GQA, E + (L.wv ? 1 : 2) * GQA);
         if (!L.wv) dump_dev(c, "v", il, c->qkv + E + GQA, ntok, GQA, E + 2 * GQA);
-        TL(6, il, pib_rope_kv_store(c->qkv, desc, c->rope, c->rope_n_pos, ntok, E, GQA, hd, 0, c->q16, c->kcache + lo, c->vcache + lo, cancel, st,
-                                    L.wv ? c->vsep : nullptr));
-        TL(7, il, pib_attention(c->q16, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, desc, ntok, m->n_head, m->n_head_kv, hd,
-                                (int) c->n_ctx, c->att, cancel, st));
+        TL(7, il, pib_attention(c->qkv, L.wv ? c->vsep : nullptr, desc, c->rope, c->rope_n_pos, 0, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, ntok,
+                                m->n_head, m->n_head_kv, hd, (int) c->n_ctx, c->att, cancel, st));
         dump_dev(c, "att", il, c->att, ntok, E, E);
         TL(8, il, pib_quantize_act_c(wt, c->att, ntok, E, c->act, cancel, st));
         GEMV(1, il, L.wo, c->proj);
@@ -794,14 +788,10 @@ static int run_prompt_pass(pib_context * c, pib_run & run, int ch0, int nch, int
         if (pending_add) RC(pib_add_rmsnorm_quantize_act(wt, B.proj, B.x2, B.x, L.attn_norm, m->rms_eps, ntok, E, B.act, cancel, st));
         else             RC(pib_add_rmsnorm_quantize_act(wt, B.x, nullptr, nullptr, L.attn_norm, m->rms_eps, ntok, E, B.act, cancel, st));
         RC(pib_gemm_q4k_tc(L.wqkv, B.act, ntok, B.qkv, B.xhat, st));
-        for (int k = 0; k < nch; k++) {
+        for (int k = 0; k < nch; k++) {          // chunk k + 1 reads chunk k's cells from the cache: stream order
             const size_t off = (size_t) k * PIB_CHUNK;
-            RC(pib_rope_kv_store(B.qkv + off * (E + 2 * GQA), desc_of(k), c->rope, c->rope_n_pos, nt_of(k), E, GQA, hd, 0, B.q16 + off * E, c->kcache + lo, c->vcache + lo, cancel, st));
-        }
-        for (int k = 0; k < nch; k++) {
-            const size_t off = (size_t) k * PIB_CHUNK;
-            RC(pib_attention(B.q16 + off * E, c->kcache + lo, c->vcache + lo, B.mask + off * c->n_ctx, c->kvd.scalars, desc_of(k), nt_of(k), m->n_head, m->n_head_kv, hd,
-                             (int) c->n_ctx, B.att + off * E, cancel, st));
+            RC(pib_attention(B.qkv + off * (E + 2 * GQA), nullptr, desc_of(k), c->rope, c->rope_n_pos, 0, c->kcache + lo, c->vcache + lo, B.mask + off * c->n_ctx,
+                             c->kvd.scalars, nt_of(k), m->n_head, m->n_head_kv, hd, (int) c->n_ctx, B.att + off * E, cancel, st));
         }
         RC(pib_quantize_act_c(wt, B.att, ntok, E, B.act, cancel, st));
         RC(pib_gemm_q4k_tc(L.wo, B.act, ntok, B.proj, B.xhat, st));
