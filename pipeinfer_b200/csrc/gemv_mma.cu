@@ -345,6 +345,71 @@ gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int n_tiles, in
     }
 }
 
+// the arithmetic of one (16-row tile, super-block) record for NT n-tiles of 8 tokens, shared by the kernels below
+template <int NT>
+__device__ __forceinline__ void q4k_record(const int4 (&wq)[4], const int4 (&hq)[2], int s, int t, const int8_t * const (&a_qs)[NT],
+                                           const int8_t * const (&a_b8)[NT], const float * const (&a_dx)[NT][2], float (&acc)[NT][4]) {
+    const q4k_hdr H0 = decode_hdr(make_uint4((uint32_t) hq[0].x, (uint32_t) hq[0].y, (uint32_t) hq[0].z, (uint32_t) hq[0].w));
+    const q4k_hdr H1 = decode_hdr(make_uint4((uint32_t) hq[1].x, (uint32_t) hq[1].y, (uint32_t) hq[1].z, (uint32_t) hq[1].w));
+    int4  aq[NT][4];
+    int   amh[NT], aml[NT];
+    float adx[NT][2];
+#pragma unroll
+    for (int n = 0; n < NT; n++) {
+        const int4 * ap = reinterpret_cast<const int4 *>(a_qs[n] + (size_t) s * 256);
+#pragma unroll
+        for (int c = 0; c < 4; c++) aq[n][c] = __ldg(ap + c);
+        const int * bp = reinterpret_cast<const int *>(a_b8[n] + (size_t) s * 16);
+        amh[n] = __ldg(bp);
+        aml[n] = __ldg(bp + 2);
+#pragma unroll
+        for (int e = 0; e < 2; e++) adx[n][e] = __ldg(a_dx[n][e] + s);
+    }
+    int sumi[NT][4], sumh[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; n++)
+#pragma unroll
+        for (int i = 0; i < 4; i++) { sumi[n][i] = 0; sumh[n][i] = 0; }
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const uint32_t wx = (uint32_t) wq[c].x, wy = (uint32_t) wq[c].y, wz = (uint32_t) wq[c].z, ww = (uint32_t) wq[c].w;
+        const int j0 = 2 * c, j1 = 2 * c + 1;
+        const int sc0_lo = (int) __byte_perm(j0 < 4 ? H0.sc_lo : H0.sc_hi, 0, 0x4440 + (j0 & 3));
+        const int sc1_lo = (int) __byte_perm(j0 < 4 ? H1.sc_lo : H1.sc_hi, 0, 0x4440 + (j0 & 3));
+        const int sc0_hi = (int) __byte_perm(j1 < 4 ? H0.sc_lo : H0.sc_hi, 0, 0x4440 + (j1 & 3));
+        const int sc1_hi = (int) __byte_perm(j1 < 4 ? H1.sc_lo : H1.sc_hi, 0, 0x4440 + (j1 & 3));
+#pragma unroll
+        for (int n = 0; n < NT; n++) {
+            int c_lo[4] = { 0, 0, 0, 0 }, c_hi[4] = { 0, 0, 0, 0 };
+            mma_u8s8(c_lo, (int) (wx & 0x0F0F0F0Fu), (int) (wz & 0x0F0F0F0Fu), (int) (wy & 0x0F0F0F0Fu), (int) (ww & 0x0F0F0F0Fu),
+                     aq[n][c].x, aq[n][c].y);
+            mma_u8s8(c_hi, (int) (wx & 0xF0F0F0F0u), (int) (wz & 0xF0F0F0F0u), (int) (wy & 0xF0F0F0F0u), (int) (ww & 0xF0F0F0F0u),
+                     aq[n][c].z, aq[n][c].w);
+            sumi[n][0] += sc0_lo * c_lo[0]; sumh[n][0] += sc0_hi * c_hi[0];
+            sumi[n][1] += sc0_lo * c_lo[1]; sumh[n][1] += sc0_hi * c_hi[1];
+            sumi[n][2] += sc1_lo * c_lo[2]; sumh[n][2] += sc1_hi * c_hi[2];
+            sumi[n][3] += sc1_lo * c_lo[3]; sumh[n][3] += sc1_hi * c_hi[3];
+        }
+    }
+    const int am0 = t == 0 ? (int) H0.m_lo : t == 1 ? (int) H0.m_hi : 0;
+    const int am1 = t == 0 ? (int) H1.m_lo : t == 1 ? (int) H1.m_hi : 0;
+#pragma unroll
+    for (int n = 0; n < NT; n++) {
+        int c_mh[4] = { 0, 0, 0, 0 }, c_ml[4] = { 0, 0, 0, 0 };
+        const int bmh = t < 2 ? amh[n] : 0, bml = t < 2 ? aml[n] : 0;
+        mma_s8(c_mh, am0, am1, 0, 0, bmh, 0);
+        mma_s8(c_ml, am0, am1, 0, 0, bml, 0);
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            const float dx = adx[n][e];
+            acc[n][e]     = fmaf(__fmul_rn(dx, H0.d), (float) (sumi[n][e] + (sumh[n][e] >> 4)), acc[n][e]);
+            acc[n][e]     = fmaf(__fmul_rn(-dx, H0.dmin), (float) (64 * c_mh[e] + c_ml[e]), acc[n][e]);
+            acc[n][2 + e] = fmaf(__fmul_rn(dx, H1.d), (float) (sumi[n][2 + e] + (sumh[n][2 + e] >> 4)), acc[n][2 + e]);
+            acc[n][2 + e] = fmaf(__fmul_rn(-dx, H1.dmin), (float) (64 * c_mh[2 + e] + c_ml[2 + e]), acc[n][2 + e]);
+        }
+    }
+}
+
 // ---- direct variant: one CTA per (row tile, k split), the four warps interleave the super-blocks, weights prefetched one
 // super-block ahead into registers with streaming 128-bit loads (no shared-memory staging); same arithmetic core -------------
 #ifndef MM_L2_AHEAD
@@ -411,65 +476,7 @@ gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K
             hn[0] = ld_stream_v4(hbase + (size_t) sn * MM_TILE_BYTES);
             hn[1] = ld_stream_v4(hbase + (size_t) sn * MM_TILE_BYTES + 128);
         }
-        const q4k_hdr H0 = decode_hdr(make_uint4((uint32_t) hq[0].x, (uint32_t) hq[0].y, (uint32_t) hq[0].z, (uint32_t) hq[0].w));
-        const q4k_hdr H1 = decode_hdr(make_uint4((uint32_t) hq[1].x, (uint32_t) hq[1].y, (uint32_t) hq[1].z, (uint32_t) hq[1].w));
-        int4  aq[NT][4];
-        int   amh[NT], aml[NT];
-        float adx[NT][2];
-#pragma unroll
-        for (int n = 0; n < NT; n++) {
-            const int4 * ap = reinterpret_cast<const int4 *>(a_qs[n] + (size_t) s * 256);
-#pragma unroll
-            for (int c = 0; c < 4; c++) aq[n][c] = __ldg(ap + c);
-            const int * bp = reinterpret_cast<const int *>(a_b8[n] + (size_t) s * 16);
-            amh[n] = __ldg(bp);
-            aml[n] = __ldg(bp + 2);
-#pragma unroll
-            for (int e = 0; e < 2; e++) adx[n][e] = __ldg(a_dx[n][e] + s);
-        }
-        int sumi[NT][4], sumh[NT][4];
-#pragma unroll
-        for (int n = 0; n < NT; n++)
-#pragma unroll
-            for (int i = 0; i < 4; i++) { sumi[n][i] = 0; sumh[n][i] = 0; }
-#pragma unroll
-        for (int c = 0; c < 4; c++) {
-            const uint32_t wx = (uint32_t) wq[c].x, wy = (uint32_t) wq[c].y, wz = (uint32_t) wq[c].z, ww = (uint32_t) wq[c].w;
-            const int j0 = 2 * c, j1 = 2 * c + 1;
-            const int sc0_lo = (int) __byte_perm(j0 < 4 ? H0.sc_lo : H0.sc_hi, 0, 0x4440 + (j0 & 3));
-            const int sc1_lo = (int) __byte_perm(j0 < 4 ? H1.sc_lo : H1.sc_hi, 0, 0x4440 + (j0 & 3));
-            const int sc0_hi = (int) __byte_perm(j1 < 4 ? H0.sc_lo : H0.sc_hi, 0, 0x4440 + (j1 & 3));
-            const int sc1_hi = (int) __byte_perm(j1 < 4 ? H1.sc_lo : H1.sc_hi, 0, 0x4440 + (j1 & 3));
-#pragma unroll
-            for (int n = 0; n < NT; n++) {
-                int c_lo[4] = { 0, 0, 0, 0 }, c_hi[4] = { 0, 0, 0, 0 };
-                mma_u8s8(c_lo, (int) (wx & 0x0F0F0F0Fu), (int) (wz & 0x0F0F0F0Fu), (int) (wy & 0x0F0F0F0Fu), (int) (ww & 0x0F0F0F0Fu),
-                         aq[n][c].x, aq[n][c].y);
-                mma_u8s8(c_hi, (int) (wx & 0xF0F0F0F0u), (int) (wz & 0xF0F0F0F0u), (int) (wy & 0xF0F0F0F0u), (int) (ww & 0xF0F0F0F0u),
-                         aq[n][c].z, aq[n][c].w);
-                sumi[n][0] += sc0_lo * c_lo[0]; sumh[n][0] += sc0_hi * c_hi[0];
-                sumi[n][1] += sc0_lo * c_lo[1]; sumh[n][1] += sc0_hi * c_hi[1];
-                sumi[n][2] += sc1_lo * c_lo[2]; sumh[n][2] += sc1_hi * c_hi[2];
-                sumi[n][3] += sc1_lo * c_lo[3]; sumh[n][3] += sc1_hi * c_hi[3];
-            }
-        }
-        const int am0 = t == 0 ? (int) H0.m_lo : t == 1 ? (int) H0.m_hi : 0;
-        const int am1 = t == 0 ? (int) H1.m_lo : t == 1 ? (int) H1.m_hi : 0;
-#pragma unroll
-        for (int n = 0; n < NT; n++) {
-            int c_mh[4] = { 0, 0, 0, 0 }, c_ml[4] = { 0, 0, 0, 0 };
-            const int bmh = t < 2 ? amh[n] : 0, bml = t < 2 ? aml[n] : 0;
-            mma_s8(c_mh, am0, am1, 0, 0, bmh, 0);
-            mma_s8(c_ml, am0, am1, 0, 0, bml, 0);
-#pragma unroll
-            for (int e = 0; e < 2; e++) {
-                const float dx = adx[n][e];
-                acc[n][e]     = fmaf(__fmul_rn(dx, H0.d), (float) (sumi[n][e] + (sumh[n][e] >> 4)), acc[n][e]);
-                acc[n][e]     = fmaf(__fmul_rn(-dx, H0.dmin), (float) (64 * c_mh[e] + c_ml[e]), acc[n][e]);
-                acc[n][2 + e] = fmaf(__fmul_rn(dx, H1.d), (float) (sumi[n][2 + e] + (sumh[n][2 + e] >> 4)), acc[n][2 + e]);
-                acc[n][2 + e] = fmaf(__fmul_rn(-dx, H1.dmin), (float) (64 * c_mh[2 + e] + c_ml[2 + e]), acc[n][2 + e]);
-            }
-        }
+        q4k_record<NT>(wq, hq, s, t, a_qs, a_b8, a_dx, acc);
         if (sn < sb1) {
 #pragma unroll
             for (int c = 0; c < 4; c++) wq[c] = wn[c];
@@ -504,6 +511,120 @@ gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K
     __syncthreads();
     if (!s_last) return;
     for (int i = threadIdx.x; i < NT * 8 * 16; i += MM_THREADS) {
+        const int tok = i / 16, r = i % 16, row = T * 16 + r;
+        if (tok < b && row < N) {
+            float v = 0.f;
+            for (int sp = 0; sp < nsplit; sp++) v += __ldcg(partial + ((size_t) sp * b + tok) * N + row);
+            y[(size_t) tok * N + row] = v;
+        }
+    }
+    if (threadIdx.x == 0) counters[T] = 0;          // self-cleaning: ready for the next launch
+}
+
+// ---- ring variant (default): same decomposition and arithmetic as the direct kernel, but every warp streams its records through
+// a private ring in shared memory filled by cp.async (16 bytes per lane and copy, L2 only): RG_STAGES - 1 records in flight per warp
+// instead of one register-prefetched record.  With one wave of CTAs (attn_out, down: 512 row tiles for 592 slots) a warp's time is
+// a chain of record latencies, and that chain is what the deeper prefetch shortens.  WARPS = warps per CTA (interleaving the
+// super-blocks of the tile): 8 for single-wave shapes, 4 otherwise.
+#define RG_STAGES 4
+template <int NT, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, NT == 1 ? (WARPS == 4 ? 5 : 2) : (WARPS == 4 ? 3 : 1))
+gemv_q4k_ring_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, const int8_t * __restrict__ aqs,
+                     const float * __restrict__ ad, const int8_t * __restrict__ abs8, int b, float * __restrict__ y,
+                     float * __restrict__ partial, unsigned int * __restrict__ counters, const int * __restrict__ cancel) {
+    if (PIB_CANCELLED(cancel)) {
+        pib_pdl_wait();
+        if (gridDim.y > 1 && threadIdx.x == 0 && atomicAdd(&counters[blockIdx.x], 1u) == gridDim.y - 1) counters[blockIdx.x] = 0;
+        return;
+    }
+    extern __shared__ __align__(16) uint8_t rg_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    const int T = blockIdx.x;
+    const int nsplit = gridDim.y, split = blockIdx.y;
+    const int sb_per = (nsb + nsplit - 1) / nsplit;
+    const int sb0 = split * sb_per, sb1 = min(nsb, sb0 + sb_per);
+    const uint8_t * tbase = tiles + (size_t) T * nsb * MM_TILE_BYTES + lane * 16;
+    uint8_t *       ring  = rg_smem + warp * (RG_STAGES * MM_TILE_BYTES);
+    const uint32_t  ring_a = smem_u32(ring) + lane * 16;
+
+    // prefetch cursor: this warp's records sb0 + warp, + WARPS, ...
+    int ps = sb0 + warp;
+    auto issue = [&](int stage) {
+        if (ps < sb1) {
+            const uint8_t * src = tbase + (size_t) ps * MM_TILE_BYTES;
+            const uint32_t  dst = ring_a + stage * MM_TILE_BYTES;
+#pragma unroll
+            for (int c = 0; c < 4; c++) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + c * 512), "l"(src + c * 512) : "memory");
+            if (lane < 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 2048), "l"(src + 2048) : "memory");
+            ps += WARPS;
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    // the weights are immutable: their copies start before the wait on the kernel that produces the activations
+#pragma unroll
+    for (int i = 0; i < RG_STAGES - 1; i++) issue(i);
+
+    float acc[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; n++) { acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f; }
+    const int8_t * a_qs[NT];
+    const int8_t * a_b8[NT];
+    const float *  a_dx[NT][2];
+#pragma unroll
+    for (int n = 0; n < NT; n++) {
+        const int tok = min(n * 8 + g, b - 1);
+        a_qs[n] = aqs + (size_t) tok * K + t * 64;
+        a_b8[n] = abs8 + (size_t) tok * nsb * 16 + (t & 1) * 4;
+#pragma unroll
+        for (int e = 0; e < 2; e++) a_dx[n][e] = ad + (size_t) min(n * 8 + 2 * t + e, b - 1) * nsb;
+    }
+    pib_pdl_wait();
+    pib_pdl_trigger();
+    int stage = 0;
+    for (int s = sb0 + warp; s < sb1; s += WARPS) {
+        __syncwarp();                                           // every lane has read the stage about to be refilled
+        issue((stage + RG_STAGES - 1) % RG_STAGES);
+        asm volatile("cp.async.wait_group %0;" ::"n"(RG_STAGES - 1) : "memory");
+        __syncwarp();
+        const uint8_t * rs = ring + stage * MM_TILE_BYTES;
+        int4 wq[4], hq[2];
+#pragma unroll
+        for (int c = 0; c < 4; c++) wq[c] = *reinterpret_cast<const int4 *>(rs + c * 512 + lane * 16);
+        hq[0] = *reinterpret_cast<const int4 *>(rs + 2048 + g * 16);
+        hq[1] = *reinterpret_cast<const int4 *>(rs + 2048 + (g + 8) * 16);
+        q4k_record<NT>(wq, hq, s, t, a_qs, a_b8, a_dx, acc);
+        stage = stage + 1 == RG_STAGES ? 0 : stage + 1;
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();                                            // the rings are done with: their memory becomes the reduction buffer
+
+    // cross-warp reduction in warp order, then (k split) cross-CTA reduction in split order by the last CTA to arrive
+    float (*red)[NT * 8][16] = reinterpret_cast<float (*)[NT * 8][16]>(rg_smem);
+    __shared__ bool s_last;
+#pragma unroll
+    for (int n = 0; n < NT; n++)
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            red[warp][n * 8 + 2 * t + e][g]     = acc[n][e];
+            red[warp][n * 8 + 2 * t + e][g + 8] = acc[n][2 + e];
+        }
+    __syncthreads();
+    for (int i = threadIdx.x; i < NT * 8 * 16; i += WARPS * 32) {
+        const int tok = i / 16, r = i % 16, row = T * 16 + r;
+        if (tok < b && row < N) {
+            float v = red[0][tok][r];
+#pragma unroll
+            for (int w2 = 1; w2 < WARPS; w2++) v += red[w2][tok][r];
+            if (nsplit == 1) y[(size_t) tok * N + row] = v;
+            else partial[((size_t) split * b + tok) * N + row] = v;
+        }
+    }
+    if (nsplit == 1) return;
+    __syncthreads();
+    if (threadIdx.x == 0) { __threadfence(); s_last = atomicAdd(&counters[T], 1u) == (unsigned) nsplit - 1; }
+    __syncthreads();
+    if (!s_last) return;
+    for (int i = threadIdx.x; i < NT * 8 * 16; i += WARPS * 32) {
         const int tok = i / 16, r = i % 16, row = T * 16 + r;
         if (tok < b && row < N) {
             float v = 0.f;
@@ -622,7 +743,41 @@ int pib_gemv_mma_launch(const pib_weight * w, const void * act_dev, int b, float
     return PIB_OK;
 }
 
-// variant 2: direct (register-prefetched) kernel
+template <int NT, int WARPS>
+static int ring_launch(const pib_weight * w, const int8_t * aqs, const float * ad, const int8_t * bs, int b, float * y_dev, int split, float * partial,
+                       unsigned int * counters, const int * cancel, cudaStream_t st) {
+    const size_t smem = (size_t) WARPS * RG_STAGES * MM_TILE_BYTES;
+    static bool configured = false;
+    if (!configured) { PIB_CHECK(cudaFuncSetAttribute(gemv_q4k_ring_kernel<NT, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem)); configured = true; }
+    const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    pib_launch(gemv_q4k_ring_kernel<NT, WARPS>, dim3(n_tiles, split), dim3(WARPS * 32), smem, st, w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev,
+               partial, counters, cancel);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+
+// variant 0 / 2: the ring kernel (cp.async-staged); PIB_Q4K_FAST=direct selects the register-prefetched direct kernel instead
+int pib_gemv_ring(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
+    if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: variant 2 needs Q4_K weights with tiles"); return PIB_ERR_UNSUPP; }
+    const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    // one wave of CTAs or less (4 CTAs of 4 warps per SM): eight warps per tile halve every warp's chain of records
+    static const int wide_on = getenv("PIB_RING_WIDE") ? atoi(getenv("PIB_RING_WIDE")) : 1;
+    const bool wide = wide_on && n_tiles <= 2 * pib_num_sms() * 2 && nsb >= 16;          // <= 2 CTAs of 8 warps per SM
+    const int  split = fit_split(wide ? 1 : choose_split_direct(n_tiles, nsb), b, w->N, n_tiles);
+    mm_scratch * s = nullptr;
+    if (split > 1 && ensure_scratch((size_t) split * b * w->N, (size_t) n_tiles, st, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
+    const pib_act_layout L   = pib_act_layout_of(w->type, w->K, b);
+    const uint8_t *      act = (const uint8_t *) act_dev;
+    const int8_t * aqs = (const int8_t *) (act + L.qsp_off);
+    const float *  ad  = (const float *) (act + L.d_off);
+    const int8_t * bs  = (const int8_t *) (act + L.bs8_off);
+    float * pp = s ? s->partial : nullptr;
+    unsigned int * cc = s ? s->counters : nullptr;
+    if (wide) return b <= 8 ? ring_launch<1, 8>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st) : ring_launch<2, 8>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st);
+    return b <= 8 ? ring_launch<1, 4>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st) : ring_launch<2, 4>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st);
+}
+
+// variant 5: direct (register-prefetched) kernel
 int pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
     if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: variant 2 needs Q4_K weights with tiles"); return PIB_ERR_UNSUPP; }
     const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);

@@ -112,12 +112,13 @@ extern "C" int pib_stream_sync(pib_stream s) {
 // ---- K1 dispatch ----------------------------------------------------------------------------------------------------
 int pib_gemv_dp4a(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
-int pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 bool pib_gemv_mma_supported(const pib_weight * w, int b);
 bool pib_gemv_blk32_supported(const pib_weight * w, int b);
 int  pib_gemv_q5k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_q6k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_blk32(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
+int  pib_gemv_ring(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
+int  pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_q4k_lane(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_exact_ref(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 
@@ -133,7 +134,8 @@ int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float *
     const bool tc = pib_gemv_mma_supported(w, b);
     if (variant == 6 && tc) return pib_gemv_q4k_lane(w, act_dev, b, y_dev, cancel, st);
     if (variant == 3 && tc) return pib_gemv_mma(w, act_dev, b, y_dev, cancel, st);
-    if ((variant == 2 || variant == 0) && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);
+    if ((variant == 2 || variant == 0) && tc) return pib_gemv_ring(w, act_dev, b, y_dev, cancel, st);
+    if (variant == 5 && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);
     if ((variant == 2 || variant == 0) && pib_gemv_blk32_supported(w, b)) return pib_gemv_blk32(w, act_dev, b, y_dev, cancel, st);
     return pib_gemv_dp4a(w, act_dev, b, y_dev, cancel, st);
 }
