@@ -65,17 +65,56 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
                                                                const float * __restrict__ addend, float * sum_out,
                                                                const int * __restrict__ cancel, int64_t xstride,
                                                                const float * __restrict__ bias, const float * __restrict__ addend2) {
-    pib_pdl_wait();
-    pib_pdl_trigger();
-    if (PIB_CANCELLED(cancel)) return;
     const int     row  = blockIdx.x;
     const float * xr   = x + (size_t) row * xstride;
     const float * x2r  = x2 ? (x2_per_row ? x2 + (size_t) row * xstride : x2) : nullptr;
     const int     lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int     nwarp = AQ_THREADS / 32;
+    // RMSNorm into Q8_K with one super-block per warp (every llama shape here: K / 256 == 8 * gridDim.y): the lane's eight norm
+    // weights are immutable, so they are fetched before the wait on the producer of x, and the lane's eight x values of pass 2
+    // are kept from pass 1 instead of being read again
+    const bool own = Q8K && PRO == PRO_RMSNORM && K / PIB_QK_K == (int64_t) nwarp * gridDim.y && !x2_per_row;
+    float wk[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }, keep[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    if (own) {
+        const float4 * w4 = reinterpret_cast<const float4 *>(x2r + ((int64_t) blockIdx.y * nwarp + warp) * PIB_QK_K + lane * 8);
+        const float4 wa = w4[0], wb = w4[1];
+        wk[0] = wa.x; wk[1] = wa.y; wk[2] = wa.z; wk[3] = wa.w; wk[4] = wb.x; wk[5] = wb.y; wk[6] = wb.z; wk[7] = wb.w;
+    }
+    pib_pdl_wait();
+    pib_pdl_trigger();
+    if (PIB_CANCELLED(cancel)) return;
 
     float scale = 1.0f, mean = 0.0f;
-    if (PRO == PRO_RMSNORM || PRO == PRO_LAYERNORM) {
+    if (own) {
+        __shared__ double red1[AQ_THREADS / 32];
+        double s = 0.0;
+        const float4 * __restrict__ x4 = reinterpret_cast<const float4 *>(xr);
+        const float4 * __restrict__ a4 = addend ? reinterpret_cast<const float4 *>(addend + (size_t) row * K) : nullptr;
+        float4 *                    o4 = sum_out ? reinterpret_cast<float4 *>(sum_out + (size_t) row * K) : nullptr;
+        // warp w reads super-blocks w, w + 8, ... (a lane: the same eight elements of each); the one of index blockIdx.y is its own
+#pragma unroll 4
+        for (int j = 0; j < (int) gridDim.y; j++) {
+            const int i = (j * nwarp + warp) * (PIB_QK_K / 4) + lane * 2;
+            float4 v0 = x4[i], v1 = x4[i + 1];
+            if (a4) {
+                const float4 a0 = a4[i], a1 = a4[i + 1];
+                v0.x = __fadd_rn(v0.x, a0.x); v0.y = __fadd_rn(v0.y, a0.y); v0.z = __fadd_rn(v0.z, a0.z); v0.w = __fadd_rn(v0.w, a0.w);
+                v1.x = __fadd_rn(v1.x, a1.x); v1.y = __fadd_rn(v1.y, a1.y); v1.z = __fadd_rn(v1.z, a1.z); v1.w = __fadd_rn(v1.w, a1.w);
+                if (j == (int) blockIdx.y) { o4[i] = v0; o4[i + 1] = v1; }        // every CTA of the row writes its own quarter of the sums
+            }
+            if (j == (int) blockIdx.y) { keep[0] = v0.x; keep[1] = v0.y; keep[2] = v0.z; keep[3] = v0.w; keep[4] = v1.x; keep[5] = v1.y; keep[6] = v1.z; keep[7] = v1.w; }
+            s += (double) __fmul_rn(v0.x, v0.x); s += (double) __fmul_rn(v0.y, v0.y); s += (double) __fmul_rn(v0.z, v0.z); s += (double) __fmul_rn(v0.w, v0.w);
+            s += (double) __fmul_rn(v1.x, v1.x); s += (double) __fmul_rn(v1.y, v1.y); s += (double) __fmul_rn(v1.z, v1.z); s += (double) __fmul_rn(v1.w, v1.w);
+        }
+        s = warp_sum_d(s);
+        if (lane == 0) red1[warp] = s;
+        __syncthreads();
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < nwarp; w++) t += red1[w];                           // every thread forms the same total
+        const float ms = (float) (t / (double) K);
+        scale          = 1.0f / sqrtf(ms + eps);
+    } else if (PRO == PRO_RMSNORM || PRO == PRO_LAYERNORM) {
         __shared__ double red[AQ_THREADS / 32];
         __shared__ float  s_scale;
         double            s = 0.0;
@@ -193,7 +232,12 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
         for (int64_t sb = (int64_t) blockIdx.y * nwarp + warp; sb < nsb; sb += (int64_t) gridDim.y * nwarp) {
             const int64_t i0 = sb * PIB_QK_K + lane * 8;
             float v[8];
-            aq_value8<PRO>(xr, x2r, scale, lut, i0, v, mean, biasr);
+            if (own) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) v[j] = __fmul_rn(__fmul_rn(keep[j], scale), wk[j]);
+            } else {
+                aq_value8<PRO>(xr, x2r, scale, lut, i0, v, mean, biasr);
+            }
             // first element (in index order) with the largest |x|: strict '>' scan, ties keep the lower index
             float amax = 0.0f, mx = 0.0f;
             int   idx  = 1 << 30;

@@ -35,7 +35,7 @@ void rope_table_build(std::vector<float2> & tab, int n_pos, int n_dims, int mode
 bool pib_attention_supported(int hd, int n_head, int n_head_kv, int n_ctx);
 int  pib_attention(const float * qkv, const float * vsep, const uint8_t * desc, const float2 * rope, int rope_n_pos, int mode, __half * kc, __half * vc,
                    const uint8_t * mask, const int32_t * scalars, int n_tokens, int n_head, int n_head_kv, int hd, int n_ctx, float * out,
-                   const int * cancel, cudaStream_t st);
+                   const int * cancel, cudaStream_t st, bool cache_final);
 int  pib_sample_topk(float * logits_dev, int n_rows, int n_vocab, const int32_t * bias_ids_dev, const float * bias_val_dev, int n_bias,
                      void * out_dev, const uint8_t * desc, const int * cancel, cudaStream_t st);
 int  pib_gemm_q4k_tc(const pib_weight * w, const void * act_dev, int b, float * y_dev, void * xhat_dev, cudaStream_t st);
@@ -551,7 +551,7 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
         const bool pr__ = c->prof_now && (il_) == c->prof_layer && c->prof.size() < 8192;                                             \
         pib_context::ProfRec r__ = { (kind), ntok, nullptr, nullptr };                                                 \
         if (pr__) { cudaEventCreate(&r__.e0); cudaEventCreate(&r__.e1); cudaEventRecord(r__.e0, st); }                 \
-        RC(pib_gemv_internal((w), c->act, ntok, (out), var, cancel, st));                                              \
+        if (!(skip_mask >> (kind) & 1)) RC(pib_gemv_internal((w), c->act, ntok, (out), var, cancel, st));              \
         if (ntok > 8 && var != 2) c->n_kernels++;                                                                      \
         if (pr__) { cudaEventRecord(r__.e1, st); c->prof.push_back(r__); }                                             \
     } while (0)
@@ -561,9 +561,11 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
         const bool pr__ = c->prof_now && (il_) == c->prof_layer && c->prof.size() < 8192;                                             \
         pib_context::ProfRec r__ = { (kind), ntok, nullptr, nullptr };                                                 \
         if (pr__) { cudaEventCreate(&r__.e0); cudaEventCreate(&r__.e1); cudaEventRecord(r__.e0, st); }                 \
-        RC(call);                                                                                                      \
+        if (!(skip_mask >> (kind) & 1)) RC(call);                                                                      \
         if (pr__) { cudaEventRecord(r__.e1, st); c->prof.push_back(r__); }                                             \
     } while (0)
+    // timing experiments only (tools/pass_breakdown.py): leave out every launch of the kinds in the mask; the results are garbage
+    static const unsigned skip_mask = getenv("PIB_DEBUG_SKIP_KINDS") ? (unsigned) strtoul(getenv("PIB_DEBUG_SKIP_KINDS"), nullptr, 0) : 0u;
     if (part & 1) {
         if (c->hop_peer && !c->stage.first()) RC(pib_hop_recv_launch(c, ntok, st));
         RC(kv_device_mask(&c->kvd, tpos, tbits, ntok, c->mask, st));
@@ -591,7 +593,7 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
             if (L.attn_norm2) TL(9, il, pib_add_layernorm_quantize_act(wt, cur, nullptr, nullptr, nullptr, L.attn_norm, L.attn_norm_b, m->norm_eps, ntok, E, c->act, cancel, st));
             GEMV(2, il, L.wgu, c->gu);
             TL(7, il, pib_attention(c->qkv, nullptr, desc, c->rope, c->rope_n_pos, 2, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, ntok, m->n_head,
-                                    m->n_head_kv, hd, (int) c->n_ctx, other, cancel, st));
+                                    m->n_head_kv, hd, (int) c->n_ctx, other, cancel, st, true));
             TL(8, il, pib_quantize_act_c(wt, other, ntok, E, c->act, cancel, st));
             GEMV(1, il, L.wo, c->proj);
             TL(10, il, pib_gelu_quantize_act(wt, c->gu, ntok, FF, c->act, cancel, st));
@@ -632,7 +634,7 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
         dump_dev(c, "k", il, c->qkv + E, ntok, GQA, E + (L.wv ? 1 : 2) * GQA);
         if (!L.wv) dump_dev(c, "v", il, c->qkv + E + GQA, ntok, GQA, E + 2 * GQA);
         TL(7, il, pib_attention(c->qkv, L.wv ? c->vsep : nullptr, desc, c->rope, c->rope_n_pos, 0, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, ntok,
-                                m->n_head, m->n_head_kv, hd, (int) c->n_ctx, c->att, cancel, st));
+                                m->n_head, m->n_head_kv, hd, (int) c->n_ctx, c->att, cancel, st, true));
         dump_dev(c, "att", il, c->att, ntok, E, E);
         TL(8, il, pib_quantize_act_c(wt, c->att, ntok, E, c->act, cancel, st));
         GEMV(1, il, L.wo, c->proj);
@@ -791,7 +793,7 @@ static int run_prompt_pass(pib_context * c, pib_run & run, int ch0, int nch, int
         for (int k = 0; k < nch; k++) {          // chunk k + 1 reads chunk k's cells from the cache: stream order
             const size_t off = (size_t) k * PIB_CHUNK;
             RC(pib_attention(B.qkv + off * (E + 2 * GQA), nullptr, desc_of(k), c->rope, c->rope_n_pos, 0, c->kcache + lo, c->vcache + lo, B.mask + off * c->n_ctx,
-                             c->kvd.scalars, nt_of(k), m->n_head, m->n_head_kv, hd, (int) c->n_ctx, B.att + off * E, cancel, st));
+                             c->kvd.scalars, nt_of(k), m->n_head, m->n_head_kv, hd, (int) c->n_ctx, B.att + off * E, cancel, st, k == 0));
         }
         RC(pib_quantize_act_c(wt, B.att, ntok, E, B.act, cancel, st));
         RC(pib_gemm_q4k_tc(L.wo, B.act, ntok, B.proj, B.xhat, st));

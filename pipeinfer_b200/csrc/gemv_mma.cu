@@ -763,7 +763,8 @@ int pib_gemv_ring(const pib_weight * w, const void * act_dev, int b, float * y_d
     // one wave of CTAs or less (4 CTAs of 4 warps per SM): eight warps per tile halve every warp's chain of records
     static const int wide_on = getenv("PIB_RING_WIDE") ? atoi(getenv("PIB_RING_WIDE")) : 1;
     const bool wide = wide_on && n_tiles <= 2 * pib_num_sms() * 2 && nsb >= 16;          // <= 2 CTAs of 8 warps per SM
-    const int  split = fit_split(wide ? 1 : choose_split_direct(n_tiles, nsb), b, w->N, n_tiles);
+    static const int split_env = getenv("PIB_RING_SPLIT") ? atoi(getenv("PIB_RING_SPLIT")) : 0;
+    const int  split = fit_split(split_env > 0 ? split_env : wide ? 1 : choose_split_direct(n_tiles, nsb), b, w->N, n_tiles);
     mm_scratch * s = nullptr;
     if (split > 1 && ensure_scratch((size_t) split * b * w->N, (size_t) n_tiles, st, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
     const pib_act_layout L   = pib_act_layout_of(w->type, w->K, b);
