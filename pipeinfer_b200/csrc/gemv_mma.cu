@@ -527,7 +527,7 @@ gemv_q4k_direct_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K
 // a chain of record latencies, and that chain is what the deeper prefetch shortens.  WARPS = warps per CTA (interleaving the
 // super-blocks of the tile): 8 for single-wave shapes, 4 otherwise.
 #define RG_STAGES 4
-template <int NT, int WARPS>
+template <int NT, int WARPS, int STAGES>
 __global__ void __launch_bounds__(WARPS * 32, NT == 1 ? (WARPS == 4 ? 5 : 2) : (WARPS == 4 ? 3 : 1))
 gemv_q4k_ring_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, const int8_t * __restrict__ aqs,
                      const float * __restrict__ ad, const int8_t * __restrict__ abs8, int b, float * __restrict__ y,
@@ -544,7 +544,7 @@ gemv_q4k_ring_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, 
     const int sb_per = (nsb + nsplit - 1) / nsplit;
     const int sb0 = split * sb_per, sb1 = min(nsb, sb0 + sb_per);
     const uint8_t * tbase = tiles + (size_t) T * nsb * MM_TILE_BYTES + lane * 16;
-    uint8_t *       ring  = rg_smem + warp * (RG_STAGES * MM_TILE_BYTES);
+    uint8_t *       ring  = rg_smem + warp * (STAGES * MM_TILE_BYTES);
     const uint32_t  ring_a = smem_u32(ring) + lane * 16;
 
     // prefetch cursor: this warp's records sb0 + warp, + WARPS, ...
@@ -562,7 +562,7 @@ gemv_q4k_ring_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, 
     };
     // the weights are immutable: their copies start before the wait on the kernel that produces the activations
 #pragma unroll
-    for (int i = 0; i < RG_STAGES - 1; i++) issue(i);
+    for (int i = 0; i < STAGES - 1; i++) issue(i);
 
     float acc[NT][4];
 #pragma unroll
@@ -583,8 +583,8 @@ gemv_q4k_ring_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, 
     int stage = 0;
     for (int s = sb0 + warp; s < sb1; s += WARPS) {
         __syncwarp();                                           // every lane has read the stage about to be refilled
-        issue((stage + RG_STAGES - 1) % RG_STAGES);
-        asm volatile("cp.async.wait_group %0;" ::"n"(RG_STAGES - 1) : "memory");
+        issue((stage + STAGES - 1) % STAGES);
+        asm volatile("cp.async.wait_group %0;" ::"n"(STAGES - 1) : "memory");
         __syncwarp();
         const uint8_t * rs = ring + stage * MM_TILE_BYTES;
         int4 wq[4], hq[2];
@@ -593,7 +593,7 @@ gemv_q4k_ring_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, 
         hq[0] = *reinterpret_cast<const int4 *>(rs + 2048 + g * 16);
         hq[1] = *reinterpret_cast<const int4 *>(rs + 2048 + (g + 8) * 16);
         q4k_record<NT>(wq, hq, s, t, a_qs, a_b8, a_dx, acc);
-        stage = stage + 1 == RG_STAGES ? 0 : stage + 1;
+        stage = stage + 1 == STAGES ? 0 : stage + 1;
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();                                            // the rings are done with: their memory becomes the reduction buffer
@@ -633,6 +633,140 @@ gemv_q4k_ring_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, 
         }
     }
     if (threadIdx.x == 0) counters[T] = 0;          // self-cleaning: ready for the next launch
+}
+
+// ---- balanced variant: the matrix as ONE stream of records ---------------------------------------------------------------------
+// At b <= 4 an SM spends ~100 cycles of issue slots per record, close to what its share of HBM delivers: the SM with the most
+// records sets the kernel's time.  Row tiles are too coarse a unit for that (512 tiles over 148 SMs: 4 on some, 3 on others),
+// so here the n_tiles x nsb records -- contiguous in memory in exactly this order -- are cut into W equal runs, one per warp of a
+// grid that fills the machine once.  A warp streams its run through its ring, and whenever the run leaves a row tile (or ends)
+// it hands the tile's partial sums on: the only piece of that tile -> written to y; otherwise stored as piece k of the tile, and
+// the warp that brings the last piece adds the pieces in run order (fixed order: the result does not depend on timing).
+// No block-wide barrier anywhere: the warps of a CTA share nothing but the launch.
+#define SK_WARPS 4
+__device__ __forceinline__ int sk_owner(long long u, int W, long long U) { return (int) (((u + 1) * W - 1) / U); }   // the warp whose run holds record u
+
+template <int NT>
+__global__ void __launch_bounds__(SK_WARPS * 32, NT == 1 ? 5 : 3)
+gemv_q4k_stream_kernel(const uint8_t * __restrict__ tiles, int nsb, int n_tiles, int N, int K, const int8_t * __restrict__ aqs,
+                       const float * __restrict__ ad, const int8_t * __restrict__ abs8, int b, float * __restrict__ y,
+                       float * __restrict__ partial, unsigned int * __restrict__ counters, int pmax, int W, const int * __restrict__ cancel) {
+    extern __shared__ __align__(16) uint8_t rg_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    const long long U  = (long long) n_tiles * nsb;                        // W <= U runs: none is empty
+    const int       gw = blockIdx.x * SK_WARPS + warp;
+    if (gw >= W) return;
+    const long long u0 = U * gw / W, u1 = U * (gw + 1) / W;
+    if (PIB_CANCELLED(cancel)) {
+        // a cancelled launch still has to leave the tile counters at zero: every piece arrives, the last one resets
+        pib_pdl_wait();
+        if (lane == 0)
+            for (long long u = u0; u < u1;) {
+                const int       T     = (int) (u / nsb);
+                const long long tend  = (long long) (T + 1) * nsb;
+                const int       first = sk_owner((long long) T * nsb, W, U), last = sk_owner(tend - 1, W, U);
+                if (last > first && atomicAdd(&counters[T], 1u) == (unsigned) (last - first)) counters[T] = 0;
+                u = tend;
+            }
+        return;
+    }
+    uint8_t *       ring   = rg_smem + warp * (RG_STAGES * MM_TILE_BYTES);
+    const uint32_t  ring_a = smem_u32(ring) + lane * 16;
+    const uint8_t * wbase  = tiles + lane * 16;
+    long long pu = u0;
+    auto issue = [&](int stage) {
+        if (pu < u1) {
+            const uint8_t * src = wbase + (size_t) pu * MM_TILE_BYTES;
+            const uint32_t  dst = ring_a + stage * MM_TILE_BYTES;
+#pragma unroll
+            for (int c = 0; c < 4; c++) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + c * 512), "l"(src + c * 512) : "memory");
+            if (lane < 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 2048), "l"(src + 2048) : "memory");
+            pu++;
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    // the weights are immutable: their copies start before the wait on the kernel that produces the activations
+#pragma unroll
+    for (int i = 0; i < RG_STAGES - 1; i++) issue(i);
+
+    float acc[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; n++) { acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f; }
+    const int8_t * a_qs[NT];
+    const int8_t * a_b8[NT];
+    const float *  a_dx[NT][2];
+#pragma unroll
+    for (int n = 0; n < NT; n++) {
+        const int tok = min(n * 8 + g, b - 1);
+        a_qs[n] = aqs + (size_t) tok * K + t * 64;
+        a_b8[n] = abs8 + (size_t) tok * nsb * 16 + (t & 1) * 4;
+#pragma unroll
+        for (int e = 0; e < 2; e++) a_dx[n][e] = ad + (size_t) min(n * 8 + 2 * t + e, b - 1) * nsb;
+    }
+    pib_pdl_wait();
+    pib_pdl_trigger();
+    int T = (int) (u0 / nsb), sb = (int) (u0 - (long long) T * nsb), stage = 0;
+    for (long long u = u0; u < u1; u++) {
+        __syncwarp();                                           // every lane has read the stage about to be refilled
+        issue((stage + RG_STAGES - 1) % RG_STAGES);
+        asm volatile("cp.async.wait_group %0;" ::"n"(RG_STAGES - 1) : "memory");
+        __syncwarp();
+        const uint8_t * rs = ring + stage * MM_TILE_BYTES;
+        int4 wq[4], hq[2];
+#pragma unroll
+        for (int c = 0; c < 4; c++) wq[c] = *reinterpret_cast<const int4 *>(rs + c * 512 + lane * 16);
+        hq[0] = *reinterpret_cast<const int4 *>(rs + 2048 + g * 16);
+        hq[1] = *reinterpret_cast<const int4 *>(rs + 2048 + (g + 8) * 16);
+        q4k_record<NT>(wq, hq, sb, t, a_qs, a_b8, a_dx, acc);
+        stage = stage + 1 == RG_STAGES ? 0 : stage + 1;
+        if (++sb < nsb && u + 1 < u1) continue;
+
+        // ---- the run leaves tile T: hand its partial sums on -------------------------------------------------------------------
+        const int first = sk_owner((long long) T * nsb, W, U), last = sk_owner((long long) (T + 1) * nsb - 1, W, U);
+        const int P = last - first + 1, k = gw - first;
+        bool write_y = P == 1;
+        if (P > 1) {
+            float4 * mine = reinterpret_cast<float4 *>(partial + ((size_t) T * pmax + k) * (NT * 128)) + lane;
+#pragma unroll
+            for (int n = 0; n < NT; n++) mine[n * 32] = make_float4(acc[n][0], acc[n][1], acc[n][2], acc[n][3]);
+            // publish: the warp barrier orders every lane's stores before lane 0's release; the last arriver's acquire sees them all
+            __syncwarp();
+            unsigned int old = 0;
+            if (lane == 0) asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(counters + T) : "memory");
+            old = __shfl_sync(0xffffffffu, old, 0);
+            if (old == (unsigned) P - 1) {
+                const float4 * pc = reinterpret_cast<const float4 *>(partial + (size_t) T * pmax * (NT * 128)) + lane;
+#pragma unroll
+                for (int n = 0; n < NT; n++) {
+                    float4 v = __ldcg(pc + n * 32);
+                    for (int q = 1; q < P; q++) {
+                        const float4 o = __ldcg(pc + (size_t) q * (NT * 32) + n * 32);
+                        v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                    }
+                    acc[n][0] = v.x; acc[n][1] = v.y; acc[n][2] = v.z; acc[n][3] = v.w;
+                }
+                if (lane == 0) counters[T] = 0;          // self-cleaning: ready for the next launch
+                write_y = true;
+            }
+        }
+        if (write_y) {
+#pragma unroll
+            for (int n = 0; n < NT; n++)
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+                    const int tok = n * 8 + 2 * t + e, row = T * 16 + g;
+                    if (tok < b) {
+                        if (row < N) y[(size_t) tok * N + row] = acc[n][e];
+                        if (row + 8 < N) y[(size_t) tok * N + row + 8] = acc[n][2 + e];
+                    }
+                }
+        }
+#pragma unroll
+        for (int n = 0; n < NT; n++) { acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f; }
+        T++;
+        sb = 0;
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 // ---- launcher -----------------------------------------------------------------------------------------------------------
@@ -743,23 +877,33 @@ int pib_gemv_mma_launch(const pib_weight * w, const void * act_dev, int b, float
     return PIB_OK;
 }
 
-template <int NT, int WARPS>
+template <int NT, int WARPS, int STAGES>
 static int ring_launch(const pib_weight * w, const int8_t * aqs, const float * ad, const int8_t * bs, int b, float * y_dev, int split, float * partial,
                        unsigned int * counters, const int * cancel, cudaStream_t st) {
-    const size_t smem = (size_t) WARPS * RG_STAGES * MM_TILE_BYTES;
+    const size_t smem = (size_t) WARPS * STAGES * MM_TILE_BYTES;
     static bool configured = false;
-    if (!configured) { PIB_CHECK(cudaFuncSetAttribute(gemv_q4k_ring_kernel<NT, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem)); configured = true; }
+    if (!configured) { PIB_CHECK(cudaFuncSetAttribute(gemv_q4k_ring_kernel<NT, WARPS, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem)); configured = true; }
     const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
-    pib_launch(gemv_q4k_ring_kernel<NT, WARPS>, dim3(n_tiles, split), dim3(WARPS * 32), smem, st, w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev,
+    pib_launch(gemv_q4k_ring_kernel<NT, WARPS, STAGES>, dim3(n_tiles, split), dim3(WARPS * 32), smem, st, w->tiles, nsb, (int) w->N, (int) w->K, aqs, ad, bs, b, y_dev,
                partial, counters, cancel);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }
 
 // variant 0 / 2: the ring kernel (cp.async-staged); PIB_Q4K_FAST=direct selects the register-prefetched direct kernel instead
+int pib_gemv_stream(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
+static bool stream_plan(int n_tiles, int nsb, int b, int * runs, int * pmax);
+
 int pib_gemv_ring(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
     if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: variant 2 needs Q4_K weights with tiles"); return PIB_ERR_UNSUPP; }
     const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    // 9 .. 16 tokens (two column blocks per record): a record costs twice the issue slots, the SM with the most records sets the
+    // time, and the balanced stream kernel wins on every 70B shape (gate|up 100 vs 108 us, down 53 vs 63, attn_out 21 vs 23);
+    // at <= 8 tokens the tile-per-CTA ring is ahead (42 vs 53, 28 vs 30, 10.4 vs 12.7)
+    {
+        int runs = 0, pmax = 0;
+        if (b > 8 && (long long) n_tiles * nsb >= 16384 && stream_plan(n_tiles, nsb, b, &runs, &pmax)) return pib_gemv_stream(w, act_dev, b, y_dev, cancel, st);
+    }
     // one wave of CTAs or less (4 CTAs of 4 warps per SM): eight warps per tile halve every warp's chain of records
     static const int wide_on = getenv("PIB_RING_WIDE") ? atoi(getenv("PIB_RING_WIDE")) : 1;
     const bool wide = wide_on && n_tiles <= 2 * pib_num_sms() * 2 && nsb >= 16;          // <= 2 CTAs of 8 warps per SM
@@ -774,8 +918,49 @@ int pib_gemv_ring(const pib_weight * w, const void * act_dev, int b, float * y_d
     const int8_t * bs  = (const int8_t *) (act + L.bs8_off);
     float * pp = s ? s->partial : nullptr;
     unsigned int * cc = s ? s->counters : nullptr;
-    if (wide) return b <= 8 ? ring_launch<1, 8>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st) : ring_launch<2, 8>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st);
-    return b <= 8 ? ring_launch<1, 4>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st) : ring_launch<2, 4>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st);
+    if (wide) return b <= 8 ? ring_launch<1, 8, 4>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st) : ring_launch<2, 8, 4>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st);
+    return b <= 8 ? ring_launch<1, 4, 4>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st) : ring_launch<2, 4, 4>(w, aqs, ad, bs, b, y_dev, split, pp, cc, cancel, st);
+}
+
+// variant 8 (and the default for shapes whose row tiles do not fill the machine evenly): the balanced stream kernel
+template <int NT>
+static int stream_launch(const pib_weight * w, const int8_t * aqs, const float * ad, const int8_t * bs, int b, float * y_dev, int W, int pmax,
+                         float * partial, unsigned int * counters, const int * cancel, cudaStream_t st) {
+    const size_t smem = (size_t) SK_WARPS * RG_STAGES * MM_TILE_BYTES;
+    static bool configured = false;
+    if (!configured) { PIB_CHECK(cudaFuncSetAttribute(gemv_q4k_stream_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem)); configured = true; }
+    const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    pib_launch(gemv_q4k_stream_kernel<NT>, dim3((W + SK_WARPS - 1) / SK_WARPS), dim3(SK_WARPS * 32), smem, st, w->tiles, nsb, n_tiles, (int) w->N, (int) w->K, aqs,
+               ad, bs, b, y_dev, partial, counters, pmax, W, cancel);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+
+// grid and piece bound of the stream kernel for a shape; false when the scratch cannot hold the pieces
+static bool stream_plan(int n_tiles, int nsb, int b, int * runs, int * pmax) {
+    const int       per_sm = b <= 8 ? 5 : 3;
+    const long long U = (long long) n_tiles * nsb;
+    long long       W = (long long) pib_num_sms() * per_sm * SK_WARPS;
+    if (W > U) W = U;                                                          // tiny matrices: one record per run
+    *runs = (int) W;
+    *pmax = (int) (((long long) nsb * W + U - 1) / U) + 1;                     // pieces a tile can be cut into
+    return (size_t) n_tiles * *pmax * (b <= 8 ? 128 : 256) <= MM_SCRATCH_FLOATS && (size_t) n_tiles <= MM_SCRATCH_COUNTERS;
+}
+
+int pib_gemv_stream(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
+    if (!pib_gemv_mma_supported(w, b)) { pib_set_error("pib_gemv: variant 8 needs Q4_K weights with tiles"); return PIB_ERR_UNSUPP; }
+    const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    int runs = 0, pmax = 0;
+    if (!stream_plan(n_tiles, nsb, b, &runs, &pmax)) { pib_set_error("pib_gemv: variant 8: shape too large for the piece scratch"); return PIB_ERR_UNSUPP; }
+    mm_scratch * s = nullptr;
+    if (ensure_scratch((size_t) n_tiles * pmax * (b <= 8 ? 128 : 256), (size_t) n_tiles, st, &s) != PIB_OK) { pib_set_error("pib_gemv: scratch allocation failed"); return PIB_ERR_NOMEM; }
+    const pib_act_layout L   = pib_act_layout_of(w->type, w->K, b);
+    const uint8_t *      act = (const uint8_t *) act_dev;
+    const int8_t * aqs = (const int8_t *) (act + L.qsp_off);
+    const float *  ad  = (const float *) (act + L.d_off);
+    const int8_t * bs  = (const int8_t *) (act + L.bs8_off);
+    return b <= 8 ? stream_launch<1>(w, aqs, ad, bs, b, y_dev, runs, pmax, s->partial, s->counters, cancel, st)
+                  : stream_launch<2>(w, aqs, ad, bs, b, y_dev, runs, pmax, s->partial, s->counters, cancel, st);
 }
 
 // variant 5: direct (register-prefetched) kernel

@@ -119,6 +119,7 @@ int  pib_gemv_q6k(const pib_weight * w, const void * act_dev, int b, float * y_d
 int  pib_gemv_blk32(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_ring(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_direct(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
+int  pib_gemv_stream(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_q4k_lane(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_exact_ref(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 
@@ -136,6 +137,7 @@ int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float *
     if (variant == 3 && tc) return pib_gemv_mma(w, act_dev, b, y_dev, cancel, st);
     if ((variant == 2 || variant == 0) && tc) return pib_gemv_ring(w, act_dev, b, y_dev, cancel, st);
     if (variant == 5 && tc) return pib_gemv_direct(w, act_dev, b, y_dev, cancel, st);
+    if (variant == 8 && tc) return pib_gemv_stream(w, act_dev, b, y_dev, cancel, st);
     if ((variant == 2 || variant == 0) && pib_gemv_blk32_supported(w, b)) return pib_gemv_blk32(w, act_dev, b, y_dev, cancel, st);
     return pib_gemv_dp4a(w, act_dev, b, y_dev, cancel, st);
 }

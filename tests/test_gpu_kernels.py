@@ -102,15 +102,16 @@ def test_get_rows_bit_exact(lib, kern, name, wt):
 def variants(wt):
     # 1 = dp4a (all types), 2 = the default tensor-core kernel (all types), 3 = TMA-staged persistent kernel (Q4_K only),
     # 4 = the reference's summation order restated literally, one thread per output (all types), 6 = the tensor-core kernel that
-    # keeps the reference's order (Q4_K only)
-    return [1, 2, 3, 4, 6] if wt == op.TYPE_Q4_K else [1, 2, 4]
+    # keeps the reference's order (Q4_K only), 8 = the balanced stream kernel (Q4_K only; what variant 2 picks for row-tile counts that
+    # do not fill the machine evenly)
+    return [1, 2, 3, 4, 6, 8] if wt == op.TYPE_Q4_K else [1, 2, 4]
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 6])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 6, 8])
 @pytest.mark.parametrize("name,wt", TYPES)
 def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
     if variant not in variants(wt):
-        pytest.skip("variants 3 and 6 are Q4_K only")
+        pytest.skip("variants 3, 6 and 8 are Q4_K only")
     w, x, y = kern[name + "_w"], kern[name + "_x"], kern[name + "_y"]
     h = lib.weight_upload(wt, w, x.shape[1])
     got = lib.mul_mat(h, x, w.shape[0], variant)
@@ -118,12 +119,12 @@ def test_mul_mat_vs_golden(lib, kern, name, wt, variant):
     lib.L.pib_weight_free(h)
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 6])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 6, 8])
 @pytest.mark.parametrize("name,wt", TYPES)
 @pytest.mark.parametrize("b", [1, 2, 5, 8, 9, 16])
 def test_mul_mat_vs_oracle_batches(lib, oracle, name, wt, b, variant):
     if variant not in variants(wt):
-        pytest.skip("variants 3 and 6 are Q4_K only")
+        pytest.skip("variants 3, 6 and 8 are Q4_K only")
     rng = np.random.default_rng(100 + b)
     N, K = 96, 2048
     w = rand_blocks(rng, wt, N, K)
