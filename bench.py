@@ -420,16 +420,21 @@ def main():
         kernels[KIND[k]] = {"launches": len(lst), "N": N_.value, "K": K_.value, "mean_batch": round(mean_b, 2), "mean_ms": mean_ms,
                             "algorithmic_bytes": alg, "achieved_gbs": alg / mean_ms / 1e6, "frac": alg / mean_ms / 1e6 / peak}
     dom = kernels.get("gate_up")
-    traffic = None
+    traffic, traffic_src = None, None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("gate_up_dram_bytes_per_launch")
+        tj = json.load(open(tp))
+        traffic, traffic_src = tj.get("gate_up_dram_bytes_per_launch"), tj.get("source")
     roofline = None
     if dom:
         roofline = {"bound": "hbm", "kernel": "dequant-GEMV %s, gate|up projection %dx%d, layer %d of the target" % (TYPE_NAME[wt], dom["N"], dom["K"], prof_layer),
                     "achieved": dom["achieved_gbs"], "peak": peak, "unit": "GB/s", "frac": dom["frac"], "traffic": traffic,
-                    "peak_source": peak_src, "frac_of_8TBs_nominal": dom["achieved_gbs"] / 8000.0, "all_matmuls": kernels,
-                    "other_kernels_of_the_layer": others}
+                    "peak_source": peak_src, "frac_of_8TBs_nominal": dom["achieved_gbs"] / 8000.0, "traffic_source": traffic_src,
+                    "note": "event pairs around single launches of layer %d, one verification decode in eight, launched directly and without programmatic "
+                            "dependent launch (so the short kernels carry their launch ramp: in the pipelined pass they cost less, profiles/r2_pass_breakdown.md); "
+                            "the peak is a COPY bandwidth (half reads, half writes), a read-only weight stream can exceed it: frac > 1 means above the copy "
+                            "figure, see frac_of_8TBs_nominal" % prof_layer,
+                    "all_matmuls": kernels, "other_kernels_of_the_layer": others}
 
     cpu = None
     if not args.no_cpu_baseline and world == 1:

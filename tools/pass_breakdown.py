@@ -23,6 +23,8 @@ def child(a):
     import bench
     from pipeinfer_b200 import llama
     (L, E, H, HKV, FF, V, wt), dshape, label = bench.CONFIGS[a.config]
+    if a.draft:
+        L, E, H, HKV, FF, V, wt = dshape
     lib = llama.api()
     tgt = llama.Context(None, n_ctx=1024, max_seq=64, synthetic=(L, E, H, HKV, FF, V, wt, 1, 1, 1.0))
     prompt = [1] + [3 + (i * 7919) % (V - 3) for i in range(255)]
@@ -51,6 +53,7 @@ ap.add_argument("--batch", default="1,4")
 ap.add_argument("--ctx", type=int, default=64, help="tokens already in the cache")
 ap.add_argument("--passes", type=int, default=15)
 ap.add_argument("--child", action="store_true")
+ap.add_argument("--draft", action="store_true", help="time the config's draft model instead of its target")
 ap.add_argument("--kinds", default="", help="with --alone: only these kinds (comma separated names)")
 ap.add_argument("--alone", action="store_true", help="instead: time a pass that launches ONLY one kind (a chain of n_layer such kernels)")
 a = ap.parse_args()
@@ -63,7 +66,7 @@ if a.child:
 def run(mask):
     env = dict(os.environ, PIB_DEBUG_SKIP_KINDS=str(mask))
     r = subprocess.run([sys.executable, os.path.abspath(__file__), "--child", "--config", a.config, "--batch", ",".join(map(str, a.batch)),
-                        "--ctx", str(a.ctx), "--passes", str(a.passes)], env=env, capture_output=True, text=True)
+                        "--ctx", str(a.ctx), "--passes", str(a.passes)] + (["--draft"] if a.draft else []), env=env, capture_output=True, text=True)
     for line in r.stdout.splitlines():
         if line.startswith("RESULT "):
             return json.loads(line[7:])
