@@ -180,9 +180,11 @@ def run_reference_sample(cfg_name, args, budget="small"):
     resid = max(abs(fixed + per_layer * x - y) / y for x, y in zip(xs, ys))
     sample = ("reference `speculative` (oracle/_ref) under the mini-MPI shim, 2 target ranks + 1 draft rank x %d threads, "
               "same flags, %d tokens predicted; %s-width target at %s layers (%s s per accepted token), full draft; value = "
-              "1 / (%.4f + %d * %.4f) s extrapolated to %d layers, worst relative residual of the fit %.3f"
+              "1 / (%.4f + %d * %.4f) s extrapolated to %d layers, %s"
               % (threads, n_pred, "x".join(map(str, (E, FF))), "/".join(str(d) for d in depths), " / ".join("%.3f" % y for y in ys),
-                 fixed, L, per_layer, L, resid))
+                 fixed, L, per_layer, L,
+                 ("worst relative residual of the least-squares fit %.3f" % resid) if len(depths) > 2
+                 else "two depths in this bounded leg: the line through them, no residual (`--impl reference` fits three depths over 64 tokens)"))
     return dict(value=1.0 / full if full > 0 else None, unit="tokens/s", cores=cores, kind="reference", sample=sample,
                 raw={str(k): v for k, v in res.items()}, itl_est_s=full, fit_residual=resid)
 
