@@ -1,5 +1,5 @@
-// gemv_q4k_lane.cu -- the default Q4_K x Q8_K matmul (K1): tensor-core integer dot products that return THE SAME BITS as the
-// reference's CPU kernel (ggml_vec_dot_q4_K_q8_K, AVX2 branch, ggml-quants.c:5318-5381), not merely the same value up to fp32
+// gemv_q4k_lane.cu -- the Q4_K x Q8_K matmul (K1) of exact mode (PIB_EXACT=1, variant 6): tensor-core integer dot products that
+// return THE SAME BITS as the reference's CPU kernel (ggml_vec_dot_q4_K_q8_K, AVX2 branch, ggml-quants.c:5318-5381), not merely the same value up to fp32
 // reassociation.  That matters because everything downstream of a matmul is rounded discontinuously (int8 activations, fp16
 // K/V/P, fp16 look-up tables): a 1e-7 difference now and then lands on the other side of a rounding step, and a 22-layer model
 // turns a handful of those into ~5e-4 relative on the logits.  With the reference's own order there is nothing to flip.
