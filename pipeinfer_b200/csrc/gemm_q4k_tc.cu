@@ -152,58 +152,77 @@ gemm_q4k_tc_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, const __g
         const int T   = (row0 >> 4) + (r >> 4), rr = r & 15, g = rr & 7, hf = rr >> 3;
         const bool row_ok = row0 + r < N;
         const uint8_t * rec0 = tiles + (size_t) T * nsb * TG_TILE_BYTES;
-        uint2 wn[2];
-        uint4 hn = make_uint4(0, 0, 0, 0);
-        auto fetch = [&](int kt) {                              // the row's bytes 16 th .. 16 th + 15 of chunk kt % 4, and its header
-            const uint8_t * rec = rec0 + (size_t) (kt >> 2) * TG_TILE_BYTES;
+        // A row's bytes of one record (4 chunks x 32 bytes, in 8-byte pieces of the fragment layout) and its header are fetched one
+        // whole record (4 k-steps) ahead into registers, and the lines of the record after that are asked into L2: the weight stream
+        // is a chain of DRAM latencies otherwise (one k-step of arithmetic hides a tenth of one).
+        uint2 cur[4][2], nxt[4][2];
+        uint4 hcur = make_uint4(0, 0, 0, 0), hnxt = make_uint4(0, 0, 0, 0);
+        auto fetch_rec = [&](int ri, uint2 (&w)[4][2], uint4 & h) {
+            const uint8_t * rec = rec0 + (size_t) ri * TG_TILE_BYTES;
             if (row_ok) {
 #pragma unroll
-                for (int t = 0; t < 2; t++) wn[t] = __ldg(reinterpret_cast<const uint2 *>(rec + (kt & 3) * 512 + (g * 4 + 2 * th + t) * 16 + hf * 8));
-                hn = __ldg(reinterpret_cast<const uint4 *>(rec + 2048 + rr * 16));
-            } else { wn[0] = wn[1] = make_uint2(0, 0); }
+                for (int c = 0; c < 4; c++)
+#pragma unroll
+                    for (int t = 0; t < 2; t++) w[c][t] = __ldg(reinterpret_cast<const uint2 *>(rec + c * 512 + (g * 4 + 2 * th + t) * 16 + hf * 8));
+                h = __ldg(reinterpret_cast<const uint4 *>(rec + 2048 + rr * 16));
+            } else {
+#pragma unroll
+                for (int c = 0; c < 4; c++) w[c][0] = w[c][1] = make_uint2(0, 0);
+            }
         };
-        fetch(0);
-        for (int kt = 0; kt < n_ksteps; kt++) {
-            const int s = kt % TG_STAGES, c = kt & 3;
-            const uint2 w[2] = { wn[0], wn[1] };
-            const uint4 hd = hn;
-            if (kt + 1 < n_ksteps) fetch(kt + 1);
-            // scales / mins of sub-blocks 2c (low nibbles) and 2c + 1 (high nibbles): get_scale_min_k4 (ggml-quants.c:1446)
+        const int n_rec = n_ksteps >> 2;
+        // L2 prefetch: the CTA's 8 tiles of a record step are 8 x 18 lines of 128 bytes; thread p < 144 owns line p % 18 of tile p / 18
+        const uint8_t * pf_base = (p < 144 && row0 + (p / 18) * 16 < N) ? tiles + (size_t) ((row0 >> 4) + p / 18) * nsb * TG_TILE_BYTES + (p % 18) * 128 : nullptr;
+        fetch_rec(0, cur, hcur);
+        for (int ri = 0; ri < n_rec; ri++) {
+            if (ri + 1 < n_rec) fetch_rec(ri + 1, nxt, hnxt);
+            if (pf_base && ri + 3 < n_rec) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf_base + (size_t) (ri + 3) * TG_TILE_BYTES));
+            const uint4 hd = hcur;
+            // scales / mins of the record's eight sub-blocks: get_scale_min_k4 (ggml-quants.c:1446)
             const float d = pib_h2f((uint16_t) (hd.x & 0xffff)), dmin = pib_h2f((uint16_t) (hd.x >> 16));
             const uint32_t sc_lo = hd.y & 0x3f3f3f3fu, m_lo = hd.z & 0x3f3f3f3fu;
             const uint32_t sc_hi = (hd.w & 0x0f0f0f0fu) | (((hd.y >> 6) & 0x03030303u) << 4), m_hi = ((hd.w >> 4) & 0x0f0f0f0fu) | (((hd.z >> 6) & 0x03030303u) << 4);
-            const int j0 = 2 * c, j1 = 2 * c + 1;
-            const float sc0 = (float) (((j0 < 4 ? sc_lo : sc_hi) >> (8 * (j0 & 3))) & 0xff), mn0 = (float) (((j0 < 4 ? m_lo : m_hi) >> (8 * (j0 & 3))) & 0xff);
-            const float sc1 = (float) (((j1 < 4 ? sc_lo : sc_hi) >> (8 * (j1 & 3))) & 0xff), mn1 = (float) (((j1 < 4 ? m_lo : m_hi) >> (8 * (j1 & 3))) & 0xff);
-            // w = d1 * q - m1: the nibbles enter fp16 as 1024 + q (bit trick), minus 1024 is exact, then one fused multiply-add per pair
-            const __half2 d1_lo = __float2half2_rn(__fmul_rn(d, sc0)), d1_hi = __float2half2_rn(__fmul_rn(d, sc1));
-            const __half2 o_lo = __float2half2_rn(-__fmul_rn(dmin, mn0)), o_hi = __float2half2_rn(-__fmul_rn(dmin, mn1));
             const __half2 k1024 = __float2half2_rn(1024.f);
-            if (kt >= TG_STAGES) tg_mbar_wait(bar_e + s * 8, ((kt / TG_STAGES) - 1) & 1);
-            uint8_t * arow = sA + s * A_BYTES + r * 128;
-            // output chunk j (16 bytes = 8 k) sits at chunk position j ^ (row & 7); low nibbles -> k 0..31 (chunks 0..3), high -> 32..63
 #pragma unroll
-            for (int t = 0; t < 2; t++) {
-                // bytes 8 (2 th + t) .. + 7 of the row: two 32-bit words -> per word pairs (e0, e2), (e1, e3)
-                uint32_t lo[4], hi[4];
+            for (int c = 0; c < 4; c++) {
+                const int kt = ri * 4 + c, s = kt % TG_STAGES;
+                const uint2 w[2] = { cur[c][0], cur[c][1] };
+                // sub-blocks 2c (low nibbles) and 2c + 1 (high nibbles) of the super-block
+                const int j0 = 2 * c, j1 = 2 * c + 1;
+                const float sc0 = (float) (((j0 < 4 ? sc_lo : sc_hi) >> (8 * (j0 & 3))) & 0xff), mn0 = (float) (((j0 < 4 ? m_lo : m_hi) >> (8 * (j0 & 3))) & 0xff);
+                const float sc1 = (float) (((j1 < 4 ? sc_lo : sc_hi) >> (8 * (j1 & 3))) & 0xff), mn1 = (float) (((j1 < 4 ? m_lo : m_hi) >> (8 * (j1 & 3))) & 0xff);
+                // w = d1 * q - m1: the nibbles enter fp16 as 1024 + q (bit trick), minus 1024 is exact, then one fused multiply-add per pair
+                const __half2 d1_lo = __float2half2_rn(__fmul_rn(d, sc0)), d1_hi = __float2half2_rn(__fmul_rn(d, sc1));
+                const __half2 o_lo = __float2half2_rn(-__fmul_rn(dmin, mn0)), o_hi = __float2half2_rn(-__fmul_rn(dmin, mn1));
+                if (kt >= TG_STAGES) tg_mbar_wait(bar_e + s * 8, ((kt / TG_STAGES) - 1) & 1);
+                uint8_t * arow = sA + s * A_BYTES + r * 128;
+                // output chunk j (16 bytes = 8 k) sits at chunk position j ^ (row & 7); low nibbles -> k 0..31 (chunks 0..3), high -> 32..63
 #pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const uint32_t v = h ? w[t].y : w[t].x;
-                    const uint32_t a0 = (v & 0x000F000Fu) | 0x64006400u, a1 = ((v >> 8) & 0x000F000Fu) | 0x64006400u;
-                    const uint32_t b0 = ((v >> 4) & 0x000F000Fu) | 0x64006400u, b1 = ((v >> 12) & 0x000F000Fu) | 0x64006400u;
-                    __half2 q;
-                    q = __hfma2(__hsub2(*reinterpret_cast<const __half2 *>(&a0), k1024), d1_lo, o_lo); lo[2 * h]     = *reinterpret_cast<uint32_t *>(&q);
-                    q = __hfma2(__hsub2(*reinterpret_cast<const __half2 *>(&a1), k1024), d1_lo, o_lo); lo[2 * h + 1] = *reinterpret_cast<uint32_t *>(&q);
-                    q = __hfma2(__hsub2(*reinterpret_cast<const __half2 *>(&b0), k1024), d1_hi, o_hi); hi[2 * h]     = *reinterpret_cast<uint32_t *>(&q);
-                    q = __hfma2(__hsub2(*reinterpret_cast<const __half2 *>(&b1), k1024), d1_hi, o_hi); hi[2 * h + 1] = *reinterpret_cast<uint32_t *>(&q);
+                for (int t = 0; t < 2; t++) {
+                    // bytes 8 (2 th + t) .. + 7 of the row: two 32-bit words -> per word pairs (e0, e2), (e1, e3)
+                    uint32_t lo[4], hi[4];
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const uint32_t v = h ? w[t].y : w[t].x;
+                        const uint32_t a0 = (v & 0x000F000Fu) | 0x64006400u, a1 = ((v >> 8) & 0x000F000Fu) | 0x64006400u;
+                        const uint32_t b0 = ((v >> 4) & 0x000F000Fu) | 0x64006400u, b1 = ((v >> 12) & 0x000F000Fu) | 0x64006400u;
+                        __half2 q;
+                        q = __hfma2(__hsub2(*reinterpret_cast<const __half2 *>(&a0), k1024), d1_lo, o_lo); lo[2 * h]     = *reinterpret_cast<uint32_t *>(&q);
+                        q = __hfma2(__hsub2(*reinterpret_cast<const __half2 *>(&a1), k1024), d1_lo, o_lo); lo[2 * h + 1] = *reinterpret_cast<uint32_t *>(&q);
+                        q = __hfma2(__hsub2(*reinterpret_cast<const __half2 *>(&b0), k1024), d1_hi, o_hi); hi[2 * h]     = *reinterpret_cast<uint32_t *>(&q);
+                        q = __hfma2(__hsub2(*reinterpret_cast<const __half2 *>(&b1), k1024), d1_hi, o_hi); hi[2 * h + 1] = *reinterpret_cast<uint32_t *>(&q);
+                    }
+                    const int ck = 2 * th + t;
+                    *reinterpret_cast<uint4 *>(arow + ((ck ^ (r & 7)) << 4))       = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                    *reinterpret_cast<uint4 *>(arow + (((4 + ck) ^ (r & 7)) << 4)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
                 }
-                const int ck = 2 * th + t;
-                *reinterpret_cast<uint4 *>(arow + ((ck ^ (r & 7)) << 4))       = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                *reinterpret_cast<uint4 *>(arow + (((4 + ck) ^ (r & 7)) << 4)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                tg_fence_async_smem();                              // generic-proxy writes -> visible to the tensor core's async proxy
+                __syncwarp();
+                if (lane == 0) tg_mbar_arrive(bar_a + s * 8);
             }
-            tg_fence_async_smem();                              // generic-proxy writes -> visible to the tensor core's async proxy
-            __syncwarp();
-            if (lane == 0) tg_mbar_arrive(bar_a + s * 8);
+#pragma unroll
+            for (int c = 0; c < 4; c++) { cur[c][0] = nxt[c][0]; cur[c][1] = nxt[c][1]; }
+            hcur = hnxt;
         }
         // ---- epilogue: accumulators -> y[token][row]; warp w reads tensor-memory lanes 32 (w % 4) .. + 31 ----
         tg_mbar_wait(bar_t, 0);

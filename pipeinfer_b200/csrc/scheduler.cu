@@ -566,6 +566,14 @@ int Scheduler::run(const llama_token * prompt, int n_prompt, llama_token * out, 
     const int64_t t_dec_end = llama_time_us();
     ev("end", n_predict);
     dump_trace();
+    if (chain_policy > 0) {
+        // the text is complete: what is still in flight is only waited for, so it is stopped first (a stopped run costs its launches,
+        // not its weights).  Not counted in n_cancelled: the reference's statistic is about rejected speculation.  Under the reference
+        // policy (PIB_SCHED_CHAIN=0) the schedule stays the reference's event for event: it waits for them.
+        std::vector<int32_t> ids;
+        for (auto & r : tgt_runs) if (!r.canceled) ids.push_back(r.batch.batch_id);
+        if (!ids.empty()) llama_cancel_run(ctx_tgt, ids.data(), (int) ids.size());
+    }
     for (int i = (int) tgt_runs.size() - 1; i >= 0; i--) llama_finish_async_decode(*ctx_tgt, tgt_runs[i].batch.view(max_seq + 1), tgt_runs[i].handle);
     tgt_runs.clear();
     if (res) {
