@@ -101,6 +101,16 @@ int pib_gemv_q4k_noalloc(const pib_weight * w, const void * act_dev, int b, floa
 /* Number of K splits pib_gemv_q4k_noalloc uses for an N x K matrix on the current device (1 = no scratch touched); lets a
  * caller -- and the tests -- see which shapes go through the built-in array.  No counterpart in the reference. */
 int pib_gemv_direct_splits(int64_t N, int64_t K);
+/* y = W . quantise(prologue(x)) in ONE launch, for narrow models whose passes are bound by the number of launches (Q4_K, b <= 8,
+ * K <= 8192; -3 otherwise): the kernel quantises the activations itself -- what the reference does at the top of
+ * ggml_compute_forward_mul_mat (ggml.c:9493-9509) -- after one of the element-wise ops that precede a matmul in build_llama:
+ *   prologue 0: x                                             (quantize_row_q8_K of the attention output)
+ *   prologue 1: rmsnorm(x [+ addend]) * x2, eps               (ggml_add, ggml_rms_norm ggml.c:9028, ggml_mul; sum_out, if given, receives x + addend)
+ *   prologue 2: silu(x) * x2                                  (ggml_silu through the fp16 table ggml.c:1490, ggml_mul; x and x2 rows xstride apart)
+ * Device pointers; x [b][xstride or K] fp32, y [b][N] fp32.  Same values as pib_quantize_act / pib_norm_quantize_act followed by pib_gemv
+ * up to the order of the fp32 additions. */
+int pib_gemv_fused(const pib_weight * w, int prologue, const float * x_dev, const float * x2_dev, const float * addend_dev, float * sum_out_dev,
+                   int64_t xstride, float eps, int b, float * y_dev, pib_stream s);
 /* Host-buffer convenience used by the parity tests and the end-to-end timing: x_host float [b][K] -> y_host [b][N];
  * includes the H2D copy of x, quantisation, GEMV and the D2H copy of y. */
 int pib_mul_mat_host(const pib_weight * w, const float * x_host, int b, float * y_host, int variant);

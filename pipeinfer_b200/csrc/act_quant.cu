@@ -13,6 +13,7 @@
 //   PRO_SILU_MUL  v = silu_f16lut(x) * x2                        (ggml.c:1490 table look-up, then ggml_mul; llama.cpp:3680)
 //   PRO_GELU      v = gelu_f16lut(x)                             (ggml.c:1433; falcon MLP)
 #include "pib_common.cuh"
+#include "q8k_quant.cuh"
 
 enum { PRO_PLAIN = 0, PRO_RMSNORM = 1, PRO_SILU_MUL = 2, PRO_GELU = 3, PRO_LAYERNORM = 4 };
 
@@ -238,60 +239,14 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
             } else {
                 aq_value8<PRO>(xr, x2r, scale, lut, i0, v, mean, biasr);
             }
-            // first element (in index order) with the largest |x|: strict '>' scan, ties keep the lower index
-            float amax = 0.0f, mx = 0.0f;
-            int   idx  = 1 << 30;
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-                const float ax = fabsf(v[j]);
-                if (ax > amax) { amax = ax; mx = v[j]; idx = lane * 8 + j; }
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
-                const float om = __shfl_xor_sync(0xffffffffu, mx, o);
-                const int   oi = __shfl_xor_sync(0xffffffffu, idx, o);
-                if (oa > amax || (oa == amax && oi < idx)) { amax = oa; mx = om; idx = oi; }
-            }
-            int q[8];
-            float dval = 0.0f;
-            if (amax == 0.0f) {
-#pragma unroll
-                for (int j = 0; j < 8; j++) q[j] = 0;
-            } else {
-                const float iscale = -128.f / mx;
-#pragma unroll
-                for (int j = 0; j < 8; j++) q[j] = min(127, __float2int_rn(__fmul_rn(iscale, v[j])));
-                dval = 1.0f / iscale;
-            }
-            int2 packed;
-            packed.x = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((q[3] & 0xff) << 24);
-            packed.y = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((q[7] & 0xff) << 24);
-            *reinterpret_cast<int2 *>(qs + (size_t) row * K + i0) = packed;
-            // fragment-order copy for the tensor-core GEMV: lane = 8c + 4h + t  ->  offset 64t + 16c + 8h
-            *reinterpret_cast<int2 *>(qsp + (size_t) row * K + sb * PIB_QK_K + (lane & 3) * 64 + (lane >> 3) * 16 + ((lane >> 2) & 1) * 8) = packed;
             if (vout) {
                 float4 * vo = reinterpret_cast<float4 *>(vout + (size_t) row * K + i0);
                 vo[0] = make_float4(v[0], v[1], v[2], v[3]);
                 vo[1] = make_float4(v[4], v[5], v[6], v[7]);
             }
-            int s8 = q[0] + q[1] + q[2] + q[3] + q[4] + q[5] + q[6] + q[7];
-            int s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
-            if ((lane & 1) == 0) ((int16_t *) bsplane)[(size_t) row * (K / 16) + sb * 16 + (lane >> 1)] = (int16_t) s16;
-            const int s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);        // the 32-element sub-block sum (lanes 4j..4j+3)
-            if ((lane & 3) == 0) {
-                int8_t * o = bs8plane + ((size_t) row * nsb + sb) * 16 + (lane >> 2);
-                o[0] = (int8_t) (s32 >> 6);
-                o[8] = (int8_t) (s32 & 63);
-                sbs[((size_t) row * nsb + sb) * 8 + (lane >> 2)] = (int16_t) s32;
-            }
-            // lane-group copy for the lane-exact kernel: this lane holds lane groups 2 (lane % 4) and 2 (lane % 4) + 1 of sub-block lane / 4
-            {
-                int2 * o = qsl + (((size_t) row * nsb + sb) * 8 + 2 * (lane & 3)) * 8 + (lane >> 2);
-                o[0] = make_int2(packed.x, 0);
-                o[8] = make_int2(0, packed.y);
-            }
-            if (lane == 0) dplane[(size_t) row * nsb + sb] = dval;
+            const size_t rs = (size_t) row * nsb + sb;
+            q8k_quantise_sb(v, lane, qs + (size_t) row * K + sb * PIB_QK_K, qsp + (size_t) row * K + sb * PIB_QK_K, (int16_t *) bsplane + rs * 16, bs8plane + rs * 16,
+                            sbs + rs * 8, qsl + rs * 64, dplane + rs);
         }
     }
 }

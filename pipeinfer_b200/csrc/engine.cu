@@ -22,6 +22,9 @@
 
 // kernels implemented in the other translation units
 int  pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, const int * cancel, cudaStream_t st);
+bool pib_gemv_pro_supported(const pib_weight * w, int b);
+int  pib_gemv_pro(const pib_weight * w, int pro, const float * x, const float * x2, const float * addend, float * sum_out, int64_t xstride, float eps,
+                  int b, float * y, const int * cancel, cudaStream_t st);
 int  pib_silu_mul_quantize_act(int wtype, const float * gate_dev, const float * up_dev, int64_t row_stride, int b, int64_t K,
                                void * act_dev, const int * cancel, cudaStream_t st);
 int  pib_quantize_act_c(int wtype, const float * x_dev, int b, int64_t K, void * act_dev, const int * cancel, cudaStream_t st);
@@ -438,6 +441,13 @@ pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_st
     CK(cudaMalloc(&c->desc_dev, c->desc_stride * (c->desc_slots + 65)));
     c->desc_ev.assign(c->desc_slots + 65, nullptr);
     { const char * g = getenv("PIB_GRAPHS"); c->use_graphs = !g || atoi(g) != 0; }
+    {
+        // prologue-fused GEMVs (PIB_FUSE_PRO=1; off by default): measured on the 1.1B draft, 204 -> 160 launches per step buy 1.6 % at one
+        // token (0.754 -> 0.742 ms) and lose at two (0.769 -> 0.864): the step is a chain of dependent memory round trips, and moving a
+        // quantiser into the matmul moves its round trips along with it
+        const char * g = getenv("PIB_FUSE_PRO");
+        c->fuse_pro = g ? atoi(g) : 0;
+    }
     { const char * g = getenv("PIB_PROMPT_GEMM"); c->prompt_gemm = (g && atoi(g) == 0) || pib_exact_mode() ? 0 : 1; }
     c->ops_cap = 1 << 16;
     CK(cudaMallocHost(&c->ops_host, sizeof(KvOp) * c->ops_cap));
@@ -625,6 +635,32 @@ static int run_chunk_body(pib_context * c, pib_run & run, int chunk, int ntok, i
     for (int il = m->layer_begin; (part & 1) && il < m->layer_end; il++) {
         const pib_layer & L  = m->layers[il];
         const size_t      lo = (size_t) (il - m->layer_begin) * c->n_ctx * GQA;
+        // PIB_FUSE_PRO=1: with one or two tokens the QKV and attention-output matmuls form their own quantised activations
+        // (gemv_q4k_pro_kernel: prologue 1 = [add +] RMSNorm, 0 = plain), 9 -> 7 launches per layer.  gate|up (704 CTAs on the draft, each
+        // redoing the 2048-wide norm) and down (silu over 5632 values per CTA) lose outright -- 17 against 8.9 and 8.0 us -- and are never fused.
+        const bool fuse = c->fuse_pro && var == 0 && !L.wv && ntok <= 2 && pib_gemv_pro_supported(L.wqkv, ntok) && pib_gemv_pro_supported(L.wo, ntok) &&
+                          L.wqkv->N <= 16 * 592 && L.wo->N <= 16 * 592;
+#define GEMVP(kind, ...) do {                                                                                          \
+        const bool pr__ = c->prof_now && il == c->prof_layer && c->prof.size() < 8192;                                 \
+        pib_context::ProfRec r__ = { (kind), ntok, nullptr, nullptr };                                                 \
+        if (pr__) { cudaEventCreate(&r__.e0); cudaEventCreate(&r__.e1); cudaEventRecord(r__.e0, st); }                 \
+        if (!(skip_mask >> (kind) & 1)) RC(pib_gemv_pro(__VA_ARGS__, cancel, st));                                     \
+        if (pr__) { cudaEventRecord(r__.e1, st); c->prof.push_back(r__); }                                             \
+    } while (0)
+        if (fuse) {
+            if (pending_add) GEMVP(0, L.wqkv, 1, c->proj, L.attn_norm, c->x2, c->x, 0, m->rms_eps, ntok, c->qkv);
+            else             GEMVP(0, L.wqkv, 1, c->x, L.attn_norm, nullptr, nullptr, 0, m->rms_eps, ntok, c->qkv);
+            TL(7, il, pib_attention(c->qkv, nullptr, desc, c->rope, c->rope_n_pos, 0, c->kcache + lo, c->vcache + lo, c->mask, c->kvd.scalars, ntok,
+                                    m->n_head, m->n_head_kv, hd, (int) c->n_ctx, c->att, cancel, st, true));
+            GEMVP(1, L.wo, 0, c->att, nullptr, nullptr, nullptr, 0, 0.f, ntok, c->proj);
+            TL(9, il, pib_add_rmsnorm_quantize_act(wt, c->proj, c->x, c->x2, L.ffn_norm, m->rms_eps, ntok, E, c->act, cancel, st));   // x2 = ffn_inp
+            GEMV(2, il, L.wgu, c->gu);
+            TL(10, il, pib_silu_mul_quantize_act(wt, c->gu, c->gu + FF, 2 * (int64_t) FF, ntok, FF, c->act, cancel, st));
+            GEMV(3, il, L.wdown, c->proj);
+            pending_add = true;
+            continue;
+        }
+#undef GEMVP
         if (pending_add) TL(5, il, pib_add_rmsnorm_quantize_act(wt, c->proj, c->x2, c->x, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
         else             TL(5, il, pib_add_rmsnorm_quantize_act(wt, c->x, nullptr, nullptr, L.attn_norm, m->rms_eps, ntok, E, c->act, cancel, st));
         GEMV(0, il, L.wqkv, c->qkv);

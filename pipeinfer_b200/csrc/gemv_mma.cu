@@ -23,6 +23,7 @@
 #include <mutex>
 #include <utility>
 #include "pib_common.cuh"
+#include "q8k_quant.cuh"
 
 #define MM_WARPS   4
 #define MM_THREADS (MM_WARPS * 32)
@@ -346,7 +347,8 @@ gemv_q4k_mma_kernel(const uint8_t * __restrict__ tiles, int nsb, int n_tiles, in
 }
 
 // the arithmetic of one (16-row tile, super-block) record for NT n-tiles of 8 tokens, shared by the kernels below
-template <int NT>
+// (ACT_SMEM: the activation planes live in shared memory -- the prologue-fused kernel -- and are read with ordinary loads)
+template <int NT, bool ACT_SMEM = false>
 __device__ __forceinline__ void q4k_record(const int4 (&wq)[4], const int4 (&hq)[2], int s, int t, const int8_t * const (&a_qs)[NT],
                                            const int8_t * const (&a_b8)[NT], const float * const (&a_dx)[NT][2], float (&acc)[NT][4]) {
     const q4k_hdr H0 = decode_hdr(make_uint4((uint32_t) hq[0].x, (uint32_t) hq[0].y, (uint32_t) hq[0].z, (uint32_t) hq[0].w));
@@ -358,12 +360,12 @@ __device__ __forceinline__ void q4k_record(const int4 (&wq)[4], const int4 (&hq)
     for (int n = 0; n < NT; n++) {
         const int4 * ap = reinterpret_cast<const int4 *>(a_qs[n] + (size_t) s * 256);
 #pragma unroll
-        for (int c = 0; c < 4; c++) aq[n][c] = __ldg(ap + c);
+        for (int c = 0; c < 4; c++) aq[n][c] = ACT_SMEM ? ap[c] : __ldg(ap + c);
         const int * bp = reinterpret_cast<const int *>(a_b8[n] + (size_t) s * 16);
-        amh[n] = __ldg(bp);
-        aml[n] = __ldg(bp + 2);
+        amh[n] = ACT_SMEM ? bp[0] : __ldg(bp);
+        aml[n] = ACT_SMEM ? bp[2] : __ldg(bp + 2);
 #pragma unroll
-        for (int e = 0; e < 2; e++) adx[n][e] = __ldg(a_dx[n][e] + s);
+        for (int e = 0; e < 2; e++) adx[n][e] = ACT_SMEM ? a_dx[n][e][s] : __ldg(a_dx[n][e] + s);
     }
     int sumi[NT][4], sumh[NT][4];
 #pragma unroll
@@ -633,6 +635,168 @@ gemv_q4k_ring_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, 
         }
     }
     if (threadIdx.x == 0) counters[T] = 0;          // self-cleaning: ready for the next launch
+}
+
+// ---- prologue-fused variant (small models): the GEMV quantises its own activations ------------------------------------------------
+// A model as small as the 1.1B draft is bound by the number of launches, not by bytes: every kernel costs a ~1.7 us hop however
+// little it does.  Here the kernel that used to stand in front of a matmul -- residual add + RMSNorm + quantise, plain quantise, or
+// SiLU(gate) * up + quantise -- runs inside the matmul: every CTA (one 16-row tile, as in the ring kernel) forms the quantised
+// activation planes of all b tokens in its own shared memory (K <= 8192 values per token: a few microseconds of redundant work per
+// CTA instead of a launch), then streams its records exactly as the ring kernel does -- same decomposition, same order of fp32
+// additions, same bytes out.  The quantiser is the one of act_quant.cu (q8k_quant.cuh).  CTA 0 also writes the residual sum.
+enum { GP_PLAIN = 0, GP_RMSNORM = 1, GP_SILU_MUL = 2 };
+#define GP_WARPS 4
+template <int PRO>
+__global__ void __launch_bounds__(GP_WARPS * 32, 4)
+gemv_q4k_pro_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, int b, float * __restrict__ y,
+                    const float * __restrict__ x, const float * __restrict__ x2, const float * __restrict__ addend, float * __restrict__ sum_out,
+                    int64_t xstride, float eps, const uint16_t * __restrict__ lut, const int * __restrict__ cancel) {
+    if (PIB_CANCELLED(cancel)) { pib_pdl_wait(); return; }
+    extern __shared__ __align__(16) uint8_t rg_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    const int T = blockIdx.x;
+    constexpr int STAGES = RG_STAGES;
+    const uint8_t * tbase  = tiles + (size_t) T * nsb * MM_TILE_BYTES + lane * 16;
+    uint8_t *       ring   = rg_smem + warp * (STAGES * MM_TILE_BYTES);
+    const uint32_t  ring_a = smem_u32(ring) + lane * 16;
+    // activation planes behind the rings: qsp [b][K] int8, bs8 [b][nsb][16] int8, d [b][nsb] float
+    int8_t * s_qsp = reinterpret_cast<int8_t *>(rg_smem + GP_WARPS * STAGES * MM_TILE_BYTES);
+    int8_t * s_bs8 = s_qsp + (size_t) b * K;
+    float *  s_d   = reinterpret_cast<float *>(s_bs8 + (size_t) b * nsb * 16);
+    __shared__ double s_red[GP_WARPS][8];
+    int ps = warp;
+    auto issue = [&](int stage) {
+        if (ps < nsb) {
+            const uint8_t * src = tbase + (size_t) ps * MM_TILE_BYTES;
+            const uint32_t  dst = ring_a + stage * MM_TILE_BYTES;
+#pragma unroll
+            for (int c = 0; c < 4; c++) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + c * 512), "l"(src + c * 512) : "memory");
+            if (lane < 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 2048), "l"(src + 2048) : "memory");
+            ps += GP_WARPS;
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#pragma unroll
+    for (int i = 0; i < STAGES - 1; i++) issue(i);
+    pib_pdl_wait();
+    pib_pdl_trigger();
+
+    // ---- prologue: the activation planes of all b tokens ---------------------------------------------------------------------
+    float scale[8];
+#pragma unroll
+    for (int tk = 0; tk < 8; tk++) scale[tk] = 1.f;
+    if (PRO == GP_RMSNORM) {
+        // sum of squares per token in double (ggml.c:9028), residual add in front when there is an addend; CTA 0 stores the sums
+        const int n4 = K / 4;
+#pragma unroll 1
+        for (int tk = 0; tk < b; tk++) {
+            const float4 * x4 = reinterpret_cast<const float4 *>(x + (size_t) tk * xstride);
+            const float4 * a4 = addend ? reinterpret_cast<const float4 *>(addend + (size_t) tk * K) : nullptr;
+            float4 *       o4 = (sum_out && T == 0) ? reinterpret_cast<float4 *>(sum_out + (size_t) tk * K) : nullptr;
+            double sm = 0.0;
+#pragma unroll 4
+            for (int i = threadIdx.x; i < n4; i += GP_WARPS * 32) {
+                float4 v = x4[i];
+                if (a4) {
+                    const float4 a = a4[i];
+                    v.x = __fadd_rn(v.x, a.x); v.y = __fadd_rn(v.y, a.y); v.z = __fadd_rn(v.z, a.z); v.w = __fadd_rn(v.w, a.w);
+                    if (o4) o4[i] = v;
+                }
+                sm += (double) __fmul_rn(v.x, v.x); sm += (double) __fmul_rn(v.y, v.y); sm += (double) __fmul_rn(v.z, v.z); sm += (double) __fmul_rn(v.w, v.w);
+            }
+            sm = warp_sum_d(sm);
+            if (lane == 0) s_red[warp][tk] = sm;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int tk = 0; tk < 8; tk++)
+            if (tk < b) {
+                double tt = 0.0;
+#pragma unroll
+                for (int w = 0; w < GP_WARPS; w++) tt += s_red[w][tk];
+                scale[tk] = 1.0f / sqrtf((float) (tt / (double) K) + eps);
+            }
+    }
+    for (int task = warp; task < b * nsb; task += GP_WARPS) {
+        const int tk = task / nsb, sb = task - tk * nsb;
+        const int64_t i0 = (int64_t) sb * 256 + lane * 8;
+        const float * xr = x + (size_t) tk * xstride + i0;
+        const float4 xa = *reinterpret_cast<const float4 *>(xr), xb = *reinterpret_cast<const float4 *>(xr + 4);
+        float xv[8] = { xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w };
+        float v[8];
+        if (PRO == GP_RMSNORM) {
+            if (addend) {
+                const float4 aa = *reinterpret_cast<const float4 *>(addend + (size_t) tk * K + i0), ab = *reinterpret_cast<const float4 *>(addend + (size_t) tk * K + i0 + 4);
+                xv[0] = __fadd_rn(xv[0], aa.x); xv[1] = __fadd_rn(xv[1], aa.y); xv[2] = __fadd_rn(xv[2], aa.z); xv[3] = __fadd_rn(xv[3], aa.w);
+                xv[4] = __fadd_rn(xv[4], ab.x); xv[5] = __fadd_rn(xv[5], ab.y); xv[6] = __fadd_rn(xv[6], ab.z); xv[7] = __fadd_rn(xv[7], ab.w);
+            }
+            const float4 wa = *reinterpret_cast<const float4 *>(x2 + i0), wb = *reinterpret_cast<const float4 *>(x2 + i0 + 4);
+            const float  w8[8] = { wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w };
+            float sc = 1.f;
+#pragma unroll
+            for (int q = 0; q < 8; q++) if (q == tk) sc = scale[q];
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = __fmul_rn(__fmul_rn(xv[j], sc), w8[j]);
+        } else if (PRO == GP_SILU_MUL) {
+            const float * ur = x2 + (size_t) tk * xstride + i0;
+            const float4 ua = *reinterpret_cast<const float4 *>(ur), ub = *reinterpret_cast<const float4 *>(ur + 4);
+            const float  u8[8] = { ua.x, ua.y, ua.z, ua.w, ub.x, ub.y, ub.z, ub.w };
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = __fmul_rn(pib_h2f(lut[pib_f2h(xv[j])]), u8[j]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = xv[j];
+        }
+        q8k_quantise_sb(v, lane, nullptr, s_qsp + (size_t) tk * K + sb * 256, nullptr, s_bs8 + ((size_t) tk * nsb + sb) * 16, nullptr, nullptr,
+                        s_d + (size_t) tk * nsb + sb);
+    }
+    __syncthreads();
+
+    // ---- main loop: the ring kernel's, activations from shared memory ---------------------------------------------------------------
+    float acc[1][4] = { { 0.f, 0.f, 0.f, 0.f } };
+    const int8_t * a_qs[1];
+    const int8_t * a_b8[1];
+    const float *  a_dx[1][2];
+    {
+        const int tok = min(g, b - 1);
+        a_qs[0] = s_qsp + (size_t) tok * K + t * 64;
+        a_b8[0] = s_bs8 + (size_t) tok * nsb * 16 + (t & 1) * 4;
+#pragma unroll
+        for (int e = 0; e < 2; e++) a_dx[0][e] = s_d + (size_t) min(2 * t + e, b - 1) * nsb;
+    }
+    int stage = 0;
+    for (int s = warp; s < nsb; s += GP_WARPS) {
+        __syncwarp();
+        issue((stage + STAGES - 1) % STAGES);
+        asm volatile("cp.async.wait_group %0;" ::"n"(STAGES - 1) : "memory");
+        __syncwarp();
+        const uint8_t * rs = ring + stage * MM_TILE_BYTES;
+        int4 wq[4], hq[2];
+#pragma unroll
+        for (int c = 0; c < 4; c++) wq[c] = *reinterpret_cast<const int4 *>(rs + c * 512 + lane * 16);
+        hq[0] = *reinterpret_cast<const int4 *>(rs + 2048 + g * 16);
+        hq[1] = *reinterpret_cast<const int4 *>(rs + 2048 + (g + 8) * 16);
+        q4k_record<1, true>(wq, hq, s, t, a_qs, a_b8, a_dx, acc);
+        stage = stage + 1 == STAGES ? 0 : stage + 1;
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();                                            // the rings are done with: their memory becomes the reduction buffer
+    float (*red)[8][16] = reinterpret_cast<float (*)[8][16]>(rg_smem);
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+        red[warp][2 * t + e][g]     = acc[0][e];
+        red[warp][2 * t + e][g + 8] = acc[0][2 + e];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 8 * 16; i += GP_WARPS * 32) {
+        const int tok = i / 16, r = i % 16, row = T * 16 + r;
+        if (tok < b && row < N) {
+            float v = red[0][tok][r];
+#pragma unroll
+            for (int w2 = 1; w2 < GP_WARPS; w2++) v += red[w2][tok][r];
+            y[(size_t) tok * N + row] = v;
+        }
+    }
 }
 
 // ---- balanced variant: the matrix as ONE stream of records ---------------------------------------------------------------------
@@ -961,6 +1125,43 @@ int pib_gemv_stream(const pib_weight * w, const void * act_dev, int b, float * y
     const int8_t * bs  = (const int8_t *) (act + L.bs8_off);
     return b <= 8 ? stream_launch<1>(w, aqs, ad, bs, b, y_dev, runs, pmax, s->partial, s->counters, cancel, st)
                   : stream_launch<2>(w, aqs, ad, bs, b, y_dev, runs, pmax, s->partial, s->counters, cancel, st);
+}
+
+// matmul with the activation prologue inside (see gemv_q4k_pro_kernel).  pro: 0 plain (x), 1 [x + addend ->] RMSNorm * x2, 2 silu(x) * x2
+bool pib_gemv_pro_supported(const pib_weight * w, int b) {
+    if (!w || w->type != PIB_TYPE_Q4_K || !w->tiles || b < 1 || b > 8 || w->K > 8192 || w->K % 256) return false;
+    const int nsb = (int) (w->K / 256);
+    return (size_t) GP_WARPS * RG_STAGES * MM_TILE_BYTES + (size_t) b * (w->K + nsb * 20) <= 100 * 1024;
+}
+
+template <int PRO>
+static int pro_launch(const pib_weight * w, int b, float * y, const float * x, const float * x2, const float * addend, float * sum_out, int64_t xstride,
+                      float eps, const uint16_t * lut, const int * cancel, cudaStream_t st) {
+    const int    nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    const size_t smem = (size_t) GP_WARPS * RG_STAGES * MM_TILE_BYTES + (size_t) b * (w->K + nsb * 20);
+    static size_t configured = 0;
+    if (smem > configured) {
+        PIB_CHECK(cudaFuncSetAttribute(gemv_q4k_pro_kernel<PRO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (100 * 1024)));
+        PIB_CHECK(cudaFuncSetAttribute(gemv_q4k_pro_kernel<PRO>, cudaFuncAttributePreferredSharedMemoryCarveout, (int) cudaSharedmemCarveoutMaxShared));
+        configured = 100 * 1024;
+    }
+    pib_launch(gemv_q4k_pro_kernel<PRO>, dim3(n_tiles), dim3(GP_WARPS * 32), smem, st, w->tiles, nsb, (int) w->N, (int) w->K, b, y, x, x2, addend, sum_out,
+               xstride, eps, lut, cancel);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+
+int pib_gemv_pro(const pib_weight * w, int pro, const float * x, const float * x2, const float * addend, float * sum_out, int64_t xstride, float eps,
+                 int b, float * y, const int * cancel, cudaStream_t st) {
+    if (!pib_gemv_pro_supported(w, b)) { pib_set_error("pib_gemv_pro: unsupported matrix / batch"); return PIB_ERR_UNSUPP; }
+    if (xstride == 0) xstride = w->K;
+    switch (pro) {
+        case GP_PLAIN:    return pro_launch<GP_PLAIN>(w, b, y, x, nullptr, nullptr, nullptr, xstride, 0.f, nullptr, cancel, st);
+        case GP_RMSNORM:  return pro_launch<GP_RMSNORM>(w, b, y, x, x2, addend, sum_out, xstride, eps, nullptr, cancel, st);
+        case GP_SILU_MUL: return pro_launch<GP_SILU_MUL>(w, b, y, x, x2, nullptr, nullptr, xstride, 0.f, pib_get_luts().silu_f16, cancel, st);
+    }
+    pib_set_error("pib_gemv_pro: unknown prologue %d", pro);
+    return PIB_ERR_ARG;
 }
 
 // variant 5: direct (register-prefetched) kernel

@@ -155,6 +155,17 @@ extern "C" int pib_gemv(const pib_weight * w, const void * act_dev, int b, float
     return pib_gemv_internal(w, act_dev, b, y_dev, variant, nullptr, (cudaStream_t) s);
 }
 
+int pib_gemv_pro(const pib_weight * w, int pro, const float * x, const float * x2, const float * addend, float * sum_out, int64_t xstride, float eps,
+                 int b, float * y, const int * cancel, cudaStream_t st);
+extern "C" int pib_gemv_fused(const pib_weight * w, int prologue, const float * x_dev, const float * x2_dev, const float * addend_dev, float * sum_out_dev,
+                              int64_t xstride, float eps, int b, float * y_dev, pib_stream s) {
+    if (!w || !x_dev || !y_dev || prologue < 0 || prologue > 2 || (prologue > 0 && !x2_dev) || (sum_out_dev && !addend_dev)) {
+        pib_set_error("pib_gemv_fused: bad arguments");
+        return PIB_ERR_ARG;
+    }
+    return pib_gemv_pro(w, prologue, x_dev, x2_dev, addend_dev, sum_out_dev, xstride, eps, b, y_dev, nullptr, (cudaStream_t) s);
+}
+
 extern "C" int pib_mul_mat_host(const pib_weight * w, const float * x_host, int b, float * y_host, int variant) {
     if (!w || b < 1 || b > PIB_MAX_BATCH) { pib_set_error("pib_mul_mat_host: bad arguments"); return PIB_ERR_ARG; }
     const size_t xb = (size_t) b * w->K * 4, yb = (size_t) b * w->N * 4, ab = pib_act_bytes(pib_act_family(w->type), w->K, b);
