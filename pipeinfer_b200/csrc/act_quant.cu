@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
                                                                int8_t * __restrict__ qs, float * __restrict__ dplane,
                                                                void * __restrict__ bsplane, int8_t * __restrict__ bs8plane,
                                                                int8_t * __restrict__ qsp, int2 * __restrict__ qsl,
-                                                               int16_t * __restrict__ sbs,
+                                                               int16_t * __restrict__ sbs, int8_t * __restrict__ q6p, int8_t * __restrict__ b16,
                                                                float * __restrict__ vout,
                                                                const uint16_t * __restrict__ lut,
                                                                const float * __restrict__ addend, float * sum_out,
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(AQ_THREADS) act_quant_kernel(const float * x, 
             }
             const size_t rs = (size_t) row * nsb + sb;
             q8k_quantise_sb(v, lane, qs + (size_t) row * K + sb * PIB_QK_K, qsp + (size_t) row * K + sb * PIB_QK_K, (int16_t *) bsplane + rs * 16, bs8plane + rs * 16,
-                            sbs + rs * 8, qsl + rs * 64, dplane + rs);
+                            sbs + rs * 8, qsl + rs * 64, dplane + rs, q6p + (size_t) row * K + sb * PIB_QK_K, b16 + rs * 32);
         }
     }
 }
@@ -265,11 +265,13 @@ static int launch_aq(int wtype, const float * x, const float * x2, int x2_per_ro
     int8_t * qp = (int8_t *) act + L.qsp_off;
     int2 *    ql = (int2 *) ((uint8_t *) act + L.qsl_off);
     int16_t * sb = (int16_t *) ((uint8_t *) act + L.sbs_off);
+    int8_t *  q6 = (int8_t *) act + L.q6p_off;
+    int8_t *  b6 = (int8_t *) act + L.b16_off;
     const int64_t units = wtype == PIB_TYPE_Q4_K ? K / PIB_QK_K : K / PIB_QK / 4;        // super-blocks, or groups of 4 blocks
     const int     parts = (int) max((int64_t) 1, min((int64_t) 32, units / (AQ_THREADS / 32)));
     const dim3    grid(b, parts);
-    if (wtype == PIB_TYPE_Q4_K) pib_launch(act_quant_kernel<true, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, ql, sb, vout, lut, addend, sum_out, cancel, xstride, bias, addend2);
-    else                        pib_launch(act_quant_kernel<false, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, ql, sb, vout, lut, addend, sum_out, cancel, xstride, bias, addend2);
+    if (wtype == PIB_TYPE_Q4_K) pib_launch(act_quant_kernel<true, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, ql, sb, q6, b6, vout, lut, addend, sum_out, cancel, xstride, bias, addend2);
+    else                        pib_launch(act_quant_kernel<false, PRO>, grid, dim3(AQ_THREADS), 0, st, x, x2, x2_per_row, eps, K, qs, d, bs, b8, qp, ql, sb, q6, b6, vout, lut, addend, sum_out, cancel, xstride, bias, addend2);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }

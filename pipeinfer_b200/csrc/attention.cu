@@ -40,45 +40,6 @@ void rope_table_build(std::vector<float2> & tab, int n_pos, int n_dims, int mode
     }
 }
 
-// one CTA per token: rotate Q (-> fp16) and K (-> fp16 cache), copy V (-> fp16 cache)
-// qkv: [b][E + 2*GQA] fp32 (fused projection output);  mode 0: pairs (2i, 2i+1);  mode 2: pairs (i, i + hd/2)
-__global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8_t * __restrict__ desc,
-                                     const float2 * __restrict__ rope, int rope_n_pos, int E, int GQA, int hd, int mode,
-                                     __half * __restrict__ q16, __half * __restrict__ kcache, __half * __restrict__ vcache,
-                                     const int * __restrict__ cancel, const float * __restrict__ vsep) {
-    const int32_t * hdr = reinterpret_cast<const int32_t *>(desc + PIB_DESC_HDR_OFF);
-    pib_pdl_wait();
-    pib_pdl_trigger();
-    if (PIB_CANCELLED(cancel)) return;
-    const int       t    = blockIdx.x;
-    const int       pos  = reinterpret_cast<const int32_t *>(desc + PIB_DESC_POS_OFF)[t];
-    const int       cell = hdr[PIB_DH_KVHEAD] + t;
-    // vsep != null: V comes from its own matmul ([b][GQA]; Wv of another weight type than Wq|Wk) and qkv rows hold Q|K only
-    const float *   row  = qkv + (size_t) t * (E + (vsep ? 1 : 2) * GQA);
-    const int       half = hd / 2;
-    const float2 *  cs   = rope + (size_t) min(pos, rope_n_pos - 1) * half;
-    const int       nq = E / 2, nk = GQA / 2;
-    const int       tid0 = blockIdx.y * blockDim.x + threadIdx.x, nthr = gridDim.y * blockDim.x;
-    for (int i = tid0; i < nq + nk; i += nthr) {
-        const bool    isq  = i < nq;
-        const int     pi   = isq ? i : i - nq;          // pair index inside Q or K
-        const int     h    = pi / half, j = pi % half;
-        const float * src  = (isq ? row : row + E) + (size_t) h * hd;
-        const float2  c    = cs[j];
-        int i0, i1;
-        if (mode & 2) { i0 = j; i1 = j + half; } else { i0 = 2 * j; i1 = 2 * j + 1; }
-        const float x0 = src[i0], x1 = src[i1];
-        // unfused: the reference is built without fp contraction (-std=c11)
-        const float y0 = __fsub_rn(__fmul_rn(x0, c.x), __fmul_rn(x1, c.y));
-        const float y1 = __fadd_rn(__fmul_rn(x0, c.y), __fmul_rn(x1, c.x));
-        __half * dst = isq ? q16 + (size_t) t * E + (size_t) h * hd : kcache + (size_t) cell * GQA + (size_t) h * hd;
-        dst[i0] = __float2half_rn(y0);
-        dst[i1] = __float2half_rn(y1);
-    }
-    const float * v = vsep ? vsep + (size_t) t * GQA : row + E + GQA;
-    for (int i = tid0; i < GQA; i += nthr) vcache[(size_t) cell * GQA + i] = __float2half_rn(v[i]);
-}
-
 // ---- attention ------------------------------------------------------------------------------------------------------
 // grid (n_head, n_tokens), 256 threads; one CTA per (query head, token).  Every fp32 sum is formed in the reference's order
 // (ggml_vec_dot_f16 for both K.Q and V.P), so the output is bit-identical to the CPU's: phase 1 gives every thread whole cells
@@ -91,8 +52,8 @@ __global__ void rope_kv_store_kernel(const float * __restrict__ qkv, const uint8
 // ALL tokens of the batch for its KV head into shared memory (<= 16 rows: the batch's cells are the contiguous range starting at
 // the descriptor's kv head, and a token of a tree batch attends to earlier tokens of the same batch), and the first query head
 // of each KV group also writes its token's K / V row to the cache.  Cells of the batch are therefore never read from global
-// memory, cells outside it never written: no ordering between CTAs is needed.  Values and roundings are those of the separate
-// rope_kv_store_kernel (reference rope_f32 ggml.c:11006, dup f32 -> f16 :6528).
+// memory, cells outside it never written: no ordering between CTAs is needed.  Values and roundings are the reference's
+// (rope_f32 ggml.c:11006, dup f32 -> f16 :6528).
 //
 // The kernel is a chain of dependent memory round trips, not of arithmetic, so everything that does not depend on the QKV
 // projection is fetched BEFORE the wait on it: the descriptor words and positions, the RoPE entries, the mask bytes and K rows of
@@ -340,14 +301,6 @@ static int launch_att_qh(const float * qkv, const float * vsep, const uint8_t * 
     }
     pib_launch(attention_qh_kernel<HD>, dim3(n_head, n_tokens), dim3(ATQ_THREADS), smem, st, qkv, vsep, desc, rope, rope_n_pos, mode, kc, vc, mask, scalars,
                pib_get_luts().exp_f16, E, GQA, n_ctx, 1.0f / sqrtf((float) HD), out, cancel, gdiv, vcap, early);
-    PIB_CHECK(cudaGetLastError());
-    return PIB_OK;
-}
-
-int pib_rope_kv_store(const float * qkv, const uint8_t * desc, const float2 * rope, int rope_n_pos, int n_tokens, int E, int GQA,
-                      int hd, int mode, __half * q16, __half * kc, __half * vc, const int * cancel, cudaStream_t st, const float * vsep) {
-    const int parts = max(1, min(16, (E / 2 + GQA / 2 + 511) / 512));
-    pib_launch(rope_kv_store_kernel, dim3(n_tokens, parts), dim3(256), 0, st, qkv, desc, rope, rope_n_pos, E, GQA, hd, mode, q16, kc, vc, cancel, vsep);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;
 }

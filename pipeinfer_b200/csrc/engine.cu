@@ -419,7 +419,6 @@ pib_context * pib_context_new(pib_model * m, uint32_t n_ctx, int max_seq, pib_st
     CK(cudaMalloc(&c->att, (size_t) B * E * 4));
     CK(cudaMalloc(&c->proj, (size_t) B * E * 4));
     CK(cudaMalloc(&c->gu, (size_t) B * 2 * FF * 4));
-    CK(cudaMalloc(&c->q16, (size_t) B * E * 2));
     CK(cudaMalloc(&c->mask, (size_t) B * n_ctx));
     actb = std::max(pib_act_bytes(m->wtype, E, B), pib_act_bytes(m->wtype, FF, B));
     CK(cudaMalloc(&c->act, actb));
@@ -465,10 +464,10 @@ void pib_context_free(pib_context * c) {
     if (!c) return;
     if (c->stream) cudaStreamSynchronize(c->stream);
     pib_pipe_hop_free(c);
-    for (void * b : { (void *) c->pb.x, (void *) c->pb.x2, (void *) c->pb.qkv, (void *) c->pb.att, (void *) c->pb.proj, (void *) c->pb.gu, (void *) c->pb.q16,
+    for (void * b : { (void *) c->pb.x, (void *) c->pb.x2, (void *) c->pb.qkv, (void *) c->pb.att, (void *) c->pb.proj, (void *) c->pb.gu,
                       (void *) c->pb.mask, c->pb.act, c->pb.xhat }) if (b) cudaFree(b);
     kv_device_free(&c->kvd);
-    void * bufs[] = { c->vsep, c->kcache, c->vcache, c->x, c->x2, c->qkv, c->att, c->proj, c->gu, c->q16, c->mask, c->act, c->rope,
+    void * bufs[] = { c->vsep, c->kcache, c->vcache, c->x, c->x2, c->qkv, c->att, c->proj, c->gu, c->mask, c->act, c->rope,
                       c->cancel_table, c->desc_dev, c->ops_dev, c->bias_ids_dev, c->bias_val_dev, c->logits_fetch_dev };
     for (void * b : bufs) if (b) cudaFree(b);
     if (c->desc_host) cudaFreeHost(c->desc_host);
@@ -789,7 +788,7 @@ static int prompt_bufs(pib_context * c) {
     auto & b = c->pb;
     if (cudaMalloc(&b.x, P * E * 4) != cudaSuccess || cudaMalloc(&b.x2, P * E * 4) != cudaSuccess || cudaMalloc(&b.qkv, P * (E + 2 * GQA) * 4) != cudaSuccess ||
         cudaMalloc(&b.att, P * E * 4) != cudaSuccess || cudaMalloc(&b.proj, P * E * 4) != cudaSuccess || cudaMalloc(&b.gu, P * 2 * FF * 4) != cudaSuccess ||
-        cudaMalloc(&b.q16, P * E * 2) != cudaSuccess || cudaMalloc(&b.mask, P * c->n_ctx) != cudaSuccess ||
+        cudaMalloc(&b.mask, P * c->n_ctx) != cudaSuccess ||
         cudaMalloc(&b.act, pib_act_bytes(PIB_TYPE_Q4_K, (int64_t) KM, (int) P)) != cudaSuccess || cudaMalloc(&b.xhat, pib_gemm_xhat_bytes((int64_t) KM, (int) P)) != cudaSuccess) {
         cudaGetLastError();
         pib_set_error("decode: out of memory for the prompt path's work buffers");

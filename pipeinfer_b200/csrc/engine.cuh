@@ -112,7 +112,6 @@ struct pib_context {
     // per-chunk work buffers
     float * vsep = nullptr;               // [chunk][n_embd_gqa]: V of a layer whose Wv is a separate matrix
     float * x = nullptr, * x2 = nullptr, * qkv = nullptr, * att = nullptr, * proj = nullptr, * gu = nullptr;
-    __half * q16 = nullptr;
     uint8_t * mask = nullptr;
     void *  act = nullptr;
     float2 * rope = nullptr;
@@ -124,7 +123,7 @@ struct pib_context {
     bool     cancel_ev_pending = false;
 
     // wide-batch (prompt) path: work buffers for up to PIB_PROMPT_MAX tokens at once, allocated on the first prompt that uses them
-    struct PromptBufs { float * x = nullptr, * x2 = nullptr, * qkv = nullptr, * att = nullptr, * proj = nullptr, * gu = nullptr; __half * q16 = nullptr;
+    struct PromptBufs { float * x = nullptr, * x2 = nullptr, * qkv = nullptr, * att = nullptr, * proj = nullptr, * gu = nullptr;
                         uint8_t * mask = nullptr; void * act = nullptr, * xhat = nullptr; bool ready = false; } pb;
     int      fuse_pro = 0;                 // 1: small llama-arch Q4_K models run norm / quantise / silu inside the consuming GEMV (PIB_FUSE_PRO, engine.cu)
     int      prompt_gemm = 1;              // 0: prompts go through the GEMV kernels in chunks of 16 (PIB_PROMPT_GEMM=0, and always in exact mode)

@@ -141,6 +141,10 @@ struct pib_act_layout {
     size_t qsl_off;    // Q8_K family: int2 [b][K/256][8 lane groups g][8 sub-blocks j]: {x if g even else 0, x if g odd else 0} with x =
                        //   the four quants 4g .. 4g+3 of sub-block j -- the two B registers of the lane-exact kernel (gemv_q4k_lane.cu)
     size_t sbs_off;    // Q8_K family: int16 [b][K/32] sub-block sums bsums[2j] + bsums[2j+1]
+    size_t q6p_off;    // Q8_K family: int8 [b][K], the quants in the B-fragment order of mma.m16n8k16 over the 16-element groups of
+                       //   Q6_K: inside each super-block element e = 16j + 4t + i (group j, lane quarter t) sits at 64t + 4j + i
+    size_t b16_off;    // Q8_K family: int8 [b][K/256][32] = {hi_0..hi_15, lo_0..lo_15}: the 16 bsums split as 64 * hi + lo, so that the
+                       //   -32 offset of Q6_K (sum_j scale_j * bsum_j) is two more tensor-core dot products (gemv_q6k.cu)
     size_t total;
 };
 __host__ __device__ inline pib_act_layout pib_act_layout_of(int wtype, int64_t K, int b) {
@@ -159,6 +163,8 @@ __host__ __device__ inline pib_act_layout pib_act_layout_of(int wtype, int64_t K
     L.qsp_off = (L.bs8_off + nbs8 + 255) & ~(size_t) 255;
     L.qsl_off = (L.qsp_off + ((wtype == PIB_TYPE_Q4_K) ? qs : (size_t) b * ngr * 256) + 255) & ~(size_t) 255;
     L.sbs_off = (L.qsl_off + ((wtype == PIB_TYPE_Q4_K) ? 2 * qs : 0) + 255) & ~(size_t) 255;
-    L.total   = (L.sbs_off + ((wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / 32) * 2 : 0) + 255) & ~(size_t) 255;
+    L.q6p_off = (L.sbs_off + ((wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / 32) * 2 : 0) + 255) & ~(size_t) 255;
+    L.b16_off = (L.q6p_off + ((wtype == PIB_TYPE_Q4_K) ? qs : 0) + 255) & ~(size_t) 255;
+    L.total   = (L.b16_off + ((wtype == PIB_TYPE_Q4_K) ? (size_t) b * (K / PIB_QK_K) * 32 : 0) + 255) & ~(size_t) 255;
     return L;
 }

@@ -9,8 +9,9 @@
 //   qs   [256] int8   quants in element order           qsp [256] int8   the same in B-fragment order of mma.m16n8k32
 //   bs   [16]  int16  sums of 16                         bs8 [16]  int8   sub-block (32) sums split as 64 hi + lo: hi[8], lo[8]
 //   sbs  [8]   int16  sub-block sums                     qsl [64]  int2   B registers of the lane-exact kernel     d [1] float
+//   q6p  [256] int8   quants in the k16 B-fragment order of the Q6_K kernel      b16 [32] int8   sums of 16 split as 64 hi + lo: hi[16], lo[16]
 __device__ __forceinline__ void q8k_quantise_sb(const float (&v)[8], int lane, int8_t * qs, int8_t * qsp, int16_t * bs, int8_t * bs8,
-                                                int16_t * sbs, int2 * qsl, float * d) {
+                                                int16_t * sbs, int2 * qsl, float * d, int8_t * q6p = nullptr, int8_t * b16 = nullptr) {
     // first element (in index order) with the largest |x|: strict '>' scan, ties keep the lower index
     float amax = 0.0f, mx = 0.0f;
     int   idx  = 1 << 30;
@@ -43,9 +44,15 @@ __device__ __forceinline__ void q8k_quantise_sb(const float (&v)[8], int lane, i
     if (qs) *reinterpret_cast<int2 *>(qs + lane * 8) = packed;
     // fragment-order copy for the tensor-core GEMV: lane = 8c + 4h + t  ->  offset 64t + 16c + 8h
     if (qsp) *reinterpret_cast<int2 *>(qsp + (lane & 3) * 64 + (lane >> 3) * 16 + ((lane >> 2) & 1) * 8) = packed;
+    // lane l holds elements 8l .. 8l+7 = group l / 2, offsets 8 (l & 1) ..: quarters t = 2 (l & 1) and 2 (l & 1) + 1
+    if (q6p) {
+        *reinterpret_cast<int *>(q6p + (2 * (lane & 1)) * 64 + (lane >> 1) * 4)     = packed.x;
+        *reinterpret_cast<int *>(q6p + (2 * (lane & 1) + 1) * 64 + (lane >> 1) * 4) = packed.y;
+    }
     const int s8  = q[0] + q[1] + q[2] + q[3] + q[4] + q[5] + q[6] + q[7];
     const int s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
     if (bs && (lane & 1) == 0) bs[lane >> 1] = (int16_t) s16;
+    if (b16 && (lane & 1) == 0) { b16[lane >> 1] = (int8_t) (s16 >> 6); b16[16 + (lane >> 1)] = (int8_t) (s16 & 63); }
     const int s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);        // the 32-element sub-block sum (lanes 4j..4j+3)
     if ((lane & 3) == 0) {
         if (bs8) { bs8[lane >> 2] = (int8_t) (s32 >> 6); bs8[8 + (lane >> 2)] = (int8_t) (s32 & 63); }

@@ -201,6 +201,26 @@ def test_mul_mat_benchmark_shapes_vs_oracle(lib, oracle, wt, N, K):
     lib.L.pib_weight_free(h)
 
 
+def test_q6_k_lm_head_shape_vs_oracle(lib, oracle):
+    """the lm_head of a 70B Q4_K_M file (32000 x 8192, Q6_K) through the tensor-core kernel: sampled rows against the oracle, b = 1, 4, 16"""
+    rng = np.random.default_rng(6)
+    N, K = 32000, 8192
+    w = rng.integers(0, 256, (N, K // 256, 210), dtype=np.uint8)
+    w[:, :, 208:210] = (rng.uniform(0.5, 1.5, (N, K // 256)) * 0.001).astype(np.float16).view(np.uint8).reshape(N, K // 256, 2)
+    w = w.reshape(N, -1)
+    rows = np.array(sorted(set(range(32)) | set(range(N - 32, N)) | set(int(r) for r in rng.integers(0, N, 512))))
+    h = lib.weight_upload(op.TYPE_Q6_K, w, K)
+    wsub = np.ascontiguousarray(w[rows])
+    del w
+    for b in (1, 4, 16):
+        x = rng.standard_normal((b, K)).astype(np.float32)
+        ref = oracle.mul_mat(op.TYPE_Q6_K, wsub, x)
+        got = lib.mul_mat(h, x, N, 0)
+        assert np.isfinite(got).all()
+        assert np.abs(got[:, rows] - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max()), b
+    lib.L.pib_weight_free(h)
+
+
 @pytest.mark.parametrize("wt", [op.TYPE_Q4_0, op.TYPE_Q8_0])
 @pytest.mark.parametrize("b", [1, 7, 12])
 def test_mul_mat_width_not_a_multiple_of_256(lib, oracle, wt, b):
