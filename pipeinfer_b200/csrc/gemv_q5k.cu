@@ -10,6 +10,8 @@
 // positions 8p..8p+7): two sub-blocks' worth of bytes assembled with SIMD-in-a-word logic, dp4a.
 #include "pib_common.cuh"
 
+#include <stdlib.h>
+
 #define Q5_WARPS 4
 
 // 6-bit scale / min of sub-block j from the 12 packed bytes (reference get_scale_min_k4, ggml-quants.c:1446-1454)
@@ -80,10 +82,218 @@ static cudaError_t launch_q5(const pib_weight * w, const uint8_t * act, const pi
                       bs, y + (size_t) t0 * N, N, K, cancel);
 }
 
+// ---- tensor-core kernel (default when the matrix has its tiles) ----------------------------------------------------------------------
+// The Q4_K ring kernel (gemv_mma.cu) with a fifth bit: a record is the Q4_K record of the (16-row tile, super-block) -- 2048 bytes of
+// nibbles in mma.m16n8k32 A-fragment order + 16 row headers -- followed by 32 lanes x 16 bytes of fifth bits, 2816 bytes = the 16 x 176
+// of the reference blocks.  Lane (g, t) word c holds the bits of chunk c: in byte k, bit s belongs to value k of set
+// s = 4 sub + 2 lhalf + rowsel (sub: low / high-nibble sub-block 2c / 2c+1; lhalf: chunk positions 8t.. / 8t+4..; rowsel: row g / g+8),
+// so every A register is (nibbles & 0x0f0f0f0f) | ((word >> s) & 0x01010101) << 4.  Integer sums exact, fp32 terms per super-block.
+#define Q5T_BYTES  2816
+#define Q5T_WARPS  4
+#define Q5T_STAGES 4
+
+__device__ __forceinline__ void q5_mma_u8s8(int (&c)[4], int a0, int a1, int a2, int a3, int b0, int b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void q5_mma_s8s8(int (&c)[4], int a0, int a1, int a2, int a3, int b0, int b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// one thread per (record, lane)
+__global__ void q5k_tiles_kernel(const uint8_t * __restrict__ qs, const uint8_t * __restrict__ hdr, int64_t N, int64_t K, uint8_t * __restrict__ tiles) {
+    const int64_t nsb = K / 256, n_tiles = (N + 15) / 16;
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_tiles * nsb * 32) return;
+    const int     lane = (int) (i & 31), g = lane >> 2, t = lane & 3;
+    const int64_t rec = i >> 5, T = rec / nsb, S = rec % nsb;
+    uint8_t *     out = tiles + rec * Q5T_BYTES;
+    const int64_t r0 = T * 16 + g, r1 = r0 + 8;
+    const uint8_t * b0 = r0 < N ? qs + (r0 * nsb + S) * 160 : nullptr;
+    const uint8_t * b1 = r1 < N ? qs + (r1 * nsb + S) * 160 : nullptr;
+    uint32_t H[4];
+    for (int c = 0; c < 4; c++) {
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (b0) { const uint2 a = *reinterpret_cast<const uint2 *>(b0 + c * 32 + t * 8); v.x = a.x; v.y = a.y; }
+        if (b1) { const uint2 a = *reinterpret_cast<const uint2 *>(b1 + c * 32 + t * 8); v.z = a.x; v.w = a.y; }
+        *reinterpret_cast<uint4 *>(out + c * 512 + lane * 16) = v;
+        uint32_t h = 0;
+        for (int r = 0; r < 2; r++) {
+            const uint8_t * blk = r ? b1 : b0;
+            if (!blk) continue;
+            for (int lh = 0; lh < 2; lh++)
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t q = blk[128 + 8 * t + 4 * lh + k];                  // qh[l]: bit j = fifth bit of element 32 j + l
+                    h |= ((q >> (2 * c)) & 1u) << (8 * k + 2 * lh + r);
+                    h |= ((q >> (2 * c + 1)) & 1u) << (8 * k + 4 + 2 * lh + r);
+                }
+        }
+        H[c] = h;
+    }
+    *reinterpret_cast<uint4 *>(out + 2304 + lane * 16) = make_uint4(H[0], H[1], H[2], H[3]);
+    if (lane < 16) {
+        const int64_t r = T * 16 + lane;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (r < N) v = *reinterpret_cast<const uint4 *>(hdr + (r * nsb + S) * 16);     // rows beyond N: d = dmin = 0
+        *reinterpret_cast<uint4 *>(out + 2048 + lane * 16) = v;
+    }
+}
+
+int pib_weight_build_tiles_q5k(pib_weight * w) {
+    if (w->type != PIB_TYPE_Q5_K || w->tiles) return PIB_OK;
+    const int64_t nsb = w->K / 256, n_tiles = (w->N + 15) / 16;
+    const size_t  bytes = (size_t) n_tiles * nsb * Q5T_BYTES;
+    if (cudaMalloc(&w->tiles, bytes) != cudaSuccess) { cudaGetLastError(); pib_set_error("q5_K tiles: cudaMalloc of %zu bytes failed", bytes); w->tiles = nullptr; return PIB_ERR_NOMEM; }
+    w->tile_bytes = bytes;
+    const int64_t n = n_tiles * nsb * 32;
+    q5k_tiles_kernel<<<(unsigned) ((n + 127) / 128), 128>>>(w->qs, (const uint8_t *) w->d, w->N, w->K, w->tiles);
+    PIB_CHECK(cudaGetLastError());
+    return PIB_OK;
+}
+
+template <int NT>
+__global__ void __launch_bounds__(Q5T_WARPS * 32, NT == 1 ? 4 : 3)
+gemv_q5k_tc_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, int K, const int8_t * __restrict__ aqs, const float * __restrict__ ad,
+                   const int8_t * __restrict__ abs8, int b, float * __restrict__ y, const int * __restrict__ cancel) {
+    if (PIB_CANCELLED(cancel)) { pib_pdl_wait(); return; }
+    extern __shared__ __align__(16) uint8_t q5_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    const int T = blockIdx.x;
+    const uint8_t * tbase  = tiles + (size_t) T * nsb * Q5T_BYTES + lane * 16;
+    uint8_t *       ring   = q5_smem + warp * (Q5T_STAGES * Q5T_BYTES);
+    const uint32_t  ring_a = (uint32_t) __cvta_generic_to_shared(ring) + lane * 16;
+    int ps = warp;
+    auto issue = [&](int stage) {
+        if (ps < nsb) {
+            const uint8_t * src = tbase + (size_t) ps * Q5T_BYTES;
+            const uint32_t  dst = ring_a + stage * Q5T_BYTES;
+#pragma unroll
+            for (int c = 0; c < 4; c++) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + c * 512), "l"(src + c * 512) : "memory");
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 2304), "l"(src + 2304) : "memory");
+            if (lane < 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 2048), "l"(src + 2048) : "memory");
+            ps += Q5T_WARPS;
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#pragma unroll
+    for (int i = 0; i < Q5T_STAGES - 1; i++) issue(i);        // weights are immutable: before the wait on the producer of the activations
+
+    float acc[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; n++) { acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f; }
+    const int8_t * a_qs[NT];
+    const int8_t * a_b8[NT];
+    const float *  a_dx[NT][2];
+#pragma unroll
+    for (int n = 0; n < NT; n++) {
+        const int tok = min(n * 8 + g, b - 1);
+        a_qs[n] = aqs + (size_t) tok * K + t * 64;
+        a_b8[n] = abs8 + (size_t) tok * nsb * 16 + (t & 1) * 4;
+#pragma unroll
+        for (int e = 0; e < 2; e++) a_dx[n][e] = ad + (size_t) min(n * 8 + 2 * t + e, b - 1) * nsb;
+    }
+    pib_pdl_wait();
+    pib_pdl_trigger();
+    int stage = 0;
+    for (int s = warp; s < nsb; s += Q5T_WARPS) {
+        __syncwarp();
+        issue((stage + Q5T_STAGES - 1) % Q5T_STAGES);
+        asm volatile("cp.async.wait_group %0;" ::"n"(Q5T_STAGES - 1) : "memory");
+        __syncwarp();
+        const uint8_t * rs = ring + stage * Q5T_BYTES;
+        uint4 wq[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) wq[c] = *reinterpret_cast<const uint4 *>(rs + c * 512 + lane * 16);
+        const uint4 hb = *reinterpret_cast<const uint4 *>(rs + 2304 + lane * 16);
+        const uint4 h0 = *reinterpret_cast<const uint4 *>(rs + 2048 + g * 16), h1 = *reinterpret_cast<const uint4 *>(rs + 2048 + (g + 8) * 16);
+        // headers of rows g and g + 8: get_scale_min_k4 (ggml-quants.c:1446) for all eight sub-blocks at once
+        const float    d0 = pib_h2f((uint16_t) (h0.x & 0xffff)), dm0 = pib_h2f((uint16_t) (h0.x >> 16));
+        const float    d1 = pib_h2f((uint16_t) (h1.x & 0xffff)), dm1 = pib_h2f((uint16_t) (h1.x >> 16));
+        const uint32_t sc0[2] = { h0.y & 0x3f3f3f3fu, (h0.w & 0x0f0f0f0fu) | (((h0.y >> 6) & 0x03030303u) << 4) };
+        const uint32_t sc1[2] = { h1.y & 0x3f3f3f3fu, (h1.w & 0x0f0f0f0fu) | (((h1.y >> 6) & 0x03030303u) << 4) };
+        const uint32_t m0[2]  = { h0.z & 0x3f3f3f3fu, ((h0.w >> 4) & 0x0f0f0f0fu) | (((h0.z >> 6) & 0x03030303u) << 4) };
+        const uint32_t m1[2]  = { h1.z & 0x3f3f3f3fu, ((h1.w >> 4) & 0x0f0f0f0fu) | (((h1.z >> 6) & 0x03030303u) << 4) };
+        const uint32_t hw[4]  = { hb.x, hb.y, hb.z, hb.w };
+#pragma unroll
+        for (int n = 0; n < NT; n++) {
+            const int4 * ap = reinterpret_cast<const int4 *>(a_qs[n] + (size_t) s * 256);
+            const int *  bp = reinterpret_cast<const int *>(a_b8[n] + (size_t) s * 16);
+            const int    amh = __ldg(bp), aml = __ldg(bp + 2);
+            const float  dx0 = __ldg(a_dx[n][0] + s), dx1 = __ldg(a_dx[n][1] + s);
+            int sum[4] = { 0, 0, 0, 0 };
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const int4     aq = __ldg(ap + c);
+                const uint32_t wx = wq[c].x, wy = wq[c].y, wz = wq[c].z, ww = wq[c].w, H = hw[c];
+                int c_lo[4] = { 0, 0, 0, 0 }, c_hi[4] = { 0, 0, 0, 0 };
+                q5_mma_u8s8(c_lo, (int) ((wx & 0x0F0F0F0Fu) | ((H << 4) & 0x10101010u)), (int) ((wz & 0x0F0F0F0Fu) | ((H << 3) & 0x10101010u)),
+                            (int) ((wy & 0x0F0F0F0Fu) | ((H << 2) & 0x10101010u)), (int) ((ww & 0x0F0F0F0Fu) | ((H << 1) & 0x10101010u)), aq.x, aq.y);
+                q5_mma_u8s8(c_hi, (int) (((wx >> 4) & 0x0F0F0F0Fu) | (H & 0x10101010u)), (int) (((wz >> 4) & 0x0F0F0F0Fu) | ((H >> 1) & 0x10101010u)),
+                            (int) (((wy >> 4) & 0x0F0F0F0Fu) | ((H >> 2) & 0x10101010u)), (int) (((ww >> 4) & 0x0F0F0F0Fu) | ((H >> 3) & 0x10101010u)), aq.z, aq.w);
+                const int j0 = 2 * c, j1 = 2 * c + 1;
+                const int s00 = (int) ((sc0[j0 >> 2] >> (8 * (j0 & 3))) & 0xff), s01 = (int) ((sc0[j1 >> 2] >> (8 * (j1 & 3))) & 0xff);
+                const int s10 = (int) ((sc1[j0 >> 2] >> (8 * (j0 & 3))) & 0xff), s11 = (int) ((sc1[j1 >> 2] >> (8 * (j1 & 3))) & 0xff);
+                sum[0] += s00 * c_lo[0] + s01 * c_hi[0]; sum[1] += s00 * c_lo[1] + s01 * c_hi[1];
+                sum[2] += s10 * c_lo[2] + s11 * c_hi[2]; sum[3] += s10 * c_lo[3] + s11 * c_hi[3];
+            }
+            // the min term: sum_j m_j * bsum_j with the sub-block sums split as 64 hi + lo (bs8 plane), mins as the A operand
+            const int am0 = t == 0 ? (int) m0[0] : t == 1 ? (int) m0[1] : 0, am1 = t == 0 ? (int) m1[0] : t == 1 ? (int) m1[1] : 0;
+            const int bmh = t < 2 ? amh : 0, bml = t < 2 ? aml : 0;
+            int c_mh[4] = { 0, 0, 0, 0 }, c_ml[4] = { 0, 0, 0, 0 };
+            q5_mma_s8s8(c_mh, am0, am1, 0, 0, bmh, 0);
+            q5_mma_s8s8(c_ml, am0, am1, 0, 0, bml, 0);
+            acc[n][0] = fmaf(__fmul_rn(dx0, d0), (float) sum[0], acc[n][0]);  acc[n][0] = fmaf(__fmul_rn(-dx0, dm0), (float) (64 * c_mh[0] + c_ml[0]), acc[n][0]);
+            acc[n][1] = fmaf(__fmul_rn(dx1, d0), (float) sum[1], acc[n][1]);  acc[n][1] = fmaf(__fmul_rn(-dx1, dm0), (float) (64 * c_mh[1] + c_ml[1]), acc[n][1]);
+            acc[n][2] = fmaf(__fmul_rn(dx0, d1), (float) sum[2], acc[n][2]);  acc[n][2] = fmaf(__fmul_rn(-dx0, dm1), (float) (64 * c_mh[2] + c_ml[2]), acc[n][2]);
+            acc[n][3] = fmaf(__fmul_rn(dx1, d1), (float) sum[3], acc[n][3]);  acc[n][3] = fmaf(__fmul_rn(-dx1, dm1), (float) (64 * c_mh[3] + c_ml[3]), acc[n][3]);
+        }
+        stage = stage + 1 == Q5T_STAGES ? 0 : stage + 1;
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();                                            // the rings are done with: their memory becomes the reduction buffer
+    float (*red)[NT * 8][16] = reinterpret_cast<float (*)[NT * 8][16]>(q5_smem);
+#pragma unroll
+    for (int n = 0; n < NT; n++)
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            red[warp][n * 8 + 2 * t + e][g]     = acc[n][e];
+            red[warp][n * 8 + 2 * t + e][g + 8] = acc[n][2 + e];
+        }
+    __syncthreads();
+    for (int i = threadIdx.x; i < NT * 8 * 16; i += Q5T_WARPS * 32) {
+        const int tok = i / 16, r = i % 16, row = T * 16 + r;
+        if (tok < b && row < N) {
+            float v = red[0][tok][r];
+#pragma unroll
+            for (int w2 = 1; w2 < Q5T_WARPS; w2++) v += red[w2][tok][r];
+            y[(size_t) tok * N + row] = v;
+        }
+    }
+}
+
+template <int NT>
+static int launch_q5_tc(const pib_weight * w, const uint8_t * act, const pib_act_layout & L, int b, float * y, const int * cancel, cudaStream_t st) {
+    const size_t smem = (size_t) Q5T_WARPS * Q5T_STAGES * Q5T_BYTES;
+    static bool configured = false;
+    if (!configured) {
+        PIB_CHECK(cudaFuncSetAttribute(gemv_q5k_tc_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        PIB_CHECK(cudaFuncSetAttribute(gemv_q5k_tc_kernel<NT>, cudaFuncAttributePreferredSharedMemoryCarveout, (int) cudaSharedmemCarveoutMaxShared));
+        configured = true;
+    }
+    const int nsb = (int) (w->K / 256), n_tiles = (int) ((w->N + 15) / 16);
+    PIB_CHECK(pib_launch(gemv_q5k_tc_kernel<NT>, dim3(n_tiles), dim3(Q5T_WARPS * 32), smem, st, w->tiles, nsb, (int) w->N, (int) w->K,
+                         (const int8_t *) (act + L.qsp_off), (const float *) (act + L.d_off), (const int8_t *) (act + L.bs8_off), b, y, cancel));
+    return PIB_OK;
+}
+
 int pib_gemv_q5k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st) {
-    if (!w || w->type != PIB_TYPE_Q5_K || !w->qs) { pib_set_error("pib_gemv: not a resident Q5_K matrix"); return PIB_ERR_UNSUPP; }
+    if (!w || w->type != PIB_TYPE_Q5_K || (!w->qs && !w->tiles)) { pib_set_error("pib_gemv: not a resident Q5_K matrix"); return PIB_ERR_UNSUPP; }
     const pib_act_layout L   = pib_act_layout_of(PIB_TYPE_Q4_K, w->K, b);          // Q8_K family activations
     const uint8_t *      act = (const uint8_t *) act_dev;
+    static const int use_tc = getenv("PIB_Q5K_TC") ? atoi(getenv("PIB_Q5K_TC")) : 1;
+    if (w->tiles && (use_tc || !w->qs) && b <= PIB_MAX_BATCH)
+        return b <= 8 ? launch_q5_tc<1>(w, act, L, b, y_dev, cancel, st) : launch_q5_tc<2>(w, act, L, b, y_dev, cancel, st);
     for (int t0 = 0; t0 < b; t0 += 8) {
         const int   nb = b - t0 < 8 ? b - t0 : 8;
         cudaError_t e  = cudaSuccess;
