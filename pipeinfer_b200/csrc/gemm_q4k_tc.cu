@@ -21,6 +21,8 @@
 
 #include <map>
 #include <mutex>
+#include <utility>
+#include <stdlib.h>
 
 #include "pib_common.cuh"
 
@@ -88,7 +90,8 @@ __global__ void tg_xhat_kernel(const int8_t * __restrict__ qs, const float * __r
 // NB = tokens per CTA tile (UMMA N): 32 .. 256, a multiple of 16.
 template <int NB>
 __global__ void __launch_bounds__(TG_THREADS, 2)
-gemm_q4k_tc_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, const __grid_constant__ CUtensorMap xmap, int b, float * __restrict__ y) {
+gemm_q4k_tc_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, const __grid_constant__ CUtensorMap xmap, int b, float * __restrict__ y,
+                   float * __restrict__ partial) {
     extern __shared__ __align__(1024) uint8_t tg_dsm[];
     constexpr int A_BYTES = TG_BM * TG_BK * 2, B_BYTES = NB * TG_BK * 2;
     constexpr int TG_STAGES = NB <= 64 ? 4 : (NB <= 128 ? 3 : 2);      // two CTAs per SM in every configuration
@@ -99,8 +102,12 @@ gemm_q4k_tc_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, const __g
     uint32_t * tmem_slot = reinterpret_cast<uint32_t *>(bar + 3 * TG_STAGES + 1);
     const uint32_t bar_a = tg_smem(bar), bar_b = bar_a + TG_STAGES * 8, bar_e = bar_a + 2 * TG_STAGES * 8, bar_t = bar_a + 3 * TG_STAGES * 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_ksteps = nsb * 4;
+    // k split (gridDim.y > 1: matrices with too few 128-row tiles to fill the machine): this CTA takes super-blocks [sb_lo, sb_hi) and
+    // writes its partial sums to partial[split][b][N]; tg_reduce_kernel adds the splits in order
+    const int sb_lo = (int) ((long long) nsb * blockIdx.y / gridDim.y), sb_hi = (int) ((long long) nsb * (blockIdx.y + 1) / gridDim.y);
+    const int n_ksteps = (sb_hi - sb_lo) * 4;
     const int row0 = blockIdx.x * TG_BM;
+    if (gridDim.y > 1) y = partial + (size_t) blockIdx.y * b * N;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < TG_STAGES; s++) { tg_mbar_init(bar_a + s * 8, TG_PWARPS); tg_mbar_init(bar_b + s * 8, 1); tg_mbar_init(bar_e + s * 8, 1); }
@@ -123,7 +130,7 @@ gemm_q4k_tc_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, const __g
                 const int s = kt % TG_STAGES;
                 if (kt >= TG_STAGES) tg_mbar_wait(bar_e + s * 8, ((kt / TG_STAGES) - 1) & 1);
                 tg_mbar_expect_tx(bar_b + s * 8, B_BYTES);
-                tg_tma_2d(tg_smem(sB + s * B_BYTES), &xmap, bar_b + s * 8, kt * TG_BK, 0);
+                tg_tma_2d(tg_smem(sB + s * B_BYTES), &xmap, bar_b + s * 8, (sb_lo * 4 + kt) * TG_BK, 0);
             }
         }
     } else if (warp == 1) {
@@ -151,7 +158,7 @@ gemm_q4k_tc_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, const __g
         const int r   = p >> 1, th = p & 1;
         const int T   = (row0 >> 4) + (r >> 4), rr = r & 15, g = rr & 7, hf = rr >> 3;
         const bool row_ok = row0 + r < N;
-        const uint8_t * rec0 = tiles + (size_t) T * nsb * TG_TILE_BYTES;
+        const uint8_t * rec0 = tiles + ((size_t) T * nsb + sb_lo) * TG_TILE_BYTES;
         // A row's bytes of one record (4 chunks x 32 bytes, in 8-byte pieces of the fragment layout) and its header are fetched one
         // whole record (4 k-steps) ahead into registers, and the lines of the record after that are asked into L2: the weight stream
         // is a chain of DRAM latencies otherwise (one k-step of arithmetic hides a tenth of one).
@@ -172,7 +179,7 @@ gemm_q4k_tc_kernel(const uint8_t * __restrict__ tiles, int nsb, int N, const __g
         };
         const int n_rec = n_ksteps >> 2;
         // L2 prefetch: the CTA's 8 tiles of a record step are 8 x 18 lines of 128 bytes; thread p < 144 owns line p % 18 of tile p / 18
-        const uint8_t * pf_base = (p < 144 && row0 + (p / 18) * 16 < N) ? tiles + (size_t) ((row0 >> 4) + p / 18) * nsb * TG_TILE_BYTES + (p % 18) * 128 : nullptr;
+        const uint8_t * pf_base = (p < 144 && row0 + (p / 18) * 16 < N) ? tiles + ((size_t) ((row0 >> 4) + p / 18) * nsb + sb_lo) * TG_TILE_BYTES + (p % 18) * 128 : nullptr;
         fetch_rec(0, cur, hcur);
         for (int ri = 0; ri < n_rec; ri++) {
             if (ri + 1 < n_rec) fetch_rec(ri + 1, nxt, hnxt);
@@ -267,6 +274,37 @@ static tg_encode_fn tg_encode() {
     return fn;
 }
 
+// y = sum over the k splits, in split order (deterministic)
+__global__ void tg_reduce_kernel(const float4 * __restrict__ partial, float4 * __restrict__ y, size_t n4, int nsplit) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    float4 v = partial[i];
+    for (int sp = 1; sp < nsplit; sp++) { const float4 o = partial[(size_t) sp * n4 + i]; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+    y[i] = v;
+}
+
+// partial sums of the k split: one buffer per (device, stream), allocated on first use (prompt passes are not captured in graphs)
+#define TG_PARTIAL_BYTES ((size_t) 64 << 20)
+static float * tg_partial(cudaStream_t st) {
+    static std::map<std::pair<int, cudaStream_t>, float *> bufs;
+    static std::mutex mu;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lock(mu);
+    float *& p = bufs[std::make_pair(dev, st)];
+    if (!p && cudaMalloc(&p, TG_PARTIAL_BYTES) != cudaSuccess) { cudaGetLastError(); p = nullptr; }
+    return p;
+}
+// splits for a matrix of N rows: fill the 2 x SMs CTA slots once; every split keeps at least four super-blocks
+static int tg_ksplit(int64_t N, int64_t K, int b) {
+    static const int env = getenv("PIB_GEMM_KSPLIT") ? atoi(getenv("PIB_GEMM_KSPLIT")) : 0;
+    const int ctas = (int) ((N + TG_BM - 1) / TG_BM), nsb = (int) (K / 256);
+    int s = env > 0 ? env : (2 * pib_num_sms()) / ctas;
+    if (s > 4) s = 4;
+    while (s > 1 && (nsb / s < 4 || (size_t) s * b * N * sizeof(float) > TG_PARTIAL_BYTES || (N * b) % 4)) s--;
+    return s < 1 ? 1 : s;
+}
+
 static int tg_nb_of(int b) { return b <= 32 ? 32 : b <= 64 ? 64 : b <= 128 ? 128 : 256; }
 size_t pib_gemm_xhat_bytes(int64_t K, int b) { return (size_t) tg_nb_of(b) * K * sizeof(__half); }
 
@@ -287,8 +325,16 @@ static int tg_launch(const pib_weight * w, const __half * xh, int b, float * y, 
     static bool configured = false;
     if (!configured) { PIB_CHECK(cudaFuncSetAttribute(gemm_q4k_tc_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem)); configured = true; }
     const int grid = (int) ((w->N + TG_BM - 1) / TG_BM);
-    gemm_q4k_tc_kernel<NB><<<grid, TG_THREADS, smem, st>>>(w->tiles, (int) (w->K / 256), (int) w->N, map, b, y);
+    int       ks   = tg_ksplit(w->N, w->K, b);
+    float *   part = ks > 1 ? tg_partial(st) : nullptr;
+    if (ks > 1 && !part) ks = 1;
+    gemm_q4k_tc_kernel<NB><<<dim3(grid, ks), TG_THREADS, smem, st>>>(w->tiles, (int) (w->K / 256), (int) w->N, map, b, y, part);
     PIB_CHECK(cudaGetLastError());
+    if (ks > 1) {
+        const size_t n4 = (size_t) b * w->N / 4;
+        tg_reduce_kernel<<<(unsigned) ((n4 + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float4 *>(part), reinterpret_cast<float4 *>(y), n4, ks);
+        PIB_CHECK(cudaGetLastError());
+    }
     return PIB_OK;
 }
 
