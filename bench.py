@@ -480,7 +480,7 @@ def main():
     if hops is not None:
         line["nvlink_hops"] = {"per_rank_over_timed_steps": hops,
                                "formula": "n_tokens * n_embd * 4 B of fp32 activations per hop (%d B per token), stored by the sending stage's last kernel into the "
-                                          "next stage's memory; 72 B per verification batch (device-side acceptance walk) back to the head" % (E * 4),
+                                          "next stage's memory; 80 B per verification batch (device-side acceptance walk) back to the head" % (E * 4),
                                "nvlink_tx_bytes_counter": "not exposed on this driver: NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX returns NVML_ERROR_NOT_SUPPORTED and "
                                                           "`nvidia-smi nvlink -gt d` prints N/A (tools/nvlink_probe.py); the byte counts above are counted at the "
                                                           "point where each transfer is enqueued" if all(h["nvlink_tx_bytes_counter"] is None for h in hops) else "KiB counters read around the timed steps"}

@@ -553,7 +553,7 @@ static int hop_send(pib_context * c, const float * x, int n_tokens, const int * 
     P.hop_bytes += n * 4; P.hop_msgs++;
     return PIB_OK;
 }
-// what comes back from the last stage: the result of the device-side acceptance walk when the batch carried a table (72 bytes),
+// what comes back from the last stage: the result of the device-side acceptance walk when the batch carried a table (80 bytes),
 // else the sampled rows (96 bytes per row).  Both ends know which: the table travels in the descriptor.
 int pib_pipe_send_results(pib_context * c, pib_run & run) {
     const size_t bytes = run.has_walk ? sizeof(pib_accept_result) : sizeof(pib_row_result) * (size_t) run.n_tokens;

@@ -76,7 +76,9 @@ def main():
         assert tgt.serve() == 1
         hop_bytes, hop_msgs, back = pipeline.traffic()
         if rank == world - 1:
-            assert hop_msgs == 0 and back > 0 and (back - 5 * TGT[5] * 4) % 96 == 0          # result rows + the five fetched logits rows
+            # 80-byte acceptance records (verification batches: the walk runs on this stage), 96-byte top-8 rows (batches without a
+            # table) and the five fetched logits rows
+            assert hop_msgs == 0 and back > 5 * TGT[5] * 4 and (back - 5 * TGT[5] * 4) % 16 == 0, (hop_msgs, back)
     pipeline.close_pipeline()
     dist.destroy_process_group()
     print("PIPELINE_GPU_OK rank %d" % rank)
