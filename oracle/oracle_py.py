@@ -14,10 +14,11 @@ REF_DIR = os.path.join(HERE, "_ref")
 
 TYPE_F32, TYPE_Q4_0, TYPE_Q8_0, TYPE_Q4_K = 0, 2, 8, 12
 TYPE_Q5_K = 13
+TYPE_Q3_K = 11          # only matmul / dequantise (Q3_K_M files: the type of the authors' 70B target, scripts/dolphin_tinyllama_8_nodes.sh)
 TYPE_Q6_K = 14          # only matmul / dequantise (Q4_K_M files keep output.weight and some attn_v / ffn_down in it)
 TYPE_NAMES = {"q4_0": TYPE_Q4_0, "q8_0": TYPE_Q8_0, "q4_k": TYPE_Q4_K}
-BLOCK = {TYPE_Q4_0: (32, 18), TYPE_Q8_0: (32, 34), TYPE_Q4_K: (256, 144), TYPE_Q5_K: (256, 176), TYPE_Q6_K: (256, 210)}   # (elements, bytes) per block
-ACT_BLOCK = {TYPE_Q4_0: (32, 34), TYPE_Q8_0: (32, 34), TYPE_Q4_K: (256, 292), TYPE_Q5_K: (256, 292), TYPE_Q6_K: (256, 292)}  # activation format per weight type
+BLOCK = {TYPE_Q4_0: (32, 18), TYPE_Q8_0: (32, 34), TYPE_Q4_K: (256, 144), TYPE_Q5_K: (256, 176), TYPE_Q6_K: (256, 210), TYPE_Q3_K: (256, 110)}   # (elements, bytes) per block
+ACT_BLOCK = {TYPE_Q4_0: (32, 34), TYPE_Q8_0: (32, 34), TYPE_Q4_K: (256, 292), TYPE_Q5_K: (256, 292), TYPE_Q6_K: (256, 292), TYPE_Q3_K: (256, 292)}  # activation format per weight type
 
 
 def build(ref=True):
@@ -109,7 +110,7 @@ class Oracle:
         be, bb = ACT_BLOCK[wtype]
         rows = x.reshape(-1, K)
         out = np.zeros((rows.shape[0], K // be * bb), dtype=np.uint8)
-        fn = self.L.po_quantize_row_q8_K if wtype in (TYPE_Q4_K, TYPE_Q5_K, TYPE_Q6_K) else self.L.po_quantize_row_q8_0
+        fn = self.L.po_quantize_row_q8_K if wtype in (TYPE_Q3_K, TYPE_Q4_K, TYPE_Q5_K, TYPE_Q6_K) else self.L.po_quantize_row_q8_0
         for r in range(rows.shape[0]):
             fn(_ptr(rows[r]), _ptr(out[r]), C.c_int(K))
         return out.reshape(x.shape[:-1] + (out.shape[1],))
@@ -120,7 +121,7 @@ class Oracle:
         N = w.shape[0]
         out = np.empty((N, K), dtype=np.float32)
         fn = {TYPE_Q4_0: self.L.po_dequantize_row_q4_0, TYPE_Q8_0: self.L.po_dequantize_row_q8_0,
-              TYPE_Q4_K: self.L.po_dequantize_row_q4_K, TYPE_Q5_K: self.L.po_dequantize_row_q5_K, TYPE_Q6_K: self.L.po_dequantize_row_q6_K}[wtype]
+              TYPE_Q4_K: self.L.po_dequantize_row_q4_K, TYPE_Q5_K: self.L.po_dequantize_row_q5_K, TYPE_Q6_K: self.L.po_dequantize_row_q6_K, TYPE_Q3_K: self.L.po_dequantize_row_q3_K}[wtype]
         for r in range(N):
             fn(_ptr(w[r]), _ptr(out[r]), C.c_int(K))
         return out
@@ -164,7 +165,7 @@ class Ref:
         be, bb = BLOCK[wtype]
         out = np.zeros((N, K // be * bb), dtype=np.uint8)
         fn = {TYPE_Q4_0: self.L.quantize_row_q4_0_reference, TYPE_Q8_0: self.L.quantize_row_q8_0_reference,
-              TYPE_Q4_K: self.L.quantize_row_q4_K_reference, TYPE_Q5_K: self.L.quantize_row_q5_K_reference, TYPE_Q6_K: self.L.quantize_row_q6_K_reference}[wtype]
+              TYPE_Q4_K: self.L.quantize_row_q4_K_reference, TYPE_Q5_K: self.L.quantize_row_q5_K_reference, TYPE_Q6_K: self.L.quantize_row_q6_K_reference, TYPE_Q3_K: self.L.quantize_row_q3_K_reference}[wtype]
         for r in range(N):
             fn(_ptr(w[r]), _ptr(out[r]), C.c_int(K))
         return out
@@ -175,7 +176,7 @@ class Ref:
         be, bb = ACT_BLOCK[wtype]
         rows = x.reshape(-1, K)
         out = np.zeros((rows.shape[0], K // be * bb), dtype=np.uint8)
-        fn = self.L.quantize_row_q8_K if wtype in (TYPE_Q4_K, TYPE_Q5_K, TYPE_Q6_K) else self.L.quantize_row_q8_0
+        fn = self.L.quantize_row_q8_K if wtype in (TYPE_Q3_K, TYPE_Q4_K, TYPE_Q5_K, TYPE_Q6_K) else self.L.quantize_row_q8_0
         for r in range(rows.shape[0]):
             fn(_ptr(rows[r]), _ptr(out[r]), C.c_int(K))
         return out.reshape(x.shape[:-1] + (out.shape[1],))
@@ -185,7 +186,7 @@ class Ref:
         N = w.shape[0]
         out = np.empty((N, K), dtype=np.float32)
         fn = {TYPE_Q4_0: self.L.dequantize_row_q4_0, TYPE_Q8_0: self.L.dequantize_row_q8_0,
-              TYPE_Q4_K: self.L.dequantize_row_q4_K, TYPE_Q5_K: self.L.dequantize_row_q5_K, TYPE_Q6_K: self.L.dequantize_row_q6_K}[wtype]
+              TYPE_Q4_K: self.L.dequantize_row_q4_K, TYPE_Q5_K: self.L.dequantize_row_q5_K, TYPE_Q6_K: self.L.dequantize_row_q6_K, TYPE_Q3_K: self.L.dequantize_row_q3_K}[wtype]
         for r in range(N):
             fn(_ptr(w[r]), _ptr(out[r]), C.c_int(K))
         return out
@@ -193,7 +194,7 @@ class Ref:
     def vec_dot(self, wtype, wrow, arow, K):
         s = C.c_float(0)
         fn = {TYPE_Q4_0: self.L.ggml_vec_dot_q4_0_q8_0, TYPE_Q8_0: self.L.ggml_vec_dot_q8_0_q8_0,
-              TYPE_Q4_K: self.L.ggml_vec_dot_q4_K_q8_K, TYPE_Q5_K: self.L.ggml_vec_dot_q5_K_q8_K, TYPE_Q6_K: self.L.ggml_vec_dot_q6_K_q8_K}[wtype]
+              TYPE_Q4_K: self.L.ggml_vec_dot_q4_K_q8_K, TYPE_Q5_K: self.L.ggml_vec_dot_q5_K_q8_K, TYPE_Q6_K: self.L.ggml_vec_dot_q6_K_q8_K, TYPE_Q3_K: self.L.ggml_vec_dot_q3_K_q8_K}[wtype]
         fn(C.c_int(K), C.byref(s), _ptr(wrow), _ptr(arow))
         return s.value
 

@@ -57,6 +57,7 @@ typedef struct { po_fp16 d; int8_t qs[QK]; } blk_q8_0;                          
 typedef struct { po_fp16 d; po_fp16 dmin; uint8_t scales[12]; uint8_t qs[QK_K / 2]; } blk_q4_K; /* 144 B */
 typedef struct { float d; int8_t qs[QK_K]; int16_t bsums[QK_K / 16]; } blk_q8_K;              /* 292 B */
 typedef struct { po_fp16 d; po_fp16 dmin; uint8_t scales[12]; uint8_t qh[QK_K / 8]; uint8_t qs[QK_K / 2]; } blk_q5_K;   /* 176 B, ggml-quants.h:138-145 */
+typedef struct { uint8_t hmask[QK_K / 8]; uint8_t qs[QK_K / 4]; uint8_t scales[12]; po_fp16 d; } blk_q3_K;                       /* 110 B, ggml-quants.h:95-101 */
 typedef struct { uint8_t ql[QK_K / 2]; uint8_t qh[QK_K / 4]; int8_t scales[QK_K / 16]; po_fp16 d; } blk_q6_K;   /* 210 B, ggml-quants.h:152-157 */
 #pragma pack(pop)
 
@@ -338,6 +339,83 @@ void po_vec_dot_q5_K_q8_K(int n, float * s, const void * vx, const void * vy) {
     *s = hsum8(acc) + summs;
 }
 
+/* the sixteen 6-bit scales of a Q3_K super-block (ggml-quants.c:1720-1730, :4459-4465), minus 32 */
+static void q3k_scales(const uint8_t * packed, int8_t * out) {
+    const uint32_t kmask1 = 0x03030303, kmask2 = 0x0f0f0f0f;
+    uint32_t aux[4];
+    memcpy(aux, packed, 12);
+    const uint32_t tmp = aux[2];
+    aux[2] = ((aux[0] >> 4) & kmask2) | (((tmp >> 4) & kmask1) << 4);
+    aux[3] = ((aux[1] >> 4) & kmask2) | (((tmp >> 6) & kmask1) << 4);
+    aux[0] = (aux[0] & kmask2) | (((tmp >> 0) & kmask1) << 4);
+    aux[1] = (aux[1] & kmask2) | (((tmp >> 2) & kmask1) << 4);
+    for (int i = 0; i < 16; i++) out[i] = (int8_t) (((const uint8_t *) aux)[i] - 32);
+}
+
+/* ggml-quants.c:1711-1758 */
+void po_dequantize_row_q3_K(const void * vx, float * y, int k) {
+    const blk_q3_K * x = (const blk_q3_K *) vx;
+    const int nb = k / QK_K;
+    for (int i = 0; i < nb; i++) {
+        const float     d_all = po_fp16_to_fp32(x[i].d);
+        const uint8_t * q  = x[i].qs;
+        const uint8_t * hm = x[i].hmask;
+        uint8_t m = 1;
+        int8_t  scales[16];
+        q3k_scales(x[i].scales, scales);
+        int is = 0;
+        for (int n = 0; n < QK_K; n += 128) {
+            int shift = 0;
+            for (int j = 0; j < 4; ++j) {
+                float dl = d_all * scales[is++];
+                for (int l = 0; l < 16; ++l) *y++ = dl * ((int8_t) ((q[l + 0] >> shift) & 3) - ((hm[l + 0] & m) ? 0 : 4));
+                dl = d_all * scales[is++];
+                for (int l = 0; l < 16; ++l) *y++ = dl * ((int8_t) ((q[l + 16] >> shift) & 3) - ((hm[l + 16] & m) ? 0 : 4));
+                shift += 2;
+                m <<= 1;
+            }
+            q += 32;
+        }
+    }
+}
+
+/* ggml-quants.c:4443-4546 (AVX2).  Per super-block d = y.d * fp16(x.d).  The 256 values are 2 halves x 4 groups of 32 (group g of half
+ * j: bits 2g, 2g+1 of the 32 qs bytes of the half, bit 4j + g of the hmask bytes, y[128 j + 32 g ..]); value = low2 - (high bit ? 0 : 4).
+ * maddubs gives int16 pair sums (no saturation), madd with the group's two scales - 32 (first 16 values / last 16) gives 8 int32
+ * lanes, lane m = elements 4m..4m+3 of the group; the lanes add up over the 8 groups, then acc = fma(d, float(sumi), acc) and
+ * hsum_float_8. */
+void po_vec_dot_q3_K_q8_K(int n, float * s, const void * vx, const void * vy) {
+    const blk_q3_K * x  = (const blk_q3_K *) vx;
+    const blk_q8_K * y  = (const blk_q8_K *) vy;
+    const int        nb = n / QK_K;
+    float acc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    for (int i = 0; i < nb; ++i) {
+        const float     d  = y[i].d * po_fp16_to_fp32(x[i].d);
+        const uint8_t * q3 = x[i].qs;
+        const uint8_t * hm = x[i].hmask;
+        const int8_t *  q8 = y[i].qs;
+        int8_t scales[16];
+        q3k_scales(x[i].scales, scales);
+        int32_t sumi[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+        for (int j = 0; j < QK_K / 128; ++j) {
+            for (int g = 0; g < 4; g++) {
+                for (int m = 0; m < 8; m++) {
+                    int dot = 0;
+                    for (int t = 0; t < 4; t++) {
+                        const int l = 4 * m + t;
+                        const int q = ((q3[l] >> (2 * g)) & 3) - ((hm[l] & (1 << (4 * j + g))) ? 0 : 4);
+                        dot += q * (int) q8[32 * g + l];
+                    }
+                    sumi[m] += (int) scales[8 * j + 2 * g + (m >= 4)] * dot;
+                }
+            }
+            q3 += 32; q8 += 128;
+        }
+        for (int l = 0; l < 8; l++) acc[l] = fmaf(d, (float) sumi[l], acc[l]);
+    }
+    *s = hsum8(acc);
+}
+
 /* ggml-quants.c:1994-2040 */
 void po_dequantize_row_q6_K(const void * vx, float * y, int k) {
     const blk_q6_K * x = (const blk_q6_K *) vx;
@@ -425,6 +503,7 @@ size_t po_row_size(int type, int64_t k) {
         case PO_TYPE_Q4_0: return (size_t) (k / QK) * sizeof(blk_q4_0);
         case PO_TYPE_Q8_0: return (size_t) (k / QK) * sizeof(blk_q8_0);
         case PO_TYPE_Q4_K: return (size_t) (k / QK_K) * sizeof(blk_q4_K);
+        case PO_TYPE_Q3_K: return (size_t) (k / QK_K) * sizeof(blk_q3_K);
         case PO_TYPE_Q5_K: return (size_t) (k / QK_K) * sizeof(blk_q5_K);
         case PO_TYPE_Q6_K: return (size_t) (k / QK_K) * sizeof(blk_q6_K);
         case PO_TYPE_F32:  return (size_t) k * 4;
@@ -436,7 +515,7 @@ size_t po_row_size(int type, int64_t k) {
  * weights, Q8_K for Q4_K: ggml.c:455-465, 541-548), then dst[i1][ir0] = vec_dot(ne00, src0 row ir0, src1 row i1). */
 void po_mul_mat(int type, const void * w, int64_t N, int64_t K, const float * x, int b, float * y) {
     const size_t wrow = po_row_size(type, K);
-    const int    kq   = type == PO_TYPE_Q4_K || type == PO_TYPE_Q5_K || type == PO_TYPE_Q6_K;             /* K-quants multiply with Q8_K activations */
+    const int    kq   = type == PO_TYPE_Q3_K || type == PO_TYPE_Q4_K || type == PO_TYPE_Q5_K || type == PO_TYPE_Q6_K;             /* K-quants multiply with Q8_K activations */
     const size_t arow = kq ? (size_t) (K / QK_K) * sizeof(blk_q8_K) : (size_t) (K / QK) * sizeof(blk_q8_0);
     char * act = (char *) malloc(arow * (size_t) b);
     for (int t = 0; t < b; t++) {
@@ -451,6 +530,7 @@ void po_mul_mat(int type, const void * w, int64_t N, int64_t K, const float * x,
                 case PO_TYPE_Q4_0: po_vec_dot_q4_0_q8_0((int) K, o, wr, act + arow * t); break;
                 case PO_TYPE_Q8_0: po_vec_dot_q8_0_q8_0((int) K, o, wr, act + arow * t); break;
                 case PO_TYPE_Q4_K: po_vec_dot_q4_K_q8_K((int) K, o, wr, act + arow * t); break;
+                case PO_TYPE_Q3_K: po_vec_dot_q3_K_q8_K((int) K, o, wr, act + arow * t); break;
                 case PO_TYPE_Q5_K: po_vec_dot_q5_K_q8_K((int) K, o, wr, act + arow * t); break;
                 case PO_TYPE_Q6_K: po_vec_dot_q6_K_q8_K((int) K, o, wr, act + arow * t); break;
             }
@@ -700,6 +780,7 @@ static void dequant_row(int type, const void * w, int64_t row, int64_t k, float 
         case PO_TYPE_Q4_0: po_dequantize_row_q4_0(p, out, (int) k); break;
         case PO_TYPE_Q8_0: po_dequantize_row_q8_0(p, out, (int) k); break;
         case PO_TYPE_Q4_K: po_dequantize_row_q4_K(p, out, (int) k); break;
+        case PO_TYPE_Q3_K: po_dequantize_row_q3_K(p, out, (int) k); break;
         case PO_TYPE_Q5_K: po_dequantize_row_q5_K(p, out, (int) k); break;
         case PO_TYPE_Q6_K: po_dequantize_row_q6_K(p, out, (int) k); break;
         case PO_TYPE_F32:  memcpy(out, p, 4 * (size_t) k); break;

@@ -22,7 +22,7 @@ extern "C" {
 typedef uint16_t po_fp16;
 
 /* ggml type ids (ggml.h:305-333) for the three weight formats on the path */
-enum { PO_TYPE_F32 = 0, PO_TYPE_Q4_0 = 2, PO_TYPE_Q8_0 = 8, PO_TYPE_Q4_K = 12, PO_TYPE_Q5_K = 13, PO_TYPE_Q6_K = 14 };
+enum { PO_TYPE_F32 = 0, PO_TYPE_Q4_0 = 2, PO_TYPE_Q8_0 = 8, PO_TYPE_Q3_K = 11, PO_TYPE_Q4_K = 12, PO_TYPE_Q5_K = 13, PO_TYPE_Q6_K = 14 };
 
 /* --- scalar helpers ------------------------------------------------------------------------------------------ */
 float   po_fp16_to_fp32(po_fp16 h);
@@ -55,6 +55,8 @@ void po_rms_norm(const float * x, float * y, int n, float eps);                 
 void po_norm(const float * x, float * y, int n, float eps);                     /* ggml.c:8959 */
 void po_dequantize_row_q5_K(const void * x, float * y, int k);                  /* ggml-quants.c:1917 */
 void po_vec_dot_q5_K_q8_K(int n, float * s, const void * x, const void * y);    /* ggml-quants.c:5680 (AVX2 path) */
+void po_dequantize_row_q3_K(const void * vx, float * y, int k);
+void po_vec_dot_q3_K_q8_K(int n, float * s, const void * vx, const void * vy);
 void po_dequantize_row_q6_K(const void * x, float * y, int k);                  /* ggml-quants.c:1994 */
 void po_vec_dot_q6_K_q8_K(int n, float * s, const void * x, const void * y);    /* ggml-quants.c:6594 (AVX2 path :6739) */
 void po_rope(float * x, int n_head, int head_dim, int n_dims, int pos, int mode,

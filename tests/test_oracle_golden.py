@@ -171,7 +171,7 @@ def test_split_range_examples(oracle):
     assert all(r[i][1] == r[i + 1][0] for i in range(7))
 
 
-@pytest.mark.parametrize("wt,fname", [(op.TYPE_Q6_K, "kernels_q6k.npz"), (op.TYPE_Q5_K, "kernels_q5k.npz")])
+@pytest.mark.parametrize("wt,fname", [(op.TYPE_Q6_K, "kernels_q6k.npz"), (op.TYPE_Q5_K, "kernels_q5k.npz"), (op.TYPE_Q3_K, "kernels_q3k.npz")])
 def test_q6_k_q5_k_match_reference_golden(oracle, golden_dir, wt, fname):
     # the types Q4_K_M files keep output.weight, attn_v and part of ffn_down in (reference ggml-quants.c:1917, 1994, 5680, 6594)
     g = np.load(os.path.join(golden_dir, fname))
