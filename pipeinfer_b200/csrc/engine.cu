@@ -83,6 +83,9 @@ static size_t row_bytes_of(int type, int64_t K) {
         case PIB_TYPE_Q4_0: return (size_t) (K / 32) * 18;
         case PIB_TYPE_Q8_0: return (size_t) (K / 32) * 34;
         case PIB_TYPE_Q4_K: return (size_t) (K / 256) * 144;
+        case PIB_TYPE_Q3_K: return (size_t) (K / 256) * 110;
+        case PIB_TYPE_Q5_K: return (size_t) (K / 256) * 176;
+        case PIB_TYPE_Q6_K: return (size_t) (K / 256) * 210;
     }
     return 0;
 }
@@ -147,9 +150,11 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
     const bool nothing_resident = !want_embd && !want_output && layer_begin == layer_end && layer_end >= 0;
     if ((!emb && !nothing_resident) || m->n_layer <= 0 || m->n_embd <= 0 || m->n_head <= 0) { pib_set_error("gguf: missing hyper-parameters / token_embd"); delete m; return nullptr; }
     m->n_vocab = emb ? (int) emb->ne[1] : (int) m->tok_text.size();
-    m->wtype   = emb ? emb->type : PIB_TYPE_Q8_0;
-    if (m->wtype != PIB_TYPE_Q4_0 && m->wtype != PIB_TYPE_Q8_0 && m->wtype != PIB_TYPE_Q4_K) {
-        pib_set_error("gguf: token_embd of type %d not supported (Q4_0, Q8_0, Q4_K; other matrices may also be Q6_K)", m->wtype);
+    // wtype = the activation family the model multiplies with; a Q3_K_M file (token_embd in Q3_K) is of the Q4_K / Q8_K family
+    const int emb_type = emb ? emb->type : PIB_TYPE_Q8_0;
+    m->wtype   = pib_act_family(emb_type);
+    if (emb_type != PIB_TYPE_Q4_0 && emb_type != PIB_TYPE_Q8_0 && emb_type != PIB_TYPE_Q4_K && emb_type != PIB_TYPE_Q3_K) {
+        pib_set_error("gguf: token_embd of type %d not supported (Q4_0, Q8_0, Q4_K, Q3_K; other matrices may also be Q5_K / Q6_K)", emb_type);
         delete m;
         return nullptr;
     }

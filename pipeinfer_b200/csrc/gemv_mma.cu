@@ -56,11 +56,13 @@ __global__ void q4k_tiles_kernel(const uint8_t * __restrict__ qs, const uint8_t 
 int pib_weight_build_tiles_blk32(pib_weight * w);     // gemv_blk32.cu
 int pib_weight_build_tiles_q6k(pib_weight * w);       // gemv_q6k.cu
 int pib_weight_build_tiles_q5k(pib_weight * w);       // gemv_q5k.cu
+int pib_weight_build_tiles_q3k(pib_weight * w);       // gemv_q3k.cu
 
 int pib_weight_build_tiles(pib_weight * w) {
     if (w->type == PIB_TYPE_Q4_0 || w->type == PIB_TYPE_Q8_0) return pib_weight_build_tiles_blk32(w);
     if (w->type == PIB_TYPE_Q6_K) return pib_weight_build_tiles_q6k(w);
     if (w->type == PIB_TYPE_Q5_K) return pib_weight_build_tiles_q5k(w);
+    if (w->type == PIB_TYPE_Q3_K) return pib_weight_build_tiles_q3k(w);
     if (w->type != PIB_TYPE_Q4_K || w->tiles) return PIB_OK;
     const int64_t nsb = w->K / 256, n_tiles = (w->N + 15) / 16;
     const size_t  bytes = (size_t) n_tiles * nsb * MM_TILE_BYTES;

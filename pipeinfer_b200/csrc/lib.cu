@@ -115,6 +115,8 @@ int pib_gemv_mma(const pib_weight * w, const void * act_dev, int b, float * y_de
 bool pib_gemv_mma_supported(const pib_weight * w, int b);
 bool pib_gemv_blk32_supported(const pib_weight * w, int b);
 int  pib_gemv_q5k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
+int  pib_gemv_q3k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
+int  pib_get_rows_q3k(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, cudaStream_t st);
 int  pib_gemv_q6k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_blk32(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_ring(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
@@ -127,6 +129,7 @@ int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float *
                       cudaStream_t st) {
     if (w->type == PIB_TYPE_Q6_K) return pib_gemv_q6k(w, act_dev, b, y_dev, cancel, st);
     if (w->type == PIB_TYPE_Q5_K) return pib_gemv_q5k(w, act_dev, b, y_dev, cancel, st);
+    if (w->type == PIB_TYPE_Q3_K) return pib_gemv_q3k(w, act_dev, b, y_dev, cancel, st);
     // variants: 0 / 2 the fast tensor-core kernels (fp32 block terms added in the kernel's own order), 1 dp4a, 3 TMA-staged persistent
     // (Q4_K), 4 the reference's summation order restated literally (one thread per output; bit-identical to the CPU, slow), 6 the
     // tensor-core kernel that keeps the reference's order (Q4_K; bit-identical to the CPU).  7 = "exact mode": 6 where it exists, else 4.
@@ -147,7 +150,7 @@ extern "C" int pib_gemv(const pib_weight * w, const void * act_dev, int b, float
         pib_set_error("pib_gemv: bad arguments (b = %d, limit %d)", b, PIB_MAX_BATCH);
         return PIB_ERR_ARG;
     }
-    if (w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K) variant = 0;            // one kernel for these types
+    if (w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K || w->type == PIB_TYPE_Q3_K) variant = 0;            // one kernel for these types
     if (((variant == 3 || variant == 6) && !pib_gemv_mma_supported(w, b)) || (variant == 2 && !pib_gemv_mma_supported(w, b) && !pib_gemv_blk32_supported(w, b))) {
         pib_set_error("pib_gemv: variant 2 needs tiles (Q4_K, Q4_0, Q8_0), variants 3 and 6 Q4_K");
         return PIB_ERR_UNSUPP;
@@ -231,6 +234,7 @@ __global__ void get_rows_kernel(int type, const uint8_t * __restrict__ qs, const
 extern "C" int pib_get_rows(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, pib_stream s) {
     if (!w || !ids_dev || !out_dev || n < 1) { pib_set_error("pib_get_rows: bad arguments"); return PIB_ERR_ARG; }
     if (!w->qs) { pib_set_error("pib_get_rows: this matrix keeps only its tensor-core tiles"); return PIB_ERR_UNSUPP; }
+    if (w->type == PIB_TYPE_Q3_K) return pib_get_rows_q3k(w, ids_dev, n, out_dev, (cudaStream_t) s);
     if (w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K) { pib_set_error("pib_get_rows: Q5_K / Q6_K embeddings are not supported (Q4_K_M files keep token_embd in Q4_K)"); return PIB_ERR_UNSUPP; }
     pib_launch(get_rows_kernel, dim3(n), dim3(256), 0, (cudaStream_t) s, w->type, w->qs, w->d, w->K, ids_dev, out_dev);
     PIB_CHECK(cudaGetLastError());

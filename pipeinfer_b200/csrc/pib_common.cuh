@@ -124,7 +124,7 @@ struct pib_weight {
 
 // activation format a weight type multiplies with, named by the weight type that owns the layout below: the K-quants share
 // Q8_K (reference type_traits[].vec_dot_type, ggml.c:455-560)
-static inline int pib_act_family(int wtype) { return (wtype == PIB_TYPE_Q6_K || wtype == PIB_TYPE_Q5_K) ? PIB_TYPE_Q4_K : wtype; }
+static inline int pib_act_family(int wtype) { return (wtype == PIB_TYPE_Q6_K || wtype == PIB_TYPE_Q5_K || wtype == PIB_TYPE_Q3_K) ? PIB_TYPE_Q4_K : wtype; }
 
 // byte layout of a quantised-activation buffer for `b` tokens (device, produced by act_quant.cu)
 struct pib_act_layout {

@@ -8,6 +8,7 @@
 //   Q4_0:  qs  uint8 [N][K/2]        d   fp16 [N][K/32]      (byte j of a block = element j low nibble, j+16 high)
 //   Q4_K:  qs  uint8 [N][K/2]        hdr 16 B [N][K/256]     {fp16 d, fp16 dmin, uint8 scales[12]}
 //   Q5_K:  qs  160 B [N][K/256]      hdr 16 B [N][K/256]     {qs[128], qh[32]} and {fp16 d, fp16 dmin, uint8 scales[12]}
+//   Q3_K:  qs   96 B [N][K/256]      hdr 16 B [N][K/256]     {qs[64] low bit pairs, hmask[32]} and {scales[12], fp16 d, pad}
 //   Q6_K:  qs  192 B [N][K/256]      hdr 32 B [N][K/256]     {ql[128], qh[64]} and {int8 scales[16], fp16 d, pad}
 //
 // The tensor-core GEMV additionally builds fragment-major tiles from these planes (gemv_mma.cu).
@@ -72,11 +73,24 @@ static __global__ void repack_q6_K(const uint8_t * __restrict__ src, uint8_t * _
     else if (p == 13) { hdr[blk * 32 + 16] = b[208]; hdr[blk * 32 + 17] = b[209]; for (int k = 18; k < 32; k++) hdr[blk * 32 + k] = 0; }
 }
 
+// block_q3_K (ggml-quants.h:95-101): hmask[32], qs[64], scales[12], d -- 110 bytes
+static __global__ void repack_q3_K(const uint8_t * __restrict__ src, uint8_t * __restrict__ qs, uint8_t * __restrict__ hdr, int64_t nblk) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nblk * 8) return;                 // 8 threads per super-block: 4 x 16 bytes of qs, 2 x 16 of hmask, 1 x header, 1 idle
+    const int64_t blk = i / 8;
+    const int     p   = (int) (i % 8);
+    const uint8_t * b = src + blk * 110;
+    if (p < 4)       { for (int k = 0; k < 16; k++) qs[blk * 96 + p * 16 + k] = b[32 + p * 16 + k]; }
+    else if (p < 6)  { for (int k = 0; k < 16; k++) qs[blk * 96 + 64 + (p - 4) * 16 + k] = b[(p - 4) * 16 + k]; }
+    else if (p == 6) { for (int k = 0; k < 14; k++) hdr[blk * 16 + k] = b[96 + k]; hdr[blk * 16 + 14] = 0; hdr[blk * 16 + 15] = 0; }
+}
+
 static int block_geom(int type, int * elems, int * bytes) {
     switch (type) {
         case PIB_TYPE_Q4_0: *elems = 32;  *bytes = 18;  return 0;
         case PIB_TYPE_Q8_0: *elems = 32;  *bytes = 34;  return 0;
         case PIB_TYPE_Q4_K: *elems = 256; *bytes = 144; return 0;
+        case PIB_TYPE_Q3_K: *elems = 256; *bytes = 110; return 0;
         case PIB_TYPE_Q5_K: *elems = 256; *bytes = 176; return 0;
         case PIB_TYPE_Q6_K: *elems = 256; *bytes = 210; return 0;
     }
@@ -94,8 +108,9 @@ static pib_weight * alloc_weight(int type, int64_t N, int64_t K) {
     w->N     = N;
     w->K     = K;
     w->bytes = (size_t) N * (K / be) * bb;
-    size_t qs_bytes = (type == PIB_TYPE_Q8_0) ? (size_t) N * K : (type == PIB_TYPE_Q6_K) ? (size_t) N * (K / 256) * 192 : (type == PIB_TYPE_Q5_K) ? (size_t) N * (K / 256) * 160 : (size_t) N * K / 2;
-    size_t d_bytes  = (type == PIB_TYPE_Q4_K || type == PIB_TYPE_Q5_K) ? (size_t) N * (K / 256) * 16 : (type == PIB_TYPE_Q6_K) ? (size_t) N * (K / 256) * 32
+    size_t qs_bytes = (type == PIB_TYPE_Q8_0) ? (size_t) N * K : (type == PIB_TYPE_Q6_K) ? (size_t) N * (K / 256) * 192 : (type == PIB_TYPE_Q5_K) ? (size_t) N * (K / 256) * 160
+                    : (type == PIB_TYPE_Q3_K) ? (size_t) N * (K / 256) * 96 : (size_t) N * K / 2;
+    size_t d_bytes  = (type == PIB_TYPE_Q4_K || type == PIB_TYPE_Q5_K || type == PIB_TYPE_Q3_K) ? (size_t) N * (K / 256) * 16 : (type == PIB_TYPE_Q6_K) ? (size_t) N * (K / 256) * 32
                                                                             : (size_t) N * (K / 32) * 2;
     size_t d_off    = (qs_bytes + 255) & ~(size_t) 255;
     if (cudaMalloc(&w->base, d_off + d_bytes + 256) != cudaSuccess) {
@@ -126,6 +141,9 @@ static int repack_from_device(pib_weight * w, const uint8_t * src, int64_t row0,
             break;
         case PIB_TYPE_Q5_K:
             repack_q5_K<<<(unsigned) ((nblk * 11 + T - 1) / T), T, 0, st>>>(src, w->qs + blk0 * 160, (uint8_t *) w->d + blk0 * 16, nblk);
+            break;
+        case PIB_TYPE_Q3_K:
+            repack_q3_K<<<(unsigned) ((nblk * 8 + T - 1) / T), T, 0, st>>>(src, w->qs + blk0 * 96, (uint8_t *) w->d + blk0 * 16, nblk);
             break;
         case PIB_TYPE_Q6_K:
             repack_q6_K<<<(unsigned) ((nblk * 16 + T - 1) / T), T, 0, st>>>(src, w->qs + blk0 * 192, (uint8_t *) w->d + blk0 * 32, nblk);
@@ -216,6 +234,15 @@ extern "C" int pib_weight_row_blocks(const pib_weight * w, int64_t row, void * o
             PIB_CHECK(cudaMemcpy(o + s * 176, (uint8_t *) w->d + (row * nsb + s) * 16, 16, cudaMemcpyDeviceToHost));
             PIB_CHECK(cudaMemcpy(o + s * 176 + 16, w->qs + (row * nsb + s) * 160 + 128, 32, cudaMemcpyDeviceToHost));
             PIB_CHECK(cudaMemcpy(o + s * 176 + 48, w->qs + (row * nsb + s) * 160, 128, cudaMemcpyDeviceToHost));
+        }
+        return PIB_OK;
+    }
+    if (w->type == PIB_TYPE_Q3_K) {
+        const int64_t nsb = w->K / 256;
+        for (int64_t s = 0; s < nsb; s++) {
+            PIB_CHECK(cudaMemcpy(o + s * 110, w->qs + (row * nsb + s) * 96 + 64, 32, cudaMemcpyDeviceToHost));
+            PIB_CHECK(cudaMemcpy(o + s * 110 + 32, w->qs + (row * nsb + s) * 96, 64, cudaMemcpyDeviceToHost));
+            PIB_CHECK(cudaMemcpy(o + s * 110 + 96, (uint8_t *) w->d + (row * nsb + s) * 16, 14, cudaMemcpyDeviceToHost));
         }
         return PIB_OK;
     }

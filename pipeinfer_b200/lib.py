@@ -8,10 +8,11 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(HERE, "libpipeinfer_b200.so")
 
 TYPE_Q4_0, TYPE_Q8_0, TYPE_Q4_K = 2, 8, 12
+TYPE_Q3_K = 11        # matmul + embedding rows (Q3_K_M files); activations as Q4_K
 TYPE_Q5_K = 13
 TYPE_Q6_K = 14        # matmul only; multiplies with the same activations as Q4_K
 TYPES = {"q4_0": TYPE_Q4_0, "q8_0": TYPE_Q8_0, "q4_k": TYPE_Q4_K}
-BLOCK = {TYPE_Q4_0: (32, 18), TYPE_Q8_0: (32, 34), TYPE_Q4_K: (256, 144), TYPE_Q5_K: (256, 176), TYPE_Q6_K: (256, 210)}
+BLOCK = {TYPE_Q4_0: (32, 18), TYPE_Q8_0: (32, 34), TYPE_Q4_K: (256, 144), TYPE_Q5_K: (256, 176), TYPE_Q6_K: (256, 210), TYPE_Q3_K: (256, 110)}
 ACT_BLOCK = {TYPE_Q4_0: (32, 34), TYPE_Q8_0: (32, 34), TYPE_Q4_K: (256, 292)}
 
 

@@ -44,7 +44,8 @@ def test_decode_trace_vs_reference_exact_mode(llama, golden_dir, q):
     assert n_dec == 8 and max(errs) == 0.0
 
 
-@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m", "q4_k_s"])
+# q3_k_m: the type of the authors' 70B target: Q3_K token_embd / attn_q / attn_k / ffn_gate / ffn_up, the rest Q4_K, Q5_K, Q6_K
+@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m", "q4_k_s", "q3_k_m"])
 def test_decode_trace_vs_reference(llama, golden_dir, q):
     ctx = llama.Context(os.path.join(golden_dir, "tiny_%s.gguf" % q), n_ctx=48, max_seq=8)
     errs, row_errs = [], []

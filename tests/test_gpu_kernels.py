@@ -237,10 +237,12 @@ def test_mul_mat_width_not_a_multiple_of_256(lib, oracle, wt, b):
     lib.L.pib_weight_free(h)
 
 
-@pytest.mark.parametrize("wt,fname,bb,dpos", [(op.TYPE_Q6_K, "kernels_q6k.npz", 210, 208), (op.TYPE_Q5_K, "kernels_q5k.npz", 176, 0)])
+@pytest.mark.parametrize("wt,fname,bb,dpos", [(op.TYPE_Q6_K, "kernels_q6k.npz", 210, 208), (op.TYPE_Q5_K, "kernels_q5k.npz", 176, 0),
+                                              (op.TYPE_Q3_K, "kernels_q3k.npz", 110, 108)])
 @pytest.mark.parametrize("b", [1, 3, 8, 9, 16])
 def test_q6_k_q5_k_mul_mat(lib, oracle, golden_dir, b, wt, fname, bb, dpos):
-    # Q6_K / Q5_K: output.weight, attn_v and part of ffn_down of Q4_K_M files.  Block round trip, the reference's golden, random raw blocks
+    # Q6_K / Q5_K: output.weight, attn_v and part of ffn_down of Q4_K_M files; Q3_K: the bulk of Q3_K_M files.  Block round trip, the
+    # reference's golden, random raw blocks
     g = np.load(os.path.join(golden_dir, fname))
     K = g["x"].shape[1]
     h = lib.weight_upload(wt, g["w"], K)
@@ -309,4 +311,15 @@ def test_prologue_fused_gemv_vs_oracle(lib, oracle, pro, b):
     assert lib.L.pib_gemv_fused(h, 7, xd, None, None, None, 0, 0.0, 1, yd, None) < 0       # unknown prologue
     for d in (xd, x2d, ad, yd, sd):
         lib.free(d)
+    lib.L.pib_weight_free(h)
+
+
+def test_q3_k_embedding_rows_bit_exact(lib, golden_dir):
+    # token_embd of a Q3_K_M file is Q3_K: get_rows must return dequantize_row_q3_K's bits
+    g = np.load(os.path.join(golden_dir, "kernels_q3k.npz"))
+    K = g["x"].shape[1]
+    h = lib.weight_upload(op.TYPE_Q3_K, g["w"], K)
+    ids = np.array([3, 0, 11, 3], dtype=np.int32)
+    got = lib.get_rows(h, ids, K)
+    assert np.array_equal(got.view(np.uint32), g["deq"][ids].view(np.uint32))
     lib.L.pib_weight_free(h)

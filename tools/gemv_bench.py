@@ -10,14 +10,14 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--type", default="q4_k"); ap.add_argument("--N", type=int, default=57344); ap.add_argument("--K", type=int, default=8192)
 ap.add_argument("--b", default="1,4"); ap.add_argument("--variant", default="0"); ap.add_argument("--reps", type=int, default=50)
 a = ap.parse_args()
-wt = {"q4_k": 12, "q4_0": 2, "q8_0": 8, "q6_k": 14, "q5_k": 13}[a.type]
-bb = {12: 144, 2: 18, 8: 34, 14: 210, 13: 176}[wt]; be = {12: 256, 2: 32, 8: 32, 14: 256, 13: 256}[wt]
+wt = {"q4_k": 12, "q4_0": 2, "q8_0": 8, "q6_k": 14, "q5_k": 13, "q3_k": 11}[a.type]
+bb = {12: 144, 2: 18, 8: 34, 14: 210, 13: 176, 11: 110}[wt]; be = {12: 256, 2: 32, 8: 32, 14: 256, 13: 256, 11: 256}[wt]
 lib = load(); lib.init(0)
 rng = np.random.default_rng(0)
 wbytes = a.N * a.K // be * bb
 ncopies = max(1, int(300e6 // wbytes) + 1)
 blk = rng.integers(0, 256, (a.N, a.K // be, bb), dtype=np.uint8)
-dpos = 208 if wt == 14 else 0
+dpos = 208 if wt == 14 else 108 if wt == 11 else 0
 blk[:, :, dpos:dpos + 2] = (rng.uniform(0.5, 1.5, (a.N, a.K // be)) * 0.0025).astype(np.float16).view(np.uint8).reshape(a.N, a.K // be, 2)
 if wt in (12, 13):
     blk[:, :, 2:4] = (rng.uniform(0.5, 1.5, (a.N, a.K // be)) * 0.001).astype(np.float16).view(np.uint8).reshape(a.N, a.K // be, 2)
@@ -44,7 +44,7 @@ for b in [int(x) for x in a.b.split(",")]:
         continue
     x = rng.standard_normal((b, a.K)).astype(np.float32)
     xd = lib.to_device(x)
-    awt = 12 if wt in (13, 14) else wt                       # the K-quants share the Q8_K activation layout
+    awt = 12 if wt in (11, 13, 14) else wt                       # the K-quants share the Q8_K activation layout
     act = lib.alloc(lib.L.pib_act_bytes(awt, a.K, b))
     yd = lib.alloc(b * a.N * 4)
     lib.check(lib.L.pib_quantize_act(awt, xd, b, a.K, act, None))
