@@ -45,7 +45,9 @@ class Model(C.Structure):
                 ("ffn_up", C.POINTER(C.c_void_p)),
                 ("arch", C.c_int32), ("norm_eps", C.c_float),
                 ("attn_norm_b", C.POINTER(C.c_void_p)), ("attn_norm2", C.POINTER(C.c_void_p)),
-                ("attn_norm2_b", C.POINTER(C.c_void_p)), ("output_norm_b", C.c_void_p)]
+                ("attn_norm2_b", C.POINTER(C.c_void_p)), ("output_norm_b", C.c_void_p),
+                ("t_wq", C.POINTER(C.c_int32)), ("t_wk", C.POINTER(C.c_int32)), ("t_wv", C.POINTER(C.c_int32)), ("t_wo", C.POINTER(C.c_int32)),
+                ("t_gate", C.POINTER(C.c_int32)), ("t_down", C.POINTER(C.c_int32)), ("t_up", C.POINTER(C.c_int32)), ("t_output", C.c_int32)]
 
 
 class KvMeta(C.Structure):
@@ -277,6 +279,16 @@ def load_gguf_model(path):
     m.ffn_gate = arr("blk.%d.ffn_gate.weight")
     m.ffn_down = arr("blk.%d.ffn_down.weight")
     m.ffn_up = arr("blk.%d.ffn_up.weight")
+
+    def types(fmt):
+        a = (C.c_int32 * L)(*[int(t[fmt % i].tensor_type) for i in range(L)])
+        keep.append(a)
+        return C.cast(a, C.POINTER(C.c_int32))
+
+    # per-tensor types: files made without --pure mix them (Q4_K_M: Q6_K output.weight ...)
+    m.t_wq, m.t_wk, m.t_wv, m.t_wo = types("blk.%d.attn_q.weight"), types("blk.%d.attn_k.weight"), types("blk.%d.attn_v.weight"), types("blk.%d.attn_output.weight")
+    m.t_gate, m.t_down, m.t_up = types("blk.%d.ffn_gate.weight"), types("blk.%d.ffn_down.weight"), types("blk.%d.ffn_up.weight")
+    m.t_output = int(t["output.weight"].tensor_type)
     m._keep = keep
     m._reader = r
     return m

@@ -930,6 +930,7 @@ int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t
     po_fp16 * q16 = (po_fp16 *) malloc(2 * (size_t) hd);
     po_fp16 * p16 = (po_fp16 *) malloc(2 * (size_t) n_kv);
 
+#define TT(arr) ((arr) ? (arr)[il] : m->wtype)          /* per-tensor type of a mixed file */
     for (int t = 0; t < T; t++) dequant_row(m->wtype, m->tok_embd, token[t], E, inpL + (size_t) t * E);   /* get_rows */
 
     for (int il = 0; il < m->n_layer; il++) {
@@ -940,9 +941,9 @@ int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t
             po_rms_norm(inpL + (size_t) t * E, cur + (size_t) t * E, E, m->rms_eps);
             for (int i = 0; i < E; i++) cur[(size_t) t * E + i] *= m->attn_norm[il][i];       /* ggml_mul :3593 */
         }
-        po_mul_mat(m->wtype, m->wq[il], E, E, cur, T, q);
-        po_mul_mat(m->wtype, m->wk[il], GQA, E, cur, T, kc);
-        po_mul_mat(m->wtype, m->wv[il], GQA, E, cur, T, vc);
+        po_mul_mat(TT(m->t_wq), m->wq[il], E, E, cur, T, q);
+        po_mul_mat(TT(m->t_wk), m->wk[il], GQA, E, cur, T, kc);
+        po_mul_mat(TT(m->t_wv), m->wv[il], GQA, E, cur, T, vc);
         po_dump("q", il, q, (size_t) T * E); po_dump("k", il, kc, (size_t) T * GQA); po_dump("v", il, vc, (size_t) T * GQA);
         for (int t = 0; t < T; t++) {
             po_rope(q + (size_t) t * E, H, hd, m->n_rot, pos[t], 0, m->rope_freq_base, m->rope_freq_scale);
@@ -974,7 +975,7 @@ int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t
             }
         }
         po_dump("att", il, att, (size_t) T * E);
-        po_mul_mat(m->wtype, m->wo[il], E, E, att, T, cur);
+        po_mul_mat(TT(m->t_wo), m->wo[il], E, E, att, T, cur);
         po_dump("o", il, cur, (size_t) T * E);
         for (size_t i = 0; i < (size_t) T * E; i++) ffi[i] = cur[i] + inpL[i];               /* ffn_inp :3944 */
         po_dump("ffi", il, ffi, (size_t) T * E);
@@ -982,12 +983,12 @@ int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t
             po_rms_norm(ffi + (size_t) t * E, cur + (size_t) t * E, E, m->rms_eps);
             for (int i = 0; i < E; i++) cur[(size_t) t * E + i] *= m->ffn_norm[il][i];
         }
-        po_mul_mat(m->wtype, m->ffn_up[il], FF, E, cur, T, up);                              /* llm_build_ffn :3611 */
-        po_mul_mat(m->wtype, m->ffn_gate[il], FF, E, cur, T, gate);
+        po_mul_mat(TT(m->t_up), m->ffn_up[il], FF, E, cur, T, up);                              /* llm_build_ffn :3611 */
+        po_mul_mat(TT(m->t_gate), m->ffn_gate[il], FF, E, cur, T, gate);
         po_dump("gate", il, gate, (size_t) T * FF); po_dump("up", il, up, (size_t) T * FF);
         po_silu(gate, T * FF);
         for (size_t i = 0; i < (size_t) T * FF; i++) gate[i] = gate[i] * up[i];
-        po_mul_mat(m->wtype, m->ffn_down[il], E, FF, gate, T, cur);
+        po_mul_mat(TT(m->t_down), m->ffn_down[il], E, FF, gate, T, cur);
         po_dump("down", il, cur, (size_t) T * E);
         for (size_t i = 0; i < (size_t) T * E; i++) inpL[i] = cur[i] + ffi[i];               /* l_out :3962 */
     }
@@ -995,7 +996,8 @@ int po_decode(po_context * c, int n_tokens, const int32_t * token, const int32_t
         po_rms_norm(inpL + (size_t) t * E, cur + (size_t) t * E, E, m->rms_eps);
         for (int i = 0; i < E; i++) cur[(size_t) t * E + i] *= m->output_norm[i];
     }
-    po_mul_mat(m->wtype, m->output, m->n_vocab, E, cur, T, logits);
+    po_mul_mat(m->t_output ? m->t_output : m->wtype, m->output, m->n_vocab, E, cur, T, logits);
+#undef TT
 
     kv->head += (uint32_t) T;                                                                /* :5708-5713 */
     if (kv->head >= kv->size) kv->head = 0;

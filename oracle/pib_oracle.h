@@ -107,6 +107,10 @@ typedef struct {
     float          norm_eps;
     const float ** attn_norm_b, ** attn_norm2, ** attn_norm2_b;
     const float *  output_norm_b;
+    /* mixed files (quantize without --pure: Q4_K_M, Q4_K_S, Q3_K_M ...), llama architecture: per-layer types of the matrices and the
+     * type of output.weight; NULL / 0 = wtype */
+    const int32_t * t_wq, * t_wk, * t_wv, * t_wo, * t_gate, * t_down, * t_up;
+    int32_t         t_output;
 } po_model;
 
 typedef struct {
