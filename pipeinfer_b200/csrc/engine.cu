@@ -57,8 +57,10 @@ static void drop_planes_of(pib_model * m) {
     const char * keep = getenv("PIB_KEEP_PLANES");
     if (keep && atoi(keep) != 0) return;
     if (pib_exact_mode() && m->wtype != PIB_TYPE_Q4_K) return;
-    if (m->output) pib_weight_drop_planes(m->output);
-    for (auto & L : m->layers) for (pib_weight * w : { L.wqkv, L.wv, L.wo, L.wgu, L.wdown }) if (w) pib_weight_drop_planes(w);
+    // exact mode on a mixed file: Q4_K has its order-keeping tensor-core kernel, the other K-quants keep their planes for gemv_exact.cu
+    auto drop = [&](pib_weight * w) { if (w && !(pib_exact_mode() && w->type != PIB_TYPE_Q4_K)) pib_weight_drop_planes(w); };
+    drop(m->output);
+    for (auto & L : m->layers) for (pib_weight * w : { L.wqkv, L.wv, L.wo, L.wgu, L.wdown }) drop(w);
 }
 int pib_weight_build_tiles(pib_weight * w);
 

@@ -127,6 +127,9 @@ int  pib_gemv_exact_ref(const pib_weight * w, const void * act_dev, int b, float
 
 int pib_gemv_internal(const pib_weight * w, const void * act_dev, int b, float * y_dev, int variant, const int * cancel,
                       cudaStream_t st) {
+    // the other K-quants have one fast kernel each; exact mode (7) and variant 4 take the reference-order kernel when the planes are there
+    if ((variant == 7 || variant == 4) && (w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K || w->type == PIB_TYPE_Q3_K) && w->qs)
+        return pib_gemv_exact_ref(w, act_dev, b, y_dev, cancel, st);
     if (w->type == PIB_TYPE_Q6_K) return pib_gemv_q6k(w, act_dev, b, y_dev, cancel, st);
     if (w->type == PIB_TYPE_Q5_K) return pib_gemv_q5k(w, act_dev, b, y_dev, cancel, st);
     if (w->type == PIB_TYPE_Q3_K) return pib_gemv_q3k(w, act_dev, b, y_dev, cancel, st);
@@ -150,7 +153,7 @@ extern "C" int pib_gemv(const pib_weight * w, const void * act_dev, int b, float
         pib_set_error("pib_gemv: bad arguments (b = %d, limit %d)", b, PIB_MAX_BATCH);
         return PIB_ERR_ARG;
     }
-    if (w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K || w->type == PIB_TYPE_Q3_K) variant = 0;            // one kernel for these types
+    if ((w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K || w->type == PIB_TYPE_Q3_K) && variant != 4 && variant != 7) variant = 0;   // one fast kernel for these types
     if (((variant == 3 || variant == 6) && !pib_gemv_mma_supported(w, b)) || (variant == 2 && !pib_gemv_mma_supported(w, b) && !pib_gemv_blk32_supported(w, b))) {
         pib_set_error("pib_gemv: variant 2 needs tiles (Q4_K, Q4_0, Q8_0), variants 3 and 6 Q4_K");
         return PIB_ERR_UNSUPP;

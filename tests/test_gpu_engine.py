@@ -37,9 +37,9 @@ def llama():
 # llama architecture in the three weight types; falcon architecture (LayerNorm + bias, NeoX RoPE, fused QKV, GELU MLP in
 # parallel with attention) in its 7B layout (multi-query, one norm) and its 40B/180B layout (two norms per layer)
 # q4_k_m: a file as the reference's quantize makes it without --pure (Q4_K with Q6_K output.weight and some attn_v / ffn_down)
-@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0"])
+@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m", "q4_k_s", "q3_k_m"])
 def test_decode_trace_vs_reference_exact_mode(llama, golden_dir, q):
-    """exact mode on the toy fixtures, both architectures: the reference's bits"""
+    """exact mode on the toy fixtures, both architectures and the mixed K-quant files: the reference's bits"""
     n_dec, errs, rows, ties = _replay_checked(llama, golden_dir, os.path.join(golden_dir, "tiny_%s.gguf" % q), q, 48, 8, exact=True)
     assert n_dec == 8 and max(errs) == 0.0
 

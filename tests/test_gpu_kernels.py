@@ -262,6 +262,9 @@ def test_q6_k_q5_k_mul_mat(lib, oracle, golden_dir, b, wt, fname, bb, dpos):
     ref = oracle.mul_mat(wt, w, x)
     got = lib.mul_mat(h, x, N, 0)
     assert np.abs(got - ref).max() <= REL_TOL * max(1.0, np.abs(ref).max())
+    # variant 4 (what exact mode runs for these types): the reference's summation order, the oracle's bits
+    ex = lib.mul_mat(h, x, N, 4)
+    assert np.array_equal(ex.view(np.uint32), ref.view(np.uint32)), float(np.abs(ex - ref).max())
     lib.L.pib_weight_free(h)
 
 
