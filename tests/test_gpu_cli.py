@@ -15,8 +15,8 @@ ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
 CLI = os.path.join(ROOT, "pipeinfer_b200", "bin", "speculative")
 
 
-def cli_args(golden_dir, gold):
-    return ["-m", os.path.join(golden_dir, "tiny_q8_0.gguf"), "-md", os.path.join(golden_dir, "tiny_draft_q8_0.gguf"),
+def cli_args(golden_dir, gold, target="tiny_q8_0.gguf"):
+    return ["-m", os.path.join(golden_dir, target), "-md", os.path.join(golden_dir, "tiny_draft_q8_0.gguf"),
             "-p", gold["prompt"], "-n", "24", "-c", "256", "--temp", "-1", "--repeat-last-n", "0", "--ignore-eos", "-t", "2",
             "--draft", "4", "-np", "1", "--mpi-layer-split", "0.5,0.5/1.0"]
 
@@ -37,6 +37,19 @@ def test_cli_single_gpu_matches_reference_text(golden_dir, tmp_path):
     assert b"decoded" in r.stderr and b"n_accept" in r.stderr
     row = open(os.path.join(tmp_path, "results.csv")).read().strip().split(",")
     assert len(row) == 4 and float(row[1]) > 0
+
+
+def test_cli_on_a_q3_k_m_target_matches_reference_text(golden_dir, tmp_path):
+    """the authors' launch script runs a Q3_K_M target (scripts/dolphin_tinyllama_8_nodes.sh): the reference's `speculative` on a Q3_K_M
+    file (Q3_K / Q4_K / Q5_K / Q6_K tensors) against this program on the same files.  Exact mode, so that the comparison cannot hinge on
+    a near tie of two logits."""
+    gold = json.load(open(os.path.join(golden_dir, "speculative_q3_k_m.json")))
+    r = subprocess.run([CLI] + cli_args(golden_dir, gold, "tiny_q3_k_m.gguf"), cwd=tmp_path, capture_output=True, timeout=300,
+                       env=dict(os.environ, PIB_EXACT="1"))
+    assert r.returncode == 0, r.stderr[-2000:]
+    got, ref = generated(r.stdout, gold)
+    n = min(len(got), len(ref))
+    assert n >= 20 and got[:n] == ref[:n], (got, ref)
 
 
 def test_cli_two_stages_matches_reference_text(golden_dir, tmp_path):
