@@ -155,8 +155,9 @@ pib_model * pib_model_load_gguf(const char * path, int layer_begin, int layer_en
     // wtype = the activation family the model multiplies with; a Q3_K_M file (token_embd in Q3_K) is of the Q4_K / Q8_K family
     const int emb_type = emb ? emb->type : PIB_TYPE_Q8_0;
     m->wtype   = pib_act_family(emb_type);
-    if (emb_type != PIB_TYPE_Q4_0 && emb_type != PIB_TYPE_Q8_0 && emb_type != PIB_TYPE_Q4_K && emb_type != PIB_TYPE_Q3_K) {
-        pib_set_error("gguf: token_embd of type %d not supported (Q4_0, Q8_0, Q4_K, Q3_K; other matrices may also be Q5_K / Q6_K)", emb_type);
+    if (emb_type != PIB_TYPE_Q4_0 && emb_type != PIB_TYPE_Q8_0 && emb_type != PIB_TYPE_Q4_K && emb_type != PIB_TYPE_Q3_K && emb_type != PIB_TYPE_Q5_K &&
+        emb_type != PIB_TYPE_Q6_K) {
+        pib_set_error("gguf: token_embd of type %d not supported (Q4_0, Q8_0, Q3_K, Q4_K, Q5_K, Q6_K)", emb_type);
         delete m;
         return nullptr;
     }

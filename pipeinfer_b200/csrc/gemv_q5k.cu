@@ -311,3 +311,26 @@ int pib_gemv_q5k(const pib_weight * w, const void * act_dev, int b, float * y_de
     }
     return PIB_OK;
 }
+
+// embedding rows (token_embd of Q5_K_S / Q5_K_M files): dequantize_row_q5_K (ggml-quants.c:1930-1960), y = (d * sc) * q - min * m
+__global__ void q5k_get_rows_kernel(const uint8_t * __restrict__ qs, const uint8_t * __restrict__ hdr, int64_t K, const int32_t * __restrict__ ids,
+                                    float * __restrict__ out) {
+    const int64_t row = ids[blockIdx.x], nsb = K / 256;
+    for (int64_t e = threadIdx.x; e < K; e += blockDim.x) {
+        const int64_t sb = e >> 8;
+        const int     ee = (int) (e & 255), j = ee >> 6, r = ee & 63, l = r & 31, hi = r >> 5;
+        const uint8_t * blk = qs + (row * nsb + sb) * 160;
+        const uint8_t * h   = hdr + (row * nsb + sb) * 16;
+        const float d = pib_h2f(*reinterpret_cast<const uint16_t *>(h)), mn = pib_h2f(*reinterpret_cast<const uint16_t *>(h + 2));
+        int sc, m;
+        q5_scale_min(2 * j + hi, h + 4, sc, m);
+        const int q = (hi ? (blk[32 * j + l] >> 4) : (blk[32 * j + l] & 0xF)) + (((blk[128 + l] >> (2 * j + hi)) & 1) ? 16 : 0);
+        const float d1 = __fmul_rn(d, (float) sc), m1 = __fmul_rn(mn, (float) m);
+        out[(size_t) blockIdx.x * K + e] = __fsub_rn(__fmul_rn(d1, (float) q), m1);
+    }
+}
+int pib_get_rows_q5k(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, cudaStream_t st) {
+    if (!w->qs) { pib_set_error("pib_get_rows: this matrix keeps only its tensor-core tiles"); return PIB_ERR_UNSUPP; }
+    PIB_CHECK(pib_launch(q5k_get_rows_kernel, dim3(n), dim3(256), 0, st, (const uint8_t *) w->qs, (const uint8_t *) w->d, w->K, ids_dev, out_dev));
+    return PIB_OK;
+}

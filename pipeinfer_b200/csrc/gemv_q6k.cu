@@ -313,3 +313,24 @@ int pib_gemv_q6k(const pib_weight * w, const void * act_dev, int b, float * y_de
     }
     return PIB_OK;
 }
+
+// embedding rows (token_embd of Q6_K files): dequantize_row_q6_K (ggml-quants.c:1994-2040), y = (d * scale) * q, one thread per element
+__global__ void q6k_get_rows_kernel(const uint8_t * __restrict__ qs, const uint8_t * __restrict__ hdr, int64_t K, const int32_t * __restrict__ ids,
+                                    float * __restrict__ out) {
+    const int64_t row = ids[blockIdx.x], nsb = K / 256;
+    for (int64_t e = threadIdx.x; e < K; e += blockDim.x) {
+        const int64_t sb = e >> 8;
+        const int     ee = (int) (e & 255), n = ee >> 7, ep = ee & 127, quarter = ep >> 5, l = ep & 31;
+        const uint8_t * blk = qs + (row * nsb + sb) * 192;
+        const uint8_t * h   = hdr + (row * nsb + sb) * 32;
+        const int q = (int) (int8_t) q6_value(blk, ee) - 32;
+        const float d  = pib_h2f(*reinterpret_cast<const uint16_t *>(h + 16));
+        const float sc = (float) reinterpret_cast<const int8_t *>(h)[8 * n + (l >> 4) + 2 * quarter];
+        out[(size_t) blockIdx.x * K + e] = __fmul_rn(__fmul_rn(d, sc), (float) q);
+    }
+}
+int pib_get_rows_q6k(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, cudaStream_t st) {
+    if (!w->qs) { pib_set_error("pib_get_rows: this matrix keeps only its tensor-core tiles"); return PIB_ERR_UNSUPP; }
+    PIB_CHECK(pib_launch(q6k_get_rows_kernel, dim3(n), dim3(256), 0, st, (const uint8_t *) w->qs, (const uint8_t *) w->d, w->K, ids_dev, out_dev));
+    return PIB_OK;
+}

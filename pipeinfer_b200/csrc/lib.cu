@@ -117,6 +117,8 @@ bool pib_gemv_blk32_supported(const pib_weight * w, int b);
 int  pib_gemv_q5k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_q3k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_get_rows_q3k(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, cudaStream_t st);
+int  pib_get_rows_q5k(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, cudaStream_t st);
+int  pib_get_rows_q6k(const pib_weight * w, const int32_t * ids_dev, int n, float * out_dev, cudaStream_t st);
 int  pib_gemv_q6k(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_blk32(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
 int  pib_gemv_ring(const pib_weight * w, const void * act_dev, int b, float * y_dev, const int * cancel, cudaStream_t st);
@@ -238,7 +240,8 @@ extern "C" int pib_get_rows(const pib_weight * w, const int32_t * ids_dev, int n
     if (!w || !ids_dev || !out_dev || n < 1) { pib_set_error("pib_get_rows: bad arguments"); return PIB_ERR_ARG; }
     if (!w->qs) { pib_set_error("pib_get_rows: this matrix keeps only its tensor-core tiles"); return PIB_ERR_UNSUPP; }
     if (w->type == PIB_TYPE_Q3_K) return pib_get_rows_q3k(w, ids_dev, n, out_dev, (cudaStream_t) s);
-    if (w->type == PIB_TYPE_Q6_K || w->type == PIB_TYPE_Q5_K) { pib_set_error("pib_get_rows: Q5_K / Q6_K embeddings are not supported (Q4_K_M files keep token_embd in Q4_K)"); return PIB_ERR_UNSUPP; }
+    if (w->type == PIB_TYPE_Q5_K) return pib_get_rows_q5k(w, ids_dev, n, out_dev, (cudaStream_t) s);
+    if (w->type == PIB_TYPE_Q6_K) return pib_get_rows_q6k(w, ids_dev, n, out_dev, (cudaStream_t) s);
     pib_launch(get_rows_kernel, dim3(n), dim3(256), 0, (cudaStream_t) s, w->type, w->qs, w->d, w->K, ids_dev, out_dev);
     PIB_CHECK(cudaGetLastError());
     return PIB_OK;

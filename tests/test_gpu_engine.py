@@ -37,7 +37,7 @@ def llama():
 # llama architecture in the three weight types; falcon architecture (LayerNorm + bias, NeoX RoPE, fused QKV, GELU MLP in
 # parallel with attention) in its 7B layout (multi-query, one norm) and its 40B/180B layout (two norms per layer)
 # q4_k_m: a file as the reference's quantize makes it without --pure (Q4_K with Q6_K output.weight and some attn_v / ffn_down)
-@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m", "q4_k_s", "q3_k_m"])
+@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m", "q4_k_s", "q3_k_m", "q5_k_m", "q6_k"])
 def test_decode_trace_vs_reference_exact_mode(llama, golden_dir, q):
     """exact mode on the toy fixtures, both architectures and the mixed K-quant files: the reference's bits"""
     n_dec, errs, rows, ties = _replay_checked(llama, golden_dir, os.path.join(golden_dir, "tiny_%s.gguf" % q), q, 48, 8, exact=True)
@@ -45,7 +45,8 @@ def test_decode_trace_vs_reference_exact_mode(llama, golden_dir, q):
 
 
 # q3_k_m: the type of the authors' 70B target: Q3_K token_embd / attn_q / attn_k / ffn_gate / ffn_up, the rest Q4_K, Q5_K, Q6_K
-@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m", "q4_k_s", "q3_k_m"])
+# q5_k_m / q6_k: files whose token embedding is Q5_K / Q6_K
+@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m", "q4_k_s", "q3_k_m", "q5_k_m", "q6_k"])
 def test_decode_trace_vs_reference(llama, golden_dir, q):
     ctx = llama.Context(os.path.join(golden_dir, "tiny_%s.gguf" % q), n_ctx=48, max_seq=8)
     errs, row_errs = [], []
@@ -84,6 +85,10 @@ def test_decode_trace_vs_reference(llama, golden_dir, q):
     elif q == "q4_k_s":
         # same story: one flip in the second decode (4 layers of Q5_K attn_v / ffn_down) that the cache then carries along
         assert errs[0] < LOGIT_TOL_TYPICAL
+    elif q == "q5_k_m":
+        # and again: the LAST row of the first decode flips (0.017; the same value with the tensor-core and the dp4a kernels, zero in
+        # exact mode), its cache cell carries it into every later decode.  The other six rows of that decode are exact.
+        assert np.sort(row_errs[0])[-2] < LOGIT_TOL_TYPICAL
     else:
         assert np.median(errs) < LOGIT_TOL_TYPICAL
     ctx.close()

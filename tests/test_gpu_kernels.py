@@ -317,11 +317,12 @@ def test_prologue_fused_gemv_vs_oracle(lib, oracle, pro, b):
     lib.L.pib_weight_free(h)
 
 
-def test_q3_k_embedding_rows_bit_exact(lib, golden_dir):
-    # token_embd of a Q3_K_M file is Q3_K: get_rows must return dequantize_row_q3_K's bits
-    g = np.load(os.path.join(golden_dir, "kernels_q3k.npz"))
+@pytest.mark.parametrize("wt,fname", [(op.TYPE_Q3_K, "kernels_q3k.npz"), (op.TYPE_Q5_K, "kernels_q5k.npz"), (op.TYPE_Q6_K, "kernels_q6k.npz")])
+def test_k_quant_embedding_rows_bit_exact(lib, golden_dir, wt, fname):
+    # token_embd of Q3_K_M / Q5_K_M / Q6_K files: get_rows must return the bits of the reference's dequantize_row_q{3,5,6}_K
+    g = np.load(os.path.join(golden_dir, fname))
     K = g["x"].shape[1]
-    h = lib.weight_upload(op.TYPE_Q3_K, g["w"], K)
+    h = lib.weight_upload(wt, g["w"], K)
     ids = np.array([3, 0, 11, 3], dtype=np.int32)
     got = lib.get_rows(h, ids, K)
     assert np.array_equal(got.view(np.uint32), g["deq"][ids].view(np.uint32))

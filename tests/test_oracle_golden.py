@@ -93,7 +93,7 @@ def _replay(oracle, golden_dir, model_file, stem, n_ctx=48, max_seq=8, check_log
 
 
 # q4_k_m / q4_k_s / q3_k_m: files as the reference's quantize mixes them (Q3_K, Q4_K, Q5_K, Q6_K tensors side by side)
-@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m", "q4_k_s", "q3_k_m"])
+@pytest.mark.parametrize("q", ["q8_0", "q4_0", "q4_k", "falcon_q4_0", "falcon40_q8_0", "q4_k_m", "q4_k_s", "q3_k_m", "q5_k_m", "q6_k"])
 def test_decode_trace_matches_reference_bit_exact(oracle, golden_dir, q):
     # R2/R6/R7/R8 + K1..K9: multi-sequence batches, tree-speculation masks, no-slot failure (-1), GQA
     n_dec, n_kv = _replay(oracle, golden_dir, "tiny_%s.gguf" % q, "decode_%s" % q)

@@ -150,7 +150,7 @@ def build(args):
     if args.quant != "f32":
         q = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle", "_ref", "quantize")
         # q4_k_m / q4_k_s: the reference's mixed recipes (no --pure): output.weight Q6_K, attn_v / ffn_down partly Q6_K resp. Q5_K
-        r = subprocess.run([q] + ([] if args.quant in ("q4_k_m", "q4_k_s", "q3_k_m") else ["--pure"]) + [args.out + ".f32.gguf", args.out, args.quant.upper()],
+        r = subprocess.run([q] + ([] if args.quant in ("q4_k_m", "q4_k_s", "q3_k_m", "q5_k_m") else ["--pure"]) + [args.out + ".f32.gguf", args.out, args.quant.upper()],
                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if r.returncode != 0:
             sys.stderr.write(r.stdout)
@@ -263,7 +263,7 @@ def main():
     ap.add_argument("--n-ff", type=int, default=1408)
     ap.add_argument("--n-vocab", type=int, default=32000)
     ap.add_argument("--n-ctx-train", type=int, default=2048)
-    ap.add_argument("--quant", default="q8_0", choices=["f32", "q8_0", "q4_0", "q4_k", "q4_k_m", "q4_k_s", "q3_k_m"])
+    ap.add_argument("--quant", default="q8_0", choices=["f32", "q8_0", "q4_0", "q4_k", "q4_k_m", "q4_k_s", "q3_k_m", "q5_k_m", "q6_k"])
     ap.add_argument("--flavour", default="iid", choices=["iid", "bigram"])
     ap.add_argument("--eps", type=float, default=0.25)
     ap.add_argument("--emb-scale", type=float, default=1.0)
