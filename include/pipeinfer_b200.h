@@ -33,8 +33,8 @@ extern "C" {
 #define PIB_TYPE_Q8_0  8
 #define PIB_TYPE_Q4_K 12
 #define PIB_TYPE_Q3_K 11   /* matmul + embedding rows (Q3_K_M files: token_embd, attn_q / attn_k, ffn_gate / ffn_up); activations as for Q4_K (Q8_K) */
-#define PIB_TYPE_Q5_K 13   /* matmul only (attn_v of 70B-class Q4_K_M files) */
-#define PIB_TYPE_Q6_K 14   /* matmul only (output.weight / attn_v / ffn_down of Q4_K_M files); activations as for Q4_K (Q8_K) */
+#define PIB_TYPE_Q5_K 13   /* matmul + embedding rows (Q4_K_S / Q5_K_M files); activations as for Q4_K (Q8_K) */
+#define PIB_TYPE_Q6_K 14   /* matmul + embedding rows (output.weight / attn_v / ffn_down of Q4_K_M files, Q6_K files); activations as for Q4_K (Q8_K) */
 
 #define PIB_MAX_BATCH 16          /* verification batch handled by the dequant-GEMV path (north_star: batch 1-16) */
 
