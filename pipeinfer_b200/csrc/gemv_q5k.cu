@@ -7,7 +7,8 @@
 //
 // Layout (weights.cu): per row and super-block 160 bytes {qs[128] low nibbles, qh[32] fifth bits} and the 16-byte header
 // {d, dmin, scales[12]} of Q4_K.  One warp per row, half a warp per super-block: lane = (64-value chunk j, eight byte
-// positions 8p..8p+7): two sub-blocks' worth of bytes assembled with SIMD-in-a-word logic, dp4a.
+// positions 8p..8p+7): two sub-blocks' worth of bytes assembled with SIMD-in-a-word logic, dp4a.  That was round 1's kernel (kept as
+// PIB_Q5K_TC=0); the default since round 2 is the tensor-core kernel on fragment-major records further down.
 #include "pib_common.cuh"
 
 #include <stdlib.h>

@@ -8,8 +8,8 @@
 // Layout (weights.cu): per row and super-block 192 bytes {ql[128] low nibbles, qh[64] two high bits} in the reference's
 // order, and a 32-byte header {int8 scales[16], fp16 d, pad}.  One warp per row; half a warp per super-block: lane =
 // (half j of the super-block, 4 positions l = 4p..4p+3) assembles the four groups' bytes with SIMD-in-a-word logic and
-// multiplies with dp4a.  This is the simple kernel of the type (HBM-bound, 30-40 % of peak): the lm_head pass of a Q4_K_M
-// model is 215 MB, the layers stay on the tensor-core kernels of their own types.
+// multiplies with dp4a.  That was round 1's kernel (30-40 % of the HBM peak; kept as PIB_Q6K_TC=0); the default since round 2 is the
+// tensor-core kernel on fragment-major records further down (0.90 of peak on the 215 MB lm_head of a 70B Q4_K_M model).
 #include "pib_common.cuh"
 
 #include <stdlib.h>
