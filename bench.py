@@ -189,6 +189,22 @@ def run_reference_sample(cfg_name, args, budget="small"):
                 raw={str(k): v for k, v in res.items()}, itl_est_s=full, fit_residual=resid)
 
 
+def head_layers(world, tshape, dshape, n_draft):
+    """How many of the target's layers the head GPU takes.  It also runs the draft, so it gets the share that evens out the work per
+    run: n_draft draft steps + L0 layers on the head against (L - L0) / (N - 1) layers on every other stage.  Costs from the shapes: a
+    target layer streams its weights at ~5 TB/s plus ~25 us of small kernels; a draft step is a chain of nine dependent kernels per
+    layer (~28 us) plus its bytes.  Returns (L0, the drafting of one run expressed in target layers)."""
+    def layer_bytes(e, h, hkv, ff, t):
+        return (e * (e + 2 * e // h * hkv) + e * e + 3 * e * ff) * ({Q4_K: 4.5, 2: 4.5, 8: 8.5}.get(t, 4.5) / 8.0)
+    L, E, H, HKV, FF, V, wt = tshape
+    dL, dE, dH, dHKV, dFF, dV, dwt = dshape
+    t_layer = layer_bytes(E, H, HKV, FF, wt) / 5.0e12 + 25e-6
+    t_draft = dL * (layer_bytes(dE, dH, dHKV, dFF, dwt) / 5.0e12 + 28e-6) + 60e-6
+    r = n_draft * t_draft / t_layer
+    l0 = int(round((L - r * (world - 1)) / world))
+    return max(1, min(L // world, l0)), r
+
+
 # --------------------------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
@@ -280,17 +296,7 @@ def main():
     t_load = time.time()
     head_share = args.head_share
     if head_share is None and world > 1:
-        # The head GPU also runs the draft, so it gets the share of the target's layers that evens out the work per run: n_draft draft
-        # steps + L0 layers on the head against (L - L0) / (N - 1) layers on every other stage.  Costs from the shapes: a target layer
-        # streams its weights at ~5 TB/s plus ~25 us of small kernels; a draft step is a chain of nine dependent kernels per layer (~28 us) plus its bytes.
-        def layer_bytes(e, h, hkv, ff, t):
-            return (e * (e + 2 * e // h * hkv) + e * e + 3 * e * ff) * ({Q4_K: 4.5, 2: 4.5, 8: 8.5}.get(t, 4.5) / 8.0)
-        dL, dE, dH, dHKV, dFF, dV, dwt = dshape
-        t_layer = layer_bytes(E, H, HKV, FF, wt) / 5.0e12 + 25e-6
-        t_draft = dL * (layer_bytes(dE, dH, dHKV, dFF, dwt) / 5.0e12 + 28e-6) + 60e-6
-        r = args.draft * t_draft / t_layer                                   # the drafting of one run, in target layers
-        l0 = int(round((L - r * (world - 1)) / world))
-        l0 = max(1, min(L // world, l0))
+        l0, r = head_layers(world, (L, E, H, HKV, FF, V, wt), dshape, args.draft)
         head_share = (l0 + 0.25) / L
         config["head_layers_rule"] = "draft work per run ~ %.1f target layers -> %d layer(s) on the head" % (r, l0)
     weights = [float(x) for x in args.layer_split.split(",")] if args.layer_split else pipeline.default_weights(world, head_share)
