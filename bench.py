@@ -266,7 +266,7 @@ def main():
                 "data": "synthetic", "config": config, "latency_p50_ms": None, "latency_mean_ms": 1000.0 * r["itl_est_s"],
                 "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": r["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                "raw": r["raw"], "wall_s": time.time() - t0}
+                "fit_residual": r.get("fit_residual"), "raw": r["raw"], "wall_s": time.time() - t0}
         print(json.dumps(line))
         return 0
 
