@@ -5,6 +5,8 @@
   python tests/sched_sim/explore.py sensitivity  tokens/s in the model when the draft step / the stage time / the agreement change,
                                                  under the reference policy and under PIB_SCHED_CHAIN=1
   python tests/sched_sim/explore.py scaling      1, 2, 4, 8 stages
+  python tests/sched_sim/explore.py round2       the same with round 2's constants (pass 9.39 ms + 0.34 ms per extra token, draft step 0.74 ms,
+                                                 policy chain2, balanced layer split) against round 2's measurements, and what would move them
 
 Every run also checks that the text is the greedy text.  Numbers are means over 6 prompts / model seeds.
 """
@@ -69,5 +71,24 @@ def scaling():
         print(line)
 
 
+MEASURED_R2 = {1: 157.3, 2: 213.6, 4: 244.8, 8: 260.6}          # profiles/r2_bench_70b_n*.json
+SPLITS_R2 = {1: (0, 0), 2: (30 / 80, 50 / 80), 4: (5 / 80, 27 / 80), 8: (1 / 80, 13 / 80)}
+
+
+def round2():
+    """round 2's engine in the model: a pass of 9.39 ms at one token + 0.343 ms per further token (profiles/r2_pass_breakdown.md),
+    a draft step of 0.74 ms of which 0.15 ms is host time, policy chain2, bench.py's balanced layer split"""
+    os.environ["PIB_SCHED_CHAIN"] = "2"
+    base = dict(draft_us=590)
+    for stages in (1, 2, 4, 8):
+        cfg = dict(base, n_stages=stages, stage_us=9390.0 / stages, stage_tok_us=343.0 / stages, head_frac=SPLITS_R2[stages][0], tail_frac=SPLITS_R2[stages][1])
+        band = lambda extra: "%5.1f..%5.1f" % tuple(mean_tps(dict(cfg, share_gpu0=sh, **extra), n_draft=3, max_spec_runs=stages + 1) for sh in (1.0, 0.0))
+        print("%d stage(s): measured %5.1f   model %s   draft step 0.35 ms %s   agreement 0.9 %s   both %s" %
+              (stages, MEASURED_R2[stages], band({}), band(dict(draft_us=200)), band(dict(agree=0.9)), band(dict(draft_us=200, agree=0.9))))
+    os.environ["PIB_SCHED_CHAIN"] = "0"
+    cfg = dict(base, n_stages=8, stage_us=9390.0 / 8, stage_tok_us=343.0 / 8)
+    print("plain pipelined decode, 8 stages: measured 105.3   model %5.1f" % mean_tps(cfg, mode="plain"))
+
+
 if __name__ == "__main__":
-    {"calibrate": calibrate, "sensitivity": sensitivity, "scaling": scaling}[sys.argv[1] if len(sys.argv) > 1 else "calibrate"]()
+    {"calibrate": calibrate, "sensitivity": sensitivity, "scaling": scaling, "round2": round2}[sys.argv[1] if len(sys.argv) > 1 else "calibrate"]()
